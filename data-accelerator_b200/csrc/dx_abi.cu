@@ -1,0 +1,189 @@
+// dx_abi.cu — extern "C" entry points of libdxgpu.so (see include/dxgpu.h).
+#include "dx_common.h"
+#include "dx_abi_types.h"
+#include "dx_decode_host.h"
+
+int dx_gen_device(dx_ctx* c, const dx_gen_params* g, int64_t first, int64_t n, uint8_t** bytes_out,
+                  int64_t* n_bytes_out, int64_t** offsets_out);
+
+// Every table handed across the ABI is a heap-allocated shared_ptr holder.
+struct TableHandle { DxTableP t; };
+static inline const DxTable* T(const dx_table* h) { return reinterpret_cast<const TableHandle*>(h)->t.get(); }
+dx_table* dx_wrap_table(const DxTableP& t) { return reinterpret_cast<dx_table*>(new TableHandle{t}); }
+DxTableP dx_unwrap_table(const dx_table* h) { return reinterpret_cast<const TableHandle*>(h)->t; }
+
+extern "C" {
+
+int dx_ctx_create(int device_ordinal, dx_ctx** out) {
+    if (!out) return DX_ERR_ARG;
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || device_ordinal < 0 || device_ordinal >= n) return DX_ERR_CUDA;
+    if (cudaSetDevice(device_ordinal) != cudaSuccess) return DX_ERR_CUDA;
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device_ordinal) != cudaSuccess) return DX_ERR_CUDA;
+    if (prop.major != 10) return DX_ERR_UNSUPPORTED;   // sm_100a binary only; no other code path exists
+    dx_ctx* c = new dx_ctx();
+    c->device = device_ordinal; c->pool.device = device_ordinal; c->sm_count = prop.multiProcessorCount;
+    if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return DX_ERR_CUDA; }
+    *out = c;
+    return DX_OK;
+}
+void dx_ctx_destroy(dx_ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    cudaStreamDestroy(c->stream);
+    delete c;
+}
+const char* dx_ctx_last_error(const dx_ctx* c) { return c ? c->last_error.c_str() : "null context"; }
+int dx_ctx_set_timing(dx_ctx* c, int enabled) { c->timing = enabled != 0; return DX_OK; }
+int dx_ctx_take_stage_ms(dx_ctx* c, const char* stage, double* total_ms, int64_t* samples) {
+    auto it = c->stage_ms.find(stage);
+    double t = 0; int64_t n = 0;
+    if (it != c->stage_ms.end()) { for (float v : it->second) t += v; n = (int64_t)it->second.size(); it->second.clear(); }
+    if (total_ms) *total_ms = t;
+    if (samples) *samples = n;
+    return DX_OK;
+}
+int64_t dx_ctx_take_launches(dx_ctx* c) {
+    int64_t n = 0;
+    for (auto& kv : c->launches) { n += kv.second; kv.second = 0; }
+    return n;
+}
+void* dx_ctx_stream(dx_ctx* c) { return reinterpret_cast<void*>(c->stream); }
+int dx_ctx_synchronize(dx_ctx* c) { DX_CUDA(c, cudaStreamSynchronize(c->stream)); return DX_OK; }
+int dx_dev_alloc(dx_ctx* c, int64_t bytes, void** out) {
+    if (bytes < 0 || !out) return c->set_error(DX_ERR_ARG, "dx_dev_alloc: bad arguments");
+    cudaSetDevice(c->device);
+    void* p = c->pool.alloc((size_t)bytes + 64);
+    if (!p) return c->set_error(DX_ERR_CUDA, "device allocation failed");
+    *out = p; return DX_OK;
+}
+void dx_dev_free(dx_ctx* c, void* p) { if (c && p) c->pool.release(p); }
+int dx_copy_h2d(dx_ctx* c, void* dst, const void* src, int64_t bytes) {
+    DX_CUDA(c, cudaMemcpyAsync(dst, src, (size_t)bytes, cudaMemcpyHostToDevice, c->stream));
+    DX_CUDA(c, cudaStreamSynchronize(c->stream)); return DX_OK;
+}
+int dx_copy_d2h(dx_ctx* c, void* dst, const void* src, int64_t bytes) {
+    DX_CUDA(c, cudaMemcpyAsync(dst, src, (size_t)bytes, cudaMemcpyDeviceToHost, c->stream));
+    DX_CUDA(c, cudaStreamSynchronize(c->stream)); return DX_OK;
+}
+
+// ---- decoder -------------------------------------------------------------------------------
+int dx_decoder_create(dx_ctx* c, const char* schema_json, dx_decoder** out) {
+    if (!c || !schema_json || !out) return DX_ERR_ARG;
+    cudaSetDevice(c->device);
+    dx_decoder* d = new dx_decoder();
+    int rc = d->init(c, schema_json);
+    if (rc) { delete d; return rc; }
+    *out = d; return DX_OK;
+}
+void dx_decoder_destroy(dx_decoder* d) { delete d; }
+int dx_decoder_decode(dx_decoder* d, const uint8_t* json, int64_t n_bytes, const int64_t* offsets,
+                      int64_t n_events, int memory_kind, dx_table** out) {
+    if (!d || !out || (n_bytes > 0 && !json)) return DX_ERR_ARG;
+    cudaSetDevice(d->ctx->device);
+    DxTableP t;
+    int rc = (memory_kind == DX_MEM_DEVICE) ? d->decode_device(json, n_bytes, offsets, n_events, &t)
+                                            : d->decode_host(json, n_bytes, offsets, n_events, &t);
+    if (rc) return rc;
+    *out = dx_wrap_table(t);
+    return DX_OK;
+}
+int dx_decoder_stats(const dx_decoder* d, int64_t* rows, int64_t* null_rows, int64_t* fast_rows) {
+    if (rows) *rows = (int64_t)d->last_stats.rows;
+    if (null_rows) *null_rows = (int64_t)d->last_stats.null_rows;
+    if (fast_rows) *fast_rows = (int64_t)d->last_stats.fast_rows;
+    return DX_OK;
+}
+
+// ---- tables --------------------------------------------------------------------------------
+int64_t dx_table_num_rows(const dx_table* h) { return T(h)->n_rows; }
+int dx_table_num_columns(const dx_table* h) { return (int)T(h)->cols.size(); }
+const char* dx_table_column_name(const dx_table* h, int col) {
+    const DxTable* t = T(h);
+    return (col >= 0 && col < (int)t->cols.size()) ? t->cols[col].name.c_str() : nullptr;
+}
+int dx_table_column_type(const dx_table* h, int col) {
+    const DxTable* t = T(h);
+    return (col >= 0 && col < (int)t->cols.size()) ? t->cols[col].type : 0;
+}
+int dx_table_find_column(const dx_table* h, const char* name) { return T(h)->find(name); }
+int dx_table_flag_words(const dx_table* h, int col) {
+    const DxTable* t = T(h);
+    return (col >= 0 && col < (int)t->cols.size()) ? t->cols[col].flag_words : 0;
+}
+int dx_table_column_device(const dx_table* h, int col, const void** data, const void** vmask, int* vw, int* vb) {
+    const DxTable* t = T(h);
+    if (col < 0 || col >= (int)t->cols.size()) return t->ctx->set_error(DX_ERR_ARG, "column index out of range");
+    const DxColumn& c = t->cols[col];
+    if (data) *data = c.data ? c.data->p : nullptr;
+    if (vmask) *vmask = c.vmask ? c.vmask->p : nullptr;
+    if (vw) *vw = c.vwidth;
+    if (vb) *vb = c.vbit;
+    return DX_OK;
+}
+
+int dx_table_column_to_host(const dx_table* h, int col, void* data, uint8_t* valid) {
+    const DxTable* t = T(h);
+    dx_ctx* c = t->ctx;
+    if (col < 0 || col >= (int)t->cols.size()) return c->set_error(DX_ERR_ARG, "column index out of range");
+    cudaSetDevice(c->device);
+    const DxColumn& k = t->cols[col];
+    const int64_t n = t->n_rows;
+    size_t w = (k.type == DX_T_FLAGS) ? (size_t)k.flag_words * 4 : (size_t)dx_type_width(k.type);
+    if (data && n > 0) {
+        if (k.data) DX_CUDA(c, cudaMemcpyAsync(data, k.data->p, (size_t)n * w, cudaMemcpyDeviceToHost, c->stream));
+        else {
+            // constant column: replicate on the host side of the ABI (sink hand-off convenience)
+            for (int64_t i = 0; i < n; i++) {
+                if (k.type == DX_T_F64) reinterpret_cast<double*>(data)[i] = k.const_f;
+                else if (k.type == DX_T_STR) reinterpret_cast<int32_t*>(data)[i] = (int32_t)k.const_i;
+                else reinterpret_cast<int64_t*>(data)[i] = k.const_i;
+            }
+        }
+    }
+    if (valid && n > 0) {
+        if (k.all_null) memset(valid, 0, (size_t)n);
+        else if (!k.vmask) memset(valid, 1, (size_t)n);
+        else {
+            std::vector<uint8_t> m((size_t)n * k.vwidth);
+            DX_CUDA(c, cudaMemcpyAsync(m.data(), k.vmask->p, m.size(), cudaMemcpyDeviceToHost, c->stream));
+            DX_CUDA(c, cudaStreamSynchronize(c->stream));
+            for (int64_t i = 0; i < n; i++) {
+                uint32_t v = (k.vwidth == 1) ? m[i] : reinterpret_cast<const uint32_t*>(m.data())[i];
+                valid[i] = (v >> k.vbit) & 1u;
+            }
+        }
+    }
+    DX_CUDA(c, cudaStreamSynchronize(c->stream));
+    return DX_OK;
+}
+
+int dx_table_dict_size(const dx_table* h, int col, int64_t* n_codes) {
+    const DxTable* t = T(h);
+    if (col < 0 || col >= (int)t->cols.size() || !t->cols[col].dict) return t->ctx->set_error(DX_ERR_ARG, "not a dictionary column");
+    cudaSetDevice(t->ctx->device);
+    int rc = t->cols[col].dict->sync_to_host();
+    if (rc) return rc;
+    *n_codes = (int64_t)t->cols[col].dict->host_strings.size();
+    return DX_OK;
+}
+int dx_table_dict_string(const dx_table* h, int col, int64_t code, const char** bytes, int64_t* len) {
+    const DxTable* t = T(h);
+    if (col < 0 || col >= (int)t->cols.size() || !t->cols[col].dict) return t->ctx->set_error(DX_ERR_ARG, "not a dictionary column");
+    const auto& hs = t->cols[col].dict->host_strings;
+    if (code < 0 || code >= (int64_t)hs.size()) return t->ctx->set_error(DX_ERR_ARG, "dictionary code out of range (call dx_table_dict_size first)");
+    *bytes = hs[(size_t)code].data(); *len = (int64_t)hs[(size_t)code].size();
+    return DX_OK;
+}
+void dx_table_release(dx_table* h) { delete reinterpret_cast<TableHandle*>(h); }
+
+// ---- generator -----------------------------------------------------------------------------
+int dx_gen_events(dx_ctx* c, const dx_gen_params* p, int64_t first, int64_t n, uint8_t** bytes, int64_t* n_bytes, int64_t** offsets) {
+    if (!c || !p || !bytes || !n_bytes) return DX_ERR_ARG;
+    cudaSetDevice(c->device);
+    return dx_gen_device(c, p, first, n, bytes, n_bytes, offsets);
+}
+
+} // extern "C"

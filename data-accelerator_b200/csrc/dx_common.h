@@ -1,0 +1,181 @@
+// dx_common.h — shared host/device definitions for libdxgpu (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+#include <string>
+#include <vector>
+#include <map>
+#include <memory>
+#include <mutex>
+
+#define DX_OK 0
+#define DX_ERR_CUDA 1
+#define DX_ERR_ARG 2
+#define DX_ERR_UNSUPPORTED 3   // construct outside the supported subset: fail loudly, never a CPU path
+#define DX_ERR_PARSE 4
+#define DX_ERR_CAPACITY 5
+#define DX_ERR_STATE 6
+
+// column physical types
+enum DxType : int32_t {
+    DX_T_I64 = 1,   // long/int/short/byte
+    DX_T_F64 = 2,   // double/float
+    DX_T_STR = 3,   // int32 dictionary code
+    DX_T_BOOL = 4,  // stored as int64 0/1
+    DX_T_TS = 5,    // timestamp, int64 microseconds since epoch (UTC)
+    DX_T_FLAGS = 6, // rule flag bitmap: words_per_row uint32 per row
+    DX_T_NULL = 7,  // untyped NULL literal column
+};
+
+static inline int dx_type_width(int t) { return t == DX_T_STR ? 4 : 8; }
+
+struct dx_ctx;
+
+// Device memory pool: cudaMalloc'ed blocks recycled by size class so a steady-state
+// micro-batch loop performs no allocation calls.
+struct DxPool {
+    std::multimap<size_t, void*> free_blocks;
+    std::map<void*, size_t> live;
+    size_t bytes_reserved = 0;
+    std::mutex mu;
+    int device = 0;
+    void* alloc(size_t bytes);
+    void release(void* p);
+    void trim();
+    ~DxPool();
+};
+
+struct dx_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    DxPool pool;
+    std::string last_error;
+    int sm_count = 148;
+    // stage timing (CUDA events on this ctx's stream)
+    bool timing = false;
+    std::map<std::string, std::vector<float>> stage_ms;
+    std::map<std::string, long long> launches;
+    int set_error(int code, const std::string& msg) { last_error = msg; return code; }
+};
+
+#define DX_CUDA(ctx, call)                                                                      \
+    do {                                                                                        \
+        cudaError_t _e = (call);                                                                \
+        if (_e != cudaSuccess) {                                                                \
+            char _b[512];                                                                       \
+            snprintf(_b, sizeof _b, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(_e),    \
+                     __FILE__, __LINE__);                                                       \
+            return (ctx)->set_error(DX_ERR_CUDA, _b);                                           \
+        }                                                                                       \
+    } while (0)
+
+// RAII handle for pooled device memory.
+struct DevBuf {
+    dx_ctx* ctx = nullptr;
+    void* p = nullptr;
+    size_t bytes = 0;
+    DevBuf() {}
+    DevBuf(dx_ctx* c, size_t n) : ctx(c), bytes(n) { p = n ? c->pool.alloc(n) : nullptr; }
+    DevBuf(const DevBuf&) = delete;
+    DevBuf& operator=(const DevBuf&) = delete;
+    DevBuf(DevBuf&& o) noexcept { ctx = o.ctx; p = o.p; bytes = o.bytes; o.p = nullptr; o.bytes = 0; }
+    DevBuf& operator=(DevBuf&& o) noexcept {
+        if (this != &o) { reset(); ctx = o.ctx; p = o.p; bytes = o.bytes; o.p = nullptr; o.bytes = 0; }
+        return *this;
+    }
+    void reset() { if (p && ctx) ctx->pool.release(p); p = nullptr; bytes = 0; }
+    ~DevBuf() { reset(); }
+    template <typename T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+typedef std::shared_ptr<DevBuf> DevBufP;
+static inline DevBufP make_buf(dx_ctx* c, size_t n) { return std::make_shared<DevBuf>(c, n); }
+
+// ---------------------------------------------------------------------------------------
+// String dictionary (one per string column lineage).  Device-resident open-addressing
+// table; codes are dense int32 assigned on first sight.  Strings of <= 16 bytes are
+// identified exactly by their packed bytes (w0,w1,len); longer ones by a 64-bit hash plus
+// a byte compare against the heap.
+// ---------------------------------------------------------------------------------------
+struct DictSlot {          // 32 bytes = one L2 sector
+    uint64_t w0, w1;
+    uint32_t len;
+    uint32_t heap_off;
+    int32_t code;
+    uint32_t state;        // 0 empty, 1 being filled, 2 ready
+};
+struct DictDev {
+    DictSlot* slots;
+    uint32_t cap_mask;     // capacity - 1 (power of two)
+    uint32_t max_codes;
+    uint8_t* heap;
+    uint32_t heap_cap;
+    uint32_t* counters;    // [0] = n_codes, [1] = heap_used, [2] = overflow flag
+    uint32_t* code_off;    // [max_codes]
+    uint32_t* code_len;    // [max_codes]
+};
+struct DxDict {
+    dx_ctx* ctx;
+    DictDev dev;
+    DevBuf slots, heap, counters, code_off, code_len;
+    // host mirror, refreshed on demand
+    std::vector<std::string> host_strings;
+    int init(dx_ctx* c, uint32_t capacity_pow2, uint32_t heap_bytes);
+    int insert_host(const std::string& s, int32_t* code_out);   // pre-seed literals
+    int sync_to_host();                                          // pulls new entries
+    int lookup_host(const std::string& s) const;                 // -1 if absent (after sync)
+};
+typedef std::shared_ptr<DxDict> DxDictP;
+
+// ---------------------------------------------------------------------------------------
+// Device-resident columnar table.  A column's validity is bit `vbit` of the per-row mask
+// array `vmask` (element width vwidth bytes); several columns may share one mask array
+// (the decoder writes one byte per row holding all leaf bits) and forwarded columns keep
+// pointing at their producer's buffers (zero copy).
+// ---------------------------------------------------------------------------------------
+struct DxColumn {
+    std::string name;        // dotted path for decoded leaves, alias for derived columns
+    int32_t type = 0;
+    DevBufP data;            // null => constant column
+    DevBufP vmask;           // null => never NULL (or always NULL if all_null)
+    int32_t vwidth = 0;      // 1 or 4
+    int32_t vbit = 0;
+    bool is_const = false;
+    bool all_null = false;
+    int64_t const_i = 0;     // I64/BOOL/TS/STR(code) constant
+    double const_f = 0;
+    std::string const_s;     // STR constant text (also entered into dict when one is attached)
+    DxDictP dict;            // STR columns
+    int32_t flag_words = 0;  // FLAGS columns: uint32 words per row
+    std::shared_ptr<void> aux; // FLAGS: the static rule table
+};
+
+struct DxTable {
+    dx_ctx* ctx = nullptr;
+    std::string name;
+    int64_t n_rows = 0;
+    std::vector<DxColumn> cols;
+    int find(const std::string& n) const {
+        for (size_t i = 0; i < cols.size(); i++) if (cols[i].name == n) return (int)i;
+        return -1;
+    }
+};
+typedef std::shared_ptr<DxTable> DxTableP;
+
+// stage timing helper
+struct StageTimer {
+    dx_ctx* ctx; const char* name; cudaEvent_t a = nullptr, b = nullptr;
+    StageTimer(dx_ctx* c, const char* n) : ctx(c), name(n) {
+        if (ctx->timing) { cudaEventCreate(&a); cudaEventCreate(&b); cudaEventRecord(a, ctx->stream); }
+    }
+    void stop() {
+        if (ctx->timing && a) {
+            cudaEventRecord(b, ctx->stream); cudaEventSynchronize(b);
+            float ms = 0; cudaEventElapsedTime(&ms, a, b);
+            ctx->stage_ms[name].push_back(ms);
+            cudaEventDestroy(a); cudaEventDestroy(b); a = b = nullptr;
+        }
+    }
+    ~StageTimer() { stop(); }
+};

@@ -1,0 +1,122 @@
+// dx_core.cu — context, device memory pool, string dictionary host operations.
+#include "dx_decode.cuh"
+
+// ------------------------------- pool ---------------------------------------------------
+static size_t round_size(size_t n) {
+    // size classes: next multiple of 1/8 of the leading power of two (<= 12.5 % slack), min 512 B
+    if (n < 512) return 512;
+    size_t p = 1; while ((p << 1) <= n) p <<= 1;
+    size_t step = p >> 3;
+    return (n + step - 1) / step * step;
+}
+
+void* DxPool::alloc(size_t bytes) {
+    size_t sz = round_size(bytes);
+    std::lock_guard<std::mutex> g(mu);
+    auto it = free_blocks.lower_bound(sz);
+    if (it != free_blocks.end() && it->first <= sz + sz / 4) {
+        void* p = it->second; size_t s = it->first;
+        free_blocks.erase(it); live[p] = s;
+        return p;
+    }
+    void* p = nullptr;
+    cudaError_t e = cudaMalloc(&p, sz);
+    if (e != cudaSuccess) {
+        // release cached blocks and retry once
+        for (auto& kv : free_blocks) { cudaFree(kv.second); bytes_reserved -= kv.first; }
+        free_blocks.clear();
+        cudaGetLastError();
+        e = cudaMalloc(&p, sz);
+        if (e != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    }
+    bytes_reserved += sz;
+    live[p] = sz;
+    return p;
+}
+void DxPool::release(void* p) {
+    if (!p) return;
+    std::lock_guard<std::mutex> g(mu);
+    auto it = live.find(p);
+    if (it == live.end()) return;
+    free_blocks.emplace(it->second, p);
+    live.erase(it);
+}
+void DxPool::trim() {
+    std::lock_guard<std::mutex> g(mu);
+    for (auto& kv : free_blocks) { cudaFree(kv.second); bytes_reserved -= kv.first; }
+    free_blocks.clear();
+}
+DxPool::~DxPool() {
+    for (auto& kv : free_blocks) cudaFree(kv.second);
+    for (auto& kv : live) cudaFree(kv.first);
+}
+
+// ------------------------------- dictionary ---------------------------------------------
+__global__ void dict_insert_one(DictDev d, const uint8_t* bytes, uint32_t len, int32_t* code_out, unsigned long long* err) {
+    uint64_t w0, w1; dict_pack(bytes, len, w0, w1);
+    *code_out = dict_get_or_insert(d, w0, w1, len, bytes, err);
+}
+
+int DxDict::init(dx_ctx* c, uint32_t capacity_pow2, uint32_t heap_bytes) {
+    ctx = c;
+    uint32_t cap = 16; while (cap < capacity_pow2) cap <<= 1;
+    slots = DevBuf(c, (size_t)cap * sizeof(DictSlot));
+    heap = DevBuf(c, heap_bytes);
+    counters = DevBuf(c, 64);
+    uint32_t max_codes = cap / 2;
+    code_off = DevBuf(c, (size_t)max_codes * 4);
+    code_len = DevBuf(c, (size_t)max_codes * 4);
+    if (!slots.p || !heap.p || !counters.p || !code_off.p || !code_len.p) return c->set_error(DX_ERR_CUDA, "dictionary allocation failed");
+    DX_CUDA(c, cudaMemsetAsync(slots.p, 0, (size_t)cap * sizeof(DictSlot), c->stream));
+    DX_CUDA(c, cudaMemsetAsync(counters.p, 0, 64, c->stream));
+    dev.slots = slots.as<DictSlot>(); dev.cap_mask = cap - 1; dev.max_codes = max_codes;
+    dev.heap = heap.as<uint8_t>(); dev.heap_cap = heap_bytes;
+    dev.counters = counters.as<uint32_t>();
+    dev.code_off = code_off.as<uint32_t>(); dev.code_len = code_len.as<uint32_t>();
+    return DX_OK;
+}
+
+int DxDict::insert_host(const std::string& s, int32_t* code_out) {
+    dx_ctx* c = ctx;
+    DevBuf tmp(c, s.size() + 32);
+    uint8_t* d = tmp.as<uint8_t>();
+    // layout: [0,8) err flags, [8,12) code, [16, ...) bytes
+    DX_CUDA(c, cudaMemsetAsync(d, 0, 16, c->stream));
+    if (!s.empty()) DX_CUDA(c, cudaMemcpyAsync(d + 16, s.data(), s.size(), cudaMemcpyHostToDevice, c->stream));
+    dict_insert_one<<<1, 1, 0, c->stream>>>(dev, d + 16, (uint32_t)s.size(), reinterpret_cast<int32_t*>(d + 8),
+                                            reinterpret_cast<unsigned long long*>(d));
+    unsigned long long err = 0; int32_t code = -1;
+    DX_CUDA(c, cudaMemcpyAsync(&err, d, 8, cudaMemcpyDeviceToHost, c->stream));
+    DX_CUDA(c, cudaMemcpyAsync(&code, d + 8, 4, cudaMemcpyDeviceToHost, c->stream));
+    DX_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (err || code < 0) return c->set_error(DX_ERR_CAPACITY, "string dictionary overflow");
+    if (code_out) *code_out = code;
+    return DX_OK;
+}
+
+int DxDict::sync_to_host() {
+    dx_ctx* c = ctx;
+    uint32_t cnt[4] = {0, 0, 0, 0};
+    DX_CUDA(c, cudaMemcpyAsync(cnt, counters.p, 16, cudaMemcpyDeviceToHost, c->stream));
+    DX_CUDA(c, cudaStreamSynchronize(c->stream));
+    uint32_t n = cnt[0] < dev.max_codes ? cnt[0] : dev.max_codes;
+    size_t have = host_strings.size();
+    if (n <= have) return DX_OK;
+    std::vector<uint32_t> off(n - have), len(n - have);
+    DX_CUDA(c, cudaMemcpyAsync(off.data(), dev.code_off + have, (n - have) * 4, cudaMemcpyDeviceToHost, c->stream));
+    DX_CUDA(c, cudaMemcpyAsync(len.data(), dev.code_len + have, (n - have) * 4, cudaMemcpyDeviceToHost, c->stream));
+    uint32_t heap_used = cnt[1] < dev.heap_cap ? cnt[1] : dev.heap_cap;
+    std::vector<uint8_t> hb(heap_used + 1);
+    if (heap_used) DX_CUDA(c, cudaMemcpyAsync(hb.data(), dev.heap, heap_used, cudaMemcpyDeviceToHost, c->stream));
+    DX_CUDA(c, cudaStreamSynchronize(c->stream));
+    for (size_t i = 0; i < n - have; i++) {
+        if ((size_t)off[i] + len[i] > heap_used) return c->set_error(DX_ERR_STATE, "dictionary heap out of sync");
+        host_strings.emplace_back(reinterpret_cast<const char*>(hb.data()) + off[i], len[i]);
+    }
+    return DX_OK;
+}
+
+int DxDict::lookup_host(const std::string& s) const {
+    for (size_t i = 0; i < host_strings.size(); i++) if (host_strings[i] == s) return (int)i;
+    return -1;
+}

@@ -1,0 +1,631 @@
+// dx_decode.cu — K1: NDJSON / offset-framed JSON events -> columnar buffers (sm_100a).
+//
+// Replaces from_json(inputNormalizerUdf(Raw), rawBlockSchema) in project()
+// (reference: datax/processor/CommonProcessorFactory.scala:90-103, schema from
+// datax/input/SchemaFile.scala:22-34) for the supported leaf types.
+//
+// Shape of the kernel (one persistent CTA loop, several CTAs per SM so that one CTA's bulk
+// load overlaps another's parsing):
+//   1. tile t (dynamic index from an atomic counter) = 32 KiB of the byte stream plus an
+//      overlap; moved global->shared with cp.async.bulk (TMA bulk copy) completing on an mbarrier;
+//   2. warp-parallel structural scan: every lane classifies 16 bytes at a time, newline masks
+//      are counted and prefix-summed with warp shuffles -> list of record starts in the tile;
+//   3. the tile's record count is published and the tile's first row index obtained by a
+//      decoupled look-back over earlier tiles (single pass over the input, no pre-count pass);
+//   4. one thread per record: schema-ordered template fast path (word-wise literal compare,
+//      digit loops) with fall-through to a general Spark-2.4-conformant parser in the same
+//      kernel; lanes hold consecutive rows, so every column store is a coalesced 128/256 B line.
+#include "dx_decode.cuh"
+#include "dx_json.h"
+#include "dx_decode_host.h"
+
+#define K1_T 32768          // tile bytes
+#define K1_OVL 2048         // overlap bytes past the tile (records starting in the tile may end here)
+#define K1_PAD 32
+#define K1_NT 256           // threads per CTA
+#define K1_SC 1024          // record starts held in shared memory per round
+
+// ------------------------------- PTX wrappers ------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+
+// ------------------------------- shared-memory readers ---------------------------------
+__device__ __forceinline__ uint32_t ld32u(const uint8_t* buf, uint32_t pos) {
+    const uint32_t* w = reinterpret_cast<const uint32_t*>(buf + (pos & ~3u));
+    return __funnelshift_r(w[0], w[1], (pos & 3u) << 3);
+}
+struct SRd {
+    const uint8_t* buf; uint32_t pos; uint32_t word;
+    __device__ __forceinline__ void seek(uint32_t p) { pos = p; word = *reinterpret_cast<const uint32_t*>(buf + (p & ~3u)); }
+    __device__ __forceinline__ uint32_t peek() const { return (word >> ((pos & 3u) << 3)) & 0xffu; }
+    __device__ __forceinline__ void adv() { pos++; if ((pos & 3u) == 0) word = *reinterpret_cast<const uint32_t*>(buf + pos); }
+};
+
+// Template fast path.  Accepts exactly: the schema-ordered compact serialisation with plain
+// integer / short decimal / escape-free string values.  Anything else -> false (general path).
+__device__ bool fast_record(const uint8_t* buf, uint32_t pos, uint32_t end, const DSeg* segs, int n_segs,
+                            const uint32_t* lits, RowSink& o) {
+    o.valid = 0;
+    for (int si = 0; si < n_segs; si++) {
+        const DSeg sg = segs[si];
+        const uint32_t* lw = lits + (sg.lit_off >> 2);
+        const uint32_t L = sg.lit_len;
+        uint32_t k = 0, diff = 0;
+        for (; k + 4 <= L; k += 4) diff |= ld32u(buf, pos + k) ^ lw[k >> 2];
+        if (L & 3u) diff |= (ld32u(buf, pos + k) ^ lw[k >> 2]) & ((1u << ((L & 3u) << 3)) - 1u);
+        if (diff) return false;
+        pos += L;
+        if (sg.type == 0) break;
+        SRd r; r.buf = buf; r.seek(pos);
+        uint32_t c = r.peek();
+        switch (sg.type) {
+        case DX_T_I64: {
+            bool neg = false;
+            if (c == '-') { neg = true; r.adv(); c = r.peek(); }
+            uint32_t d = c - '0';
+            if (d > 9) return false;
+            unsigned long long v = d; int nd = 1;
+            r.adv(); c = r.peek();
+            if (d == 0 && (c - '0') <= 9u) return false;
+            while ((d = c - '0') <= 9u) {
+                v = v * 10 + d; r.adv(); c = r.peek();
+                if (++nd > 18) return false;
+            }
+            sink_i64(o, sg.leaf, neg ? -(long long)v : (long long)v);
+            break;
+        }
+        case DX_T_F64: {
+            bool neg = false;
+            if (c == '-') { neg = true; r.adv(); c = r.peek(); }
+            uint32_t d = c - '0';
+            if (d > 9) return false;
+            unsigned long long m = d; int nd = 1, nf = 0;
+            r.adv(); c = r.peek();
+            if (d == 0 && (c - '0') <= 9u) return false;
+            while ((d = c - '0') <= 9u) { m = m * 10 + d; nd++; r.adv(); c = r.peek(); if (nd > 15) return false; }
+            bool is_int = true;
+            if (c == '.') {
+                is_int = false;
+                r.adv(); c = r.peek();
+                if ((c - '0') > 9u) return false;
+                while ((d = c - '0') <= 9u) { m = m * 10 + d; nd++; nf++; r.adv(); c = r.peek(); if (nd > 15) return false; }
+            }
+            if (c == 'e' || c == 'E') return false;
+            double x;
+            if (is_int) x = (double)(neg ? -(long long)m : (long long)m);
+            else { x = (double)m / dx_pow10_exact[nf]; if (neg) x = -x; }
+            sink_f64(o, sg.leaf, x);
+            break;
+        }
+        case DX_T_BOOL: {
+            uint32_t w = ld32u(buf, pos);
+            if (w == 0x65757274u) { sink_i64(o, sg.leaf, 1); r.seek(pos + 4); }               // "true"
+            else if (w == 0x736c6166u && buf[pos + 4] == 'e') { sink_i64(o, sg.leaf, 0); r.seek(pos + 5); } // "false"
+            else return false;
+            break;
+        }
+        case DX_T_STR: {
+            if (c != '"') return false;
+            r.adv();
+            const uint32_t s0 = r.pos;
+            uint64_t w0 = 0, w1 = 0; uint32_t len = 0;
+            for (;;) {
+                c = r.peek();
+                if (c == '"') break;
+                if (c < 0x20u || c == '\\') return false;
+                if (len < 8) w0 |= (uint64_t)c << (len << 3);
+                else if (len < 16) w1 |= (uint64_t)c << ((len - 8) << 3);
+                len++; r.adv();
+                if (r.pos >= end) return false;
+            }
+            if (len > 16) dict_pack(buf + s0, len, w0, w1);
+            int32_t code = dict_get_or_insert(o.a->dicts[sg.leaf], w0, w1, len, buf + s0, &o.a->stats->flags);
+            sink_code(o, sg.leaf, code);
+            r.adv();
+            break;
+        }
+        default: return false;
+        }
+        pos = r.pos;
+    }
+    return pos == end;
+}
+
+__device__ __forceinline__ unsigned long long ld_state(const unsigned long long* p) {
+    return *reinterpret_cast<const volatile unsigned long long*>(p);
+}
+
+// Decoupled look-back over per-tile record counts; executed by one full warp.
+__device__ long long tile_lookback(unsigned long long* state, long long tile, unsigned long long my_count) {
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    const unsigned long long VAL = (1ull << 62) - 1;
+    if (tile == 0) {
+        if (lane == 0) atomicExch(&state[0], (2ull << 62) | my_count);
+        return 0;
+    }
+    if (lane == 0) atomicExch(&state[tile], (1ull << 62) | my_count);
+    long long excl = 0;
+    long long j = tile - 1;
+    for (;;) {
+        long long idx = j - lane;
+        unsigned long long v;
+        do {
+            v = (idx >= 0) ? ld_state(&state[idx]) : (2ull << 62);
+        } while (__any_sync(full, (v >> 62) == 0));
+        unsigned pmask = __ballot_sync(full, (v >> 62) == 2);
+        int first = pmask ? (__ffs(pmask) - 1) : 31;
+        long long contrib = (lane <= first) ? (long long)(v & VAL) : 0;
+        for (int s = 16; s > 0; s >>= 1) contrib += __shfl_xor_sync(full, contrib, s);
+        excl += contrib;
+        if (pmask) break;
+        j -= 32;
+    }
+    if (lane == 0) atomicExch(&state[tile], (2ull << 62) | (unsigned long long)(excl + (long long)my_count));
+    return excl;
+}
+
+__global__ void __launch_bounds__(K1_NT) k1_decode(const __grid_constant__ DecodeArgs a) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    uint8_t* buf = smem;                                                  // K1_T + K1_OVL + K1_PAD
+    uint16_t* s_starts = reinterpret_cast<uint16_t*>(smem + K1_T + K1_OVL + K1_PAD);   // K1_SC + 2
+    uint32_t* s_lits = reinterpret_cast<uint32_t*>(s_starts + K1_SC + 2);  // DX_LITS_BYTES
+    DSeg* s_segs = reinterpret_cast<DSeg*>(s_lits + DX_LITS_BYTES / 4);    // DX_MAX_SEGS
+    __shared__ uint64_t s_bar;
+    __shared__ long long s_tile;
+    __shared__ long long s_rowbase;
+    __shared__ uint32_t s_wtot[K1_NT / 32];
+    __shared__ long long s_r0;
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const DSchemaDev* S = a.schema;
+    const int n_segs = S->n_segs;
+    for (int i = tid; i < DX_LITS_BYTES / 4; i += K1_NT) s_lits[i] = S->lits[i];
+    for (int i = tid; i < DX_MAX_SEGS; i += K1_NT) s_segs[i] = S->segs[i];
+    if (tid == 0) { mbar_init(&s_bar, 1); fence_mbar_init(); }
+    __syncthreads();
+
+    const uint32_t n_leaves = (uint32_t)S->n_leaves;
+    const uint32_t all_valid = (n_leaves >= 32) ? 0xFFFFFFFFu : ((1u << n_leaves) - 1u);
+    unsigned long long c_rows = 0, c_null = 0, c_fast = 0; uint32_t c_err = 0;
+    uint32_t phase = 0;
+
+    for (;;) {
+        if (tid == 0) s_tile = (long long)atomicAdd(a.tile_counter, 1u);
+        __syncthreads();
+        const long long tile = s_tile;
+        if (tile >= a.n_tiles) break;
+        const long long lo = tile * (long long)K1_T;                 // absolute (relative to base_al)
+        long long avail = a.n_end - lo;                              // bytes of data from lo on
+        if (avail > K1_T + K1_OVL) avail = K1_T + K1_OVL;
+        const uint32_t bulk = (uint32_t)avail & ~15u;
+        if (tid == 0) {
+            fence_proxy_async();
+            if (bulk) {
+                mbar_expect_tx(&s_bar, bulk);
+                uint32_t off = 0;
+                while (off < bulk) {
+                    uint32_t n = bulk - off; if (n > 16384u) n = 16384u;
+                    bulk_g2s(buf + off, a.base_al + lo + off, n, &s_bar);
+                    off += n;
+                }
+            }
+        }
+        // ragged tail (< 16 bytes) and sentinel by ordinary stores
+        if (tid < (int)((uint32_t)avail - bulk)) buf[bulk + tid] = a.base_al[lo + bulk + tid];
+        if (tid == 32 && lo + avail == a.n_end) buf[avail] = '\n';
+        if (bulk) { while (!mbar_try_wait(&s_bar, phase)) {} phase ^= 1; }
+        __syncthreads();
+
+        long long n_rec = 0; long long rec0 = 0;   // offsets mode: records [rec0, rec0+n_rec)
+        uint32_t my_masks[4]; uint32_t my_base = 0; // NDJSON mode
+        const bool first_virtual = (tile == 0 && (long long)a.skew < a.n_end);
+        if (a.offsets == nullptr) {
+            // --- structural scan: newline q in [lo, hi) owns the record starting at q+1 ---
+            // warp w scans chunks [w*CPW, (w+1)*CPW), lane-strided so shared loads are conflict-free
+            constexpr int CPW = (K1_T / 16) / (K1_NT / 32);   // 256
+            constexpr int ROUNDS = CPW / 32;                  // 8
+            uint32_t cnt_total = 0;
+            uint32_t excl_in_warp[ROUNDS];
+#pragma unroll
+            for (int r = 0; r < ROUNDS; r++) {
+                const int chunk = warp * CPW + r * 32 + lane;
+                const uint4 v = *reinterpret_cast<const uint4*>(buf + chunk * 16);
+                uint32_t m = 0;
+                const uint32_t ws[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                for (int k = 0; k < 4; k++) {
+                    const uint32_t x = ws[k] ^ 0x0A0A0A0Au;                 // zero byte where '\n'
+                    uint32_t t = (x & 0x7F7F7F7Fu) + 0x7F7F7F7Fu;           // exact per-byte zero test
+                    t = ~(t | x | 0x7F7F7F7Fu);                             // 0x80 in each byte that was zero
+                    m |= ((t * 0x00204081u) >> 28) << (k * 4);              // gather the four flags
+                }
+                // validity of each candidate q = lo + chunk*16 + i : start q+1 must be data (< n_end), q >= skew
+                const long long q0 = lo + (long long)chunk * 16;
+                if (q0 + 16 >= a.n_end) {
+                    for (int i = 0; i < 16; i++) if (q0 + i + 1 >= a.n_end) m &= ~(1u << i);
+                }
+                if (q0 < (long long)a.skew) {
+                    for (int i = 0; i < 16; i++) if (q0 + i < (long long)a.skew) m &= ~(1u << i);
+                }
+                if (r & 1) my_masks[r >> 1] |= m << 16; else my_masks[r >> 1] = m;
+                uint32_t c = __popc(m);
+                uint32_t inc = c;
+#pragma unroll
+                for (int s = 1; s < 32; s <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, inc, s); if (lane >= s) inc += t; }
+                excl_in_warp[r] = cnt_total + inc - c;
+                cnt_total += __shfl_sync(0xffffffffu, inc, 31);
+            }
+            if (lane == 0) s_wtot[warp] = cnt_total;
+            __syncthreads();
+            uint32_t wbase = first_virtual ? 1u : 0u, total = first_virtual ? 1u : 0u;
+#pragma unroll
+            for (int w = 0; w < K1_NT / 32; w++) { uint32_t t = s_wtot[w]; if (w < warp) wbase += t; total += t; }
+            n_rec = total;
+            // fold warp base into per-round exclusive ranks; keep only round-0 rank + masks (ranks are
+            // recomputed from popcounts when emitting)
+            my_base = wbase;
+            // stash per-round exclusive offsets compactly: emit loop recomputes them in the same order
+            // (excl_in_warp[r] are kept in registers; ROUNDS is small)
+            if (warp == 0) {
+                long long rb = tile_lookback(a.tile_state, tile, (unsigned long long)n_rec);
+                if (lane == 0) s_rowbase = rb;
+            }
+            // emit + parse in rounds of K1_SC records
+            for (long long round0 = 0; round0 < n_rec || round0 == 0; round0 += K1_SC) {
+                __syncthreads();
+                if (first_virtual && tid == 0 && round0 == 0) s_starts[0] = (uint16_t)a.skew;
+#pragma unroll
+                for (int r = 0; r < ROUNDS; r++) {
+                    uint32_t m = (r & 1) ? (my_masks[r >> 1] >> 16) : (my_masks[r >> 1] & 0xffffu);
+                    long long rank = (long long)my_base + excl_in_warp[r];
+                    const int chunk = warp * CPW + r * 32 + lane;
+                    while (m) {
+                        int i = __ffs(m) - 1; m &= m - 1;
+                        long long rel = rank - round0;
+                        if (rel >= 0 && rel <= K1_SC) s_starts[rel] = (uint16_t)(chunk * 16 + i + 1);
+                        rank++;
+                    }
+                }
+                __syncthreads();
+                const long long row_base = s_rowbase;
+                long long cnt = n_rec - round0; if (cnt > K1_SC) cnt = K1_SC;
+                for (long long idx = tid; idx < cnt; idx += K1_NT) {
+                    const uint32_t st = s_starts[idx];
+                    const long long rank = round0 + idx;
+                    uint32_t en; bool in_smem = true; long long en_abs = 0;
+                    if (rank + 1 < n_rec) en = (uint32_t)s_starts[idx + 1] - 1u;
+                    else {
+                        // last record owned by this tile: its newline lies at or past the tile end
+                        uint32_t p = st;
+                        const uint32_t lim = (uint32_t)avail + ((lo + avail == a.n_end) ? 1u : 0u);
+                        while (p < lim && buf[p] != '\n') p++;
+                        if (p < lim) en = p;
+                        else {
+                            in_smem = false; en = 0;
+                            long long g = lo + p;
+                            while (g < a.n_end && a.base_al[g] != '\n') g++;
+                            en_abs = g;
+                        }
+                    }
+                    RowSink o; o.a = &a; o.row = row_base + rank; o.valid = 0; o.err = 0;
+                    if (o.row >= a.max_rows) { c_err |= DXF_ROW_OVERFLOW; continue; }
+                    bool ok;
+                    if (in_smem) {
+                        ok = fast_record(buf, st, en, s_segs, n_segs, s_lits, o);
+                        if (ok) c_fast++;
+                        else ok = g_record(buf + st, buf + en, S, o);
+                    } else {
+                        ok = g_record(a.base_al + lo + st, a.base_al + en_abs, S, o);
+                    }
+                    c_rows++; if (!ok) c_null++;
+                    c_err |= o.err;
+                    if (o.valid != all_valid) {
+                        for (uint32_t k = 0; k < n_leaves; k++) if (!((o.valid >> k) & 1u)) {
+                            if (S->leaf_type[k] == DX_T_STR) reinterpret_cast<int32_t*>(a.cols[k])[o.row] = -1;
+                            else reinterpret_cast<long long*>(a.cols[k])[o.row] = 0;
+                        }
+                    }
+                    if (a.mask_width == 1) reinterpret_cast<uint8_t*>(a.mask)[o.row] = (uint8_t)(o.valid | (ok ? 0x80u : 0u));
+                    else reinterpret_cast<uint32_t*>(a.mask)[o.row] = o.valid | (ok ? 0x80000000u : 0u);
+                }
+                if (n_rec == 0) break;
+            }
+        } else {
+            // --- caller-provided framing: records whose first byte lies in [lo, hi) ---
+            if (tid == 0) {
+                // first record r with skew + offsets[r] >= lo  (offsets ascending, n_rows+1 entries)
+                long long l = 0, h = a.max_rows;
+                while (l < h) { long long m = (l + h) >> 1; if ((long long)a.skew + a.offsets[m] >= lo) h = m; else l = m + 1; }
+                s_r0 = l;
+                long long l2 = l, h2 = a.max_rows;
+                const long long hi = lo + K1_T;
+                while (l2 < h2) { long long m = (l2 + h2) >> 1; if ((long long)a.skew + a.offsets[m] >= hi) h2 = m; else l2 = m + 1; }
+                s_rowbase = l2;
+            }
+            __syncthreads();
+            rec0 = s_r0; n_rec = s_rowbase - rec0;
+            for (long long idx = tid; idx < n_rec; idx += K1_NT) {
+                const long long r = rec0 + idx;
+                const long long st_abs = (long long)a.skew + a.offsets[r];
+                const long long en_abs = (long long)a.skew + a.offsets[r + 1];
+                RowSink o; o.a = &a; o.row = r; o.valid = 0; o.err = 0;
+                bool ok;
+                if (en_abs - lo <= avail) {
+                    uint32_t st = (uint32_t)(st_abs - lo), en = (uint32_t)(en_abs - lo);
+                    // a trailing newline inside the frame is whitespace; the fast path wants the bare record
+                    uint32_t en_f = en; if (en_f > st && buf[en_f - 1] == '\n') en_f--;
+                    ok = fast_record(buf, st, en_f, s_segs, n_segs, s_lits, o);
+                    if (ok) c_fast++;
+                    else ok = g_record(buf + st, buf + en, S, o);
+                } else {
+                    ok = g_record(a.base_al + st_abs, a.base_al + en_abs, S, o);
+                }
+                c_rows++; if (!ok) c_null++;
+                c_err |= o.err;
+                if (o.valid != all_valid) {
+                    for (uint32_t k = 0; k < n_leaves; k++) if (!((o.valid >> k) & 1u)) {
+                        if (S->leaf_type[k] == DX_T_STR) reinterpret_cast<int32_t*>(a.cols[k])[o.row] = -1;
+                        else reinterpret_cast<long long*>(a.cols[k])[o.row] = 0;
+                    }
+                }
+                if (a.mask_width == 1) reinterpret_cast<uint8_t*>(a.mask)[o.row] = (uint8_t)(o.valid | (ok ? 0x80u : 0u));
+                else reinterpret_cast<uint32_t*>(a.mask)[o.row] = o.valid | (ok ? 0x80000000u : 0u);
+            }
+        }
+        __syncthreads();
+    }
+    // per-warp reduction of the counters, one atomic each
+    for (int s = 16; s > 0; s >>= 1) {
+        c_rows += __shfl_xor_sync(0xffffffffu, c_rows, s);
+        c_null += __shfl_xor_sync(0xffffffffu, c_null, s);
+        c_fast += __shfl_xor_sync(0xffffffffu, c_fast, s);
+        c_err |= __shfl_xor_sync(0xffffffffu, c_err, s);
+    }
+    if (lane == 0) {
+        if (c_rows) atomicAdd(&a.stats->rows, c_rows);
+        if (c_null) atomicAdd(&a.stats->null_rows, c_null);
+        if (c_fast) atomicAdd(&a.stats->fast_rows, c_fast);
+        if (c_err) atomicOr(&a.stats->flags, (unsigned long long)c_err);
+    }
+}
+
+// Counts records of an NDJSON buffer (used only when the caller does not state n_events).
+__global__ void k1_count_records(const uint8_t* bytes, long long n, unsigned long long* out) {
+    unsigned long long c = 0;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+        c += (bytes[i] == '\n') ? 1 : 0;
+    for (int s = 16; s > 0; s >>= 1) c += __shfl_xor_sync(0xffffffffu, c, s);
+    if ((threadIdx.x & 31) == 0 && c) atomicAdd(out, c);
+}
+
+// =======================================================================================
+// host side
+// =======================================================================================
+static size_t k1_smem_bytes() {
+    return K1_T + K1_OVL + K1_PAD + (K1_SC + 2) * 2 + DX_LITS_BYTES + DX_MAX_SEGS * sizeof(DSeg) + 64;
+}
+
+static int map_spark_type(const std::string& t) {
+    if (t == "long" || t == "integer" || t == "int" || t == "short" || t == "byte") return DX_T_I64;
+    if (t == "double" || t == "float") return DX_T_F64;
+    if (t == "string") return DX_T_STR;
+    if (t == "boolean") return DX_T_BOOL;
+    return 0;
+}
+
+struct SchemaBuilder {
+    DSchemaDev* S;
+    std::vector<std::string>* leaf_names;
+    std::string names;
+    std::string err;
+    // Fast-path template pieces
+    std::vector<std::string> seg_lits; std::vector<int> seg_types; std::vector<int> seg_leaves;
+    std::string pending;
+
+    // Reserves the struct entry first so children structs get higher indices; fields of one
+    // struct are contiguous.
+    int add_struct(const JVal& st, const std::string& prefix) {
+        const JVal* fields = st.get("fields");
+        if (!fields || fields->kind != JVal::ARR) { err = "struct without fields"; return -1; }
+        if (S->n_structs >= DX_MAX_STRUCTS) { err = "too many nested structs"; return -1; }
+        int sidx = S->n_structs++;
+        int nf = (int)fields->arr.size();
+        if (S->n_fields + nf > DX_MAX_FIELDS) { err = "too many fields"; return -1; }
+        int first = S->n_fields; S->n_fields += nf;
+        S->structs[sidx].first_field = first; S->structs[sidx].n_fields = nf;
+        S->structs[sidx].first_leaf = S->n_leaves;
+        pending += "{";
+        for (int i = 0; i < nf; i++) {
+            const JVal& f = fields->arr[i];
+            const JVal* nm = f.get("name"); const JVal* ty = f.get("type");
+            if (!nm || !ty || nm->kind != JVal::STR) { err = "field without name/type"; return -1; }
+            DField& df = S->fields[first + i];
+            if (names.size() + nm->str.size() > DX_NAMES_BYTES) { err = "field names too long"; return -1; }
+            df.name_off = (uint16_t)names.size(); df.name_len = (uint16_t)nm->str.size();
+            names += nm->str;
+            pending += (i ? ",\"" : "\"") + nm->str + "\":";
+            if (ty->kind == JVal::STR) {
+                int t = map_spark_type(ty->str);
+                if (!t) { err = "unsupported field type '" + ty->str + "' for " + prefix + nm->str; return -1; }
+                if (S->n_leaves >= DX_MAX_LEAVES) { err = "more than 31 leaf fields"; return -1; }
+                df.type = t; df.target = S->n_leaves;
+                S->leaf_type[S->n_leaves] = t;
+                leaf_names->push_back(prefix + nm->str);
+                seg_lits.push_back(pending); seg_types.push_back(t); seg_leaves.push_back(S->n_leaves);
+                pending.clear();
+                S->n_leaves++;
+            } else if (ty->kind == JVal::OBJ && ty->get("type") && ty->get("type")->str == "struct") {
+                df.type = 100;
+                int child = add_struct(*ty, prefix + nm->str + ".");
+                if (child < 0) return -1;
+                df.target = child;
+            } else { err = "unsupported field type (array/map) for " + prefix + nm->str; return -1; }
+        }
+        pending += "}";
+        S->structs[sidx].n_leaves = S->n_leaves - S->structs[sidx].first_leaf;
+        return sidx;
+    }
+};
+
+int dx_decoder::init(dx_ctx* c, const std::string& schema_json) {
+    ctx = c;
+    memset(&hs, 0, sizeof hs);
+    JVal root;
+    try { root = dx_parse_json(schema_json); } catch (std::exception& e) { return c->set_error(DX_ERR_PARSE, e.what()); }
+    SchemaBuilder b; b.S = &hs; b.leaf_names = &leaf_names;
+    if (b.add_struct(root, "") < 0) return c->set_error(DX_ERR_UNSUPPORTED, "input schema: " + b.err);
+    memcpy(hs.names, b.names.data(), b.names.size());
+    // template: literals before each leaf value, then the closing braces
+    b.seg_lits.push_back(b.pending); b.seg_types.push_back(0); b.seg_leaves.push_back(0);
+    size_t lit_used = 0; hs.n_segs = 0;
+    bool tmpl_ok = b.seg_lits.size() <= DX_MAX_SEGS;
+    for (size_t i = 0; tmpl_ok && i < b.seg_lits.size(); i++) {
+        size_t L = b.seg_lits[i].size(), Lp = (L + 3) & ~size_t(3);
+        if (lit_used + Lp > DX_LITS_BYTES) { tmpl_ok = false; break; }
+        memcpy(reinterpret_cast<char*>(hs.lits) + lit_used, b.seg_lits[i].data(), L);
+        hs.segs[i].lit_off = (uint16_t)lit_used; hs.segs[i].lit_len = (uint16_t)L;
+        hs.segs[i].type = b.seg_types[i]; hs.segs[i].leaf = b.seg_leaves[i];
+        lit_used += Lp; hs.n_segs++;
+    }
+    if (!tmpl_ok) { hs.n_segs = 1; hs.segs[0].lit_off = 0; hs.segs[0].lit_len = 4; hs.segs[0].type = 0; memcpy(hs.lits, "\x01\x01\x01\x01", 4); }
+    for (int k = 0; k < hs.n_leaves; k++) leaf_types.push_back(hs.leaf_type[k]);
+    dev_schema = DevBuf(c, sizeof(DSchemaDev));
+    DX_CUDA(c, cudaMemcpyAsync(dev_schema.p, &hs, sizeof hs, cudaMemcpyHostToDevice, c->stream));
+    dicts.resize(hs.n_leaves);
+    std::vector<DictDev> dd(hs.n_leaves);
+    memset(dd.data(), 0, dd.size() * sizeof(DictDev));
+    for (int k = 0; k < hs.n_leaves; k++) if (hs.leaf_type[k] == DX_T_STR) {
+        dicts[k] = std::make_shared<DxDict>();
+        int rc = dicts[k]->init(c, dict_capacity, dict_heap_bytes);
+        if (rc) return rc;
+        dd[k] = dicts[k]->dev;
+    }
+    dev_dicts = DevBuf(c, sizeof(DictDev) * (hs.n_leaves + 1));
+    DX_CUDA(c, cudaMemcpyAsync(dev_dicts.p, dd.data(), sizeof(DictDev) * hs.n_leaves, cudaMemcpyHostToDevice, c->stream));
+    dev_stats = DevBuf(c, sizeof(DecodeStats) + 16);
+    DX_CUDA(c, cudaFuncSetAttribute(k1_decode, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k1_smem_bytes()));
+    int occ = 0;
+    DX_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k1_decode, K1_NT, k1_smem_bytes()));
+    ctas_per_sm = occ > 0 ? occ : 1;
+    DX_CUDA(c, cudaStreamSynchronize(c->stream));
+    return DX_OK;
+}
+
+// json_dev: device pointer to the first JSON byte.  offsets_dev: optional device array of
+// n_events+1 record offsets.  n_events < 0 with NDJSON framing => counted on the device first.
+int dx_decoder::decode_device(const uint8_t* json_dev, int64_t n_bytes, const int64_t* offsets_dev,
+                              int64_t n_events, DxTableP* out) {
+    dx_ctx* c = ctx;
+    if (n_bytes < 0) return c->set_error(DX_ERR_ARG, "negative byte count");
+    if (n_events < 0) {
+        if (offsets_dev) return c->set_error(DX_ERR_ARG, "n_events required with offsets");
+        DX_CUDA(c, cudaMemsetAsync(dev_stats.p, 0, sizeof(DecodeStats) + 16, c->stream));
+        unsigned long long* cnt = reinterpret_cast<unsigned long long*>(dev_stats.as<uint8_t>() + sizeof(DecodeStats));
+        if (n_bytes > 0) {
+            k1_count_records<<<c->sm_count * 8, 256, 0, c->stream>>>(json_dev, n_bytes, cnt);
+            c->launches["k1_count_records"]++;
+        }
+        unsigned long long h = 0; uint8_t last = '\n';
+        DX_CUDA(c, cudaMemcpyAsync(&h, cnt, 8, cudaMemcpyDeviceToHost, c->stream));
+        if (n_bytes > 0) DX_CUDA(c, cudaMemcpyAsync(&last, json_dev + n_bytes - 1, 1, cudaMemcpyDeviceToHost, c->stream));
+        DX_CUDA(c, cudaStreamSynchronize(c->stream));
+        n_events = (int64_t)h + ((n_bytes > 0 && last != '\n') ? 1 : 0);
+    }
+    auto t = std::make_shared<DxTable>();
+    t->ctx = c; t->n_rows = n_events; t->name = "Raw";
+    const int nl = hs.n_leaves;
+    const int mw = (nl <= 7) ? 1 : 4;
+    DevBufP mask = make_buf(c, (size_t)(n_events > 0 ? n_events : 1) * mw);
+    DecodeArgs a; memset(&a, 0, sizeof a);
+    for (int k = 0; k < nl; k++) {
+        DxColumn col;
+        col.name = leaf_names[k]; col.type = hs.leaf_type[k];
+        col.data = make_buf(c, (size_t)(n_events > 0 ? n_events : 1) * dx_type_width(col.type));
+        col.vmask = mask; col.vwidth = mw; col.vbit = k;
+        col.dict = dicts[k];
+        a.cols[k] = col.data->p;
+        t->cols.push_back(std::move(col));
+    }
+    if (n_events == 0 || n_bytes == 0) {
+        if (n_events > 0) DX_CUDA(c, cudaMemsetAsync(mask->p, 0, (size_t)n_events * mw, c->stream));
+        last_stats = DecodeStats{(unsigned long long)n_events, (unsigned long long)n_events, 0, 0};
+        *out = t; return DX_OK;
+    }
+    uintptr_t addr = reinterpret_cast<uintptr_t>(json_dev);
+    a.skew = (uint32_t)(addr & 15);
+    a.base_al = reinterpret_cast<const uint8_t*>(addr - a.skew);
+    a.n_end = (long long)a.skew + n_bytes;
+    a.n_tiles = (a.n_end + K1_T - 1) / K1_T;
+    a.max_rows = n_events;
+    a.offsets = reinterpret_cast<const long long*>(offsets_dev);
+    a.mask = mask->p; a.mask_width = mw;
+    a.dicts = dev_dicts.as<DictDev>();
+    a.schema = dev_schema.as<DSchemaDev>();
+    size_t need = (size_t)(a.n_tiles + 2) * 8 + 16;
+    if (tile_state.bytes < need) tile_state = DevBuf(c, need * 2);
+    DX_CUDA(c, cudaMemsetAsync(tile_state.p, 0, need, c->stream));
+    a.tile_counter = tile_state.as<unsigned int>();
+    a.tile_state = tile_state.as<unsigned long long>() + 2;
+    DX_CUDA(c, cudaMemsetAsync(dev_stats.p, 0, sizeof(DecodeStats), c->stream));
+    a.stats = dev_stats.as<DecodeStats>();
+    // offsets mode writes every row; NDJSON mode too unless the caller overstated n_events — clear the mask
+    // so never-written rows read as NULL rows
+    long long grid = (long long)c->sm_count * ctas_per_sm;
+    if (grid > a.n_tiles) grid = a.n_tiles;
+    {
+        StageTimer tm(c, "k1_decode");
+        k1_decode<<<(unsigned)grid, K1_NT, k1_smem_bytes(), c->stream>>>(a);
+        c->launches["k1_decode"]++;
+    }
+    DX_CUDA(c, cudaGetLastError());
+    DX_CUDA(c, cudaMemcpyAsync(&last_stats, dev_stats.p, sizeof(DecodeStats), cudaMemcpyDeviceToHost, c->stream));
+    DX_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (last_stats.flags) {
+        char b[256];
+        snprintf(b, sizeof b, "decode failed: flags=0x%llx (1 dictionary overflow, 2 number beyond 19-digit window, "
+                 "4 object/array into string field, 8 escaped string > %d bytes, 16 more records than n_events)",
+                 last_stats.flags, DX_UNESC_CAP);
+        return c->set_error((last_stats.flags & DXF_DICT_OVERFLOW) ? DX_ERR_CAPACITY : DX_ERR_UNSUPPORTED, b);
+    }
+    if ((int64_t)last_stats.rows != n_events) {
+        char b[160];
+        snprintf(b, sizeof b, "decode: caller stated %lld events but the batch frames %llu records",
+                 (long long)n_events, last_stats.rows);
+        return c->set_error(DX_ERR_ARG, b);
+    }
+    *out = t;
+    return DX_OK;
+}
+
+int dx_decoder::decode_host(const uint8_t* json, int64_t n_bytes, const int64_t* offsets, int64_t n_events, DxTableP* out) {
+    dx_ctx* c = ctx;
+    size_t need = (size_t)n_bytes + 64;
+    if (staging.bytes < need) staging = DevBuf(c, need + need / 4);
+    if (n_bytes > 0) DX_CUDA(c, cudaMemcpyAsync(staging.p, json, (size_t)n_bytes, cudaMemcpyHostToDevice, c->stream));
+    const int64_t* off_dev = nullptr;
+    if (offsets) {
+        size_t ob = (size_t)(n_events + 1) * 8;
+        if (staging_off.bytes < ob) staging_off = DevBuf(c, ob + ob / 4);
+        DX_CUDA(c, cudaMemcpyAsync(staging_off.p, offsets, ob, cudaMemcpyHostToDevice, c->stream));
+        off_dev = staging_off.as<int64_t>();
+    }
+    return decode_device(staging.as<uint8_t>(), n_bytes, off_dev, n_events, out);
+}

@@ -1,0 +1,19 @@
+// dx_decode_host.h — host-side handle of the K1 decoder.
+#pragma once
+#include "dx_decode.cuh"
+
+struct dx_decoder {
+    dx_ctx* ctx = nullptr;
+    DSchemaDev hs;
+    std::vector<std::string> leaf_names;   // dotted paths, e.g. deviceDetails.deviceId
+    std::vector<int> leaf_types;
+    std::vector<DxDictP> dicts;            // per leaf; null for non-string leaves
+    DevBuf dev_schema, dev_dicts, dev_stats, tile_state, staging, staging_off;
+    DecodeStats last_stats{0, 0, 0, 0};
+    uint32_t dict_capacity = 1u << 16;     // slots per string column (power of two)
+    uint32_t dict_heap_bytes = 4u << 20;
+    int ctas_per_sm = 1;
+    int init(dx_ctx* c, const std::string& schema_json);
+    int decode_device(const uint8_t* json_dev, int64_t n_bytes, const int64_t* offsets_dev, int64_t n_events, DxTableP* out);
+    int decode_host(const uint8_t* json, int64_t n_bytes, const int64_t* offsets, int64_t n_events, DxTableP* out);
+};

@@ -1,0 +1,117 @@
+/*
+ * dxgpu.h — C ABI of libdxgpu.so, the B200 (sm_100a) flow processor for Data Accelerator.
+ *
+ * This is the drop-in boundary: the functions a JNI / Java-FFM shim inside the reference's
+ * Scala host (datax-host) binds in place of the Spark-SQL work done by
+ * CommonProcessorFactory.createProcessor (reference:
+ * DataProcessing/datax-host/src/main/scala/datax/processor/CommonProcessorFactory.scala:50-657).
+ * Plain pointers and sizes only; no C++ or torch types cross this line.  INTEGRATION.md shows
+ * the Scala-side binding.
+ *
+ * Conventions: every function returning int returns 0 on success, non-zero on failure (the
+ * message is available through dx_ctx_last_error); nothing here falls back to a CPU path —
+ * an unsupported construct is an error at create time.  Device pointers handed out by the
+ * library stay valid until the owning object is released.
+ */
+#ifndef DXGPU_H
+#define DXGPU_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct dx_ctx dx_ctx;         /* one per (process, GPU): stream, memory pool, error text   */
+typedef struct dx_decoder dx_decoder; /* K1: JSON events -> columns for one input schema           */
+typedef struct dx_table dx_table;     /* device-resident columnar table                            */
+
+/* column physical types (dx_table_column_type) */
+#define DX_TYPE_I64 1   /* long/int/short/byte                                  8 B/row */
+#define DX_TYPE_F64 2   /* double/float                                         8 B/row */
+#define DX_TYPE_STR 3   /* dictionary code (int32) + per-column dictionary      4 B/row */
+#define DX_TYPE_BOOL 4  /* int64 0/1                                            8 B/row */
+#define DX_TYPE_TS 5    /* timestamp, int64 microseconds since epoch            8 B/row */
+#define DX_TYPE_FLAGS 6 /* rule flag bitmap, dx_table_flag_words uint32 per row         */
+
+#define DX_MEM_HOST 0
+#define DX_MEM_DEVICE 1
+
+/* ---- context -------------------------------------------------------------------------- */
+/* Replaces the SparkSession / executor pool a processor runs on
+ * (reference: datax/host/SparkSessionSingleton.scala:20-24).                                */
+int dx_ctx_create(int device_ordinal, dx_ctx** out);
+void dx_ctx_destroy(dx_ctx* ctx);
+const char* dx_ctx_last_error(const dx_ctx* ctx);
+/* CUDA-event timing of every kernel stage on the context's stream (off by default). */
+int dx_ctx_set_timing(dx_ctx* ctx, int enabled);
+/* Sum of recorded milliseconds and number of samples for a stage ("k1_decode", ...); resets it. */
+int dx_ctx_take_stage_ms(dx_ctx* ctx, const char* stage, double* total_ms, int64_t* samples);
+/* Number of launches of this library's kernels since the last call (resets the counter). */
+int64_t dx_ctx_take_launches(dx_ctx* ctx);
+void* dx_ctx_stream(dx_ctx* ctx);                     /* cudaStream_t, for event timing by the caller */
+int dx_ctx_synchronize(dx_ctx* ctx);
+/* pooled device memory for callers that stage inputs themselves */
+int dx_dev_alloc(dx_ctx* ctx, int64_t bytes, void** out);
+void dx_dev_free(dx_ctx* ctx, void* p);
+int dx_copy_h2d(dx_ctx* ctx, void* dst_dev, const void* src_host, int64_t bytes);
+int dx_copy_d2h(dx_ctx* ctx, void* dst_host, const void* src_dev, int64_t bytes);
+
+/* ---- K1: JSON decode -------------------------------------------------------------------- */
+/* Replaces from_json(Raw, rawBlockSchema) in project()
+ * (reference: CommonProcessorFactory.scala:93; schema JSON as read by
+ * datax/input/SchemaFile.scala:22-34 — a Spark StructType in JSON).
+ * Leaves of nested structs become columns named by their dotted path.                       */
+int dx_decoder_create(dx_ctx* ctx, const char* spark_schema_json, dx_decoder** out);
+void dx_decoder_destroy(dx_decoder* d);
+/* json: n_bytes of events.  offsets == NULL: NDJSON framing (every '\n' ends a record, a final
+ * unterminated record counts).  offsets != NULL: n_events+1 int64 offsets, record i =
+ * json[offsets[i], offsets[i+1]).  n_events < 0 (NDJSON only): counted on the device.
+ * memory_kind says where json/offsets live.  The resulting table owns its columns.           */
+int dx_decoder_decode(dx_decoder* d, const uint8_t* json, int64_t n_bytes, const int64_t* offsets,
+                      int64_t n_events, int memory_kind, dx_table** out);
+/* rows decoded / rows that became NULL structs / rows taken by the template fast path, last call */
+int dx_decoder_stats(const dx_decoder* d, int64_t* rows, int64_t* null_rows, int64_t* fast_rows);
+
+/* ---- tables ----------------------------------------------------------------------------- */
+/* What the Scala shim wraps into a DataFrame for the unchanged sinks
+ * (reference: OutputOperator.output(DataFrame, Timestamp), datax-core sink/package.scala:32-35). */
+int64_t dx_table_num_rows(const dx_table* t);
+int dx_table_num_columns(const dx_table* t);
+const char* dx_table_column_name(const dx_table* t, int col);
+int dx_table_column_type(const dx_table* t, int col);
+int dx_table_find_column(const dx_table* t, const char* name);      /* -1 if absent */
+int dx_table_flag_words(const dx_table* t, int col);                /* FLAGS columns */
+/* Raw device views: data pointer (NULL for constant columns), validity mask pointer with element
+ * width (1 or 4 bytes) and the bit holding this column's validity (mask NULL => never NULL).  */
+int dx_table_column_device(const dx_table* t, int col, const void** data, const void** vmask,
+                           int* vmask_width, int* vmask_bit);
+/* Copies a column to host: data = n_rows elements of the physical width (FLAGS: words*4 per row),
+ * valid = n_rows bytes (1 = non-NULL).  Either destination may be NULL.                        */
+int dx_table_column_to_host(const dx_table* t, int col, void* data, uint8_t* valid);
+/* Dictionary of a STR column: number of codes, and the UTF-8 text of one code.                */
+int dx_table_dict_size(const dx_table* t, int col, int64_t* n_codes);
+int dx_table_dict_string(const dx_table* t, int col, int64_t code, const char** bytes, int64_t* len);
+void dx_table_release(dx_table* t);
+
+/* ---- synthetic events (measurement tooling; shapes of the reference's simulated IoT data) -- */
+/* Event shapes after DataGenerator.scala:27-209 / HomeAutomationLocal.json:288. */
+typedef struct dx_gen_params {
+    uint64_t seed;
+    int64_t n_keys;          /* deviceId uniform in 1..n_keys                    */
+    int64_t n_homes;         /* homeId = 1 + mix(deviceId) % n_homes             */
+    int64_t base_ms;         /* batch time, epoch milliseconds                   */
+    int64_t interval_ms;
+    int64_t watermark_ms;
+    int32_t shape;           /* 1 = S1 (5 fields), 2 = S2 (+temperature,humidity) */
+    int32_t late_permille;   /* events older than the watermark                  */
+    int32_t future_permille; /* events stamped after the batch time              */
+    int32_t pad;
+} dx_gen_params;
+/* Writes events [first, first+n) as NDJSON into a pooled device buffer (*bytes, *n_bytes);
+ * offsets (optional) receives a device array of n+1 offsets.  Free both with dx_dev_free.      */
+int dx_gen_events(dx_ctx* ctx, const dx_gen_params* p, int64_t first, int64_t n, uint8_t** bytes,
+                  int64_t* n_bytes, int64_t** offsets);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DXGPU_H */

@@ -1,0 +1,202 @@
+"""CPU ORACLE — Python side (test infrastructure, NOT product code).
+
+Wraps oracle/libdxo.so (dxo_core.c) and restates the reference's host-side control flow in plain
+Python/numpy.  Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference
+legs import this module; the product path (data-accelerator_b200/) never does.
+
+PARITY UNPINNED at the Spark boundary (see dxo_core.c header and DESIGN.md §2); pinned pieces:
+  TransformSQLParser.parse / replaceTableNames  <- datax/sql/TransformSqlParser.scala:27-104,
+      KAT datax/test/sql/TransformSQLParserTests.scala:11-21
+  string_to_timestamp                           <- datax/utility/ConcurrentDateFormat.scala:38-62,
+      KAT datax/utility/test/ConcurrentDateFormatTests.scala:13-15
+"""
+import ctypes as C
+import json
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+LONG, DOUBLE, STRING, BOOL, STRUCT = 1, 2, 3, 4, 5
+_TYPE = {"long": LONG, "integer": LONG, "int": LONG, "short": LONG, "byte": LONG, "double": DOUBLE,
+         "float": DOUBLE, "string": STRING, "boolean": BOOL}
+
+
+class _Field(C.Structure):
+    _fields_ = [("name", C.c_char_p), ("name_len", C.c_int32), ("type", C.c_int32), ("target", C.c_int32)]
+
+
+class _Struct(C.Structure):
+    _fields_ = [("first_field", C.c_int32), ("n_fields", C.c_int32), ("first_leaf", C.c_int32),
+                ("n_leaves", C.c_int32)]
+
+
+class GenParams(C.Structure):
+    _fields_ = [("seed", C.c_uint64), ("n_keys", C.c_int64), ("n_homes", C.c_int64), ("base_ms", C.c_int64),
+                ("interval_ms", C.c_int64), ("watermark_ms", C.c_int64), ("shape", C.c_int32),
+                ("late_permille", C.c_int32), ("future_permille", C.c_int32), ("pad", C.c_int32)]
+
+
+class Agg(C.Structure):
+    _fields_ = [("count_star", C.c_int64), ("count_v", C.c_int64), ("sum_i", C.c_int64), ("sum_d", C.c_double),
+                ("min_i", C.c_int64), ("max_i", C.c_int64), ("min_d", C.c_double), ("max_d", C.c_double)]
+
+
+def build():
+    subprocess.check_call(["make", "-s", "-C", _HERE])
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        path = os.path.join(_HERE, "libdxo.so")
+        if not os.path.exists(path):
+            build()
+        _LIB = C.CDLL(path)
+        _LIB.dxo_decode.restype = C.c_int64
+        _LIB.dxo_decode_mt.restype = C.c_int64
+        _LIB.dxo_split.restype = C.c_int64
+        _LIB.dxo_gen_events.restype = C.c_int64
+        _LIB.dxo_group_agg.restype = C.c_int64
+    return _LIB
+
+
+class Schema:
+    """Flattened view of a Spark StructType JSON (SchemaFile.loadInputSchema, SchemaFile.scala:22-34)."""
+
+    def __init__(self, schema_json: str):
+        root = json.loads(schema_json.lstrip("﻿"))
+        self.structs, self.fields, self.leaf_names, self.leaf_types = [], [], [], []
+        self._keep = []
+        self._add(root, "")
+        self.c_structs = (_Struct * len(self.structs))(*self.structs)
+        self.c_fields = (_Field * len(self.fields))(*self.fields)
+
+    def _add(self, st, prefix):
+        sidx = len(self.structs)
+        self.structs.append(None)
+        flds = st["fields"]
+        first = len(self.fields)
+        self.fields.extend([None] * len(flds))
+        first_leaf = len(self.leaf_names)
+        for i, f in enumerate(flds):
+            name = f["name"].encode("utf-8")
+            self._keep.append(name)
+            ty = f["type"]
+            if isinstance(ty, str):
+                if ty not in _TYPE:
+                    raise ValueError(f"unsupported field type {ty}")
+                t = _TYPE[ty]
+                self.fields[first + i] = _Field(name, len(name), t, len(self.leaf_names))
+                self.leaf_names.append(prefix + f["name"])
+                self.leaf_types.append(t)
+            elif isinstance(ty, dict) and ty.get("type") == "struct":
+                child = self._add(ty, prefix + f["name"] + ".")
+                self.fields[first + i] = _Field(name, len(name), STRUCT, child)
+            else:
+                raise ValueError("unsupported field type (array/map)")
+        self.structs[sidx] = _Struct(first, len(flds), first_leaf, len(self.leaf_names) - first_leaf)
+        return sidx
+
+
+def split_ndjson(data: bytes):
+    """NDJSON framing -> (starts, ends) int64 arrays."""
+    buf = np.frombuffer(data, dtype=np.uint8)
+    cap = int((buf == 10).sum()) + 1
+    starts = np.zeros(cap, dtype=np.int64)
+    ends = np.zeros(cap, dtype=np.int64)
+    n = lib().dxo_split(buf.ctypes.data_as(C.c_void_p), C.c_int64(buf.size), starts.ctypes.data_as(C.c_void_p),
+                        ends.ctypes.data_as(C.c_void_p), C.c_int64(cap))
+    return starts[:n].copy(), ends[:n].copy()
+
+
+def decode(schema: Schema, data: bytes, offsets=None, threads=0):
+    """from_json over a batch.  Returns dict leaf -> (values, valid) plus '__rowok'.
+    Strings come back as object arrays of bytes (None when NULL)."""
+    buf = np.frombuffer(data, dtype=np.uint8)
+    if offsets is None:
+        starts, ends = split_ndjson(data)
+    else:
+        offsets = np.ascontiguousarray(offsets, dtype=np.int64)
+        starts, ends = offsets[:-1].copy(), offsets[1:].copy()
+    n = len(starts)
+    nl = len(schema.leaf_names)
+    vals = np.zeros((nl, max(n, 1)), dtype=np.int64)
+    lens = np.zeros((nl, max(n, 1)), dtype=np.int32)
+    valid = np.zeros((nl, max(n, 1)), dtype=np.uint8)
+    rowok = np.zeros(max(n, 1), dtype=np.uint8)
+    heap = np.zeros(buf.size + 16, dtype=np.uint8)
+    used = C.c_int64(0)
+    vp = C.c_void_p
+    if threads and threads > 0:
+        rc = lib().dxo_decode_mt(buf.ctypes.data_as(vp), starts.ctypes.data_as(vp), ends.ctypes.data_as(vp),
+                                 C.c_int64(n), schema.c_structs, schema.c_fields, C.c_int32(nl),
+                                 vals.ctypes.data_as(vp), lens.ctypes.data_as(vp), valid.ctypes.data_as(vp),
+                                 rowok.ctypes.data_as(vp), C.c_int(threads))
+    else:
+        rc = lib().dxo_decode(buf.ctypes.data_as(vp), starts.ctypes.data_as(vp), ends.ctypes.data_as(vp),
+                              C.c_int64(n), schema.c_structs, schema.c_fields, C.c_int32(nl),
+                              vals.ctypes.data_as(vp), lens.ctypes.data_as(vp), valid.ctypes.data_as(vp),
+                              rowok.ctypes.data_as(vp), heap.ctypes.data_as(vp), C.c_int64(heap.size), C.byref(used))
+    if rc < 0:
+        raise RuntimeError(f"oracle limitation hit (code {rc}): -2 heap, -3 object/array into string field")
+    out = {"__rowok": rowok[:n].astype(bool)}
+    for k, name in enumerate(schema.leaf_names):
+        v = valid[k, :n].astype(bool)
+        t = schema.leaf_types[k]
+        if t == DOUBLE:
+            out[name] = (vals[k, :n].view(np.float64).copy(), v)
+        elif t == STRING and not threads:
+            hb = heap.tobytes()
+            s = np.empty(n, dtype=object)
+            for r in range(n):
+                s[r] = hb[vals[k, r]: vals[k, r] + lens[k, r]] if v[r] else None
+            out[name] = (s, v)
+        else:
+            out[name] = (vals[k, :n].copy(), v)
+    return out
+
+
+TYPES = [b"DoorLock", b"WindowLock", b"Heating", b"GarageDoorLock"]
+
+
+def gen_events(p: GenParams, first, n):
+    cap = n * 200 + 64
+    out = np.zeros(cap, dtype=np.uint8)
+    used = lib().dxo_gen_events(C.byref(p), C.c_int64(first), C.c_int64(n), out.ctypes.data_as(C.c_void_p),
+                                C.c_int64(cap))
+    assert used >= 0
+    return out[:used].tobytes()
+
+
+def gen_fields(p: GenParams, first, n):
+    a = {k: np.zeros(n, dtype=np.int64) for k in ("deviceId", "eventTime", "homeId", "status")}
+    ty = np.zeros(n, dtype=np.int32)
+    temp = np.zeros(n, dtype=np.float64)
+    hum = np.zeros(n, dtype=np.float64)
+    vp = C.c_void_p
+    lib().dxo_gen_fields(C.byref(p), C.c_int64(first), C.c_int64(n), a["deviceId"].ctypes.data_as(vp),
+                         ty.ctypes.data_as(vp), a["eventTime"].ctypes.data_as(vp), a["homeId"].ctypes.data_as(vp),
+                         a["status"].ctypes.data_as(vp), temp.ctypes.data_as(vp), hum.ctypes.data_as(vp))
+    a["deviceType"] = ty
+    a["temperature"] = temp
+    a["humidity"] = hum
+    return a
+
+
+def iot_schema_json(shape=2, event_time_type="long"):
+    """Spark StructType JSON of the home-automation event (HomeAutomationLocal.json:288), plus the
+    two double fields of shape S2 (BasicLocal.json:185)."""
+    f = [{"name": "deviceId", "type": "long", "nullable": True, "metadata": {}},
+         {"name": "deviceType", "type": "string", "nullable": True, "metadata": {}},
+         {"name": "eventTime", "type": event_time_type, "nullable": True, "metadata": {}},
+         {"name": "homeId", "type": "long", "nullable": True, "metadata": {}},
+         {"name": "status", "type": "long", "nullable": True, "metadata": {}}]
+    if shape == 2:
+        f += [{"name": "temperature", "type": "double", "nullable": True, "metadata": {}},
+              {"name": "humidity", "type": "double", "nullable": True, "metadata": {}}]
+    return json.dumps({"type": "struct", "fields": [
+        {"name": "deviceDetails", "type": {"type": "struct", "fields": f}, "nullable": True, "metadata": {}}]})

@@ -1,0 +1,178 @@
+"""K1 parity: CUDA decode (through the C ABI) vs the CPU oracle on the same bytes."""
+import math
+
+import numpy as np
+import pytest
+
+import dxo
+from adversarial import all_records, to_ndjson, HAND
+
+pytestmark = pytest.mark.gpu
+
+SCHEMA2 = dxo.iot_schema_json(2)
+S2 = dxo.Schema(SCHEMA2)
+
+
+def gp(dx, shape=2, n_keys=1_000_000, seed=20260102):
+    args = (seed, n_keys, 100_000, 1_700_000_000_000, 60_000, 60_000, shape, 10, 1, 0)
+    return dx.GenParams(*args), dxo.GenParams(*args)
+
+
+def compare(table, ora, schema):
+    n = table.num_rows
+    assert n == len(ora["__rowok"])
+    for k, name in enumerate(schema.leaf_names):
+        ev, eok = ora[name]
+        gv, gok = table.column(name)
+        assert (gok == eok).all(), (name, np.nonzero(gok != eok)[0][:10])
+        t = schema.leaf_types[k]
+        if t == dxo.DOUBLE:
+            a, b = gv.view(np.int64)[eok], ev.view(np.int64)[eok]
+            nan = np.isnan(gv[eok]) & np.isnan(ev[eok])
+            bad = (a != b) & ~nan
+            assert not bad.any(), (name, np.nonzero(bad)[0][:10])
+        elif t == dxo.STRING:
+            idx = np.nonzero(eok)[0]
+            for i in idx:
+                assert gv[i] == ev[i], (name, i, gv[i], ev[i])
+        else:
+            assert (gv[eok] == ev[eok]).all(), (name, np.nonzero(gv != ev)[0][:10])
+
+
+def test_generator_matches_cpu_twin(dx, ctx):
+    g, o = gp(dx)
+    ptr, nb, _ = ctx.gen_events(g, 1000, 50_000)
+    dev = ctx.d2h(ptr, nb).tobytes()
+    ctx.free(ptr)
+    assert dev == dxo.gen_events(o, 1000, 50_000)
+
+
+@pytest.mark.parametrize("shape", [1, 2])
+def test_clean_events_bit_exact(dx, ctx, shape):
+    g, o = gp(dx, shape)
+    n = 300_000
+    ptr, nb, _ = ctx.gen_events(g, 0, n)
+    schema_json = dxo.iot_schema_json(shape)
+    dec = dx.Decoder(ctx, schema_json)
+    t = dec.decode_device(ptr, nb, n_events=n)
+    st = dec.stats()
+    assert st["rows"] == n and st["null_rows"] == 0 and st["fast_rows"] == n
+    truth = dxo.gen_fields(o, 0, n)
+    for f in ("deviceId", "eventTime", "homeId", "status"):
+        v, ok = t.column("deviceDetails." + f)
+        assert ok.all() and (v == truth[f]).all(), f
+    if shape == 2:
+        for f in ("temperature", "humidity"):
+            v, ok = t.column("deviceDetails." + f)
+            assert ok.all() and (v.view(np.int64) == truth[f].view(np.int64)).all(), f
+    codes, ok = t.codes("deviceDetails.deviceType")
+    d = t.dictionary("deviceDetails.deviceType")
+    assert ok.all() and sorted(d) == sorted(dxo.TYPES)
+    lut = np.array([dxo.TYPES.index(s) for s in d])
+    assert (lut[codes] == truth["deviceType"]).all()
+    # and against the oracle proper on a prefix of the same bytes
+    host = ctx.d2h(ptr, nb).tobytes()
+    cut = host.index(b"\n", 2_000_000) + 1
+    t2 = dec.decode_host(host[:cut])
+    compare(t2, dxo.decode(dxo.Schema(schema_json), host[:cut]), dxo.Schema(schema_json))
+    ctx.free(ptr)
+    dec.close()
+
+
+def test_counts_records_when_n_events_unknown(dx, ctx):
+    g, _ = gp(dx)
+    ptr, nb, _ = ctx.gen_events(g, 0, 12_345)
+    dec = dx.Decoder(ctx, SCHEMA2)
+    t = dec.decode_device(ptr, nb)                      # n_events = -1
+    assert t.num_rows == 12_345
+    t = dec.decode_device(ptr, nb - 1)                  # last record without trailing newline
+    assert t.num_rows == 12_345 and dec.stats()["null_rows"] == 0
+    with pytest.raises(dx.DxError):
+        dec.decode_device(ptr, nb, n_events=12_000)     # caller understates the batch
+    ctx.free(ptr)
+    dec.close()
+
+
+def test_adversarial_records_match_oracle(dx, ctx):
+    recs = all_records(4000, seed=11)
+    data = to_ndjson(recs)
+    dec = dx.Decoder(ctx, SCHEMA2)
+    t = dec.decode_host(data)
+    ora = dxo.decode(S2, data)
+    compare(t, ora, S2)
+    assert dec.stats()["null_rows"] == int((~ora["__rowok"]).sum())
+    dec.close()
+
+
+def test_hand_cases_one_by_one(dx, ctx):
+    dec = dx.Decoder(ctx, SCHEMA2)
+    for rec in HAND:
+        data = to_ndjson([rec])
+        compare(dec.decode_host(data), dxo.decode(S2, data), S2)
+    dec.close()
+
+
+def test_offsets_framing_and_unaligned_device_pointer(dx, ctx):
+    recs = all_records(2000, seed=5)
+    blob = "".join(recs).encode("utf-8")               # no separators at all: framing by offsets only
+    offs = np.zeros(len(recs) + 1, dtype=np.int64)
+    offs[1:] = np.cumsum([len(r.encode("utf-8")) for r in recs])
+    dec = dx.Decoder(ctx, SCHEMA2)
+    t = dec.decode_host(blob, offsets=offs)
+    ora = dxo.decode(S2, blob, offsets=offs)
+    compare(t, ora, S2)
+    # NDJSON at every misalignment of the device pointer
+    data = to_ndjson(recs[:500])
+    ora = dxo.decode(S2, data)
+    base = ctx.alloc(len(data) + 64)
+    for skew in (1, 3, 7, 8, 13, 15):
+        ctx.h2d(base + skew, np.frombuffer(data, dtype=np.uint8))
+        compare(dec.decode_device(base + skew, len(data)), ora, S2)
+    ctx.free(base)
+    dec.close()
+
+
+def test_long_records_and_tile_boundaries(dx, ctx):
+    # records longer than the tile overlap go through the global-memory path; vary padding so
+    # record starts sweep across tile boundaries
+    dec = dx.Decoder(ctx, SCHEMA2)
+    good = '{"deviceDetails":{"deviceId":%d,"deviceType":"Heating","eventTime":1,"homeId":2,"status":1,"temperature":1.5,"humidity":2.5}}'
+    recs = []
+    for i in range(700):
+        if i % 50 == 7:
+            recs.append('{"pad":"%s","deviceDetails":{"deviceId":%d}}' % ("x" * (3000 + 997 * (i % 7)), i))
+        elif i % 50 == 9:
+            recs.append('{"pad":"%s","deviceDetails":{"deviceId":%d}}' % ("y" * 40000, i))
+        else:
+            recs.append(good % i)
+    data = to_ndjson(recs)
+    compare(dec.decode_host(data), dxo.decode(S2, data), S2)
+    # tiny records: more record starts per tile than the shared start list holds
+    tiny = to_ndjson(["{}"] * 40_000 + [good % 5] * 10 + [""] * 5000)
+    compare(dec.decode_host(tiny), dxo.decode(S2, tiny), S2)
+    dec.close()
+
+
+def test_empty_batch(dx, ctx):
+    dec = dx.Decoder(ctx, SCHEMA2)
+    assert dec.decode_host(b"").num_rows == 0
+    assert dec.decode_host(b"\n").num_rows == 1
+    dec.close()
+
+
+def test_double_rounding_matches_strtod(dx, ctx):
+    import random
+    from adversarial import random_number
+    rng = random.Random(99)
+    nums = [random_number(rng) for _ in range(200_000)]
+    recs = ['{"deviceDetails":{"temperature":%s}}' % s for s in nums]
+    data = to_ndjson(recs)
+    dec = dx.Decoder(ctx, SCHEMA2)
+    compare(dec.decode_host(data), dxo.decode(S2, data), S2)
+    dec.close()
+
+
+def test_unsupported_schema_fails_loudly(dx, ctx):
+    bad = '{"type":"struct","fields":[{"name":"a","type":{"type":"array","elementType":"long","containsNull":true},"nullable":true,"metadata":{}}]}'
+    with pytest.raises(dx.DxError):
+        dx.Decoder(ctx, bad)
