@@ -6,7 +6,6 @@
 // DESIGN.md §3 and mirrored (independently) by oracle/dxo_core.c.
 #pragma once
 #include "dx_common.h"
-#include "dx_pow5_table.h"
 
 #define DX_MAX_LEAVES 31
 #define DX_MAX_STRUCTS 16
@@ -139,99 +138,7 @@ static __device__ __forceinline__ void dict_pack(const uint8_t* bytes, uint32_t 
     }
 }
 
-// ------------------------------- decimal -> double -------------------------------------
-static __device__ const double dx_pow10_exact[23] = {1e0, 1e1, 1e2, 1e3, 1e4, 1e5, 1e6, 1e7, 1e8, 1e9, 1e10, 1e11,
-                                              1e12, 1e13, 1e14, 1e15, 1e16, 1e17, 1e18, 1e19, 1e20, 1e21, 1e22};
-
-// Eisel-Lemire: w * 10^q -> nearest binary64 bits (w != 0).  Returns false if q out of the table.
-static __device__ bool dx_eisel_lemire(uint64_t w, int q, uint64_t* bits_out) {
-    if (q < DX_POW5_MIN_Q) { *bits_out = 0; return true; }
-    if (q > DX_POW5_MAX_Q) { *bits_out = 0x7FF0000000000000ull; return true; }
-    int lz = __clzll((long long)w);
-    w <<= lz;
-    const uint64_t* tp = dx_pow5_128 + 2 * (q - DX_POW5_MIN_Q);
-    uint64_t hi = __umul64hi(w, tp[0]), lo = w * tp[0];
-    const uint64_t precision_mask = 0xFFFFFFFFFFFFFFFFull >> 55;
-    if ((hi & precision_mask) == precision_mask) {
-        uint64_t hi2 = __umul64hi(w, tp[1]);
-        lo += hi2;
-        if (hi2 > lo) hi++;
-    }
-    int upperbit = (int)(hi >> 63);
-    uint64_t mantissa = hi >> (upperbit + 64 - 52 - 3);
-    lz += 1 ^ upperbit;
-    int power2 = (((152170 + 65536) * q) >> 16) + 63 + upperbit - lz + 1023;
-    if (power2 <= 0) {
-        if (-power2 + 1 >= 64) { *bits_out = 0; return true; }
-        mantissa >>= -power2 + 1;
-        mantissa += (mantissa & 1);
-        mantissa >>= 1;
-        power2 = (mantissa < (1ull << 52)) ? 0 : 1;
-        *bits_out = (mantissa & ~(1ull << 52)) | ((uint64_t)power2 << 52);
-        return true;
-    }
-    if (lo <= 1 && q >= -4 && q <= 23 && (mantissa & 3) == 1) {
-        if ((mantissa << (upperbit + 64 - 52 - 3)) == hi) mantissa &= ~1ull;
-    }
-    mantissa += (mantissa & 1);
-    mantissa >>= 1;
-    if (mantissa >= (2ull << 52)) { mantissa = 1ull << 52; power2++; }
-    mantissa &= ~(1ull << 52);
-    if (power2 >= 0x7FF) { *bits_out = 0x7FF0000000000000ull; return true; }
-    *bits_out = mantissa | ((uint64_t)power2 << 52);
-    return true;
-}
-
-// s..e: a syntactically valid JSON number token.  is_int: no fraction/exponent.
-// Returns false when the value cannot be decided with the 19-digit window (flagged by caller).
-static __device__ bool dx_number_to_double(const uint8_t* s, const uint8_t* e, bool is_int, double* out) {
-    const uint8_t* p = s;
-    bool neg = false;
-    if (*p == '-') { neg = true; p++; }
-    uint64_t w = 0; int nd = 0; int dropped = 0; bool trunc_nz = false; int frac_digits = 0;
-    bool in_frac = false;
-    for (; p < e; p++) {
-        uint8_t c = *p;
-        if (c == '.') { in_frac = true; continue; }
-        if (c == 'e' || c == 'E') break;
-        uint32_t d = c - '0';
-        if (nd == 0 && d == 0) { if (in_frac) frac_digits++; continue; } // leading zeros carry no digits
-        if (nd < 19) { w = w * 10 + d; nd++; if (in_frac) frac_digits++; }
-        else { if (!in_frac) dropped++; if (d) trunc_nz = true; }
-    }
-    int exp10 = 0;
-    if (p < e) { // exponent
-        p++;
-        bool eneg = false;
-        if (*p == '+') p++; else if (*p == '-') { eneg = true; p++; }
-        int ev = 0;
-        for (; p < e; p++) { if (ev < 100000) ev = ev * 10 + (*p - '0'); }
-        exp10 = eneg ? -ev : ev;
-    }
-    exp10 += dropped - frac_digits;
-    if (w == 0) { *out = neg ? -0.0 : 0.0; if (is_int) *out = 0.0; return true; }
-    if (is_int && nd <= 18 && !trunc_nz && dropped == 0) {
-        // Jackson parses an integer token as int/long first; (double) of that long
-        long long v = neg ? -(long long)w : (long long)w;
-        *out = (double)v; return true;
-    }
-    double r;
-    if (!trunc_nz && w < (1ull << 53) && exp10 >= -22 && exp10 <= 22) {
-        r = (double)w;
-        if (exp10 < 0) r = r / dx_pow10_exact[-exp10]; else r = r * dx_pow10_exact[exp10];
-    } else {
-        uint64_t b1;
-        dx_eisel_lemire(w, exp10, &b1);
-        if (trunc_nz) {
-            uint64_t b2;
-            dx_eisel_lemire(w + 1, exp10, &b2);
-            if (b1 != b2) return false;
-        }
-        r = __longlong_as_double((long long)b1);
-    }
-    *out = neg ? -r : r;
-    return true;
-}
+#include "dx_numconv.cuh"
 
 // ------------------------------- general (any-JSON) parser ------------------------------
 struct GCur { const uint8_t* p; const uint8_t* end; };
