@@ -2,6 +2,7 @@
 #include "dx_common.h"
 #include "dx_abi_types.h"
 #include "dx_decode_host.h"
+#include "dx_flow.h"
 
 int dx_gen_device(dx_ctx* c, const dx_gen_params* g, int64_t first, int64_t n, uint8_t** bytes_out,
                   int64_t* n_bytes_out, int64_t** offsets_out);
@@ -138,7 +139,7 @@ int dx_table_column_to_host(const dx_table* h, int col, void* data, uint8_t* val
             // constant column: replicate on the host side of the ABI (sink hand-off convenience)
             for (int64_t i = 0; i < n; i++) {
                 if (k.type == DX_T_F64) reinterpret_cast<double*>(data)[i] = k.const_f;
-                else if (k.type == DX_T_STR) reinterpret_cast<int32_t*>(data)[i] = (int32_t)k.const_i;
+                else if (k.type == DX_T_STR) reinterpret_cast<int32_t*>(data)[i] = 0;   // constant string: one-entry dictionary
                 else reinterpret_cast<int64_t*>(data)[i] = k.const_i;
             }
         }
@@ -162,6 +163,7 @@ int dx_table_column_to_host(const dx_table* h, int col, void* data, uint8_t* val
 
 int dx_table_dict_size(const dx_table* h, int col, int64_t* n_codes) {
     const DxTable* t = T(h);
+    if (col >= 0 && col < (int)t->cols.size() && t->cols[col].type == DX_T_STR && !t->cols[col].data) { *n_codes = 1; return DX_OK; }
     if (col < 0 || col >= (int)t->cols.size() || !t->cols[col].dict) return t->ctx->set_error(DX_ERR_ARG, "not a dictionary column");
     cudaSetDevice(t->ctx->device);
     int rc = t->cols[col].dict->sync_to_host();
@@ -171,6 +173,9 @@ int dx_table_dict_size(const dx_table* h, int col, int64_t* n_codes) {
 }
 int dx_table_dict_string(const dx_table* h, int col, int64_t code, const char** bytes, int64_t* len) {
     const DxTable* t = T(h);
+    if (col >= 0 && col < (int)t->cols.size() && t->cols[col].type == DX_T_STR && !t->cols[col].data && code == 0) {
+        *bytes = t->cols[col].const_s.data(); *len = (int64_t)t->cols[col].const_s.size(); return DX_OK;
+    }
     if (col < 0 || col >= (int)t->cols.size() || !t->cols[col].dict) return t->ctx->set_error(DX_ERR_ARG, "not a dictionary column");
     const auto& hs = t->cols[col].dict->host_strings;
     if (code < 0 || code >= (int64_t)hs.size()) return t->ctx->set_error(DX_ERR_ARG, "dictionary code out of range (call dx_table_dict_size first)");
@@ -178,6 +183,101 @@ int dx_table_dict_string(const dx_table* h, int col, int64_t code, const char** 
     return DX_OK;
 }
 void dx_table_release(dx_table* h) { delete reinterpret_cast<TableHandle*>(h); }
+
+int dx_table_rule_count(const dx_table* h, int col) {
+    const DxTable* t = T(h);
+    if (col < 0 || col >= (int)t->cols.size() || !t->cols[col].aux) return 0;
+    return (int)static_cast<RuleTable*>(t->cols[col].aux.get())->rules.size();
+}
+static std::string json_escape(const std::string& s) {
+    std::string o;
+    for (unsigned char c : s) {
+        if (c == '"' || c == '\\') { o.push_back('\\'); o.push_back((char)c); }
+        else if (c < 0x20) { char b[8]; snprintf(b, sizeof b, "\\u%04x", c); o += b; }
+        else o.push_back((char)c);
+    }
+    return o;
+}
+int dx_table_rule_json(const dx_table* h, int col, int rule, const char** json, int64_t* len) {
+    const DxTable* t = T(h);
+    if (col < 0 || col >= (int)t->cols.size() || !t->cols[col].aux) return t->ctx->set_error(DX_ERR_ARG, "not a rule-flag column");
+    RuleTable* rt = static_cast<RuleTable*>(t->cols[col].aux.get());
+    if (rule < 0 || rule >= (int)rt->rules.size()) return t->ctx->set_error(DX_ERR_ARG, "rule index out of range");
+    static thread_local std::string buf;
+    buf = "{";
+    for (size_t i = 0; i < rt->rules[rule].size(); i++) {
+        if (i) buf += ",";
+        buf += "\"" + json_escape(rt->rules[rule][i].first) + "\":\"" + json_escape(rt->rules[rule][i].second) + "\"";
+    }
+    buf += "}";
+    *json = buf.c_str(); *len = (int64_t)buf.size();
+    return DX_OK;
+}
+
+// ---- flow ------------------------------------------------------------------------------------
+int dx_flow_create(dx_ctx* c, const char* conf_text, const char* schema_json, const char* const* projection_steps, int n_steps,
+                   const char* transform_text, dx_flow** out) {
+    if (!c || !schema_json || !out || n_steps < 0) return DX_ERR_ARG;
+    cudaSetDevice(c->device);
+    try { return dx_flow_build(c, conf_text, schema_json, projection_steps, n_steps, transform_text, out); }
+    catch (std::exception& e) { return c->set_error(DX_ERR_PARSE, e.what()); }
+}
+void dx_flow_destroy(dx_flow* f) { delete f; }
+int dx_flow_process_batch(dx_flow* f, const char* name_space, const uint8_t* json, int64_t n_bytes, const int64_t* offsets, int64_t n_events,
+                          int memory_kind, int64_t batch_time_ms, int64_t interval_ms, int64_t output_partition_time_ms, int64_t now_ms, dx_result** out) {
+    if (!f || !out || (n_bytes > 0 && !json)) return DX_ERR_ARG;
+    (void)output_partition_time_ms;   // consumed by the sinks on the host side of the boundary
+    cudaSetDevice(f->ctx->device);
+    try { return f->process(name_space ? name_space : "", json, n_bytes, offsets, n_events, memory_kind, batch_time_ms, interval_ms, now_ms, out); }
+    catch (std::exception& e) { return f->ctx->set_error(DX_ERR_STATE, e.what()); }
+}
+int dx_result_metrics(dx_result* r, const char* const** keys, const double** vals, int* n) {
+    *keys = r->metric_key_ptrs.data(); *vals = r->metric_vals.data(); *n = (int)r->metric_vals.size();
+    return DX_OK;
+}
+int dx_result_num_tables(const dx_result* r) { return (int)r->dataset_order.size(); }
+const char* dx_result_table_name(const dx_result* r, int i) { return (i >= 0 && i < (int)r->dataset_order.size()) ? r->dataset_order[i].c_str() : nullptr; }
+int dx_result_table(dx_result* r, const char* dataset, dx_table** out) {
+    auto it = r->datasets.find(dataset);
+    if (it == r->datasets.end()) return r->flow->ctx->set_error(DX_ERR_ARG, std::string("could not find data set name '") + dataset + "'");
+    *out = dx_wrap_table(it->second);
+    return DX_OK;
+}
+void dx_result_release(dx_result* r) { delete r; }
+int dx_flow_state_export(dx_flow* f, const char* table, dx_table** out, int* active_is_b) {
+    auto it = f->state_tables.find(table);
+    if (it == f->state_tables.end()) return f->ctx->set_error(DX_ERR_ARG, std::string("no state table '") + table + "'");
+    *out = dx_wrap_table(it->second.phys[it->second.active]);
+    if (active_is_b) *active_is_b = it->second.active;
+    return DX_OK;
+}
+
+// ---- host-side parsers -------------------------------------------------------------------------
+static int put_text(const std::string& s, char* buf, int64_t cap) {
+    if (cap <= 0) return DX_ERR_ARG;
+    size_t n = std::min<size_t>(s.size(), (size_t)cap - 1);
+    memcpy(buf, s.data(), n); buf[n] = 0;
+    return DX_OK;
+}
+int dx_sql_canonical(const char* sql, char* buf, int64_t cap) {
+    try { dxsql::Parser p(sql); auto st = p.statement(); return put_text(dxsql::to_string(st), buf, cap); }
+    catch (std::exception& e) { put_text(e.what(), buf, cap); return DX_ERR_PARSE; }
+}
+int dx_transform_split(const char* text, char* buf, int64_t cap) {
+    ParsedTransform pt; std::string err;
+    int rc = dx_parse_transform(text, &pt, &err);
+    if (rc) { put_text(err, buf, cap); return rc; }
+    std::string out;
+    for (auto& c : pt.commands) out += c.name + "\t" + (c.is_query ? "Query" : "Command") + "\t" + c.text + "\n";
+    for (auto& kv : pt.view_reference_count) out += "#ref\t" + kv.first + "\t" + std::to_string(kv.second) + "\n";
+    return put_text(out, buf, cap);
+}
+int dx_string_to_timestamp(const char* s, int64_t* us) {
+    long long v = 0;
+    if (!s || !dx_string_to_timestamp_us(s, &v)) return 0;
+    *us = v; return 1;
+}
+int64_t dx_duration_seconds(const char* s) { bool ok = false; long long v = dx_parse_duration_seconds(s ? s : "", &ok); return ok ? v : -1; }
 
 // ---- generator -----------------------------------------------------------------------------
 int dx_gen_events(dx_ctx* c, const dx_gen_params* p, int64_t first, int64_t n, uint8_t** bytes, int64_t* n_bytes, int64_t** offsets) {

@@ -1,0 +1,967 @@
+// dx_flow.cu — flow artefact loading, statement planning/execution and route() bookkeeping.
+// Reference call sites are listed in dx_flow.h; each function below names the lines it restates.
+#include "dx_flow.h"
+#include <cmath>
+#include <sstream>
+
+using namespace dxsql;
+
+// =======================================================================================
+// artefact loaders
+// =======================================================================================
+static std::string strip_bom(const std::string& s) {
+    if (s.size() >= 3 && (unsigned char)s[0] == 0xEF && (unsigned char)s[1] == 0xBB && (unsigned char)s[2] == 0xBF) return s.substr(3);
+    return s;
+}
+static std::string trim(const std::string& s) {
+    size_t a = 0, b = s.size();
+    while (a < b && isspace((unsigned char)s[a])) a++;
+    while (b > a && isspace((unsigned char)s[b - 1])) b--;
+    return s.substr(a, b - a);
+}
+static std::vector<std::string> split_lines(const std::string& text) {
+    std::vector<std::string> out; std::string cur;
+    for (char c : text) { if (c == '\n') { if (!cur.empty() && cur.back() == '\r') cur.pop_back(); out.push_back(cur); cur.clear(); } else cur.push_back(c); }
+    if (!cur.empty() && cur.back() == '\r') cur.pop_back();
+    out.push_back(cur);
+    return out;
+}
+
+// ConfigManager.loadConfig: "key=value" lines, '#' comments (reference: datax/config/ConfigManager.scala:98-135)
+static void parse_conf(const std::string& text, std::map<std::string, std::string>* out) {
+    for (auto& raw : split_lines(strip_bom(text))) {
+        std::string line = trim(raw);
+        if (line.empty() || line[0] == '#') continue;
+        size_t eq = line.find('=');
+        if (eq == std::string::npos || eq == 0) continue;
+        (*out)[trim(line.substr(0, eq))] = trim(line.substr(eq + 1));
+    }
+}
+
+// scala.concurrent.duration.Duration.create("5 minutes" | "60 second" | "1 hour" ...), as used by
+// TimeWindowHandler.scala:33-35,53 and SettingDictionary.scala:45-46.  Returns whole seconds
+// (route() only ever uses .toSeconds, CommonProcessorFactory.scala:161-163).
+long long dx_parse_duration_seconds(const std::string& s0, bool* ok) {
+    std::string s = trim(s0); *ok = false;
+    size_t i = 0; while (i < s.size() && (isdigit((unsigned char)s[i]) || s[i] == '.')) i++;
+    if (i == 0) return 0;
+    double v = atof(s.substr(0, i).c_str());
+    std::string u = lower(trim(s.substr(i)));
+    double mul;
+    if (u == "d" || u == "day" || u == "days") mul = 86400;
+    else if (u == "h" || u == "hr" || u == "hrs" || u == "hour" || u == "hours") mul = 3600;
+    else if (u == "m" || u == "min" || u == "mins" || u == "minute" || u == "minutes") mul = 60;
+    else if (u == "s" || u == "sec" || u == "secs" || u == "second" || u == "seconds") mul = 1;
+    else if (u == "ms" || u == "milli" || u == "millis" || u == "millisecond" || u == "milliseconds") mul = 1e-3;
+    else return 0;
+    *ok = true;
+    return (long long)std::floor(v * mul);
+}
+
+// TransformSQLParser.parse (reference: datax/sql/TransformSqlParser.scala:27-95), line by line.
+static bool word_boundary_contains(const std::string& text, const std::string& word) {
+    auto isw = [](char c) { return isalnum((unsigned char)c) || c == '_'; };
+    size_t pos = 0;
+    while ((pos = text.find(word, pos)) != std::string::npos) {
+        bool lb = pos == 0 || !isw(text[pos - 1]);
+        bool rb = pos + word.size() >= text.size() || !isw(text[pos + word.size()]);
+        if (lb && rb) return true;
+        pos++;
+    }
+    return false;
+}
+int dx_parse_transform(const std::string& text0, ParsedTransform* out, std::string* err) {
+    std::vector<std::string> buffer; std::string table_name; bool has_name = false;
+    std::vector<std::string> order;
+    auto append = [&](bool named) -> bool {
+        std::string sql;
+        for (auto& l : buffer) { if (l.empty()) continue; if (!sql.empty()) sql += " "; sql += l; }
+        SqlCommand c; c.text = sql; c.name = named ? table_name : ""; c.is_query = named;
+        out->commands.push_back(c);
+        if (named && !table_name.empty()) {
+            if (out->view_reference_count.count(table_name)) {
+                *err = "dataset name '" + table_name + "' has been created, please check the query to make sure it is not created again";
+                return false;
+            }
+            out->view_reference_count[table_name] = 0;
+            for (auto& kv : out->view_reference_count) if (word_boundary_contains(sql, kv.first)) kv.second++;
+        }
+        return true;
+    };
+    for (auto& line : split_lines(strip_bom(text0))) {
+        if (trim(line).empty()) continue;
+        if (line == "--DataXQuery--") {               // String.matches("^--DataXQuery--"): the whole line
+            if (!buffer.empty()) { if (!append(has_name)) return DX_ERR_PARSE; }
+            has_name = false; table_name.clear(); buffer.clear();
+            continue;
+        }
+        size_t k = 0; while (k < line.size() && isspace((unsigned char)line[k])) k++;
+        if (line.compare(k, 2, "--") == 0) continue;  // comment line
+        if (buffer.empty()) {
+            // ^\s*([a-zA-Z0-9_]+)\s*=(.*)$
+            size_t a = k, b = a;
+            while (b < line.size() && (isalnum((unsigned char)line[b]) || line[b] == '_')) b++;
+            size_t c = b; while (c < line.size() && isspace((unsigned char)line[c])) c++;
+            if (b > a && c < line.size() && line[c] == '=') {
+                table_name = line.substr(a, b - a); has_name = true;
+                buffer.push_back(trim(line.substr(c + 1)));
+            } else buffer.push_back(trim(line));
+        } else buffer.push_back(trim(line));
+    }
+    if (has_name && !buffer.empty()) { if (!append(true)) return DX_ERR_PARSE; }
+    return DX_OK;
+}
+
+// ---- stringToTimestamp (reference: datax/utility/ConcurrentDateFormat.scala:14-62), UTC session ----
+static long long days_from_civil(long long y, long long m, long long d) {
+    y -= m <= 2;
+    const long long era = (y >= 0 ? y : y - 399) / 400;
+    const long long yoe = y - era * 400;
+    const long long doy = (153 * (m + (m > 2 ? -3 : 9)) + 2) / 5 + d - 1;
+    const long long doe = yoe * 365 + yoe / 4 - yoe / 100 + doy;
+    return era * 146097 + doe - 719468;
+}
+static long long lenient_epoch_s(long long y, long long mo, long long d, long long h, long long mi, long long s) {
+    long long m0 = mo - 1;
+    long long yy = y + (m0 >= 0 ? m0 / 12 : -((11 - m0) / 12));
+    long long mm = ((m0 % 12) + 12) % 12 + 1;
+    return (days_from_civil(yy, mm, 1) + (d - 1)) * 86400 + h * 3600 + mi * 60 + s;
+}
+static bool parse_uint(const std::string& s, size_t& i, long long* v, int min_digits = 1, int max_digits = 18) {
+    size_t j = i; long long x = 0;
+    while (j < s.size() && isdigit((unsigned char)s[j]) && (int)(j - i) < max_digits) { x = x * 10 + (s[j] - '0'); j++; }
+    if ((int)(j - i) < min_digits) return false;
+    *v = x; i = j; return true;
+}
+static bool timestamp_value_of(const std::string& s0, long long* us) {      // java.sql.Timestamp.valueOf
+    std::string s = trim(s0);
+    size_t sp = s.find(' ');
+    if (sp == std::string::npos) return false;
+    std::string d = s.substr(0, sp), t = s.substr(sp + 1);
+    size_t d1 = d.find('-'), d2 = d1 == std::string::npos ? d1 : d.find('-', d1 + 1);
+    if (d1 == std::string::npos || d2 == std::string::npos || d1 != 4 || d2 - d1 - 1 < 1 || d2 - d1 - 1 > 2 ||
+        d.size() - d2 - 1 < 1 || d.size() - d2 - 1 > 2) return false;
+    for (size_t i = 0; i < d.size(); i++) if (i != d1 && i != d2 && !isdigit((unsigned char)d[i])) return false;
+    long long y = atoll(d.substr(0, 4).c_str()), mo = atoll(d.substr(d1 + 1, d2 - d1 - 1).c_str()), da = atoll(d.substr(d2 + 1).c_str());
+    size_t c1 = t.find(':'), c2 = c1 == std::string::npos ? c1 : t.find(':', c1 + 1);
+    if (c1 == std::string::npos || c2 == std::string::npos || c1 == 0 || c2 == c1 + 1 || c2 + 1 >= t.size()) return false;
+    size_t p = t.find('.', c2 + 1);
+    std::string hs = t.substr(0, c1), ms = t.substr(c1 + 1, c2 - c1 - 1);
+    std::string ss = p == std::string::npos ? t.substr(c2 + 1) : t.substr(c2 + 1, p - c2 - 1);
+    std::string fs = p == std::string::npos ? "" : t.substr(p + 1);
+    auto alld = [](const std::string& x) { if (x.empty()) return false; for (char c : x) if (!isdigit((unsigned char)c)) return false; return true; };
+    if (!alld(hs) || !alld(ms) || !alld(ss)) return false;
+    if (p != std::string::npos && (!alld(fs) || fs.size() > 9)) return false;
+    long long nanos = 0;
+    if (!fs.empty()) { std::string f = fs; while (f.size() < 9) f.push_back('0'); nanos = atoll(f.c_str()); }
+    *us = lenient_epoch_s(y, mo, da, atoll(hs.c_str()), atoll(ms.c_str()), atoll(ss.c_str())) * 1000000 + nanos / 1000;
+    return true;
+}
+static bool simple_date_format(const std::string& s, const char* pattern, long long* us) {   // lenient SimpleDateFormat.parse
+    long long y = 1970, mo = 1, d = 1, h = 0, mi = 0, se = 0;
+    size_t i = 0;
+    while (i < s.size() && isspace((unsigned char)s[i])) i++;   // DateFormat.parse skips nothing; kept strict below
+    i = 0;
+    for (const char* p = pattern; *p;) {
+        char c = *p;
+        if (c == '\'') { p++; while (*p && *p != '\'') { if (i >= s.size() || s[i] != *p) return false; i++; p++; } if (*p) p++; continue; }
+        if (c == 'y' || c == 'M' || c == 'd' || c == 'H' || c == 'm' || c == 's') {
+            while (*p == c) p++;
+            long long v; if (!parse_uint(s, i, &v)) return false;
+            if (c == 'y') y = v; else if (c == 'M') mo = v; else if (c == 'd') d = v; else if (c == 'H') h = v; else if (c == 'm') mi = v; else se = v;
+            continue;
+        }
+        if (i >= s.size() || s[i] != c) return false;
+        i++; p++;
+    }
+    *us = lenient_epoch_s(y, mo, d, h, mi, se) * 1000000;
+    return true;
+}
+bool dx_string_to_timestamp_us(const std::string& s, long long* out_us) {
+    if (s.empty()) return false;
+    if (timestamp_value_of(s, out_us)) return true;
+    if (simple_date_format(s, "yyyy-MM-dd'T'HH:mm:ss'Z'", out_us)) return true;
+    if (simple_date_format(s, "MM/dd/yyyy HH:mm:ss", out_us)) return true;
+    return false;
+}
+
+// =======================================================================================
+// table helpers
+// =======================================================================================
+static std::string last_part(const std::string& n) { size_t k = n.rfind('.'); return k == std::string::npos ? n : n.substr(k + 1); }
+
+__global__ void k_fill_i64(long long* p, long long n, long long v) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) p[i] = v;
+}
+__global__ void k_finalize(int mode, const unsigned long long* a, const unsigned long long* cnt, const unsigned long long* keynull, int keybit,
+                           long long n, void* out, int out_width, uint32_t* vmask32, int vbit) {
+    // mode 0: key copy (valid = !keynull bit); 1: accumulator copy, always valid; 2: accumulator copy, valid iff cnt>0;
+    // 3: average = sum_f / cnt
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        bool valid = true; unsigned long long v = a ? a[i] : 0;
+        if (mode == 0) valid = !((keynull[i] >> keybit) & 1ull);
+        else if (mode == 2) valid = cnt[i] > 0;
+        else if (mode == 3) { valid = cnt[i] > 0; double s = __longlong_as_double((long long)v); v = valid ? (unsigned long long)__double_as_longlong(s / (double)cnt[i]) : 0ull; }
+        if (!valid) v = 0;
+        if (out_width == 4) reinterpret_cast<int32_t*>(out)[i] = (int32_t)v; else reinterpret_cast<unsigned long long*>(out)[i] = v;
+        if (valid) atomicOr(&vmask32[i], 1u << vbit);
+    }
+}
+
+// Allocates the validity mask arrays for a freshly materialised table: one uint32 per row per
+// group of 32 columns, zeroed.
+struct MaskAlloc {
+    dx_ctx* ctx; int64_t n; std::vector<DevBufP> bufs;
+    MaskAlloc(dx_ctx* c, int64_t n_) : ctx(c), n(n_) {}
+    int assign(DxColumn* col, int index) {
+        size_t g = (size_t)index / 32;
+        while (bufs.size() <= g) {
+            DevBufP b = make_buf(ctx, (size_t)(n > 0 ? n : 1) * 4);
+            if (!b->p) return ctx->set_error(DX_ERR_CUDA, "mask allocation failed");
+            DX_CUDA(ctx, cudaMemsetAsync(b->p, 0, (size_t)(n > 0 ? n : 1) * 4, ctx->stream));
+            bufs.push_back(b);
+        }
+        col->vmask = bufs[g]; col->vwidth = 4; col->vbit = index % 32;
+        return DX_OK;
+    }
+};
+
+static ExprP ts_const(long long us) { auto e = std::make_shared<Expr>(); e->kind = EK::Func; e->sval = "__TS_US"; e->ival = us; return e; }
+
+// =======================================================================================
+// statement execution
+// =======================================================================================
+struct Exec {
+    dx_flow* F; dx_ctx* ctx;
+    std::map<std::string, View>* views;
+    long long now_us;
+    std::string stmt_name;
+
+    int fail(int code, const std::string& m) { return ctx->set_error(code, (stmt_name.empty() ? std::string() : "[" + stmt_name + "] ") + m); }
+
+    BindScope scope_for(const DxTable* t, const SelectCore& core) {
+        BindScope sc; sc.table = t; sc.now_us = now_us;
+        sc.qualifiers.push_back(core.from);
+        if (!core.from_alias.empty()) sc.qualifiers.push_back(core.from_alias);
+        return sc;
+    }
+
+    // WHERE (plus the view's time range) -> selection indices for one chunk.  sel == null && !filtered: all rows.
+    int chunk_selection(const View& v, const DxTableP& chunk, const SelectCore& core, DevBufP* sel, int64_t* n_sel, bool* filtered) {
+        ExprP cond = core.where;
+        if (v.ranged) {
+            auto col = std::make_shared<Expr>(); col->kind = EK::Col; col->parts = {v.ts_col};
+            auto ge = std::make_shared<Expr>(); ge->kind = EK::Bin; ge->sval = ">="; ge->args = {col, ts_const(v.lo_us)};
+            auto lt = std::make_shared<Expr>(); lt->kind = EK::Bin; lt->sval = "<"; lt->args = {col, ts_const(v.hi_us)};
+            auto rng = std::make_shared<Expr>(); rng->kind = EK::Bin; rng->sval = "AND"; rng->args = {ge, lt};
+            if (cond) { auto both = std::make_shared<Expr>(); both->kind = EK::Bin; both->sval = "AND"; both->args = {rng, cond}; cond = both; }
+            else cond = rng;
+        }
+        if (!cond) { *filtered = false; *n_sel = chunk->n_rows; return DX_OK; }
+        *filtered = true;
+        if (chunk->n_rows == 0) { *n_sel = 0; *sel = make_buf(ctx, 8); return DX_OK; }
+        ExprPrograms P; BindScope sc = scope_for(chunk.get(), core);
+        int rc = dx_compile_expr(ctx, sc, cond, &P); if (rc) return rc;
+        DevPrograms D; rc = dx_upload_programs(ctx, &P, &D); if (rc) return rc;
+        DevBuf flags(ctx, (size_t)chunk->n_rows * 4);
+        rc = dx_eval_flags(ctx, D, chunk->n_rows, nullptr, flags.as<uint32_t>(), 1); if (rc) return rc;
+        return dx_select_rows(ctx, flags.as<uint32_t>(), 1, chunk->n_rows, sel, n_sel);
+    }
+
+    static bool is_agg_func(const ExprP& e) {
+        if (e->kind != EK::Func) return false;
+        const std::string& f = e->sval;
+        return f == "COUNT" || f == "SUM" || f == "MIN" || f == "MAX" || f == "AVG";
+    }
+    static bool contains_agg(const ExprP& e) {
+        if (!e) return false;
+        if (is_agg_func(e)) return true;
+        for (auto& a : e->args) if (contains_agg(a)) return true;
+        return false;
+    }
+    static bool is_literal(const ExprP& e) { return e->kind == EK::Int || e->kind == EK::Dec || e->kind == EK::Str || e->kind == EK::Null || e->kind == EK::Bool; }
+
+    static std::string item_name(const SelectItem& it) {
+        if (!it.alias.empty()) return it.alias;
+        if (it.expr->kind == EK::Col) return it.expr->parts.back();
+        if (it.expr->kind == EK::Str) return it.expr->sval;
+        return to_string(it.expr);
+    }
+    static DxColumn literal_column(const ExprP& e, const std::string& name) {
+        DxColumn c; c.name = name; c.is_const = true;
+        switch (e->kind) {
+        case EK::Int: c.type = DX_T_I64; c.const_i = e->ival; break;
+        case EK::Dec: c.type = DX_T_F64; c.const_f = e->dval; break;
+        case EK::Bool: c.type = DX_T_BOOL; c.const_i = e->ival; break;
+        case EK::Str: c.type = DX_T_STR; c.const_s = e->sval; c.const_i = -1; break;
+        default: c.type = DX_T_NULL; c.all_null = true; break;
+        }
+        return c;
+    }
+
+    // filterNull(Array(IF(cond, MAP('k','v',...), NULL), ...)) and IF(cond, MAP(...), NULL):
+    // the rule-array shape emitted by CodegenRules (Engine.cs:232-266, 380-397; Rule.cs:272-281).
+    static bool match_rule_if(const ExprP& e, ExprP* cond, std::vector<std::pair<std::string, std::string>>* map) {
+        if (e->kind != EK::Func || e->sval != "IF" || e->args.size() != 3) return false;
+        if (e->args[2]->kind != EK::Null) return false;
+        const ExprP& m = e->args[1];
+        if (m->kind != EK::Func || m->sval != "MAP" || m->args.size() % 2) return false;
+        for (size_t i = 0; i < m->args.size(); i += 2) {
+            if (m->args[i]->kind != EK::Str) return false;
+            const ExprP& v = m->args[i + 1];
+            std::string sv;
+            if (v->kind == EK::Str) sv = v->sval; else if (v->kind == EK::Int) sv = std::to_string(v->ival); else if (v->kind == EK::Dec) sv = v->sval; else return false;
+            map->emplace_back(m->args[i]->sval, sv);
+        }
+        *cond = e->args[0];
+        return true;
+    }
+    static bool match_rules(const ExprP& e, std::vector<ExprP>* conds, std::shared_ptr<RuleTable>* rt) {
+        auto table = std::make_shared<RuleTable>();
+        ExprP c; std::vector<std::pair<std::string, std::string>> m;
+        if (match_rule_if(e, &c, &m)) { conds->push_back(c); table->rules.push_back(m); *rt = table; return true; }
+        if (e->kind != EK::Func || upper(e->sval) != "FILTERNULL" || e->args.size() != 1) return false;
+        const ExprP& arr = e->args[0];
+        if (arr->kind != EK::Func || arr->sval != "ARRAY") return false;
+        for (auto& a : arr->args) {
+            m.clear();
+            if (!match_rule_if(a, &c, &m)) return false;
+            conds->push_back(c); table->rules.push_back(m);
+        }
+        *rt = table;
+        return !conds->empty();
+    }
+
+    int exec_statement(const Statement& st, DxTableP* out) {
+        std::vector<DxTableP> parts;
+        for (auto& core : st.selects) { DxTableP t; int rc = exec_core(core, &t); if (rc) return rc; parts.push_back(t); }
+        if (parts.size() == 1) { *out = parts[0]; return DX_OK; }
+        DxTableP u; int rc = concat(parts, &u); if (rc) return rc;
+        bool any_distinct = false; for (bool a : st.union_all) if (!a) any_distinct = true;
+        if (!any_distinct) { *out = u; return DX_OK; }
+        // UNION = UNION ALL + DISTINCT over all columns
+        View v; v.chunks.push_back(u);
+        (*views)["__union"] = v;
+        SelectCore d; d.distinct = true; d.from = "__union";
+        SelectItem star; star.expr = std::make_shared<Expr>(); star.expr->kind = EK::Star; d.items.push_back(star);
+        rc = exec_core(d, out);
+        views->erase("__union");
+        return rc;
+    }
+
+    // positional concatenation (UNION ALL): same arity, compatible physical types
+    int concat(const std::vector<DxTableP>& parts, DxTableP* out) {
+        size_t nc = parts[0]->cols.size(); int64_t total = 0;
+        for (auto& p : parts) { if (p->cols.size() != nc) return fail(DX_ERR_UNSUPPORTED, "UNION branches have different column counts"); total += p->n_rows; }
+        auto t = std::make_shared<DxTable>(); t->ctx = ctx; t->n_rows = total;
+        MaskAlloc masks(ctx, total);
+        for (size_t c = 0; c < nc; c++) {
+            DxColumn oc; oc.name = parts[0]->cols[c].name;
+            int type = DX_T_NULL; DxDictP dict; bool all_const_same = true;
+            for (auto& p : parts) {
+                const DxColumn& pc = p->cols[c];
+                if (pc.type == DX_T_NULL || pc.all_null) continue;
+                if (type == DX_T_NULL) type = pc.type;
+                else if (type != pc.type) {
+                    bool il = (type == DX_T_I64 || type == DX_T_BOOL) && (pc.type == DX_T_I64 || pc.type == DX_T_BOOL);
+                    if (!il) return fail(DX_ERR_UNSUPPORTED, "UNION column '" + oc.name + "' mixes types");
+                }
+                if (pc.type == DX_T_STR && pc.data && p->n_rows > 0) {
+                    if (dict && dict != pc.dict) return fail(DX_ERR_UNSUPPORTED, "UNION of string columns from different dictionaries");
+                    dict = pc.dict;
+                }
+                if (pc.type == DX_T_FLAGS) return fail(DX_ERR_UNSUPPORTED, "UNION over a rule-flag column");
+            }
+            (void)all_const_same;
+            oc.type = type;
+            if (type == DX_T_NULL) { oc.all_null = true; t->cols.push_back(oc); continue; }
+            oc.dict = dict;
+            int w = dx_type_width(type);
+            oc.data = make_buf(ctx, (size_t)(total > 0 ? total : 1) * w);
+            int rc = masks.assign(&oc, (int)c); if (rc) return rc;
+            int64_t off = 0;
+            for (auto& p : parts) {
+                const DxColumn& pc = p->cols[c];
+                if (p->n_rows == 0) continue;
+                uint8_t* dst = oc.data->as<uint8_t>() + (size_t)off * w;
+                uint32_t* vm = oc.vmask->as<uint32_t>() + off;
+                if (pc.type == DX_T_NULL || pc.all_null) { DX_CUDA(ctx, cudaMemsetAsync(dst, 0, (size_t)p->n_rows * w, ctx->stream)); }
+                else if (!pc.data) {
+                    DxColumn tmp = pc;
+                    rc = materialize_const(&tmp, p->n_rows, dict); if (rc) return rc;
+                    rc = dx_gather_column(ctx, tmp, p->n_rows, nullptr, dst, vm, oc.vbit); if (rc) return rc;
+                } else { rc = dx_gather_column(ctx, pc, p->n_rows, nullptr, dst, vm, oc.vbit); if (rc) return rc; }
+                off += p->n_rows;
+            }
+            t->cols.push_back(oc);
+        }
+        *out = t; return DX_OK;
+    }
+
+    // turns a constant column into a materialised one (needed when it meets real columns in a UNION / as a group key)
+    int materialize_const(DxColumn* c, int64_t n, DxDictP dict) {
+        long long v = c->const_i;
+        if (c->type == DX_T_F64) memcpy(&v, &c->const_f, 8);
+        if (c->type == DX_T_STR) {
+            if (!dict) { dict = std::make_shared<DxDict>(); int rc = dict->init(ctx, 1024, 1 << 16); if (rc) return rc; }
+            int32_t code; int rc = dict->insert_host(c->const_s, &code); if (rc) return rc;
+            v = code; c->dict = dict;
+        }
+        // physical width 8 for the fill, then narrowed for dictionary codes
+        DevBufP b = make_buf(ctx, (size_t)(n > 0 ? n : 1) * 8);
+        if (n > 0) { k_fill_i64<<<(unsigned)std::min<long long>((n + 255) / 256, 4096), 256, 0, ctx->stream>>>(b->as<long long>(), n, v); ctx->launches["k_fill"]++; }
+        if (c->type == DX_T_STR && n > 0) {
+            DevBufP b4 = make_buf(ctx, (size_t)n * 4);
+            DxColumn wide; wide.type = DX_T_I64; wide.data = b;
+            // narrow by gathering through the 8-byte view
+            std::vector<int32_t> host((size_t)n, (int32_t)v);
+            DX_CUDA(ctx, cudaMemcpyAsync(b4->p, host.data(), (size_t)n * 4, cudaMemcpyHostToDevice, ctx->stream));
+            DX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+            b = b4;
+        }
+        c->data = b; c->is_const = false; c->vmask = nullptr;
+        return DX_OK;
+    }
+
+    int exec_core(const SelectCore& core, DxTableP* out) {
+        auto vit = views->find(core.from);
+        if (vit == views->end()) return fail(DX_ERR_ARG, "table or view '" + core.from + "' not found");
+        if (!core.joins.empty()) return fail(DX_ERR_UNSUPPORTED, "JOIN is not yet inside the supported SQL subset");
+        const View& v = vit->second;
+        if (v.chunks.empty()) return fail(DX_ERR_STATE, "view '" + core.from + "' has no data");
+        bool agg = core.distinct || !core.group_by.empty();
+        for (auto& it : core.items) if (contains_agg(it.expr)) agg = true;
+        return agg ? exec_agg(core, v, out) : exec_plain(core, v, out);
+    }
+
+    // ---------------- SELECT without aggregation: filter + project ----------------
+    int exec_plain(const SelectCore& core, const View& v, DxTableP* out) {
+        struct ChunkSel { DevBufP sel; int64_t n = 0; bool filtered = false; };
+        std::vector<ChunkSel> cs(v.chunks.size());
+        int64_t total = 0;
+        for (size_t k = 0; k < v.chunks.size(); k++) {
+            int rc = chunk_selection(v, v.chunks[k], core, &cs[k].sel, &cs[k].n, &cs[k].filtered); if (rc) return rc;
+            total += cs[k].n;
+        }
+        const bool zero_copy = v.chunks.size() == 1 && !cs[0].filtered;
+        auto t = std::make_shared<DxTable>(); t->ctx = ctx; t->n_rows = total;
+        MaskAlloc masks(ctx, total);
+        const DxTable* proto = v.chunks[0].get();
+        int out_index = 0;
+        for (auto& it : core.items) {
+            const ExprP& e = it.expr;
+            std::vector<int> src_cols;   // columns forwarded as they are
+            if (e->kind == EK::Star) {
+                if (e->parts.empty() || e->parts[0] == core.from || e->parts[0] == core.from_alias || (e->parts.size() == 1 && e->parts[0] == "Raw"))
+                    for (size_t c = 0; c < proto->cols.size(); c++) src_cols.push_back((int)c);
+                else {
+                    std::string prefix; for (auto& p : e->parts) prefix += p + ".";
+                    if (prefix.compare(0, 4, "Raw.") == 0) prefix = prefix.substr(4);
+                    for (size_t c = 0; c < proto->cols.size(); c++) if (proto->cols[c].name.compare(0, prefix.size(), prefix) == 0) src_cols.push_back((int)c);
+                    if (src_cols.empty()) return fail(DX_ERR_ARG, "cannot expand '" + to_string(e) + "'");
+                }
+            } else if (e->kind == EK::Col) {
+                BindScope sc = scope_for(proto, core); sc.qualifiers.push_back("Raw");
+                std::string err; int ci = dx_resolve_column(sc, e->parts, &err);
+                if (ci < 0) {
+                    // transport metadata the ABI does not carry: NULL columns
+                    const std::string& n0 = e->parts[0];
+                    if (n0 == "Properties" || n0 == "SystemProperties" || n0 == "__DataX_FileInfo" || n0 == "DataXProperties") {
+                        DxColumn c; c.name = item_name(it); c.type = DX_T_NULL; c.all_null = true; t->cols.push_back(c); out_index++; continue;
+                    }
+                    return fail(DX_ERR_ARG, err);
+                }
+                src_cols.push_back(ci);
+            }
+            if (!src_cols.empty()) {
+                for (int ci : src_cols) {
+                    DxColumn oc = proto->cols[ci];
+                    if (e->kind == EK::Col) oc.name = item_name(it);
+                    if (!(oc.all_null || !oc.data || zero_copy)) {
+                        const int words = oc.type == DX_T_FLAGS ? oc.flag_words : 1;
+                        const int w = oc.type == DX_T_FLAGS ? 4 : dx_type_width(oc.type);
+                        DevBufP nb = make_buf(ctx, (size_t)(total > 0 ? total : 1) * w * words);
+                        DxColumn dst = oc; dst.data = nb;
+                        int rc = masks.assign(&dst, out_index); if (rc) return rc;
+                        int64_t off = 0;
+                        for (size_t k = 0; k < v.chunks.size(); k++) {
+                            const DxColumn& sc = v.chunks[k]->cols[ci];
+                            if (cs[k].n == 0) continue;
+                            for (int wd = 0; wd < words; wd++) {
+                                DxColumn view = sc;
+                                if (oc.type == DX_T_FLAGS) {
+                                    // word-major bitmap: gather each word plane as a 4-byte column
+                                    view.type = DX_T_STR; view.vmask = nullptr;
+                                    auto alias = std::make_shared<DevBuf>(); alias->p = sc.data->as<uint8_t>() + (size_t)wd * v.chunks[k]->n_rows * 4;
+                                    view.data = alias;   // non-owning (ctx == nullptr => no release)
+                                }
+                                int rc2 = dx_gather_column(ctx, view, cs[k].n, cs[k].filtered ? cs[k].sel->as<int64_t>() : nullptr,
+                                                           nb->as<uint8_t>() + ((size_t)wd * total + off) * w, dst.vmask->as<uint32_t>() + off, dst.vbit);
+                                if (rc2) return rc2;
+                            }
+                            off += cs[k].n;
+                        }
+                        oc = dst;
+                    }
+                    t->cols.push_back(oc); out_index++;
+                }
+                continue;
+            }
+            if (is_literal(e)) { t->cols.push_back(literal_column(e, item_name(it))); out_index++; continue; }
+            // rule arrays -> flag bitmap column
+            std::vector<ExprP> conds; std::shared_ptr<RuleTable> rt;
+            if (match_rules(e, &conds, &rt)) {
+                DxColumn oc; oc.name = item_name(it); oc.type = DX_T_FLAGS; oc.flag_words = ((int)conds.size() + 31) / 32; oc.aux = rt;
+                oc.data = make_buf(ctx, (size_t)(total > 0 ? total : 1) * 4 * oc.flag_words);
+                int64_t off = 0;
+                for (size_t k = 0; k < v.chunks.size(); k++) {
+                    if (cs[k].n == 0) continue;
+                    if (v.chunks.size() > 1) return fail(DX_ERR_UNSUPPORTED, "rule evaluation over a multi-batch window view");
+                    ExprPrograms P; BindScope sc = scope_for(v.chunks[k].get(), core);
+                    for (auto& c : conds) { int rc = dx_compile_expr(ctx, sc, c, &P); if (rc) return rc; }
+                    DevPrograms D; int rc = dx_upload_programs(ctx, &P, &D); if (rc) return rc;
+                    rc = dx_eval_flags(ctx, D, cs[k].n, cs[k].filtered ? cs[k].sel->as<int64_t>() : nullptr, oc.data->as<uint32_t>() + off, oc.flag_words);
+                    if (rc) return rc;
+                    off += cs[k].n;
+                }
+                t->cols.push_back(oc); out_index++; continue;
+            }
+            // computed column
+            {
+                DxColumn oc; oc.name = item_name(it);
+                int rtype = 0; DevBufP data; int64_t off = 0;
+                for (size_t k = 0; k < v.chunks.size(); k++) {
+                    ExprPrograms P; BindScope sc = scope_for(v.chunks[k].get(), core); sc.qualifiers.push_back("Raw");
+                    int rc = compile_scalar(sc, e, &P); if (rc) return rc;
+                    if (k == 0) {
+                        rtype = P.result_type[0]; if (rtype == DX_T_NULL) rtype = DX_T_I64;
+                        data = make_buf(ctx, (size_t)(total > 0 ? total : 1) * dx_type_width(rtype));
+                        oc.type = rtype; oc.data = data; oc.dict = P.result_dict[0];
+                        rc = masks.assign(&oc, out_index); if (rc) return rc;
+                    }
+                    if (cs[k].n == 0) continue;
+                    DevPrograms D; rc = dx_upload_programs(ctx, &P, &D); if (rc) return rc;
+                    rc = dx_eval_column(ctx, D, 0, cs[k].n, cs[k].filtered ? cs[k].sel->as<int64_t>() : nullptr,
+                                        data->as<uint8_t>() + (size_t)off * dx_type_width(rtype), dx_type_width(rtype), oc.vmask->as<uint32_t>() + off, oc.vbit);
+                    if (rc) return rc;
+                    off += cs[k].n;
+                }
+                t->cols.push_back(oc); out_index++;
+            }
+        }
+        *out = t; return DX_OK;
+    }
+
+    // scalar expression with the two host-assisted built-ins handled here
+    int compile_scalar(const BindScope& sc, const ExprP& e, ExprPrograms* P) {
+        return dx_compile_expr(ctx, sc, e, P);
+    }
+
+    // ---------------- GROUP BY / DISTINCT / aggregates ----------------
+    struct KeySpec { ExprP expr; int src_col = -1; bool is_const = false; DxColumn const_col; };
+    struct AggSpec { std::string func; ExprP arg; bool star = false; int val_index = -1; int acc = -1, acc_cnt = -1; int arg_type = 0; };
+
+    int exec_agg(const SelectCore& core, const View& v, DxTableP* out) {
+        const DxTable* proto = v.chunks[0].get();
+        BindScope psc = scope_for(proto, core);
+        // expand the select list ('*' only makes sense with DISTINCT)
+        std::vector<SelectItem> items;
+        for (auto& it : core.items) {
+            if (it.expr->kind == EK::Star) {
+                for (size_t c = 0; c < proto->cols.size(); c++) {
+                    SelectItem s; s.expr = std::make_shared<Expr>(); s.expr->kind = EK::Col; s.expr->parts = {proto->cols[c].name}; s.alias = proto->cols[c].name;
+                    items.push_back(s);
+                }
+            } else items.push_back(it);
+        }
+        // group expressions: source columns first, then select aliases (spark.sql.groupByAliases)
+        std::vector<ExprP> gexprs;
+        if (!core.group_by.empty()) {
+            for (auto& g : core.group_by) {
+                ExprP ge = g;
+                if (g->kind == EK::Col) {
+                    std::string err; int ci = dx_resolve_column(psc, g->parts, &err);
+                    if (ci < 0 && g->parts.size() == 1) {
+                        for (auto& it : items) if (item_name(it) == g->parts[0] && !contains_agg(it.expr)) { ge = it.expr; break; }
+                    }
+                }
+                gexprs.push_back(ge);
+            }
+        } else if (core.distinct) {
+            for (auto& it : items) { if (contains_agg(it.expr)) return fail(DX_ERR_UNSUPPORTED, "DISTINCT with aggregates"); gexprs.push_back(it.expr); }
+        }
+        std::vector<KeySpec> keys;
+        for (auto& ge : gexprs) {
+            KeySpec k; k.expr = ge;
+            if (is_literal(ge)) { k.is_const = true; k.const_col = literal_column(ge, ""); }
+            else if (ge->kind == EK::Col) {
+                std::string err; int ci = dx_resolve_column(psc, ge->parts, &err);
+                if (ci < 0) return fail(DX_ERR_ARG, err);
+                const DxColumn& c = proto->cols[ci];
+                if (c.type == DX_T_FLAGS) return fail(DX_ERR_UNSUPPORTED, "grouping by a rule-flag column");
+                if (!c.data || c.all_null) { k.is_const = true; k.const_col = c; } else k.src_col = ci;
+            }
+            keys.push_back(k);
+        }
+        // aggregates and the mapping of every select item
+        std::vector<AggSpec> aggs; std::vector<ExprP> val_exprs; std::vector<AggAccDesc> accs;
+        struct ItemMap { int key = -1; int agg = -1; bool literal = false; };
+        std::vector<ItemMap> imap(items.size());
+        auto add_acc = [&](int kind, int col) { for (size_t a = 0; a < accs.size(); a++) if (accs[a].kind == kind && accs[a].col == col) return (int)a; accs.push_back({kind, col}); return (int)accs.size() - 1; };
+        for (size_t i = 0; i < items.size(); i++) {
+            const ExprP& e = items[i].expr;
+            if (is_agg_func(e)) {
+                AggSpec a; a.func = e->sval;
+                if (e->distinct) return fail(DX_ERR_UNSUPPORTED, "COUNT(DISTINCT ...) is not yet inside the supported subset");
+                if (e->star_arg || (a.func == "COUNT" && e->args.size() == 1 && is_literal(e->args[0]) && e->args[0]->kind != EK::Null)) { a.star = true; a.acc = add_acc(ACC_COUNT_STAR, -1); }
+                else {
+                    if (e->args.size() != 1) return fail(DX_ERR_UNSUPPORTED, a.func + " needs one argument");
+                    a.arg = e->args[0];
+                    int vi = -1; std::string key = to_string(a.arg);
+                    for (size_t k2 = 0; k2 < val_exprs.size(); k2++) if (to_string(val_exprs[k2]) == key) vi = (int)k2;
+                    if (vi < 0) { val_exprs.push_back(a.arg); vi = (int)val_exprs.size() - 1; }
+                    a.val_index = vi;
+                }
+                aggs.push_back(a); imap[i].agg = (int)aggs.size() - 1;
+            } else if (contains_agg(e)) return fail(DX_ERR_UNSUPPORTED, "expressions over aggregates: '" + to_string(e) + "'");
+            else {
+                std::string key = to_string(e); int hit = -1;
+                for (size_t k2 = 0; k2 < keys.size(); k2++) if (to_string(keys[k2].expr) == key) hit = (int)k2;
+                if (hit < 0 && e->kind == EK::Col) {   // same column under another spelling
+                    std::string err; int ci = dx_resolve_column(psc, e->parts, &err);
+                    for (size_t k2 = 0; k2 < keys.size(); k2++) if (ci >= 0 && keys[k2].src_col == ci) hit = (int)k2;
+                }
+                if (hit >= 0) imap[i].key = hit;
+                else if (is_literal(e)) imap[i].literal = true;
+                else return fail(DX_ERR_ARG, "'" + key + "' is neither aggregated nor in GROUP BY");
+            }
+        }
+        if ((int)val_exprs.size() > DX_AGG_MAX_ACCS) return fail(DX_ERR_UNSUPPORTED, "too many aggregate arguments");
+        // type the aggregate arguments against the first chunk
+        std::vector<int> val_type(val_exprs.size()), val_src(val_exprs.size(), -1);
+        std::vector<DxDictP> val_dict(val_exprs.size());
+        for (size_t k2 = 0; k2 < val_exprs.size(); k2++) {
+            if (val_exprs[k2]->kind == EK::Col) {
+                std::string err; int ci = dx_resolve_column(psc, val_exprs[k2]->parts, &err);
+                if (ci < 0) return fail(DX_ERR_ARG, err);
+                if (proto->cols[ci].data && !proto->cols[ci].all_null) { val_src[k2] = ci; val_type[k2] = proto->cols[ci].type; val_dict[k2] = proto->cols[ci].dict; continue; }
+            }
+            ExprPrograms P; int rc = dx_compile_expr(ctx, psc, val_exprs[k2], &P); if (rc) return rc;
+            val_type[k2] = P.result_type[0] == DX_T_NULL ? DX_T_I64 : P.result_type[0];
+        }
+        for (auto& a : aggs) {
+            if (a.star) continue;
+            const int vt = val_type[a.val_index]; a.arg_type = vt;
+            const bool f = vt == DX_T_F64;
+            a.acc_cnt = add_acc(ACC_COUNT, a.val_index);
+            if (a.func == "COUNT") a.acc = a.acc_cnt;
+            else if (vt == DX_T_STR) return fail(DX_ERR_UNSUPPORTED, a.func + " over a string column");
+            else if (a.func == "SUM") a.acc = add_acc(f ? ACC_SUM_F : ACC_SUM_I, a.val_index);
+            else if (a.func == "AVG") {
+                if (f) a.acc = add_acc(ACC_SUM_F, a.val_index);
+                else {   // AVG(long) accumulates CAST(x AS DOUBLE): a derived double value column
+                    auto cast = std::make_shared<Expr>(); cast->kind = EK::Cast; cast->sval = "double"; cast->args = {val_exprs[a.val_index]};
+                    val_exprs.push_back(cast); val_type.push_back(DX_T_F64); val_src.push_back(-1); val_dict.push_back(nullptr);
+                    a.acc = add_acc(ACC_SUM_F, (int)val_exprs.size() - 1);
+                }
+            }
+            else if (a.func == "MIN") a.acc = add_acc(f ? ACC_MIN_F : ACC_MIN_I, a.val_index);
+            else if (a.func == "MAX") a.acc = add_acc(f ? ACC_MAX_F : ACC_MAX_I, a.val_index);
+        }
+        if (accs.empty()) accs.push_back({ACC_COUNT_STAR, -1});
+        std::vector<int> hashed;   // keys that take part in hashing
+        for (size_t k2 = 0; k2 < keys.size(); k2++) if (!keys[k2].is_const) hashed.push_back((int)k2);
+        if ((int)hashed.size() > DX_AGG_MAX_KEYS) return fail(DX_ERR_UNSUPPORTED, "more than 8 group-by keys");
+
+        // selections per chunk
+        struct ChunkSel { DevBufP sel; int64_t n = 0; bool filtered = false; };
+        std::vector<ChunkSel> cs(v.chunks.size()); int64_t total = 0;
+        for (size_t k = 0; k < v.chunks.size(); k++) {
+            int rc = chunk_selection(v, v.chunks[k], core, &cs[k].sel, &cs[k].n, &cs[k].filtered); if (rc) return rc;
+            total += cs[k].n;
+        }
+        unsigned long long cap = 1024;
+        auto hint = F->agg_capacity_hint.find(stmt_name);
+        if (hint != F->agg_capacity_hint.end()) cap = hint->second;
+        else { unsigned long long want = (unsigned long long)std::min<int64_t>(total, 1 << 22) * 2; while (cap < want) cap <<= 1; }
+        AggTable T; unsigned long long n_groups = 0;
+        std::vector<int> key_type(keys.size(), DX_T_I64); std::vector<DxDictP> key_dict(keys.size());
+        for (int attempt = 0;; attempt++) {
+            int rc = T.init(ctx, (int)hashed.size(), (int)val_exprs.size(), accs, cap); if (rc) return rc;
+            for (size_t k = 0; k < v.chunks.size(); k++) {
+                if (cs[k].n == 0) continue;
+                const DxTable* ch = v.chunks[k].get();
+                BindScope sc = scope_for(ch, core);
+                AggInput in; memset(&in, 0, sizeof in);
+                in.sel = cs[k].filtered ? cs[k].sel->as<long long>() : nullptr; in.n_rows = cs[k].n;
+                std::vector<DevBufP> temps; DevBufP tmask;
+                auto col_desc = [&](const DxColumn& c) { ProgCol pc; pc.data = c.data->p; pc.vmask = c.vmask ? c.vmask->p : nullptr; pc.vwidth = c.vwidth; pc.vbit = c.vbit; pc.width = dx_type_width(c.type); pc.pad = 0; return pc; };
+                auto eval_temp = [&](const ExprP& e, int* type_out, ProgCol* pc) -> int {
+                    ExprPrograms P; int rc2 = dx_compile_expr(ctx, sc, e, &P); if (rc2) return rc2;
+                    DevPrograms D; rc2 = dx_upload_programs(ctx, &P, &D); if (rc2) return rc2;
+                    int ty = P.result_type[0] == DX_T_NULL ? DX_T_I64 : P.result_type[0];
+                    DevBufP b = make_buf(ctx, (size_t)ch->n_rows * dx_type_width(ty)); temps.push_back(b);
+                    if (!tmask) { tmask = make_buf(ctx, (size_t)ch->n_rows * 4); DX_CUDA(ctx, cudaMemsetAsync(tmask->p, 0, (size_t)ch->n_rows * 4, ctx->stream)); }
+                    int bit = (int)temps.size() - 1;
+                    if (bit >= 32) return fail(DX_ERR_UNSUPPORTED, "too many computed group/aggregate expressions");
+                    rc2 = dx_eval_column(ctx, D, 0, ch->n_rows, nullptr, b->p, dx_type_width(ty), tmask->as<uint32_t>(), bit); if (rc2) return rc2;
+                    pc->data = b->p; pc->vmask = tmask->p; pc->vwidth = 4; pc->vbit = bit; pc->width = dx_type_width(ty); pc->pad = 0;
+                    *type_out = ty; return DX_OK;
+                };
+                for (size_t hk = 0; hk < hashed.size(); hk++) {
+                    KeySpec& ks = keys[hashed[hk]];
+                    if (ks.expr->kind == EK::Col) {
+                        std::string err; int ci = dx_resolve_column(sc, ks.expr->parts, &err);
+                        if (ci < 0) return fail(DX_ERR_ARG, err);
+                        const DxColumn& c = ch->cols[ci];
+                        if (!c.data) return fail(DX_ERR_UNSUPPORTED, "group key constant in one batch and materialised in another");
+                        in.keys[hk] = col_desc(c); key_type[hashed[hk]] = c.type;
+                        if (c.type == DX_T_STR) {
+                            if (key_dict[hashed[hk]] && key_dict[hashed[hk]] != c.dict) return fail(DX_ERR_UNSUPPORTED, "group key dictionaries differ between batches");
+                            key_dict[hashed[hk]] = c.dict;
+                        }
+                    } else { int ty; rc = eval_temp(ks.expr, &ty, &in.keys[hk]); if (rc) return rc; key_type[hashed[hk]] = ty; }
+                }
+                for (size_t vi = 0; vi < val_exprs.size(); vi++) {
+                    bool done = false;
+                    if (val_exprs[vi]->kind == EK::Col) {
+                        std::string err; int ci = dx_resolve_column(sc, val_exprs[vi]->parts, &err);
+                        if (ci >= 0 && ch->cols[ci].data && !ch->cols[ci].all_null) { in.vals[vi] = col_desc(ch->cols[ci]); done = true; }
+                    }
+                    if (!done) { int ty; rc = eval_temp(val_exprs[vi], &ty, &in.vals[vi]); if (rc) return rc; }
+                }
+                rc = T.update(in); if (rc) return rc;
+                DX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));   // temps die with this scope
+            }
+            bool overflow = false;
+            rc = T.finish(&n_groups, &overflow); if (rc) return rc;
+            if (!overflow) break;
+            if (attempt > 12) return fail(DX_ERR_CAPACITY, "aggregation table overflow");
+            cap = T.capacity * 4;
+        }
+        if (!stmt_name.empty()) { unsigned long long h = 1024; while (h < n_groups * 2 + 16) h <<= 1; F->agg_capacity_hint[stmt_name] = std::max(h, std::min(T.capacity, h * 2)); }
+
+        // global aggregate over zero rows -> one row (count 0, others NULL)
+        const bool global = core.group_by.empty() && !core.distinct;
+        int64_t n_out = (int64_t)n_groups;
+        const bool synth = global && n_groups == 0;
+        if (synth) n_out = 1;
+        // pull the groups out
+        std::vector<DevBufP> kbufs(hashed.size()), abufs(accs.size());
+        DevBufP knull = make_buf(ctx, (size_t)(n_out > 0 ? n_out : 1) * 8);
+        long long* kptr[DX_AGG_MAX_KEYS]; unsigned long long* aptr[DX_AGG_MAX_ACCS];
+        for (size_t k = 0; k < hashed.size(); k++) { kbufs[k] = make_buf(ctx, (size_t)(n_out > 0 ? n_out : 1) * 8); kptr[k] = kbufs[k]->as<long long>(); }
+        for (size_t a = 0; a < accs.size(); a++) { abufs[a] = make_buf(ctx, (size_t)(n_out > 0 ? n_out : 1) * 8); aptr[a] = abufs[a]->as<unsigned long long>(); }
+        if (synth) {
+            DX_CUDA(ctx, cudaMemsetAsync(knull->p, 0, 8, ctx->stream));
+            for (auto& b : abufs) DX_CUDA(ctx, cudaMemsetAsync(b->p, 0, 8, ctx->stream));
+        } else { int rc = T.extract(n_groups, kptr, knull->as<unsigned long long>(), aptr); if (rc) return rc; }
+
+        auto t = std::make_shared<DxTable>(); t->ctx = ctx; t->n_rows = n_out;
+        MaskAlloc masks(ctx, n_out);
+        auto finalize = [&](int mode, const unsigned long long* a, const unsigned long long* cnt, int keybit, DxColumn* oc, int index) -> int {
+            int w = dx_type_width(oc->type);
+            oc->data = make_buf(ctx, (size_t)(n_out > 0 ? n_out : 1) * w);
+            int rc = masks.assign(oc, index); if (rc) return rc;
+            if (n_out > 0) {
+                k_finalize<<<(unsigned)std::min<long long>((n_out + 255) / 256, 8192), 256, 0, ctx->stream>>>(mode, a, cnt, knull->as<unsigned long long>(), keybit, n_out,
+                    oc->data->p, w, oc->vmask->as<uint32_t>(), oc->vbit);
+                ctx->launches["k_finalize"]++;
+            }
+            return DX_OK;
+        };
+        for (size_t i = 0; i < items.size(); i++) {
+            DxColumn oc; oc.name = item_name(items[i]);
+            if (imap[i].literal) { oc = literal_column(items[i].expr, oc.name); t->cols.push_back(oc); continue; }
+            if (imap[i].key >= 0) {
+                KeySpec& ks = keys[imap[i].key];
+                if (ks.is_const) { DxColumn c = ks.const_col; c.name = oc.name; t->cols.push_back(c); continue; }
+                int hk = (int)(std::find(hashed.begin(), hashed.end(), imap[i].key) - hashed.begin());
+                oc.type = key_type[imap[i].key]; oc.dict = key_dict[imap[i].key];
+                int rc = finalize(0, reinterpret_cast<unsigned long long*>(kptr[hk]), nullptr, hk, &oc, (int)i); if (rc) return rc;
+                t->cols.push_back(oc); continue;
+            }
+            const AggSpec& a = aggs[imap[i].agg];
+            int rc;
+            if (a.func == "COUNT") { oc.type = DX_T_I64; rc = finalize(1, aptr[a.acc], nullptr, 0, &oc, (int)i); }
+            else if (a.func == "AVG") { oc.type = DX_T_F64; rc = finalize(3, aptr[a.acc], aptr[a.acc_cnt], 0, &oc, (int)i); }
+            else { oc.type = (a.func == "SUM" && a.arg_type != DX_T_F64) ? DX_T_I64 : a.arg_type; if (a.func != "SUM" && a.arg_type == DX_T_TS) oc.type = DX_T_TS; rc = finalize(2, aptr[a.acc], aptr[a.acc_cnt], 0, &oc, (int)i); }
+            if (rc) return rc;
+            t->cols.push_back(oc);
+        }
+        DX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        *out = t; return DX_OK;
+    }
+};
+
+// =======================================================================================
+// flow construction
+// =======================================================================================
+static bool parse_state_schema(const std::string& s, std::vector<std::pair<std::string, int>>* out) {
+    std::stringstream ss(s); std::string part;
+    while (std::getline(ss, part, ',')) {
+        std::string p = trim(part); if (p.empty()) continue;
+        size_t sp = p.find_first_of(" \t:");
+        if (sp == std::string::npos) return false;
+        std::string name = trim(p.substr(0, sp)), ty = lower(trim(p.substr(sp + 1)));
+        if (!ty.empty() && ty[0] == ':') ty = trim(ty.substr(1));
+        int t = (ty == "long" || ty == "bigint" || ty == "int" || ty == "integer") ? DX_T_I64 : (ty == "double" || ty == "float") ? DX_T_F64 :
+                (ty == "string") ? DX_T_STR : (ty == "timestamp") ? DX_T_TS : (ty == "boolean") ? DX_T_BOOL : 0;
+        if (!t) return false;
+        out->emplace_back(name, t);
+    }
+    return !out->empty();
+}
+
+static DxTableP empty_table(dx_ctx* ctx, const std::vector<std::pair<std::string, int>>& schema) {
+    auto t = std::make_shared<DxTable>(); t->ctx = ctx; t->n_rows = 0;
+    for (auto& kv : schema) { DxColumn c; c.name = kv.first; c.type = kv.second; c.data = make_buf(ctx, 8); t->cols.push_back(c); }
+    return t;
+}
+
+int dx_flow_build(dx_ctx* ctx, const char* conf_text, const char* schema_json, const char* const* projection_steps, int n_steps,
+                  const char* transform_text, dx_flow** out) {
+    std::unique_ptr<dx_flow> F(new dx_flow()); F->ctx = ctx;
+    parse_conf(conf_text ? conf_text : "", &F->conf);
+    F->decoder.reset(new dx_decoder());
+    int rc = F->decoder->init(ctx, strip_bom(schema_json)); if (rc) return rc;
+    // projection steps: one selectExpr string per line (ProjectionHandler.scala:23-36)
+    for (int s = 0; s < n_steps; s++) {
+        std::vector<SelectItem> items;
+        for (auto& line : split_lines(strip_bom(projection_steps[s]))) {
+            std::string l = trim(line); if (l.empty()) continue;
+            try { Parser p(l); items.push_back(p.select_item()); }
+            catch (SqlError& e) { return ctx->set_error(DX_ERR_PARSE, "projection '" + l + "': " + e.what()); }
+        }
+        if (!items.empty()) F->projections.push_back(items);
+    }
+    // transform
+    std::string err;
+    rc = dx_parse_transform(transform_text ? transform_text : "", &F->transform, &err);
+    if (rc) return ctx->set_error(rc, err);
+    for (auto& c : F->transform.commands) {
+        if (!c.is_query) return ctx->set_error(DX_ERR_UNSUPPORTED, "non-query statement in transform: '" + c.text.substr(0, 80) + "'");
+        try { Parser p(c.text); c.stmt = p.statement(); }
+        catch (SqlError& e) { return ctx->set_error(DX_ERR_PARSE, "statement '" + c.name + "': " + e.what()); }
+    }
+    // time windows (TimeWindowHandler.scala:41-67)
+    const std::string root = "datax.job.process.";
+    for (auto& kv : F->conf) {
+        const std::string pre = root + "timewindow.";
+        if (kv.first.compare(0, pre.size(), pre) == 0) {
+            std::string rest = kv.first.substr(pre.size());
+            size_t dot = rest.rfind('.');
+            if (dot != std::string::npos && rest.substr(dot + 1) == "windowduration") {
+                bool ok; long long s = dx_parse_duration_seconds(kv.second, &ok);
+                if (!ok) return ctx->set_error(DX_ERR_PARSE, "bad window duration '" + kv.second + "'");
+                F->windows.emplace_back(rest.substr(0, dot), s);
+                F->max_window_s = std::max(F->max_window_s, s);
+            }
+        }
+        const std::string spre = root + "statetable.";
+        if (kv.first.compare(0, spre.size(), spre) == 0) {
+            std::string rest = kv.first.substr(spre.size());
+            size_t dot = rest.rfind('.');
+            if (dot != std::string::npos && rest.substr(dot + 1) == "schema") {
+                StateTable st; st.name = rest.substr(0, dot);
+                if (!parse_state_schema(kv.second, &st.schema)) return ctx->set_error(DX_ERR_PARSE, "bad state table schema '" + kv.second + "'");
+                st.phys[0] = empty_table(ctx, st.schema); st.phys[1] = empty_table(ctx, st.schema);
+                F->state_tables[st.name] = st;
+            }
+        }
+        const std::string opre = "datax.job.output.";
+        if (kv.first.compare(0, opre.size(), opre) == 0) {
+            std::string rest = kv.first.substr(opre.size());
+            size_t dot = rest.find('.');
+            std::string name = dot == std::string::npos ? rest : rest.substr(0, dot);
+            if (std::find(F->outputs.begin(), F->outputs.end(), name) == F->outputs.end()) F->outputs.push_back(name);
+        }
+    }
+    auto wm = F->conf.find(root + "watermark"); auto tc = F->conf.find(root + "timestampcolumn");
+    F->windows_enabled = !F->windows.empty() && wm != F->conf.end() && tc != F->conf.end();
+    if (F->windows_enabled) {
+        bool ok; F->watermark_s = dx_parse_duration_seconds(wm->second, &ok);
+        if (!ok) return ctx->set_error(DX_ERR_PARSE, "bad watermark '" + wm->second + "'");
+        F->ts_column = tc->second;
+    } else { F->max_window_s = 0; }
+    *out = F.release();
+    return DX_OK;
+}
+
+// =======================================================================================
+// one micro-batch: processDataset -> project -> route (CommonProcessorFactory.scala:333-399)
+// =======================================================================================
+int dx_flow::process(const std::string& name_space, const uint8_t* json, int64_t n_bytes, const int64_t* offsets, int64_t n_events,
+                     int memory_kind, long long batch_ms, long long interval_ms, long long now_ms, dx_result** out) {
+    std::unique_ptr<dx_result> R(new dx_result()); R->flow = this;
+    auto metric = [&](const std::string& k, double v) { R->metric_keys.push_back(k); R->metric_vals.push_back(v); };
+    // ---- project(): from_json + selectExpr steps (CPF:90-103)
+    DxTableP raw;
+    int rc = memory_kind == 1 ? decoder->decode_device(json, n_bytes, offsets, n_events, &raw) : decoder->decode_host(json, n_bytes, offsets, n_events, &raw);
+    if (rc) return rc;
+    std::map<std::string, View> views;
+    Exec X{this, ctx, &views, now_ms * 1000, ""};
+    DxTableP projected = raw;
+    for (auto& step : projections) {
+        View v; v.chunks.push_back(projected); views["Raw"] = v;
+        SelectCore core; core.from = "Raw"; core.items = step;
+        X.stmt_name = "projection";
+        DxTableP next; rc = X.exec_plain(core, views["Raw"], &next); if (rc) return rc;
+        projected = next;
+    }
+    views.erase("Raw");
+    // ---- route() (CPF:131-328)
+    metric("Input_Normalized_Events_Count", (double)projected->n_rows);
+    NamespaceState& NS = ns[name_space];
+    if (windows_enabled) {
+        const long long T = batch_ms;
+        const long long E = T - watermark_s * 1000, S = E - max_window_s * 1000;
+        View all; all.chunks.push_back(projected);
+        views["__projected"] = all;
+        SelectCore keep; keep.from = "__projected";
+        SelectItem star; star.expr = std::make_shared<Expr>(); star.expr->kind = EK::Star; keep.items.push_back(star);
+        auto col = std::make_shared<Expr>(); col->kind = EK::Col; col->parts = {ts_column};
+        auto ge = std::make_shared<Expr>(); ge->kind = EK::Bin; ge->sval = ">="; ge->args = {col, ts_const(E * 1000)};
+        keep.where = ge;
+        X.stmt_name = "window-cache";
+        DxTableP cur; rc = X.exec_plain(keep, views["__projected"], &cur); if (rc) return rc;
+        views.erase("__projected");
+        metric("Input_DataXProcessedInput_Events_Count", (double)cur->n_rows);
+        const long long cut = T - (watermark_s + max_window_s) * 1000;
+        for (auto it = NS.past_batches.begin(); it != NS.past_batches.end();) { if (it->first <= cut) it = NS.past_batches.erase(it); else ++it; }
+        std::vector<DxTableP> U; U.push_back(cur);
+        if (NS.past_batches.size() > 1) for (auto& kv : NS.past_batches) U.push_back(kv.second);   // the reference's size>1 quirk (CPF:198-201)
+        auto ranged = [&](long long lo_ms, long long hi_ms) { View v; v.chunks = U; v.ranged = true; v.ts_col = ts_column; v.lo_us = lo_ms * 1000; v.hi_us = hi_ms * 1000; return v; };
+        views["DataXProcessedInput_Window"] = ranged(S, E);
+        for (auto& w : windows) views[w.first] = ranged(E - w.second * 1000, E);
+        views["DataXProcessedInput"] = ranged(E - (interval_ms / 1000) * 1000, E);
+        View b; b.chunks.push_back(projected); views["DataXProcessedInput_Batch"] = b;
+        NS.past_batches[T] = cur;
+    } else {
+        metric("Input_DataXProcessedInput_Events_Count", (double)projected->n_rows);
+        View v; v.chunks.push_back(projected); views["DataXProcessedInput"] = v;
+    }
+    for (auto& kv : state_tables) { View v; v.chunks.push_back(kv.second.phys[kv.second.active]); views[kv.first] = v; }
+    for (auto& cmd : transform.commands) {
+        X.stmt_name = cmd.name;
+        DxTableP res; rc = X.exec_statement(cmd.stmt, &res); if (rc) return rc;
+        res->name = cmd.name;
+        auto st = state_tables.find(cmd.name);
+        if (st != state_tables.end()) {
+            // INSERT OVERWRITE standby + flip (StateTableHandler.scala:99-115; CPF:259-264)
+            StateTable& S2 = st->second;
+            if (res->cols.size() != S2.schema.size()) return ctx->set_error(DX_ERR_ARG, "state table '" + cmd.name + "': query yields " + std::to_string(res->cols.size()) + " columns, schema has " + std::to_string(S2.schema.size()));
+            for (size_t c = 0; c < res->cols.size(); c++) res->cols[c].name = S2.schema[c].first;   // INSERT is positional
+            S2.phys[1 - S2.active] = res; S2.active = 1 - S2.active; S2.flipped = !S2.flipped;
+            View v; v.chunks.push_back(res); views[cmd.name] = v;
+        } else {
+            View v; v.chunks.push_back(res); views[cmd.name] = v;
+        }
+        R->datasets[cmd.name] = res; R->dataset_order.push_back(cmd.name);
+    }
+    for (auto& o : outputs) if (!R->datasets.count(o)) return ctx->set_error(DX_ERR_ARG, "could not find data set name '" + o + "' for output '" + o + "'");
+    R->datasets["DataXProcessedInput_Batch"] = projected;
+    for (auto& k : R->metric_keys) R->metric_key_ptrs.push_back(k.c_str());
+    *out = R.release();
+    return DX_OK;
+}

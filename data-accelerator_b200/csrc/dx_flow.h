@@ -1,0 +1,81 @@
+// dx_flow.h — the per-micro-batch flow processor behind the C ABI (dx_flow_*).
+//
+// Host-side restatement target: the closure built by CommonProcessorFactory.createProcessor
+// (reference: datax/processor/CommonProcessorFactory.scala:50-657): project() :90-103,
+// route() :131-328, processDataset() :333-399, with TimeWindowHandler.scala:41-67,
+// StateTableHandler.scala:70-128, TransformSqlParser.scala:27-104, ConfigManager.scala:98-135.
+#pragma once
+#include "dx_common.h"
+#include "dx_sql.h"
+#include "dx_expr.h"
+#include "dx_agg.h"
+#include "dx_decode_host.h"
+#include <set>
+
+struct SqlCommand {
+    std::string text, name;        // name empty => "Command" type (TransformSqlParser.scala:24-26)
+    bool is_query = false;
+    dxsql::Statement stmt;
+};
+struct ParsedTransform {
+    std::vector<SqlCommand> commands;
+    std::map<std::string, int> view_reference_count;
+};
+// TransformSQLParser.parse restated (reference: datax/sql/TransformSqlParser.scala:27-95)
+int dx_parse_transform(const std::string& text, ParsedTransform* out, std::string* err);
+
+struct RuleTable { std::vector<std::vector<std::pair<std::string, std::string>>> rules; };   // MAP('k','v',...) per rule
+
+struct View {
+    std::vector<DxTableP> chunks;
+    bool ranged = false;
+    std::string ts_col;
+    long long lo_us = 0, hi_us = 0;
+};
+
+struct StateTable {
+    std::string name;
+    std::vector<std::pair<std::string, int>> schema;
+    DxTableP phys[2];              // "A" and "B"
+    int active = 0;                // metadata.info active=A standby=B initially (StateTableHandler.scala:45-50)
+    bool flipped = false;
+};
+
+struct NamespaceState {
+    std::map<long long, DxTableP> past_batches;    // pastRdds: arrival batch time (ms) -> cached rows
+};
+
+struct dx_result {
+    struct dx_flow* flow = nullptr;
+    std::map<std::string, DxTableP> datasets;
+    std::vector<std::string> dataset_order;
+    std::vector<std::string> metric_keys;
+    std::vector<double> metric_vals;
+    std::vector<const char*> metric_key_ptrs;
+};
+
+struct dx_flow {
+    dx_ctx* ctx = nullptr;
+    std::map<std::string, std::string> conf;
+    std::unique_ptr<dx_decoder> decoder;
+    std::vector<std::vector<dxsql::SelectItem>> projections;     // one list of selectExpr items per step
+    ParsedTransform transform;
+    // time windows (TimeWindowHandler.scala:15-21)
+    std::vector<std::pair<std::string, long long>> windows;       // name -> seconds
+    bool windows_enabled = false;
+    std::string ts_column;
+    long long watermark_s = 0, max_window_s = 0;
+    std::map<std::string, StateTable> state_tables;
+    std::vector<std::string> outputs;
+    std::map<std::string, NamespaceState> ns;
+    std::map<std::string, unsigned long long> agg_capacity_hint;  // per statement name
+    std::string last_error;
+    int process(const std::string& name_space, const uint8_t* json, int64_t n_bytes, const int64_t* offsets, int64_t n_events,
+                int memory_kind, long long batch_ms, long long interval_ms, long long now_ms, dx_result** out);
+};
+
+int dx_flow_build(dx_ctx* ctx, const char* conf_text, const char* schema_json, const char* const* projection_steps, int n_steps,
+                  const char* transform_text, dx_flow** out);
+// stringToTimestamp restated for dictionary entries (reference: ConcurrentDateFormat.scala:38-62)
+bool dx_string_to_timestamp_us(const std::string& s, long long* out_us);
+long long dx_parse_duration_seconds(const std::string& s, bool* ok);

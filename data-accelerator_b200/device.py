@@ -113,12 +113,14 @@ class Table:
         valid = np.zeros(n, dtype=np.uint8)
         if t == 6:
             w = self.L.dx_table_flag_words(self.h, i)
-            data = np.zeros((n, w), dtype=np.uint32)
+            data = np.zeros((w, n), dtype=np.uint32)   # word-major on the device: flags[w][row]
         else:
             data = np.zeros(n, dtype={1: np.int64, 2: np.float64, 3: np.int32, 4: np.int64, 5: np.int64}[t])
         self.ctx.check(self.L.dx_table_column_to_host(self.h, i, data.ctypes.data_as(C.c_void_p),
                                                       valid.ctypes.data_as(C.c_void_p)))
         valid = valid.astype(bool)
+        if t == 6:
+            return np.ascontiguousarray(data.T), valid      # -> (n_rows, words)
         if t == 3:
             d = self.dictionary(i)
             out = np.empty(n, dtype=object)

@@ -1,0 +1,209 @@
+"""Host-side mirror of the reference's processor interface, over the C ABI.
+
+The reference builds its processor with
+    CommonProcessorFactory.createProcessor(config: UnifiedConfig): CommonProcessor
+(datax/processor/CommonProcessorFactory.scala:50) and drives it per micro-batch through
+    processJson / processEventData / ... -> processDataset(data, batchTime, batchInterval,
+                                                           outputPartitionTime, targets, namespace)
+(CommonProcessorFactory.scala:333-338, 405-461) which returns the metrics Map[String, Double].
+There is no JVM in this image, so the Scala shim cannot be compiled here; this
+module is the same surface in Python — same names, argument meaning and error behaviour — and
+is what the parity tests drive.  All work happens in libdxgpu.so; nothing here computes.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import _native as N
+from ._native import DxError
+from .device import Context, Table
+
+vp, i64, i32, cp = C.c_void_p, C.c_int64, C.c_int, C.c_char_p
+P = C.POINTER
+_SIG = {
+    "dx_flow_create": (i32, [vp, cp, cp, P(cp), i32, cp, P(vp)]),
+    "dx_flow_destroy": (None, [vp]),
+    "dx_flow_process_batch": (i32, [vp, cp, vp, i64, vp, i64, i32, i64, i64, i64, i64, P(vp)]),
+    "dx_result_metrics": (i32, [vp, P(P(cp)), P(P(C.c_double)), P(i32)]),
+    "dx_result_num_tables": (i32, [vp]),
+    "dx_result_table_name": (cp, [vp, i32]),
+    "dx_result_table": (i32, [vp, cp, P(vp)]),
+    "dx_result_release": (None, [vp]),
+    "dx_flow_state_export": (i32, [vp, cp, P(vp), P(i32)]),
+    "dx_table_rule_count": (i32, [vp, i32]),
+    "dx_table_rule_json": (i32, [vp, i32, i32, P(vp), P(i64)]),
+    "dx_sql_canonical": (i32, [cp, C.c_char_p, i64]),
+    "dx_transform_split": (i32, [cp, C.c_char_p, i64]),
+    "dx_string_to_timestamp": (i32, [cp, P(i64)]),
+    "dx_duration_seconds": (i64, [cp]),
+}
+_bound = False
+
+
+def _lib():
+    global _bound
+    L = N.lib()
+    if not _bound:
+        for name, (res, args) in _SIG.items():
+            fn = getattr(L, name)
+            fn.restype, fn.argtypes = res, args
+        _bound = True
+    return L
+
+
+# ---- host-side artefact parsers (no GPU) ---------------------------------------------------------
+def sql_canonical(sql: str) -> str:
+    buf = C.create_string_buffer(1 << 20)
+    rc = _lib().dx_sql_canonical(sql.encode("utf-8"), buf, len(buf))
+    if rc:
+        raise DxError(buf.value.decode("utf-8", "replace"))
+    return buf.value.decode("utf-8")
+
+
+def transform_split(text: str):
+    """TransformSQLParser.parse -> (commands [(name|None, type, text)], viewReferenceCount dict)."""
+    buf = C.create_string_buffer(4 << 20)
+    rc = _lib().dx_transform_split(text.encode("utf-8"), buf, len(buf))
+    if rc:
+        raise DxError(buf.value.decode("utf-8", "replace"))
+    cmds, refs = [], {}
+    for line in buf.value.decode("utf-8").split("\n"):
+        if not line:
+            continue
+        a, b, c = line.split("\t", 2)
+        if a == "#ref":
+            refs[b] = int(c)
+        else:
+            cmds.append((a or None, b, c))
+    return cmds, refs
+
+
+def string_to_timestamp(s: str):
+    """stringToTimestamp built-in -> epoch microseconds (UTC session) or None."""
+    us = C.c_int64()
+    return us.value if _lib().dx_string_to_timestamp(s.encode("utf-8"), C.byref(us)) else None
+
+
+def duration_seconds(s: str) -> int:
+    return int(_lib().dx_duration_seconds(s.encode("utf-8")))
+
+
+# ---- the processor ------------------------------------------------------------------------------
+class BatchResult:
+    def __init__(self, ctx, handle):
+        self.ctx, self.h, self.L = ctx, handle, ctx.L
+
+    @property
+    def metrics(self):
+        keys, vals, n = P(cp)(), P(C.c_double)(), C.c_int()
+        self.ctx.check(self.L.dx_result_metrics(self.h, C.byref(keys), C.byref(vals), C.byref(n)))
+        return {keys[i].decode(): vals[i] for i in range(n.value)}
+
+    @property
+    def table_names(self):
+        return [self.L.dx_result_table_name(self.h, i).decode() for i in range(self.L.dx_result_num_tables(self.h))]
+
+    def table(self, name) -> Table:
+        t = C.c_void_p()
+        self.ctx.check(self.L.dx_result_table(self.h, name.encode(), C.byref(t)))
+        return Table(self.ctx, t)
+
+    def release(self):
+        if self.h:
+            self.L.dx_result_release(self.h)
+            self.h = None
+
+    __del__ = release
+
+
+def rules_of(table: Table, col="Rules"):
+    """Static rule table behind a FLAGS column -> list of dicts (the MAP(...) constants)."""
+    import json
+    L = _lib()
+    i = table._idx(col)
+    out = []
+    for r in range(L.dx_table_rule_count(table.h, i)):
+        p, ln = C.c_void_p(), C.c_int64()
+        table.ctx.check(L.dx_table_rule_json(table.h, i, r, C.byref(p), C.byref(ln)))
+        out.append(json.loads(C.string_at(p.value, ln.value).decode("utf-8")))
+    return out
+
+
+class CommonProcessor:
+    """What createProcessor returns (CommonProcessor case class, datax/processor/CommonProcessor.scala:17-31),
+    reduced to the ingest adapters this ABI serves: JSON strings, in host or device memory."""
+
+    def __init__(self, ctx: Context, conf_text, schema_json, projection_steps, transform_text):
+        self.ctx = ctx
+        self.L = _lib()
+        steps = (cp * len(projection_steps))(*[s.encode("utf-8") for s in projection_steps])
+        h = C.c_void_p()
+        rc = self.L.dx_flow_create(ctx.h, conf_text.encode("utf-8"), schema_json.encode("utf-8"), steps,
+                                   len(projection_steps), transform_text.encode("utf-8"), C.byref(h))
+        ctx.check(rc)
+        self.h = h
+
+    def close(self):
+        if self.h:
+            self.L.dx_flow_destroy(self.h)
+            self.h = None
+
+    def process_json(self, data, batch_time_ms, batch_interval_ms, output_partition_time_ms=None, namespace="",
+                     now_ms=None, offsets=None, n_events=-1) -> BatchResult:
+        """processJson (CPF:458-461): data = NDJSON bytes (or bytes + offsets) in HOST memory."""
+        buf = np.frombuffer(data, dtype=np.uint8) if not isinstance(data, np.ndarray) else data
+        off_p = None
+        if offsets is not None:
+            offsets = np.ascontiguousarray(offsets, dtype=np.int64)
+            off_p = offsets.ctypes.data_as(C.c_void_p)
+            n_events = len(offsets) - 1
+        r = C.c_void_p()
+        ptr = buf.ctypes.data_as(C.c_void_p) if buf.size else None
+        self.ctx.check(self.L.dx_flow_process_batch(
+            self.h, namespace.encode(), ptr, buf.size, off_p, n_events, 0, batch_time_ms, batch_interval_ms,
+            output_partition_time_ms if output_partition_time_ms is not None else batch_time_ms,
+            now_ms if now_ms is not None else batch_time_ms, C.byref(r)))
+        return BatchResult(self.ctx, r)
+
+    def process_device(self, ptr, n_bytes, batch_time_ms, batch_interval_ms, namespace="", now_ms=None, n_events=-1,
+                       offsets_ptr=None) -> BatchResult:
+        """Same, with the batch already resident in device memory."""
+        r = C.c_void_p()
+        self.ctx.check(self.L.dx_flow_process_batch(
+            self.h, namespace.encode(), C.c_void_p(ptr), n_bytes, C.c_void_p(offsets_ptr) if offsets_ptr else None,
+            n_events, 1, batch_time_ms, batch_interval_ms, batch_time_ms,
+            now_ms if now_ms is not None else batch_time_ms, C.byref(r)))
+        return BatchResult(self.ctx, r)
+
+    def state_table(self, name):
+        t, b = C.c_void_p(), C.c_int()
+        self.ctx.check(self.L.dx_flow_state_export(self.h, name.encode(), C.byref(t), C.byref(b)))
+        return Table(self.ctx, t), ("B" if b.value else "A")
+
+
+class CommonProcessorFactory:
+    """CommonProcessorFactory.createProcessor (CPF:50).  `config` carries what UnifiedConfig.dict points
+    at: the .conf text plus the contents of the files it names (schema, projection steps, transform)."""
+
+    @staticmethod
+    def createProcessor(ctx: Context, conf_text: str, schema_json: str, projection_steps, transform_text: str):
+        return CommonProcessor(ctx, conf_text, schema_json, list(projection_steps), transform_text)
+
+    @staticmethod
+    def createProcessorFromFiles(ctx: Context, conf_path: str, read=lambda p: open(p, encoding="utf-8-sig").read()):
+        """Loads the artefacts the way the reference does: the .conf names the other files
+        (datax.job.input.default.blobschemafile, .process.projection (';'-separated), .process.transform)."""
+        conf_text = read(conf_path)
+        d = {}
+        for line in conf_text.splitlines():
+            line = line.strip().lstrip("﻿")
+            if line and not line.startswith("#") and "=" in line:
+                k, v = line.split("=", 1)
+                d[k.strip()] = v.strip()
+        base = os.path.dirname(conf_path)
+        rel = lambda p: p if os.path.isabs(p) else os.path.join(base, p)
+        schema = read(rel(d["datax.job.input.default.blobschemafile"]))
+        steps = [read(rel(p)) for p in d.get("datax.job.process.projection", "").split(";") if p]
+        transform = read(rel(d["datax.job.process.transform"])) if d.get("datax.job.process.transform") else ""
+        return CommonProcessor(ctx, conf_text, schema, steps, transform)

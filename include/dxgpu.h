@@ -92,6 +92,56 @@ int dx_table_dict_size(const dx_table* t, int col, int64_t* n_codes);
 int dx_table_dict_string(const dx_table* t, int col, int64_t code, const char** bytes, int64_t* len);
 void dx_table_release(dx_table* t);
 
+/* Rule metadata of a FLAGS column: the constant MAP('ruleId',...,'severity',...) of rule r as a JSON
+ * object.  Flags are stored word-major: flags[w * n_rows + row], bit (r % 32) of word r / 32 set
+ * <=> rule r's condition is TRUE for the row — the device form of the reference's
+ * filterNull(Array(IF(cond_r, MAP(...), NULL), ...)) AS Rules (CodegenRules Engine.cs:232-266).   */
+int dx_table_rule_count(const dx_table* t, int col);
+int dx_table_rule_json(const dx_table* t, int col, int rule, const char** json, int64_t* len);
+
+/* ---- the flow processor (drop-in boundary) ------------------------------------------------ */
+typedef struct dx_flow dx_flow;       /* one per flow: decoder, parsed SQL, window cache, state tables */
+typedef struct dx_result dx_result;   /* what one micro-batch produced                                */
+/* Replaces CommonProcessorFactory.createProcessor(config) (CommonProcessorFactory.scala:50-126).
+ * conf_text: contents of <flow>.conf (ConfigManager.scala:98-135); schema_json: inputschema.json;
+ * projection_steps: contents of each projection file (ProjectionHandler.scala:23-36);
+ * transform_text: <flow>-combined.txt (TransformHandler.scala:25-53).  Unsupported SQL, types or
+ * hooks fail here, at construction, with a message — never later and never on a CPU path.       */
+int dx_flow_create(dx_ctx* ctx, const char* conf_text, const char* schema_json,
+                   const char* const* projection_steps, int n_steps, const char* transform_text,
+                   dx_flow** out);
+void dx_flow_destroy(dx_flow* flow);
+/* Replaces CommonProcessor.processDataset(data, batchTime, batchInterval, outputPartitionTime,
+ * targets, namespace) (CommonProcessorFactory.scala:333-399): decode -> projection -> windows ->
+ * SQL statements -> state tables.  now_ms is the fixed clock behind current_timestamp().
+ * Calls on one (flow, name_space) must not overlap.                                               */
+int dx_flow_process_batch(dx_flow* flow, const char* name_space, const uint8_t* json, int64_t n_bytes,
+                          const int64_t* offsets, int64_t n_events, int memory_kind,
+                          int64_t batch_time_ms, int64_t interval_ms, int64_t output_partition_time_ms,
+                          int64_t now_ms, dx_result** out);
+/* The Map[String, Double] processDataset returns (Input_Normalized_Events_Count, ...). */
+int dx_result_metrics(dx_result* r, const char* const** keys, const double** vals, int* n);
+int dx_result_num_tables(const dx_result* r);
+const char* dx_result_table_name(const dx_result* r, int i);
+/* A named dataset of this batch (OutputManager looks tables up by name, CPF:297-306); the returned
+ * handle must be released with dx_table_release and may outlive the result.                       */
+int dx_result_table(dx_result* r, const char* dataset, dx_table** out);
+void dx_result_release(dx_result* r);
+/* Accumulator (state) tables: the active physical table and whether it is the "B" copy
+ * (StateTableHandler.scala:26-52: metadata.info active=/standby=), for Parquet A/B persistence. */
+int dx_flow_state_export(dx_flow* flow, const char* table, dx_table** out, int* active_is_b);
+
+/* ---- host-side artefact parsers, exposed for tests (no GPU needed) ------------------------- */
+/* Canonical text of a statement as the SQL-subset parser understood it; error text on failure. */
+int dx_sql_canonical(const char* sql, char* buf, int64_t cap);
+/* TransformSQLParser.parse (TransformSqlParser.scala:27-95): one line per command
+ * "name<TAB>type<TAB>text", then "#ref<TAB>name<TAB>count" lines.                               */
+int dx_transform_split(const char* text, char* buf, int64_t cap);
+/* stringToTimestamp (ConcurrentDateFormat.scala:38-62), UTC session: 1 and *us on success, 0 = NULL. */
+int dx_string_to_timestamp(const char* s, int64_t* us);
+/* scala Duration.create(...).toSeconds as used by TimeWindowHandler.scala:33-35; -1 on error.     */
+int64_t dx_duration_seconds(const char* s);
+
 /* ---- synthetic events (measurement tooling; shapes of the reference's simulated IoT data) -- */
 /* Event shapes after DataGenerator.scala:27-209 / HomeAutomationLocal.json:288. */
 typedef struct dx_gen_params {

@@ -1,0 +1,81 @@
+"""Compare a device Table (through the C ABI) with an oracle Tab as multisets of rows."""
+import math
+
+import numpy as np
+
+REL_TOL = 1e-6      # floating-point aggregates: order-dependent sums (BASELINE.json north_star)
+
+
+def gpu_rows(table, dx):
+    cols = []
+    for i, name in enumerate(table.columns):
+        t = table.column_type(i)
+        if t == 0 or t == 7:
+            cols.append([None] * table.num_rows)
+            continue
+        v, ok = table.column(i)
+        if t == 6:
+            nr = len(dx.rules_of(table, i))
+            bits = np.unpackbits(v.view(np.uint8), axis=1, bitorder="little")[:, :nr].astype(bool) if table.num_rows else np.zeros((0, nr), bool)
+            cols.append([tuple(np.nonzero(r)[0].tolist()) for r in bits])
+        elif t == 2:
+            cols.append([float(x) if k else None for x, k in zip(v, ok)])
+        elif t == 3:
+            cols.append([x if k else None for x, k in zip(v, ok)])
+        else:
+            cols.append([int(x) if k else None for x, k in zip(v, ok)])
+    return [tuple(c[r] for c in cols) for r in range(table.num_rows)]
+
+
+def oracle_rows(tab):
+    cols = []
+    for name, ty, v, ok in tab.cols:
+        if ty == "null" or v is None:
+            cols.append([None] * tab.n)
+        elif ty == "rules":
+            cols.append([tuple(np.nonzero(r)[0].tolist()) for r in v])
+        elif ty == "double":
+            cols.append([float(x) if k else None for x, k in zip(v, ok)])
+        elif ty == "string":
+            cols.append([x if k else None for x, k in zip(v, ok)])
+        else:
+            cols.append([int(x) if k else None for x, k in zip(v, ok)])
+    return [tuple(c[r] for c in cols) for r in range(tab.n)]
+
+
+def _key(row):
+    out = []
+    for x in row:
+        if x is None:
+            out.append((0, 0))
+        elif isinstance(x, float):
+            out.append((1, 0))                    # doubles do not take part in the ordering (tolerance)
+        elif isinstance(x, bytes):
+            out.append((2, x))
+        elif isinstance(x, tuple):
+            out.append((3, x))
+        else:
+            out.append((4, x))
+    return out
+
+
+def _fkey(row):
+    return [x if isinstance(x, float) and not math.isnan(x) else 0.0 for x in row if isinstance(x, float)]
+
+
+def assert_same_rows(table, tab, dx, ordered=False):
+    assert table.columns == tab.names(), (table.columns, tab.names())
+    g, o = gpu_rows(table, dx), oracle_rows(tab)
+    assert len(g) == len(o), (len(g), len(o))
+    if not ordered:
+        g.sort(key=lambda r: (_key(r), _fkey(r)))
+        o.sort(key=lambda r: (_key(r), _fkey(r)))
+    for a, b in zip(g, o):
+        for x, y in zip(a, b):
+            if isinstance(x, float) and isinstance(y, float):
+                if math.isnan(x) or math.isnan(y):
+                    assert math.isnan(x) and math.isnan(y), (a, b)
+                else:
+                    assert x == y or abs(x - y) <= REL_TOL * max(abs(x), abs(y)), (a, b)
+            else:
+                assert x == y, (a, b)

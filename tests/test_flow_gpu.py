@@ -1,0 +1,196 @@
+"""Flow-level parity: libdxgpu's processor (C ABI) vs the CPU oracle's restatement of
+CommonProcessorFactory.processDataset on the same batches."""
+import numpy as np
+import pytest
+
+import dxo
+import dxo_flow
+from adversarial import all_records, to_ndjson
+from flowcmp import assert_same_rows
+
+pytestmark = pytest.mark.gpu
+
+SCHEMA2 = dxo.iot_schema_json(2)
+SCHEMA1 = dxo.iot_schema_json(1)
+PROJ_TS = "CAST(Raw.deviceDetails.eventTime / 1000 AS timestamp) AS eventTimeStamp\nRaw.*\n"
+T0 = 1_700_000_040_000      # a multiple of 60 s
+I = 60_000
+
+
+def both(dx, ctx, conf, schema, proj, transform):
+    g = dx.CommonProcessorFactory.createProcessor(ctx, conf, schema, proj, transform)
+    o = dxo_flow.Flow(conf, schema, proj, transform)
+    return g, o
+
+
+def gen(dx, n, first=0, shape=2, n_keys=1000, base=T0, seed=20260103, late=10, future=1, wm=60_000):
+    p = dxo.GenParams(seed, n_keys, max(1, n_keys // 10), base, I, wm, shape, late, future, 0)
+    return dxo.gen_events(p, first, n)
+
+
+def check_batch(dx, g, o, data, batch_ms, now_ms=None, tables=None):
+    rg = g.process_json(data, batch_ms, I, now_ms=now_ms)
+    ro, mo = o.process(data, batch_ms, I, now_ms=now_ms)
+    assert rg.metrics == mo, (rg.metrics, mo)
+    for name in (tables or rg.table_names):
+        assert_same_rows(rg.table(name), ro[name], dx)
+    rg.release()
+
+
+def test_rules_flags_match_oracle(dx, ctx):
+    rules = dx.flowgen.make_rules(200, n_keys=1000, n_homes=100)
+    tr = dx.flowgen.process_rules_sql(rules)
+    conf = dx.flowgen.conf_text("c2", outputs=["Rules"])
+    g, o = both(dx, ctx, conf, SCHEMA2, ["Raw.*\n"], tr)
+    data = gen(dx, 50_000)
+    rg = g.process_json(data, T0, I)
+    ro, mo = o.process(data, T0, I)
+    t = rg.table("Rules")
+    assert dx.rules_of(t, "Rules") == ro["Rules"].rule_table
+    assert_same_rows(t, ro["Rules"], dx, ordered=True)
+    flags, _ = t.column("Rules")
+    assert flags.shape == (50_000, 7)
+    # every rule fires at least once on 50k events except the very selective ones; none fires always
+    fired = np.unpackbits(flags.view(np.uint8), axis=1, bitorder="little")[:, :200].sum(axis=0)
+    assert (fired > 0).sum() > 150 and (fired < 50_000).all()
+    g.close()
+
+
+def test_rules_on_adversarial_events_three_valued_logic(dx, ctx):
+    rules = [{"ruleId": "R%d" % i, "ruleDescription": "d", "severity": "Critical", "tagName": "Tag", "tag": "t", "condition": c}
+             for i, c in enumerate([
+                 "deviceDetails.temperature > 50", "deviceDetails.temperature <= 50 OR deviceDetails.humidity > 1e300",
+                 "NOT (deviceDetails.temperature > 50)", "deviceDetails.status = 1 AND deviceDetails.deviceType = 'Heating'",
+                 "deviceDetails.deviceType <> 'Heating'", "deviceDetails.deviceType LIKE '%Lock'", "deviceDetails.deviceType NOT LIKE 'Door%'",
+                 "deviceDetails.deviceType LIKE '_eating'", "deviceDetails.deviceId IN (1, 2, 3, 5, 8)", "deviceDetails.homeId BETWEEN 10 AND 5000",
+                 "deviceDetails.status IS NULL", "deviceDetails.status IS NOT NULL AND deviceDetails.temperature IS NULL",
+                 "deviceDetails.temperature = deviceDetails.humidity", "deviceDetails.deviceId + deviceDetails.homeId * 2 > 1000000",
+                 "deviceDetails.deviceId / 0 > 1", "deviceDetails.temperature / deviceDetails.humidity >= 1.5",
+                 "deviceDetails.deviceId % 7 = 3", "deviceDetails.temperature > deviceDetails.deviceId",
+                 "IF(deviceDetails.status = 1, deviceDetails.temperature, deviceDetails.humidity) < 20",
+                 "deviceDetails.status = 1 OR NULL", "deviceDetails.eventTime >= 1600000000000 AND deviceDetails.eventTime < 1600000500000",
+                 "-deviceDetails.temperature < -99.5", "deviceDetails.homeId <> 150 OR deviceDetails.deviceId = 3"])]
+    tr = dx.flowgen.process_rules_sql(rules)
+    g, o = both(dx, ctx, dx.flowgen.conf_text("adv"), SCHEMA2, ["Raw.*\n"], tr)
+    data = to_ndjson(all_records(3000, seed=21))
+    rg = g.process_json(data, T0, I)
+    ro, _ = o.process(data, T0, I)
+    assert_same_rows(rg.table("Rules"), ro["Rules"], dx, ordered=True)
+    g.close()
+
+
+def test_filter_project_and_alert_statements(dx, ctx):
+    tr = """--DataXQuery--
+sa1_1_1 = SELECT *, 'R100' AS ruleId, 'DoorLock Close' AS ruleDescription, 'Critical' AS severity, 'CLOSE' AS Tag
+    FROM DataXProcessedInput WHERE deviceDetails.deviceType = 'DoorLock' AND deviceDetails.status = 1
+--DataXQuery--
+sa2_1_1 = SELECT * FROM sa1_1_1
+--DataXQuery--
+CLOSEAlert = SELECT DISTINCT DATE_TRUNC('second', current_timestamp()) AS EventTime, 'CLOSEAlert' AS MetricName, 0 as Metric,
+    'iotsample' AS Product, 'DoorLock Close' AS Pivot1 FROM sa1_1_1
+--DataXQuery--
+HeaterStateFiltered = SELECT eventTimeStamp, deviceDetails.deviceId, deviceDetails.deviceType, deviceDetails.homeId, deviceDetails.status
+    FROM DataXProcessedInput WHERE deviceDetails.homeId = 15 AND deviceDetails.deviceType = 'Heating'
+    GROUP BY eventTimeStamp, deviceId, deviceType, homeId, status
+--DataXQuery--
+HeaterStateOneIsOn = SELECT DISTINCT DATE_TRUNC('second', current_timestamp()) AS EventTime, 'HeaterStateOneIsOn' AS MetricName,
+    status AS Metric, 'iotsample' AS Product, '' AS Pivot1 FROM HeaterStateFiltered GROUP BY EventTime, MetricName, Metric, Product, Pivot1
+--DataXQuery--
+Derived = SELECT deviceDetails.deviceId AS id, deviceDetails.temperature * 1.8 + 32 AS fahrenheit, hour(eventTimeStamp) AS h,
+    deviceDetails.status = 1 AS isOn, CAST(deviceDetails.humidity AS long) AS hum FROM DataXProcessedInput WHERE deviceDetails.temperature > 90
+"""
+    g, o = both(dx, ctx, dx.flowgen.conf_text("alerts"), SCHEMA2, [PROJ_TS], tr)
+    data = gen(dx, 40_000, n_keys=200)
+    check_batch(dx, g, o, data, T0, now_ms=T0 + 1234)
+    check_batch(dx, g, o, b"", T0 + I, now_ms=T0 + I)      # empty micro-batch
+    g.close()
+
+
+AGG_TR = """--DataXQuery--
+PerKey = SELECT deviceDetails.deviceId, deviceDetails.homeId, COUNT(*) AS Count, SUM(deviceDetails.status) AS SumStatus,
+    MIN(deviceDetails.status) AS MinStatus, MAX(deviceDetails.status) AS MaxStatus, AVG(deviceDetails.status) AS AvgStatus,
+    SUM(deviceDetails.temperature) AS SumT, MIN(deviceDetails.temperature) AS MinT, MAX(deviceDetails.temperature) AS MaxT,
+    AVG(deviceDetails.temperature) AS AvgT, MAX(eventTimeStamp) AS LastSeen, COUNT(deviceDetails.humidity) AS NHum
+    FROM DataXProcessedInput GROUP BY deviceDetails.deviceId, deviceDetails.homeId
+--DataXQuery--
+PerType = SELECT deviceDetails.deviceType, COUNT(*) AS Count, AVG(deviceDetails.temperature) AS Temperature_AVG FROM DataXProcessedInput GROUP BY deviceDetails.deviceType
+--DataXQuery--
+Total = SELECT COUNT(*) AS Count, MAX(deviceDetails.temperature) AS MaxT FROM DataXProcessedInput WHERE deviceDetails.status = 1
+--DataXQuery--
+Nothing = SELECT COUNT(*) AS Count, MIN(deviceDetails.homeId) AS m FROM DataXProcessedInput WHERE deviceDetails.status = 7
+--DataXQuery--
+ar2 = SELECT *, IF(Temperature_AVG > 50 AND Count > 10, MAP('ruleId', 'R3', 'ruleDescription', 'hot on average', 'severity', 'Critical', 'Tag', 'HotAgg'), NULL) AS RuleObject FROM PerType
+"""
+
+
+def test_group_by_aggregates(dx, ctx):
+    g, o = both(dx, ctx, dx.flowgen.conf_text("agg"), SCHEMA2, [PROJ_TS], AGG_TR)
+    check_batch(dx, g, o, gen(dx, 60_000, n_keys=3000), T0)
+    # NULL keys / NULL values / malformed rows take part as Spark says
+    check_batch(dx, g, o, to_ndjson(all_records(3000, seed=31)), T0 + I)
+    g.close()
+
+
+WIN_TR = """--DataXQuery--
+Tumbling = SELECT deviceDetails.deviceId, deviceDetails.homeId, COUNT(*) AS Count, SUM(deviceDetails.status) AS S, MIN(deviceDetails.status) AS Mn,
+    MAX(deviceDetails.status) AS Mx, AVG(deviceDetails.status) AS Av FROM DataXProcessedInput GROUP BY deviceDetails.deviceId, deviceDetails.homeId
+--DataXQuery--
+Sliding5 = SELECT deviceDetails.deviceId, deviceDetails.homeId, COUNT(*) AS Count, SUM(deviceDetails.status) AS S, MAX(eventTimeStamp) AS Last
+    FROM DataXProcessedInput_5minutes GROUP BY deviceDetails.deviceId, deviceDetails.homeId
+--DataXQuery--
+Sliding2 = SELECT COUNT(*) AS Count FROM DataXProcessedInput_2minutes
+--DataXQuery--
+WholeWindow = SELECT COUNT(*) AS Count, MIN(eventTimeStamp) AS First FROM DataXProcessedInput_Window
+--DataXQuery--
+ThisBatch = SELECT COUNT(*) AS Count FROM DataXProcessedInput_Batch
+"""
+
+
+@pytest.mark.parametrize("wm", ["60 second", "0 second", "90 second"])
+def test_time_windows_with_reference_quirks(dx, ctx, wm):
+    conf = dx.flowgen.conf_text("win", timestamp_column="eventTimeStamp", watermark=wm,
+                                windows=[("DataXProcessedInput_5minutes", "5 minutes"), ("DataXProcessedInput_2minutes", "2 minutes")])
+    g, o = both(dx, ctx, conf, SCHEMA1, [PROJ_TS], WIN_TR)
+    wm_ms = dxo_flow.parse_duration(wm) * 1000
+    for b in range(12):
+        T = T0 + b * I
+        data = gen(dx, 4000, first=b * 4000, shape=1, n_keys=300, base=T, late=30, future=20, wm=wm_ms)
+        check_batch(dx, g, o, data, T)
+    g.close()
+
+
+def test_state_table_append_with_retention_and_upsert(dx, ctx):
+    tr = """--DataXQuery--
+PerKey = SELECT deviceDetails.deviceId, deviceDetails.homeId, MAX(eventTimeStamp) AS WindowEnd, COUNT(*) AS Count
+    FROM DataXProcessedInput GROUP BY deviceDetails.deviceId, deviceDetails.homeId
+--DataXQuery--
+acc_new = SELECT deviceId, homeId, WindowEnd, Count FROM PerKey
+    UNION ALL SELECT deviceId, homeId, WindowEnd, Count FROM acc WHERE unix_timestamp() - to_unix_timestamp(WindowEnd, 'yyyy-MM-dd') < 200
+--DataXQuery--
+acc = SELECT deviceId, homeId, WindowEnd, Count FROM acc_new
+--DataXQuery--
+merged = SELECT deviceId, homeId, Count FROM PerKey UNION ALL SELECT deviceId, homeId, Count FROM totals
+--DataXQuery--
+totals = SELECT deviceId, homeId, SUM(Count) AS Count FROM merged GROUP BY deviceId, homeId
+"""
+    conf = dx.flowgen.conf_text("state", state_tables=[("acc", "deviceId long, homeId long, WindowEnd Timestamp, Count long"),
+                                                       ("totals", "deviceId long, homeId long, Count long")])
+    g, o = both(dx, ctx, conf, SCHEMA1, [PROJ_TS], tr)
+    for b in range(8):
+        T = T0 + b * I
+        check_batch(dx, g, o, gen(dx, 3000, first=b * 3000, shape=1, n_keys=200, base=T), T, now_ms=T + 5)
+        t, which = g.state_table("totals")
+        assert which == o.state["totals"]["active"]
+        assert_same_rows(t, o.state["totals"]["tables"][o.state["totals"]["active"]], dx)
+    g.close()
+
+
+def test_unsupported_sql_fails_at_create(dx, ctx):
+    for bad in ["--DataXQuery--\nx = SELECT a FROM t ORDER BY a\n", "--DataXQuery--\nSET spark.x=1\n--DataXQuery--\n"]:
+        with pytest.raises(dx.DxError):
+            dx.CommonProcessorFactory.createProcessor(ctx, dx.flowgen.conf_text("bad"), SCHEMA1, ["Raw.*\n"], bad)
+    g = dx.CommonProcessorFactory.createProcessor(ctx, dx.flowgen.conf_text("bad2"), SCHEMA1, ["Raw.*\n"],
+                                                 "--DataXQuery--\nx = SELECT nosuch FROM DataXProcessedInput\n")
+    with pytest.raises(dx.DxError):
+        g.process_json(b'{"deviceDetails":{"deviceId":1}}\n', T0, I)
+    g.close()
