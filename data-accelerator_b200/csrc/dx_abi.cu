@@ -61,6 +61,17 @@ int dx_dev_alloc(dx_ctx* c, int64_t bytes, void** out) {
     *out = p; return DX_OK;
 }
 void dx_dev_free(dx_ctx* c, void* p) { if (c && p) c->pool.release(p); }
+int dx_host_alloc(dx_ctx* c, int64_t bytes, void** out) {
+    if (bytes < 0 || !out) return c->set_error(DX_ERR_ARG, "dx_host_alloc: bad arguments");
+    cudaSetDevice(c->device);
+    DX_CUDA(c, cudaHostAlloc(out, (size_t)bytes + 64, cudaHostAllocDefault));
+    return DX_OK;
+}
+void dx_host_free(dx_ctx* c, void* p) { if (c && p) { cudaSetDevice(c->device); cudaFreeHost(p); } }
+int dx_copy_d2h_async(dx_ctx* c, void* dst, const void* src, int64_t bytes) {
+    DX_CUDA(c, cudaMemcpyAsync(dst, src, (size_t)bytes, cudaMemcpyDeviceToHost, c->stream));
+    return DX_OK;
+}
 int dx_copy_h2d(dx_ctx* c, void* dst, const void* src, int64_t bytes) {
     DX_CUDA(c, cudaMemcpyAsync(dst, src, (size_t)bytes, cudaMemcpyHostToDevice, c->stream));
     DX_CUDA(c, cudaStreamSynchronize(c->stream)); return DX_OK;

@@ -121,6 +121,7 @@ struct DxDict {
     DevBuf slots, heap, counters, code_off, code_len;
     // host mirror, refreshed on demand
     std::vector<std::string> host_strings;
+    std::map<std::string, int32_t> seeded;   // literals already entered from the host
     int init(dx_ctx* c, uint32_t capacity_pow2, uint32_t heap_bytes);
     int insert_host(const std::string& s, int32_t* code_out);   // pre-seed literals
     int sync_to_host();                                          // pulls new entries

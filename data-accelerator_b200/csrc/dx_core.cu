@@ -78,6 +78,8 @@ int DxDict::init(dx_ctx* c, uint32_t capacity_pow2, uint32_t heap_bytes) {
 
 int DxDict::insert_host(const std::string& s, int32_t* code_out) {
     dx_ctx* c = ctx;
+    auto hit = seeded.find(s);
+    if (hit != seeded.end()) { if (code_out) *code_out = hit->second; return DX_OK; }
     DevBuf tmp(c, s.size() + 32);
     uint8_t* d = tmp.as<uint8_t>();
     // layout: [0,8) err flags, [8,12) code, [16, ...) bytes
@@ -90,6 +92,7 @@ int DxDict::insert_host(const std::string& s, int32_t* code_out) {
     DX_CUDA(c, cudaMemcpyAsync(&code, d + 8, 4, cudaMemcpyDeviceToHost, c->stream));
     DX_CUDA(c, cudaStreamSynchronize(c->stream));
     if (err || code < 0) return c->set_error(DX_ERR_CAPACITY, "string dictionary overflow");
+    seeded[s] = code;
     if (code_out) *code_out = code;
     return DX_OK;
 }

@@ -587,7 +587,7 @@ class Ev:
         if at == "string" or bt == "string":
             if o not in ("=", "<>"):
                 raise NotImplementedError("string ordering")
-            eq = np.array([av[i] == bv[i] for i in range(len(av))], dtype=bool)
+            eq = np.asarray(av == bv, dtype=bool) if len(av) else np.zeros(0, bool)
             return "bool", (eq if o == "=" else ~eq).astype(np.int64), ok
         if at == "double" or bt == "double":
             x, y = av.astype(np.float64), bv.astype(np.float64)
