@@ -102,6 +102,14 @@ int dx_decoder_decode(dx_decoder* d, const uint8_t* json, int64_t n_bytes, const
     *out = dx_wrap_table(t);
     return DX_OK;
 }
+// Decode for callers that must not allocate device memory in their per-batch path (see the block
+// comment above dx_decoder::decode_noalloc in dx_decode.cu).  No pool, no cudaMalloc/cudaFree here.
+int dx_decoder_decode_noalloc(dx_decoder* d, const uint8_t* json_dev, int64_t n_bytes, int64_t n_events,
+                              void* const* column_ptrs, int n_columns, void* mask_ptr, int64_t* rows, int64_t* null_rows) {
+    if (!d) return DX_ERR_ARG;
+    if (cudaSetDevice(d->ctx->device) != cudaSuccess) return d->ctx->set_error(DX_ERR_CUDA, "cudaSetDevice failed");
+    return d->decode_noalloc(json_dev, n_bytes, n_events, column_ptrs, n_columns, mask_ptr, rows, null_rows);
+}
 int dx_decoder_stats(const dx_decoder* d, int64_t* rows, int64_t* null_rows, int64_t* fast_rows) {
     if (rows) *rows = (int64_t)d->last_stats.rows;
     if (null_rows) *null_rows = (int64_t)d->last_stats.null_rows;

@@ -629,3 +629,121 @@ int dx_decoder::decode_host(const uint8_t* json, int64_t n_bytes, const int64_t*
     }
     return decode_device(staging.as<uint8_t>(), n_bytes, off_dev, n_events, out);
 }
+
+// =======================================================================================
+// Allocation-free decode.
+//
+// Some hosts of this library size all of their device memory when the job starts and must not
+// allocate afterwards: a Spark executor that shares the GPU with other flows cannot afford a
+// cudaMalloc in its per-batch path (cudaMalloc/cudaFree synchronise the whole device, stalling
+// every other stream, and can fail late when memory is tight), and a latency-bound caller wants a
+// per-batch call whose cost never includes the driver's allocator.  For them this variant of K1
+// keeps the kernel's scratch — the tile counter, the decode statistics and the per-tile look-back
+// states — in one fixed array that lives inside the loaded library image on every GPU that loads
+// it (DX_NOALLOC_SCRATCH_BYTES, about 512 KiB, held until the process exits).  The caller passes
+// the input bytes and every output buffer; nothing is taken from the pool or the driver.
+//
+// The array is shared by all calls on a device and keeps the previous call's contents, so each
+// call first clears the part it is going to use; two calls whose GPU work overlaps (different
+// streams or threads) would race on it — callers serialise.
+// =======================================================================================
+#define DX_NOALLOC_MAX_TILES 65536                                   /* x 32 KiB tiles = 2 GiB of JSON per call */
+#define DX_NOALLOC_HEADER_WORDS 8                                    /* [0] tile counter, [2..5] DecodeStats */
+#define DX_NOALLOC_SCRATCH_WORDS (DX_NOALLOC_HEADER_WORDS + DX_NOALLOC_MAX_TILES + 2)
+#define DX_NOALLOC_SCRATCH_BYTES (DX_NOALLOC_SCRATCH_WORDS * 8)
+static __device__ __align__(256) unsigned long long dx_noalloc_scratch[DX_NOALLOC_SCRATCH_WORDS];
+
+#define DX_NOALLOC_MAX_DEVICES 64
+static std::mutex g_noalloc_mu;
+static unsigned long long* g_noalloc_dev_ptr[DX_NOALLOC_MAX_DEVICES];   // device address of the array, per GPU
+
+// In host code `dx_noalloc_scratch` is only a handle for the runtime, not a device address; the
+// address the kernel needs comes from cudaGetSymbolAddress, asked once per device with that device
+// current.  The first call on a device therefore does this one-time set-up (no allocation, but a
+// runtime query): make that first call before starting any stream capture.
+static int noalloc_scratch_address(dx_ctx* c, unsigned long long** out) {
+    if (c->device < 0 || c->device >= DX_NOALLOC_MAX_DEVICES) return c->set_error(DX_ERR_ARG, "device ordinal out of range");
+    std::lock_guard<std::mutex> g(g_noalloc_mu);
+    if (!g_noalloc_dev_ptr[c->device]) {
+        DX_CUDA(c, cudaSetDevice(c->device));
+        void* p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, dx_noalloc_scratch);
+        if (e != cudaSuccess || !p) {
+            return c->set_error(DX_ERR_CUDA, std::string("cudaGetSymbolAddress(dx_noalloc_scratch) failed: ") + cudaGetErrorString(e));
+        }
+        g_noalloc_dev_ptr[c->device] = reinterpret_cast<unsigned long long*>(p);
+    }
+    *out = g_noalloc_dev_ptr[c->device];
+    return DX_OK;
+}
+
+int dx_decoder::decode_noalloc(const uint8_t* json_dev, int64_t n_bytes, int64_t n_events, void* const* column_ptrs,
+                               int n_columns, void* mask_ptr, int64_t* rows_out, int64_t* null_rows_out) {
+    dx_ctx* c = ctx;
+    const int nl = hs.n_leaves;
+    if (n_bytes < 0 || n_events < 0 || (n_bytes > 0 && !json_dev) || !column_ptrs || !mask_ptr)
+        return c->set_error(DX_ERR_ARG, "decode_noalloc: bad arguments (n_events must be stated; NDJSON framing only)");
+    if (n_columns != nl) {
+        char b[160]; snprintf(b, sizeof b, "decode_noalloc: %d column buffers passed, the schema has %d leaf columns", n_columns, nl);
+        return c->set_error(DX_ERR_ARG, b);
+    }
+    for (int k = 0; k < nl; k++) if (!column_ptrs[k]) return c->set_error(DX_ERR_ARG, "decode_noalloc: null column buffer");
+    if (rows_out) *rows_out = 0;
+    if (null_rows_out) *null_rows_out = 0;
+    const int mw = (nl <= 7) ? 1 : 4;
+    if (n_bytes == 0) {
+        if (n_events != 0) return c->set_error(DX_ERR_ARG, "decode_noalloc: empty input but n_events > 0");
+        return DX_OK;
+    }
+    DecodeArgs a; memset(&a, 0, sizeof a);
+    uintptr_t addr = reinterpret_cast<uintptr_t>(json_dev);
+    a.skew = (uint32_t)(addr & 15);
+    a.base_al = reinterpret_cast<const uint8_t*>(addr - a.skew);
+    a.n_end = (long long)a.skew + n_bytes;
+    a.n_tiles = (a.n_end + K1_T - 1) / K1_T;
+    if (a.n_tiles > DX_NOALLOC_MAX_TILES) {
+        char b[256];
+        snprintf(b, sizeof b, "decode_noalloc: a batch of %lld bytes needs %lld tiles; this entry point's fixed scratch handles at most %d tiles "
+                 "(%lld bytes) per call — split the batch or use dx_decoder_decode", (long long)n_bytes, a.n_tiles, DX_NOALLOC_MAX_TILES,
+                 (long long)DX_NOALLOC_MAX_TILES * K1_T);
+        return c->set_error(DX_ERR_CAPACITY, b);
+    }
+    unsigned long long* scratch = nullptr;
+    int rc = noalloc_scratch_address(c, &scratch);
+    if (rc) return rc;
+    DX_CUDA(c, cudaSetDevice(c->device));
+    // the array still holds the last call's counter, statistics and tile states: clear what this call reads
+    DX_CUDA(c, cudaMemsetAsync(scratch, 0, (size_t)(DX_NOALLOC_HEADER_WORDS + a.n_tiles + 2) * 8, c->stream));
+    a.max_rows = n_events;
+    a.offsets = nullptr;
+    for (int k = 0; k < nl; k++) a.cols[k] = column_ptrs[k];
+    a.mask = mask_ptr; a.mask_width = mw;
+    a.dicts = dev_dicts.as<DictDev>();
+    a.schema = dev_schema.as<DSchemaDev>();
+    a.tile_counter = reinterpret_cast<unsigned int*>(scratch);
+    a.stats = reinterpret_cast<DecodeStats*>(scratch + 2);
+    a.tile_state = scratch + DX_NOALLOC_HEADER_WORDS;
+    long long grid = (long long)c->sm_count * ctas_per_sm;
+    if (grid > a.n_tiles) grid = a.n_tiles;
+    k1_decode<<<(unsigned)grid, K1_NT, k1_smem_bytes(), c->stream>>>(a);
+    c->launches["k1_decode"]++;
+    DX_CUDA(c, cudaGetLastError());
+    DecodeStats st;
+    DX_CUDA(c, cudaMemcpyAsync(&st, a.stats, sizeof st, cudaMemcpyDeviceToHost, c->stream));
+    DX_CUDA(c, cudaStreamSynchronize(c->stream));
+    last_stats = st;
+    if (st.flags) {
+        char b[200];
+        snprintf(b, sizeof b, "decode_noalloc failed: flags=0x%llx (1 dictionary overflow, 2 number beyond 19-digit window, "
+                 "4 object/array into string field, 8 long escaped string, 16 more records than n_events)", st.flags);
+        return c->set_error((st.flags & DXF_DICT_OVERFLOW) ? DX_ERR_CAPACITY : DX_ERR_UNSUPPORTED, b);
+    }
+    if ((int64_t)st.rows != n_events) {
+        char b[160];
+        snprintf(b, sizeof b, "decode_noalloc: caller stated %lld events but the batch frames %llu records", (long long)n_events, st.rows);
+        return c->set_error(DX_ERR_ARG, b);
+    }
+    if (rows_out) *rows_out = (int64_t)st.rows;
+    if (null_rows_out) *null_rows_out = (int64_t)st.null_rows;
+    return DX_OK;
+}

@@ -16,4 +16,7 @@ struct dx_decoder {
     int init(dx_ctx* c, const std::string& schema_json);
     int decode_device(const uint8_t* json_dev, int64_t n_bytes, const int64_t* offsets_dev, int64_t n_events, DxTableP* out);
     int decode_host(const uint8_t* json, int64_t n_bytes, const int64_t* offsets, int64_t n_events, DxTableP* out);
+    // allocation-free variant: caller-owned outputs, kernel scratch in a fixed in-library device array
+    int decode_noalloc(const uint8_t* json_dev, int64_t n_bytes, int64_t n_events, void* const* column_ptrs, int n_columns,
+                       void* mask_ptr, int64_t* rows_out, int64_t* null_rows_out);
 };

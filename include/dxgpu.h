@@ -72,6 +72,31 @@ void dx_decoder_destroy(dx_decoder* d);
  * memory_kind says where json/offsets live.  The resulting table owns its columns.           */
 int dx_decoder_decode(dx_decoder* d, const uint8_t* json, int64_t n_bytes, const int64_t* offsets,
                       int64_t n_events, int memory_kind, dx_table** out);
+/* No counterpart in the reference: an entry point for hosts that must not allocate device memory once
+ * the job is running.  Typical cases: a Spark executor sharing the GPU with other flows, where a
+ * cudaMalloc/cudaFree inside the per-batch path would synchronise the whole device and stall every
+ * other stream (and could fail late under memory pressure); or a latency-bound ingest loop that
+ * pre-sizes all of its buffers at start-up.  Same decode as dx_decoder_decode on NDJSON-framed device
+ * input, but every output is caller-owned and the kernel's scratch (tile counter, statistics, per-tile
+ * look-back states) lives in a fixed array inside the library image: about 512 KiB of device memory on
+ * every GPU that loads libdxgpu.so, held until the process exits.  The call performs no cudaMalloc,
+ * cudaFree or pooled allocation.
+ *   json_dev, n_bytes : the batch in DEVICE memory; n_events must be stated (>= 0).
+ *   column_ptrs[n_columns] : one device buffer per leaf column, in the order and with the element
+ *       width of the columns of a table returned by dx_decoder_decode (8 B per row; 4 B for strings).
+ *   mask_ptr : n_events validity elements, 1 byte each when the schema has <= 7 leaf columns, else
+ *       4 bytes: bit k = column k non-NULL, top bit = the event parsed to a non-NULL struct.
+ *   rows / null_rows : optional counts for this call.
+ * Limit: one call handles at most 65536 tiles of 32 KiB = 2 GiB of JSON; larger batches are rejected
+ * with an error (split them, or use dx_decoder_decode).
+ * The scratch array is shared by all calls on a device and still holds the previous call's values, so
+ * each call clears the part it uses first; calls whose GPU work overlaps (other streams, other
+ * threads) race on it and must be serialised by the caller.  The first call on a device also looks up
+ * the array's device address (a one-time runtime query): make that first call before any stream
+ * capture is begun.                                                                              */
+int dx_decoder_decode_noalloc(dx_decoder* d, const uint8_t* json_dev, int64_t n_bytes, int64_t n_events,
+                              void* const* column_ptrs, int n_columns, void* mask_ptr,
+                              int64_t* rows, int64_t* null_rows);
 /* rows decoded / rows that became NULL structs / rows taken by the template fast path, last call */
 int dx_decoder_stats(const dx_decoder* d, int64_t* rows, int64_t* null_rows, int64_t* fast_rows);
 
