@@ -1,6 +1,7 @@
 // dx_flow.cu — flow artefact loading, statement planning/execution and route() bookkeeping.
 // Reference call sites are listed in dx_flow.h; each function below names the lines it restates.
 #include "dx_flow.h"
+#include "dx_rules.h"
 #include <cmath>
 #include <sstream>
 
@@ -517,11 +518,18 @@ struct Exec {
                 for (size_t k = 0; k < v.chunks.size(); k++) {
                     if (cs[k].n == 0) continue;
                     if (v.chunks.size() > 1) return fail(DX_ERR_UNSUPPORTED, "rule evaluation over a multi-batch window view");
-                    ExprPrograms P; BindScope sc = scope_for(v.chunks[k].get(), core);
-                    for (auto& c : conds) { int rc = dx_compile_expr(ctx, sc, c, &P); if (rc) return rc; }
-                    DevPrograms D; int rc = dx_upload_programs(ctx, &P, &D); if (rc) return rc;
-                    rc = dx_eval_flags(ctx, D, cs[k].n, cs[k].filtered ? cs[k].sel->as<int64_t>() : nullptr, oc.data->as<uint32_t>() + off, oc.flag_words);
+                    BindScope sc = scope_for(v.chunks[k].get(), core);
+                    const int64_t* selp = cs[k].filtered ? cs[k].sel->as<int64_t>() : nullptr;
+                    bool fast = false;
+                    int rc = F->generic_rules_only ? DX_OK : dx_rules_eval(ctx, sc, conds, cs[k].n, selp, oc.data->as<uint32_t>() + off, oc.flag_words, &fast);
                     if (rc) return rc;
+                    if (!fast) {   // rule set outside the bucketed planner's limits: generic interpreter
+                        ExprPrograms P;
+                        for (auto& c : conds) { rc = dx_compile_expr(ctx, sc, c, &P); if (rc) return rc; }
+                        DevPrograms D; rc = dx_upload_programs(ctx, &P, &D); if (rc) return rc;
+                        rc = dx_eval_flags(ctx, D, cs[k].n, selp, oc.data->as<uint32_t>() + off, oc.flag_words);
+                        if (rc) return rc;
+                    }
                     off += cs[k].n;
                 }
                 t->cols.push_back(oc); out_index++; continue;
@@ -877,6 +885,7 @@ int dx_flow_build(dx_ctx* ctx, const char* conf_text, const char* schema_json, c
             if (std::find(F->outputs.begin(), F->outputs.end(), name) == F->outputs.end()) F->outputs.push_back(name);
         }
     }
+    { auto g = F->conf.find(root + "gpu.genericrules"); F->generic_rules_only = g != F->conf.end() && lower(g->second) == "true"; }
     auto wm = F->conf.find(root + "watermark"); auto tc = F->conf.find(root + "timestampcolumn");
     F->windows_enabled = !F->windows.empty() && wm != F->conf.end() && tc != F->conf.end();
     if (F->windows_enabled) {

@@ -1,0 +1,628 @@
+// dx_rules.cu — K2 for rule sets: bucketed, bit-sliced predicate evaluation.
+//
+// What it replaces: Spark evaluating R `IF(cond_r, MAP(...), NULL)` expressions per row for the
+// rules CodegenRules compiles into SQL (reference: DataX.Flow.CodegenRules/Engine.cs:232-266,
+// executed by spark.sql at CommonProcessorFactory.scala:271; rule grammar from the GUI:
+// Website/Packages/datax-pipeline/src/modules/flowDefinition/flowHelpers.js:93-217).
+//
+// A naive evaluator costs O(R x leaves) operations per event and is ALU-bound by ~100x.  Here:
+//   * every leaf predicate that depends on ONE column (`col op const`, IN, BETWEEN, LIKE on a
+//     dictionary column, IS [NOT] NULL) is grouped by (column, comparison domain); the column's
+//     constants are sorted once on the host; per event ONE binary search per column yields a
+//     bucket, and a precomputed table row gives the truth of all that column's leaves at once;
+//   * table rows are laid out in RULE ORDER per leaf slot (bit r of slot j = truth of rule r's
+//     j-th distinct leaf), so OR-ing the rows of all columns assembles R-bit vectors directly in
+//     output order — no bit permutation;
+//   * each rule's AND/OR/NOT tree is put in disjunctive normal form over its (<= 4) slots; rules
+//     with the same DNF shape form a class and are combined with 32-rules-per-instruction word
+//     operations under the class's membership mask.  Three-valued logic is exact: tables hold a
+//     TRUE plane and (only if some rule negates) a FALSE plane; NULL inputs select a bucket whose
+//     rows are neither.
+//   * anything that is not a one-column predicate (col-vs-col, arithmetic, IF ...) becomes a
+//     "generic leaf" evaluated by the bytecode interpreter inside the same kernel; a rule that
+//     does not fit (more than 4 distinct leaves, DNF blow-up) becomes one generic leaf as a whole.
+#include "dx_rules.h"
+#include "dx_expr_eval.cuh"
+#include <cmath>
+
+using namespace dxsql;
+
+#define RB_MAX_SPACES 32
+#define RB_MAX_CLASSES 16
+#define RB_MAX_TERMS 8
+#define RB_JMAX 4
+#define RB_WG 8                      // flag words handled per pass (256 rules)
+#define RB_SMEM_TABLE_BYTES (160 * 1024)
+
+enum { DOM_I64 = 0, DOM_F64 = 1, DOM_F64_FROM_I64 = 2, DOM_CODE = 3, DOM_GENERIC = 4 };
+
+struct RSpaceDev {
+    ProgCol col;
+    int32_t domain;
+    int32_t n_consts;        // numeric domains
+    int32_t const_off;       // index into consts[]
+    int32_t lut_off, lut_size, other_bucket;   // DOM_CODE: code -> bucket
+    int32_t null_bucket;
+    int32_t row_base;        // first table row of this space
+    uint32_t slot_mask;      // slots (bits 0..J-1) some rule places a leaf of this space in
+    uint32_t prog_start;     // DOM_GENERIC
+    int32_t pad;
+};
+struct RClassDev {
+    int32_t n_terms;
+    uint8_t use[RB_MAX_TERMS], neg[RB_MAX_TERMS];
+    int32_t mask_off;        // index into class_masks[] (Wp words)
+};
+struct RulesDev {
+    const RSpaceDev* spaces; int32_t n_spaces;
+    const RClassDev* classes; int32_t n_classes;
+    const long long* consts; int32_t n_consts;
+    const int32_t* luts; int32_t n_luts;
+    const uint32_t* class_masks;
+    const uint32_t* table_t; const uint32_t* table_f;   // [rows][J][Wp]
+    int32_t total_rows, J, Wp, words;
+    int32_t table_in_smem;
+    // generic leaves
+    const uint32_t* code; const long long* gconsts; const ProgCol* gcols; const ProgLut* gluts; int32_t n_gcols;
+};
+
+static __device__ __forceinline__ int bucket_i64(const long long* c, int m, long long v) {
+    int lo = 0, hi = m;
+    while (lo < hi) { int mid = (lo + hi) >> 1; if (c[mid] < v) lo = mid + 1; else hi = mid; }
+    return 2 * lo + ((lo < m && c[lo] == v) ? 1 : 0);
+}
+static __device__ __forceinline__ int bucket_f64(const long long* c, int m, double v) {
+    if (v != v) return 2 * m;                                   // NaN is greater than every constant
+    int lo = 0, hi = m;
+    while (lo < hi) { int mid = (lo + hi) >> 1; if (__longlong_as_double(c[mid]) < v) lo = mid + 1; else hi = mid; }
+    return 2 * lo + ((lo < m && __longlong_as_double(c[lo]) == v) ? 1 : 0);
+}
+
+template <int J, bool NEEDF>
+__global__ void __launch_bounds__(256) k2_rules_bucket(const __grid_constant__ RulesDev D, long long n_rows, const long long* sel, uint32_t* flags) {
+    extern __shared__ __align__(16) uint8_t rsm[];
+    // shared layout: spaces | classes | class masks | consts | luts | [table_t | table_f]
+    RSpaceDev* s_spaces = reinterpret_cast<RSpaceDev*>(rsm);
+    RClassDev* s_classes = reinterpret_cast<RClassDev*>(s_spaces + D.n_spaces);
+    uint32_t* s_cmask = reinterpret_cast<uint32_t*>(s_classes + D.n_classes);
+    long long* s_consts = reinterpret_cast<long long*>(s_cmask + ((D.n_classes * D.Wp + 1) & ~1));
+    int32_t* s_luts = reinterpret_cast<int32_t*>(s_consts + D.n_consts);
+    uint32_t* s_tab = reinterpret_cast<uint32_t*>((reinterpret_cast<uintptr_t>(s_luts + ((D.n_luts + 3) & ~3)) + 15) & ~uintptr_t(15));
+    for (int i = threadIdx.x; i < D.n_spaces; i += blockDim.x) s_spaces[i] = D.spaces[i];
+    for (int i = threadIdx.x; i < D.n_classes; i += blockDim.x) s_classes[i] = D.classes[i];
+    for (int i = threadIdx.x; i < D.n_classes * D.Wp; i += blockDim.x) s_cmask[i] = D.class_masks[i];
+    for (int i = threadIdx.x; i < D.n_consts; i += blockDim.x) s_consts[i] = D.consts[i];
+    for (int i = threadIdx.x; i < D.n_luts; i += blockDim.x) s_luts[i] = D.luts[i];
+    const int row_words = J * D.Wp;
+    const long long tab_words = (long long)D.total_rows * row_words;
+    const uint32_t* tab_t = D.table_t; const uint32_t* tab_f = D.table_f;
+    if (D.table_in_smem) {
+        const uint4* src = reinterpret_cast<const uint4*>(D.table_t); uint4* dst = reinterpret_cast<uint4*>(s_tab);
+        for (long long i = threadIdx.x; i < tab_words / 4; i += blockDim.x) dst[i] = src[i];
+        tab_t = s_tab;
+        if (NEEDF) {
+            const uint4* srcf = reinterpret_cast<const uint4*>(D.table_f); uint4* dstf = reinterpret_cast<uint4*>(s_tab + tab_words);
+            for (long long i = threadIdx.x; i < tab_words / 4; i += blockDim.x) dstf[i] = srcf[i];
+            tab_f = s_tab + tab_words;
+        }
+    }
+    __syncthreads();
+    EvalView gv{D.code, D.gconsts, D.gcols, D.gluts};
+    const int n_wg = D.Wp / RB_WG;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_rows; i += (long long)gridDim.x * blockDim.x) {
+        const long long row = sel ? sel[i] : i;
+        int brow[RB_MAX_SPACES];
+        for (int s = 0; s < D.n_spaces; s++) {
+            const RSpaceDev& sp = s_spaces[s];
+            int b;
+            if (sp.domain == DOM_GENERIC) {
+                long long val; bool isnull;
+                eval_program(gv, sp.prog_start, row, val, isnull);
+                b = isnull ? 2 : (val != 0 ? 1 : 0);
+            } else {
+                bool valid = true;
+                if (sp.col.vmask) {
+                    uint32_t m = sp.col.vwidth == 1 ? reinterpret_cast<const uint8_t*>(sp.col.vmask)[row] : reinterpret_cast<const uint32_t*>(sp.col.vmask)[row];
+                    valid = (m >> sp.col.vbit) & 1u;
+                }
+                if (!valid) b = sp.null_bucket;
+                else if (sp.domain == DOM_CODE) {
+                    int code = reinterpret_cast<const int32_t*>(sp.col.data)[row];
+                    b = (code >= 0 && code < sp.lut_size) ? s_luts[sp.lut_off + code] : sp.other_bucket;
+                } else {
+                    long long v = reinterpret_cast<const long long*>(sp.col.data)[row];
+                    if (sp.domain == DOM_I64) b = bucket_i64(s_consts + sp.const_off, sp.n_consts, v);
+                    else if (sp.domain == DOM_F64) b = bucket_f64(s_consts + sp.const_off, sp.n_consts, __longlong_as_double(v));
+                    else b = bucket_f64(s_consts + sp.const_off, sp.n_consts, (double)v);
+                }
+            }
+            brow[s] = (sp.row_base + b) * row_words;
+        }
+        for (int wg = 0; wg < n_wg; wg++) {
+            uint32_t T[J][RB_WG], F[NEEDF ? J : 1][RB_WG];
+#pragma unroll
+            for (int j = 0; j < J; j++)
+#pragma unroll
+                for (int w = 0; w < RB_WG; w++) { T[j][w] = 0; if (NEEDF) F[j][w] = 0; }
+            for (int s = 0; s < D.n_spaces; s++) {
+                const uint32_t sm = s_spaces[s].slot_mask;
+                const int base = brow[s] + wg * RB_WG;
+#pragma unroll
+                for (int j = 0; j < J; j++) {
+                    if ((sm >> j) & 1u) {
+                        const uint4 a = *reinterpret_cast<const uint4*>(tab_t + base + j * D.Wp);
+                        const uint4 b4 = *reinterpret_cast<const uint4*>(tab_t + base + j * D.Wp + 4);
+                        T[j][0] |= a.x; T[j][1] |= a.y; T[j][2] |= a.z; T[j][3] |= a.w;
+                        T[j][4] |= b4.x; T[j][5] |= b4.y; T[j][6] |= b4.z; T[j][7] |= b4.w;
+                        if (NEEDF) {
+                            const uint4 c = *reinterpret_cast<const uint4*>(tab_f + base + j * D.Wp);
+                            const uint4 d = *reinterpret_cast<const uint4*>(tab_f + base + j * D.Wp + 4);
+                            F[j][0] |= c.x; F[j][1] |= c.y; F[j][2] |= c.z; F[j][3] |= c.w;
+                            F[j][4] |= d.x; F[j][5] |= d.y; F[j][6] |= d.z; F[j][7] |= d.w;
+                        }
+                    }
+                }
+            }
+            uint32_t out[RB_WG];
+#pragma unroll
+            for (int w = 0; w < RB_WG; w++) out[w] = 0;
+            for (int k = 0; k < D.n_classes; k++) {
+                const RClassDev& cl = s_classes[k];
+                const uint32_t* cm = s_cmask + cl.mask_off + wg * RB_WG;
+                for (int t = 0; t < cl.n_terms; t++) {
+                    const uint32_t use = cl.use[t], neg = cl.neg[t];
+                    uint32_t acc[RB_WG];
+#pragma unroll
+                    for (int w = 0; w < RB_WG; w++) acc[w] = cm[w];
+#pragma unroll
+                    for (int j = 0; j < J; j++) {
+                        if ((use >> j) & 1u) {
+                            if (NEEDF && ((neg >> j) & 1u)) {
+#pragma unroll
+                                for (int w = 0; w < RB_WG; w++) acc[w] &= F[j][w];
+                            } else {
+#pragma unroll
+                                for (int w = 0; w < RB_WG; w++) acc[w] &= T[j][w];
+                            }
+                        }
+                    }
+#pragma unroll
+                    for (int w = 0; w < RB_WG; w++) out[w] |= acc[w];
+                }
+            }
+#pragma unroll
+            for (int w = 0; w < RB_WG; w++) {
+                const int gw = wg * RB_WG + w;
+                if (gw < D.words) flags[(long long)gw * n_rows + i] = out[w];
+            }
+        }
+    }
+}
+
+// =======================================================================================
+// host-side planner
+// =======================================================================================
+namespace {
+
+struct BNode { int kind; std::vector<BNode> ch; int leaf = -1; };   // kind: 0 leaf, 1 AND, 2 OR, 3 NOT
+struct Lit { int leaf; bool neg; bool operator<(const Lit& o) const { return leaf != o.leaf ? leaf < o.leaf : neg < o.neg; } bool operator==(const Lit& o) const { return leaf == o.leaf && neg == o.neg; } };
+typedef std::vector<Lit> Term;
+
+struct LeafDef {
+    int space = -1;
+    int kind = 0;             // 0 numeric compare, 1 code compare, 2 like, 3 is-null, 4 generic
+    int op = 0;               // 0 = 1 <> 2 < 3 <= 4 > 5 >=
+    long long cbits = 0;      // numeric constant (int64 or double bits) before sorting
+    int cidx = -1;            // index among the space's sorted constants / literal index for codes
+    int code = -1;
+    bool negated = false;     // IS NOT NULL / NOT LIKE
+    std::string pattern;
+};
+struct SpaceDef {
+    int table_col = -1, domain = 0;
+    std::vector<long long> consts;          // sorted distinct (numeric domains)
+    std::vector<int> lit_codes;             // DOM_CODE: literal codes -> bucket index
+    bool per_code = false;                  // DOM_CODE with LIKE: one bucket per dictionary code
+    DxDictP dict;
+    int n_buckets = 0, null_bucket = 0, other_bucket = 0, row_base = 0;
+    uint32_t slot_mask = 0;
+    int prog = -1;                          // DOM_GENERIC
+};
+
+struct Planner {
+    dx_ctx* ctx; const BindScope& sc;
+    std::vector<LeafDef> leaves; std::map<std::string, int> leaf_by_key;
+    std::vector<SpaceDef> spaces; std::map<std::pair<int, int>, int> space_by_key;
+    ExprPrograms G;
+    std::string err;
+
+    Planner(dx_ctx* c, const BindScope& s) : ctx(c), sc(s) {}
+
+    int space_for(int col, int domain) {
+        auto key = std::make_pair(col, domain);
+        auto it = space_by_key.find(key);
+        if (it != space_by_key.end()) return it->second;
+        SpaceDef sp; sp.table_col = col; sp.domain = domain; sp.dict = sc.table->cols[col].dict;
+        spaces.push_back(sp); space_by_key[key] = (int)spaces.size() - 1;
+        return (int)spaces.size() - 1;
+    }
+    int any_space_for_column(int col) {
+        for (size_t s = 0; s < spaces.size(); s++) if (spaces[s].table_col == col && spaces[s].domain != DOM_GENERIC) return (int)s;
+        int t = sc.table->cols[col].type;
+        return space_for(col, t == DX_T_STR ? DOM_CODE : (t == DX_T_F64 ? DOM_F64 : DOM_I64));
+    }
+    int generic_leaf(const ExprP& e) {
+        std::string key = "G:" + to_string(e);
+        auto it = leaf_by_key.find(key);
+        if (it != leaf_by_key.end()) return it->second;
+        int prog = (int)G.prog_start.size();
+        if (dx_compile_expr(ctx, sc, e, &G)) { err = ctx->last_error; return -1; }
+        SpaceDef sp; sp.domain = DOM_GENERIC; sp.prog = prog;
+        spaces.push_back(sp);
+        LeafDef l; l.kind = 4; l.space = (int)spaces.size() - 1;
+        leaves.push_back(l); leaf_by_key[key] = (int)leaves.size() - 1;
+        return (int)leaves.size() - 1;
+    }
+    // column with device data, or -1
+    int data_column(const ExprP& e) {
+        if (e->kind != EK::Col) return -1;
+        std::string er; int ci = dx_resolve_column(sc, e->parts, &er);
+        if (ci < 0) return -1;
+        const DxColumn& c = sc.table->cols[ci];
+        if (!c.data || c.all_null || c.type == DX_T_FLAGS || c.type == DX_T_NULL) return -1;
+        return ci;
+    }
+    static bool numeric_literal(const ExprP& e, bool* is_dec, long long* iv, double* dv) {
+        const Expr* x = e.get(); bool neg = false;
+        if (x->kind == EK::Neg && (x->args[0]->kind == EK::Int || x->args[0]->kind == EK::Dec)) { neg = true; x = x->args[0].get(); }
+        if (x->kind == EK::Int) { *is_dec = false; *iv = neg ? -x->ival : x->ival; *dv = (double)*iv; return true; }
+        if (x->kind == EK::Dec) { *is_dec = true; *dv = neg ? -x->dval : x->dval; *iv = 0; return true; }
+        return false;
+    }
+    int leaf_for(const ExprP& e) {
+        std::string key = to_string(e);
+        auto it = leaf_by_key.find(key);
+        if (it != leaf_by_key.end()) return it->second;
+        LeafDef l; bool ok = false;
+        if (e->kind == EK::Bin) {
+            static const char* ops[] = {"=", "<>", "<", "<=", ">", ">="};
+            static const int flip[] = {0, 1, 4, 5, 2, 3};
+            int op = -1; for (int k = 0; k < 6; k++) if (e->sval == ops[k]) op = k;
+            if (op >= 0) {
+                int lc = data_column(e->args[0]), rc = data_column(e->args[1]);
+                const ExprP* lit = nullptr; int col = -1;
+                if (lc >= 0 && rc < 0) { col = lc; lit = &e->args[1]; }
+                else if (rc >= 0 && lc < 0) { col = rc; lit = &e->args[0]; op = flip[op]; }
+                if (col >= 0) {
+                    const DxColumn& c = sc.table->cols[col];
+                    bool is_dec; long long iv; double dv;
+                    if (c.type == DX_T_STR) {
+                        if ((*lit)->kind == EK::Str && op <= 1 && c.dict) {
+                            int32_t code;
+                            if (c.dict->insert_host((*lit)->sval, &code)) { err = ctx->last_error; return -1; }
+                            l.kind = 1; l.op = op; l.code = code; l.space = space_for(col, DOM_CODE); ok = true;
+                        }
+                    } else if (numeric_literal(*lit, &is_dec, &iv, &dv) && c.type != DX_T_TS) {
+                        l.kind = 0; l.op = op;
+                        if (c.type == DX_T_F64) { l.space = space_for(col, DOM_F64); memcpy(&l.cbits, &dv, 8); }
+                        else if (is_dec) { l.space = space_for(col, DOM_F64_FROM_I64); memcpy(&l.cbits, &dv, 8); }
+                        else { l.space = space_for(col, DOM_I64); l.cbits = iv; }
+                        ok = true;
+                    }
+                }
+            }
+        } else if (e->kind == EK::IsNull) {
+            int col = data_column(e->args[0]);
+            if (col >= 0) { l.kind = 3; l.negated = e->negated; l.space = any_space_for_column(col); ok = true; }
+        } else if (e->kind == EK::Like) {
+            int col = data_column(e->args[0]);
+            if (col >= 0 && sc.table->cols[col].type == DX_T_STR && sc.table->cols[col].dict && e->args[1]->kind == EK::Str) {
+                if (sc.table->cols[col].dict->sync_to_host()) { err = ctx->last_error; return -1; }
+                if (sc.table->cols[col].dict->host_strings.size() <= 4096) {
+                    l.kind = 2; l.negated = e->negated; l.pattern = e->args[1]->sval; l.space = space_for(col, DOM_CODE);
+                    spaces[l.space].per_code = true; ok = true;
+                }
+            }
+        }
+        if (!ok) return generic_leaf(e);
+        leaves.push_back(l); leaf_by_key[key] = (int)leaves.size() - 1;
+        return (int)leaves.size() - 1;
+    }
+    bool build(const ExprP& e, BNode* out) {
+        if (e->kind == EK::Bin && (e->sval == "AND" || e->sval == "OR")) {
+            out->kind = e->sval == "AND" ? 1 : 2; out->ch.resize(2);
+            return build(e->args[0], &out->ch[0]) && build(e->args[1], &out->ch[1]);
+        }
+        if (e->kind == EK::Not) { out->kind = 3; out->ch.resize(1); return build(e->args[0], &out->ch[0]); }
+        if (e->kind == EK::In && e->args.size() >= 2) {
+            BNode orn; orn.kind = 2;
+            for (size_t i = 1; i < e->args.size(); i++) {
+                auto eq = std::make_shared<Expr>(); eq->kind = EK::Bin; eq->sval = "="; eq->args = {e->args[0], e->args[i]};
+                BNode c; c.kind = 0; c.leaf = leaf_for(eq); if (c.leaf < 0) return false; orn.ch.push_back(c);
+            }
+            if (orn.ch.size() == 1) orn = orn.ch[0];
+            if (e->negated) { out->kind = 3; out->ch.push_back(orn); } else *out = orn;
+            return true;
+        }
+        if (e->kind == EK::Between) {
+            auto ge = std::make_shared<Expr>(); ge->kind = EK::Bin; ge->sval = ">="; ge->args = {e->args[0], e->args[1]};
+            auto le = std::make_shared<Expr>(); le->kind = EK::Bin; le->sval = "<="; le->args = {e->args[0], e->args[2]};
+            BNode an; an.kind = 1; an.ch.resize(2);
+            an.ch[0].kind = 0; an.ch[0].leaf = leaf_for(ge); an.ch[1].kind = 0; an.ch[1].leaf = leaf_for(le);
+            if (an.ch[0].leaf < 0 || an.ch[1].leaf < 0) return false;
+            if (e->negated) { out->kind = 3; out->ch.push_back(an); } else *out = an;
+            return true;
+        }
+        out->kind = 0; out->leaf = leaf_for(e);
+        return out->leaf >= 0;
+    }
+    // DNF of a tree with negation pushed to the leaves (valid in Kleene logic); false on blow-up
+    static bool dnf(const BNode& n, bool neg, std::vector<Term>* out) {
+        int kind = n.kind;
+        if (kind == 3) return dnf(n.ch[0], !neg, out);
+        if (kind == 0) { out->push_back(Term{Lit{n.leaf, neg}}); return true; }
+        bool is_and = (kind == 1) != neg;     // De Morgan
+        std::vector<std::vector<Term>> parts(n.ch.size());
+        for (size_t i = 0; i < n.ch.size(); i++) if (!dnf(n.ch[i], neg, &parts[i])) return false;
+        if (!is_and) { for (auto& p : parts) for (auto& t : p) out->push_back(t); }
+        else {
+            std::vector<Term> acc{Term{}};
+            for (auto& p : parts) {
+                std::vector<Term> next;
+                for (auto& a : acc) for (auto& t : p) {
+                    Term m = a; for (auto& l : t) if (std::find(m.begin(), m.end(), l) == m.end()) m.push_back(l);
+                    next.push_back(m);
+                    if (next.size() > 64) return false;
+                }
+                acc.swap(next);
+            }
+            for (auto& t : acc) out->push_back(t);
+        }
+        return out->size() <= 64;
+    }
+};
+
+// truth of a leaf in a bucket: 1 TRUE, 0 FALSE, 2 NULL
+static int leaf_truth(const LeafDef& l, const SpaceDef& sp, int b) {
+    if (sp.domain == DOM_GENERIC) return b == 1 ? 1 : (b == 0 ? 0 : 2);
+    if (l.kind == 3) { bool isnull = b == sp.null_bucket; return (isnull != l.negated) ? 1 : 0; }
+    if (b == sp.null_bucket) return 2;
+    if (l.kind == 0) {
+        int pos = b >> 1, eq = b & 1, ci = l.cidx, cmp;      // cmp = sign(value - const)
+        if (eq) cmp = pos == ci ? 0 : (ci > pos ? -1 : 1);
+        else cmp = ci >= pos ? -1 : 1;
+        switch (l.op) { case 0: return cmp == 0; case 1: return cmp != 0; case 2: return cmp < 0; case 3: return cmp <= 0; case 4: return cmp > 0; default: return cmp >= 0; }
+    }
+    if (l.kind == 1) {
+        bool same;
+        if (sp.per_code) same = (b == l.code);
+        else same = (b < (int)sp.lit_codes.size() && sp.lit_codes[b] == l.code);
+        return (l.op == 0) == same ? 1 : 0;
+    }
+    return 0;
+}
+
+// SQL LIKE on one dictionary entry (same matcher as the generic path)
+static bool like_match2(const std::string& s, const std::string& p) {
+    size_t n = s.size(), m = p.size();
+    std::vector<size_t> cps; for (size_t i = 0; i < n; i++) if ((s[i] & 0xC0) != 0x80) cps.push_back(i);
+    cps.push_back(n); size_t ns = cps.size() - 1;
+    struct PT { int kind; std::string lit; }; std::vector<PT> pt;
+    for (size_t i = 0; i < m;) {
+        char c = p[i];
+        if (c == '\\' && i + 1 < m) { i++; size_t j = i + 1; while (j < m && (p[j] & 0xC0) == 0x80) j++; pt.push_back({0, p.substr(i, j - i)}); i = j; }
+        else if (c == '%') { pt.push_back({2, ""}); i++; }
+        else if (c == '_') { pt.push_back({1, ""}); i++; }
+        else { size_t j = i + 1; while (j < m && (p[j] & 0xC0) == 0x80) j++; pt.push_back({0, p.substr(i, j - i)}); i = j; }
+    }
+    size_t np = pt.size(); std::vector<char> dp((ns + 1) * (np + 1), 0);
+    auto at = [&](size_t i, size_t j) -> char& { return dp[i * (np + 1) + j]; };
+    at(0, 0) = 1;
+    for (size_t j = 1; j <= np; j++) at(0, j) = at(0, j - 1) && pt[j - 1].kind == 2;
+    for (size_t i = 1; i <= ns; i++) for (size_t j = 1; j <= np; j++) {
+        const PT& t = pt[j - 1];
+        if (t.kind == 2) at(i, j) = at(i, j - 1) || at(i - 1, j);
+        else if (t.kind == 1) at(i, j) = at(i - 1, j - 1);
+        else at(i, j) = at(i - 1, j - 1) && s.compare(cps[i - 1], cps[i] - cps[i - 1], t.lit) == 0;
+    }
+    return at(ns, np) != 0;
+}
+
+} // namespace
+
+template <int J, bool NEEDF>
+static void launch_rules(dx_ctx* ctx, const RulesDev& D, size_t smem, int64_t n_rows, const int64_t* sel, uint32_t* flags) {
+    cudaFuncSetAttribute(k2_rules_bucket<J, NEEDF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    int occ = 1;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k2_rules_bucket<J, NEEDF>, 256, smem);
+    if (occ < 1) occ = 1;
+    long long blocks = (n_rows + 255) / 256, cap = (long long)ctx->sm_count * occ;
+    if (blocks > cap) blocks = cap;
+    k2_rules_bucket<J, NEEDF><<<(unsigned)blocks, 256, smem, ctx->stream>>>(D, n_rows, reinterpret_cast<const long long*>(sel), flags);
+}
+
+int dx_rules_eval(dx_ctx* ctx, const BindScope& sc, const std::vector<ExprP>& conds, int64_t n_rows, const int64_t* sel,
+                  uint32_t* flags, int words, bool* used_fast) {
+    *used_fast = false;
+    if (n_rows <= 0 || conds.empty()) return DX_OK;
+    const int R = (int)conds.size();
+    Planner P(ctx, sc);
+    // per rule: DNF over leaf ids
+    std::vector<std::vector<Term>> rule_terms(R);
+    for (int r = 0; r < R; r++) {
+        BNode root; std::vector<Term> terms; bool fits = false;
+        size_t leaves_before = P.leaves.size(), spaces_before = P.spaces.size();
+        (void)leaves_before; (void)spaces_before;
+        if (P.build(conds[r], &root) && Planner::dnf(root, false, &terms)) {
+            std::vector<int> distinct;
+            for (auto& t : terms) for (auto& l : t) if (std::find(distinct.begin(), distinct.end(), l.leaf) == distinct.end()) distinct.push_back(l.leaf);
+            fits = distinct.size() <= RB_JMAX && terms.size() <= RB_MAX_TERMS;
+        }
+        if (!P.err.empty()) return ctx->set_error(DX_ERR_UNSUPPORTED, P.err);
+        if (!fits) {
+            int g = P.generic_leaf(conds[r]);
+            if (g < 0) return ctx->set_error(DX_ERR_UNSUPPORTED, P.err);
+            terms.assign(1, Term{Lit{g, false}});
+        }
+        rule_terms[r] = terms;
+    }
+    if ((int)P.spaces.size() > RB_MAX_SPACES) return DX_OK;     // caller falls back to the generic kernel
+    // finalise spaces: constants, buckets
+    for (auto& l : P.leaves) {
+        SpaceDef& sp = P.spaces[l.space];
+        if (l.kind == 0) sp.consts.push_back(l.cbits);
+        if (l.kind == 1 && std::find(sp.lit_codes.begin(), sp.lit_codes.end(), l.code) == sp.lit_codes.end()) sp.lit_codes.push_back(l.code);
+    }
+    std::vector<long long> all_consts; std::vector<int32_t> all_luts;
+    std::vector<RSpaceDev> sdev(P.spaces.size());
+    int total_rows = 0;
+    for (size_t s = 0; s < P.spaces.size(); s++) {
+        SpaceDef& sp = P.spaces[s]; RSpaceDev& d = sdev[s]; memset(&d, 0, sizeof d);
+        d.domain = sp.domain;
+        if (sp.domain == DOM_GENERIC) { sp.n_buckets = 3; sp.null_bucket = 2; d.prog_start = P.G.prog_start[sp.prog]; }
+        else {
+            const DxColumn& c = sc.table->cols[sp.table_col];
+            d.col.data = c.data->p; d.col.vmask = c.vmask ? c.vmask->p : nullptr; d.col.vwidth = c.vwidth; d.col.vbit = c.vbit; d.col.width = dx_type_width(c.type);
+            if (sp.domain == DOM_CODE) {
+                if (sp.per_code) {
+                    int n = (int)sp.dict->host_strings.size();
+                    sp.other_bucket = n; sp.null_bucket = n + 1; sp.n_buckets = n + 2;
+                    d.lut_off = (int)all_luts.size(); d.lut_size = n;
+                    for (int k = 0; k < n; k++) all_luts.push_back(k);
+                } else {
+                    int n = (int)sp.lit_codes.size(), mx = -1;
+                    for (int cde : sp.lit_codes) mx = std::max(mx, cde);
+                    sp.other_bucket = n; sp.null_bucket = n + 1; sp.n_buckets = n + 2;
+                    d.lut_off = (int)all_luts.size(); d.lut_size = mx + 1;
+                    for (int k = 0; k <= mx; k++) { int b = n; for (int q = 0; q < n; q++) if (sp.lit_codes[q] == k) b = q; all_luts.push_back(b); }
+                }
+            } else {
+                if (sp.domain == DOM_I64) std::sort(sp.consts.begin(), sp.consts.end());
+                else std::sort(sp.consts.begin(), sp.consts.end(), [](long long a, long long b) { double x, y; memcpy(&x, &a, 8); memcpy(&y, &b, 8); return x < y; });
+                if (sp.domain == DOM_I64) sp.consts.erase(std::unique(sp.consts.begin(), sp.consts.end()), sp.consts.end());
+                else sp.consts.erase(std::unique(sp.consts.begin(), sp.consts.end(), [](long long a, long long b) { double x, y; memcpy(&x, &a, 8); memcpy(&y, &b, 8); return x == y; }), sp.consts.end());
+                int m = (int)sp.consts.size();
+                sp.null_bucket = 2 * m + 1; sp.n_buckets = 2 * m + 2;
+                d.const_off = (int)all_consts.size(); d.n_consts = m;
+                for (long long v : sp.consts) all_consts.push_back(v);
+            }
+        }
+        d.other_bucket = sp.other_bucket; d.null_bucket = sp.null_bucket;
+        sp.row_base = total_rows; d.row_base = total_rows; total_rows += sp.n_buckets;
+    }
+    for (auto& l : P.leaves) {
+        SpaceDef& sp = P.spaces[l.space];
+        if (l.kind == 0) {
+            for (size_t k = 0; k < sp.consts.size(); k++) {
+                bool same;
+                if (sp.domain == DOM_I64) same = sp.consts[k] == l.cbits;
+                else { double x, y; memcpy(&x, &sp.consts[k], 8); memcpy(&y, &l.cbits, 8); same = x == y; }
+                if (same) l.cidx = (int)k;
+            }
+        }
+    }
+    // slots and classes
+    int J = 1; bool needf = false;
+    struct RulePlan { std::vector<int> slot_leaf; std::vector<std::pair<uint8_t, uint8_t>> terms; int cls = -1; };
+    std::vector<RulePlan> plans(R);
+    std::map<std::string, int> class_by_sig; std::vector<RClassDev> classes;
+    for (int r = 0; r < R; r++) {
+        RulePlan& rp = plans[r];
+        for (auto& t : rule_terms[r]) {
+            uint8_t use = 0, neg = 0;
+            for (auto& l : t) {
+                int j = (int)(std::find(rp.slot_leaf.begin(), rp.slot_leaf.end(), l.leaf) - rp.slot_leaf.begin());
+                if (j == (int)rp.slot_leaf.size()) rp.slot_leaf.push_back(l.leaf);
+                use |= 1u << j; if (l.neg) { neg |= 1u << j; needf = true; }
+            }
+            rp.terms.emplace_back(use, neg);
+        }
+        std::sort(rp.terms.begin(), rp.terms.end());
+        rp.terms.erase(std::unique(rp.terms.begin(), rp.terms.end()), rp.terms.end());
+        J = std::max(J, (int)rp.slot_leaf.size());
+        std::string sig;
+        for (auto& t : rp.terms) { sig += std::to_string(t.first) + "/" + std::to_string(t.second) + ";"; }
+        auto it = class_by_sig.find(sig);
+        if (it == class_by_sig.end()) {
+            if ((int)classes.size() >= RB_MAX_CLASSES) return DX_OK;     // fall back
+            RClassDev c; memset(&c, 0, sizeof c); c.n_terms = (int)rp.terms.size();
+            for (size_t t = 0; t < rp.terms.size(); t++) { c.use[t] = rp.terms[t].first; c.neg[t] = rp.terms[t].second; }
+            classes.push_back(c); class_by_sig[sig] = (int)classes.size() - 1; rp.cls = (int)classes.size() - 1;
+        } else rp.cls = it->second;
+    }
+    const int Wp = ((words + RB_WG - 1) / RB_WG) * RB_WG;
+    std::vector<uint32_t> cmask((size_t)classes.size() * Wp, 0);
+    for (size_t k = 0; k < classes.size(); k++) classes[k].mask_off = (int)k * Wp;
+    for (int r = 0; r < R; r++) cmask[(size_t)plans[r].cls * Wp + r / 32] |= 1u << (r % 32);
+    // truth tables in rule order per slot
+    const size_t row_words = (size_t)J * Wp;
+    std::vector<uint32_t> tt((size_t)total_rows * row_words, 0), tf(needf ? (size_t)total_rows * row_words : 0, 0);
+    std::map<std::pair<int, int>, std::vector<uint8_t>> like_cache;   // (space, leaf) -> per-code result
+    for (int r = 0; r < R; r++) {
+        for (size_t j = 0; j < plans[r].slot_leaf.size(); j++) {
+            const int li = plans[r].slot_leaf[j];
+            const LeafDef& l = P.leaves[li]; SpaceDef& sp = P.spaces[l.space];
+            sp.slot_mask |= 1u << j;
+            for (int b = 0; b < sp.n_buckets; b++) {
+                int tv;
+                if (l.kind == 2) {
+                    if (b == sp.null_bucket) tv = 2;
+                    else if (b == sp.other_bucket) tv = l.negated ? 1 : 0;    // codes that appear later: rebuilt next batch before use
+                    else { bool m = like_match2(sp.dict->host_strings[b], l.pattern); tv = (m != l.negated) ? 1 : 0; }
+                } else tv = leaf_truth(l, sp, b);
+                size_t off = ((size_t)(sp.row_base + b) * J + j) * Wp + r / 32;
+                if (tv == 1) tt[off] |= 1u << (r % 32);
+                else if (tv == 0 && needf) tf[off] |= 1u << (r % 32);
+            }
+        }
+    }
+    for (size_t s = 0; s < P.spaces.size(); s++) sdev[s].slot_mask = P.spaces[s].slot_mask;
+    // a per-code LIKE space must see every code of this batch: the dictionary was synced when the leaf was planned,
+    // i.e. after this batch was decoded, so the table covers all codes present in the columns.
+    // ---- upload
+    DevPrograms GD;
+    if (!P.G.prog_start.empty()) { int rc = dx_upload_programs(ctx, &P.G, &GD); if (rc) return rc; }
+    if (P.G.cols.size() > 32) return DX_OK;
+    auto up = [&](const void* src, size_t bytes, DevBuf* dst) -> int {
+        *dst = DevBuf(ctx, bytes + 64);
+        if (!dst->p) return ctx->set_error(DX_ERR_CUDA, "rule table allocation failed");
+        if (bytes) DX_CUDA(ctx, cudaMemcpyAsync(dst->p, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+        return DX_OK;
+    };
+    DevBuf b_spaces, b_classes, b_cmask, b_consts, b_luts, b_tt, b_tf;
+    int rc;
+    if ((rc = up(sdev.data(), sdev.size() * sizeof(RSpaceDev), &b_spaces))) return rc;
+    if ((rc = up(classes.data(), classes.size() * sizeof(RClassDev), &b_classes))) return rc;
+    if ((rc = up(cmask.data(), cmask.size() * 4, &b_cmask))) return rc;
+    if ((rc = up(all_consts.data(), all_consts.size() * 8, &b_consts))) return rc;
+    if ((rc = up(all_luts.data(), all_luts.size() * 4, &b_luts))) return rc;
+    if ((rc = up(tt.data(), tt.size() * 4, &b_tt))) return rc;
+    if ((rc = up(tf.data(), tf.size() * 4, &b_tf))) return rc;
+    RulesDev D; memset(&D, 0, sizeof D);
+    D.spaces = b_spaces.as<RSpaceDev>(); D.n_spaces = (int)sdev.size();
+    D.classes = b_classes.as<RClassDev>(); D.n_classes = (int)classes.size();
+    D.consts = b_consts.as<long long>(); D.n_consts = (int)all_consts.size();
+    D.luts = b_luts.as<int32_t>(); D.n_luts = (int)all_luts.size();
+    D.class_masks = b_cmask.as<uint32_t>();
+    D.table_t = b_tt.as<uint32_t>(); D.table_f = b_tf.as<uint32_t>();
+    D.total_rows = total_rows; D.J = J; D.Wp = Wp; D.words = words;
+    if (!P.G.prog_start.empty()) {
+        D.code = GD.code.as<uint32_t>(); D.gconsts = GD.consts.as<long long>(); D.gcols = GD.cols.as<ProgCol>(); D.gluts = GD.luts.as<ProgLut>(); D.n_gcols = GD.n_cols;
+    }
+    size_t fixed = sdev.size() * sizeof(RSpaceDev) + classes.size() * sizeof(RClassDev) + ((cmask.size() + 1) & ~size_t(1)) * 4 +
+                   all_consts.size() * 8 + ((all_luts.size() + 3) & ~size_t(3)) * 4 + 64;
+    size_t tab_bytes = tt.size() * 4 * (needf ? 2 : 1);
+    D.table_in_smem = (fixed + tab_bytes <= RB_SMEM_TABLE_BYTES) ? 1 : 0;
+    size_t smem = fixed + (D.table_in_smem ? tab_bytes : 0);
+    if (fixed > 64 * 1024) return DX_OK;       // pathological constant count: generic kernel
+    {
+        StageTimer tm(ctx, "k2_rules_bucket");
+#define RB_LAUNCH(JJ) do { if (needf) launch_rules<JJ, true>(ctx, D, smem, n_rows, sel, flags); else launch_rules<JJ, false>(ctx, D, smem, n_rows, sel, flags); } while (0)
+        if (J == 1) RB_LAUNCH(1); else if (J == 2) RB_LAUNCH(2); else if (J == 3) RB_LAUNCH(3); else RB_LAUNCH(4);
+        ctx->launches["k2_rules_bucket"]++;
+    }
+    DX_CUDA(ctx, cudaGetLastError());
+    DX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));     // the uploaded tables die with this scope
+    *used_fast = true;
+    return DX_OK;
+}

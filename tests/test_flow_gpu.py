@@ -194,3 +194,34 @@ def test_unsupported_sql_fails_at_create(dx, ctx):
     with pytest.raises(dx.DxError):
         g.process_json(b'{"deviceDetails":{"deviceId":1}}\n', T0, I)
     g.close()
+
+
+def test_bucketed_and_generic_rule_kernels_agree(dx, ctx):
+    """The bucketed bit-sliced K2 and the bytecode interpreter are two implementations of the same rules."""
+    rules = dx.flowgen.make_rules(200, seed=5, n_keys=1000, n_homes=100)
+    extra = ["deviceDetails.temperature > deviceDetails.humidity", "NOT (deviceDetails.status = 1 OR deviceDetails.temperature < 50)",
+             "deviceDetails.deviceId IN (1, 2, 3) AND deviceDetails.homeId NOT IN (5, 6)", "deviceDetails.temperature NOT BETWEEN 20 AND 80",
+             "deviceDetails.deviceType LIKE '%Lock' AND NOT (deviceDetails.deviceType = 'DoorLock')", "deviceDetails.status IS NULL OR deviceDetails.homeId > 50",
+             "deviceDetails.homeId > 10.5 AND deviceDetails.homeId < 90",
+             "(deviceDetails.status = 1 AND deviceDetails.homeId = 3) OR (deviceDetails.temperature > 99 AND deviceDetails.humidity < 1) OR deviceDetails.deviceId = 7 OR deviceDetails.deviceId = 8 OR deviceDetails.deviceId = 9"]
+    for i, c in enumerate(extra):
+        rules.append({"ruleId": "X%d" % i, "ruleDescription": "x", "severity": "Low", "tagName": "Tag", "tag": "x", "condition": c})
+    tr = dx.flowgen.process_rules_sql(rules)
+    conf = dx.flowgen.conf_text("k2")
+    fast = dx.CommonProcessorFactory.createProcessor(ctx, conf, SCHEMA2, ["Raw.*\n"], tr)
+    slow = dx.CommonProcessorFactory.createProcessor(ctx, conf + "datax.job.process.gpu.genericrules=true\n", SCHEMA2, ["Raw.*\n"], tr)
+    o = dxo_flow.Flow(conf, SCHEMA2, ["Raw.*\n"], tr)
+    for data in (gen(dx, 30_000), to_ndjson(all_records(3000, seed=21))):
+        ctx.set_timing(True)
+        a = fast.process_json(data, T0, I).table("Rules")
+        assert ctx.take_stage_ms("k2_rules_bucket")[1] == 1 and ctx.take_stage_ms("k2_eval_flags")[1] == 0
+        b = slow.process_json(data, T0, I).table("Rules")
+        assert ctx.take_stage_ms("k2_eval_flags")[1] == 1
+        ctx.set_timing(False)
+        fa, _ = a.column("Rules")
+        fb, _ = b.column("Rules")
+        assert (fa == fb).all()
+        ro, _ = o.process(data, T0, I)
+        assert_same_rows(a, ro["Rules"], dx, ordered=True)
+    fast.close()
+    slow.close()
