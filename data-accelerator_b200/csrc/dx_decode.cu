@@ -51,102 +51,7 @@ __device__ __forceinline__ uint32_t ld32u(const uint8_t* buf, uint32_t pos) {
     const uint32_t* w = reinterpret_cast<const uint32_t*>(buf + (pos & ~3u));
     return __funnelshift_r(w[0], w[1], (pos & 3u) << 3);
 }
-struct SRd {
-    const uint8_t* buf; uint32_t pos; uint32_t word;
-    __device__ __forceinline__ void seek(uint32_t p) { pos = p; word = *reinterpret_cast<const uint32_t*>(buf + (p & ~3u)); }
-    __device__ __forceinline__ uint32_t peek() const { return (word >> ((pos & 3u) << 3)) & 0xffu; }
-    __device__ __forceinline__ void adv() { pos++; if ((pos & 3u) == 0) word = *reinterpret_cast<const uint32_t*>(buf + pos); }
-};
-
-// Template fast path.  Accepts exactly: the schema-ordered compact serialisation with plain
-// integer / short decimal / escape-free string values.  Anything else -> false (general path).
-__device__ bool fast_record(const uint8_t* buf, uint32_t pos, uint32_t end, const DSeg* segs, int n_segs,
-                            const uint32_t* lits, RowSink& o) {
-    o.valid = 0;
-    for (int si = 0; si < n_segs; si++) {
-        const DSeg sg = segs[si];
-        const uint32_t* lw = lits + (sg.lit_off >> 2);
-        const uint32_t L = sg.lit_len;
-        uint32_t k = 0, diff = 0;
-        for (; k + 4 <= L; k += 4) diff |= ld32u(buf, pos + k) ^ lw[k >> 2];
-        if (L & 3u) diff |= (ld32u(buf, pos + k) ^ lw[k >> 2]) & ((1u << ((L & 3u) << 3)) - 1u);
-        if (diff) return false;
-        pos += L;
-        if (sg.type == 0) break;
-        SRd r; r.buf = buf; r.seek(pos);
-        uint32_t c = r.peek();
-        switch (sg.type) {
-        case DX_T_I64: {
-            bool neg = false;
-            if (c == '-') { neg = true; r.adv(); c = r.peek(); }
-            uint32_t d = c - '0';
-            if (d > 9) return false;
-            unsigned long long v = d; int nd = 1;
-            r.adv(); c = r.peek();
-            if (d == 0 && (c - '0') <= 9u) return false;
-            while ((d = c - '0') <= 9u) {
-                v = v * 10 + d; r.adv(); c = r.peek();
-                if (++nd > 18) return false;
-            }
-            sink_i64(o, sg.leaf, neg ? -(long long)v : (long long)v);
-            break;
-        }
-        case DX_T_F64: {
-            bool neg = false;
-            if (c == '-') { neg = true; r.adv(); c = r.peek(); }
-            uint32_t d = c - '0';
-            if (d > 9) return false;
-            unsigned long long m = d; int nd = 1, nf = 0;
-            r.adv(); c = r.peek();
-            if (d == 0 && (c - '0') <= 9u) return false;
-            while ((d = c - '0') <= 9u) { m = m * 10 + d; nd++; r.adv(); c = r.peek(); if (nd > 15) return false; }
-            bool is_int = true;
-            if (c == '.') {
-                is_int = false;
-                r.adv(); c = r.peek();
-                if ((c - '0') > 9u) return false;
-                while ((d = c - '0') <= 9u) { m = m * 10 + d; nd++; nf++; r.adv(); c = r.peek(); if (nd > 15) return false; }
-            }
-            if (c == 'e' || c == 'E') return false;
-            double x;
-            if (is_int) x = (double)(neg ? -(long long)m : (long long)m);
-            else { x = (double)m / dx_pow10_exact[nf]; if (neg) x = -x; }
-            sink_f64(o, sg.leaf, x);
-            break;
-        }
-        case DX_T_BOOL: {
-            uint32_t w = ld32u(buf, pos);
-            if (w == 0x65757274u) { sink_i64(o, sg.leaf, 1); r.seek(pos + 4); }               // "true"
-            else if (w == 0x736c6166u && buf[pos + 4] == 'e') { sink_i64(o, sg.leaf, 0); r.seek(pos + 5); } // "false"
-            else return false;
-            break;
-        }
-        case DX_T_STR: {
-            if (c != '"') return false;
-            r.adv();
-            const uint32_t s0 = r.pos;
-            uint64_t w0 = 0, w1 = 0; uint32_t len = 0;
-            for (;;) {
-                c = r.peek();
-                if (c == '"') break;
-                if (c < 0x20u || c == '\\') return false;
-                if (len < 8) w0 |= (uint64_t)c << (len << 3);
-                else if (len < 16) w1 |= (uint64_t)c << ((len - 8) << 3);
-                len++; r.adv();
-                if (r.pos >= end) return false;
-            }
-            if (len > 16) dict_pack(buf + s0, len, w0, w1);
-            int32_t code = dict_get_or_insert(o.a->dicts[sg.leaf], w0, w1, len, buf + s0, &o.a->stats->flags);
-            sink_code(o, sg.leaf, code);
-            r.adv();
-            break;
-        }
-        default: return false;
-        }
-        pos = r.pos;
-    }
-    return pos == end;
-}
+#include "dx_decode_fast.cuh"
 
 __device__ __forceinline__ unsigned long long ld_state(const unsigned long long* p) {
     return *reinterpret_cast<const volatile unsigned long long*>(p);
@@ -307,44 +212,48 @@ __global__ void __launch_bounds__(K1_NT) k1_decode(const __grid_constant__ Decod
                 __syncthreads();
                 const long long row_base = s_rowbase;
                 long long cnt = n_rec - round0; if (cnt > K1_SC) cnt = K1_SC;
-                for (long long idx = tid; idx < cnt; idx += K1_NT) {
-                    const uint32_t st = s_starts[idx];
+                for (long long base = 0; base < cnt; base += K1_NT) {
+                    const long long idx = base + tid;
+                    const bool has = idx < cnt;
+                    uint32_t st = 0, en = 0; bool in_smem = true; long long en_abs = 0;
                     const long long rank = round0 + idx;
-                    uint32_t en; bool in_smem = true; long long en_abs = 0;
-                    if (rank + 1 < n_rec) en = (uint32_t)s_starts[idx + 1] - 1u;
-                    else {
-                        // last record owned by this tile: its newline lies at or past the tile end
-                        uint32_t p = st;
-                        const uint32_t lim = (uint32_t)avail + ((lo + avail == a.n_end) ? 1u : 0u);
-                        while (p < lim && buf[p] != '\n') p++;
-                        if (p < lim) en = p;
+                    if (has) {
+                        st = s_starts[idx];
+                        if (rank + 1 < n_rec) en = (uint32_t)s_starts[idx + 1] - 1u;
                         else {
-                            in_smem = false; en = 0;
-                            long long g = lo + p;
-                            while (g < a.n_end && a.base_al[g] != '\n') g++;
-                            en_abs = g;
+                            // last record owned by this tile: its newline lies at or past the tile end
+                            uint32_t p = st;
+                            const uint32_t lim = (uint32_t)avail + ((lo + avail == a.n_end) ? 1u : 0u);
+                            while (p < lim && buf[p] != '\n') p++;
+                            if (p < lim) en = p;
+                            else {
+                                in_smem = false;
+                                long long g = lo + p;
+                                while (g < a.n_end && a.base_al[g] != '\n') g++;
+                                en_abs = g;
+                            }
                         }
                     }
                     RowSink o; o.a = &a; o.row = row_base + rank; o.valid = 0; o.err = 0;
-                    if (o.row >= a.max_rows) { c_err |= DXF_ROW_OVERFLOW; continue; }
-                    bool ok;
-                    if (in_smem) {
-                        ok = fast_record(buf, st, en, s_segs, n_segs, s_lits, o);
+                    const bool overflow = has && o.row >= a.max_rows;
+                    if (overflow) c_err |= DXF_ROW_OVERFLOW;
+                    const bool live = has && !overflow;
+                    bool ok = fast_record_warp(buf, st, en, live && in_smem, s_segs, n_segs, s_lits, o);
+                    if (live) {
                         if (ok) c_fast++;
-                        else ok = g_record(buf + st, buf + en, S, o);
-                    } else {
-                        ok = g_record(a.base_al + lo + st, a.base_al + en_abs, S, o);
-                    }
-                    c_rows++; if (!ok) c_null++;
-                    c_err |= o.err;
-                    if (o.valid != all_valid) {
-                        for (uint32_t k = 0; k < n_leaves; k++) if (!((o.valid >> k) & 1u)) {
-                            if (S->leaf_type[k] == DX_T_STR) reinterpret_cast<int32_t*>(a.cols[k])[o.row] = -1;
-                            else reinterpret_cast<long long*>(a.cols[k])[o.row] = 0;
+                        else if (in_smem) ok = g_record(buf + st, buf + en, S, o);
+                        else ok = g_record(a.base_al + lo + st, a.base_al + en_abs, S, o);
+                        c_rows++; if (!ok) c_null++;
+                        c_err |= o.err;
+                        if (o.valid != all_valid) {
+                            for (uint32_t k = 0; k < n_leaves; k++) if (!((o.valid >> k) & 1u)) {
+                                if (S->leaf_type[k] == DX_T_STR) reinterpret_cast<int32_t*>(a.cols[k])[o.row] = -1;
+                                else reinterpret_cast<long long*>(a.cols[k])[o.row] = 0;
+                            }
                         }
+                        if (a.mask_width == 1) reinterpret_cast<uint8_t*>(a.mask)[o.row] = (uint8_t)(o.valid | (ok ? 0x80u : 0u));
+                        else reinterpret_cast<uint32_t*>(a.mask)[o.row] = o.valid | (ok ? 0x80000000u : 0u);
                     }
-                    if (a.mask_width == 1) reinterpret_cast<uint8_t*>(a.mask)[o.row] = (uint8_t)(o.valid | (ok ? 0x80u : 0u));
-                    else reinterpret_cast<uint32_t*>(a.mask)[o.row] = o.valid | (ok ? 0x80000000u : 0u);
                 }
                 if (n_rec == 0) break;
             }
@@ -362,32 +271,38 @@ __global__ void __launch_bounds__(K1_NT) k1_decode(const __grid_constant__ Decod
             }
             __syncthreads();
             rec0 = s_r0; n_rec = s_rowbase - rec0;
-            for (long long idx = tid; idx < n_rec; idx += K1_NT) {
-                const long long r = rec0 + idx;
-                const long long st_abs = (long long)a.skew + a.offsets[r];
-                const long long en_abs = (long long)a.skew + a.offsets[r + 1];
-                RowSink o; o.a = &a; o.row = r; o.valid = 0; o.err = 0;
-                bool ok;
-                if (en_abs - lo <= avail) {
-                    uint32_t st = (uint32_t)(st_abs - lo), en = (uint32_t)(en_abs - lo);
-                    // a trailing newline inside the frame is whitespace; the fast path wants the bare record
-                    uint32_t en_f = en; if (en_f > st && buf[en_f - 1] == '\n') en_f--;
-                    ok = fast_record(buf, st, en_f, s_segs, n_segs, s_lits, o);
-                    if (ok) c_fast++;
-                    else ok = g_record(buf + st, buf + en, S, o);
-                } else {
-                    ok = g_record(a.base_al + st_abs, a.base_al + en_abs, S, o);
-                }
-                c_rows++; if (!ok) c_null++;
-                c_err |= o.err;
-                if (o.valid != all_valid) {
-                    for (uint32_t k = 0; k < n_leaves; k++) if (!((o.valid >> k) & 1u)) {
-                        if (S->leaf_type[k] == DX_T_STR) reinterpret_cast<int32_t*>(a.cols[k])[o.row] = -1;
-                        else reinterpret_cast<long long*>(a.cols[k])[o.row] = 0;
+            for (long long base = 0; base < n_rec; base += K1_NT) {
+                const long long idx = base + tid;
+                const bool has = idx < n_rec;
+                const long long r = rec0 + (has ? idx : 0);
+                long long st_abs = 0, en_abs = 0; uint32_t st = 0, en = 0, en_f = 0; bool in_smem = false;
+                if (has) {
+                    st_abs = (long long)a.skew + a.offsets[r];
+                    en_abs = (long long)a.skew + a.offsets[r + 1];
+                    in_smem = en_abs - lo <= avail;
+                    if (in_smem) {
+                        st = (uint32_t)(st_abs - lo); en = (uint32_t)(en_abs - lo);
+                        // a trailing newline inside the frame is whitespace; the fast path wants the bare record
+                        en_f = en; if (en_f > st && buf[en_f - 1] == '\n') en_f--;
                     }
                 }
-                if (a.mask_width == 1) reinterpret_cast<uint8_t*>(a.mask)[o.row] = (uint8_t)(o.valid | (ok ? 0x80u : 0u));
-                else reinterpret_cast<uint32_t*>(a.mask)[o.row] = o.valid | (ok ? 0x80000000u : 0u);
+                RowSink o; o.a = &a; o.row = r; o.valid = 0; o.err = 0;
+                bool ok = fast_record_warp(buf, st, en_f, has && in_smem, s_segs, n_segs, s_lits, o);
+                if (has) {
+                    if (ok) c_fast++;
+                    else if (in_smem) ok = g_record(buf + st, buf + en, S, o);
+                    else ok = g_record(a.base_al + st_abs, a.base_al + en_abs, S, o);
+                    c_rows++; if (!ok) c_null++;
+                    c_err |= o.err;
+                    if (o.valid != all_valid) {
+                        for (uint32_t k = 0; k < n_leaves; k++) if (!((o.valid >> k) & 1u)) {
+                            if (S->leaf_type[k] == DX_T_STR) reinterpret_cast<int32_t*>(a.cols[k])[o.row] = -1;
+                            else reinterpret_cast<long long*>(a.cols[k])[o.row] = 0;
+                        }
+                    }
+                    if (a.mask_width == 1) reinterpret_cast<uint8_t*>(a.mask)[o.row] = (uint8_t)(o.valid | (ok ? 0x80u : 0u));
+                    else reinterpret_cast<uint32_t*>(a.mask)[o.row] = o.valid | (ok ? 0x80000000u : 0u);
+                }
             }
         }
         __syncthreads();

@@ -1,0 +1,151 @@
+// dx_decode_fast.cuh — the template fast path of K1 (see dx_decode.cu): one lane parses one
+// record out of the shared-memory tile, the 32 lanes of a warp walk the template segments in
+// lock step (reconverging at every segment), literals are compared a word at a time through a
+// carried funnel shift, digit runs and string bodies are classified eight bytes at a time (SWAR).
+// The path accepts only the schema-ordered compact serialisation with plain integers, short
+// decimals and escape-free strings; anything else reports false and the record is re-parsed from
+// its first byte by the general Spark-conformant parser, so results never depend on which path ran.
+#pragma once
+#include "dx_decode.cuh"
+
+static __device__ __forceinline__ uint64_t ld64u(const uint8_t* buf, uint32_t pos) {
+    const uint32_t* w = reinterpret_cast<const uint32_t*>(buf + (pos & ~3u));
+    const uint32_t sh = (pos & 3u) << 3;
+    const uint32_t a = w[0], b = w[1], c = w[2];
+    return ((uint64_t)__funnelshift_r(b, c, sh) << 32) | __funnelshift_r(a, b, sh);
+}
+
+// number of leading ASCII digits among the 8 bytes of w (byte 0 first)
+static __device__ __forceinline__ int leading_digits8(uint64_t w) {
+    const uint64_t hi = (w + 0x4646464646464646ull) | (w - 0x3030303030303030ull);   // >'9' or <'0' set the top bit
+    const uint64_t nd = hi & 0x8080808080808080ull;       // exact up to and including the first non-digit
+    return nd ? ((__ffsll((long long)nd) - 1) >> 3) : 8;
+}
+
+// value of the first m (1..4) digits of the 32-bit window x
+static __device__ __forceinline__ uint32_t digits4(uint32_t x, int m) {
+    uint32_t t = (x - 0x30303030u) & (0xFFFFFFFFu >> ((4 - m) << 3));
+    t <<= (4 - m) << 3;                                    // right-align: missing leading digits are zero
+    const uint32_t p = (t * 10u + (t >> 8)) & 0x00FF00FFu; // [d0 d1] in byte 0, [d2 d3] in byte 2
+    return (p & 0xFFu) * 100u + (p >> 16);
+}
+
+static __device__ const uint32_t dx_pow10_u32[9] = {1u, 10u, 100u, 1000u, 10000u, 100000u, 1000000u, 10000000u, 100000000u};
+
+// Parses a run of digits at pos.  Returns the digit count (0 = none, -1 = more than 18) and the value.
+static __device__ __forceinline__ int parse_digit_run(const uint8_t* buf, uint32_t pos, unsigned long long* value, uint32_t* first_digit) {
+    unsigned long long v = 0; int nd = 0;
+    for (;;) {
+        const uint64_t w = ld64u(buf, pos + nd);
+        const int n = leading_digits8(w);
+        if (nd == 0) *first_digit = (uint32_t)(w & 0xffu) - '0';
+        if (n) {
+            const uint32_t lo = (uint32_t)w, hi = (uint32_t)(w >> 32);
+            uint32_t chunk = digits4(lo, n < 4 ? n : 4);
+            if (n > 4) chunk = chunk * dx_pow10_u32[n - 4] + digits4(hi, n - 4);
+            v = v * dx_pow10_u32[n] + chunk;
+            nd += n;
+        }
+        if (n < 8) break;
+        if (nd > 18) return -1;
+    }
+    *value = v;
+    return nd > 18 ? -1 : nd;
+}
+
+// One record, executed by ALL lanes of the warp together (lanes without a record pass has=false).
+static __device__ bool fast_record_warp(const uint8_t* buf, uint32_t pos, uint32_t end, bool has, const DSeg* segs, int n_segs,
+                                        const uint32_t* lits, RowSink& o) {
+    bool ok = has;
+    o.valid = 0;
+    for (int si = 0; si < n_segs; si++) {
+        __syncwarp();
+        const DSeg sg = segs[si];
+        if (ok) {
+            const uint32_t* lw = lits + (sg.lit_off >> 2);
+            const uint32_t L = sg.lit_len, nw = L >> 2, sh = (pos & 3u) << 3;
+            const uint32_t* wp = reinterpret_cast<const uint32_t*>(buf + (pos & ~3u));
+            uint32_t lo = wp[0], diff = 0;
+            for (uint32_t k = 0; k < nw; k++) { const uint32_t hi = wp[k + 1]; diff |= __funnelshift_r(lo, hi, sh) ^ lw[k]; lo = hi; }
+            if (L & 3u) { const uint32_t hi = wp[nw + 1]; diff |= (__funnelshift_r(lo, hi, sh) ^ lw[nw]) & ((1u << ((L & 3u) << 3)) - 1u); }
+            ok = diff == 0;
+            pos += L;
+        }
+        if (sg.type == 0) break;
+        if (ok) {
+            switch (sg.type) {
+            case DX_T_I64: {
+                bool neg = buf[pos] == '-';
+                if (neg) pos++;
+                unsigned long long v; uint32_t d0;
+                const int nd = parse_digit_run(buf, pos, &v, &d0);
+                if (nd <= 0 || (d0 == 0 && nd > 1)) { ok = false; break; }
+                sink_i64(o, sg.leaf, neg ? -(long long)v : (long long)v);
+                pos += nd;
+                break;
+            }
+            case DX_T_F64: {
+                bool neg = buf[pos] == '-';
+                if (neg) pos++;
+                unsigned long long ip, fp = 0; uint32_t d0, f0;
+                const int ni = parse_digit_run(buf, pos, &ip, &d0);
+                if (ni <= 0 || (d0 == 0 && ni > 1)) { ok = false; break; }
+                pos += ni;
+                int nf = 0;
+                if (buf[pos] == '.') {
+                    nf = parse_digit_run(buf, pos + 1, &fp, &f0);
+                    if (nf <= 0) { ok = false; break; }
+                    pos += 1 + nf;
+                }
+                const uint32_t c = buf[pos];
+                if (ni + nf > 15 || c == 'e' || c == 'E') { ok = false; break; }
+                double x;
+                if (nf == 0) x = (double)(neg ? -(long long)ip : (long long)ip);
+                else {
+                    unsigned long long m = ip;
+                    if (nf > 8) { m = m * dx_pow10_u32[8]; m = m * dx_pow10_u32[nf - 8]; } else m = m * dx_pow10_u32[nf];
+                    x = (double)(m + fp) / dx_pow10_exact[nf];
+                    if (neg) x = -x;
+                }
+                sink_f64(o, sg.leaf, x);
+                break;
+            }
+            case DX_T_BOOL: {
+                const uint32_t w = ld32u(buf, pos);
+                if (w == 0x65757274u) { sink_i64(o, sg.leaf, 1); pos += 4; }
+                else if (w == 0x736c6166u && buf[pos + 4] == 'e') { sink_i64(o, sg.leaf, 0); pos += 5; }
+                else ok = false;
+                break;
+            }
+            case DX_T_STR: {
+                if (buf[pos] != '"') { ok = false; break; }
+                const uint32_t s0 = pos + 1;
+                uint64_t w0 = 0, w1 = 0; uint32_t len = 0; bool bad = false;
+                for (;;) {
+                    const uint64_t w = ld64u(buf, s0 + len);
+                    // first byte that is '"', '\\' or a control character
+                    const uint64_t q = w ^ 0x2222222222222222ull, b = w ^ 0x5C5C5C5C5C5C5C5Cull;
+                    const uint64_t zq = (q - 0x0101010101010101ull) & ~q, zb = (b - 0x0101010101010101ull) & ~b, zc = (w - 0x2020202020202020ull) & ~w;
+                    const uint64_t stop = (zq | zb | zc) & 0x8080808080808080ull;
+                    const int n = stop ? ((__ffsll((long long)stop) - 1) >> 3) : 8;
+                    if (len == 0) w0 = w; else if (len == 8) w1 = w;
+                    len += n;
+                    if (n < 8) { bad = ((w >> (n << 3)) & 0xffu) != '"'; break; }
+                    if (s0 + len >= end) { bad = true; break; }
+                }
+                if (bad) { ok = false; break; }
+                if (len <= 16) {   // keep exactly the string's bytes in the packed identity
+                    if (len < 8) { w0 &= (len ? (~0ull >> ((8 - len) << 3)) : 0ull); w1 = 0; }
+                    else if (len < 16) w1 &= (len > 8 ? (~0ull >> ((16 - len) << 3)) : 0ull);
+                } else dict_pack(buf + s0, len, w0, w1);
+                const int32_t code = dict_get_or_insert(o.a->dicts[sg.leaf], w0, w1, len, buf + s0, &o.a->stats->flags);
+                sink_code(o, sg.leaf, code);
+                pos = s0 + len + 1;
+                break;
+            }
+            default: ok = false;
+            }
+        }
+    }
+    return ok && pos == end;
+}
