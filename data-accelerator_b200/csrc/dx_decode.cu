@@ -24,6 +24,12 @@
 #define K1_PAD 32
 #define K1_NT 256           // threads per CTA
 #define K1_SC 1024          // record starts held in shared memory per round
+#ifndef K1_STAGES
+#define K1_STAGES 1         // shared-memory tile stages; 2 = prefetch the next tile while parsing (measured slower: 3 CTAs/SM already overlap copy and parse)
+#endif
+#ifndef K1_MIN_CTAS
+#define K1_MIN_CTAS 3       // resident CTAs per SM the register allocation is held to
+#endif
 
 // ------------------------------- PTX wrappers ------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -87,56 +93,77 @@ __device__ long long tile_lookback(unsigned long long* state, long long tile, un
     return excl;
 }
 
-__global__ void __launch_bounds__(K1_NT) k1_decode(const __grid_constant__ DecodeArgs a) {
+__global__ void __launch_bounds__(K1_NT, K1_MIN_CTAS) k1_decode(const __grid_constant__ DecodeArgs a) {
     extern __shared__ __align__(128) uint8_t smem[];
-    uint8_t* buf = smem;                                                  // K1_T + K1_OVL + K1_PAD
-    uint16_t* s_starts = reinterpret_cast<uint16_t*>(smem + K1_T + K1_OVL + K1_PAD);   // K1_SC + 2
+    constexpr int TILE_BYTES = K1_T + K1_OVL + K1_PAD;                     // one staged tile (multiple of 16)
+    uint16_t* s_starts = reinterpret_cast<uint16_t*>(smem + K1_STAGES * TILE_BYTES);   // K1_SC + 2
     uint32_t* s_lits = reinterpret_cast<uint32_t*>(s_starts + K1_SC + 2);  // DX_LITS_BYTES
     DSeg* s_segs = reinterpret_cast<DSeg*>(s_lits + DX_LITS_BYTES / 4);    // DX_MAX_SEGS
-    __shared__ uint64_t s_bar;
+    __shared__ uint64_t s_bar[K1_STAGES];
     __shared__ long long s_tile;
     __shared__ long long s_rowbase;
     __shared__ uint32_t s_wtot[K1_NT / 32];
     __shared__ long long s_r0;
+    __shared__ uint32_t s_tail_nl;   // first newline at or past the tile end (shared-memory position), ~0u if none loaded
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const DSchemaDev* S = a.schema;
     const int n_segs = S->n_segs;
     for (int i = tid; i < DX_LITS_BYTES / 4; i += K1_NT) s_lits[i] = S->lits[i];
     for (int i = tid; i < DX_MAX_SEGS; i += K1_NT) s_segs[i] = S->segs[i];
-    if (tid == 0) { mbar_init(&s_bar, 1); fence_mbar_init(); }
+    if (tid == 0) { for (int k = 0; k < K1_STAGES; k++) mbar_init(&s_bar[k], 1); fence_mbar_init(); }
     __syncthreads();
 
     const uint32_t n_leaves = (uint32_t)S->n_leaves;
     const uint32_t all_valid = (n_leaves >= 32) ? 0xFFFFFFFFu : ((1u << n_leaves) - 1u);
     unsigned long long c_rows = 0, c_null = 0, c_fast = 0; uint32_t c_err = 0;
-    uint32_t phase = 0;
+    uint32_t phase_bits = 0;     // bit k: parity the next completion of stage k will have
 
-    for (;;) {
-        if (tid == 0) s_tile = (long long)atomicAdd(a.tile_counter, 1u);
-        __syncthreads();
-        const long long tile = s_tile;
-        if (tile >= a.n_tiles) break;
-        const long long lo = tile * (long long)K1_T;                 // absolute (relative to base_al)
-        long long avail = a.n_end - lo;                              // bytes of data from lo on
-        if (avail > K1_T + K1_OVL) avail = K1_T + K1_OVL;
-        const uint32_t bulk = (uint32_t)avail & ~15u;
+    // Stages one tile: bulk (TMA) copy of the 16-byte-aligned part onto the stage's mbarrier, the ragged
+    // tail (< 16 bytes) and the end-of-data sentinel by ordinary stores.  All threads call it.
+    auto stage_tile = [&](int slot, long long tile) {
+        uint8_t* dst = smem + slot * TILE_BYTES;
+        const long long lo_ = tile * (long long)K1_T;
+        long long av = a.n_end - lo_; if (av > K1_T + K1_OVL) av = K1_T + K1_OVL;
+        const uint32_t bulk_ = (uint32_t)av & ~15u;
         if (tid == 0) {
             fence_proxy_async();
-            if (bulk) {
-                mbar_expect_tx(&s_bar, bulk);
+            if (bulk_) {
+                mbar_expect_tx(&s_bar[slot], bulk_);
                 uint32_t off = 0;
-                while (off < bulk) {
-                    uint32_t n = bulk - off; if (n > 16384u) n = 16384u;
-                    bulk_g2s(buf + off, a.base_al + lo + off, n, &s_bar);
+                while (off < bulk_) {
+                    uint32_t n = bulk_ - off; if (n > 16384u) n = 16384u;
+                    bulk_g2s(dst + off, a.base_al + lo_ + off, n, &s_bar[slot]);
                     off += n;
                 }
             }
         }
-        // ragged tail (< 16 bytes) and sentinel by ordinary stores
-        if (tid < (int)((uint32_t)avail - bulk)) buf[bulk + tid] = a.base_al[lo + bulk + tid];
-        if (tid == 32 && lo + avail == a.n_end) buf[avail] = '\n';
-        if (bulk) { while (!mbar_try_wait(&s_bar, phase)) {} phase ^= 1; }
+        if (tid < (int)((uint32_t)av - bulk_)) dst[bulk_ + tid] = a.base_al[lo_ + bulk_ + tid];
+        if (tid == 32 && lo_ + av == a.n_end) dst[av] = '\n';
+    };
+
+    if (tid == 0) s_tile = (long long)atomicAdd(a.tile_counter, 1u);
+    __syncthreads();
+    long long tile = s_tile;
+    int slot = 0;
+    if (tile < a.n_tiles) stage_tile(0, tile);
+    for (;;) {
+        if (tile >= a.n_tiles) break;
+        long long next_tile = a.n_tiles;
+        if (K1_STAGES > 1) {
+            // claim the following tile now and start its copy into the other stage, so it lands while this one is parsed
+            __syncthreads();
+            if (tid == 0) s_tile = (long long)atomicAdd(a.tile_counter, 1u);
+            __syncthreads();
+            next_tile = s_tile;
+            if (next_tile < a.n_tiles) stage_tile(slot ^ 1, next_tile);
+        }
+        uint8_t* buf = smem + slot * TILE_BYTES;
+        const long long lo = tile * (long long)K1_T;                 // absolute (relative to base_al)
+        long long avail = a.n_end - lo;                              // bytes of data from lo on
+        if (avail > K1_T + K1_OVL) avail = K1_T + K1_OVL;
+        const uint32_t bulk = (uint32_t)avail & ~15u;
+        if (bulk) { while (!mbar_try_wait(&s_bar[slot], (phase_bits >> slot) & 1u)) {} phase_bits ^= 1u << slot; }
         __syncthreads();
 
         long long n_rec = 0; long long rec0 = 0;   // offsets mode: records [rec0, rec0+n_rec)
@@ -179,6 +206,35 @@ __global__ void __launch_bounds__(K1_NT) k1_decode(const __grid_constant__ Decod
                 cnt_total += __shfl_sync(0xffffffffu, inc, 31);
             }
             if (lane == 0) s_wtot[warp] = cnt_total;
+            if (warp == K1_NT / 32 - 1) {
+                // the tile's last record ends at the first newline at or past the tile end: find it with the
+                // whole warp (16 bytes per lane per round) instead of one lane walking bytes
+                const uint32_t lim = (uint32_t)avail + ((lo + avail == a.n_end) ? 1u : 0u);
+                uint32_t found = 0xFFFFFFFFu;
+                for (uint32_t c0 = K1_T / 16; c0 * 16 < lim && found == 0xFFFFFFFFu; c0 += 32) {
+                    const uint32_t chunk = c0 + lane;
+                    uint32_t m = 0;
+                    if (chunk * 16 < lim) {
+                        const uint4 v = *reinterpret_cast<const uint4*>(buf + chunk * 16);
+                        const uint32_t ws[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                        for (int k = 0; k < 4; k++) {
+                            const uint32_t x = ws[k] ^ 0x0A0A0A0Au;
+                            uint32_t t = (x & 0x7F7F7F7Fu) + 0x7F7F7F7Fu;
+                            t = ~(t | x | 0x7F7F7F7Fu);
+                            m |= ((t * 0x00204081u) >> 28) << (k * 4);
+                        }
+                        if (chunk * 16 + 16 > lim) m &= (1u << (lim - chunk * 16)) - 1u;
+                    }
+                    const unsigned who = __ballot_sync(0xffffffffu, m != 0);
+                    if (who) {
+                        const int src = __ffs(who) - 1;
+                        const uint32_t mm = __shfl_sync(0xffffffffu, m, src);
+                        found = (c0 + src) * 16 + (__ffs(mm) - 1);
+                    }
+                }
+                if (lane == 0) s_tail_nl = found;
+            }
             __syncthreads();
             uint32_t wbase = first_virtual ? 1u : 0u, total = first_virtual ? 1u : 0u;
 #pragma unroll
@@ -222,13 +278,16 @@ __global__ void __launch_bounds__(K1_NT) k1_decode(const __grid_constant__ Decod
                         if (rank + 1 < n_rec) en = (uint32_t)s_starts[idx + 1] - 1u;
                         else {
                             // last record owned by this tile: its newline lies at or past the tile end
-                            uint32_t p = st;
                             const uint32_t lim = (uint32_t)avail + ((lo + avail == a.n_end) ? 1u : 0u);
-                            while (p < lim && buf[p] != '\n') p++;
-                            if (p < lim) en = p;
-                            else {
+                            const uint32_t p = s_tail_nl;
+                            if (p != 0xFFFFFFFFu) en = p;
+                            else if (lo + avail == a.n_end) {
+                                // the data ends inside the tile proper: the record runs to the final newline or the end of data
+                                const uint32_t av = (uint32_t)avail;
+                                en = (av > st && buf[av - 1] == '\n') ? av - 1 : av;
+                            } else {
                                 in_smem = false;
-                                long long g = lo + p;
+                                long long g = lo + lim;
                                 while (g < a.n_end && a.base_al[g] != '\n') g++;
                                 en_abs = g;
                             }
@@ -306,6 +365,13 @@ __global__ void __launch_bounds__(K1_NT) k1_decode(const __grid_constant__ Decod
             }
         }
         __syncthreads();
+        if (K1_STAGES > 1) { tile = next_tile; slot ^= 1; }
+        else {
+            if (tid == 0) s_tile = (long long)atomicAdd(a.tile_counter, 1u);
+            __syncthreads();
+            tile = s_tile;
+            if (tile < a.n_tiles) stage_tile(0, tile);
+        }
     }
     // per-warp reduction of the counters, one atomic each
     for (int s = 16; s > 0; s >>= 1) {
@@ -335,7 +401,7 @@ __global__ void k1_count_records(const uint8_t* bytes, long long n, unsigned lon
 // host side
 // =======================================================================================
 static size_t k1_smem_bytes() {
-    return K1_T + K1_OVL + K1_PAD + (K1_SC + 2) * 2 + DX_LITS_BYTES + DX_MAX_SEGS * sizeof(DSeg) + 64;
+    return K1_STAGES * (K1_T + K1_OVL + K1_PAD) + (K1_SC + 2) * 2 + DX_LITS_BYTES + DX_MAX_SEGS * sizeof(DSeg) + 64;
 }
 
 static int map_spark_type(const std::string& t) {

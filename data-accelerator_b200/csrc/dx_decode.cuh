@@ -79,7 +79,7 @@ static __device__ __forceinline__ bool dict_slot_match(const DictDev& d, uint64_
 
 // bytes: generic pointer to the (unescaped) string; for len<=16 (w0,w1) are the packed bytes,
 // otherwise w0 is a 64-bit hash of the bytes and w1 = 0.
-static __device__ int32_t dict_get_or_insert(const DictDev& d, uint64_t w0, uint64_t w1, uint32_t len,
+static __device__ __noinline__ int32_t dict_get_or_insert(const DictDev& d, uint64_t w0, uint64_t w1, uint32_t len,
                                       const uint8_t* bytes, unsigned long long* err_flags) {
     uint64_t h = dx_mix64(w0 ^ dx_mix64(w1 + len));
     uint32_t i = (uint32_t)h & d.cap_mask;
@@ -473,7 +473,7 @@ static __device__ int g_object(GCur& c, const DSchemaDev* S, RowSink& o, int bas
 }
 
 // One record through the general path.  Returns true when the row is non-NULL.
-static __device__ bool g_record(const uint8_t* s, const uint8_t* e, const DSchemaDev* S, RowSink& o) {
+static __device__ __noinline__ bool g_record(const uint8_t* s, const uint8_t* e, const DSchemaDev* S, RowSink& o) {
     GCur c{s, e};
     o.valid = 0;
     g_ws(c);

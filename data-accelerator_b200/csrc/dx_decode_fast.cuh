@@ -66,7 +66,12 @@ static __device__ bool fast_record_warp(const uint8_t* buf, uint32_t pos, uint32
             const uint32_t L = sg.lit_len, nw = L >> 2, sh = (pos & 3u) << 3;
             const uint32_t* wp = reinterpret_cast<const uint32_t*>(buf + (pos & ~3u));
             uint32_t lo = wp[0], diff = 0;
-            for (uint32_t k = 0; k < nw; k++) { const uint32_t hi = wp[k + 1]; diff |= __funnelshift_r(lo, hi, sh) ^ lw[k]; lo = hi; }
+            // literals are short (key names): the first eight words are straight-line code under a uniform predicate
+#pragma unroll
+            for (uint32_t k = 0; k < 8; k++) {
+                if (k < nw) { const uint32_t hi = wp[k + 1]; diff |= __funnelshift_r(lo, hi, sh) ^ lw[k]; lo = hi; }
+            }
+            for (uint32_t k = 8; k < nw; k++) { const uint32_t hi = wp[k + 1]; diff |= __funnelshift_r(lo, hi, sh) ^ lw[k]; lo = hi; }
             if (L & 3u) { const uint32_t hi = wp[nw + 1]; diff |= (__funnelshift_r(lo, hi, sh) ^ lw[nw]) & ((1u << ((L & 3u) << 3)) - 1u); }
             ok = diff == 0;
             pos += L;
