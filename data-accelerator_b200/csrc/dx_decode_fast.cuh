@@ -15,11 +15,10 @@ static __device__ __forceinline__ uint64_t ld64u(const uint8_t* buf, uint32_t po
     return ((uint64_t)__funnelshift_r(b, c, sh) << 32) | __funnelshift_r(a, b, sh);
 }
 
-// number of leading ASCII digits among the 8 bytes of w (byte 0 first)
-static __device__ __forceinline__ int leading_digits8(uint64_t w) {
-    const uint64_t hi = (w + 0x4646464646464646ull) | (w - 0x3030303030303030ull);   // >'9' or <'0' set the top bit
-    const uint64_t nd = hi & 0x8080808080808080ull;       // exact up to and including the first non-digit
-    return nd ? ((__ffsll((long long)nd) - 1) >> 3) : 8;
+// number of leading ASCII digits among the 4 bytes of w (byte 0 first)
+static __device__ __forceinline__ int leading_digits4(uint32_t w) {
+    const uint32_t nd = ((w + 0x46464646u) | (w - 0x30303030u)) & 0x80808080u;   // exact up to and including the first non-digit
+    return nd ? ((__ffs((int)nd) - 1) >> 3) : 4;
 }
 
 // value of the first m (1..4) digits of the 32-bit window x
@@ -32,22 +31,33 @@ static __device__ __forceinline__ uint32_t digits4(uint32_t x, int m) {
 
 static __device__ const uint32_t dx_pow10_u32[9] = {1u, 10u, 100u, 1000u, 10000u, 100000u, 1000000u, 10000000u, 100000000u};
 
-// Parses a run of digits at pos.  Returns the digit count (0 = none, -1 = more than 18) and the value.
+// Parses a run of digits at pos, four bytes per step through a carried pair of aligned words.
+// Returns the digit count (0 = none, -1 = more than 18) and the value.
 static __device__ __forceinline__ int parse_digit_run(const uint8_t* buf, uint32_t pos, unsigned long long* value, uint32_t* first_digit) {
-    unsigned long long v = 0; int nd = 0;
-    for (;;) {
-        const uint64_t w = ld64u(buf, pos + nd);
-        const int n = leading_digits8(w);
-        if (nd == 0) *first_digit = (uint32_t)(w & 0xffu) - '0';
-        if (n) {
-            const uint32_t lo = (uint32_t)w, hi = (uint32_t)(w >> 32);
-            uint32_t chunk = digits4(lo, n < 4 ? n : 4);
-            if (n > 4) chunk = chunk * dx_pow10_u32[n - 4] + digits4(hi, n - 4);
-            v = v * dx_pow10_u32[n] + chunk;
-            nd += n;
+    const uint32_t* wp = reinterpret_cast<const uint32_t*>(buf + (pos & ~3u));
+    const uint32_t sh = (pos & 3u) << 3;
+    uint32_t a = wp[0], b = wp[1];
+    uint32_t w = __funnelshift_r(a, b, sh);
+    *first_digit = (w & 0xffu) - '0';
+    int n = leading_digits4(w);
+    if (n == 0) { *value = 0; return 0; }
+    uint32_t v32 = digits4(w, n); int nd = n;
+    // up to 8 digits stay in 32-bit arithmetic
+    if (n == 4) {
+        a = b; b = wp[2]; w = __funnelshift_r(a, b, sh);
+        n = leading_digits4(w);
+        if (n) { v32 = v32 * dx_pow10_u32[n] + digits4(w, n); nd += n; }
+    }
+    unsigned long long v = v32;
+    if (nd == 8) {
+        int k = 3;
+        for (;;) {
+            a = b; b = wp[k++]; w = __funnelshift_r(a, b, sh);
+            n = leading_digits4(w);
+            if (n) { v = v * dx_pow10_u32[n] + digits4(w, n); nd += n; }
+            if (n < 4) break;
+            if (nd > 18) return -1;
         }
-        if (n < 8) break;
-        if (nd > 18) return -1;
     }
     *value = v;
     return nd > 18 ? -1 : nd;
@@ -65,14 +75,26 @@ static __device__ bool fast_record_warp(const uint8_t* buf, uint32_t pos, uint32
             const uint32_t* lw = lits + (sg.lit_off >> 2);
             const uint32_t L = sg.lit_len, nw = L >> 2, sh = (pos & 3u) << 3;
             const uint32_t* wp = reinterpret_cast<const uint32_t*>(buf + (pos & ~3u));
-            uint32_t lo = wp[0], diff = 0;
-            // literals are short (key names): the first eight words are straight-line code under a uniform predicate
+            uint32_t lo = wp[0], diff = 0, hi;
+            uint32_t k = 0;
+            for (; k + 8 <= nw; k += 8) {   // long literals: eight words per trip
 #pragma unroll
-            for (uint32_t k = 0; k < 8; k++) {
-                if (k < nw) { const uint32_t hi = wp[k + 1]; diff |= __funnelshift_r(lo, hi, sh) ^ lw[k]; lo = hi; }
+                for (int u = 0; u < 8; u++) { hi = wp[k + u + 1]; diff |= __funnelshift_r(lo, hi, sh) ^ lw[k + u]; lo = hi; }
             }
-            for (uint32_t k = 8; k < nw; k++) { const uint32_t hi = wp[k + 1]; diff |= __funnelshift_r(lo, hi, sh) ^ lw[k]; lo = hi; }
-            if (L & 3u) { const uint32_t hi = wp[nw + 1]; diff |= (__funnelshift_r(lo, hi, sh) ^ lw[nw]) & ((1u << ((L & 3u) << 3)) - 1u); }
+            wp += k; lw += k;
+#define DX_LIT_WORD(i) hi = wp[(i) + 1]; diff |= __funnelshift_r(lo, hi, sh) ^ lw[i]; lo = hi;
+            switch (nw - k) {               // the remaining 0..7 words as straight-line code, exactly as many as needed
+            case 7: DX_LIT_WORD(0) wp++; lw++;
+            case 6: DX_LIT_WORD(0) wp++; lw++;
+            case 5: DX_LIT_WORD(0) wp++; lw++;
+            case 4: DX_LIT_WORD(0) wp++; lw++;
+            case 3: DX_LIT_WORD(0) wp++; lw++;
+            case 2: DX_LIT_WORD(0) wp++; lw++;
+            case 1: DX_LIT_WORD(0) wp++; lw++;
+            default: break;
+            }
+#undef DX_LIT_WORD
+            if (L & 3u) { hi = wp[1]; diff |= (__funnelshift_r(lo, hi, sh) ^ lw[0]) & ((1u << ((L & 3u) << 3)) - 1u); }
             ok = diff == 0;
             pos += L;
         }
