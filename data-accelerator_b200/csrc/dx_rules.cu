@@ -46,13 +46,16 @@ struct RSpaceDev {
     int32_t row_base;        // first table row of this space
     uint32_t slot_mask;      // slots (bits 0..J-1) some rule places a leaf of this space in
     uint32_t prog_start;     // DOM_GENERIC
-    int32_t pad;
+    int32_t pad;             // numeric domains: largest power of two <= n_consts (binary-search first step)
 };
 struct RClassDev {
     int32_t n_terms;
     uint8_t use[RB_MAX_TERMS], neg[RB_MAX_TERMS];
     int32_t mask_off;        // index into class_masks[] (Wp words)
+    int32_t shape;           // 0 = generic DNF loop; 1 a, 2 a&b, 3 a|b, 4 a&(b|c), 5 a&b&c (no negation)
+    int32_t pad;             // keeps sizeof a multiple of 8: the shared-memory arrays behind it hold 64-bit words
 };
+static_assert(sizeof(RSpaceDev) % 8 == 0 && sizeof(RClassDev) % 8 == 0, "shared layout needs 8-byte multiples");
 struct RulesDev {
     const RSpaceDev* spaces; int32_t n_spaces;
     const RClassDev* classes; int32_t n_classes;
@@ -62,19 +65,21 @@ struct RulesDev {
     const uint32_t* table_t; const uint32_t* table_f;   // [rows][J][Wp]
     int32_t total_rows, J, Wp, words;
     int32_t table_in_smem;
+    const void* shared_vmask; int32_t shared_vwidth;   // validity mask array shared by most spaces (loaded once per row)
     // generic leaves
     const uint32_t* code; const long long* gconsts; const ProgCol* gcols; const ProgLut* gluts; int32_t n_gcols;
 };
 
-static __device__ __forceinline__ int bucket_i64(const long long* c, int m, long long v) {
-    int lo = 0, hi = m;
-    while (lo < hi) { int mid = (lo + hi) >> 1; if (c[mid] < v) lo = mid + 1; else hi = mid; }
+// branch-free lower bound: number of constants < v, in ceil(log2(m+1)) fixed steps
+static __device__ __forceinline__ int bucket_i64(const long long* c, int m, int top, long long v) {
+    int lo = 0;
+    for (int step = top; step; step >>= 1) { const int idx = lo + step; if (idx <= m && c[idx - 1] < v) lo = idx; }
     return 2 * lo + ((lo < m && c[lo] == v) ? 1 : 0);
 }
-static __device__ __forceinline__ int bucket_f64(const long long* c, int m, double v) {
+static __device__ __forceinline__ int bucket_f64(const long long* c, int m, int top, double v) {
     if (v != v) return 2 * m;                                   // NaN is greater than every constant
-    int lo = 0, hi = m;
-    while (lo < hi) { int mid = (lo + hi) >> 1; if (__longlong_as_double(c[mid]) < v) lo = mid + 1; else hi = mid; }
+    int lo = 0;
+    for (int step = top; step; step >>= 1) { const int idx = lo + step; if (idx <= m && __longlong_as_double(c[idx - 1]) < v) lo = idx; }
     return 2 * lo + ((lo < m && __longlong_as_double(c[lo]) == v) ? 1 : 0);
 }
 
@@ -109,10 +114,23 @@ __global__ void __launch_bounds__(256) k2_rules_bucket(const __grid_constant__ R
     __syncthreads();
     EvalView gv{D.code, D.gconsts, D.gcols, D.gluts};
     const int n_wg = D.Wp / RB_WG;
+    const int ns = D.n_spaces;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_rows; i += (long long)gridDim.x * blockDim.x) {
         const long long row = sel ? sel[i] : i;
+        // phase A: every column value this rule set looks at, issued back to back (memory-level parallelism)
+        long long vv[RB_MAX_SPACES];
+        uint32_t shared_mask = 0xFFFFFFFFu;
+        if (D.shared_vmask) shared_mask = D.shared_vwidth == 1 ? reinterpret_cast<const uint8_t*>(D.shared_vmask)[row] : reinterpret_cast<const uint32_t*>(D.shared_vmask)[row];
+        for (int s = 0; s < ns; s++) {
+            const RSpaceDev& sp = s_spaces[s];
+            long long v = 0;
+            if (sp.domain == DOM_CODE) v = reinterpret_cast<const int32_t*>(sp.col.data)[row];
+            else if (sp.domain != DOM_GENERIC) v = reinterpret_cast<const long long*>(sp.col.data)[row];
+            vv[s] = v;
+        }
+        // phase B: one bucket per space
         int brow[RB_MAX_SPACES];
-        for (int s = 0; s < D.n_spaces; s++) {
+        for (int s = 0; s < ns; s++) {
             const RSpaceDev& sp = s_spaces[s];
             int b;
             if (sp.domain == DOM_GENERIC) {
@@ -122,19 +140,17 @@ __global__ void __launch_bounds__(256) k2_rules_bucket(const __grid_constant__ R
             } else {
                 bool valid = true;
                 if (sp.col.vmask) {
-                    uint32_t m = sp.col.vwidth == 1 ? reinterpret_cast<const uint8_t*>(sp.col.vmask)[row] : reinterpret_cast<const uint32_t*>(sp.col.vmask)[row];
+                    uint32_t m = shared_mask;
+                    if (!D.shared_vmask || sp.col.vmask != D.shared_vmask)
+                        m = sp.col.vwidth == 1 ? reinterpret_cast<const uint8_t*>(sp.col.vmask)[row] : reinterpret_cast<const uint32_t*>(sp.col.vmask)[row];
                     valid = (m >> sp.col.vbit) & 1u;
                 }
+                const long long v = vv[s];
                 if (!valid) b = sp.null_bucket;
-                else if (sp.domain == DOM_CODE) {
-                    int code = reinterpret_cast<const int32_t*>(sp.col.data)[row];
-                    b = (code >= 0 && code < sp.lut_size) ? s_luts[sp.lut_off + code] : sp.other_bucket;
-                } else {
-                    long long v = reinterpret_cast<const long long*>(sp.col.data)[row];
-                    if (sp.domain == DOM_I64) b = bucket_i64(s_consts + sp.const_off, sp.n_consts, v);
-                    else if (sp.domain == DOM_F64) b = bucket_f64(s_consts + sp.const_off, sp.n_consts, __longlong_as_double(v));
-                    else b = bucket_f64(s_consts + sp.const_off, sp.n_consts, (double)v);
-                }
+                else if (sp.domain == DOM_CODE) b = (v >= 0 && v < sp.lut_size) ? s_luts[sp.lut_off + (int)v] : sp.other_bucket;
+                else if (sp.domain == DOM_I64) b = bucket_i64(s_consts + sp.const_off, sp.n_consts, sp.pad, v);
+                else if (sp.domain == DOM_F64) b = bucket_f64(s_consts + sp.const_off, sp.n_consts, sp.pad, __longlong_as_double(v));
+                else b = bucket_f64(s_consts + sp.const_off, sp.n_consts, sp.pad, (double)v);
             }
             brow[s] = (sp.row_base + b) * row_words;
         }
@@ -144,7 +160,7 @@ __global__ void __launch_bounds__(256) k2_rules_bucket(const __grid_constant__ R
             for (int j = 0; j < J; j++)
 #pragma unroll
                 for (int w = 0; w < RB_WG; w++) { T[j][w] = 0; if (NEEDF) F[j][w] = 0; }
-            for (int s = 0; s < D.n_spaces; s++) {
+            for (int s = 0; s < ns; s++) {
                 const uint32_t sm = s_spaces[s].slot_mask;
                 const int base = brow[s] + wg * RB_WG;
 #pragma unroll
@@ -169,25 +185,57 @@ __global__ void __launch_bounds__(256) k2_rules_bucket(const __grid_constant__ R
             for (int k = 0; k < D.n_classes; k++) {
                 const RClassDev& cl = s_classes[k];
                 const uint32_t* cm = s_cmask + cl.mask_off + wg * RB_WG;
-                for (int t = 0; t < cl.n_terms; t++) {
-                    const uint32_t use = cl.use[t], neg = cl.neg[t];
-                    uint32_t acc[RB_WG];
+                // the common rule shapes as straight-line word operations; everything else through the DNF loop
+                switch (cl.shape) {
+                case 1:   // a
 #pragma unroll
-                    for (int w = 0; w < RB_WG; w++) acc[w] = cm[w];
+                    for (int w = 0; w < RB_WG; w++) out[w] |= cm[w] & T[0][w];
+                    break;
+                case 2:   // a AND b
+                    if (J >= 2) {
 #pragma unroll
-                    for (int j = 0; j < J; j++) {
-                        if ((use >> j) & 1u) {
-                            if (NEEDF && ((neg >> j) & 1u)) {
+                        for (int w = 0; w < RB_WG; w++) out[w] |= cm[w] & T[0][w] & T[J >= 2 ? 1 : 0][w];
+                    }
+                    break;
+                case 3:   // a OR b
+                    if (J >= 2) {
 #pragma unroll
-                                for (int w = 0; w < RB_WG; w++) acc[w] &= F[j][w];
-                            } else {
+                        for (int w = 0; w < RB_WG; w++) out[w] |= cm[w] & (T[0][w] | T[J >= 2 ? 1 : 0][w]);
+                    }
+                    break;
+                case 4:   // a AND (b OR c)
+                    if (J >= 3) {
 #pragma unroll
-                                for (int w = 0; w < RB_WG; w++) acc[w] &= T[j][w];
+                        for (int w = 0; w < RB_WG; w++) out[w] |= cm[w] & T[0][w] & (T[J >= 3 ? 1 : 0][w] | T[J >= 3 ? 2 : 0][w]);
+                    }
+                    break;
+                case 5:   // a AND b AND c
+                    if (J >= 3) {
+#pragma unroll
+                        for (int w = 0; w < RB_WG; w++) out[w] |= cm[w] & T[0][w] & T[J >= 3 ? 1 : 0][w] & T[J >= 3 ? 2 : 0][w];
+                    }
+                    break;
+                default:
+                    for (int t = 0; t < cl.n_terms; t++) {
+                        const uint32_t use = cl.use[t], neg = cl.neg[t];
+                        uint32_t acc[RB_WG];
+#pragma unroll
+                        for (int w = 0; w < RB_WG; w++) acc[w] = cm[w];
+#pragma unroll
+                        for (int j = 0; j < J; j++) {
+                            if ((use >> j) & 1u) {
+                                if (NEEDF && ((neg >> j) & 1u)) {
+#pragma unroll
+                                    for (int w = 0; w < RB_WG; w++) acc[w] &= F[j][w];
+                                } else {
+#pragma unroll
+                                    for (int w = 0; w < RB_WG; w++) acc[w] &= T[j][w];
+                                }
                             }
                         }
-                    }
 #pragma unroll
-                    for (int w = 0; w < RB_WG; w++) out[w] |= acc[w];
+                        for (int w = 0; w < RB_WG; w++) out[w] |= acc[w];
+                    }
                 }
             }
 #pragma unroll
@@ -504,6 +552,7 @@ int dx_rules_eval(dx_ctx* ctx, const BindScope& sc, const std::vector<ExprP>& co
                 int m = (int)sp.consts.size();
                 sp.null_bucket = 2 * m + 1; sp.n_buckets = 2 * m + 2;
                 d.const_off = (int)all_consts.size(); d.n_consts = m;
+                { int top = 0; if (m > 0) { top = 1; while (top * 2 <= m) top *= 2; } d.pad = top; }
                 for (long long v : sp.consts) all_consts.push_back(v);
             }
         }
@@ -547,6 +596,12 @@ int dx_rules_eval(dx_ctx* ctx, const BindScope& sc, const std::vector<ExprP>& co
             if ((int)classes.size() >= RB_MAX_CLASSES) return DX_OK;     // fall back
             RClassDev c; memset(&c, 0, sizeof c); c.n_terms = (int)rp.terms.size();
             for (size_t t = 0; t < rp.terms.size(); t++) { c.use[t] = rp.terms[t].first; c.neg[t] = rp.terms[t].second; }
+            c.shape = 0;
+            if (sig == "1/0;") c.shape = 1;
+            else if (sig == "3/0;") c.shape = 2;
+            else if (sig == "1/0;2/0;") c.shape = 3;
+            else if (sig == "3/0;5/0;") c.shape = 4;
+            else if (sig == "7/0;") c.shape = 5;
             classes.push_back(c); class_by_sig[sig] = (int)classes.size() - 1; rp.cls = (int)classes.size() - 1;
         } else rp.cls = it->second;
     }
@@ -606,6 +661,11 @@ int dx_rules_eval(dx_ctx* ctx, const BindScope& sc, const std::vector<ExprP>& co
     D.class_masks = b_cmask.as<uint32_t>();
     D.table_t = b_tt.as<uint32_t>(); D.table_f = b_tf.as<uint32_t>();
     D.total_rows = total_rows; D.J = J; D.Wp = Wp; D.words = words;
+    {   // the validity array most spaces share (the decoder writes one mask byte per row for all leaves)
+        std::map<const void*, int> votes; const void* best = nullptr; int bw = 0, bc = 0;
+        for (auto& d : sdev) if (d.domain != DOM_GENERIC && d.col.vmask) { int c = ++votes[d.col.vmask]; if (c > bc) { bc = c; best = d.col.vmask; bw = d.col.vwidth; } }
+        D.shared_vmask = bc >= 2 ? best : nullptr; D.shared_vwidth = bw;
+    }
     if (!P.G.prog_start.empty()) {
         D.code = GD.code.as<uint32_t>(); D.gconsts = GD.consts.as<long long>(); D.gcols = GD.cols.as<ProgCol>(); D.gluts = GD.luts.as<ProgLut>(); D.n_gcols = GD.n_cols;
     }
