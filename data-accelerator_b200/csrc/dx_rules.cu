@@ -33,6 +33,9 @@ using namespace dxsql;
 #define RB_JMAX 4
 #define RB_WG 8                      // flag words handled per pass (256 rules)
 #define RB_SMEM_TABLE_BYTES (160 * 1024)
+#ifndef K2_MIN_CTAS
+#define K2_MIN_CTAS 4
+#endif
 
 enum { DOM_I64 = 0, DOM_F64 = 1, DOM_F64_FROM_I64 = 2, DOM_CODE = 3, DOM_GENERIC = 4 };
 
@@ -83,8 +86,8 @@ static __device__ __forceinline__ int bucket_f64(const long long* c, int m, int 
     return 2 * lo + ((lo < m && __longlong_as_double(c[lo]) == v) ? 1 : 0);
 }
 
-template <int J, bool NEEDF>
-__global__ void __launch_bounds__(256) k2_rules_bucket(const __grid_constant__ RulesDev D, long long n_rows, const long long* sel, uint32_t* flags) {
+template <int J, bool NEEDF, int NSMAX>
+__global__ void __launch_bounds__(256, K2_MIN_CTAS) k2_rules_bucket(const __grid_constant__ RulesDev D, long long n_rows, const long long* sel, uint32_t* flags) {
     extern __shared__ __align__(16) uint8_t rsm[];
     // shared layout: spaces | classes | class masks | consts | luts | [table_t | table_f]
     RSpaceDev* s_spaces = reinterpret_cast<RSpaceDev*>(rsm);
@@ -118,10 +121,12 @@ __global__ void __launch_bounds__(256) k2_rules_bucket(const __grid_constant__ R
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_rows; i += (long long)gridDim.x * blockDim.x) {
         const long long row = sel ? sel[i] : i;
         // phase A: every column value this rule set looks at, issued back to back (memory-level parallelism)
-        long long vv[RB_MAX_SPACES];
+        long long vv[NSMAX];
         uint32_t shared_mask = 0xFFFFFFFFu;
         if (D.shared_vmask) shared_mask = D.shared_vwidth == 1 ? reinterpret_cast<const uint8_t*>(D.shared_vmask)[row] : reinterpret_cast<const uint32_t*>(D.shared_vmask)[row];
-        for (int s = 0; s < ns; s++) {
+#pragma unroll
+        for (int s = 0; s < NSMAX; s++) {
+            if (s >= ns) break;
             const RSpaceDev& sp = s_spaces[s];
             long long v = 0;
             if (sp.domain == DOM_CODE) v = reinterpret_cast<const int32_t*>(sp.col.data)[row];
@@ -129,8 +134,10 @@ __global__ void __launch_bounds__(256) k2_rules_bucket(const __grid_constant__ R
             vv[s] = v;
         }
         // phase B: one bucket per space
-        int brow[RB_MAX_SPACES];
-        for (int s = 0; s < ns; s++) {
+        int brow[NSMAX];
+#pragma unroll
+        for (int s = 0; s < NSMAX; s++) {
+            if (s >= ns) break;
             const RSpaceDev& sp = s_spaces[s];
             int b;
             if (sp.domain == DOM_GENERIC) {
@@ -160,7 +167,9 @@ __global__ void __launch_bounds__(256) k2_rules_bucket(const __grid_constant__ R
             for (int j = 0; j < J; j++)
 #pragma unroll
                 for (int w = 0; w < RB_WG; w++) { T[j][w] = 0; if (NEEDF) F[j][w] = 0; }
-            for (int s = 0; s < ns; s++) {
+#pragma unroll
+            for (int s = 0; s < NSMAX; s++) {
+                if (s >= ns) break;
                 const uint32_t sm = s_spaces[s].slot_mask;
                 const int base = brow[s] + wg * RB_WG;
 #pragma unroll
@@ -478,15 +487,15 @@ static bool like_match2(const std::string& s, const std::string& p) {
 
 } // namespace
 
-template <int J, bool NEEDF>
+template <int J, bool NEEDF, int NSMAX>
 static void launch_rules(dx_ctx* ctx, const RulesDev& D, size_t smem, int64_t n_rows, const int64_t* sel, uint32_t* flags) {
-    cudaFuncSetAttribute(k2_rules_bucket<J, NEEDF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaFuncSetAttribute(k2_rules_bucket<J, NEEDF, NSMAX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     int occ = 1;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k2_rules_bucket<J, NEEDF>, 256, smem);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k2_rules_bucket<J, NEEDF, NSMAX>, 256, smem);
     if (occ < 1) occ = 1;
     long long blocks = (n_rows + 255) / 256, cap = (long long)ctx->sm_count * occ;
     if (blocks > cap) blocks = cap;
-    k2_rules_bucket<J, NEEDF><<<(unsigned)blocks, 256, smem, ctx->stream>>>(D, n_rows, reinterpret_cast<const long long*>(sel), flags);
+    k2_rules_bucket<J, NEEDF, NSMAX><<<(unsigned)blocks, 256, smem, ctx->stream>>>(D, n_rows, reinterpret_cast<const long long*>(sel), flags);
 }
 
 int dx_rules_eval(dx_ctx* ctx, const BindScope& sc, const std::vector<ExprP>& conds, int64_t n_rows, const int64_t* sel,
@@ -677,7 +686,8 @@ int dx_rules_eval(dx_ctx* ctx, const BindScope& sc, const std::vector<ExprP>& co
     if (fixed > 64 * 1024) return DX_OK;       // pathological constant count: generic kernel
     {
         StageTimer tm(ctx, "k2_rules_bucket");
-#define RB_LAUNCH(JJ) do { if (needf) launch_rules<JJ, true>(ctx, D, smem, n_rows, sel, flags); else launch_rules<JJ, false>(ctx, D, smem, n_rows, sel, flags); } while (0)
+#define RB_LAUNCH_NS(JJ, FF) do { if (D.n_spaces <= 8) launch_rules<JJ, FF, 8>(ctx, D, smem, n_rows, sel, flags); else launch_rules<JJ, FF, RB_MAX_SPACES>(ctx, D, smem, n_rows, sel, flags); } while (0)
+#define RB_LAUNCH(JJ) do { if (needf) RB_LAUNCH_NS(JJ, true); else RB_LAUNCH_NS(JJ, false); } while (0)
         if (J == 1) RB_LAUNCH(1); else if (J == 2) RB_LAUNCH(2); else if (J == 3) RB_LAUNCH(3); else RB_LAUNCH(4);
         ctx->launches["k2_rules_bucket"]++;
     }

@@ -2,7 +2,7 @@
 # usage: tools/k1_sweep.sh "<define variants...>"  — rebuilds dx_decode.o per variant on the GPU box and prints K1/K2 ms
 cd /root/repo/data-accelerator_b200/csrc
 for v in "$@"; do
-  touch dx_decode.cu
+  touch dx_decode.cu dx_rules.cu
   make -s EXTRA="$v" 2>&1 | grep -E "error" 
   cd /root/repo
   python bench.py --events 40000000 --steps 3 --warmup 2 --no-cpu-baseline 2>&1 | tail -1 | python -c "
