@@ -51,6 +51,11 @@ int64_t dx_ctx_take_launches(dx_ctx* c) {
     for (auto& kv : c->launches) { n += kv.second; kv.second = 0; }
     return n;
 }
+int64_t dx_ctx_take_counter(dx_ctx* c, const char* name) {
+    auto it = c->counters.find(name);
+    if (it == c->counters.end()) return 0;
+    int64_t v = it->second; it->second = 0; return v;
+}
 void* dx_ctx_stream(dx_ctx* c) { return reinterpret_cast<void*>(c->stream); }
 int dx_ctx_synchronize(dx_ctx* c) { DX_CUDA(c, cudaStreamSynchronize(c->stream)); return DX_OK; }
 int dx_dev_alloc(dx_ctx* c, int64_t bytes, void** out) {

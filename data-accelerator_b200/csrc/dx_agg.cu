@@ -27,7 +27,12 @@ static __device__ __forceinline__ bool load_val(const ProgCol& c, long long row,
 __global__ void __launch_bounds__(256) k3_hash_agg(const __grid_constant__ AggTableDev T, const __grid_constant__ AggInput in) {
     const int nk = T.n_keys, na = T.n_accs, sw = T.slot_words;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < in.n_rows; i += (long long)gridDim.x * blockDim.x) {
+        if (*reinterpret_cast<volatile unsigned long long*>(&T.counters[1])) return;   // table declared too small: the host retries with a larger one
         const long long row = in.sel ? in.sel[i] : i;
+        if (in.has_range) {     // the window view's [start, end) filter, fused (CommonProcessorFactory.scala:203-227)
+            long long t;
+            if (!load_val(in.range_col, row, t) || t < in.range_lo || t >= in.range_hi) continue;
+        }
         long long kv[DX_AGG_MAX_KEYS];
         unsigned long long nullbits = 0, h = 0x2545F4914F6CDD1Dull;
 #pragma unroll
@@ -42,7 +47,7 @@ __global__ void __launch_bounds__(256) k3_hash_agg(const __grid_constant__ AggTa
         const unsigned long long tag = h | 0x8000000000000000ull;     // never 0 (empty) or 1 (being filled)
         unsigned long long idx = (h >> 3) & T.cap_mask;
         unsigned long long* slot = nullptr;
-        for (unsigned long long probes = 0; probes <= T.cap_mask; ) {
+        for (unsigned long long probes = 0; probes <= T.cap_mask && probes < 256; ) {   // a probe run this long means the table is crowded: give up, grow
             unsigned long long* s = T.slots + idx * sw;
             unsigned long long cur = *reinterpret_cast<volatile unsigned long long*>(s);
             if (cur == tag) {
@@ -137,6 +142,7 @@ int AggTable::update(const AggInput& in) {
     if (in.n_rows <= 0) return DX_OK;
     long long blocks = (in.n_rows + 255) / 256;
     long long capb = (long long)ctx->sm_count * 8; if (blocks > capb) blocks = capb;
+    ctx->counters["k3_rows"] += in.n_rows;
     StageTimer tm(ctx, "k3_hash_agg");
     k3_hash_agg<<<(unsigned)blocks, 256, 0, ctx->stream>>>(dev, in);
     ctx->launches["k3_hash_agg"]++;

@@ -20,6 +20,9 @@ struct AggInput {                 // one chunk of input rows
     ProgCol vals[DX_AGG_MAX_ACCS];
     const long long* sel;         // optional row selection
     long long n_rows;             // rows to visit (length of sel if given)
+    ProgCol range_col;            // optional fused time-range filter: keep rows with lo <= range_col < hi (NULL fails)
+    long long range_lo, range_hi;
+    int32_t has_range, pad;
 };
 
 struct AggTableDev {

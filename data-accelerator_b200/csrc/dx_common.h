@@ -57,6 +57,7 @@ struct dx_ctx {
     bool timing = false;
     std::map<std::string, std::vector<float>> stage_ms;
     std::map<std::string, long long> launches;
+    std::map<std::string, long long> counters;     // work counters (rows visited by K3, rows moved by K4 ...)
     int set_error(int code, const std::string& msg) { last_error = msg; return code; }
 };
 
@@ -157,6 +158,8 @@ struct DxTable {
     std::string name;
     int64_t n_rows = 0;
     std::vector<DxColumn> cols;
+    bool has_ts_bounds = false;     // window cache: bounds of the flow's timestamp column over this table's rows
+    long long ts_min = 0, ts_max = 0;
     int find(const std::string& n) const {
         for (size_t i = 0; i < cols.size(); i++) if (cols[i].name == n) return (int)i;
         return -1;

@@ -194,6 +194,19 @@ static std::string last_part(const std::string& n) { size_t k = n.rfind('.'); re
 __global__ void k_fill_i64(long long* p, long long n, long long v) {
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) p[i] = v;
 }
+__global__ void k_minmax_i64(const long long* v, const void* vmask, int vwidth, int vbit, long long n, long long* out /* [min, max, count] */) {
+    long long mn = 0x7FFFFFFFFFFFFFFFll, mx = (long long)0x8000000000000000ull, cnt = 0;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        bool valid = true;
+        if (vmask) { uint32_t m = vwidth == 1 ? reinterpret_cast<const uint8_t*>(vmask)[i] : reinterpret_cast<const uint32_t*>(vmask)[i]; valid = (m >> vbit) & 1u; }
+        if (valid) { long long x = v[i]; mn = x < mn ? x : mn; mx = x > mx ? x : mx; cnt++; }
+    }
+    for (int s = 16; s > 0; s >>= 1) {
+        long long a = __shfl_xor_sync(0xffffffffu, mn, s), b = __shfl_xor_sync(0xffffffffu, mx, s);
+        mn = a < mn ? a : mn; mx = b > mx ? b : mx; cnt += __shfl_xor_sync(0xffffffffu, cnt, s);
+    }
+    if ((threadIdx.x & 31) == 0 && cnt) { atomicMin(&out[0], mn); atomicMax(&out[1], mx); atomicAdd(reinterpret_cast<unsigned long long*>(&out[2]), (unsigned long long)cnt); }
+}
 __global__ void k_finalize(int mode, const unsigned long long* a, const unsigned long long* cnt, const unsigned long long* keynull, int keybit,
                            long long n, void* out, int out_width, uint32_t* vmask32, int vbit) {
     // mode 0: key copy (valid = !keynull bit); 1: accumulator copy, always valid; 2: accumulator copy, valid iff cnt>0;
@@ -257,6 +270,9 @@ struct Exec {
             auto rng = std::make_shared<Expr>(); rng->kind = EK::Bin; rng->sval = "AND"; rng->args = {ge, lt};
             if (cond) { auto both = std::make_shared<Expr>(); both->kind = EK::Bin; both->sval = "AND"; both->args = {rng, cond}; cond = both; }
             else cond = rng;
+        }
+        if (v.ranged && chunk->has_ts_bounds && (chunk->ts_max < v.lo_us || chunk->ts_min >= v.hi_us)) {
+            *filtered = true; *n_sel = 0; *sel = make_buf(ctx, 8); return DX_OK;      // no row of this cached batch is inside the window
         }
         if (!cond) { *filtered = false; *n_sel = chunk->n_rows; return DX_OK; }
         *filtered = true;
@@ -684,14 +700,25 @@ struct Exec {
         // selections per chunk
         struct ChunkSel { DevBufP sel; int64_t n = 0; bool filtered = false; };
         std::vector<ChunkSel> cs(v.chunks.size()); int64_t total = 0;
+        const bool fuse_range = v.ranged && !core.where;
         for (size_t k = 0; k < v.chunks.size(); k++) {
-            int rc = chunk_selection(v, v.chunks[k], core, &cs[k].sel, &cs[k].n, &cs[k].filtered); if (rc) return rc;
+            if (fuse_range) {
+                // no WHERE: the window's time range is applied inside the aggregation kernel, no selection pass
+                const DxTableP& ch = v.chunks[k];
+                const bool outside = ch->has_ts_bounds && (ch->ts_max < v.lo_us || ch->ts_min >= v.hi_us);
+                cs[k].filtered = false; cs[k].n = outside ? 0 : ch->n_rows;
+            } else {
+                int rc = chunk_selection(v, v.chunks[k], core, &cs[k].sel, &cs[k].n, &cs[k].filtered); if (rc) return rc;
+            }
             total += cs[k].n;
         }
         unsigned long long cap = 1024;
         auto hint = F->agg_capacity_hint.find(stmt_name);
-        if (hint != F->agg_capacity_hint.end()) cap = hint->second;
-        else { unsigned long long want = (unsigned long long)std::min<int64_t>(total, 1 << 22) * 2; while (cap < want) cap <<= 1; }
+        {   // remembered size of this statement's table, but never far below what this batch's row count could need
+            unsigned long long want = (unsigned long long)std::min<int64_t>(total, 1 << 22) * 2;
+            if (hint != F->agg_capacity_hint.end()) { cap = hint->second; want = std::min<unsigned long long>(want, 1ull << 20); }
+            while (cap < want) cap <<= 1;
+        }
         AggTable T; unsigned long long n_groups = 0;
         std::vector<int> key_type(keys.size(), DX_T_I64); std::vector<DxDictP> key_dict(keys.size());
         for (int attempt = 0;; attempt++) {
@@ -702,6 +729,15 @@ struct Exec {
                 BindScope sc = scope_for(ch, core);
                 AggInput in; memset(&in, 0, sizeof in);
                 in.sel = cs[k].filtered ? cs[k].sel->as<long long>() : nullptr; in.n_rows = cs[k].n;
+                if (fuse_range) {
+                    std::string err; int tc = dx_resolve_column(sc, std::vector<std::string>{v.ts_col}, &err);
+                    if (tc < 0) return fail(DX_ERR_ARG, err);
+                    const DxColumn& c = ch->cols[tc];
+                    if (!c.data || c.type != DX_T_TS) return fail(DX_ERR_UNSUPPORTED, "window timestamp column must be a materialised timestamp");
+                    in.range_col.data = c.data->p; in.range_col.vmask = c.vmask ? c.vmask->p : nullptr; in.range_col.vwidth = c.vwidth;
+                    in.range_col.vbit = c.vbit; in.range_col.width = 8;
+                    in.range_lo = v.lo_us; in.range_hi = v.hi_us; in.has_range = 1;
+                }
                 std::vector<DevBufP> temps; DevBufP tmask;
                 auto col_desc = [&](const DxColumn& c) { ProgCol pc; pc.data = c.data->p; pc.vmask = c.vmask ? c.vmask->p : nullptr; pc.vwidth = c.vwidth; pc.vbit = c.vbit; pc.width = dx_type_width(c.type); pc.pad = 0; return pc; };
                 auto eval_temp = [&](const ExprP& e, int* type_out, ProgCol* pc) -> int {
@@ -936,6 +972,23 @@ int dx_flow::process(const std::string& name_space, const uint8_t* json, int64_t
         DxTableP cur; rc = X.exec_plain(keep, views["__projected"], &cur); if (rc) return rc;
         views.erase("__projected");
         metric("Input_DataXProcessedInput_Events_Count", (double)cur->n_rows);
+        {   // bounds of the timestamp column over the cached rows: later window views skip batches that cannot intersect them
+            BindScope bs; bs.table = cur.get();
+            std::string err; int tc = dx_resolve_column(bs, std::vector<std::string>{ts_column}, &err);
+            if (tc >= 0 && cur->cols[tc].data && cur->cols[tc].type == DX_T_TS && cur->n_rows > 0) {
+                const DxColumn& c = cur->cols[tc];
+                DevBuf mm(ctx, 32);
+                long long init[3] = {0x7FFFFFFFFFFFFFFFll, (long long)0x8000000000000000ull, 0};
+                DX_CUDA(ctx, cudaMemcpyAsync(mm.p, init, 24, cudaMemcpyHostToDevice, ctx->stream));
+                k_minmax_i64<<<(unsigned)std::min<long long>((cur->n_rows + 255) / 256, 2048), 256, 0, ctx->stream>>>(
+                    c.data->as<long long>(), c.vmask ? c.vmask->p : nullptr, c.vwidth, c.vbit, cur->n_rows, mm.as<long long>());
+                ctx->launches["k_minmax"]++;
+                long long h[3];
+                DX_CUDA(ctx, cudaMemcpyAsync(h, mm.p, 24, cudaMemcpyDeviceToHost, ctx->stream));
+                DX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+                if (h[2] > 0) { cur->has_ts_bounds = true; cur->ts_min = h[0]; cur->ts_max = h[1]; }
+            } else if (cur->n_rows == 0) { cur->has_ts_bounds = true; cur->ts_min = 1; cur->ts_max = 0; }
+        }
         const long long cut = T - (watermark_s + max_window_s) * 1000;
         for (auto it = NS.past_batches.begin(); it != NS.past_batches.end();) { if (it->first <= cut) it = NS.past_batches.erase(it); else ++it; }
         std::vector<DxTableP> U; U.push_back(cur);

@@ -41,6 +41,11 @@ class Context:
     def take_launches(self):
         return int(self.L.dx_ctx_take_launches(self.h))
 
+    def take_counter(self, name):
+        fn = self.L.dx_ctx_take_counter
+        fn.restype, fn.argtypes = C.c_int64, [C.c_void_p, C.c_char_p]
+        return int(fn(self.h, name.encode()))
+
     def synchronize(self):
         self.check(self.L.dx_ctx_synchronize(self.h))
 

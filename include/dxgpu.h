@@ -47,6 +47,8 @@ int dx_ctx_set_timing(dx_ctx* ctx, int enabled);
 int dx_ctx_take_stage_ms(dx_ctx* ctx, const char* stage, double* total_ms, int64_t* samples);
 /* Number of launches of this library's kernels since the last call (resets the counter). */
 int64_t dx_ctx_take_launches(dx_ctx* ctx);
+/* Work counters for roofline arithmetic ("k3_rows": rows visited by the aggregation kernel, "gather_bytes"); resets. */
+int64_t dx_ctx_take_counter(dx_ctx* ctx, const char* name);
 void* dx_ctx_stream(dx_ctx* ctx);                     /* cudaStream_t, for event timing by the caller */
 int dx_ctx_synchronize(dx_ctx* ctx);
 /* pooled device memory for callers that stage inputs themselves */
