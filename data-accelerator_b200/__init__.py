@@ -9,3 +9,4 @@ from .device import Context, Decoder, Table  # noqa: F401
 from .processor import (CommonProcessorFactory, CommonProcessor, BatchResult, rules_of, sql_canonical,  # noqa: F401
                         transform_split, string_to_timestamp, duration_seconds)
 from . import flowgen  # noqa: F401
+from . import parallel  # noqa: F401

@@ -3,6 +3,7 @@
 #include "dx_abi_types.h"
 #include "dx_decode_host.h"
 #include "dx_flow.h"
+#include "dx_shuffle.h"
 
 int dx_gen_device(dx_ctx* c, const dx_gen_params* g, int64_t first, int64_t n, uint8_t** bytes_out,
                   int64_t* n_bytes_out, int64_t** offsets_out);
@@ -273,6 +274,63 @@ int dx_flow_state_export(dx_flow* f, const char* table, dx_table** out, int* act
     if (it == f->state_tables.end()) return f->ctx->set_error(DX_ERR_ARG, std::string("no state table '") + table + "'");
     *out = dx_wrap_table(it->second.phys[it->second.active]);
     if (active_is_b) *active_is_b = it->second.active;
+    return DX_OK;
+}
+
+// ---- multi-GPU: projection only, route only, key-hash shuffle ------------------------------------
+int dx_flow_project(dx_flow* f, const uint8_t* json, int64_t n_bytes, const int64_t* offsets, int64_t n_events, int memory_kind,
+                    int64_t now_ms, dx_table** out) {
+    if (!f || !out || (n_bytes > 0 && !json)) return DX_ERR_ARG;
+    cudaSetDevice(f->ctx->device);
+    DxTableP t;
+    try { int rc = f->project(json, n_bytes, offsets, n_events, memory_kind, now_ms, &t); if (rc) return rc; }
+    catch (std::exception& e) { return f->ctx->set_error(DX_ERR_STATE, e.what()); }
+    *out = dx_wrap_table(t);
+    return DX_OK;
+}
+int dx_flow_process_table(dx_flow* f, const char* name_space, const dx_table* projected, int64_t batch_time_ms, int64_t interval_ms,
+                          int64_t now_ms, dx_result** out) {
+    if (!f || !projected || !out) return DX_ERR_ARG;
+    cudaSetDevice(f->ctx->device);
+    try { return f->route(name_space ? name_space : "", dx_unwrap_table(projected), batch_time_ms, interval_ms, now_ms, out); }
+    catch (std::exception& e) { return f->ctx->set_error(DX_ERR_STATE, e.what()); }
+}
+int dx_table_shuffle_pack(const dx_table* h, const char* const* cols, int n_cols, const char* const* key_cols, int n_keys, int world,
+                          void* packed_dev, int64_t* counts, int64_t* rec_bytes) {
+    const DxTable* t = T(h);
+    dx_ctx* c = t->ctx;
+    cudaSetDevice(c->device);
+    if (n_cols < 1 || n_keys < 0 || n_keys > 8 || !counts) return c->set_error(DX_ERR_ARG, "shuffle_pack: bad arguments");
+    BindScope sc; sc.table = t;
+    std::vector<int> idx, kpos;
+    for (int i = 0; i < n_cols; i++) {
+        std::string err; std::vector<std::string> parts;
+        std::string nm = cols[i]; size_t p0 = 0;
+        while (true) { size_t d = nm.find('.', p0); if (d == std::string::npos) { parts.push_back(nm.substr(p0)); break; } parts.push_back(nm.substr(p0, d - p0)); p0 = d + 1; }
+        int ci = dx_resolve_column(sc, parts, &err);
+        if (ci < 0) return c->set_error(DX_ERR_ARG, "shuffle_pack: " + err);
+        idx.push_back(ci);
+    }
+    for (int k = 0; k < n_keys; k++) {
+        int pos = -1;
+        for (int i = 0; i < n_cols; i++) if (std::string(cols[i]) == key_cols[k]) pos = i;
+        if (pos < 0) return c->set_error(DX_ERR_ARG, std::string("shuffle_pack: key column '") + key_cols[k] + "' is not among the sent columns");
+        kpos.push_back(pos);
+    }
+    if (rec_bytes) *rec_bytes = 8 * (int64_t)(n_cols + 1);
+    if (t->n_rows > 0 && !packed_dev) return c->set_error(DX_ERR_ARG, "shuffle_pack: null output buffer");
+    return dx_shuffle_pack(c, t, idx, kpos, world, packed_dev, counts);
+}
+int dx_table_from_packed(dx_ctx* c, const char* const* col_names, const int* col_types, int n_cols, const void* packed_dev, int64_t n_rows,
+                         dx_table** out) {
+    if (!c || !out || n_cols < 1 || n_rows < 0) return DX_ERR_ARG;
+    cudaSetDevice(c->device);
+    std::vector<std::string> names; std::vector<int> types;
+    for (int i = 0; i < n_cols; i++) { names.push_back(col_names[i]); types.push_back(col_types[i]); }
+    DxTableP t;
+    int rc = dx_shuffle_unpack(c, names, types, packed_dev, n_rows, &t);
+    if (rc) return rc;
+    *out = dx_wrap_table(t);
     return DX_OK;
 }
 

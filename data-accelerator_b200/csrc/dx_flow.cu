@@ -936,11 +936,9 @@ int dx_flow_build(dx_ctx* ctx, const char* conf_text, const char* schema_json, c
 // =======================================================================================
 // one micro-batch: processDataset -> project -> route (CommonProcessorFactory.scala:333-399)
 // =======================================================================================
-int dx_flow::process(const std::string& name_space, const uint8_t* json, int64_t n_bytes, const int64_t* offsets, int64_t n_events,
-                     int memory_kind, long long batch_ms, long long interval_ms, long long now_ms, dx_result** out) {
-    std::unique_ptr<dx_result> R(new dx_result()); R->flow = this;
-    auto metric = [&](const std::string& k, double v) { R->metric_keys.push_back(k); R->metric_vals.push_back(v); };
-    // ---- project(): from_json + selectExpr steps (CPF:90-103)
+// project(): from_json + selectExpr steps (CommonProcessorFactory.scala:90-103)
+int dx_flow::project(const uint8_t* json, int64_t n_bytes, const int64_t* offsets, int64_t n_events, int memory_kind,
+                     long long now_ms, DxTableP* out) {
     DxTableP raw;
     int rc = memory_kind == 1 ? decoder->decode_device(json, n_bytes, offsets, n_events, &raw) : decoder->decode_host(json, n_bytes, offsets, n_events, &raw);
     if (rc) return rc;
@@ -954,7 +952,27 @@ int dx_flow::process(const std::string& name_space, const uint8_t* json, int64_t
         DxTableP next; rc = X.exec_plain(core, views["Raw"], &next); if (rc) return rc;
         projected = next;
     }
-    views.erase("Raw");
+    *out = projected;
+    return DX_OK;
+}
+
+int dx_flow::process(const std::string& name_space, const uint8_t* json, int64_t n_bytes, const int64_t* offsets, int64_t n_events,
+                     int memory_kind, long long batch_ms, long long interval_ms, long long now_ms, dx_result** out) {
+    DxTableP projected;
+    int rc = project(json, n_bytes, offsets, n_events, memory_kind, now_ms, &projected);
+    if (rc) return rc;
+    return route(name_space, projected, batch_ms, interval_ms, now_ms, out);
+}
+
+// route() on an already projected table (CommonProcessorFactory.scala:131-328).  Multi-GPU runs call this on the
+// rows a rank received from the key-hash shuffle.
+int dx_flow::route(const std::string& name_space, const DxTableP& projected, long long batch_ms, long long interval_ms, long long now_ms,
+                   dx_result** out) {
+    std::unique_ptr<dx_result> R(new dx_result()); R->flow = this;
+    auto metric = [&](const std::string& k, double v) { R->metric_keys.push_back(k); R->metric_vals.push_back(v); };
+    int rc = DX_OK;
+    std::map<std::string, View> views;
+    Exec X{this, ctx, &views, now_ms * 1000, ""};
     // ---- route() (CPF:131-328)
     metric("Input_Normalized_Events_Count", (double)projected->n_rows);
     NamespaceState& NS = ns[name_space];

@@ -71,6 +71,8 @@ struct dx_flow {
     std::map<std::string, unsigned long long> agg_capacity_hint;  // per statement name
     std::string last_error;
     bool generic_rules_only = false;   // tests: force the bytecode interpreter for rule arrays (conf datax.job.process.gpu.genericrules=true)
+    int project(const uint8_t* json, int64_t n_bytes, const int64_t* offsets, int64_t n_events, int memory_kind, long long now_ms, DxTableP* out);
+    int route(const std::string& name_space, const DxTableP& projected, long long batch_ms, long long interval_ms, long long now_ms, dx_result** out);
     int process(const std::string& name_space, const uint8_t* json, int64_t n_bytes, const int64_t* offsets, int64_t n_events,
                 int memory_kind, long long batch_ms, long long interval_ms, long long now_ms, dx_result** out);
 };

@@ -1,0 +1,154 @@
+// dx_shuffle.cu — K5: key-hash partition + pack, and unpack, around the multi-GPU all-to-all.
+//
+// What it replaces: the Exchange(hashpartitioning(keys)) Spark plans between the partial and final
+// HashAggregateExec of every GROUP BY the flow SQL sends through spark.sql
+// (CommonProcessorFactory.scala:271).  On one 8xB200 box events are decoded and
+// rule-checked where they arrive; rows that feed keyed window aggregates are sent to the GPU that
+// owns hash64(group key) % G, so every key's window cache and state live on exactly one GPU.
+// The exchange itself is one NCCL all-to-all over NVLink, issued by the host harness
+// (torch.distributed.all_to_all_single) on the buffers these kernels fill and read.
+//
+// Record layout on the wire: n_cols x 8 B values (dictionary-free columns only) + 8 B validity bits.
+#include "dx_shuffle.h"
+
+static __device__ __forceinline__ unsigned long long smix64(unsigned long long z) {
+    z += 0x9E3779B97F4A7C15ull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+static __device__ __forceinline__ bool sh_load(const ProgCol& c, long long row, long long& v) {
+    if (c.vmask) {
+        uint32_t m = c.vwidth == 1 ? reinterpret_cast<const uint8_t*>(c.vmask)[row] : reinterpret_cast<const uint32_t*>(c.vmask)[row];
+        if (!((m >> c.vbit) & 1u)) { v = 0; return false; }
+    }
+    v = c.width == 4 ? (long long)reinterpret_cast<const int32_t*>(c.data)[row] : reinterpret_cast<const long long*>(c.data)[row];
+    return true;
+}
+// owner(key) — the same function on every rank: a 64-bit mix over the key values (NULL hashes as a
+// fixed constant), reduced to [0, G) by multiply-shift
+static __device__ __forceinline__ int owner_of(const ShuffleArgs& a, long long row) {
+    unsigned long long h = 0x6A09E667F3BCC909ull;
+    for (int k = 0; k < a.n_keys; k++) {
+        long long v; bool ok = sh_load(a.cols[a.key_idx[k]], row, v);
+        h = smix64(h ^ (ok ? (unsigned long long)v : 0x5BD1E9955BD1E995ull));
+    }
+    return (int)(((h >> 32) * (unsigned long long)a.world) >> 32);
+}
+
+__global__ void __launch_bounds__(256) k5_count(const __grid_constant__ ShuffleArgs a, unsigned long long* counts) {
+    __shared__ unsigned int s_cnt[DX_SHUFFLE_MAX_WORLD];
+    for (int i = threadIdx.x; i < a.world; i += blockDim.x) s_cnt[i] = 0;
+    __syncthreads();
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < a.n_rows; i += (long long)gridDim.x * blockDim.x)
+        atomicAdd(&s_cnt[owner_of(a, i)], 1u);
+    __syncthreads();
+    for (int i = threadIdx.x; i < a.world; i += blockDim.x) if (s_cnt[i]) atomicAdd(&counts[i], (unsigned long long)s_cnt[i]);
+}
+
+// Rows are written grouped by destination; within a destination the order is arbitrary (the
+// consumer is a group-by).  One global atomic per (warp, destination) instead of per row.
+__global__ void __launch_bounds__(256) k5_scatter(const __grid_constant__ ShuffleArgs a, const unsigned long long* base, unsigned long long* cursor,
+                                                  unsigned long long* out) {
+    const int rec_words = a.n_cols + 1;
+    const int lane = threadIdx.x & 31;
+    for (long long i0 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) - lane; i0 < a.n_rows; i0 += (long long)gridDim.x * blockDim.x) {
+        const long long i = i0 + lane;
+        const bool has = i < a.n_rows;
+        const int dst = has ? owner_of(a, i) : -1;
+        const unsigned peers = __match_any_sync(0xffffffffu, dst);
+        const int leader = __ffs(peers) - 1;
+        const int rank_in_group = __popc(peers & ((1u << lane) - 1u));
+        unsigned long long start = 0;
+        if (has && lane == leader) start = atomicAdd(&cursor[dst], (unsigned long long)__popc(peers));
+        start = __shfl_sync(0xffffffffu, start, leader);
+        if (!has) continue;
+        unsigned long long* rec = out + (base[dst] + start + rank_in_group) * rec_words;
+        unsigned long long valid = 0;
+        for (int c = 0; c < a.n_cols; c++) {
+            long long v; if (sh_load(a.cols[c], i, v)) valid |= 1ull << c;
+            rec[c] = (unsigned long long)v;
+        }
+        rec[a.n_cols] = valid;
+    }
+}
+
+__global__ void __launch_bounds__(256) k5_unpack(const unsigned long long* packed, long long n_rows, int n_cols, UnpackCols cols, uint32_t* vmask32) {
+    const int rec_words = n_cols + 1;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_rows; i += (long long)gridDim.x * blockDim.x) {
+        const unsigned long long* rec = packed + i * rec_words;
+        for (int c = 0; c < n_cols; c++) cols.p[c][i] = (long long)rec[c];
+        vmask32[i] = (uint32_t)rec[n_cols];
+    }
+}
+
+static unsigned grid_of(dx_ctx* c, long long n) {
+    long long b = (n + 255) / 256, cap = (long long)c->sm_count * 8;
+    return (unsigned)(b > cap ? cap : (b < 1 ? 1 : b));
+}
+
+int dx_shuffle_pack(dx_ctx* ctx, const DxTable* t, const std::vector<int>& cols, const std::vector<int>& key_pos, int world,
+                    void* packed_dev, int64_t* counts_host) {
+    if (world < 1 || world > DX_SHUFFLE_MAX_WORLD) return ctx->set_error(DX_ERR_ARG, "shuffle: world size out of range");
+    if (cols.empty() || (int)cols.size() > DX_SHUFFLE_MAX_COLS) return ctx->set_error(DX_ERR_ARG, "shuffle: 1..32 columns");
+    ShuffleArgs a; memset(&a, 0, sizeof a);
+    a.n_cols = (int)cols.size(); a.n_keys = (int)key_pos.size(); a.world = world; a.n_rows = t->n_rows;
+    for (size_t c = 0; c < cols.size(); c++) {
+        const DxColumn& col = t->cols[cols[c]];
+        if (col.type == DX_T_STR || col.type == DX_T_FLAGS) return ctx->set_error(DX_ERR_UNSUPPORTED, "shuffle: dictionary-coded and flag columns are rank-local and cannot be sent ('" + col.name + "')");
+        if (!col.data || col.all_null) return ctx->set_error(DX_ERR_UNSUPPORTED, "shuffle: constant column '" + col.name + "'");
+        a.cols[c].data = col.data->p; a.cols[c].vmask = col.vmask ? col.vmask->p : nullptr; a.cols[c].vwidth = col.vwidth; a.cols[c].vbit = col.vbit; a.cols[c].width = dx_type_width(col.type);
+    }
+    for (size_t k = 0; k < key_pos.size(); k++) a.key_idx[k] = key_pos[k];
+    for (int r = 0; r < world; r++) counts_host[r] = 0;
+    if (t->n_rows == 0) return DX_OK;
+    DevBuf st(ctx, 3 * DX_SHUFFLE_MAX_WORLD * 8);
+    unsigned long long* counts = st.as<unsigned long long>();
+    unsigned long long* base = counts + DX_SHUFFLE_MAX_WORLD;
+    unsigned long long* cursor = base + DX_SHUFFLE_MAX_WORLD;
+    DX_CUDA(ctx, cudaMemsetAsync(st.p, 0, 3 * DX_SHUFFLE_MAX_WORLD * 8, ctx->stream));
+    {
+        StageTimer tm(ctx, "k5_count");
+        k5_count<<<grid_of(ctx, t->n_rows), 256, 0, ctx->stream>>>(a, counts);
+        ctx->launches["k5_count"]++;
+    }
+    unsigned long long h[DX_SHUFFLE_MAX_WORLD];
+    DX_CUDA(ctx, cudaMemcpyAsync(h, counts, world * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    DX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    unsigned long long hb[DX_SHUFFLE_MAX_WORLD], acc = 0;
+    for (int r = 0; r < world; r++) { hb[r] = acc; acc += h[r]; counts_host[r] = (int64_t)h[r]; }
+    DX_CUDA(ctx, cudaMemcpyAsync(base, hb, world * 8, cudaMemcpyHostToDevice, ctx->stream));
+    {
+        StageTimer tm(ctx, "k5_scatter");
+        k5_scatter<<<grid_of(ctx, t->n_rows), 256, 0, ctx->stream>>>(a, base, cursor, reinterpret_cast<unsigned long long*>(packed_dev));
+        ctx->launches["k5_scatter"]++;
+    }
+    DX_CUDA(ctx, cudaGetLastError());
+    DX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return DX_OK;
+}
+
+int dx_shuffle_unpack(dx_ctx* ctx, const std::vector<std::string>& names, const std::vector<int>& types, const void* packed_dev, int64_t n_rows,
+                      DxTableP* out) {
+    if (names.empty() || names.size() != types.size() || (int)names.size() > DX_SHUFFLE_MAX_COLS) return ctx->set_error(DX_ERR_ARG, "unpack: 1..32 columns");
+    auto t = std::make_shared<DxTable>(); t->ctx = ctx; t->n_rows = n_rows;
+    DevBufP mask = make_buf(ctx, (size_t)(n_rows > 0 ? n_rows : 1) * 4);
+    UnpackCols uc; memset(&uc, 0, sizeof uc);
+    for (size_t c = 0; c < names.size(); c++) {
+        if (types[c] == DX_T_STR || types[c] == DX_T_FLAGS) return ctx->set_error(DX_ERR_UNSUPPORTED, "unpack: dictionary-coded and flag columns cannot be received");
+        DxColumn col; col.name = names[c]; col.type = types[c];
+        col.data = make_buf(ctx, (size_t)(n_rows > 0 ? n_rows : 1) * 8);
+        col.vmask = mask; col.vwidth = 4; col.vbit = (int)c;
+        uc.p[c] = col.data->as<long long>();
+        t->cols.push_back(col);
+    }
+    if (n_rows > 0) {
+        StageTimer tm(ctx, "k5_unpack");
+        k5_unpack<<<grid_of(ctx, n_rows), 256, 0, ctx->stream>>>(reinterpret_cast<const unsigned long long*>(packed_dev), n_rows, (int)names.size(), uc, mask->as<uint32_t>());
+        ctx->launches["k5_unpack"]++;
+        DX_CUDA(ctx, cudaGetLastError());
+    }
+    DX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    *out = t;
+    return DX_OK;
+}

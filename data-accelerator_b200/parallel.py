@@ -1,0 +1,116 @@
+"""Multi-GPU plumbing for one 8xB200 box: one process per GPU (torchrun), torch.distributed for the
+rendezvous and the all-to-all; the partition/pack/unpack work is done by libdxgpu's K5 kernels.
+
+Stands in for Spark's hash-partitioned shuffle between partial and final aggregation (the Exchange
+behind every GROUP BY executed at CommonProcessorFactory.scala:271): rows are sent to the rank that
+owns hash64(group key) % world; that rank's flow holds the key's window cache and state tables.
+
+`exchange_counts` / `exchange_records` are backend-agnostic (nccl on GPUs; gloo in the CPU tests,
+where the buffers are numpy/torch CPU tensors produced by the oracle's partitioner).
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _native as N
+from .device import Table
+
+vp, i64, i32, cp = C.c_void_p, C.c_int64, C.c_int, C.c_char_p
+P = C.POINTER
+_bound = False
+
+
+def _lib():
+    global _bound
+    L = N.lib()
+    if not _bound:
+        L.dx_flow_project.restype, L.dx_flow_project.argtypes = i32, [vp, vp, i64, vp, i64, i32, i64, P(vp)]
+        L.dx_flow_process_table.restype, L.dx_flow_process_table.argtypes = i32, [vp, cp, vp, i64, i64, i64, P(vp)]
+        L.dx_table_shuffle_pack.restype = i32
+        L.dx_table_shuffle_pack.argtypes = [vp, P(cp), i32, P(cp), i32, i32, vp, P(i64), P(i64)]
+        L.dx_table_from_packed.restype = i32
+        L.dx_table_from_packed.argtypes = [vp, P(cp), P(i32), i32, vp, i64, P(vp)]
+        _bound = True
+    return L
+
+
+def project_device(proc, ptr, n_bytes, n_events, now_ms):
+    """Decode + projection of a device-resident batch -> Table (no windows / SQL)."""
+    L = _lib()
+    t = C.c_void_p()
+    proc.ctx.check(L.dx_flow_project(proc.h, C.c_void_p(ptr), n_bytes, None, n_events, 1, now_ms, C.byref(t)))
+    return Table(proc.ctx, t)
+
+
+def process_table(proc, table, batch_ms, interval_ms, now_ms=None, namespace=""):
+    """route() on a projected table (e.g. rows received from the shuffle)."""
+    from .processor import BatchResult
+    L = _lib()
+    r = C.c_void_p()
+    proc.ctx.check(L.dx_flow_process_table(proc.h, namespace.encode(), table.h, batch_ms, interval_ms,
+                                           batch_ms if now_ms is None else now_ms, C.byref(r)))
+    return BatchResult(proc.ctx, r)
+
+
+def pack_by_key(table, cols, key_cols, world, out_ptr):
+    """K5: fixed records grouped by owner rank into out_ptr (device).  -> (counts[world], rec_bytes)."""
+    L = _lib()
+    c_cols = (cp * len(cols))(*[c.encode() for c in cols])
+    c_keys = (cp * len(key_cols))(*[c.encode() for c in key_cols])
+    counts = (i64 * world)()
+    rec = i64()
+    table.ctx.check(L.dx_table_shuffle_pack(table.h, c_cols, len(cols), c_keys, len(key_cols), world, C.c_void_p(out_ptr), counts, C.byref(rec)))
+    return np.array(list(counts), dtype=np.int64), rec.value
+
+
+def table_from_packed(ctx, names, types, ptr, n_rows):
+    L = _lib()
+    c_names = (cp * len(names))(*[n.encode() for n in names])
+    c_types = (i32 * len(types))(*types)
+    t = C.c_void_p()
+    ctx.check(L.dx_table_from_packed(ctx.h, c_names, c_types, len(names), C.c_void_p(ptr), n_rows, C.byref(t)))
+    return Table(ctx, t)
+
+
+# ---- backend-agnostic exchange (torch.distributed) ---------------------------------------------------
+def exchange_counts(send_counts, group=None):
+    """send_counts[r] = records this rank sends to rank r  ->  recv_counts[r] = records it receives from r."""
+    import torch
+    import torch.distributed as dist
+    dev = "cuda" if dist.get_backend(group) == "nccl" else "cpu"
+    s = torch.as_tensor(np.asarray(send_counts, dtype=np.int64), device=dev)
+    r = torch.empty_like(s)
+    dist.all_to_all_single(r, s, group=group)
+    return r.cpu().numpy()
+
+
+def exchange_records(send_buf, send_counts, recv_counts, rec_words, group=None):
+    """All-to-all-v of fixed-size records.  send_buf: 1-D int64 tensor laid out by destination rank
+    (send_counts[r] records of rec_words words each); returns the received 1-D int64 tensor."""
+    import torch
+    import torch.distributed as dist
+    recv = torch.empty(int(np.sum(recv_counts)) * rec_words, dtype=torch.int64, device=send_buf.device)
+    in_split = [int(c) * rec_words for c in send_counts]
+    out_split = [int(c) * rec_words for c in recv_counts]
+    dist.all_to_all_single(recv, send_buf, output_split_sizes=out_split, input_split_sizes=in_split, group=group)
+    return recv
+
+
+def shuffle_table(table, cols, types, key_cols, group=None):
+    """Full K5 -> all-to-all -> K5 round trip for one table on the current rank (GPU, nccl)."""
+    import torch
+    import torch.distributed as dist
+    world = dist.get_world_size(group)
+    n = table.num_rows
+    rec_words = len(cols) + 1
+    send = torch.empty(max(1, n) * rec_words, dtype=torch.int64, device="cuda")
+    counts, rec_bytes = pack_by_key(table, cols, key_cols, world, send.data_ptr())
+    assert rec_bytes == rec_words * 8
+    torch.cuda.synchronize()
+    recv_counts = exchange_counts(counts, group)
+    recv = exchange_records(send[: n * rec_words], counts, recv_counts, rec_words, group)
+    torch.cuda.synchronize()
+    n_recv = int(recv_counts.sum())
+    out = table_from_packed(table.ctx, cols, types, recv.data_ptr() if n_recv else 0, n_recv)
+    return out, {"sent_records": int(counts.sum()), "received_records": n_recv, "rec_bytes": rec_bytes,
+                 "wire_bytes_out": int((counts.sum() - counts[dist.get_rank(group)]) * rec_bytes)}

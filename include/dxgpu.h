@@ -162,6 +162,28 @@ void dx_result_release(dx_result* r);
  * (StateTableHandler.scala:26-52: metadata.info active=/standby=), for Parquet A/B persistence. */
 int dx_flow_state_export(dx_flow* flow, const char* table, dx_table** out, int* active_is_b);
 
+/* ---- one 8xB200 box: event-range sharding + key-hash shuffle ------------------------------- */
+/* Spark runs every GROUP BY as partial aggregate -> Exchange(hashpartitioning(keys)) -> final aggregate
+ * (the plans behind spark.sql at CommonProcessorFactory.scala:271).  Here each GPU decodes, projects
+ * and rule-checks the events it received; the rows that feed keyed window aggregates are sent to the
+ * GPU that owns hash64(group key) % world, whose flow keeps that key's window cache and state.
+ * The exchange itself is one NCCL all-to-all issued by the host (one process per GPU).           */
+/* project() only (CPF:90-103): decode + projection steps, no window/SQL work. */
+int dx_flow_project(dx_flow* flow, const uint8_t* json, int64_t n_bytes, const int64_t* offsets,
+                    int64_t n_events, int memory_kind, int64_t now_ms, dx_table** out);
+/* route() only (CPF:131-328) on an already projected table, e.g. the rows received from the shuffle. */
+int dx_flow_process_table(dx_flow* flow, const char* name_space, const dx_table* projected,
+                          int64_t batch_time_ms, int64_t interval_ms, int64_t now_ms, dx_result** out);
+/* K5 pack: writes the named columns of every row as fixed records (8 B per column + 8 B validity bits,
+ * *rec_bytes) into packed_dev (device, n_rows * rec_bytes, caller-owned), grouped by owner rank;
+ * counts[r] = rows for rank r.  key_cols must be among cols.  Dictionary-coded columns are rank-local
+ * and are refused.                                                                               */
+int dx_table_shuffle_pack(const dx_table* t, const char* const* cols, int n_cols, const char* const* key_cols,
+                          int n_keys, int world, void* packed_dev, int64_t* counts, int64_t* rec_bytes);
+/* K5 unpack: n_rows received records -> a table with the given column names and DX_TYPE_* types. */
+int dx_table_from_packed(dx_ctx* ctx, const char* const* col_names, const int* col_types, int n_cols,
+                         const void* packed_dev, int64_t n_rows, dx_table** out);
+
 /* ---- host-side artefact parsers, exposed for tests (no GPU needed) ------------------------- */
 /* Canonical text of a statement as the SQL-subset parser understood it; error text on failure. */
 int dx_sql_canonical(const char* sql, char* buf, int64_t cap);

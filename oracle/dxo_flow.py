@@ -1009,3 +1009,28 @@ class Flow:
             datasets[name] = res
         datasets["DataXProcessedInput_Batch"] = projected
         return datasets, metrics
+
+
+# --------------------------------------------------------------------------------------------------
+# multi-GPU key ownership (stands in for Spark's hashpartitioning(keys) Exchange)
+# --------------------------------------------------------------------------------------------------
+_M64 = np.uint64(0xFFFFFFFFFFFFFFFF)
+
+
+def _mix64(z):
+    with np.errstate(over="ignore"):
+        z = (z + np.uint64(0x9E3779B97F4A7C15)) & _M64
+        z = ((z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)) & _M64
+        z = ((z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)) & _M64
+        return z ^ (z >> np.uint64(31))
+
+
+def owner_of(key_cols, world):
+    """key_cols: list of (int64 values, valid bool).  -> owner rank per row, the same function as the
+    product's K5 kernel: 64-bit mix over the key values (NULL = fixed constant), multiply-shift to [0, world)."""
+    n = len(key_cols[0][0])
+    h = np.full(n, 0x6A09E667F3BCC909, dtype=np.uint64)
+    for v, ok in key_cols:
+        x = np.where(ok, v.astype(np.int64).view(np.uint64), np.uint64(0x5BD1E9955BD1E995))
+        h = _mix64(h ^ x)
+    return (((h >> np.uint64(32)) * np.uint64(world)) >> np.uint64(32)).astype(np.int64)
