@@ -277,6 +277,17 @@ int dx_flow_state_export(dx_flow* f, const char* table, dx_table** out, int* act
     return DX_OK;
 }
 
+int dx_flow_add_refdata(dx_flow* f, const char* name, const char* csv_text, char delimiter, int has_header) {
+    if (!f || !name || !csv_text) return DX_ERR_ARG;
+    cudaSetDevice(f->ctx->device);
+    return dx_flow_add_refdata_impl(f, name, csv_text, delimiter ? delimiter : ',', has_header != 0);
+}
+int dx_flow_register_udf(dx_flow* f, const char* name, dx_udf1_fn fn, void* user) {
+    if (!f || !name || !fn) return DX_ERR_ARG;
+    f->udfs[dxsql::upper(name)] = dx_flow::Udf{fn, user};
+    return DX_OK;
+}
+
 // ---- multi-GPU: projection only, route only, key-hash shuffle ------------------------------------
 int dx_flow_project(dx_flow* f, const uint8_t* json, int64_t n_bytes, const int64_t* offsets, int64_t n_events, int memory_kind,
                     int64_t now_ms, dx_table** out) {

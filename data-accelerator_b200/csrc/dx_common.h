@@ -158,6 +158,7 @@ struct DxTable {
     std::string name;
     int64_t n_rows = 0;
     std::vector<DxColumn> cols;
+    std::vector<std::string> col_owner;   // join results: the table (name or alias) each column came from, for qualified references
     bool has_ts_bounds = false;     // window cache: bounds of the flow's timestamp column over this table's rows
     long long ts_min = 0, ts_max = 0;
     int find(const std::string& n) const {

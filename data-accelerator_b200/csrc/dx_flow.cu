@@ -2,6 +2,7 @@
 // Reference call sites are listed in dx_flow.h; each function below names the lines it restates.
 #include "dx_flow.h"
 #include "dx_rules.h"
+#include "dx_join.h"
 #include <cmath>
 #include <sstream>
 
@@ -247,7 +248,7 @@ static ExprP ts_const(long long us) { auto e = std::make_shared<Expr>(); e->kind
 // =======================================================================================
 struct Exec {
     dx_flow* F; dx_ctx* ctx;
-    std::map<std::string, View>* views;
+    ViewMap* views;
     long long now_us;
     std::string stmt_name;
 
@@ -443,7 +444,7 @@ struct Exec {
     int exec_core(const SelectCore& core, DxTableP* out) {
         auto vit = views->find(core.from);
         if (vit == views->end()) return fail(DX_ERR_ARG, "table or view '" + core.from + "' not found");
-        if (!core.joins.empty()) return fail(DX_ERR_UNSUPPORTED, "JOIN is not yet inside the supported SQL subset");
+        if (!core.joins.empty()) return exec_join(core, out);
         const View& v = vit->second;
         if (v.chunks.empty()) return fail(DX_ERR_STATE, "view '" + core.from + "' has no data");
         bool agg = core.distinct || !core.group_by.empty();
@@ -451,8 +452,142 @@ struct Exec {
         return agg ? exec_agg(core, v, out) : exec_plain(core, v, out);
     }
 
+    // ---------------- [INNER] JOIN ... ON a = b [AND c = d] ----------------
+    int materialize_view(const std::string& name, DxTableP* out) {
+        auto vit = views->find(name);
+        if (vit == views->end()) return fail(DX_ERR_ARG, "table or view '" + name + "' not found");
+        const View& v = vit->second;
+        if (v.chunks.size() == 1 && !v.ranged) { *out = v.chunks[0]; return DX_OK; }
+        SelectCore all; all.from = name;
+        SelectItem star; star.expr = std::make_shared<Expr>(); star.expr->kind = EK::Star; all.items.push_back(star);
+        return exec_plain(all, v, out);
+    }
+    // join key as an int64 column: integers as they are, strings parsed to long when the other side is numeric
+    // (Spark casts the string side; unparsable -> NULL, which never matches), string-vs-string through the left dictionary
+    int join_key_column(const DxTable* t, int ci, bool other_is_string, const DxColumn* left_str, DxColumn* out) {
+        const DxColumn& c = t->cols[ci];
+        if (!c.data || c.all_null) return fail(DX_ERR_UNSUPPORTED, "join key '" + c.name + "' is a constant column");
+        if (c.type == DX_T_I64 || c.type == DX_T_TS || c.type == DX_T_BOOL) { *out = c; return DX_OK; }
+        if (c.type != DX_T_STR) return fail(DX_ERR_UNSUPPORTED, "join on a double or flag column");
+        char kb[96]; snprintf(kb, sizeof kb, "@%p/%p/%d", (void*)c.dict.get(), left_str ? (void*)left_str->dict.get() : nullptr, (int)other_is_string);
+        std::shared_ptr<LutCache>& lut = F->luts[std::string("joinkey") + kb];
+        if (!lut) lut = std::make_shared<LutCache>();
+        int rc;
+        if (!other_is_string) {
+            rc = dx_lut_refresh(ctx, lut.get(), c.dict, [](const std::string& s, long long* v) {
+                if (s.empty()) return false;
+                size_t a = 0, b = s.size();
+                while (a < b && isspace((unsigned char)s[a])) a++;
+                while (b > a && isspace((unsigned char)s[b - 1])) b--;
+                if (a == b) return false;
+                size_t i = a; bool neg = false;
+                if (s[i] == '-' || s[i] == '+') { neg = s[i] == '-'; i++; }
+                if (i == b) return false;
+                long long x = 0;
+                for (; i < b; i++) { if (!isdigit((unsigned char)s[i])) return false; x = x * 10 + (s[i] - '0'); }
+                *v = neg ? -x : x; return true;
+            });
+        } else if (left_str) {
+            DxDictP ld = left_str->dict;
+            rc = ld->sync_to_host(); if (rc) return rc;
+            lut->built = 0;   // the left dictionary may have grown: rebuild (reference tables are small)
+            rc = dx_lut_refresh(ctx, lut.get(), c.dict, [&](const std::string& s, long long* v) { int k = ld->lookup_host(s); if (k < 0) return false; *v = k; return true; });
+        } else { *out = c; return DX_OK; }     // the left side of a string-vs-string key: its own codes
+        if (rc) return rc;
+        out->name = c.name; out->type = DX_T_I64; out->is_const = false; out->all_null = false;
+        out->data = make_buf(ctx, (size_t)(t->n_rows > 0 ? t->n_rows : 1) * 8);
+        out->vmask = make_buf(ctx, (size_t)(t->n_rows > 0 ? t->n_rows : 1) * 4); out->vwidth = 4; out->vbit = 0;
+        DX_CUDA(ctx, cudaMemsetAsync(out->vmask->p, 0, (size_t)(t->n_rows > 0 ? t->n_rows : 1) * 4, ctx->stream));
+        return dx_lut_apply(ctx, c, *lut, t->n_rows, nullptr, out->data->p, 8, out->vmask->as<uint32_t>(), 0);
+    }
+    static void flatten_and(const ExprP& e, std::vector<ExprP>* out) {
+        if (e->kind == EK::Bin && e->sval == "AND") { flatten_and(e->args[0], out); flatten_and(e->args[1], out); } else out->push_back(e);
+    }
+    int exec_join(const SelectCore& core, DxTableP* out) {
+        DxTableP left; int rc = materialize_view(core.from, &left); if (rc) return rc;
+        std::string left_name = core.from_alias.empty() ? core.from : core.from_alias;
+        std::vector<std::string> owners;
+        if (left->col_owner.empty()) owners.assign(left->cols.size(), left_name); else owners = left->col_owner;
+        DxTableP acc = left;
+        for (auto& j : core.joins) {
+            DxTableP right; rc = materialize_view(j.table, &right); if (rc) return rc;
+            const std::string right_name = j.alias.empty() ? j.table : j.alias;
+            auto accT = std::make_shared<DxTable>(*acc); accT->col_owner = owners;      // left scope with owners for qualified names
+            BindScope ls; ls.table = accT.get(); ls.now_us = now_us;
+            BindScope rs; rs.table = right.get(); rs.now_us = now_us; rs.qualifiers = {j.table, right_name};
+            std::vector<ExprP> conj; flatten_and(j.on, &conj);
+            if (conj.empty() || conj.size() > DX_JOIN_MAX_KEYS) return fail(DX_ERR_UNSUPPORTED, "JOIN ... ON needs 1 to 4 equalities");
+            JoinSide L, R; memset(&L, 0, sizeof L); memset(&R, 0, sizeof R);
+            std::vector<DxColumn> keep;
+            for (auto& c : conj) {
+                if (c->kind != EK::Bin || c->sval != "=" || c->args[0]->kind != EK::Col || c->args[1]->kind != EK::Col)
+                    return fail(DX_ERR_UNSUPPORTED, "JOIN condition '" + to_string(c) + "' is not column = column");
+                std::string e1, e2;
+                int la = dx_resolve_column(ls, c->args[0]->parts, &e1), rb = dx_resolve_column(rs, c->args[1]->parts, &e2);
+                if (la < 0 || rb < 0) {   // written the other way round
+                    la = dx_resolve_column(ls, c->args[1]->parts, &e1); rb = dx_resolve_column(rs, c->args[0]->parts, &e2);
+                    if (la < 0 || rb < 0) return fail(DX_ERR_ARG, "JOIN condition '" + to_string(c) + "': " + (la < 0 ? e1 : e2));
+                }
+                const bool lstr = accT->cols[la].type == DX_T_STR, rstr = right->cols[rb].type == DX_T_STR;
+                DxColumn lk, rk;
+                rc = join_key_column(accT.get(), la, rstr, nullptr, &lk); if (rc) return rc;
+                rc = join_key_column(right.get(), rb, lstr, lstr ? &accT->cols[la] : nullptr, &rk); if (rc) return rc;
+                auto desc = [](const DxColumn& k) { ProgCol pc; pc.data = k.data->p; pc.vmask = k.vmask ? k.vmask->p : nullptr; pc.vwidth = k.vwidth; pc.vbit = k.vbit; pc.width = dx_type_width(k.type); pc.pad = 0; return pc; };
+                L.keys[L.n_keys++] = desc(lk); R.keys[R.n_keys++] = desc(rk);
+                keep.push_back(lk); keep.push_back(rk);
+            }
+            DevBufP li, ri; int64_t np = 0;
+            rc = dx_join_pairs(ctx, L, acc->n_rows, nullptr, R, right->n_rows, &li, &ri, &np); if (rc) return rc;
+            auto jt = std::make_shared<DxTable>(); jt->ctx = ctx; jt->n_rows = np;
+            MaskAlloc masks(ctx, np);
+            std::vector<std::string> new_owners;
+            int idx = 0;
+            auto add_side = [&](const DxTable* t, const std::vector<std::string>& own, const DevBufP& sel) -> int {
+                for (size_t c = 0; c < t->cols.size(); c++) {
+                    DxColumn oc = t->cols[c];
+                    if (oc.type == DX_T_FLAGS) return fail(DX_ERR_UNSUPPORTED, "JOIN over a rule-flag column");
+                    if (oc.data && !oc.all_null) {
+                        DevBufP nb = make_buf(ctx, (size_t)(np > 0 ? np : 1) * dx_type_width(oc.type));
+                        DxColumn dst = oc; dst.data = nb;
+                        int rc2 = masks.assign(&dst, idx); if (rc2) return rc2;
+                        if (np > 0) { rc2 = dx_gather_column(ctx, oc, np, sel->as<int64_t>(), nb->p, dst.vmask->as<uint32_t>(), dst.vbit); if (rc2) return rc2; }
+                        oc = dst;
+                    }
+                    jt->cols.push_back(oc); new_owners.push_back(own[c]); idx++;
+                }
+                return DX_OK;
+            };
+            rc = add_side(acc.get(), owners, li); if (rc) return rc;
+            std::vector<std::string> rown(right->cols.size(), right_name);
+            rc = add_side(right.get(), rown, ri); if (rc) return rc;
+            DX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+            acc = jt; owners = new_owners;
+        }
+        acc->col_owner = owners;
+        // the rest of the statement runs over the joined rows
+        View jv; jv.chunks.push_back(acc);
+        (*views)["__join"] = jv;
+        SelectCore rest = core; rest.joins.clear(); rest.from = "__join"; rest.from_alias.clear();
+        rc = exec_core(rest, out);
+        views->erase("__join");
+        if (*out) (*out)->col_owner.clear();
+        return rc;
+    }
+
     // ---------------- SELECT without aggregation: filter + project ----------------
     int exec_plain(const SelectCore& core, const View& v, DxTableP* out) {
+        if (v.chunks.size() > 1) {
+            // rule arrays are evaluated over one contiguous table: gather a multi-batch window view first
+            bool has_rules = false;
+            for (auto& it : core.items) { std::vector<ExprP> cds; std::shared_ptr<RuleTable> rt; if (match_rules(it.expr, &cds, &rt)) has_rules = true; }
+            if (has_rules) {
+                SelectCore all; all.from = core.from;
+                SelectItem star; star.expr = std::make_shared<Expr>(); star.expr->kind = EK::Star; all.items.push_back(star);
+                DxTableP m; int rc = exec_plain(all, v, &m); if (rc) return rc;
+                View one; one.chunks.push_back(m);
+                return exec_plain(core, one, out);
+            }
+        }
         struct ChunkSel { DevBufP sel; int64_t n = 0; bool filtered = false; };
         std::vector<ChunkSel> cs(v.chunks.size());
         int64_t total = 0;
@@ -550,6 +685,31 @@ struct Exec {
                 }
                 t->cols.push_back(oc); out_index++; continue;
             }
+            // string-valued results (CONCAT, CAST AS STRING, user functions) and stringToTimestamp
+            {
+                BindScope psc = scope_for(proto, core); psc.qualifiers.push_back("Raw");
+                if (needs_string_engine(e, psc)) {
+                    DxColumn oc; oc.name = item_name(it);
+                    int64_t off = 0; bool first = true; int w = 4;
+                    for (size_t k = 0; k < v.chunks.size(); k++) {
+                        BindScope sc = scope_for(v.chunks[k].get(), core); sc.qualifiers.push_back("Raw");
+                        DxColumn full; int rc = eval_string_full(sc, v.chunks[k].get(), e, stmt_name + "#" + oc.name, &full); if (rc) return rc;
+                        if (first) {
+                            oc.type = full.type; oc.dict = full.dict; w = dx_type_width(full.type);
+                            oc.data = make_buf(ctx, (size_t)(total > 0 ? total : 1) * w);
+                            rc = masks.assign(&oc, out_index); if (rc) return rc;
+                            first = false;
+                        }
+                        if (cs[k].n == 0 || full.all_null) { off += cs[k].n; continue; }
+                        rc = dx_gather_column(ctx, full, cs[k].n, cs[k].filtered ? cs[k].sel->as<int64_t>() : nullptr,
+                                              oc.data->as<uint8_t>() + (size_t)off * w, oc.vmask->as<uint32_t>() + off, oc.vbit);
+                        if (rc) return rc;
+                        off += cs[k].n;
+                    }
+                    DX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+                    t->cols.push_back(oc); out_index++; continue;
+                }
+            }
             // computed column
             {
                 DxColumn oc; oc.name = item_name(it);
@@ -574,6 +734,116 @@ struct Exec {
             }
         }
         *out = t; return DX_OK;
+    }
+
+    // ---------------- string-valued expressions (dictionary columns) ----------------
+    bool is_udf(const ExprP& e) const { return e->kind == EK::Func && F->udfs.count(e->sval) && e->args.size() == 1; }
+    bool string_valued(const ExprP& e, const BindScope& sc) const {
+        if (e->kind == EK::Str) return true;
+        if (e->kind == EK::Col) { std::string er; int ci = dx_resolve_column(sc, e->parts, &er); return ci >= 0 && sc.table->cols[ci].type == DX_T_STR; }
+        if (e->kind == EK::Cast) return e->sval == "string" || e->sval == "varchar";
+        if (e->kind == EK::Func) return e->sval == "CONCAT" || is_udf(e);
+        return false;
+    }
+    bool needs_string_engine(const ExprP& e, const BindScope& sc) const {
+        if (e->kind == EK::Func && e->sval == "STRINGTOTIMESTAMP" && e->args.size() == 1) return true;
+        if (e->kind == EK::Cast && (e->sval == "string" || e->sval == "varchar")) return true;
+        if (e->kind == EK::Func && (e->sval == "CONCAT" || is_udf(e))) return true;
+        return false;
+    }
+    DxDictP result_dict(const std::string& key) {
+        auto it = F->expr_dicts.find(key);
+        if (it != F->expr_dicts.end()) return it->second;
+        auto d = std::make_shared<DxDict>();
+        if (d->init(ctx, 1u << 16, 4u << 20)) return nullptr;
+        F->expr_dicts[key] = d;
+        return d;
+    }
+    // Evaluates a string-engine expression over ALL rows of chunk t (row-aligned result).
+    int eval_string_full(const BindScope& sc, const DxTable* t, const ExprP& e, const std::string& key, DxColumn* out) {
+        const int64_t n = t->n_rows;
+        if (e->kind == EK::Col) {
+            std::string er; int ci = dx_resolve_column(sc, e->parts, &er);
+            if (ci < 0) return fail(DX_ERR_ARG, er);
+            *out = t->cols[ci]; return DX_OK;
+        }
+        DevBufP mask = make_buf(ctx, (size_t)(n > 0 ? n : 1) * 4);
+        DX_CUDA(ctx, cudaMemsetAsync(mask->p, 0, (size_t)(n > 0 ? n : 1) * 4, ctx->stream));
+        out->vmask = mask; out->vwidth = 4; out->vbit = 0; out->is_const = false; out->all_null = false;
+        if (e->kind == EK::Func && (e->sval == "STRINGTOTIMESTAMP" || is_udf(e))) {
+            DxColumn arg; int rc = eval_string_full(sc, t, e->args[0], key + "/arg", &arg); if (rc) return rc;
+            if (arg.type != DX_T_STR) return fail(DX_ERR_UNSUPPORTED, e->sval + " needs a string argument");
+            if (!arg.data) {   // constant argument: materialise through a one-entry dictionary
+                rc = materialize_const(&arg, n, nullptr); if (rc) return rc;
+            }
+            const bool is_ts = e->sval == "STRINGTOTIMESTAMP";
+            char kb[64]; snprintf(kb, sizeof kb, "@%p", (void*)arg.dict.get());
+            std::shared_ptr<LutCache>& lut = F->luts[to_string(e) + kb];
+            if (!lut) lut = std::make_shared<LutCache>();
+            if (is_ts) {
+                rc = dx_lut_refresh(ctx, lut.get(), arg.dict, [](const std::string& s, long long* v) { return dx_string_to_timestamp_us(s, v); });
+            } else {
+                if (!lut->out_dict) { lut->out_dict = std::make_shared<DxDict>(); rc = lut->out_dict->init(ctx, 1u << 16, 4u << 20); if (rc) return rc; }
+                const dx_flow::Udf u = F->udfs[e->sval];
+                DxDictP od = lut->out_dict; dx_ctx* c = ctx; std::string uerr;
+                rc = dx_lut_refresh(ctx, lut.get(), arg.dict, [&](const std::string& s, long long* v) {
+                    std::vector<char> buf(4096); int64_t ol = -1;
+                    if (u.fn(u.user, s.data(), (int64_t)s.size(), buf.data(), (int64_t)buf.size(), &ol) != 0) { uerr = "user function " + e->sval + " failed"; return false; }
+                    if (ol < 0) return false;
+                    int32_t code; if (od->insert_host(std::string(buf.data(), (size_t)ol), &code)) { uerr = c->last_error; return false; }
+                    *v = code; return true;
+                });
+                if (!uerr.empty()) return fail(DX_ERR_STATE, uerr);
+            }
+            if (rc) return rc;
+            out->type = is_ts ? DX_T_TS : DX_T_STR; out->dict = is_ts ? nullptr : lut->out_dict;
+            const int w = is_ts ? 8 : 4;
+            out->data = make_buf(ctx, (size_t)(n > 0 ? n : 1) * w);
+            return dx_lut_apply(ctx, arg, *lut, n, nullptr, out->data->p, w, mask->as<uint32_t>(), 0);
+        }
+        // CONCAT / CAST AS STRING -> per-row byte assembly
+        std::vector<ExprP> args;
+        if (e->kind == EK::Cast) args.push_back(e->args[0]); else args = e->args;
+        if (args.size() > DX_STRBUILD_MAX_PARTS) return fail(DX_ERR_UNSUPPORTED, "CONCAT with more than 16 arguments");
+        StrBuildArgs a; memset(&a, 0, sizeof a);
+        std::string lit; std::vector<DxColumn> keep;
+        for (size_t k = 0; k < args.size(); k++) {
+            StrPart& sp = a.parts[a.n_parts++];
+            const ExprP& x = args[k];
+            if (x->kind == EK::Str) { sp.kind = SP_LIT; sp.off = (uint32_t)lit.size(); sp.len = (uint32_t)x->sval.size(); lit += x->sval; continue; }
+            if (x->kind == EK::Int) { std::string sv = std::to_string(x->ival); sp.kind = SP_LIT; sp.off = (uint32_t)lit.size(); sp.len = (uint32_t)sv.size(); lit += sv; continue; }
+            DxColumn c;
+            if (string_valued(x, sc)) { int rc = eval_string_full(sc, t, x, key + "/" + std::to_string(k), &c); if (rc) return rc; }
+            else if (x->kind == EK::Col) {
+                std::string er; int ci = dx_resolve_column(sc, x->parts, &er);
+                if (ci < 0) return fail(DX_ERR_ARG, er);
+                c = t->cols[ci];
+            } else {   // numeric sub-expression: evaluate it first
+                ExprPrograms P; int rc = dx_compile_expr(ctx, sc, x, &P); if (rc) return rc;
+                DevPrograms D; rc = dx_upload_programs(ctx, &P, &D); if (rc) return rc;
+                c.type = P.result_type[0]; c.data = make_buf(ctx, (size_t)(n > 0 ? n : 1) * 8);
+                c.vmask = make_buf(ctx, (size_t)(n > 0 ? n : 1) * 4); c.vwidth = 4; c.vbit = 0;
+                DX_CUDA(ctx, cudaMemsetAsync(c.vmask->p, 0, (size_t)(n > 0 ? n : 1) * 4, ctx->stream));
+                rc = dx_eval_column(ctx, D, 0, n, nullptr, c.data->p, 8, c.vmask->as<uint32_t>(), 0); if (rc) return rc;
+            }
+            if (c.all_null || c.type == DX_T_NULL) { out->type = DX_T_STR; out->all_null = true; out->data = nullptr; return DX_OK; }
+            if (!c.data) {   // constant column: its text
+                std::string sv = c.type == DX_T_STR ? c.const_s : std::to_string(c.const_i);
+                if (c.type == DX_T_F64) return fail(DX_ERR_UNSUPPORTED, "double to string formatting");
+                sp.kind = SP_LIT; sp.off = (uint32_t)lit.size(); sp.len = (uint32_t)sv.size(); lit += sv; continue;
+            }
+            if (c.type == DX_T_F64 || c.type == DX_T_TS || c.type == DX_T_FLAGS) return fail(DX_ERR_UNSUPPORTED, "only strings and integers can be turned into text here");
+            sp.kind = c.type == DX_T_STR ? SP_STRCOL : SP_I64;
+            sp.col.data = c.data->p; sp.col.vmask = c.vmask ? c.vmask->p : nullptr; sp.col.vwidth = c.vwidth; sp.col.vbit = c.vbit; sp.col.width = dx_type_width(c.type);
+            if (c.type == DX_T_STR) { if (!c.dict) return fail(DX_ERR_STATE, "string column without dictionary"); sp.dict = c.dict->dev; }
+            keep.push_back(c);
+        }
+        DxDictP od = result_dict(key);
+        if (!od) return fail(DX_ERR_CUDA, "dictionary allocation failed");
+        out->type = DX_T_STR; out->dict = od;
+        out->data = make_buf(ctx, (size_t)(n > 0 ? n : 1) * 4);
+        a.n_rows = n; a.sel = nullptr;
+        return dx_strbuild(ctx, a, lit, od, out->data->as<int32_t>(), mask->as<uint32_t>(), 0);
     }
 
     // scalar expression with the two host-assisted built-ins handled here
@@ -738,7 +1008,7 @@ struct Exec {
                     in.range_col.vbit = c.vbit; in.range_col.width = 8;
                     in.range_lo = v.lo_us; in.range_hi = v.hi_us; in.has_range = 1;
                 }
-                std::vector<DevBufP> temps; DevBufP tmask;
+                std::vector<DevBufP> temps; DevBufP tmask; std::vector<DxColumn> string_keys;
                 auto col_desc = [&](const DxColumn& c) { ProgCol pc; pc.data = c.data->p; pc.vmask = c.vmask ? c.vmask->p : nullptr; pc.vwidth = c.vwidth; pc.vbit = c.vbit; pc.width = dx_type_width(c.type); pc.pad = 0; return pc; };
                 auto eval_temp = [&](const ExprP& e, int* type_out, ProgCol* pc) -> int {
                     ExprPrograms P; int rc2 = dx_compile_expr(ctx, sc, e, &P); if (rc2) return rc2;
@@ -764,6 +1034,14 @@ struct Exec {
                             if (key_dict[hashed[hk]] && key_dict[hashed[hk]] != c.dict) return fail(DX_ERR_UNSUPPORTED, "group key dictionaries differ between batches");
                             key_dict[hashed[hk]] = c.dict;
                         }
+                    } else if (needs_string_engine(ks.expr, sc)) {
+                        // CONCAT(...) / CAST AS STRING / user function as a group key (e.g. SELECT DISTINCT ... CONCAT(...) AS Pivot1)
+                        DxColumn full; rc = eval_string_full(sc, ch, ks.expr, stmt_name + "#key" + std::to_string(hashed[hk]), &full); if (rc) return rc;
+                        if (!full.data || full.all_null) return fail(DX_ERR_UNSUPPORTED, "constant string expression as a group key");
+                        string_keys.push_back(full);     // keeps the buffers alive until the kernel has run
+                        in.keys[hk] = col_desc(full); key_type[hashed[hk]] = full.type;
+                        if (key_dict[hashed[hk]] && key_dict[hashed[hk]] != full.dict) return fail(DX_ERR_UNSUPPORTED, "group key dictionaries differ between batches");
+                        key_dict[hashed[hk]] = full.dict;
                     } else { int ty; rc = eval_temp(ks.expr, &ty, &in.keys[hk]); if (rc) return rc; key_type[hashed[hk]] = ty; }
                 }
                 for (size_t vi = 0; vi < val_exprs.size(); vi++) {
@@ -933,6 +1211,52 @@ int dx_flow_build(dx_ctx* ctx, const char* conf_text, const char* schema_json, c
     return DX_OK;
 }
 
+// Reference data: CSV text -> a small device table whose columns are all strings, as
+// CSVUtil.loadCSVReferenceData does (datax-utility CSVUtil.scala:27-29: header option, no schema inference).
+int dx_flow_add_refdata_impl(dx_flow* F, const std::string& name, const std::string& csv, char delim, bool header) {
+    dx_ctx* ctx = F->ctx;
+    std::vector<std::vector<std::string>> rows; std::vector<std::vector<bool>> nulls;
+    {
+        std::string text = strip_bom(csv);
+        std::vector<std::string> cur; std::vector<bool> curn; std::string field; bool inq = false, quoted = false; bool any = false;
+        auto end_field = [&]() { cur.push_back(field); curn.push_back(field.empty() && !quoted); field.clear(); quoted = false; };
+        auto end_row = [&]() { end_field(); if (!(cur.size() == 1 && cur[0].empty() && !any)) { rows.push_back(cur); nulls.push_back(curn); } cur.clear(); curn.clear(); any = false; };
+        for (size_t i = 0; i < text.size(); i++) {
+            char c = text[i];
+            if (inq) { if (c == '"') { if (i + 1 < text.size() && text[i + 1] == '"') { field.push_back('"'); i++; } else inq = false; } else field.push_back(c); continue; }
+            if (c == '"') { inq = true; quoted = true; any = true; }
+            else if (c == delim) { end_field(); any = true; }
+            else if (c == '\n') { if (!field.empty() && field.back() == '\r') field.pop_back(); end_row(); }
+            else { field.push_back(c); any = true; }
+        }
+        if (!field.empty() || !cur.empty()) { if (!field.empty() && field.back() == '\r') field.pop_back(); end_row(); }
+    }
+    if (rows.empty()) return ctx->set_error(DX_ERR_PARSE, "reference data '" + name + "' is empty");
+    std::vector<std::string> names;
+    size_t ncol = rows[0].size();
+    if (header) { names = rows[0]; rows.erase(rows.begin()); nulls.erase(nulls.begin()); }
+    else for (size_t c = 0; c < ncol; c++) names.push_back("_c" + std::to_string(c));
+    auto t = std::make_shared<DxTable>(); t->ctx = ctx; t->n_rows = (int64_t)rows.size(); t->name = name;
+    for (size_t c = 0; c < ncol; c++) {
+        DxColumn col; col.name = names[c]; col.type = DX_T_STR;
+        col.dict = std::make_shared<DxDict>();
+        int rc = col.dict->init(ctx, 1u << 12, 1u << 20); if (rc) return rc;
+        std::vector<int32_t> codes(rows.size(), -1); std::vector<uint32_t> mask(rows.size(), 0);
+        for (size_t r = 0; r < rows.size(); r++) {
+            if (c >= rows[r].size() || nulls[r][c]) continue;       // empty field -> NULL (Spark CSV nullValue default)
+            int32_t code; rc = col.dict->insert_host(rows[r][c], &code); if (rc) return rc;
+            codes[r] = code; mask[r] = 1;
+        }
+        col.data = make_buf(ctx, rows.size() * 4 + 16); col.vmask = make_buf(ctx, rows.size() * 4 + 16); col.vwidth = 4; col.vbit = 0;
+        DX_CUDA(ctx, cudaMemcpyAsync(col.data->p, codes.data(), rows.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
+        DX_CUDA(ctx, cudaMemcpyAsync(col.vmask->p, mask.data(), rows.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
+        DX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        t->cols.push_back(col);
+    }
+    F->ref_tables[name] = t;
+    return DX_OK;
+}
+
 // =======================================================================================
 // one micro-batch: processDataset -> project -> route (CommonProcessorFactory.scala:333-399)
 // =======================================================================================
@@ -942,7 +1266,7 @@ int dx_flow::project(const uint8_t* json, int64_t n_bytes, const int64_t* offset
     DxTableP raw;
     int rc = memory_kind == 1 ? decoder->decode_device(json, n_bytes, offsets, n_events, &raw) : decoder->decode_host(json, n_bytes, offsets, n_events, &raw);
     if (rc) return rc;
-    std::map<std::string, View> views;
+    ViewMap views;
     Exec X{this, ctx, &views, now_ms * 1000, ""};
     DxTableP projected = raw;
     for (auto& step : projections) {
@@ -971,7 +1295,7 @@ int dx_flow::route(const std::string& name_space, const DxTableP& projected, lon
     std::unique_ptr<dx_result> R(new dx_result()); R->flow = this;
     auto metric = [&](const std::string& k, double v) { R->metric_keys.push_back(k); R->metric_vals.push_back(v); };
     int rc = DX_OK;
-    std::map<std::string, View> views;
+    ViewMap views;
     Exec X{this, ctx, &views, now_ms * 1000, ""};
     // ---- route() (CPF:131-328)
     metric("Input_Normalized_Events_Count", (double)projected->n_rows);
@@ -979,7 +1303,18 @@ int dx_flow::route(const std::string& name_space, const DxTableP& projected, lon
     if (windows_enabled) {
         const long long T = batch_ms;
         const long long E = T - watermark_s * 1000, S = E - max_window_s * 1000;
-        View all; all.chunks.push_back(projected);
+        DxTableP proj_w = projected;
+        {   // e.g. `current_timestamp() AS eventTimeStamp` (HomeAutomationLocal.json:290): the window column is a per-batch
+            // constant; give it a buffer so the cached rows carry their own timestamps
+            BindScope bs; bs.table = projected.get();
+            std::string err; int tc = dx_resolve_column(bs, std::vector<std::string>{ts_column}, &err);
+            if (tc < 0) return ctx->set_error(DX_ERR_ARG, "timestamp column: " + err);
+            if (!projected->cols[tc].data && !projected->cols[tc].all_null) {
+                proj_w = std::make_shared<DxTable>(*projected);
+                rc = X.materialize_const(&proj_w->cols[tc], proj_w->n_rows, nullptr); if (rc) return rc;
+            }
+        }
+        View all; all.chunks.push_back(proj_w);
         views["__projected"] = all;
         SelectCore keep; keep.from = "__projected";
         SelectItem star; star.expr = std::make_shared<Expr>(); star.expr->kind = EK::Star; keep.items.push_back(star);
@@ -1022,6 +1357,7 @@ int dx_flow::route(const std::string& name_space, const DxTableP& projected, lon
         View v; v.chunks.push_back(projected); views["DataXProcessedInput"] = v;
     }
     for (auto& kv : state_tables) { View v; v.chunks.push_back(kv.second.phys[kv.second.active]); views[kv.first] = v; }
+    for (auto& kv : ref_tables) { View v; v.chunks.push_back(kv.second); views[kv.first] = v; }
     for (auto& cmd : transform.commands) {
         X.stmt_name = cmd.name;
         DxTableP res; rc = X.exec_statement(cmd.stmt, &res); if (rc) return rc;

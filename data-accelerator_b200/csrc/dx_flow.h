@@ -10,6 +10,7 @@
 #include "dx_expr.h"
 #include "dx_agg.h"
 #include "dx_decode_host.h"
+#include "dx_strings.h"
 #include <set>
 
 struct SqlCommand {
@@ -26,12 +27,21 @@ int dx_parse_transform(const std::string& text, ParsedTransform* out, std::strin
 
 struct RuleTable { std::vector<std::vector<std::pair<std::string, std::string>>> rules; };   // MAP('k','v',...) per rule
 
+struct CiLess {   // Spark resolves table (and column) names case-insensitively (spark.sql.caseSensitive=false)
+    bool operator()(const std::string& a, const std::string& b) const {
+        size_t n = a.size() < b.size() ? a.size() : b.size();
+        for (size_t i = 0; i < n; i++) { int x = tolower((unsigned char)a[i]), y = tolower((unsigned char)b[i]); if (x != y) return x < y; }
+        return a.size() < b.size();
+    }
+};
 struct View {
     std::vector<DxTableP> chunks;
     bool ranged = false;
     std::string ts_col;
     long long lo_us = 0, hi_us = 0;
 };
+
+typedef std::map<std::string, View, CiLess> ViewMap;
 
 struct StateTable {
     std::string name;
@@ -65,11 +75,18 @@ struct dx_flow {
     bool windows_enabled = false;
     std::string ts_column;
     long long watermark_s = 0, max_window_s = 0;
-    std::map<std::string, StateTable> state_tables;
+    std::map<std::string, StateTable, CiLess> state_tables;
+    std::map<std::string, DxTableP, CiLess> ref_tables;           // reference data views (ReferenceDataHandler.scala:42-60)
     std::vector<std::string> outputs;
     std::map<std::string, NamespaceState> ns;
     std::map<std::string, unsigned long long> agg_capacity_hint;  // per statement name
     std::string last_error;
+    // user functions evaluated on the host side of the boundary, once per distinct dictionary entry
+    typedef int (*udf1_fn)(void* user, const char* arg, int64_t arg_len, char* out, int64_t out_cap, int64_t* out_len);
+    struct Udf { udf1_fn fn; void* user; };
+    std::map<std::string, Udf> udfs;                               // upper-cased name -> callback
+    std::map<std::string, std::shared_ptr<LutCache>> luts;        // (expression, dictionary) -> device lookup table
+    std::map<std::string, DxDictP> expr_dicts;                     // (statement, item) -> dictionary of a string-valued result, stable across batches
     bool generic_rules_only = false;   // tests: force the bytecode interpreter for rule arrays (conf datax.job.process.gpu.genericrules=true)
     int project(const uint8_t* json, int64_t n_bytes, const int64_t* offsets, int64_t n_events, int memory_kind, long long now_ms, DxTableP* out);
     int route(const std::string& name_space, const DxTableP& projected, long long batch_ms, long long interval_ms, long long now_ms, dx_result** out);
@@ -82,3 +99,4 @@ int dx_flow_build(dx_ctx* ctx, const char* conf_text, const char* schema_json, c
 // stringToTimestamp restated for dictionary entries (reference: ConcurrentDateFormat.scala:38-62)
 bool dx_string_to_timestamp_us(const std::string& s, long long* out_us);
 long long dx_parse_duration_seconds(const std::string& s, bool* ok);
+int dx_flow_add_refdata_impl(dx_flow* F, const std::string& name, const std::string& csv, char delim, bool header);

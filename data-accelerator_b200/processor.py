@@ -176,6 +176,37 @@ class CommonProcessor:
             now_ms if now_ms is not None else batch_time_ms, C.byref(r)))
         return BatchResult(self.ctx, r)
 
+    def add_refdata(self, name, csv_text, delimiter=",", header=True):
+        """Reference data view (ReferenceDataHandler.scala:42-60): CSV text, all columns strings."""
+        fn = self.L.dx_flow_add_refdata
+        fn.restype, fn.argtypes = C.c_int, [C.c_void_p, C.c_char_p, C.c_char_p, C.c_char, C.c_int]
+        self.ctx.check(fn(self.h, name.encode(), csv_text.encode("utf-8"), delimiter.encode()[:1], 1 if header else 0))
+
+    def register_udf(self, name, func):
+        """A String -> String user function (UDF1), e.g. datax.sample.udf.UdfHelloWorld.  func(str) -> str | None.
+        Called by the library once per distinct argument value."""
+        proto = C.CFUNCTYPE(C.c_int, C.c_void_p, C.POINTER(C.c_char), C.c_int64, C.POINTER(C.c_char), C.c_int64, C.POINTER(C.c_int64))
+
+        def thunk(user, arg, arg_len, out, out_cap, out_len):
+            try:
+                r = func(None if arg_len < 0 else C.string_at(arg, arg_len).decode("utf-8"))
+                if r is None:
+                    out_len[0] = -1
+                    return 0
+                b = r.encode("utf-8")
+                if len(b) > out_cap:
+                    return 1
+                C.memmove(out, b, len(b))
+                out_len[0] = len(b)
+                return 0
+            except Exception:
+                return 1
+        cb = proto(thunk)
+        self._udf_keepalive = getattr(self, "_udf_keepalive", []) + [cb]
+        fn = self.L.dx_flow_register_udf
+        fn.restype, fn.argtypes = C.c_int, [C.c_void_p, C.c_char_p, proto, C.c_void_p]
+        self.ctx.check(fn(self.h, name.encode(), cb, None))
+
     def state_table(self, name):
         t, b = C.c_void_p(), C.c_int()
         self.ctx.check(self.L.dx_flow_state_export(self.h, name.encode(), C.byref(t), C.byref(b)))
@@ -206,4 +237,12 @@ class CommonProcessorFactory:
         schema = read(rel(d["datax.job.input.default.blobschemafile"]))
         steps = [read(rel(p)) for p in d.get("datax.job.process.projection", "").split(";") if p]
         transform = read(rel(d["datax.job.process.transform"])) if d.get("datax.job.process.transform") else ""
-        return CommonProcessor(ctx, conf_text, schema, steps, transform)
+        proc = CommonProcessor(ctx, conf_text, schema, steps, transform)
+        # reference data views (ReferenceDataHandler.scala:25-60)
+        pre = "datax.job.input.default.referencedata."
+        for name in sorted({k[len(pre):].split(".")[0] for k in d if k.startswith(pre)}):
+            path = d.get(pre + name + ".path")
+            if path and d.get(pre + name + ".format", "csv").lower() == "csv":
+                proc.add_refdata(name, read(rel(path)), d.get(pre + name + ".delimiter", ","),
+                                 d.get(pre + name + ".header", "true").lower() == "true")
+        return proc

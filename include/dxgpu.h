@@ -162,6 +162,18 @@ void dx_result_release(dx_result* r);
  * (StateTableHandler.scala:26-52: metadata.info active=/standby=), for Parquet A/B persistence. */
 int dx_flow_state_export(dx_flow* flow, const char* table, dx_table** out, int* active_is_b);
 
+/* Reference data (ReferenceDataHandler.scala:42-60, CSVUtil.scala:27-29): the CSV text of
+ * datax.job.input.default.referencedata.<name>.path becomes a view <name> whose columns are all
+ * strings; joins against numeric event columns cast the string side, as Spark does.  Call after
+ * dx_flow_create and before the first batch.                                                      */
+int dx_flow_add_refdata(dx_flow* flow, const char* name, const char* csv_text, char delimiter, int has_header);
+/* User functions (datax-core extension/DynamicUDF.scala:12-46, SparkJarLoader.scala:82-155): a
+ * String -> String function callable from the flow SQL.  User code cannot run on the GPU: the library
+ * calls fn once per DISTINCT argument value (dictionary entry) and keeps the results as a device lookup
+ * table.  Return 0 on success; *out_len = -1 yields NULL; the result is copied out of `out` (out_cap bytes). */
+typedef int (*dx_udf1_fn)(void* user, const char* arg, int64_t arg_len, char* out, int64_t out_cap, int64_t* out_len);
+int dx_flow_register_udf(dx_flow* flow, const char* name, dx_udf1_fn fn, void* user);
+
 /* ---- one 8xB200 box: event-range sharding + key-hash shuffle ------------------------------- */
 /* Spark runs every GROUP BY as partial aggregate -> Exchange(hashpartitioning(keys)) -> final aggregate
  * (the plans behind spark.sql at CommonProcessorFactory.scala:271).  Here each GPU decodes, projects

@@ -380,8 +380,15 @@ class P:
         self.expect_kw("FROM")
         frm = self.take()[1]
         frm_alias = self.alias()
-        if self.kw("JOIN") or self.kw("INNER"):
-            raise NotImplementedError("JOIN")
+        joins = []
+        while self.kw("JOIN") or (self.kw("INNER") and self.kw("JOIN", 1)):
+            if self.kw("INNER"):
+                self.take()
+            self.take()
+            jt = self.take()[1]
+            ja = self.alias()
+            self.expect_kw("ON")
+            joins.append((jt, ja, self.expr()))
         where = self.expr() if self.accept_kw("WHERE") else None
         group = []
         if self.kw("GROUP"):
@@ -390,7 +397,7 @@ class P:
             group.append(self.expr())
             while self.accept_op(","):
                 group.append(self.expr())
-        return {"distinct": distinct, "items": items, "from": frm, "alias": frm_alias, "where": where, "group": group}
+        return {"distinct": distinct, "items": items, "from": frm, "alias": frm_alias, "where": where, "group": group, "joins": joins}
 
     def statement(self):
         sel = [self.select_core()]
@@ -422,21 +429,26 @@ class Tab:
         return [c[0] for c in self.cols]
 
     def find(self, parts, qualifiers=()):
-        def exact(n):
-            hits = [c for c in self.cols if c[0] == n]
+        # Spark resolves names case-insensitively (spark.sql.caseSensitive=false)
+        low = [p.lower() for p in parts]
+        owners = getattr(self, "owners", None)
+        if owners and len(low) >= 2 and low[0] in [o.lower() for o in owners]:
+            n = ".".join(low[1:])
+            hits = [c for c, o in zip(self.cols, owners) if o.lower() == low[0] and c[0].lower() == n]
             return hits[0] if len(hits) == 1 else None
-        for strip in range(len(parts)):
-            if strip > 0 and (strip > 1 or parts[0] not in qualifiers):
+
+        def exact(n):
+            hits = [c for c in self.cols if c[0].lower() == n]
+            return hits[0] if len(hits) == 1 else None
+        quals = [q.lower() for q in qualifiers]
+        for strip in range(len(low)):
+            if strip > 0 and (strip > 1 or low[0] not in quals):
                 break
-            n = ".".join(parts[strip:])
+            n = ".".join(low[strip:])
             h = exact(n)
             if h:
                 return h
-            if "." not in n:
-                hits = [c for c in self.cols if "." in c[0] and c[0].rsplit(".", 1)[1] == n]
-                if len(hits) == 1:
-                    return hits[0]
-        return None
+        return None      # a bare name never reaches into a struct: `deviceId` is not `deviceDetails.deviceId`
 
     def take(self, idx):
         t = Tab(len(idx))
@@ -551,6 +563,13 @@ class Ev:
                     with np.errstate(all="ignore"):
                         v = np.where(np.isnan(v), 0, np.clip(np.trunc(v), -9.2233720368547758e18, 9.2233720368547758e18)).astype(np.int64)
                 return "long", v.astype(np.int64), ok
+            if to in ("string", "varchar"):
+                if ty == "string":
+                    return ty, v, ok
+                out = np.empty(n, dtype=object)
+                for i in range(n):
+                    out[i] = str(int(v[i])).encode() if ok[i] else None
+                return "string", out, ok
             if to == "timestamp":
                 if ty == "ts":
                     return ty, v, ok
@@ -662,6 +681,28 @@ class Ev:
             assert args[0][0] == "str" and args[0][1].lower() == "second"
             ty, v, ok = self.ev(args[1])
             return "ts", v - (v % 1_000_000), ok
+        if fn == "CONCAT" or fn in UDFS:
+            vals = [self.ev(a) for a in args]
+            out = np.empty(n, dtype=object)
+            ok = np.ones(n, bool)
+            for i in range(n):
+                parts = []
+                for ty, v, k in vals:
+                    if not k[i]:
+                        parts = None
+                        break
+                    parts.append(v[i] if ty == "string" else str(int(v[i])).encode())
+                if fn == "CONCAT":
+                    if parts is None:
+                        ok[i] = False
+                        out[i] = None
+                    else:
+                        out[i] = b"".join(parts)
+                else:
+                    r = UDFS[fn](None if parts is None else parts[0].decode("utf-8"))
+                    ok[i] = r is not None
+                    out[i] = None if r is None else r.encode("utf-8")
+            return "string", out, ok
         if fn == "STRINGTOTIMESTAMP":
             ty, v, ok = self.ev(args[0])
             out = np.zeros(n, np.int64)
@@ -673,6 +714,9 @@ class Ev:
                         out[i], ok2[i] = r, True
             return "ts", out, ok2
         raise NotImplementedError(fn)
+
+
+UDFS = {}      # upper-cased name -> python callable(str | None) -> str | None (the flow's registered user functions)
 
 
 AGGS = {"COUNT", "SUM", "MIN", "MAX", "AVG"}
@@ -739,7 +783,96 @@ def _key_codes(cols):
     return inv.reshape(-1), len(first)
 
 
+class CiDict(dict):
+    """Table names are case-insensitive."""
+    def __getitem__(self, k):
+        return dict.__getitem__(self, k.lower())
+
+    def __setitem__(self, k, v):
+        dict.__setitem__(self, k.lower(), v)
+
+    def __contains__(self, k):
+        return dict.__contains__(self, k.lower())
+
+
+def _flatten_and(e, out):
+    if e[0] == "bin" and e[1] == "AND":
+        _flatten_and(e[2], out)
+        _flatten_and(e[3], out)
+    else:
+        out.append(e)
+
+
+def _to_long(b):
+    try:
+        t = b.decode("utf-8").strip()
+        if not re.fullmatch(r"[+-]?\d+", t):
+            return None
+        return int(t)
+    except Exception:
+        return None
+
+
+def _join(core, views, now_us):
+    """[INNER] JOIN ... ON a = b [AND c = d]: NULL keys never match; a string key against a numeric one is
+    cast to the numeric type (unparsable -> NULL), as Spark's implicit cast does."""
+    left = views[core["from"]]
+    lname = core["alias"] or core["from"]
+    owners = list(getattr(left, "owners", None) or [lname] * len(left.cols))
+    acc = left
+    for jt, ja, on in core["joins"]:
+        right = views[jt]
+        rname = ja or jt
+        acc.owners = owners
+        conj = []
+        _flatten_and(on, conj)
+        lkeys, rkeys = [], []
+        for c in conj:
+            assert c[0] == "bin" and c[1] == "=" and c[2][0] == "col" and c[3][0] == "col", c
+            a, b = acc.find(c[2][1]), right.find(c[3][1], [jt, rname])
+            if a is None or b is None:
+                a, b = acc.find(c[3][1]), right.find(c[2][1], [jt, rname])
+            assert a is not None and b is not None, c
+            lk = [(x if k else None) for x, k in zip(a[2], a[3])]
+            rk = [(x if k else None) for x, k in zip(b[2], b[3])]
+            if a[1] != "string" and b[1] == "string":
+                rk = [None if x is None else _to_long(x) for x in rk]
+            elif a[1] == "string" and b[1] != "string":
+                lk = [None if x is None else _to_long(x) for x in lk]
+            lkeys.append([None if x is None else (x if isinstance(x, bytes) else int(x)) for x in lk])
+            rkeys.append([None if x is None else (x if isinstance(x, bytes) else int(x)) for x in rk])
+        index = {}
+        for r in range(right.n):
+            k = tuple(col[r] for col in rkeys)
+            if None not in k:
+                index.setdefault(k, []).append(r)
+        li, ri = [], []
+        for l in range(acc.n):
+            k = tuple(col[l] for col in lkeys)
+            if None in k:
+                continue
+            for r in index.get(k, ()):
+                li.append(l)
+                ri.append(r)
+        li, ri = np.array(li, dtype=np.int64), np.array(ri, dtype=np.int64)
+        out = Tab(len(li))
+        for c in acc.cols:
+            out.add(c[0], c[1], c[2][li] if c[2] is not None else None, c[3][li])
+        for c in right.cols:
+            out.add(c[0], c[1], c[2][ri] if c[2] is not None else None, c[3][ri])
+        owners = owners + [rname] * len(right.cols)
+        acc = out
+    acc.owners = owners
+    return acc
+
+
 def exec_core(core, views, now_us):
+    if core.get("joins"):
+        v2 = CiDict(views)
+        v2["__join"] = _join(core, views, now_us)
+        rest = dict(core, joins=[], alias=None)
+        rest["from"] = "__join"
+        return exec_core(rest, v2, now_us)
     src = views[core["from"]]
     q = [core["from"]] + ([core["alias"]] if core["alias"] else []) + ["Raw"]
     ev = Ev(src, q, now_us)
@@ -898,7 +1031,7 @@ def exec_statement(sql, views, now_us):
     u = concat_tabs(tabs)
     if all(alls):
         return u
-    v2 = dict(views)
+    v2 = CiDict(views)
     v2["__union"] = u
     return exec_core({"distinct": True, "items": [(("star", []), None)], "from": "__union", "alias": None, "where": None, "group": []}, v2, now_us)
 
@@ -946,6 +1079,25 @@ class Flow:
         self.max_window = max(self.windows.values()) if self.enabled else 0
         self.past = {}        # namespace -> {batch_ms: Tab}
 
+    def add_refdata(self, name, csv_text, delimiter=",", header=True):
+        """ReferenceDataHandler / CSVUtil.scala:27-29: every column is a string; empty field -> NULL."""
+        import csv
+        import io
+        rows = [r for r in csv.reader(io.StringIO(csv_text.lstrip("\ufeff")), delimiter=delimiter) if r]
+        names = rows[0] if header else ["_c%d" % i for i in range(len(rows[0]))]
+        body = rows[1:] if header else rows
+        t = Tab(len(body))
+        for c, nm in enumerate(names):
+            v = np.empty(len(body), dtype=object)
+            ok = np.zeros(len(body), bool)
+            for r, row in enumerate(body):
+                if c < len(row) and row[c] != "":
+                    v[r], ok[r] = row[c].encode("utf-8"), True
+            t.add(nm, "string", v, ok)
+        if not hasattr(self, "refdata"):
+            self.refdata = {}
+        self.refdata[name] = t
+
     def decode(self, data, offsets=None):
         d = dxo.decode(self.schema, data, offsets)
         n = len(d["__rowok"])
@@ -964,7 +1116,9 @@ class Flow:
             core = {"distinct": False, "items": step, "from": "Raw", "alias": None, "where": None, "group": []}
             projected = exec_core(core, {"Raw": projected}, now_us)
         metrics["Input_Normalized_Events_Count"] = float(projected.n)
-        views = {}
+        views = CiDict()
+        for rn, rt in getattr(self, 'refdata', {}).items():
+            views[rn] = rt
         if self.enabled:
             T = batch_ms
             E = T - self.watermark * 1000
