@@ -225,3 +225,24 @@ def test_bucketed_and_generic_rule_kernels_agree(dx, ctx):
         assert_same_rows(a, ro["Rules"], dx, ordered=True)
     fast.close()
     slow.close()
+
+
+def test_string_to_timestamp_projection_on_reference_sample_events(dx, ctx):
+    """The cloud IoT sample's projection (Local.Test/Resource/projection.txt:1-2) over the reference's own sample
+    events (string eventTime 'MM/dd/yyyy HH:mm:ss'): stringToTimestamp is evaluated per dictionary entry."""
+    import os
+    data = open(os.path.join(os.path.dirname(__file__), "golden", "reference_sample_events.ndjson"), "rb").read()
+    schema = dxo.iot_schema_json(1, event_time_type="string")
+    proj = "stringToTimestamp(Raw.deviceDetails.eventTime) AS eventTimeStamp\nRaw.*\n"
+    tr = """--DataXQuery--
+ByHour = SELECT hour(eventTimeStamp) AS h, deviceDetails.deviceType, COUNT(*) AS Count, MAX(eventTimeStamp) AS Last FROM DataXProcessedInput GROUP BY hour(eventTimeStamp), deviceDetails.deviceType
+--DataXQuery--
+Named = SELECT CONCAT(deviceDetails.deviceType, '-', deviceDetails.deviceId) AS name, CAST(deviceDetails.homeId AS String) AS home, eventTimeStamp FROM DataXProcessedInput WHERE deviceDetails.status = 1
+"""
+    g, o = both(dx, ctx, dx.flowgen.conf_text("s2t"), schema, [proj], tr)
+    extra = b'{"deviceDetails":{"deviceId":9,"deviceType":"Heating","eventTime":"not a time","homeId":1,"status":1}}\n' \
+            b'{"deviceDetails":{"deviceId":9,"deviceType":null,"eventTime":"2018-08-10 22:55:03","homeId":null,"status":1}}\n' \
+            b'{"deviceDetails":{"deviceId":9,"deviceType":"Heating","eventTime":"08/10/2018 22:55:3","homeId":1,"status":1}}\n'
+    check_batch(dx, g, o, data + extra, T0)
+    check_batch(dx, g, o, data[:2000] + extra, T0 + I)     # second batch: lookup tables extend, dictionaries persist
+    g.close()
