@@ -189,6 +189,7 @@ int dx_table_column_to_host(const dx_table* h, int col, void* data, uint8_t* val
 int dx_table_dict_size(const dx_table* h, int col, int64_t* n_codes) {
     const DxTable* t = T(h);
     if (col >= 0 && col < (int)t->cols.size() && t->cols[col].type == DX_T_STR && !t->cols[col].data) { *n_codes = 1; return DX_OK; }
+    if (col >= 0 && col < (int)t->cols.size() && t->cols[col].type == DX_T_STR && !t->cols[col].dict) { *n_codes = 0; return DX_OK; }   // no string seen yet
     if (col < 0 || col >= (int)t->cols.size() || !t->cols[col].dict) return t->ctx->set_error(DX_ERR_ARG, "not a dictionary column");
     cudaSetDevice(t->ctx->device);
     int rc = t->cols[col].dict->sync_to_host();

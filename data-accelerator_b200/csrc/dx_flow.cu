@@ -297,6 +297,12 @@ struct Exec {
         for (auto& a : e->args) if (contains_agg(a)) return true;
         return false;
     }
+    static bool has_column_ref(const ExprP& e) {
+        if (!e) return false;
+        if (e->kind == EK::Col || e->kind == EK::Star) return true;
+        for (auto& a : e->args) if (has_column_ref(a)) return true;
+        return false;
+    }
     static bool is_literal(const ExprP& e) { return e->kind == EK::Int || e->kind == EK::Dec || e->kind == EK::Str || e->kind == EK::Null || e->kind == EK::Bool; }
 
     static std::string item_name(const SelectItem& it) {
@@ -855,7 +861,57 @@ struct Exec {
     struct KeySpec { ExprP expr; int src_col = -1; bool is_const = false; DxColumn const_col; };
     struct AggSpec { std::string func; ExprP arg; bool star = false; int val_index = -1; int acc = -1, acc_cnt = -1; int arg_type = 0; };
 
+    // COUNT(DISTINCT x) [with other decomposable aggregates]: two levels of the ordinary hash aggregation —
+    // first per (keys, x), then per keys counting the non-NULL x of the distinct pairs.
+    int exec_count_distinct(const SelectCore& core, const View& v, DxTableP* out) {
+        ExprP dx; 
+        for (auto& it : core.items) if (is_agg_func(it.expr) && it.expr->distinct) {
+            if (it.expr->sval != "COUNT" || it.expr->args.size() != 1) return fail(DX_ERR_UNSUPPORTED, "only COUNT(DISTINCT x) is supported");
+            if (dx && to_string(dx) != to_string(it.expr->args[0])) return fail(DX_ERR_UNSUPPORTED, "COUNT(DISTINCT) over two different expressions");
+            dx = it.expr->args[0];
+        }
+        auto col = [](const std::string& n) { auto e = std::make_shared<Expr>(); e->kind = EK::Col; e->parts = {n}; return e; };
+        auto agg = [](const std::string& f, ExprP a) { auto e = std::make_shared<Expr>(); e->kind = EK::Func; e->sval = f; if (a) e->args = {a}; else e->star_arg = true; return e; };
+        SelectCore inner; inner.from = core.from; inner.from_alias = core.from_alias; inner.where = core.where;
+        SelectCore outer; outer.from = "__distinct";
+        for (size_t k = 0; k < core.group_by.size(); k++) {
+            std::string nm = "__k" + std::to_string(k);
+            inner.items.push_back({core.group_by[k], nm}); inner.group_by.push_back(core.group_by[k]);
+            outer.group_by.push_back(col(nm));
+        }
+        inner.items.push_back({dx, "__dx"}); inner.group_by.push_back(dx);
+        int na = 0;
+        for (auto& it : core.items) {
+            SelectItem oi; oi.alias = item_name(it);
+            const ExprP& e = it.expr;
+            if (is_agg_func(e)) {
+                if (e->distinct) oi.expr = agg("COUNT", col("__dx"));
+                else {
+                    std::string nm = "__a" + std::to_string(na++);
+                    const std::string& f = e->sval;
+                    if (f == "AVG") return fail(DX_ERR_UNSUPPORTED, "AVG next to COUNT(DISTINCT)");
+                    inner.items.push_back({e, nm});
+                    oi.expr = agg((f == "COUNT") ? "SUM" : f, col(nm));
+                }
+            } else {
+                int hit = -1;
+                for (size_t k = 0; k < core.group_by.size(); k++) if (to_string(core.group_by[k]) == to_string(e)) hit = (int)k;
+                if (hit >= 0) oi.expr = col("__k" + std::to_string(hit));
+                else if (is_literal(e)) oi.expr = e;
+                else return fail(DX_ERR_ARG, "'" + to_string(e) + "' is neither aggregated nor in GROUP BY");
+            }
+            outer.items.push_back(oi);
+        }
+        DxTableP mid; int rc = exec_agg(inner, v, &mid); if (rc) return rc;
+        View mv; mv.chunks.push_back(mid);
+        const std::string saved = stmt_name; stmt_name = saved + "#distinct";
+        rc = exec_agg(outer, mv, out);
+        stmt_name = saved;
+        return rc;
+    }
+
     int exec_agg(const SelectCore& core, const View& v, DxTableP* out) {
+        for (auto& it : core.items) if (is_agg_func(it.expr) && it.expr->distinct) return exec_count_distinct(core, v, out);
         const DxTable* proto = v.chunks[0].get();
         BindScope psc = scope_for(proto, core);
         // expand the select list ('*' only makes sense with DISTINCT)
@@ -899,7 +955,7 @@ struct Exec {
         }
         // aggregates and the mapping of every select item
         std::vector<AggSpec> aggs; std::vector<ExprP> val_exprs; std::vector<AggAccDesc> accs;
-        struct ItemMap { int key = -1; int agg = -1; bool literal = false; };
+        struct ItemMap { int key = -1; int agg = -1; bool literal = false; bool folded = false; };
         std::vector<ItemMap> imap(items.size());
         auto add_acc = [&](int kind, int col) { for (size_t a = 0; a < accs.size(); a++) if (accs[a].kind == kind && accs[a].col == col) return (int)a; accs.push_back({kind, col}); return (int)accs.size() - 1; };
         for (size_t i = 0; i < items.size(); i++) {
@@ -927,6 +983,7 @@ struct Exec {
                 }
                 if (hit >= 0) imap[i].key = hit;
                 else if (is_literal(e)) imap[i].literal = true;
+                else if (!has_column_ref(e)) imap[i].folded = true;     // foldable: DATE_TRUNC('second', current_timestamp()) ...
                 else return fail(DX_ERR_ARG, "'" + key + "' is neither aggregated nor in GROUP BY");
             }
         }
@@ -1095,6 +1152,16 @@ struct Exec {
         for (size_t i = 0; i < items.size(); i++) {
             DxColumn oc; oc.name = item_name(items[i]);
             if (imap[i].literal) { oc = literal_column(items[i].expr, oc.name); t->cols.push_back(oc); continue; }
+            if (imap[i].folded) {
+                ExprPrograms P; int rc = dx_compile_expr(ctx, psc, items[i].expr, &P); if (rc) return rc;
+                DevPrograms D; rc = dx_upload_programs(ctx, &P, &D); if (rc) return rc;
+                oc.type = P.result_type[0] == DX_T_NULL ? DX_T_I64 : P.result_type[0];
+                oc.data = make_buf(ctx, (size_t)(n_out > 0 ? n_out : 1) * 8);
+                rc = masks.assign(&oc, (int)i); if (rc) return rc;
+                rc = dx_eval_column(ctx, D, 0, n_out, nullptr, oc.data->p, 8, oc.vmask->as<uint32_t>(), oc.vbit); if (rc) return rc;
+                DX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+                t->cols.push_back(oc); continue;
+            }
             if (imap[i].key >= 0) {
                 KeySpec& ks = keys[imap[i].key];
                 if (ks.is_const) { DxColumn c = ks.const_col; c.name = oc.name; t->cols.push_back(c); continue; }

@@ -731,6 +731,15 @@ def _has_agg(e):
         _has_agg(y) for x in e[1:] if isinstance(x, list) for y in x if isinstance(y, tuple))
 
 
+def _has_col(e):
+    if not isinstance(e, tuple):
+        return False
+    if e[0] in ("col", "star"):
+        return True
+    return any(_has_col(x) for x in e[1:] if isinstance(x, tuple)) or any(
+        _has_col(y) for x in e[1:] if isinstance(x, list) for y in x if isinstance(y, tuple))
+
+
 def _item_name(e, alias):
     if alias:
         return alias
@@ -948,7 +957,14 @@ def exec_core(core, views, now_us):
         if e[0] == "func" and e[1] in AGGS:
             _, fn, args, distinct, star = e
             if distinct:
-                raise NotImplementedError("COUNT(DISTINCT)")
+                assert fn == "COUNT"
+                ty, v, ok = ev.ev(args[0])
+                xk, _ = _key_codes([(ty, v, ok)])
+                pairs = np.unique(np.stack([gid[ok], xk[ok]], axis=1), axis=0) if ok.any() else np.zeros((0, 2), np.int64)
+                cnt = np.zeros(ng, np.int64)
+                np.add.at(cnt, pairs[:, 0], 1)
+                out.add(name, "long", cnt, np.ones(ng, bool))
+                continue
             if star or (fn == "COUNT" and args and args[0][0] in ("int", "str", "dec", "bool")):
                 cnt = np.zeros(ng, np.int64)
                 np.add.at(cnt, gid, 1)
@@ -1008,7 +1024,7 @@ def exec_core(core, views, now_us):
                 hit = kc
                 break
         if hit is None:
-            if e[0] in ("int", "dec", "str", "bool", "null"):
+            if not _has_col(e):      # literals and foldable expressions (current_timestamp() ...) need no grouping
                 ty, v, ok = Ev(Tab(ng), q, now_us).ev(e)
                 out.add(name, ty, v, ok)
                 continue
