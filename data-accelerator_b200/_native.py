@@ -62,6 +62,8 @@ def lib():
         "dx_table_num_columns": (i32, [vp]),
         "dx_table_column_name": (cp, [vp, i32]),
         "dx_table_column_type": (i32, [vp, i32]),
+        "dx_table_column_nesting": (i32, [vp, i32, P(cp)]),
+        "dx_table_column_path": (cp, [vp, i32, i32]),
         "dx_table_find_column": (i32, [vp, cp]),
         "dx_table_flag_words": (i32, [vp, i32]),
         "dx_table_column_device": (i32, [vp, i32, P(vp), P(vp), P(i32), P(i32)]),

@@ -130,6 +130,18 @@ const char* dx_table_column_name(const dx_table* h, int col) {
     const DxTable* t = T(h);
     return (col >= 0 && col < (int)t->cols.size()) ? t->cols[col].name.c_str() : nullptr;
 }
+int dx_table_column_nesting(const dx_table* h, int col, const char** kinds) {
+    const DxTable* t = T(h);
+    if (col < 0 || col >= (int)t->cols.size()) return -1;
+    if (kinds) *kinds = t->cols[col].nest_kinds.c_str();
+    return (int)t->cols[col].nest_path.size();
+}
+const char* dx_table_column_path(const dx_table* h, int col, int level) {
+    const DxTable* t = T(h);
+    if (col < 0 || col >= (int)t->cols.size()) return nullptr;
+    const auto& p = t->cols[col].nest_path;
+    return (level >= 0 && level < (int)p.size()) ? p[level].c_str() : nullptr;
+}
 int dx_table_column_type(const dx_table* h, int col) {
     const DxTable* t = T(h);
     return (col >= 0 && col < (int)t->cols.size()) ? t->cols[col].type : 0;

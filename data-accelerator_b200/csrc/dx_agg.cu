@@ -24,6 +24,8 @@ static __device__ __forceinline__ bool load_val(const ProgCol& c, long long row,
     return true;
 }
 
+// KMAX bounds the unrolled key loops (4, 8 or 16) so that narrow group-bys do not carry the registers of wide ones
+template <int KMAX>
 __global__ void __launch_bounds__(256) k3_hash_agg(const __grid_constant__ AggTableDev T, const __grid_constant__ AggInput in) {
     const int nk = T.n_keys, na = T.n_accs, sw = T.slot_words;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < in.n_rows; i += (long long)gridDim.x * blockDim.x) {
@@ -33,10 +35,10 @@ __global__ void __launch_bounds__(256) k3_hash_agg(const __grid_constant__ AggTa
             long long t;
             if (!load_val(in.range_col, row, t) || t < in.range_lo || t >= in.range_hi) continue;
         }
-        long long kv[DX_AGG_MAX_KEYS];
+        long long kv[KMAX];
         unsigned long long nullbits = 0, h = 0x2545F4914F6CDD1Dull;
 #pragma unroll
-        for (int k = 0; k < DX_AGG_MAX_KEYS; k++) {
+        for (int k = 0; k < KMAX; k++) {
             if (k < nk) {
                 long long v; bool ok = load_val(in.keys[k], row, v);
                 kv[k] = v; if (!ok) nullbits |= 1ull << k;
@@ -53,12 +55,12 @@ __global__ void __launch_bounds__(256) k3_hash_agg(const __grid_constant__ AggTa
             if (cur == tag) {
                 bool same = (s[nk + 1] == nullbits);
 #pragma unroll
-                for (int k = 0; k < DX_AGG_MAX_KEYS; k++) if (k < nk) same = same && ((long long)s[1 + k] == kv[k]);
+                for (int k = 0; k < KMAX; k++) if (k < nk) same = same && ((long long)s[1 + k] == kv[k]);
                 if (same) { slot = s; break; }
             } else if (cur == 0ull) {
                 if (atomicCAS(s, 0ull, 1ull) == 0ull) {
 #pragma unroll
-                    for (int k = 0; k < DX_AGG_MAX_KEYS; k++) if (k < nk) s[1 + k] = (unsigned long long)kv[k];
+                    for (int k = 0; k < KMAX; k++) if (k < nk) s[1 + k] = (unsigned long long)kv[k];
                     s[nk + 1] = nullbits;
                     for (int a = 0; a < na; a++) {
                         const int kind = T.accs[a].kind;
@@ -118,7 +120,7 @@ __global__ void k3_extract(const AggTableDev T, unsigned long long capacity, uns
 
 int AggTable::init(dx_ctx* c, int n_keys, int n_vals, const std::vector<AggAccDesc>& accs, unsigned long long capacity_pow2) {
     ctx = c;
-    if (n_keys > DX_AGG_MAX_KEYS) return c->set_error(DX_ERR_UNSUPPORTED, "more than 8 group-by keys");
+    if (n_keys > DX_AGG_MAX_KEYS) return c->set_error(DX_ERR_UNSUPPORTED, "more than 16 group-by keys");
     if ((int)accs.size() > DX_AGG_MAX_ACCS || n_vals > DX_AGG_MAX_ACCS) return c->set_error(DX_ERR_UNSUPPORTED, "more than 16 aggregate accumulators");
     unsigned long long cap = 64; while (cap < capacity_pow2) cap <<= 1;
     capacity = cap;
@@ -144,7 +146,9 @@ int AggTable::update(const AggInput& in) {
     long long capb = (long long)ctx->sm_count * 8; if (blocks > capb) blocks = capb;
     ctx->counters["k3_rows"] += in.n_rows;
     StageTimer tm(ctx, "k3_hash_agg");
-    k3_hash_agg<<<(unsigned)blocks, 256, 0, ctx->stream>>>(dev, in);
+    if (dev.n_keys <= 4) k3_hash_agg<4><<<(unsigned)blocks, 256, 0, ctx->stream>>>(dev, in);
+    else if (dev.n_keys <= 8) k3_hash_agg<8><<<(unsigned)blocks, 256, 0, ctx->stream>>>(dev, in);
+    else k3_hash_agg<16><<<(unsigned)blocks, 256, 0, ctx->stream>>>(dev, in);
     ctx->launches["k3_hash_agg"]++;
     DX_CUDA(ctx, cudaGetLastError());
     return DX_OK;

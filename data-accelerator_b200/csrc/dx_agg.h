@@ -10,7 +10,7 @@
 
 enum DxAcc : int32_t { ACC_COUNT_STAR = 1, ACC_COUNT = 2, ACC_SUM_I = 3, ACC_SUM_F = 4, ACC_MIN_I = 5, ACC_MAX_I = 6, ACC_MIN_F = 7, ACC_MAX_F = 8 };
 
-#define DX_AGG_MAX_KEYS 8
+#define DX_AGG_MAX_KEYS 16
 #define DX_AGG_MAX_ACCS 16
 
 struct AggAccDesc { int32_t kind; int32_t col; };   // col: index into the value column list (-1 for COUNT(*))

@@ -151,6 +151,10 @@ struct DxColumn {
     DxDictP dict;            // STR columns
     int32_t flag_words = 0;  // FLAGS columns: uint32 words per row
     std::shared_ptr<void> aux; // FLAGS: the static rule table
+    // leaf of a MAP(...) / STRUCT(...) select item: the key path below the item's alias and one
+    // 'm' (map) or 's' (struct) per level; the column's name is alias + "." + path joined by "."
+    std::vector<std::string> nest_path;
+    std::string nest_kinds;
 };
 
 struct DxTable {

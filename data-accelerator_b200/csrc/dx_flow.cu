@@ -380,7 +380,7 @@ struct Exec {
         auto t = std::make_shared<DxTable>(); t->ctx = ctx; t->n_rows = total;
         MaskAlloc masks(ctx, total);
         for (size_t c = 0; c < nc; c++) {
-            DxColumn oc; oc.name = parts[0]->cols[c].name;
+            DxColumn oc; oc.name = parts[0]->cols[c].name; oc.nest_path = parts[0]->cols[c].nest_path; oc.nest_kinds = parts[0]->cols[c].nest_kinds;
             int type = DX_T_NULL; DxDictP dict; bool all_const_same = true;
             for (auto& p : parts) {
                 const DxColumn& pc = p->cols[c];
@@ -399,6 +399,11 @@ struct Exec {
             (void)all_const_same;
             oc.type = type;
             if (type == DX_T_NULL) { oc.all_null = true; t->cols.push_back(oc); continue; }
+            if (type == DX_T_STR && !dict) {
+                // only constant strings on every side (e.g. the rule constants of two aggregate rules): one shared dictionary
+                dict = std::make_shared<DxDict>();
+                int rcd = dict->init(ctx, 1024, 1 << 16); if (rcd) return rcd;
+            }
             oc.dict = dict;
             int w = dx_type_width(type);
             oc.data = make_buf(ctx, (size_t)(total > 0 ? total : 1) * w);
@@ -447,7 +452,57 @@ struct Exec {
         return DX_OK;
     }
 
+    // MAP('k', v, ...) / STRUCT(v AS n, ...) / NAMED_STRUCT('n', v, ...) select items — the alert shaping
+    // CodegenRules emits (pivots / aggs / result / RuleObject) — become one column per leaf, named
+    // <alias>.<key>..., with the key path and container kinds kept on the column for the sink.
+    static bool is_nested_ctor(const ExprP& e) {
+        return e->kind == EK::Func && (e->sval == "MAP" || e->sval == "STRUCT" || e->sval == "NAMED_STRUCT");
+    }
+    struct NestLeaf { std::vector<std::string> path; std::string kinds; };
+    int flatten_nested(const ExprP& e, const std::string& prefix, std::vector<std::string>& path, std::string& kinds,
+                       std::vector<SelectItem>* items, std::map<std::string, NestLeaf>* nest) {
+        const bool is_struct = e->sval == "STRUCT";
+        if (!is_struct && e->args.size() % 2) return fail(DX_ERR_ARG, e->sval + " needs key/value pairs");
+        for (size_t i = 0; i < e->args.size(); i += is_struct ? 1 : 2) {
+            std::string key; ExprP val;
+            if (is_struct) {
+                val = e->args[i];
+                key = !val->alias.empty() ? val->alias : (val->kind == EK::Col ? val->parts.back() : "col" + std::to_string(i + 1));
+            } else {
+                if (e->args[i]->kind != EK::Str) return fail(DX_ERR_UNSUPPORTED, e->sval + " keys must be string literals");
+                key = e->args[i]->sval; val = e->args[i + 1];
+            }
+            path.push_back(key); kinds.push_back(is_struct ? 's' : 'm');
+            const std::string name = prefix + "." + key;
+            if (is_nested_ctor(val)) { int rc = flatten_nested(val, name, path, kinds, items, nest); if (rc) return rc; }
+            else {
+                SelectItem it; it.expr = val; it.alias = name; items->push_back(it);
+                NestLeaf nl; nl.path = path; nl.kinds = kinds; (*nest)[name] = nl;
+            }
+            path.pop_back(); kinds.pop_back();
+        }
+        return DX_OK;
+    }
+
     int exec_core(const SelectCore& core, DxTableP* out) {
+        bool nested = false;
+        for (auto& it : core.items) if (is_nested_ctor(it.expr)) nested = true;
+        if (nested) {
+            SelectCore flat = core; flat.items.clear();
+            std::map<std::string, NestLeaf> nest;
+            for (auto& it : core.items) {
+                if (!is_nested_ctor(it.expr)) { flat.items.push_back(it); continue; }
+                if (it.alias.empty()) return fail(DX_ERR_UNSUPPORTED, "a MAP/STRUCT select item needs an alias");
+                std::vector<std::string> path; std::string kinds;
+                int rc = flatten_nested(it.expr, it.alias, path, kinds, &flat.items, &nest); if (rc) return rc;
+            }
+            int rc = exec_core(flat, out); if (rc) return rc;
+            for (auto& c : (*out)->cols) {
+                auto f = nest.find(c.name);
+                if (f != nest.end()) { c.nest_path = f->second.path; c.nest_kinds = f->second.kinds; }
+            }
+            return DX_OK;
+        }
         auto vit = views->find(core.from);
         if (vit == views->end()) return fail(DX_ERR_ARG, "table or view '" + core.from + "' not found");
         if (!core.joins.empty()) return exec_join(core, out);
@@ -634,7 +689,7 @@ struct Exec {
             if (!src_cols.empty()) {
                 for (int ci : src_cols) {
                     DxColumn oc = proto->cols[ci];
-                    if (e->kind == EK::Col) oc.name = item_name(it);
+                    if (e->kind == EK::Col) { oc.name = item_name(it); oc.nest_path.clear(); oc.nest_kinds.clear(); }
                     if (!(oc.all_null || !oc.data || zero_copy)) {
                         const int words = oc.type == DX_T_FLAGS ? oc.flag_words : 1;
                         const int w = oc.type == DX_T_FLAGS ? 4 : dx_type_width(oc.type);
@@ -1022,7 +1077,7 @@ struct Exec {
         if (accs.empty()) accs.push_back({ACC_COUNT_STAR, -1});
         std::vector<int> hashed;   // keys that take part in hashing
         for (size_t k2 = 0; k2 < keys.size(); k2++) if (!keys[k2].is_const) hashed.push_back((int)k2);
-        if ((int)hashed.size() > DX_AGG_MAX_KEYS) return fail(DX_ERR_UNSUPPORTED, "more than 8 group-by keys");
+        if ((int)hashed.size() > DX_AGG_MAX_KEYS) return fail(DX_ERR_UNSUPPORTED, "more than 16 group-by keys");
 
         // selections per chunk
         struct ChunkSel { DevBufP sel; int64_t n = 0; bool filtered = false; };
@@ -1177,6 +1232,13 @@ struct Exec {
             else { oc.type = (a.func == "SUM" && a.arg_type != DX_T_F64) ? DX_T_I64 : a.arg_type; if (a.func != "SUM" && a.arg_type == DX_T_TS) oc.type = DX_T_TS; rc = finalize(2, aptr[a.acc], aptr[a.acc_cnt], 0, &oc, (int)i); }
             if (rc) return rc;
             t->cols.push_back(oc);
+        }
+        // DISTINCT / GROUP BY over MAP/STRUCT leaves keeps their shaping
+        for (size_t i = 0; i < items.size() && i < t->cols.size(); i++) {
+            DxColumn& oc = t->cols[i]; oc.nest_path.clear(); oc.nest_kinds.clear();
+            if (items[i].expr->kind != EK::Col) continue;
+            std::string err; int ci = dx_resolve_column(psc, items[i].expr->parts, &err);
+            if (ci >= 0 && proto->cols[ci].name == oc.name) { oc.nest_path = proto->cols[ci].nest_path; oc.nest_kinds = proto->cols[ci].nest_kinds; }
         }
         DX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
         *out = t; return DX_OK;

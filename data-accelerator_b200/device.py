@@ -84,9 +84,9 @@ class Table:
         self.L = ctx.L
 
     def release(self):
-        if self.h:
+        if self.h and self.ctx.h:      # handles die with their context: never touch one after dx_ctx_destroy
             self.L.dx_table_release(self.h)
-            self.h = None
+        self.h = None
 
     __del__ = release
 
@@ -101,6 +101,13 @@ class Table:
 
     def column_type(self, col):
         return self.L.dx_table_column_type(self.h, self._idx(col))
+
+    def nesting(self, col):
+        """(key path, container kinds) of a MAP/STRUCT leaf column; ([], "") for an ordinary column."""
+        i = self._idx(col)
+        kinds = C.c_char_p()
+        n = self.L.dx_table_column_nesting(self.h, i, C.byref(kinds))
+        return [self.L.dx_table_column_path(self.h, i, k).decode() for k in range(n)], (kinds.value or b"").decode()
 
     def _idx(self, col):
         if isinstance(col, int):

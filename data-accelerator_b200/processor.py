@@ -110,9 +110,9 @@ class BatchResult:
         return Table(self.ctx, t)
 
     def release(self):
-        if self.h:
+        if self.h and self.ctx.h:      # handles die with their context: never touch one after dx_ctx_destroy
             self.L.dx_result_release(self.h)
-            self.h = None
+        self.h = None
 
     __del__ = release
 
@@ -145,9 +145,9 @@ class CommonProcessor:
         self.h = h
 
     def close(self):
-        if self.h:
+        if self.h and self.ctx.h:
             self.L.dx_flow_destroy(self.h)
-            self.h = None
+        self.h = None
 
     def process_json(self, data, batch_time_ms, batch_interval_ms, output_partition_time_ms=None, namespace="",
                      now_ms=None, offsets=None, n_events=-1) -> BatchResult:

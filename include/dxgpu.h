@@ -109,6 +109,13 @@ int64_t dx_table_num_rows(const dx_table* t);
 int dx_table_num_columns(const dx_table* t);
 const char* dx_table_column_name(const dx_table* t, int col);
 int dx_table_column_type(const dx_table* t, int col);
+/* Leaves of a MAP('k', v, ...) / STRUCT(v AS n, ...) select item (the alert shaping CodegenRules emits:
+ * DataX.Flow.CodegenRules.Tests/CGenMixedAlert.txt:45-68 "pivots"/"aggs"/"result", CGenNoCode.txt:75-99) are
+ * stored as one column per leaf named <alias>.<key>[.<key>...].  Returns the number of levels below the alias
+ * (0 for an ordinary column, -1 for a bad index); *kinds gets one 'm' or 's' per level, dx_table_column_path the
+ * key at that level, so a sink can rebuild the nested value (map keys may themselves contain dots).          */
+int dx_table_column_nesting(const dx_table* t, int col, const char** kinds);
+const char* dx_table_column_path(const dx_table* t, int col, int level);
 int dx_table_find_column(const dx_table* t, const char* name);      /* -1 if absent */
 int dx_table_flag_words(const dx_table* t, int col);                /* FLAGS columns */
 /* Raw device views: data pointer (NULL for constant columns), validity mask pointer with element

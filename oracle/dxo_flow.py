@@ -284,7 +284,8 @@ class P:
     def arg(self):
         e = self.expr()
         if self.kw("AS"):
-            self.take(); self.take()
+            self.take()
+            return ("named", e, self.take()[1])      # STRUCT(x AS n)
         return e
 
     def mul(self):
@@ -421,6 +422,7 @@ class Tab:
     def __init__(self, n):
         self.n = n
         self.cols = []
+        self.nest = {}       # MAP/STRUCT leaves: column name -> (key path, 'm'/'s' per level)
 
     def add(self, name, ty, vals, valid):
         self.cols.append([name, ty, vals, valid])
@@ -454,6 +456,7 @@ class Tab:
         t = Tab(len(idx))
         for name, ty, v, ok in self.cols:
             t.add(name, ty, v[idx] if v is not None else None, ok[idx])
+        t.nest = dict(getattr(self, "nest", {}))
         return t
 
 
@@ -469,11 +472,15 @@ def concat_tabs(tabs):
         vals, oks = [], []
         for t in tabs:
             _, cty, v, ok = t.cols[c]
+            if cty not in ("null", ty) and not {cty, ty} <= {"long", "bool"}:
+                # Spark would widen (e.g. timestamp + string -> string); the cast is outside the restated subset
+                raise ValueError(f"UNION column '{name}' mixes types {ty} and {cty}")
             if cty == "null" or v is None:
                 v = np.zeros(t.n, dtype=object if ty in ("string", "rules") else (np.float64 if ty == "double" else np.int64))
             vals.append(v)
             oks.append(ok)
         out.add(name, ty, np.concatenate(vals) if vals else np.zeros(0), np.concatenate(oks) if oks else np.zeros(0, bool))
+    out.nest = dict(tabs[0].nest)
     return out
 
 
@@ -513,6 +520,8 @@ class Ev:
             if c[1] == "null":
                 return "null", np.zeros(n, np.int64), np.zeros(n, bool)
             return c[1], c[2], c[3]
+        if k == "named":
+            return self.ev(e[1])
         if k == "int":
             return self.const("long", e[1])
         if k == "dec":
@@ -750,6 +759,36 @@ def _item_name(e, alias):
     return repr(e)
 
 
+_NESTED = ("MAP", "STRUCT", "NAMED_STRUCT")
+
+
+def _flatten_nested(e, prefix, path, kinds, items, nest):
+    """MAP('k', v, ..) / STRUCT(v AS n, ..) / NAMED_STRUCT('n', v, ..) -> one item per leaf named prefix.k1.k2...;
+    nest[name] = (key path, 'm'/'s' per level).  (CodegenRules' alert shaping: pivots / aggs / result / RuleObject.)"""
+    fn, args = e[1], e[2]
+    step = 1 if fn == "STRUCT" else 2
+    if step == 2 and len(args) % 2:
+        raise ValueError(fn + " needs key/value pairs")
+    for i in range(0, len(args), step):
+        if fn == "STRUCT":
+            val = args[i]
+            if val[0] == "named":
+                key, val = val[2], val[1]
+            else:
+                key = val[1][-1] if val[0] == "col" else "col%d" % (i + 1)
+        else:
+            if args[i][0] != "str":
+                raise ValueError(fn + " keys must be string literals")
+            key, val = args[i][1], args[i + 1]
+        name = prefix + "." + key
+        p2, k2 = path + [key], kinds + ("s" if fn == "STRUCT" else "m")
+        if val[0] == "func" and val[1] in _NESTED:
+            _flatten_nested(val, name, p2, k2, items, nest)
+        else:
+            items.append((val, name))
+            nest[name] = (p2, k2)
+
+
 def _rule_shape(e):
     """filterNull(Array(IF(c, MAP(...), NULL), ...)) | IF(c, MAP(...), NULL) -> [(cond, {k: v})]"""
     def one(x):
@@ -876,6 +915,21 @@ def _join(core, views, now_us):
 
 
 def exec_core(core, views, now_us):
+    if any(e[0] == "func" and e[1] in _NESTED for e, _ in core["items"]):
+        items, nest = [], {}
+        for e, alias in core["items"]:
+            if e[0] == "func" and e[1] in _NESTED:
+                if not alias:
+                    raise ValueError("a MAP/STRUCT select item needs an alias")
+                _flatten_nested(e, alias, [], "", items, nest)
+            else:
+                items.append((e, alias))
+        out = exec_core(dict(core, items=items), views, now_us)
+        out.nest = dict(getattr(out, "nest", {}))
+        for c in out.cols:
+            if c[0] in nest:
+                out.nest[c[0]] = nest[c[0]]
+        return out
     if core.get("joins"):
         v2 = CiDict(views)
         v2["__join"] = _join(core, views, now_us)
@@ -912,6 +966,9 @@ def exec_core(core, views, now_us):
                     cols = [c for c in src.cols if c[0].startswith(prefix)]
                 for c in cols:
                     out.add(*c)
+                    if c[0] in getattr(src, "nest", {}):
+                        out.nest = dict(getattr(out, "nest", {}))
+                        out.nest[c[0]] = src.nest[c[0]]
                 continue
             rs = _rule_shape(e)
             if rs:
@@ -1034,8 +1091,11 @@ def exec_core(core, views, now_us):
             out.add(name, ty, v[first], ok[first])
         else:
             out.add(name, ty, v[:0], ok[:0])
-    if not gexprs and src.n == 0:
-        pass
+    for (e, alias), c in zip(items, out.cols):      # DISTINCT / GROUP BY over MAP/STRUCT leaves keeps their shaping
+        if e[0] == "col":
+            sc = src.find(e[1], q)
+            if sc is not None and sc[0] == c[0] and sc[0] in src.nest:
+                out.nest[c[0]] = src.nest[sc[0]]
     return out
 
 
