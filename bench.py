@@ -42,6 +42,17 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def traffic_of(kernel, events_per_launch):
+    """DRAM bytes per launch of `kernel` from the committed ncu --set full capture (profiles/ncu_traffic.json holds
+    bytes per event of the captured launch), scaled to the events one launch of this run processes; None if absent."""
+    p = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    try:
+        d = json.load(open(p))
+        return round(d[kernel]["dram_bytes_per_event"] * events_per_launch)
+    except (OSError, KeyError, ValueError):
+        return None
+
+
 class ClockSampler:
     """nvidia-smi clocks/throttle reasons sampled DURING the timed region."""
 
@@ -195,7 +206,8 @@ def run_ours(args):
     dominant = (k2_name, k2_bytes, k2_ms) if k2_ms >= k1_ms else ("k1_decode", k1_bytes, k1_ms)
     achieved = dominant[1] / (dominant[2] / 1e3) / 1e9 if dominant[2] > 0 else 0.0
     roofline = {"bound": "hbm", "kernel": dominant[0], "achieved": round(achieved, 2), "peak": peak, "unit": "GB/s",
-                "frac": round(achieved / peak, 4), "traffic": None, "peak_source": peak_src,
+                "frac": round(achieved / peak, 4), "traffic": traffic_of(dominant[0], per_chunk), "alg_bytes_per_launch": int(dominant[1] // N_CHUNKS),
+                "launch_ms": round(dominant[2] / N_CHUNKS, 4), "peak_source": peak_src,
                 "kernels": {"k1_decode": {"ms_per_step": round(k1_ms, 3), "launches": k1_n, "alg_bytes": k1_bytes,
                                           "gbs": round(k1_bytes / max(k1_ms, 1e-9) / 1e6, 2)},
                             k2_name: {"ms_per_step": round(k2_ms, 3), "launches": k2_n, "alg_bytes": k2_bytes,
