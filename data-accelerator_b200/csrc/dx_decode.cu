@@ -97,8 +97,6 @@ __global__ void __launch_bounds__(K1_NT, K1_MIN_CTAS) k1_decode(const __grid_con
     extern __shared__ __align__(128) uint8_t smem[];
     constexpr int TILE_BYTES = K1_T + K1_OVL + K1_PAD;                     // one staged tile (multiple of 16)
     uint16_t* s_starts = reinterpret_cast<uint16_t*>(smem + K1_STAGES * TILE_BYTES);   // K1_SC + 2
-    uint32_t* s_lits = reinterpret_cast<uint32_t*>(s_starts + K1_SC + 2);  // DX_LITS_BYTES
-    DSeg* s_segs = reinterpret_cast<DSeg*>(s_lits + DX_LITS_BYTES / 4);    // DX_MAX_SEGS
     __shared__ uint64_t s_bar[K1_STAGES];
     __shared__ long long s_tile;
     __shared__ long long s_rowbase;
@@ -108,9 +106,6 @@ __global__ void __launch_bounds__(K1_NT, K1_MIN_CTAS) k1_decode(const __grid_con
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const DSchemaDev* S = a.schema;
-    const int n_segs = S->n_segs;
-    for (int i = tid; i < DX_LITS_BYTES / 4; i += K1_NT) s_lits[i] = S->lits[i];
-    for (int i = tid; i < DX_MAX_SEGS; i += K1_NT) s_segs[i] = S->segs[i];
     if (tid == 0) { for (int k = 0; k < K1_STAGES; k++) mbar_init(&s_bar[k], 1); fence_mbar_init(); }
     __syncthreads();
 
@@ -297,7 +292,7 @@ __global__ void __launch_bounds__(K1_NT, K1_MIN_CTAS) k1_decode(const __grid_con
                     const bool overflow = has && o.row >= a.max_rows;
                     if (overflow) c_err |= DXF_ROW_OVERFLOW;
                     const bool live = has && !overflow;
-                    bool ok = fast_record_warp(buf, st, en, live && in_smem, s_segs, n_segs, s_lits, o);
+                    bool ok = fast_record_warp(buf, st, en, live && in_smem, a, o);
                     if (live) {
                         if (ok) c_fast++;
                         else if (in_smem) ok = g_record(buf + st, buf + en, S, o);
@@ -346,7 +341,7 @@ __global__ void __launch_bounds__(K1_NT, K1_MIN_CTAS) k1_decode(const __grid_con
                     }
                 }
                 RowSink o; o.a = &a; o.row = r; o.valid = 0; o.err = 0;
-                bool ok = fast_record_warp(buf, st, en_f, has && in_smem, s_segs, n_segs, s_lits, o);
+                bool ok = fast_record_warp(buf, st, en_f, has && in_smem, a, o);
                 if (has) {
                     if (ok) c_fast++;
                     else if (in_smem) ok = g_record(buf + st, buf + en, S, o);
@@ -401,7 +396,7 @@ __global__ void k1_count_records(const uint8_t* bytes, long long n, unsigned lon
 // host side
 // =======================================================================================
 static size_t k1_smem_bytes() {
-    return K1_STAGES * (K1_T + K1_OVL + K1_PAD) + (K1_SC + 2) * 2 + DX_LITS_BYTES + DX_MAX_SEGS * sizeof(DSeg) + 64;
+    return K1_STAGES * (K1_T + K1_OVL + K1_PAD) + (K1_SC + 2) * 2 + 64;
 }
 
 static int map_spark_type(const std::string& t) {
@@ -536,6 +531,7 @@ int dx_decoder::decode_device(const uint8_t* json_dev, int64_t n_bytes, const in
     const int mw = (nl <= 7) ? 1 : 4;
     DevBufP mask = make_buf(c, (size_t)(n_events > 0 ? n_events : 1) * mw);
     DecodeArgs a; memset(&a, 0, sizeof a);
+    a.n_segs = hs.n_segs; memcpy(a.segs, hs.segs, sizeof a.segs); memcpy(a.lits, hs.lits, sizeof a.lits);
     for (int k = 0; k < nl; k++) {
         DxColumn col;
         col.name = leaf_names[k]; col.type = hs.leaf_type[k];
@@ -677,6 +673,7 @@ int dx_decoder::decode_noalloc(const uint8_t* json_dev, int64_t n_bytes, int64_t
         return DX_OK;
     }
     DecodeArgs a; memset(&a, 0, sizeof a);
+    a.n_segs = hs.n_segs; memcpy(a.segs, hs.segs, sizeof a.segs); memcpy(a.lits, hs.lits, sizeof a.lits);
     uintptr_t addr = reinterpret_cast<uintptr_t>(json_dev);
     a.skew = (uint32_t)(addr & 15);
     a.base_al = reinterpret_cast<const uint8_t*>(addr - a.skew);

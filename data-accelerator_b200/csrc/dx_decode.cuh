@@ -56,7 +56,13 @@ struct DecodeArgs {
     unsigned long long* tile_state;
     unsigned int* tile_counter;
     DecodeStats* stats;
+    // the record template (copy of DSchemaDev's): kernel parameters sit in the constant bank, so the segment
+    // descriptors and literal words are read through the uniform data path instead of per-lane shared loads
+    int32_t n_segs, pad_;
+    DSeg segs[DX_MAX_SEGS];
+    uint32_t lits[DX_LITS_BYTES / 4];
 };
+static_assert(sizeof(DecodeArgs) <= 4096, "kernel parameter block");
 
 // ---------------------------------------------------------------------------------------
 static __device__ __forceinline__ uint64_t dx_mix64(uint64_t z) {

@@ -64,15 +64,15 @@ static __device__ __forceinline__ int parse_digit_run(const uint8_t* buf, uint32
 }
 
 // One record, executed by ALL lanes of the warp together (lanes without a record pass has=false).
-static __device__ bool fast_record_warp(const uint8_t* buf, uint32_t pos, uint32_t end, bool has, const DSeg* segs, int n_segs,
-                                        const uint32_t* lits, RowSink& o) {
+static __device__ __forceinline__ bool fast_record_warp(const uint8_t* buf, uint32_t pos, uint32_t end, bool has, const DecodeArgs& a, RowSink& o) {
     bool ok = has;
     o.valid = 0;
+    const int n_segs = a.n_segs;
     for (int si = 0; si < n_segs; si++) {
         __syncwarp();
-        const DSeg sg = segs[si];
+        const DSeg sg = a.segs[si];                      // warp-uniform: constant-bank loads
         if (ok) {
-            const uint32_t* lw = lits + (sg.lit_off >> 2);
+            const uint32_t* lw = a.lits + (sg.lit_off >> 2);
             const uint32_t L = sg.lit_len, nw = L >> 2, sh = (pos & 3u) << 3;
             const uint32_t* wp = reinterpret_cast<const uint32_t*>(buf + (pos & ~3u));
             uint32_t lo = wp[0], diff = 0, hi;
