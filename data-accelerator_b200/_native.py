@@ -8,7 +8,9 @@ import os
 import re
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libdxgpu.so")
+# DXGPU_LIB: development override used by the tuning sweeps (tools/build_variant.sh) to load a differently tuned build
+# of the same library; unset, the in-tree build is the only thing ever loaded
+LIB_PATH = os.environ.get("DXGPU_LIB") or os.path.join(_HERE, "libdxgpu.so")
 HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "dxgpu.h")
 
 _lib = None

@@ -19,10 +19,14 @@
 #include "dx_json.h"
 #include "dx_decode_host.h"
 
+#ifndef K1_T
 #define K1_T 32768          // tile bytes
+#endif
 #define K1_OVL 2048         // overlap bytes past the tile (records starting in the tile may end here)
 #define K1_PAD 32
+#ifndef K1_NT
 #define K1_NT 256           // threads per CTA
+#endif
 #define K1_SC 1024          // record starts held in shared memory per round
 #ifndef K1_STAGES
 #define K1_STAGES 1         // shared-memory tile stages; 2 = prefetch the next tile while parsing (measured slower: 3 CTAs/SM already overlap copy and parse)
