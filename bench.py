@@ -236,7 +236,7 @@ def run_ours(args):
         k2_name = "k2_eval_flags"
     peak, peak_src = peaks()
     k1_bytes = total_bytes + n_events * (6 * 8 + 4 + 1)                 # JSON bytes + 6x8 B + 4 B code + 1 B validity per event
-    k2_bytes = n_events * (5 * 8 + 4 + 1 + words * 4)                   # 6 referenced columns + validity + flag words
+    k2_bytes = n_events * (5 * 8 + 4 + 1 + (N_RULES + 7) // 8)          # 6 referenced columns (44 B) + validity + ceil(R/8) flag bytes = 70 B
     dominant = (k2_name, k2_bytes, k2_ms) if k2_ms >= k1_ms else ("k1_decode", k1_bytes, k1_ms)
     achieved = dominant[1] / (dominant[2] / 1e3) / 1e9 if dominant[2] > 0 else 0.0
     roofline = {"bound": "hbm", "kernel": dominant[0], "achieved": round(achieved, 2), "peak": peak, "unit": "GB/s",

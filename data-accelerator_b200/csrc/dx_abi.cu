@@ -290,6 +290,65 @@ int dx_flow_state_export(dx_flow* f, const char* table, dx_table** out, int* act
     return DX_OK;
 }
 
+int dx_flow_state_import(dx_flow* f, const char* table, int64_t n_rows, int n_columns, const void* const* column_data,
+                         const uint8_t* const* column_valid, const uint8_t* const* string_bytes, int active_is_b) {
+    if (!f || !table || n_rows < 0 || (n_rows > 0 && !column_data)) return DX_ERR_ARG;
+    dx_ctx* c = f->ctx;
+    cudaSetDevice(c->device);
+    auto it = f->state_tables.find(table);
+    if (it == f->state_tables.end()) return c->set_error(DX_ERR_ARG, std::string("no state table '") + table + "'");
+    StateTable& st = it->second;
+    if (n_columns != (int)st.schema.size())
+        return c->set_error(DX_ERR_ARG, "state table '" + st.name + "' has " + std::to_string(st.schema.size()) + " columns, " + std::to_string(n_columns) + " given");
+    auto t = std::make_shared<DxTable>(); t->ctx = c; t->n_rows = n_rows;
+    const size_t nr = (size_t)(n_rows > 0 ? n_rows : 1);
+    // one 32-bit validity word per row, bit k for column k (more than 32 columns: a second array)
+    std::vector<DevBufP> masks((st.schema.size() + 31) / 32);
+    std::vector<std::vector<uint32_t>> hmask(masks.size(), std::vector<uint32_t>(nr, 0));
+    for (size_t k = 0; k < st.schema.size(); k++) {
+        DxColumn col; col.name = st.schema[k].first; col.type = st.schema[k].second;
+        const int w = dx_type_width(col.type);
+        col.data = make_buf(c, nr * w);
+        if (!col.data->p) return c->set_error(DX_ERR_CUDA, "state import allocation failed");
+        if (n_rows > 0 && !column_data[k]) return c->set_error(DX_ERR_ARG, "state import: column '" + col.name + "' has no data");
+        const uint8_t* valid = column_valid ? column_valid[k] : nullptr;
+        for (int64_t r = 0; r < n_rows; r++) if (!valid || valid[r]) hmask[k / 32][r] |= 1u << (k % 32);
+        if (col.type == DX_T_STR) {
+            if (n_rows > 0 && (!string_bytes || !string_bytes[k])) return c->set_error(DX_ERR_ARG, "state import: string column '" + col.name + "' needs its bytes");
+            col.dict = std::make_shared<DxDict>();
+            int rc = col.dict->init(c, 1u << 16, 1u << 22); if (rc) return rc;
+            const int64_t* off = reinterpret_cast<const int64_t*>(column_data[k]);
+            std::vector<int32_t> codes(nr, -1);
+            std::map<std::string, int32_t> seen;
+            for (int64_t r = 0; r < n_rows; r++) {
+                if (valid && !valid[r]) continue;
+                if (off[r + 1] < off[r]) return c->set_error(DX_ERR_ARG, "state import: offsets of '" + col.name + "' are not ascending");
+                std::string sv(reinterpret_cast<const char*>(string_bytes[k]) + off[r], (size_t)(off[r + 1] - off[r]));
+                auto hit = seen.find(sv);
+                if (hit == seen.end()) { int32_t code; rc = col.dict->insert_host(sv, &code); if (rc) return rc; hit = seen.emplace(sv, code).first; }
+                codes[r] = hit->second;
+            }
+            DX_CUDA(c, cudaMemcpyAsync(col.data->p, codes.data(), nr * 4, cudaMemcpyHostToDevice, c->stream));
+            DX_CUDA(c, cudaStreamSynchronize(c->stream));
+        } else if (n_rows > 0) {
+            DX_CUDA(c, cudaMemcpyAsync(col.data->p, column_data[k], nr * w, cudaMemcpyHostToDevice, c->stream));
+            DX_CUDA(c, cudaStreamSynchronize(c->stream));
+        }
+        col.vwidth = 4; col.vbit = (int)(k % 32);
+        t->cols.push_back(col);
+    }
+    for (size_t m = 0; m < masks.size(); m++) {
+        masks[m] = make_buf(c, nr * 4);
+        if (!masks[m]->p) return c->set_error(DX_ERR_CUDA, "state import allocation failed");
+        DX_CUDA(c, cudaMemcpyAsync(masks[m]->p, hmask[m].data(), nr * 4, cudaMemcpyHostToDevice, c->stream));
+    }
+    DX_CUDA(c, cudaStreamSynchronize(c->stream));
+    for (size_t k = 0; k < t->cols.size(); k++) t->cols[k].vmask = masks[k / 32];
+    st.active = active_is_b ? 1 : 0;
+    st.phys[st.active] = t;
+    return DX_OK;
+}
+
 int dx_flow_add_refdata(dx_flow* f, const char* name, const char* csv_text, char delimiter, int has_header) {
     if (!f || !name || !csv_text) return DX_ERR_ARG;
     cudaSetDevice(f->ctx->device);

@@ -391,8 +391,7 @@ struct Exec {
                     if (!il) return fail(DX_ERR_UNSUPPORTED, "UNION column '" + oc.name + "' mixes types");
                 }
                 if (pc.type == DX_T_STR && pc.data && p->n_rows > 0) {
-                    if (dict && dict != pc.dict) return fail(DX_ERR_UNSUPPORTED, "UNION of string columns from different dictionaries");
-                    dict = pc.dict;
+                    if (!dict) dict = pc.dict;      // codes of the other sides are re-encoded into the first side's dictionary
                 }
                 if (pc.type == DX_T_FLAGS) return fail(DX_ERR_UNSUPPORTED, "UNION over a rule-flag column");
             }
@@ -419,6 +418,17 @@ struct Exec {
                     DxColumn tmp = pc;
                     rc = materialize_const(&tmp, p->n_rows, dict); if (rc) return rc;
                     rc = dx_gather_column(ctx, tmp, p->n_rows, nullptr, dst, vm, oc.vbit); if (rc) return rc;
+                } else if (pc.type == DX_T_STR && pc.dict && pc.dict != dict) {
+                    // another dictionary (a restored state table, a CONCAT result ...): translate code -> code through a
+                    // per-(source, target) lookup table that only grows with the source dictionary
+                    char kb[64]; snprintf(kb, sizeof kb, "recode@%p/%p", (void*)pc.dict.get(), (void*)dict.get());
+                    std::shared_ptr<LutCache>& lut = F->luts[kb];
+                    if (!lut) { lut = std::make_shared<LutCache>(); lut->src_dict = pc.dict; lut->out_dict = dict; }
+                    DxDictP target = dict;
+                    rc = dx_lut_refresh(ctx, lut.get(), pc.dict, [&](const std::string& sv, long long* v) {
+                        int32_t code = -1; if (target->insert_host(sv, &code)) return false; *v = code; return true; });
+                    if (rc) return rc;
+                    rc = dx_lut_apply(ctx, pc, *lut, p->n_rows, nullptr, dst, 4, vm, oc.vbit); if (rc) return rc;
                 } else { rc = dx_gather_column(ctx, pc, p->n_rows, nullptr, dst, vm, oc.vbit); if (rc) return rc; }
                 off += p->n_rows;
             }

@@ -27,6 +27,7 @@ struct LutCache {
     DevBuf vals, valid;
     uint32_t built = 0;          // codes [0, built) are filled
     DxDictP out_dict;            // string-valued tables (UDF results): dictionary of the results
+    DxDictP src_dict;            // kept alive where the cache key is the source dictionary's address
 };
 
 int dx_strbuild(dx_ctx* ctx, StrBuildArgs& a, const std::string& lit_bytes, const DxDictP& out_dict, int32_t* out_codes, uint32_t* vmask32, int vbit);

@@ -207,6 +207,35 @@ class CommonProcessor:
         fn.restype, fn.argtypes = C.c_int, [C.c_void_p, C.c_char_p, proto, C.c_void_p]
         self.ctx.check(fn(self.h, name.encode(), cb, None))
 
+    def import_state(self, name, columns, active="A"):
+        """Restart (StateTableHandler.scala:70-96): `columns` = [(values ndarray | list of bytes/None for strings, valid
+        bool ndarray | None)] in the order of the table's declared schema, as read back from the persisted copy."""
+        n = len(columns[0][0]) if columns else 0
+        keep, data, valid, sbytes = [], [], [], []
+        for vals, ok in columns:
+            if isinstance(vals, np.ndarray) and vals.dtype != object:
+                a = np.ascontiguousarray(vals.astype(np.float64) if vals.dtype.kind == "f" else vals.astype(np.int64))
+                keep.append(a); data.append(a.ctypes.data); sbytes.append(None)
+            else:
+                off, blob = np.zeros(n + 1, dtype=np.int64), bytearray()
+                for r, v in enumerate(vals):
+                    if v is not None and (ok is None or ok[r]):
+                        blob += v
+                    off[r + 1] = len(blob)
+                b = np.frombuffer(bytes(blob) or b"\0", dtype=np.uint8)
+                keep += [off, b]; data.append(off.ctypes.data); sbytes.append(b.ctypes.data)
+            if ok is None:
+                valid.append(None)
+            else:
+                m = np.ascontiguousarray(np.asarray(ok).astype(np.uint8))
+                keep.append(m); valid.append(m.ctypes.data)
+        k = len(columns)
+        fn = self.L.dx_flow_state_import
+        fn.restype = C.c_int
+        fn.argtypes = [C.c_void_p, C.c_char_p, C.c_int64, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.c_int]
+        arr = lambda xs: (C.c_void_p * k)(*[C.c_void_p(x) if x else None for x in xs])
+        self.ctx.check(fn(self.h, name.encode(), n, k, arr(data), arr(valid), arr(sbytes), 1 if active == "B" else 0))
+
     def state_table(self, name):
         t, b = C.c_void_p(), C.c_int()
         self.ctx.check(self.L.dx_flow_state_export(self.h, name.encode(), C.byref(t), C.byref(b)))

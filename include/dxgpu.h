@@ -168,6 +168,13 @@ void dx_result_release(dx_result* r);
 /* Accumulator (state) tables: the active physical table and whether it is the "B" copy
  * (StateTableHandler.scala:26-52: metadata.info active=/standby=), for Parquet A/B persistence. */
 int dx_flow_state_export(dx_flow* flow, const char* table, dx_table** out, int* active_is_b);
+/* Restart: what the JVM read back from the active Parquet copy (StateTableHandler.scala:70-96 registers the active
+ * table at start; SURVEY.md 8(b) dx_flow_state_import) becomes the active physical table again.  Host buffers, one per
+ * column in the order of the table's declared schema (datax.job.process.statetable.<name>.schema): 8-byte values for
+ * long / double / timestamp (microseconds) / boolean columns; for string columns int64 offsets[n_rows + 1] into
+ * string_bytes[k].  column_valid[k]: one byte per row (0 = NULL), or NULL for a column without NULLs.           */
+int dx_flow_state_import(dx_flow* flow, const char* table, int64_t n_rows, int n_columns, const void* const* column_data,
+                         const uint8_t* const* column_valid, const uint8_t* const* string_bytes, int active_is_b);
 
 /* Reference data (ReferenceDataHandler.scala:42-60, CSVUtil.scala:27-29): the CSV text of
  * datax.job.input.default.referencedata.<name>.path becomes a view <name> whose columns are all

@@ -185,6 +185,41 @@ totals = SELECT deviceId, homeId, SUM(Count) AS Count FROM merged GROUP BY devic
     g.close()
 
 
+def test_state_export_import_restart(dx, ctx):
+    """A processor restarted from the exported state table (dx_flow_state_export -> host -> dx_flow_state_import,
+    what the JVM does through the Parquet A/B copies) continues exactly like one that never stopped; the table has a
+    string column, so the restored dictionary and the decoder's meet in the UNION ALL."""
+    tr = """--DataXQuery--
+acc_new = SELECT deviceDetails.deviceId, deviceDetails.deviceType, eventTimeStamp AS EventTime, deviceDetails.status AS Reading
+    FROM DataXProcessedInput WHERE deviceDetails.status = 1
+    UNION ALL SELECT deviceId, deviceType, EventTime, Reading FROM acc WHERE unix_timestamp() - to_unix_timestamp(EventTime, 'yyyy-MM-dd') < 150
+--DataXQuery--
+acc = SELECT deviceId, deviceType, EventTime, Reading FROM acc_new
+--DataXQuery--
+perType = SELECT deviceType, COUNT(*) AS Cnt, MAX(EventTime) AS Last FROM acc GROUP BY deviceType
+"""
+    conf = dx.flowgen.conf_text("restart", state_tables=[("acc", "deviceId long, deviceType string, EventTime Timestamp, Reading long")])
+    g, o = both(dx, ctx, conf, SCHEMA1, [PROJ_TS], tr)
+    batch = lambda b: gen(dx, 2000, first=b * 2000, shape=1, n_keys=100, base=T0 + b * I)
+    for b in range(3):
+        check_batch(dx, g, o, batch(b), T0 + b * I, now_ms=T0 + b * I + 5)
+    t, which = g.state_table("acc")
+    saved = [t.column(i) for i in range(len(t.columns))]
+    assert t.num_rows > 0 and any(v is None for v in saved[1][0]) is False
+    g.close()
+    g2 = dx.CommonProcessorFactory.createProcessor(ctx, conf, SCHEMA1, [PROJ_TS], tr)
+    g2.import_state("acc", saved, active=which)
+    t2, which2 = g2.state_table("acc")
+    assert which2 == which
+    assert_same_rows(t2, o.state["acc"]["tables"][which], dx)
+    for b in range(3, 7):
+        check_batch(dx, g2, o, batch(b), T0 + b * I, now_ms=T0 + b * I + 5)
+        t2, which2 = g2.state_table("acc")
+        assert which2 == o.state["acc"]["active"]
+        assert_same_rows(t2, o.state["acc"]["tables"][which2], dx)
+    g2.close()
+
+
 def test_unsupported_sql_fails_at_create(dx, ctx):
     for bad in ["--DataXQuery--\nx = SELECT a FROM t ORDER BY a\n", "--DataXQuery--\nSET spark.x=1\n--DataXQuery--\n"]:
         with pytest.raises(dx.DxError):
