@@ -200,3 +200,93 @@ def iot_schema_json(shape=2, event_time_type="long"):
               {"name": "humidity", "type": "double", "nullable": True, "metadata": {}}]
     return json.dumps({"type": "struct", "fields": [
         {"name": "deviceDetails", "type": {"type": "struct", "fields": f}, "nullable": True, "metadata": {}}]})
+
+
+# --------------------------------------------------------------------------------------------------
+# threaded rule evaluation (dxo_rules.c) — CPU baseline; checked against dxo_flow's numpy evaluator
+# --------------------------------------------------------------------------------------------------
+class _ROp(C.Structure):
+    _fields_ = [("op", C.c_int32), ("arg", C.c_int32), ("i", C.c_int64), ("f", C.c_double)]
+
+
+_R = dict(LOAD_I=1, LOAD_F=2, CONST_I=3, CONST_F=4, CONST_NULL=5, I2F_TOP=6, I2F_SECOND=7, CMP_I=8, CMP_F=9, AND=10, OR=11, NOT=12,
+          ISNULL=13, ISNOTNULL=14)
+_CMP = {"=": 0, "==": 0, "<>": 1, "!=": 1, "<": 2, "<=": 3, ">": 4, ">=": 5}
+
+
+def compile_rules(conds, columns, str_code):
+    """conds: condition trees as dxo_flow.P produces them; columns: [(dotted name, 'long'|'double'|'string')];
+    str_code(column index, literal) -> the integer a string column holds for that literal.  -> (ops, rule_start)."""
+    names = [n.lower() for n, _ in columns]
+    ops, starts = [], [0]
+
+    def emit(op, arg=0, i=0, f=0.0):
+        ops.append((_R[op], arg, i, f))
+
+    def walk(e):
+        k = e[0]
+        if k == "col":
+            ci = names.index(".".join(e[1]).lower())
+            ty = columns[ci][1]
+            emit("LOAD_F" if ty == "double" else "LOAD_I", ci)
+            return ty, ci
+        if k == "int":
+            emit("CONST_I", i=int(e[1])); return "long", None
+        if k == "dec":
+            emit("CONST_F", f=float(e[1])); return "double", None
+        if k == "null":
+            emit("CONST_NULL"); return "null", None
+        if k == "not":
+            walk(e[1]); emit("NOT"); return "bool", None
+        if k == "isnull":
+            walk(e[1]); emit("ISNOTNULL" if e[2] else "ISNULL"); return "bool", None
+        if k == "bin" and e[1] in ("AND", "OR"):
+            walk(e[2]); walk(e[3]); emit(e[1]); return "bool", None
+        if k == "bin" and e[1] in _CMP:
+            a, b = e[2], e[3]
+            if a[0] == "str" or b[0] == "str":
+                col, lit = (b, a) if a[0] == "str" else (a, b)
+                if col[0] != "col" or e[1] not in ("=", "<>", "==", "!="):
+                    raise ValueError("string comparison shape outside the baseline evaluator")
+                ty, ci = walk(col)
+                emit("CONST_I", i=int(str_code(ci, lit[1])))
+                emit("CMP_I", _CMP[e[1]]); return "bool", None
+            ta, _ = walk(a)
+            tb, _ = walk(b)
+            if "double" in (ta, tb):
+                if ta != "double":
+                    emit("I2F_SECOND")
+                if tb != "double":
+                    emit("I2F_TOP")
+                emit("CMP_F", _CMP[e[1]])
+            else:
+                emit("CMP_I", _CMP[e[1]])
+            return "bool", None
+        raise ValueError("expression outside the baseline evaluator: %r" % (e,))
+
+    for c in conds:
+        walk(c)
+        starts.append(len(ops))
+    arr = (_ROp * max(1, len(ops)))()
+    for j, (op, arg, i, f) in enumerate(ops):
+        arr[j].op, arr[j].arg, arr[j].i, arr[j].f = op, arg, i, f
+    return arr, np.asarray(starts, dtype=np.int32)
+
+
+def eval_rules_mt(program, column_arrays, valid_arrays, n_rows, n_rules, threads=0):
+    """-> uint32 flags (n_rows, ceil(n_rules/32)), bit r of a row set iff rule r is TRUE."""
+    ops, starts = program
+    words = (n_rules + 31) // 32
+    flags = np.empty((max(n_rows, 1), words), dtype=np.uint32)
+    k = len(column_arrays)
+    keep = [np.ascontiguousarray(a) for a in column_arrays]
+    vkeep = [None if v is None else np.ascontiguousarray(v.astype(np.uint8)) for v in valid_arrays]
+    cols = (C.c_void_p * k)(*[a.ctypes.data for a in keep])
+    valid = (C.c_void_p * k)(*[None if v is None else v.ctypes.data for v in vkeep])
+    fn = lib().dxo_eval_rules
+    fn.restype = C.c_int
+    rc = fn(ops, starts.ctypes.data_as(C.c_void_p), C.c_int(n_rules), cols, valid, C.c_int64(n_rows), flags.ctypes.data_as(C.c_void_p),
+            C.c_int(words), C.c_int(threads or (os.cpu_count() or 1)))
+    if rc:
+        raise ValueError("dxo_eval_rules: malformed program")
+    return flags[:n_rows]

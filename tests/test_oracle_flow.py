@@ -43,3 +43,42 @@ def test_splitters_agree_on_reference_goldens(dx):
         a = dx.transform_split(text)
         b = dxo_flow.parse_transform(text)
         assert a[0] == b[0] and a[1] == b[1], f
+
+
+def test_threaded_c_rule_evaluator_matches_numpy_oracle(dx):
+    """oracle/dxo_rules.c (the CPU baseline's rule evaluation) against dxo_flow's numpy evaluator (the oracle of record),
+    on generated events and on the adversarial set (NULLs, NaN, three-valued AND/OR/NOT)."""
+    import numpy as np
+    import dxo
+    from adversarial import all_records, to_ndjson
+    conds = ["deviceDetails.temperature > 50", "deviceDetails.temperature <= 50 OR deviceDetails.humidity > 1e300",
+             "NOT (deviceDetails.temperature > 50)", "deviceDetails.status = 1 AND deviceDetails.deviceType = 'Heating'",
+             "deviceDetails.deviceType <> 'Heating'", "deviceDetails.status IS NULL", "deviceDetails.status IS NOT NULL AND deviceDetails.temperature IS NULL",
+             "deviceDetails.temperature = deviceDetails.humidity", "deviceDetails.temperature > deviceDetails.deviceId",
+             "deviceDetails.status = 1 OR NULL", "deviceDetails.homeId <> 150 OR deviceDetails.deviceId = 3",
+             "(deviceDetails.humidity < 30 OR deviceDetails.homeId >= 40) AND NOT deviceDetails.deviceType = 'DoorLock'"]
+    rules = [{"ruleId": "R%d" % i, "ruleDescription": "d", "severity": "Critical", "tagName": "Tag", "tag": "t", "condition": c} for i, c in enumerate(conds)]
+    rules += dx.flowgen.make_rules(60, seed=9, n_keys=500, n_homes=50)
+    o = dxo_flow.Flow(dx.flowgen.conf_text("r"), dxo.iot_schema_json(2), ["Raw.*\n"], dx.flowgen.process_rules_sql(rules))
+    p = dxo.GenParams(5, 500, 50, 1_700_000_040_000, 60_000, 60_000, 2, 10, 1, 0)
+    for data in (dxo.gen_events(p, 0, 20_000), to_ndjson(all_records(3000, seed=21))):
+        ro, _ = o.process(data, 1_700_000_040_000, 60_000)
+        want = [c for c in ro["Rules"].cols if c[1] == "rules"][0][2]
+        src = ro["Rules"]                        # SELECT *, <rules>: the input columns ride along
+        cols, arrs, valids, dicts = [], [], [], {}
+        for ci, (name, ty, v, ok) in enumerate(src.cols):
+            if ty == "string":
+                vocab = sorted({x for x, k in zip(v, ok) if k})
+                dicts[ci] = {s: i for i, s in enumerate(vocab)}
+                v = np.array([dicts[ci][x] if k else -1 for x, k in zip(v, ok)], dtype=np.int64)
+            elif ty not in ("long", "double"):
+                continue
+            cols.append((name, ty)); arrs.append(v); valids.append(ok)
+        cores, _ = dxo_flow.P(o.commands[0][2]).statement()
+        rs = dxo_flow._rule_shape(cores[0]["items"][1][0])
+        names = [n for n, _ in cols]
+        str_code = lambda ci, lit: dicts[[i for i, c in enumerate(src.cols) if c[0] == names[ci]][0]].get(lit.encode(), -2)
+        prog = dxo.compile_rules([c for c, _ in rs], cols, str_code)
+        flags = dxo.eval_rules_mt(prog, arrs, valids, src.n, len(rs), threads=4)
+        got = np.unpackbits(flags.view(np.uint8), axis=1, bitorder="little")[:, :len(rs)].astype(bool)
+        assert np.array_equal(got, want)
