@@ -35,12 +35,19 @@ __global__ void __launch_bounds__(256) k3_hash_agg(const __grid_constant__ AggTa
             long long t;
             if (!load_val(in.range_col, row, t) || t < in.range_lo || t >= in.range_hi) continue;
         }
+        long long pane = 0;
+        if (in.pane_us) {
+            long long t;
+            if (!load_val(in.range_col, row, t)) continue;
+            pane = t >= 0 ? t / in.pane_us : -((-t + in.pane_us - 1) / in.pane_us);
+        }
         long long kv[KMAX];
         unsigned long long nullbits = 0, h = 0x2545F4914F6CDD1Dull;
 #pragma unroll
         for (int k = 0; k < KMAX; k++) {
             if (k < nk) {
-                long long v; bool ok = load_val(in.keys[k], row, v);
+                long long v; bool ok;
+                if (in.pane_us && k == nk - 1) { v = pane; ok = true; } else ok = load_val(in.keys[k], row, v);
                 kv[k] = v; if (!ok) nullbits |= 1ull << k;
                 h = amix64(h ^ (unsigned long long)v);
             }
@@ -116,6 +123,18 @@ __global__ void k3_extract(const AggTableDev T, unsigned long long capacity, uns
             acc_out[a][g] = v;
         }
     }
+}
+
+// group null bits (bit k set = key k is NULL) -> a 32-bit validity word per group (bit k set = key k present)
+__global__ void k3_keynull_to_valid(const unsigned long long* keynull, long long n, uint32_t* valid) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) valid[i] = ~(uint32_t)keynull[i];
+}
+int dx_agg_keynull_to_valid(dx_ctx* c, const unsigned long long* keynull, long long n, uint32_t* valid) {
+    if (n <= 0) return DX_OK;
+    k3_keynull_to_valid<<<(unsigned)std::min<long long>((n + 255) / 256, 4096), 256, 0, c->stream>>>(keynull, n, valid);
+    c->launches["k3_keynull_to_valid"]++;
+    DX_CUDA(c, cudaGetLastError());
+    return DX_OK;
 }
 
 int AggTable::init(dx_ctx* c, int n_keys, int n_vals, const std::vector<AggAccDesc>& accs, unsigned long long capacity_pow2) {

@@ -23,6 +23,9 @@ struct AggInput {                 // one chunk of input rows
     ProgCol range_col;            // optional fused time-range filter: keep rows with lo <= range_col < hi (NULL fails)
     long long range_lo, range_hi;
     int32_t has_range, pad;
+    // pane partials: when pane_us > 0 the LAST key is not loaded but computed as floor(range_col / pane_us)
+    // (rows whose range_col is NULL are skipped: they belong to no window)
+    long long pane_us;
 };
 
 struct AggTableDev {
@@ -45,3 +48,5 @@ struct AggTable {
     // writes group rows: keys[k][g] (int64), key_null[g] (bit k set = NULL), acc[a][g] (raw 64-bit), acc_cnt...
     int extract(unsigned long long n_groups, long long* const* key_out, unsigned long long* keynull_out, unsigned long long* const* acc_out);
 };
+
+int dx_agg_keynull_to_valid(dx_ctx* c, const unsigned long long* keynull, long long n, uint32_t* valid);

@@ -1,6 +1,7 @@
 // dx_flow.cu — flow artefact loading, statement planning/execution and route() bookkeeping.
 // Reference call sites are listed in dx_flow.h; each function below names the lines it restates.
 #include "dx_flow.h"
+#include <chrono>
 #include "dx_rules.h"
 #include "dx_join.h"
 #include <cmath>
@@ -1113,72 +1114,174 @@ struct Exec {
         }
         AggTable T; unsigned long long n_groups = 0;
         std::vector<int> key_type(keys.size(), DX_T_I64); std::vector<DxDictP> key_dict(keys.size());
+        // One chunk's columns as the aggregation kernel's input; `hold` keeps computed columns alive until the kernel has run.
+        struct InputHold { std::vector<DevBufP> temps; DevBufP tmask; std::vector<DxColumn> string_keys; };
+        auto make_input = [&](const DxTable* ch, const long long* sel, int64_t n, bool with_range, AggInput* inp, InputHold* hold) -> int {
+            AggInput& in = *inp; memset(&in, 0, sizeof in);
+            BindScope sc = scope_for(ch, core);
+            in.sel = sel; in.n_rows = n;
+            if (with_range) {
+                std::string err; int tc = dx_resolve_column(sc, std::vector<std::string>{v.ts_col}, &err);
+                if (tc < 0) return fail(DX_ERR_ARG, err);
+                const DxColumn& c = ch->cols[tc];
+                if (!c.data || c.type != DX_T_TS) return fail(DX_ERR_UNSUPPORTED, "window timestamp column must be a materialised timestamp");
+                in.range_col.data = c.data->p; in.range_col.vmask = c.vmask ? c.vmask->p : nullptr; in.range_col.vwidth = c.vwidth;
+                in.range_col.vbit = c.vbit; in.range_col.width = 8;
+                in.range_lo = v.lo_us; in.range_hi = v.hi_us; in.has_range = 1;
+            }
+            auto col_desc = [&](const DxColumn& c) { ProgCol pc; pc.data = c.data->p; pc.vmask = c.vmask ? c.vmask->p : nullptr; pc.vwidth = c.vwidth; pc.vbit = c.vbit; pc.width = dx_type_width(c.type); pc.pad = 0; return pc; };
+            auto eval_temp = [&](const ExprP& e, int* type_out, ProgCol* pc) -> int {
+                ExprPrograms P; int rc2 = dx_compile_expr(ctx, sc, e, &P); if (rc2) return rc2;
+                DevPrograms D; rc2 = dx_upload_programs(ctx, &P, &D); if (rc2) return rc2;
+                int ty = P.result_type[0] == DX_T_NULL ? DX_T_I64 : P.result_type[0];
+                DevBufP b = make_buf(ctx, (size_t)ch->n_rows * dx_type_width(ty)); hold->temps.push_back(b);
+                if (!hold->tmask) { hold->tmask = make_buf(ctx, (size_t)ch->n_rows * 4); DX_CUDA(ctx, cudaMemsetAsync(hold->tmask->p, 0, (size_t)ch->n_rows * 4, ctx->stream)); }
+                int bit = (int)hold->temps.size() - 1;
+                if (bit >= 32) return fail(DX_ERR_UNSUPPORTED, "too many computed group/aggregate expressions");
+                rc2 = dx_eval_column(ctx, D, 0, ch->n_rows, nullptr, b->p, dx_type_width(ty), hold->tmask->as<uint32_t>(), bit); if (rc2) return rc2;
+                pc->data = b->p; pc->vmask = hold->tmask->p; pc->vwidth = 4; pc->vbit = bit; pc->width = dx_type_width(ty); pc->pad = 0;
+                *type_out = ty; return DX_OK;
+            };
+            int rc = DX_OK;
+            for (size_t hk = 0; hk < hashed.size(); hk++) {
+                KeySpec& ks = keys[hashed[hk]];
+                if (ks.expr->kind == EK::Col) {
+                    std::string err; int ci = dx_resolve_column(sc, ks.expr->parts, &err);
+                    if (ci < 0) return fail(DX_ERR_ARG, err);
+                    const DxColumn& c = ch->cols[ci];
+                    if (!c.data) return fail(DX_ERR_UNSUPPORTED, "group key constant in one batch and materialised in another");
+                    in.keys[hk] = col_desc(c); key_type[hashed[hk]] = c.type;
+                    if (c.type == DX_T_STR) {
+                        if (key_dict[hashed[hk]] && key_dict[hashed[hk]] != c.dict) return fail(DX_ERR_UNSUPPORTED, "group key dictionaries differ between batches");
+                        key_dict[hashed[hk]] = c.dict;
+                    }
+                } else if (needs_string_engine(ks.expr, sc)) {
+                    // CONCAT(...) / CAST AS STRING / user function as a group key (e.g. SELECT DISTINCT ... CONCAT(...) AS Pivot1)
+                    DxColumn full; rc = eval_string_full(sc, ch, ks.expr, stmt_name + "#key" + std::to_string(hashed[hk]), &full); if (rc) return rc;
+                    if (!full.data || full.all_null) return fail(DX_ERR_UNSUPPORTED, "constant string expression as a group key");
+                    hold->string_keys.push_back(full);     // keeps the buffers alive until the kernel has run
+                    in.keys[hk] = col_desc(full); key_type[hashed[hk]] = full.type;
+                    if (key_dict[hashed[hk]] && key_dict[hashed[hk]] != full.dict) return fail(DX_ERR_UNSUPPORTED, "group key dictionaries differ between batches");
+                    key_dict[hashed[hk]] = full.dict;
+                } else { int ty; rc = eval_temp(ks.expr, &ty, &in.keys[hk]); if (rc) return rc; key_type[hashed[hk]] = ty; }
+            }
+            for (size_t vi = 0; vi < val_exprs.size(); vi++) {
+                bool done = false;
+                if (val_exprs[vi]->kind == EK::Col) {
+                    std::string err; int ci = dx_resolve_column(sc, val_exprs[vi]->parts, &err);
+                    if (ci >= 0 && ch->cols[ci].data && !ch->cols[ci].all_null) { in.vals[vi] = col_desc(ch->cols[ci]); done = true; }
+                }
+                if (!done) { int ty; rc = eval_temp(val_exprs[vi], &ty, &in.vals[vi]); if (rc) return rc; }
+            }
+            return DX_OK;
+        };
+
+        // Pane partials: a window over several cached batches whose ends fall on batch-interval boundaries is answered from one
+        // pre-aggregated table per cached batch (built once, when the batch is first seen by this statement).
+        const long long pane_us = v.pane_us;
+        bool plain_keys = true;
+        for (int hk : hashed) if (keys[hk].expr->kind != EK::Col) plain_keys = false;
+        const bool pane_mode = fuse_range && !F->pane_partials_off && pane_us > 0 && v.chunks.size() >= 2 && !stmt_name.empty() && plain_keys &&
+                               v.lo_us % pane_us == 0 && v.hi_us % pane_us == 0 && (int)hashed.size() + 1 <= DX_AGG_MAX_KEYS;
+        if (pane_mode) {
+            std::string sig = std::to_string(pane_us) + "|" + v.ts_col;     // the views of one flow range over the same cached batches
+            for (int hk : hashed) sig += "|k:" + to_string(keys[hk].expr);
+            for (auto& ve : val_exprs) sig += "|v:" + to_string(ve);
+            for (auto& ac : accs) sig += "|a:" + std::to_string(ac.kind) + "," + std::to_string(ac.col);
+            auto& cache = F->pane_partials[sig];      // statements with the same keys, values and accumulators share the partials
+            const int nk = (int)hashed.size();
+            // evict partials of batches that left the window cache
+            for (auto it2 = cache.begin(); it2 != cache.end();) {
+                bool live = false; for (auto& chp : v.chunks) if (chp.get() == it2->first) live = true;
+                if (!live || it2->second.sig != sig) it2 = cache.erase(it2); else ++it2;
+            }
+            for (size_t k = 0; k < v.chunks.size(); k++) {
+                if (cs[k].n == 0) continue;
+                const DxTableP& chp = v.chunks[k];
+                if (cache.count(chp.get())) {       // still fills key_type / key_dict for this batch's columns
+                    BindScope sc = scope_for(chp.get(), core);
+                    for (size_t hk = 0; hk < hashed.size(); hk++) {
+                        KeySpec& ks = keys[hashed[hk]];
+                        if (ks.expr->kind != EK::Col) continue;
+                        std::string err; int ci = dx_resolve_column(sc, ks.expr->parts, &err);
+                        if (ci < 0) return fail(DX_ERR_ARG, err);
+                        key_type[hashed[hk]] = chp->cols[ci].type;
+                        if (chp->cols[ci].type == DX_T_STR) {
+                            if (key_dict[hashed[hk]] && key_dict[hashed[hk]] != chp->cols[ci].dict) return fail(DX_ERR_UNSUPPORTED, "group key dictionaries differ between batches");
+                            key_dict[hashed[hk]] = chp->cols[ci].dict;
+                        }
+                    }
+                    continue;
+                }
+                PanePartial pp; pp.chunk = chp; pp.sig = sig;
+                // sized from the previous batch's partial (groups are stable from batch to batch), else from the row count
+                unsigned long long pcap = 1024, pwant = (unsigned long long)std::min<int64_t>(chp->n_rows, 1 << 24) * 2;
+                auto phint = F->agg_capacity_hint.find("#pane|" + sig);
+                if (phint != F->agg_capacity_hint.end()) pwant = std::min(pwant, phint->second);
+                while (pcap < pwant) pcap <<= 1;
+                for (int attempt = 0;; attempt++) {
+                    AggTable P; int rc = P.init(ctx, nk + 1, (int)val_exprs.size(), accs, pcap); if (rc) return rc;
+                    InputHold hold; AggInput in;
+                    rc = make_input(chp.get(), nullptr, chp->n_rows, true, &in, &hold); if (rc) return rc;
+                    in.has_range = 0; in.pane_us = pane_us;          // every row with a timestamp, keyed by its pane
+                    memset(&in.keys[nk], 0, sizeof(ProgCol));
+                    rc = P.update(in); if (rc) return rc;
+                    unsigned long long ng = 0; bool ovf = false;
+                    rc = P.finish(&ng, &ovf); if (rc) return rc;
+                    if (ovf) { if (attempt > 12) return fail(DX_ERR_CAPACITY, "pane partial table overflow"); pcap = P.capacity * 4; continue; }
+                    pp.n = (int64_t)ng;
+                    const size_t nr = (size_t)(ng > 0 ? ng : 1);
+                    long long* kp[DX_AGG_MAX_KEYS]; unsigned long long* ap[DX_AGG_MAX_ACCS];
+                    for (int k2 = 0; k2 <= nk; k2++) { pp.keys.push_back(make_buf(ctx, nr * 8)); kp[k2] = pp.keys.back()->as<long long>(); }
+                    for (size_t a2 = 0; a2 < accs.size(); a2++) { pp.accs.push_back(make_buf(ctx, nr * 8)); ap[a2] = pp.accs.back()->as<unsigned long long>(); }
+                    DevBufP knull = make_buf(ctx, nr * 8); pp.valid32 = make_buf(ctx, nr * 4);
+                    rc = P.extract(ng, kp, knull->as<unsigned long long>(), ap); if (rc) return rc;
+                    rc = dx_agg_keynull_to_valid(ctx, knull->as<unsigned long long>(), (long long)ng, pp.valid32->as<uint32_t>()); if (rc) return rc;
+                    DX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+                    ctx->counters["k3_partial_rows_built"] += (long long)ng;
+                    { unsigned long long h2 = 1024; while (h2 < ng * 2 + 16) h2 <<= 1; F->agg_capacity_hint["#pane|" + sig] = h2 * 2; }
+                    break;
+                }
+                cache[chp.get()] = std::move(pp);
+            }
+            // combine: COUNTs become sums of partial counts, everything else keeps its operator
+            std::vector<AggAccDesc> accs2(accs.size());
+            for (size_t a2 = 0; a2 < accs.size(); a2++) {
+                accs2[a2].kind = (accs[a2].kind == ACC_COUNT_STAR || accs[a2].kind == ACC_COUNT) ? ACC_SUM_I : accs[a2].kind;
+                accs2[a2].col = (int)a2;
+            }
+            for (int attempt = 0;; attempt++) {
+                int rc = T.init(ctx, nk, (int)accs.size(), accs2, cap); if (rc) return rc;
+                for (size_t k = 0; k < v.chunks.size(); k++) {
+                    if (cs[k].n == 0) continue;
+                    const PanePartial& pp = cache[v.chunks[k].get()];
+                    if (pp.n == 0) continue;
+                    AggInput in; memset(&in, 0, sizeof in);
+                    in.n_rows = pp.n;
+                    for (int hk = 0; hk < nk; hk++) { ProgCol pc; pc.data = pp.keys[hk]->p; pc.vmask = pp.valid32->p; pc.vwidth = 4; pc.vbit = hk; pc.width = 8; pc.pad = 0; in.keys[hk] = pc; }
+                    for (size_t a2 = 0; a2 < accs.size(); a2++) { ProgCol pc; pc.data = pp.accs[a2]->p; pc.vmask = nullptr; pc.vwidth = 0; pc.vbit = 0; pc.width = 8; pc.pad = 0; in.vals[a2] = pc; }
+                    in.range_col.data = pp.keys[nk]->p; in.range_col.vmask = nullptr; in.range_col.width = 8;
+                    in.range_lo = v.lo_us / pane_us; in.range_hi = v.hi_us / pane_us; in.has_range = 1;
+                    rc = T.update(in); if (rc) return rc;
+                }
+                bool overflow = false;
+                rc = T.finish(&n_groups, &overflow); if (rc) return rc;
+                if (!overflow) break;
+                if (attempt > 12) return fail(DX_ERR_CAPACITY, "aggregation table overflow");
+                cap = T.capacity * 4;
+            }
+        } else
         for (int attempt = 0;; attempt++) {
             int rc = T.init(ctx, (int)hashed.size(), (int)val_exprs.size(), accs, cap); if (rc) return rc;
             for (size_t k = 0; k < v.chunks.size(); k++) {
                 if (cs[k].n == 0) continue;
-                const DxTable* ch = v.chunks[k].get();
-                BindScope sc = scope_for(ch, core);
-                AggInput in; memset(&in, 0, sizeof in);
-                in.sel = cs[k].filtered ? cs[k].sel->as<long long>() : nullptr; in.n_rows = cs[k].n;
-                if (fuse_range) {
-                    std::string err; int tc = dx_resolve_column(sc, std::vector<std::string>{v.ts_col}, &err);
-                    if (tc < 0) return fail(DX_ERR_ARG, err);
-                    const DxColumn& c = ch->cols[tc];
-                    if (!c.data || c.type != DX_T_TS) return fail(DX_ERR_UNSUPPORTED, "window timestamp column must be a materialised timestamp");
-                    in.range_col.data = c.data->p; in.range_col.vmask = c.vmask ? c.vmask->p : nullptr; in.range_col.vwidth = c.vwidth;
-                    in.range_col.vbit = c.vbit; in.range_col.width = 8;
-                    in.range_lo = v.lo_us; in.range_hi = v.hi_us; in.has_range = 1;
-                }
-                std::vector<DevBufP> temps; DevBufP tmask; std::vector<DxColumn> string_keys;
-                auto col_desc = [&](const DxColumn& c) { ProgCol pc; pc.data = c.data->p; pc.vmask = c.vmask ? c.vmask->p : nullptr; pc.vwidth = c.vwidth; pc.vbit = c.vbit; pc.width = dx_type_width(c.type); pc.pad = 0; return pc; };
-                auto eval_temp = [&](const ExprP& e, int* type_out, ProgCol* pc) -> int {
-                    ExprPrograms P; int rc2 = dx_compile_expr(ctx, sc, e, &P); if (rc2) return rc2;
-                    DevPrograms D; rc2 = dx_upload_programs(ctx, &P, &D); if (rc2) return rc2;
-                    int ty = P.result_type[0] == DX_T_NULL ? DX_T_I64 : P.result_type[0];
-                    DevBufP b = make_buf(ctx, (size_t)ch->n_rows * dx_type_width(ty)); temps.push_back(b);
-                    if (!tmask) { tmask = make_buf(ctx, (size_t)ch->n_rows * 4); DX_CUDA(ctx, cudaMemsetAsync(tmask->p, 0, (size_t)ch->n_rows * 4, ctx->stream)); }
-                    int bit = (int)temps.size() - 1;
-                    if (bit >= 32) return fail(DX_ERR_UNSUPPORTED, "too many computed group/aggregate expressions");
-                    rc2 = dx_eval_column(ctx, D, 0, ch->n_rows, nullptr, b->p, dx_type_width(ty), tmask->as<uint32_t>(), bit); if (rc2) return rc2;
-                    pc->data = b->p; pc->vmask = tmask->p; pc->vwidth = 4; pc->vbit = bit; pc->width = dx_type_width(ty); pc->pad = 0;
-                    *type_out = ty; return DX_OK;
-                };
-                for (size_t hk = 0; hk < hashed.size(); hk++) {
-                    KeySpec& ks = keys[hashed[hk]];
-                    if (ks.expr->kind == EK::Col) {
-                        std::string err; int ci = dx_resolve_column(sc, ks.expr->parts, &err);
-                        if (ci < 0) return fail(DX_ERR_ARG, err);
-                        const DxColumn& c = ch->cols[ci];
-                        if (!c.data) return fail(DX_ERR_UNSUPPORTED, "group key constant in one batch and materialised in another");
-                        in.keys[hk] = col_desc(c); key_type[hashed[hk]] = c.type;
-                        if (c.type == DX_T_STR) {
-                            if (key_dict[hashed[hk]] && key_dict[hashed[hk]] != c.dict) return fail(DX_ERR_UNSUPPORTED, "group key dictionaries differ between batches");
-                            key_dict[hashed[hk]] = c.dict;
-                        }
-                    } else if (needs_string_engine(ks.expr, sc)) {
-                        // CONCAT(...) / CAST AS STRING / user function as a group key (e.g. SELECT DISTINCT ... CONCAT(...) AS Pivot1)
-                        DxColumn full; rc = eval_string_full(sc, ch, ks.expr, stmt_name + "#key" + std::to_string(hashed[hk]), &full); if (rc) return rc;
-                        if (!full.data || full.all_null) return fail(DX_ERR_UNSUPPORTED, "constant string expression as a group key");
-                        string_keys.push_back(full);     // keeps the buffers alive until the kernel has run
-                        in.keys[hk] = col_desc(full); key_type[hashed[hk]] = full.type;
-                        if (key_dict[hashed[hk]] && key_dict[hashed[hk]] != full.dict) return fail(DX_ERR_UNSUPPORTED, "group key dictionaries differ between batches");
-                        key_dict[hashed[hk]] = full.dict;
-                    } else { int ty; rc = eval_temp(ks.expr, &ty, &in.keys[hk]); if (rc) return rc; key_type[hashed[hk]] = ty; }
-                }
-                for (size_t vi = 0; vi < val_exprs.size(); vi++) {
-                    bool done = false;
-                    if (val_exprs[vi]->kind == EK::Col) {
-                        std::string err; int ci = dx_resolve_column(sc, val_exprs[vi]->parts, &err);
-                        if (ci >= 0 && ch->cols[ci].data && !ch->cols[ci].all_null) { in.vals[vi] = col_desc(ch->cols[ci]); done = true; }
-                    }
-                    if (!done) { int ty; rc = eval_temp(val_exprs[vi], &ty, &in.vals[vi]); if (rc) return rc; }
-                }
+                InputHold hold; AggInput in;
+                rc = make_input(v.chunks[k].get(), cs[k].filtered ? cs[k].sel->as<long long>() : nullptr, cs[k].n, fuse_range, &in, &hold); if (rc) return rc;
                 rc = T.update(in); if (rc) return rc;
-                DX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));   // temps die with this scope
+                DX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));   // computed columns die with this scope
             }
             bool overflow = false;
-            rc = T.finish(&n_groups, &overflow); if (rc) return rc;
+            int rc2 = T.finish(&n_groups, &overflow); if (rc2) return rc2;
             if (!overflow) break;
             if (attempt > 12) return fail(DX_ERR_CAPACITY, "aggregation table overflow");
             cap = T.capacity * 4;
@@ -1339,6 +1442,7 @@ int dx_flow_build(dx_ctx* ctx, const char* conf_text, const char* schema_json, c
         }
     }
     { auto g = F->conf.find(root + "gpu.genericrules"); F->generic_rules_only = g != F->conf.end() && lower(g->second) == "true"; }
+    { auto g = F->conf.find(root + "gpu.panepartials"); F->pane_partials_off = g != F->conf.end() && lower(g->second) == "false"; }
     auto wm = F->conf.find(root + "watermark"); auto tc = F->conf.find(root + "timestampcolumn");
     F->windows_enabled = !F->windows.empty() && wm != F->conf.end() && tc != F->conf.end();
     if (F->windows_enabled) {
@@ -1422,9 +1526,14 @@ int dx_flow::project(const uint8_t* json, int64_t n_bytes, const int64_t* offset
 int dx_flow::process(const std::string& name_space, const uint8_t* json, int64_t n_bytes, const int64_t* offsets, int64_t n_events,
                      int memory_kind, long long batch_ms, long long interval_ms, long long now_ms, dx_result** out) {
     DxTableP projected;
+    const auto t0 = std::chrono::steady_clock::now();
     int rc = project(json, n_bytes, offsets, n_events, memory_kind, now_ms, &projected);
     if (rc) return rc;
-    return route(name_space, projected, batch_ms, interval_ms, now_ms, out);
+    const auto t1 = std::chrono::steady_clock::now();
+    rc = route(name_space, projected, batch_ms, interval_ms, now_ms, out);
+    ctx->counters["host_us:project"] += std::chrono::duration_cast<std::chrono::microseconds>(t1 - t0).count();
+    ctx->counters["host_us:route"] += std::chrono::duration_cast<std::chrono::microseconds>(std::chrono::steady_clock::now() - t1).count();
+    return rc;
 }
 
 // route() on an already projected table (CommonProcessorFactory.scala:131-328).  Multi-GPU runs call this on the
@@ -1485,7 +1594,7 @@ int dx_flow::route(const std::string& name_space, const DxTableP& projected, lon
         for (auto it = NS.past_batches.begin(); it != NS.past_batches.end();) { if (it->first <= cut) it = NS.past_batches.erase(it); else ++it; }
         std::vector<DxTableP> U; U.push_back(cur);
         if (NS.past_batches.size() > 1) for (auto& kv : NS.past_batches) U.push_back(kv.second);   // the reference's size>1 quirk (CPF:198-201)
-        auto ranged = [&](long long lo_ms, long long hi_ms) { View v; v.chunks = U; v.ranged = true; v.ts_col = ts_column; v.lo_us = lo_ms * 1000; v.hi_us = hi_ms * 1000; return v; };
+        auto ranged = [&](long long lo_ms, long long hi_ms) { View v; v.chunks = U; v.ranged = true; v.ts_col = ts_column; v.lo_us = lo_ms * 1000; v.hi_us = hi_ms * 1000; v.pane_us = interval_ms * 1000; return v; };
         views["DataXProcessedInput_Window"] = ranged(S, E);
         for (auto& w : windows) views[w.first] = ranged(E - w.second * 1000, E);
         views["DataXProcessedInput"] = ranged(E - (interval_ms / 1000) * 1000, E);
@@ -1499,7 +1608,9 @@ int dx_flow::route(const std::string& name_space, const DxTableP& projected, lon
     for (auto& kv : ref_tables) { View v; v.chunks.push_back(kv.second); views[kv.first] = v; }
     for (auto& cmd : transform.commands) {
         X.stmt_name = cmd.name;
+        const auto t_stmt = std::chrono::steady_clock::now();
         DxTableP res; rc = X.exec_statement(cmd.stmt, &res); if (rc) return rc;
+        ctx->counters["host_us:stmt:" + cmd.name] += std::chrono::duration_cast<std::chrono::microseconds>(std::chrono::steady_clock::now() - t_stmt).count();
         res->name = cmd.name;
         auto st = state_tables.find(cmd.name);
         if (st != state_tables.end()) {

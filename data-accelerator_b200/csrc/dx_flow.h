@@ -39,6 +39,19 @@ struct View {
     bool ranged = false;
     std::string ts_col;
     long long lo_us = 0, hi_us = 0;
+    long long pane_us = 0;          // batch interval: windows whose ends are multiples of it can be served from per-batch pane partials
+};
+
+// Per cached batch and statement: the batch's rows pre-aggregated by (group keys, pane = floor(ts / interval)).
+// A window aggregate then combines one partial per cached batch instead of rescanning every cached event each interval
+// (the reference rescans: CommonProcessorFactory.scala:203-227 re-filters the union of all cached batches per window).
+struct PanePartial {
+    DxTableP chunk;                 // keeps the batch (and with it the cache key, its address) alive
+    std::string sig;                // keys / values / accumulators / pane width this partial was built for
+    std::vector<DevBufP> keys;      // n_keys + 1 arrays of int64 (last = pane)
+    DevBufP valid32;                // bit k set: key k not NULL
+    std::vector<DevBufP> accs;      // raw accumulators, one array per accumulator
+    int64_t n = 0;
 };
 
 typedef std::map<std::string, View, CiLess> ViewMap;
@@ -80,6 +93,8 @@ struct dx_flow {
     std::vector<std::string> outputs;
     std::map<std::string, NamespaceState> ns;
     std::map<std::string, unsigned long long> agg_capacity_hint;  // per statement name
+    std::map<std::string, std::map<const DxTable*, PanePartial>> pane_partials;   // partial signature -> cached batch -> partial
+    bool pane_partials_off = false; // conf datax.job.process.gpu.panepartials=false: always rescan (tests compare both)
     std::string last_error;
     // user functions evaluated on the host side of the boundary, once per distinct dictionary entry
     typedef int (*udf1_fn)(void* user, const char* arg, int64_t arg_len, char* out, int64_t out_cap, int64_t* out_len);

@@ -159,6 +159,41 @@ def test_time_windows_with_reference_quirks(dx, ctx, wm):
     g.close()
 
 
+def test_pane_partials_match_rescan(dx, ctx):
+    """Window aggregates served from per-batch pane partials (the default when the window ends fall on interval
+    boundaries) against the full rescan of every cached batch (gpu.panepartials=false) and against the oracle:
+    integer and double aggregates, a string group key, NULL keys and values, late and future events."""
+    tr = """--DataXQuery--
+ByKey = SELECT deviceDetails.deviceId, deviceDetails.deviceType, COUNT(*) AS Count, COUNT(deviceDetails.status) AS N, SUM(deviceDetails.status) AS S,
+    MIN(deviceDetails.temperature) AS Tmin, MAX(deviceDetails.temperature) AS Tmax, AVG(deviceDetails.humidity) AS Havg, SUM(deviceDetails.temperature) AS Tsum,
+    MAX(eventTimeStamp) AS Last FROM DataXProcessedInput_5minutes GROUP BY deviceDetails.deviceId, deviceDetails.deviceType
+--DataXQuery--
+ByHome = SELECT deviceDetails.homeId, MIN(deviceDetails.eventTime) AS FirstMs, COUNT(*) AS Count FROM DataXProcessedInput_3minutes GROUP BY deviceDetails.homeId
+--DataXQuery--
+Total = SELECT COUNT(*) AS Count, AVG(deviceDetails.temperature) AS Tavg FROM DataXProcessedInput_5minutes
+"""
+    windows = [("DataXProcessedInput_5minutes", "5 minutes"), ("DataXProcessedInput_3minutes", "3 minutes")]
+    conf = dx.flowgen.conf_text("pane", timestamp_column="eventTimeStamp", watermark="60 second", windows=windows)
+    g, o = both(dx, ctx, conf, SCHEMA2, [PROJ_TS], tr)
+    g_rescan = dx.CommonProcessorFactory.createProcessor(ctx, conf + "datax.job.process.gpu.panepartials=false\n", SCHEMA2, [PROJ_TS], tr)
+    ctx.take_counter("k3_partial_rows_built")
+    for b in range(9):
+        T = T0 + b * I
+        if b == 4:
+            data = to_ndjson(all_records(1500, seed=33))          # a batch of adversarial events: NULL timestamps, keys and values
+        else:
+            data = gen(dx, 3000, first=b * 3000, shape=2, n_keys=150, base=T, late=30, future=20)
+        ro, mo = o.process(data, T, I)
+        for proc in (g, g_rescan):
+            rg = proc.process_json(data, T, I)
+            assert rg.metrics == mo
+            for name in ("ByKey", "ByHome", "Total"):
+                assert_same_rows(rg.table(name), ro[name], dx)
+            rg.release()
+    assert ctx.take_counter("k3_partial_rows_built") > 0           # the partial path really ran
+    g.close(); g_rescan.close()
+
+
 def test_state_table_append_with_retention_and_upsert(dx, ctx):
     tr = """--DataXQuery--
 PerKey = SELECT deviceDetails.deviceId, deviceDetails.homeId, MAX(eventTimeStamp) AS WindowEnd, COUNT(*) AS Count

@@ -92,6 +92,7 @@ def main():
     kg_ms, kg_n = ctx.take_stage_ms("k_gather")
     k3_rows = ctx.take_counter("k3_rows")
     g_bytes = ctx.take_counter("gather_bytes")
+    host_us = {k: ctx.take_counter("host_us:" + k) for k in ["project", "route"] + ["stmt:" + nm for nm in rows_out]}
     total_events = n * args.batches
     row_bytes = 33 if args.workload == "c3" else 8 * 4          # keys + ts + value (+validity) per visited row
     out = {"metric": "events/sec per micro-batch (%s)" % ("window aggregates C3" if args.workload == "c3" else "state-table merge C4"),
@@ -103,7 +104,7 @@ def main():
                            "rows_per_s": round(k3_rows / max(k3_ms, 1e-9) * 1e3, 1)},
            "k_gather": {"launches": kg_n, "total_ms": round(kg_ms, 2), "bytes": g_bytes, "gbs": round(g_bytes / max(kg_ms, 1e-9) / 1e6, 2),
                         "frac_of_measured_hbm": round(g_bytes / max(kg_ms, 1e-9) / 1e6 / peak, 4)},
-           "k1_decode_total_ms": round(k1_ms, 2), "wall_s": round(wall, 2), "result_rows_last_batch": rows_out,
+           "k1_decode_total_ms": round(k1_ms, 2), "host_ms_per_batch": {k: round(v / 1e3 / args.batches, 3) for k, v in host_us.items()}, "wall_s": round(wall, 2), "result_rows_last_batch": rows_out,
            "note": "per-kernel timing enabled (host sync per kernel); process time by CUDA events around each batch on the library stream"}
     print(json.dumps(out))
 
