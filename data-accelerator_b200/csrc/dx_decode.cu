@@ -482,10 +482,11 @@ int dx_decoder::init(dx_ctx* c, const std::string& schema_json) {
         if (lit_used + Lp > DX_LITS_BYTES) { tmpl_ok = false; break; }
         memcpy(reinterpret_cast<char*>(hs.lits) + lit_used, b.seg_lits[i].data(), L);
         hs.segs[i].lit_off = (uint16_t)lit_used; hs.segs[i].lit_len = (uint16_t)L;
-        hs.segs[i].type = b.seg_types[i]; hs.segs[i].leaf = b.seg_leaves[i];
+        hs.segs[i].type = (int16_t)b.seg_types[i]; hs.segs[i].leaf = (int16_t)b.seg_leaves[i];
+        hs.segs[i].tail_mask = (L & 3) ? ((1u << ((L & 3) << 3)) - 1u) : 0u;
         lit_used += Lp; hs.n_segs++;
     }
-    if (!tmpl_ok) { hs.n_segs = 1; hs.segs[0].lit_off = 0; hs.segs[0].lit_len = 4; hs.segs[0].type = 0; memcpy(hs.lits, "\x01\x01\x01\x01", 4); }
+    if (!tmpl_ok) { hs.n_segs = 1; hs.segs[0].lit_off = 0; hs.segs[0].lit_len = 4; hs.segs[0].type = 0; hs.segs[0].tail_mask = 0; memcpy(hs.lits, "\x01\x01\x01\x01", 4); }
     for (int k = 0; k < hs.n_leaves; k++) leaf_types.push_back(hs.leaf_type[k]);
     dev_schema = DevBuf(c, sizeof(DSchemaDev));
     DX_CUDA(c, cudaMemcpyAsync(dev_schema.p, &hs, sizeof hs, cudaMemcpyHostToDevice, c->stream));

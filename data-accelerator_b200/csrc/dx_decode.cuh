@@ -23,7 +23,7 @@
 
 struct DField { uint16_t name_off, name_len; int32_t type; int32_t target; };
 struct DStruct { int32_t first_field, n_fields, first_leaf, n_leaves; };
-struct DSeg { uint16_t lit_off, lit_len; int32_t type; int32_t leaf; };   // type 0: trailing literal only
+struct DSeg { uint16_t lit_off, lit_len; int16_t type, leaf; uint32_t tail_mask; };   // type 0: trailing literal only; tail_mask: the 1..3 bytes past the last whole literal word (0 = none)
 
 struct DSchemaDev {
     DStruct structs[DX_MAX_STRUCTS];

@@ -29,7 +29,7 @@ static __device__ __forceinline__ uint32_t digits4(uint32_t x, int m) {
     return (p & 0xFFu) * 100u + (p >> 16);
 }
 
-static __device__ const uint32_t dx_pow10_u32[9] = {1u, 10u, 100u, 1000u, 10000u, 100000u, 1000000u, 10000000u, 100000000u};
+static __constant__ uint32_t dx_pow10_u32[9] = {1u, 10u, 100u, 1000u, 10000u, 100000u, 1000000u, 10000000u, 100000000u};
 
 // Parses a run of digits at pos, four bytes per step through a carried pair of aligned words.
 // Returns the digit count (0 = none, -1 = more than 18) and the value.
@@ -72,29 +72,18 @@ static __device__ __forceinline__ bool fast_record_warp(const uint8_t* buf, uint
         __syncwarp();
         const DSeg sg = a.segs[si];                      // warp-uniform: constant-bank loads
         if (ok) {
-            const uint32_t* lw = a.lits + (sg.lit_off >> 2);
-            const uint32_t L = sg.lit_len, nw = L >> 2, sh = (pos & 3u) << 3;
-            const uint32_t* wp = reinterpret_cast<const uint32_t*>(buf + (pos & ~3u));
-            uint32_t lo = wp[0], diff = 0, hi;
-            uint32_t k = 0;
-            for (; k + 8 <= nw; k += 8) {   // long literals: eight words per trip
-#pragma unroll
-                for (int u = 0; u < 8; u++) { hi = wp[k + u + 1]; diff |= __funnelshift_r(lo, hi, sh) ^ lw[k + u]; lo = hi; }
-            }
-            wp += k; lw += k;
-#define DX_LIT_WORD(i) hi = wp[(i) + 1]; diff |= __funnelshift_r(lo, hi, sh) ^ lw[i]; lo = hi;
-            switch (nw - k) {               // the remaining 0..7 words as straight-line code, exactly as many as needed
-            case 7: DX_LIT_WORD(0) wp++; lw++;
-            case 6: DX_LIT_WORD(0) wp++; lw++;
-            case 5: DX_LIT_WORD(0) wp++; lw++;
-            case 4: DX_LIT_WORD(0) wp++; lw++;
-            case 3: DX_LIT_WORD(0) wp++; lw++;
-            case 2: DX_LIT_WORD(0) wp++; lw++;
-            case 1: DX_LIT_WORD(0) wp++; lw++;
-            default: break;
-            }
+            // literal: whole words through a carried funnel shift (data word i+1 is loaded once and reused as the low half of
+            // the next compare); every load sits at a compile-time offset from the block base, so no pointer is advanced per word
+            // (indices, not pointers: the literal words stay constant-bank loads c[0][reg + imm])
+            uint32_t li = sg.lit_off >> 2, wo = pos & ~3u, nw = sg.lit_len >> 2;
+            const uint32_t L = sg.lit_len, sh = (pos & 3u) << 3;
+            uint32_t lo = *reinterpret_cast<const uint32_t*>(buf + wo), diff = 0, hi;
+#define DX_LIT_WORD(i) hi = *reinterpret_cast<const uint32_t*>(buf + wo + 4 * ((i) + 1)); diff |= __funnelshift_r(lo, hi, sh) ^ a.lits[li + (i)]; lo = hi;
+            while (nw >= 4) { DX_LIT_WORD(0) DX_LIT_WORD(1) DX_LIT_WORD(2) DX_LIT_WORD(3) wo += 16; li += 4; nw -= 4; }
+            if (nw >= 2) { DX_LIT_WORD(0) DX_LIT_WORD(1) wo += 8; li += 2; nw -= 2; }
+            if (nw) { DX_LIT_WORD(0) wo += 4; li += 1; }
 #undef DX_LIT_WORD
-            if (L & 3u) { hi = wp[1]; diff |= (__funnelshift_r(lo, hi, sh) ^ lw[0]) & ((1u << ((L & 3u) << 3)) - 1u); }
+            if (sg.tail_mask) { hi = *reinterpret_cast<const uint32_t*>(buf + wo + 4); diff |= (__funnelshift_r(lo, hi, sh) ^ a.lits[li]) & sg.tail_mask; }
             ok = diff == 0;
             pos += L;
         }

@@ -8,7 +8,7 @@
 #include "dx_pow5_table.h"
 
 // ------------------------------- decimal -> double -------------------------------------
-static __device__ const double dx_pow10_exact[23] = {1e0, 1e1, 1e2, 1e3, 1e4, 1e5, 1e6, 1e7, 1e8, 1e9, 1e10, 1e11,
+static __constant__ double dx_pow10_exact[23] = {1e0, 1e1, 1e2, 1e3, 1e4, 1e5, 1e6, 1e7, 1e8, 1e9, 1e10, 1e11,
                                               1e12, 1e13, 1e14, 1e15, 1e16, 1e17, 1e18, 1e19, 1e20, 1e21, 1e22};
 
 // Eisel-Lemire: w * 10^q -> nearest binary64 bits (w != 0).  Returns false if q out of the table.

@@ -3,6 +3,7 @@
 #include <stdint.h>
 #include <string.h>
 #define __device__
+#define __constant__ const
 #define __forceinline__ inline
 #define __noinline__
 static inline int __clzll(long long x) { return x == 0 ? 64 : __builtin_clzll((unsigned long long)x); }
