@@ -1215,7 +1215,7 @@ struct Exec {
                 }
                 PanePartial pp; pp.chunk = chp; pp.sig = sig;
                 // sized from the previous batch's partial (groups are stable from batch to batch), else from the row count
-                unsigned long long pcap = 1024, pwant = (unsigned long long)std::min<int64_t>(chp->n_rows, 1 << 24) * 2;
+                unsigned long long pcap = 1024, pwant = (unsigned long long)std::min<int64_t>(chp->n_rows, 1 << 22) * 2;   // first guess; an overflow retries 4x larger
                 auto phint = F->agg_capacity_hint.find("#pane|" + sig);
                 if (phint != F->agg_capacity_hint.end()) pwant = std::min(pwant, phint->second);
                 while (pcap < pwant) pcap <<= 1;

@@ -78,6 +78,7 @@ def main():
         groups = r.table("Tumbling").num_rows
         r.release(); ctx.free(ptr)
     timed = args.batches - 1
+    host = {k: round(ctx.take_counter("host_us:" + k) / 1e3 / args.batches, 3) for k in ("route", "stmt:Tumbling", "stmt:Sliding5m")}
     g = torch.tensor([groups], device="cuda", dtype=torch.int64)
     dist.all_reduce(g)
     if rank == 0:
@@ -88,7 +89,7 @@ def main():
                           "wire_bytes_out_per_gpu_per_batch": wire // max(timed, 1), "rec_bytes": 8 * rec_words,
                           "all_to_all_gbs_per_gpu_per_direction": round(wire / max(timed, 1) / max(a2a_ms / timed, 1e-9) / 1e6, 2),
                           "nvlink_peak_gbs": 900, "frac_of_nvlink": round(wire / max(timed, 1) / max(a2a_ms / timed, 1e-9) / 1e6 / 900, 4),
-                          "tumbling_groups_all_ranks": int(g.item()), "scaling": "weak"}))
+                          "tumbling_groups_all_ranks": int(g.item()), "rank0_host_ms_per_batch": host, "scaling": "weak"}))
     dist.barrier()
     dist.destroy_process_group()
 

@@ -56,12 +56,15 @@ def main():
     ap.add_argument("--batches", type=int, default=100)
     ap.add_argument("--events-per-batch", type=int, default=5_000_000)
     ap.add_argument("--keys", type=int, default=1_000_000)
+    ap.add_argument("--no-panes", action="store_true", help="rescan every cached batch per window (gpu.panepartials=false)")
     args = ap.parse_args()
     import torch
     import dxgpu as dx
     import dxo
     ctx = dx.Context(0)
     conf, tr = c3_flow(dx) if args.workload == "c3" else c4_flow(dx)
+    if args.no_panes:
+        conf += "datax.job.process.gpu.panepartials=false\n"
     flow = dx.CommonProcessorFactory.createProcessor(ctx, conf, dxo.iot_schema_json(1), [PROJ], tr)
     stream = torch.cuda.ExternalStream(ctx.stream(), device=torch.device("cuda", 0))
     peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"] if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else 6650.0
