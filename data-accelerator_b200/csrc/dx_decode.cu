@@ -296,7 +296,11 @@ __global__ void __launch_bounds__(K1_NT, K1_MIN_CTAS) k1_decode(const __grid_con
                     const bool overflow = has && o.row >= a.max_rows;
                     if (overflow) c_err |= DXF_ROW_OVERFLOW;
                     const bool live = has && !overflow;
+#ifdef K1_SKIP_PARSE     /* tuning experiment only (tools/build_variant.sh): cost of scan + row indexing without the record parse */
+                    bool ok = live; o.valid = all_valid; if (live) reinterpret_cast<long long*>(a.cols[0])[o.row] = st + en;
+#else
                     bool ok = fast_record_warp(buf, st, en, live && in_smem, a, o);
+#endif
                     if (live) {
                         if (ok) c_fast++;
                         else if (in_smem) ok = g_record(buf + st, buf + en, S, o);
@@ -317,15 +321,27 @@ __global__ void __launch_bounds__(K1_NT, K1_MIN_CTAS) k1_decode(const __grid_con
             }
         } else {
             // --- caller-provided framing: records whose first byte lies in [lo, hi) ---
-            if (tid == 0) {
-                // first record r with skew + offsets[r] >= lo  (offsets ascending, n_rows+1 entries)
-                long long l = 0, h = a.max_rows;
-                while (l < h) { long long m = (l + h) >> 1; if ((long long)a.skew + a.offsets[m] >= lo) h = m; else l = m + 1; }
-                s_r0 = l;
-                long long l2 = l, h2 = a.max_rows;
-                const long long hi = lo + K1_T;
-                while (l2 < h2) { long long m = (l2 + h2) >> 1; if ((long long)a.skew + a.offsets[m] >= hi) h2 = m; else l2 = m + 1; }
-                s_rowbase = l2;
+            if (warp == 0) {
+                // first record r with skew + offsets[r] >= target (offsets ascending, n_rows+1 entries): a 33-way search, the 32
+                // lanes probing evenly spaced entries per round, so a tile costs ~5 dependent global loads instead of ~25
+                auto lower_bound = [&](long long l, long long h, long long target) -> long long {
+                    while (l < h) {
+                        const long long step = (h - l + 32) / 33;
+                        const long long idx = l + (long long)(lane + 1) * step - 1;
+                        const bool ge = idx >= h || (long long)a.skew + a.offsets[idx] >= target;
+                        const unsigned b = __ballot_sync(0xffffffffu, ge);
+                        const int f = b ? __ffs(b) - 1 : 32;
+                        const long long pf = l + (long long)(f + 1) * step - 1;          // first probe that is >= target (if f < 32)
+                        const long long nl = f > 0 ? l + (long long)f * step : l;          // one past the last probe that is < target
+                        long long nh = h;
+                        if (f < 32 && pf < h) nh = pf;
+                        l = nl; h = nh;
+                    }
+                    return l;
+                };
+                const long long r_lo = lower_bound(0, a.max_rows, lo);
+                const long long r_hi = lower_bound(r_lo, a.max_rows, lo + K1_T);
+                if (lane == 0) { s_r0 = r_lo; s_rowbase = r_hi; }
             }
             __syncthreads();
             rec0 = s_r0; n_rec = s_rowbase - rec0;
