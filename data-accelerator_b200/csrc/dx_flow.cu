@@ -1183,6 +1183,79 @@ struct Exec {
         for (int hk : hashed) if (keys[hk].expr->kind != EK::Col) plain_keys = false;
         const bool pane_mode = fuse_range && !F->pane_partials_off && pane_us > 0 && v.chunks.size() >= 2 && !stmt_name.empty() && plain_keys &&
                                v.lo_us % pane_us == 0 && v.hi_us % pane_us == 0 && (int)hashed.size() + 1 <= DX_AGG_MAX_KEYS;
+        // column arrays filled directly by the shared-memory path (otherwise extracted from T below)
+        std::vector<DevBufP> pre_k, pre_a; DevBufP pre_knull; bool have_cols = false;
+        const bool pane_smem = pane_mode && !F->pane_smem_off && dx_aggp_fits((int)hashed.size(), (int)accs.size());
+        if (pane_smem) {
+            std::string sig = "P|" + std::to_string(pane_us) + "|" + v.ts_col;
+            for (int hk : hashed) sig += "|k:" + to_string(keys[hk].expr);
+            for (auto& ve : val_exprs) sig += "|v:" + to_string(ve);
+            for (auto& ac : accs) sig += "|a:" + std::to_string(ac.kind) + "," + std::to_string(ac.col);
+            auto& cache = F->pane_partials_p[sig];
+            const int nk = (int)hashed.size();
+            for (auto it2 = cache.begin(); it2 != cache.end();) {
+                bool live = false; for (auto& chp : v.chunks) if (chp.get() == it2->first) live = true;
+                if (!live) it2 = cache.erase(it2); else ++it2;
+            }
+            int& P = F->pane_P[sig];
+            for (int round = 0;; round++) {
+                if (round > 6) return fail(DX_ERR_CAPACITY, "pane partitions overflow");
+                bool again = false;
+                for (size_t k = 0; k < v.chunks.size() && !again; k++) {
+                    if (cs[k].n == 0) continue;
+                    const DxTableP& chp = v.chunks[k];
+                    if (cache.count(chp.get())) {       // only the key types / dictionaries of this batch's columns are needed
+                        BindScope sc = scope_for(chp.get(), core);
+                        for (size_t hk = 0; hk < hashed.size(); hk++) {
+                            std::string err; int ci = dx_resolve_column(sc, keys[hashed[hk]].expr->parts, &err);
+                            if (ci < 0) return fail(DX_ERR_ARG, err);
+                            key_type[hashed[hk]] = chp->cols[ci].type;
+                            if (chp->cols[ci].type == DX_T_STR) {
+                                if (key_dict[hashed[hk]] && key_dict[hashed[hk]] != chp->cols[ci].dict) return fail(DX_ERR_UNSUPPORTED, "group key dictionaries differ between batches");
+                                key_dict[hashed[hk]] = chp->cols[ci].dict;
+                            }
+                        }
+                        continue;
+                    }
+                    InputHold hold; AggInput in;
+                    int rc = make_input(chp.get(), nullptr, chp->n_rows, true, &in, &hold); if (rc) return rc;
+                    if (P == 0) { P = 256; while (P < 16384 && (long long)P * 1200 < chp->n_rows) P <<= 1; }
+                    in.has_range = 0; in.pane_us = pane_us;
+                    PanePartialP pp; pp.chunk = chp;
+                    bool ovf = false;
+                    rc = dx_aggp_build(ctx, in, nk, (int)val_exprs.size(), accs, P, &pp.ap, &ovf); if (rc) return rc;
+                    if (ovf) { again = true; break; }
+                    ctx->counters["k3_partial_rows_built"] += (long long)pp.ap.n;
+                    cache[chp.get()] = std::move(pp);
+                }
+                if (!again) {
+                    std::vector<const AggPPartial*> parts; long long rows = 0;
+                    for (size_t k = 0; k < v.chunks.size(); k++) if (cs[k].n) { const AggPPartial* ap = &cache[v.chunks[k].get()].ap; parts.push_back(ap); rows += ap->n; }
+                    long long maxg = rows;
+                    auto hint2 = F->agg_capacity_hint.find(stmt_name);
+                    if (hint2 != F->agg_capacity_hint.end()) maxg = std::min<long long>(rows, (long long)hint2->second);
+                    for (int attempt = 0; attempt < 2; attempt++) {
+                        const size_t nr = (size_t)(maxg > 0 ? maxg : 1);
+                        pre_k.assign(nk, nullptr); pre_a.assign(accs.size(), nullptr);
+                        long long* kp[DX_AGG_MAX_KEYS]; unsigned long long* ap2[DX_AGG_MAX_ACCS];
+                        for (int k2 = 0; k2 < nk; k2++) { pre_k[k2] = make_buf(ctx, nr * 8); kp[k2] = pre_k[k2]->as<long long>(); }
+                        for (size_t a2 = 0; a2 < accs.size(); a2++) { pre_a[a2] = make_buf(ctx, nr * 8); ap2[a2] = pre_a[a2]->as<unsigned long long>(); }
+                        pre_knull = make_buf(ctx, nr * 8);
+                        long long ng = 0; bool ovf = false;
+                        int rc = dx_aggp_combine(ctx, parts, nk, accs, v.lo_us / pane_us, v.hi_us / pane_us, maxg, kp, pre_knull->as<unsigned long long>(), ap2, &ng, &ovf);
+                        if (rc) return rc;
+                        if (!ovf) { n_groups = (unsigned long long)ng; have_cols = true; break; }
+                        if (maxg < rows) { ctx->counters["k3p_output_regrows"]++; maxg = rows; continue; }     // the remembered size was too small: the row count always suffices
+                        again = true; break;                              // a partition overflowed its shared table
+                    }
+                }
+                ctx->counters["k3p_partitions"] = P;
+                if (!again) break;
+                ctx->counters["k3p_repartitions"]++;
+                P = std::min(P * 4, 1 << 16); cache.clear();             // finer partitions; every partial of this signature is rebuilt
+                if (P >= (1 << 16) && round > 3) return fail(DX_ERR_CAPACITY, "pane partitions overflow");
+            }
+        } else
         if (pane_mode) {
             std::string sig = std::to_string(pane_us) + "|" + v.ts_col;     // the views of one flow range over the same cached batches
             for (int hk : hashed) sig += "|k:" + to_string(keys[hk].expr);
@@ -1286,7 +1359,7 @@ struct Exec {
             if (attempt > 12) return fail(DX_ERR_CAPACITY, "aggregation table overflow");
             cap = T.capacity * 4;
         }
-        if (!stmt_name.empty()) { unsigned long long h = 1024; while (h < n_groups * 2 + 16) h <<= 1; F->agg_capacity_hint[stmt_name] = std::max(h, std::min(T.capacity, h * 2)); }
+        if (!stmt_name.empty()) { unsigned long long h = 1024; while (h < n_groups * 2 + 16) h <<= 1; F->agg_capacity_hint[stmt_name] = have_cols ? h : std::max(h, std::min(T.capacity, h * 2)); }
 
         // global aggregate over zero rows -> one row (count 0, others NULL)
         const bool global = core.group_by.empty() && !core.distinct;
@@ -1297,9 +1370,16 @@ struct Exec {
         std::vector<DevBufP> kbufs(hashed.size()), abufs(accs.size());
         DevBufP knull = make_buf(ctx, (size_t)(n_out > 0 ? n_out : 1) * 8);
         long long* kptr[DX_AGG_MAX_KEYS]; unsigned long long* aptr[DX_AGG_MAX_ACCS];
+        if (have_cols && !synth) {
+            kbufs = pre_k; abufs = pre_a; knull = pre_knull;
+            for (size_t k = 0; k < hashed.size(); k++) kptr[k] = kbufs[k]->as<long long>();
+            for (size_t a = 0; a < accs.size(); a++) aptr[a] = abufs[a]->as<unsigned long long>();
+        } else {
         for (size_t k = 0; k < hashed.size(); k++) { kbufs[k] = make_buf(ctx, (size_t)(n_out > 0 ? n_out : 1) * 8); kptr[k] = kbufs[k]->as<long long>(); }
         for (size_t a = 0; a < accs.size(); a++) { abufs[a] = make_buf(ctx, (size_t)(n_out > 0 ? n_out : 1) * 8); aptr[a] = abufs[a]->as<unsigned long long>(); }
-        if (synth) {
+        }
+        if (have_cols && !synth) {
+        } else if (synth) {
             DX_CUDA(ctx, cudaMemsetAsync(knull->p, 0, 8, ctx->stream));
             for (auto& b : abufs) DX_CUDA(ctx, cudaMemsetAsync(b->p, 0, 8, ctx->stream));
         } else { int rc = T.extract(n_groups, kptr, knull->as<unsigned long long>(), aptr); if (rc) return rc; }
@@ -1443,6 +1523,7 @@ int dx_flow_build(dx_ctx* ctx, const char* conf_text, const char* schema_json, c
     }
     { auto g = F->conf.find(root + "gpu.genericrules"); F->generic_rules_only = g != F->conf.end() && lower(g->second) == "true"; }
     { auto g = F->conf.find(root + "gpu.panepartials"); F->pane_partials_off = g != F->conf.end() && lower(g->second) == "false"; }
+    { auto g = F->conf.find(root + "gpu.panesmem"); F->pane_smem_off = g != F->conf.end() && lower(g->second) == "false"; }
     auto wm = F->conf.find(root + "watermark"); auto tc = F->conf.find(root + "timestampcolumn");
     F->windows_enabled = !F->windows.empty() && wm != F->conf.end() && tc != F->conf.end();
     if (F->windows_enabled) {

@@ -9,6 +9,7 @@
 #include "dx_sql.h"
 #include "dx_expr.h"
 #include "dx_agg.h"
+#include "dx_aggp.h"
 #include "dx_decode_host.h"
 #include "dx_strings.h"
 #include <set>
@@ -45,6 +46,7 @@ struct View {
 // Per cached batch and statement: the batch's rows pre-aggregated by (group keys, pane = floor(ts / interval)).
 // A window aggregate then combines one partial per cached batch instead of rescanning every cached event each interval
 // (the reference rescans: CommonProcessorFactory.scala:203-227 re-filters the union of all cached batches per window).
+struct PanePartialP { DxTableP chunk; AggPPartial ap; };
 struct PanePartial {
     DxTableP chunk;                 // keeps the batch (and with it the cache key, its address) alive
     std::string sig;                // keys / values / accumulators / pane width this partial was built for
@@ -94,6 +96,9 @@ struct dx_flow {
     std::map<std::string, NamespaceState> ns;
     std::map<std::string, unsigned long long> agg_capacity_hint;  // per statement name
     std::map<std::string, std::map<const DxTable*, PanePartial>> pane_partials;   // partial signature -> cached batch -> partial
+    std::map<std::string, std::map<const DxTable*, PanePartialP>> pane_partials_p;   // same, partitioned shared-memory form (dx_aggp.h)
+    std::map<std::string, int> pane_P;       // partitions per signature (every partial of a signature shares it)
+    bool pane_smem_off = false;     // conf datax.job.process.gpu.panesmem=false: partials through the global hash table (dx_agg.cu)
     bool pane_partials_off = false; // conf datax.job.process.gpu.panepartials=false: always rescan (tests compare both)
     std::string last_error;
     // user functions evaluated on the host side of the boundary, once per distinct dictionary entry

@@ -176,6 +176,7 @@ Total = SELECT COUNT(*) AS Count, AVG(deviceDetails.temperature) AS Tavg FROM Da
     conf = dx.flowgen.conf_text("pane", timestamp_column="eventTimeStamp", watermark="60 second", windows=windows)
     g, o = both(dx, ctx, conf, SCHEMA2, [PROJ_TS], tr)
     g_rescan = dx.CommonProcessorFactory.createProcessor(ctx, conf + "datax.job.process.gpu.panepartials=false\n", SCHEMA2, [PROJ_TS], tr)
+    g_global = dx.CommonProcessorFactory.createProcessor(ctx, conf + "datax.job.process.gpu.panesmem=false\n", SCHEMA2, [PROJ_TS], tr)
     ctx.take_counter("k3_partial_rows_built")
     for b in range(9):
         T = T0 + b * I
@@ -184,14 +185,15 @@ Total = SELECT COUNT(*) AS Count, AVG(deviceDetails.temperature) AS Tavg FROM Da
         else:
             data = gen(dx, 3000, first=b * 3000, shape=2, n_keys=150, base=T, late=30, future=20)
         ro, mo = o.process(data, T, I)
-        for proc in (g, g_rescan):
+        for proc in (g, g_rescan, g_global):
             rg = proc.process_json(data, T, I)
             assert rg.metrics == mo
             for name in ("ByKey", "ByHome", "Total"):
                 assert_same_rows(rg.table(name), ro[name], dx)
             rg.release()
     assert ctx.take_counter("k3_partial_rows_built") > 0           # the partial path really ran
-    g.close(); g_rescan.close()
+    assert ctx.take_launches() >= 0
+    g.close(); g_rescan.close(); g_global.close()
 
 
 def test_state_table_append_with_retention_and_upsert(dx, ctx):

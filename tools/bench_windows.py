@@ -56,6 +56,7 @@ def main():
     ap.add_argument("--batches", type=int, default=100)
     ap.add_argument("--events-per-batch", type=int, default=5_000_000)
     ap.add_argument("--keys", type=int, default=1_000_000)
+    ap.add_argument("--no-smem", action="store_true", help="pane partials through the global-memory hash table (gpu.panesmem=false)")
     ap.add_argument("--no-panes", action="store_true", help="rescan every cached batch per window (gpu.panepartials=false)")
     args = ap.parse_args()
     import torch
@@ -63,6 +64,8 @@ def main():
     import dxo
     ctx = dx.Context(0)
     conf, tr = c3_flow(dx) if args.workload == "c3" else c4_flow(dx)
+    if args.no_smem:
+        conf += "datax.job.process.gpu.panesmem=false\n"
     if args.no_panes:
         conf += "datax.job.process.gpu.panepartials=false\n"
     flow = dx.CommonProcessorFactory.createProcessor(ctx, conf, dxo.iot_schema_json(1), [PROJ], tr)
@@ -107,7 +110,8 @@ def main():
                            "rows_per_s": round(k3_rows / max(k3_ms, 1e-9) * 1e3, 1)},
            "k_gather": {"launches": kg_n, "total_ms": round(kg_ms, 2), "bytes": g_bytes, "gbs": round(g_bytes / max(kg_ms, 1e-9) / 1e6, 2),
                         "frac_of_measured_hbm": round(g_bytes / max(kg_ms, 1e-9) / 1e6 / peak, 4)},
-           "k1_decode_total_ms": round(k1_ms, 2), "host_ms_per_batch": {k: round(v / 1e3 / args.batches, 3) for k, v in host_us.items()}, "wall_s": round(wall, 2), "result_rows_last_batch": rows_out,
+           "k1_decode_total_ms": round(k1_ms, 2), "k3p": {k: ctx.take_counter(k) for k in ("k3p_partitions", "k3p_repartitions", "k3p_output_regrows", "k3_partial_rows_built")},
+           "k3p_aggregate_ms": ctx.take_stage_ms("k3p_aggregate"), "k3p_scatter_ms": ctx.take_stage_ms("k3p_scatter"), "host_ms_per_batch": {k: round(v / 1e3 / args.batches, 3) for k, v in host_us.items()}, "wall_s": round(wall, 2), "result_rows_last_batch": rows_out,
            "note": "per-kernel timing enabled (host sync per kernel); process time by CUDA events around each batch on the library stream"}
     print(json.dumps(out))
 
