@@ -28,19 +28,25 @@ static __device__ __forceinline__ bool load_val(const ProgCol& c, long long row,
 template <int KMAX>
 __global__ void __launch_bounds__(256) k3_hash_agg(const __grid_constant__ AggTableDev T, const __grid_constant__ AggInput in) {
     const int nk = T.n_keys, na = T.n_accs, sw = T.slot_words;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < in.n_rows; i += (long long)gridDim.x * blockDim.x) {
+    // Every thread of a warp makes the same number of trips, so the warp can be re-joined (__syncwarp) between the divergent
+    // slot search and the accumulator updates; without it the updates run with a handful of active lanes.
+    for (long long i0 = (long long)blockIdx.x * blockDim.x; i0 < in.n_rows; i0 += (long long)gridDim.x * blockDim.x) {
+        const long long i = i0 + threadIdx.x;
         if (*reinterpret_cast<volatile unsigned long long*>(&T.counters[1])) return;   // table declared too small: the host retries with a larger one
-        const long long row = in.sel ? in.sel[i] : i;
-        if (in.has_range) {     // the window view's [start, end) filter, fused (CommonProcessorFactory.scala:203-227)
+        bool has = i < in.n_rows;
+        const long long row = has ? (in.sel ? in.sel[i] : i) : 0;
+        if (has && in.has_range) {     // the window view's [start, end) filter, fused (CommonProcessorFactory.scala:203-227)
             long long t;
-            if (!load_val(in.range_col, row, t) || t < in.range_lo || t >= in.range_hi) continue;
+            if (!load_val(in.range_col, row, t) || t < in.range_lo || t >= in.range_hi) has = false;
         }
         long long pane = 0;
-        if (in.pane_us) {
+        if (has && in.pane_us) {
             long long t;
-            if (!load_val(in.range_col, row, t)) continue;
-            pane = t >= 0 ? t / in.pane_us : -((-t + in.pane_us - 1) / in.pane_us);
+            if (!load_val(in.range_col, row, t)) has = false;
+            else pane = t >= 0 ? t / in.pane_us : -((-t + in.pane_us - 1) / in.pane_us);
         }
+        unsigned long long* slot = nullptr;
+        if (has) {
         long long kv[KMAX];
         unsigned long long nullbits = 0, h = 0x2545F4914F6CDD1Dull;
 #pragma unroll
@@ -55,7 +61,6 @@ __global__ void __launch_bounds__(256) k3_hash_agg(const __grid_constant__ AggTa
         h = amix64(h ^ nullbits);
         const unsigned long long tag = h | 0x8000000000000000ull;     // never 0 (empty) or 1 (being filled)
         unsigned long long idx = (h >> 3) & T.cap_mask;
-        unsigned long long* slot = nullptr;
         for (unsigned long long probes = 0; probes <= T.cap_mask && probes < 256; ) {   // a probe run this long means the table is crowded: give up, grow
             unsigned long long* s = T.slots + idx * sw;
             unsigned long long cur = *reinterpret_cast<volatile unsigned long long*>(s);
@@ -88,7 +93,10 @@ __global__ void __launch_bounds__(256) k3_hash_agg(const __grid_constant__ AggTa
             }
             idx = (idx + 1) & T.cap_mask; probes++;
         }
-        if (!slot) { T.counters[1] = 1ull; continue; }
+        if (!slot) T.counters[1] = 1ull;
+        }
+        __syncwarp();
+        if (!slot) continue;
         unsigned long long* acc = slot + nk + 2;
         for (int a = 0; a < na; a++) {
             const int kind = T.accs[a].kind;
