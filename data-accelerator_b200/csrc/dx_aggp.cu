@@ -1,6 +1,8 @@
 // dx_aggp.cu — K3P: partitioned shared-memory aggregation (see dx_aggp.h).
 #include "dx_aggp.h"
 #include <cub/device/device_scan.cuh>
+#include <chrono>
+static inline long long now_us() { return std::chrono::duration_cast<std::chrono::microseconds>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
 
 #define K3P_SLOTS 1024          // shared hash-table slots per CTA
 #define K3P_NT 256
@@ -243,6 +245,7 @@ bool dx_aggp_fits(int nk, int na) { return p2_smem(1 + (nk + 1) + 1 + na) <= 200
 
 int dx_aggp_build(dx_ctx* ctx, const AggInput& in_, int nk, int nv, const std::vector<AggAccDesc>& accs, int P, AggPPartial* out, bool* overflow) {
     *overflow = false;
+    const long long t_b0 = now_us();
     out->n = 0; out->P = P; out->gw = 1 + (nk + 1) + 1 + (int)accs.size();
     int pbits = 0; while ((1 << pbits) < P) pbits++;
     if ((1 << pbits) != P) return ctx->set_error(DX_ERR_ARG, "partition count must be a power of two");
@@ -280,6 +283,8 @@ int dx_aggp_build(dx_ctx* ctx, const AggInput& in_, int nk, int nv, const std::v
         ctx->launches["k3p_scatter"]++;
     }
     DX_CUDA(ctx, cudaGetLastError());
+    DX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->counters["host_us:k3p_build_scatter"] += now_us() - t_b0;
     // aggregate each partition by (keys, pane)
     P2Seg hseg{recs.as<unsigned long long>(), bases.as<unsigned int>(), counts.as<unsigned int>()};
     DevBuf dseg(ctx, sizeof(P2Seg));
@@ -299,6 +304,7 @@ int dx_aggp_build(dx_ctx* ctx, const AggInput& in_, int nk, int nv, const std::v
     unsigned long long h[3] = {0, 0, 0};
     DX_CUDA(ctx, cudaMemcpyAsync(h, ctr.p, 24, cudaMemcpyDeviceToHost, ctx->stream));
     DX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->counters["host_us:k3p_build_total_to_agg"] += now_us() - t_b0;
     if (h[1] || h[2]) { *overflow = true; return DX_OK; }
     out->n = (int64_t)h[0];
     // keep only what the groups need (the worst-case buffer can be far larger than the partial)

@@ -98,7 +98,7 @@ def main():
     kg_ms, kg_n = ctx.take_stage_ms("k_gather")
     k3_rows = ctx.take_counter("k3_rows")
     g_bytes = ctx.take_counter("gather_bytes")
-    host_us = {k: ctx.take_counter("host_us:" + k) for k in ["project", "route"] + ["stmt:" + nm for nm in rows_out]}
+    host_us = {k: ctx.take_counter("host_us:" + k) for k in ["project", "route", "k3p_build_scatter", "k3p_build_total_to_agg"] + ["stmt:" + nm for nm in rows_out]}
     total_events = n * args.batches
     row_bytes = 33 if args.workload == "c3" else 8 * 4          # keys + ts + value (+validity) per visited row
     out = {"metric": "events/sec per micro-batch (%s)" % ("window aggregates C3" if args.workload == "c3" else "state-table merge C4"),
