@@ -744,7 +744,7 @@ struct Exec {
                     BindScope sc = scope_for(v.chunks[k].get(), core);
                     const int64_t* selp = cs[k].filtered ? cs[k].sel->as<int64_t>() : nullptr;
                     bool fast = false;
-                    int rc = F->generic_rules_only ? DX_OK : dx_rules_eval(ctx, sc, conds, cs[k].n, selp, oc.data->as<uint32_t>() + off, oc.flag_words, &fast);
+                    int rc = F->generic_rules_only ? DX_OK : dx_rules_eval(ctx, sc, conds, cs[k].n, selp, oc.data->as<uint32_t>() + off, oc.flag_words, &fast, &F->rule_plans[stmt_name + "#" + oc.name]);
                     if (rc) return rc;
                     if (!fast) {   // rule set outside the bucketed planner's limits: generic interpreter
                         ExprPrograms P;

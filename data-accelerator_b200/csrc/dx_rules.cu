@@ -498,11 +498,57 @@ static void launch_rules(dx_ctx* ctx, const RulesDev& D, size_t smem, int64_t n_
     k2_rules_bucket<J, NEEDF, NSMAX><<<(unsigned)blocks, 256, smem, ctx->stream>>>(D, n_rows, reinterpret_cast<const long long*>(sel), flags);
 }
 
+// A planned rule set kept across micro-batches: everything but the column pointers is a function of the statement text,
+// the column types and the dictionaries' literal codes, so a steady-state batch only refreshes the pointers and launches.
+struct PlanCache {
+    std::vector<RSpaceDev> sdev; std::vector<int> space_col; std::vector<std::string> space_name; std::vector<int> space_type;
+    std::vector<const void*> space_dict;
+    DevBuf b_spaces, b_classes, b_cmask, b_consts, b_luts, b_tt, b_tf;
+    RulesDev D; size_t smem = 0; int J = 1; bool needf = false; int R = 0, words = 0;
+};
+
+static void rules_shared_vmask(RulesDev& D, const std::vector<RSpaceDev>& sdev) {
+    // the validity array most spaces share (the decoder writes one mask byte per row for all leaves)
+    std::map<const void*, int> votes; const void* best = nullptr; int bw = 0, bc = 0;
+    for (auto& d : sdev) if (d.domain != DOM_GENERIC && d.col.vmask) { int c = ++votes[d.col.vmask]; if (c > bc) { bc = c; best = d.col.vmask; bw = d.col.vwidth; } }
+    D.shared_vmask = bc >= 2 ? best : nullptr; D.shared_vwidth = bw;
+}
+
+static void rules_launch(dx_ctx* ctx, const RulesDev& D, int J, bool needf, size_t smem, int64_t n_rows, const int64_t* sel, uint32_t* flags) {
+    StageTimer tm(ctx, "k2_rules_bucket");
+#define RB_LAUNCH_NS(JJ, FF) do { if (D.n_spaces <= 8) launch_rules<JJ, FF, 8>(ctx, D, smem, n_rows, sel, flags); else launch_rules<JJ, FF, RB_MAX_SPACES>(ctx, D, smem, n_rows, sel, flags); } while (0)
+#define RB_LAUNCH(JJ) do { if (needf) RB_LAUNCH_NS(JJ, true); else RB_LAUNCH_NS(JJ, false); } while (0)
+    if (J == 1) RB_LAUNCH(1); else if (J == 2) RB_LAUNCH(2); else if (J == 3) RB_LAUNCH(3); else RB_LAUNCH(4);
+#undef RB_LAUNCH
+#undef RB_LAUNCH_NS
+    ctx->launches["k2_rules_bucket"]++;
+}
+
 int dx_rules_eval(dx_ctx* ctx, const BindScope& sc, const std::vector<ExprP>& conds, int64_t n_rows, const int64_t* sel,
-                  uint32_t* flags, int words, bool* used_fast) {
+                  uint32_t* flags, int words, bool* used_fast, std::shared_ptr<void>* cache) {
     *used_fast = false;
     if (n_rows <= 0 || conds.empty()) return DX_OK;
     const int R = (int)conds.size();
+    if (cache && *cache) {
+        PlanCache* pc = static_cast<PlanCache*>(cache->get());
+        bool ok = pc->R == R && pc->words == words;
+        for (size_t s2 = 0; ok && s2 < pc->sdev.size(); s2++) {
+            const int ci = pc->space_col[s2];
+            if (ci < 0 || ci >= (int)sc.table->cols.size()) { ok = false; break; }
+            const DxColumn& c = sc.table->cols[ci];
+            ok = c.name == pc->space_name[s2] && c.type == pc->space_type[s2] && c.data && !c.all_null && (const void*)c.dict.get() == pc->space_dict[s2];
+            if (ok) { ProgCol& pcol = pc->sdev[s2].col; pcol.data = c.data->p; pcol.vmask = c.vmask ? c.vmask->p : nullptr; pcol.vwidth = c.vwidth; pcol.vbit = c.vbit; pcol.width = dx_type_width(c.type); }
+        }
+        if (ok) {
+            DX_CUDA(ctx, cudaMemcpyAsync(pc->b_spaces.p, pc->sdev.data(), pc->sdev.size() * sizeof(RSpaceDev), cudaMemcpyHostToDevice, ctx->stream));
+            rules_shared_vmask(pc->D, pc->sdev);
+            rules_launch(ctx, pc->D, pc->J, pc->needf, pc->smem, n_rows, sel, flags);
+            DX_CUDA(ctx, cudaGetLastError());
+            *used_fast = true;
+            return DX_OK;
+        }
+        cache->reset();        // schema or dictionaries changed: plan again
+    }
     Planner P(ctx, sc);
     // per rule: DNF over leaf ids
     std::vector<std::vector<Term>> rule_terms(R);
@@ -670,11 +716,7 @@ int dx_rules_eval(dx_ctx* ctx, const BindScope& sc, const std::vector<ExprP>& co
     D.class_masks = b_cmask.as<uint32_t>();
     D.table_t = b_tt.as<uint32_t>(); D.table_f = b_tf.as<uint32_t>();
     D.total_rows = total_rows; D.J = J; D.Wp = Wp; D.words = words;
-    {   // the validity array most spaces share (the decoder writes one mask byte per row for all leaves)
-        std::map<const void*, int> votes; const void* best = nullptr; int bw = 0, bc = 0;
-        for (auto& d : sdev) if (d.domain != DOM_GENERIC && d.col.vmask) { int c = ++votes[d.col.vmask]; if (c > bc) { bc = c; best = d.col.vmask; bw = d.col.vwidth; } }
-        D.shared_vmask = bc >= 2 ? best : nullptr; D.shared_vwidth = bw;
-    }
+    rules_shared_vmask(D, sdev);
     if (!P.G.prog_start.empty()) {
         D.code = GD.code.as<uint32_t>(); D.gconsts = GD.consts.as<long long>(); D.gcols = GD.cols.as<ProgCol>(); D.gluts = GD.luts.as<ProgLut>(); D.n_gcols = GD.n_cols;
     }
@@ -684,15 +726,23 @@ int dx_rules_eval(dx_ctx* ctx, const BindScope& sc, const std::vector<ExprP>& co
     D.table_in_smem = (fixed + tab_bytes <= RB_SMEM_TABLE_BYTES) ? 1 : 0;
     size_t smem = fixed + (D.table_in_smem ? tab_bytes : 0);
     if (fixed > 64 * 1024) return DX_OK;       // pathological constant count: generic kernel
-    {
-        StageTimer tm(ctx, "k2_rules_bucket");
-#define RB_LAUNCH_NS(JJ, FF) do { if (D.n_spaces <= 8) launch_rules<JJ, FF, 8>(ctx, D, smem, n_rows, sel, flags); else launch_rules<JJ, FF, RB_MAX_SPACES>(ctx, D, smem, n_rows, sel, flags); } while (0)
-#define RB_LAUNCH(JJ) do { if (needf) RB_LAUNCH_NS(JJ, true); else RB_LAUNCH_NS(JJ, false); } while (0)
-        if (J == 1) RB_LAUNCH(1); else if (J == 2) RB_LAUNCH(2); else if (J == 3) RB_LAUNCH(3); else RB_LAUNCH(4);
-        ctx->launches["k2_rules_bucket"]++;
-    }
+    rules_launch(ctx, D, J, needf, smem, n_rows, sel, flags);
     DX_CUDA(ctx, cudaGetLastError());
-    DX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));     // the uploaded tables die with this scope
+    bool cacheable = cache != nullptr && P.G.prog_start.empty();
+    for (auto& sp : P.spaces) if (sp.per_code) cacheable = false;       // per-code LIKE tables follow the dictionary
+    if (cacheable) {
+        auto pc = std::make_shared<PlanCache>();
+        pc->sdev = sdev; pc->D = D; pc->smem = smem; pc->J = J; pc->needf = needf; pc->R = R; pc->words = words;
+        for (auto& sp : P.spaces) {
+            const DxColumn& c = sc.table->cols[sp.table_col];
+            pc->space_col.push_back(sp.table_col); pc->space_name.push_back(c.name); pc->space_type.push_back(c.type); pc->space_dict.push_back(c.dict.get());
+        }
+        pc->b_spaces = std::move(b_spaces); pc->b_classes = std::move(b_classes); pc->b_cmask = std::move(b_cmask); pc->b_consts = std::move(b_consts);
+        pc->b_luts = std::move(b_luts); pc->b_tt = std::move(b_tt); pc->b_tf = std::move(b_tf);
+        *cache = pc;           // the device tables live on with the plan; nothing to wait for
+    } else {
+        DX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));     // the uploaded tables die with this scope
+    }
     *used_fast = true;
     return DX_OK;
 }

@@ -1,9 +1,12 @@
 // dx_rules.h — bucketed, bit-sliced rule evaluation (K2 fast path); see dx_rules.cu.
 #pragma once
 #include "dx_expr.h"
+#include <memory>
 
 // Evaluates conds[r] for every row (through sel if given) into word-major flag words
 // (flags[w * n_rows + i], bit r%32 of word r/32).  *used_fast = false means the rule set did not
 // fit the planner's limits and nothing was written: the caller uses the generic kernel instead.
 int dx_rules_eval(dx_ctx* ctx, const BindScope& sc, const std::vector<dxsql::ExprP>& conds, int64_t n_rows, const int64_t* sel,
-                  uint32_t* flags, int words, bool* used_fast);
+                  uint32_t* flags, int words, bool* used_fast, std::shared_ptr<void>* plan_cache = nullptr);
+// plan_cache: where the caller keeps this statement's plan between micro-batches (device tables included); it is
+// rebuilt when a referenced column changes type or dictionary.
