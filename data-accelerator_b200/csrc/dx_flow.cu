@@ -1219,6 +1219,7 @@ struct Exec {
                     }
                     InputHold hold; AggInput in;
                     int rc = make_input(chp.get(), nullptr, chp->n_rows, true, &in, &hold); if (rc) return rc;
+                    if (P == 0 && F->pane_partitions_first > 0) P = F->pane_partitions_first;      // tests start too coarse on purpose
                     if (P == 0) { P = 256; while (P < 16384 && (long long)P * 1200 < chp->n_rows) P <<= 1; }
                     in.has_range = 0; in.pane_us = pane_us;
                     PanePartialP pp; pp.chunk = chp;
@@ -1524,6 +1525,7 @@ int dx_flow_build(dx_ctx* ctx, const char* conf_text, const char* schema_json, c
     { auto g = F->conf.find(root + "gpu.genericrules"); F->generic_rules_only = g != F->conf.end() && lower(g->second) == "true"; }
     { auto g = F->conf.find(root + "gpu.panepartials"); F->pane_partials_off = g != F->conf.end() && lower(g->second) == "false"; }
     { auto g = F->conf.find(root + "gpu.panesmem"); F->pane_smem_off = g != F->conf.end() && lower(g->second) == "false"; }
+    { auto g = F->conf.find(root + "gpu.panepartitions"); if (g != F->conf.end()) { int v = atoi(g->second.c_str()); int p2 = 1; while (p2 < v) p2 <<= 1; F->pane_partitions_first = v > 0 ? p2 : 0; } }
     auto wm = F->conf.find(root + "watermark"); auto tc = F->conf.find(root + "timestampcolumn");
     F->windows_enabled = !F->windows.empty() && wm != F->conf.end() && tc != F->conf.end();
     if (F->windows_enabled) {

@@ -98,6 +98,7 @@ struct dx_flow {
     std::map<std::string, std::map<const DxTable*, PanePartial>> pane_partials;   // partial signature -> cached batch -> partial
     std::map<std::string, std::map<const DxTable*, PanePartialP>> pane_partials_p;   // same, partitioned shared-memory form (dx_aggp.h)
     std::map<std::string, int> pane_P;       // partitions per signature (every partial of a signature shares it)
+    int pane_partitions_first = 0;  // conf datax.job.process.gpu.panepartitions: first partition count tried (tests force the re-partition path)
     bool pane_smem_off = false;     // conf datax.job.process.gpu.panesmem=false: partials through the global hash table (dx_agg.cu)
     std::map<std::string, std::shared_ptr<void>> rule_plans;        // (statement, item) -> planned rule set with its device tables (dx_rules.h)
     bool pane_partials_off = false; // conf datax.job.process.gpu.panepartials=false: always rescan (tests compare both)
