@@ -19,8 +19,8 @@
 #include "dx_json.h"
 #include "dx_decode_host.h"
 
-#ifndef K1_T
-#define K1_T 32768          // tile bytes
+#ifndef K1_T_DEFAULT
+#define K1_T_DEFAULT 32768  // tile bytes when the record length is unknown (a multiple of 4096; see k1_pick_tile)
 #endif
 #define K1_OVL 2048         // overlap bytes past the tile (records starting in the tile may end here)
 #define K1_PAD 32
@@ -97,6 +97,9 @@ __device__ long long tile_lookback(unsigned long long* state, long long tile, un
     return excl;
 }
 
+// The tile size is a template parameter chosen per launch from the batch's mean record length, so that a tile holds just
+// under K1_NT records and the one-lane-per-record parse keeps (nearly) every lane of every warp busy.
+template <int K1_T>
 __global__ void __launch_bounds__(K1_NT, K1_MIN_CTAS) k1_decode(const __grid_constant__ DecodeArgs a) {
     extern __shared__ __align__(128) uint8_t smem[];
     constexpr int TILE_BYTES = K1_T + K1_OVL + K1_PAD;                     // one staged tile (multiple of 16)
@@ -166,7 +169,7 @@ __global__ void __launch_bounds__(K1_NT, K1_MIN_CTAS) k1_decode(const __grid_con
         __syncthreads();
 
         long long n_rec = 0; long long rec0 = 0;   // offsets mode: records [rec0, rec0+n_rec)
-        uint32_t my_masks[4]; uint32_t my_base = 0; // NDJSON mode
+        uint32_t my_masks[(K1_T / 128 / 32 + 1) / 2]; uint32_t my_base = 0; // NDJSON mode
         const bool first_virtual = (tile == 0 && (long long)a.skew < a.n_end);
         if (a.offsets == nullptr) {
             // --- structural scan: newline q in [lo, hi) owns the record starting at q+1 ---
@@ -415,8 +418,43 @@ __global__ void k1_count_records(const uint8_t* bytes, long long n, unsigned lon
 // =======================================================================================
 // host side
 // =======================================================================================
-static size_t k1_smem_bytes() {
-    return K1_STAGES * (K1_T + K1_OVL + K1_PAD) + (K1_SC + 2) * 2 + 64;
+static size_t k1_smem_bytes(int tile) {
+    return K1_STAGES * (tile + K1_OVL + K1_PAD) + (K1_SC + 2) * 2 + 64;
+}
+static const int k1_tiles[] = {16384, 20480, 24576, 28672, 32768, 36864, 40960, 45056, 49152};
+// tile bytes for a batch: the largest instantiated size that still keeps the expected records per tile under ~246
+static int k1_pick_tile(long long n_bytes, long long n_events) {
+    if (n_events <= 0 || n_bytes <= 0) return K1_T_DEFAULT;
+    const double avg = (double)n_bytes / (double)n_events;
+    int best = k1_tiles[0];
+    for (int t : k1_tiles) if ((double)t / avg <= 246.0) best = t;
+    return best;
+}
+template <int T> static int k1_setup_one(dx_ctx* c, int* occ_out) {
+    DX_CUDA(c, cudaFuncSetAttribute(k1_decode<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k1_smem_bytes(T)));
+    int occ = 0;
+    DX_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k1_decode<T>, K1_NT, k1_smem_bytes(T)));
+    *occ_out = occ > 0 ? occ : 1;
+    return DX_OK;
+}
+static int k1_launch(dx_ctx* c, int tile, const int* occ_by_tile, const DecodeArgs& a) {
+    int idx = 0; for (int i = 0; i < 9; i++) if (k1_tiles[i] == tile) idx = i;
+    long long grid = (long long)c->sm_count * occ_by_tile[idx];
+    if (grid > a.n_tiles) grid = a.n_tiles;
+    const size_t smem = k1_smem_bytes(tile);
+    switch (tile) {
+    case 16384: k1_decode<16384><<<(unsigned)grid, K1_NT, smem, c->stream>>>(a); break;
+    case 20480: k1_decode<20480><<<(unsigned)grid, K1_NT, smem, c->stream>>>(a); break;
+    case 24576: k1_decode<24576><<<(unsigned)grid, K1_NT, smem, c->stream>>>(a); break;
+    case 28672: k1_decode<28672><<<(unsigned)grid, K1_NT, smem, c->stream>>>(a); break;
+    case 36864: k1_decode<36864><<<(unsigned)grid, K1_NT, smem, c->stream>>>(a); break;
+    case 40960: k1_decode<40960><<<(unsigned)grid, K1_NT, smem, c->stream>>>(a); break;
+    case 45056: k1_decode<45056><<<(unsigned)grid, K1_NT, smem, c->stream>>>(a); break;
+    case 49152: k1_decode<49152><<<(unsigned)grid, K1_NT, smem, c->stream>>>(a); break;
+    default: k1_decode<32768><<<(unsigned)grid, K1_NT, smem, c->stream>>>(a); break;
+    }
+    c->launches["k1_decode"]++;
+    return DX_OK;
 }
 
 static int map_spark_type(const std::string& t) {
@@ -518,10 +556,11 @@ int dx_decoder::init(dx_ctx* c, const std::string& schema_json) {
     dev_dicts = DevBuf(c, sizeof(DictDev) * (hs.n_leaves + 1));
     DX_CUDA(c, cudaMemcpyAsync(dev_dicts.p, dd.data(), sizeof(DictDev) * hs.n_leaves, cudaMemcpyHostToDevice, c->stream));
     dev_stats = DevBuf(c, sizeof(DecodeStats) + 16);
-    DX_CUDA(c, cudaFuncSetAttribute(k1_decode, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k1_smem_bytes()));
-    int occ = 0;
-    DX_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k1_decode, K1_NT, k1_smem_bytes()));
-    ctas_per_sm = occ > 0 ? occ : 1;
+    { int rc2;
+      if ((rc2 = k1_setup_one<16384>(c, &occ_by_tile[0])) || (rc2 = k1_setup_one<20480>(c, &occ_by_tile[1])) || (rc2 = k1_setup_one<24576>(c, &occ_by_tile[2])) ||
+          (rc2 = k1_setup_one<28672>(c, &occ_by_tile[3])) || (rc2 = k1_setup_one<32768>(c, &occ_by_tile[4])) || (rc2 = k1_setup_one<36864>(c, &occ_by_tile[5])) ||
+          (rc2 = k1_setup_one<40960>(c, &occ_by_tile[6])) || (rc2 = k1_setup_one<45056>(c, &occ_by_tile[7])) || (rc2 = k1_setup_one<49152>(c, &occ_by_tile[8]))) return rc2; }
+    ctas_per_sm = occ_by_tile[4];
     DX_CUDA(c, cudaStreamSynchronize(c->stream));
     return DX_OK;
 }
@@ -571,7 +610,8 @@ int dx_decoder::decode_device(const uint8_t* json_dev, int64_t n_bytes, const in
     a.skew = (uint32_t)(addr & 15);
     a.base_al = reinterpret_cast<const uint8_t*>(addr - a.skew);
     a.n_end = (long long)a.skew + n_bytes;
-    a.n_tiles = (a.n_end + K1_T - 1) / K1_T;
+    const int tile = k1_pick_tile(n_bytes, n_events);
+    a.n_tiles = (a.n_end + tile - 1) / tile;
     a.max_rows = n_events;
     a.offsets = reinterpret_cast<const long long*>(offsets_dev);
     a.mask = mask->p; a.mask_width = mw;
@@ -586,12 +626,9 @@ int dx_decoder::decode_device(const uint8_t* json_dev, int64_t n_bytes, const in
     a.stats = dev_stats.as<DecodeStats>();
     // offsets mode writes every row; NDJSON mode too unless the caller overstated n_events — clear the mask
     // so never-written rows read as NULL rows
-    long long grid = (long long)c->sm_count * ctas_per_sm;
-    if (grid > a.n_tiles) grid = a.n_tiles;
     {
         StageTimer tm(c, "k1_decode");
-        k1_decode<<<(unsigned)grid, K1_NT, k1_smem_bytes(), c->stream>>>(a);
-        c->launches["k1_decode"]++;
+        k1_launch(c, tile, occ_by_tile, a);
     }
     DX_CUDA(c, cudaGetLastError());
     DX_CUDA(c, cudaMemcpyAsync(&last_stats, dev_stats.p, sizeof(DecodeStats), cudaMemcpyDeviceToHost, c->stream));
@@ -699,12 +736,13 @@ int dx_decoder::decode_noalloc(const uint8_t* json_dev, int64_t n_bytes, int64_t
     a.skew = (uint32_t)(addr & 15);
     a.base_al = reinterpret_cast<const uint8_t*>(addr - a.skew);
     a.n_end = (long long)a.skew + n_bytes;
-    a.n_tiles = (a.n_end + K1_T - 1) / K1_T;
+    const int tile = K1_T_DEFAULT;      // fixed: the scratch array's capacity is stated in tiles of this size
+    a.n_tiles = (a.n_end + tile - 1) / tile;
     if (a.n_tiles > DX_NOALLOC_MAX_TILES) {
         char b[256];
         snprintf(b, sizeof b, "decode_noalloc: a batch of %lld bytes needs %lld tiles; this entry point's fixed scratch handles at most %d tiles "
                  "(%lld bytes) per call — split the batch or use dx_decoder_decode", (long long)n_bytes, a.n_tiles, DX_NOALLOC_MAX_TILES,
-                 (long long)DX_NOALLOC_MAX_TILES * K1_T);
+                 (long long)DX_NOALLOC_MAX_TILES * K1_T_DEFAULT);
         return c->set_error(DX_ERR_CAPACITY, b);
     }
     unsigned long long* scratch = nullptr;
@@ -722,10 +760,7 @@ int dx_decoder::decode_noalloc(const uint8_t* json_dev, int64_t n_bytes, int64_t
     a.tile_counter = reinterpret_cast<unsigned int*>(scratch);
     a.stats = reinterpret_cast<DecodeStats*>(scratch + 2);
     a.tile_state = scratch + DX_NOALLOC_HEADER_WORDS;
-    long long grid = (long long)c->sm_count * ctas_per_sm;
-    if (grid > a.n_tiles) grid = a.n_tiles;
-    k1_decode<<<(unsigned)grid, K1_NT, k1_smem_bytes(), c->stream>>>(a);
-    c->launches["k1_decode"]++;
+    k1_launch(c, tile, occ_by_tile, a);
     DX_CUDA(c, cudaGetLastError());
     DecodeStats st;
     DX_CUDA(c, cudaMemcpyAsync(&st, a.stats, sizeof st, cudaMemcpyDeviceToHost, c->stream));
