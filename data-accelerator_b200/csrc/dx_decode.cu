@@ -253,7 +253,7 @@ __global__ void __launch_bounds__(K1_NT, K1_MIN_CTAS) k1_decode(const __grid_con
             }
             // emit + parse in rounds of K1_SC records
             for (long long round0 = 0; round0 < n_rec || round0 == 0; round0 += K1_SC) {
-                __syncthreads();
+                if (round0 > 0) __syncthreads();      // later rounds reuse s_starts; the first is already fenced by the two barriers above
                 if (first_virtual && tid == 0 && round0 == 0) s_starts[0] = (uint16_t)a.skew;
 #pragma unroll
                 for (int r = 0; r < ROUNDS; r++) {
