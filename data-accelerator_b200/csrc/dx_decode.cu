@@ -248,7 +248,11 @@ __global__ void __launch_bounds__(K1_NT, K1_MIN_CTAS) k1_decode(const __grid_con
             // stash per-round exclusive offsets compactly: emit loop recomputes them in the same order
             // (excl_in_warp[r] are kept in registers; ROUNDS is small)
             if (warp == 0) {
+#ifdef K1_NO_LOOKBACK    /* tuning experiment only: what the row-index look-back costs (row numbers are wrong in this build) */
+                long long rb = tile * 200;
+#else
                 long long rb = tile_lookback(a.tile_state, tile, (unsigned long long)n_rec);
+#endif
                 if (lane == 0) s_rowbase = rb;
             }
             // emit + parse in rounds of K1_SC records
