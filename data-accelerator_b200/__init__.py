@@ -6,7 +6,7 @@ name carries a hyphen; import it as `import dxgpu` (root shim) or via importlib.
 """
 from ._native import DxError, GenParams, lib, LIB_PATH, declared_symbols  # noqa: F401
 from .device import Context, Decoder, Table  # noqa: F401
-from .processor import (CommonProcessorFactory, CommonProcessor, BatchResult, rules_of, sql_canonical,  # noqa: F401
+from .processor import (CommonProcessorFactory, CommonProcessor, BatchResult, rules_of, rule_hits, sql_canonical,  # noqa: F401
                         transform_split, string_to_timestamp, duration_seconds)
 from . import flowgen  # noqa: F401
 from . import parallel  # noqa: F401

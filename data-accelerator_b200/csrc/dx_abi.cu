@@ -3,6 +3,7 @@
 #include "dx_abi_types.h"
 #include "dx_decode_host.h"
 #include "dx_flow.h"
+#include "dx_rules.h"
 #include "dx_shuffle.h"
 
 int dx_gen_device(dx_ctx* c, const dx_gen_params* g, int64_t first, int64_t n, uint8_t** bytes_out,
@@ -226,6 +227,16 @@ int dx_table_rule_count(const dx_table* h, int col) {
     const DxTable* t = T(h);
     if (col < 0 || col >= (int)t->cols.size() || !t->cols[col].aux) return 0;
     return (int)static_cast<RuleTable*>(t->cols[col].aux.get())->rules.size();
+}
+int dx_table_rule_hits(const dx_table* h, int col, int64_t* counts, int n_counts) {
+    const DxTable* t = T(h);
+    if (!counts || col < 0 || col >= (int)t->cols.size()) return DX_ERR_ARG;
+    const DxColumn& c = t->cols[col];
+    if (c.type != DX_T_FLAGS || !c.aux) return t->ctx->set_error(DX_ERR_ARG, "column '" + c.name + "' is not a rule-flag column");
+    const int R = (int)static_cast<RuleTable*>(c.aux.get())->rules.size();
+    if (n_counts < R) return t->ctx->set_error(DX_ERR_ARG, "rule hit counts need " + std::to_string(R) + " entries");
+    cudaSetDevice(t->ctx->device);
+    return dx_rule_counts(t->ctx, c.data->as<uint32_t>(), t->n_rows, c.flag_words, R, counts);
 }
 static std::string json_escape(const std::string& s) {
     std::string o;

@@ -746,3 +746,46 @@ int dx_rules_eval(dx_ctx* ctx, const BindScope& sc, const std::vector<ExprP>& co
     *used_fast = true;
     return DX_OK;
 }
+
+// =======================================================================================
+// per-rule hit counts of a flag bitmap ("200-bit flags/event + per-rule counts")
+// =======================================================================================
+// One warp takes 32 consecutive rows of one flag word; bit b of the 32 lanes' words is counted with one ballot.
+__global__ void __launch_bounds__(256) k2_rule_counts(const uint32_t* flags, long long n_rows, int words, unsigned long long* counts) {
+    __shared__ unsigned int s_cnt[32];
+    const int lane = threadIdx.x & 31, w = blockIdx.y;
+    if (threadIdx.x < 32) s_cnt[threadIdx.x] = 0;
+    __syncthreads();
+    unsigned int mine = 0;                      // lane b keeps the count of bit b
+    const uint32_t* col = flags + (size_t)w * n_rows;
+    const long long warp_id = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5, n_warps = ((long long)gridDim.x * blockDim.x) >> 5;
+    for (long long base = warp_id * 32; base < n_rows; base += n_warps * 32) {
+        const long long i = base + lane;
+        const uint32_t v = i < n_rows ? col[i] : 0u;
+#pragma unroll
+        for (int b = 0; b < 32; b++) {
+            const unsigned int c = __popc(__ballot_sync(0xffffffffu, (v >> b) & 1u));
+            if (lane == b) mine += c;
+        }
+    }
+    atomicAdd(&s_cnt[lane], mine);
+    __syncthreads();
+    if (threadIdx.x < 32 && s_cnt[threadIdx.x]) atomicAdd(&counts[w * 32 + threadIdx.x], (unsigned long long)s_cnt[threadIdx.x]);
+}
+
+int dx_rule_counts(dx_ctx* ctx, const uint32_t* flags, int64_t n_rows, int words, int n_rules, int64_t* counts_host) {
+    for (int r = 0; r < n_rules; r++) counts_host[r] = 0;
+    if (n_rows <= 0 || n_rules <= 0) return DX_OK;
+    DevBuf d(ctx, (size_t)words * 32 * 8 + 16);
+    if (!d.p) return ctx->set_error(DX_ERR_CUDA, "rule count allocation failed");
+    DX_CUDA(ctx, cudaMemsetAsync(d.p, 0, (size_t)words * 32 * 8, ctx->stream));
+    long long bx = (n_rows + 8191) / 8192; if (bx > ctx->sm_count * 4) bx = ctx->sm_count * 4; if (bx < 1) bx = 1;
+    k2_rule_counts<<<dim3((unsigned)bx, (unsigned)words), 256, 0, ctx->stream>>>(flags, n_rows, words, d.as<unsigned long long>());
+    ctx->launches["k2_rule_counts"]++;
+    DX_CUDA(ctx, cudaGetLastError());
+    std::vector<unsigned long long> h((size_t)words * 32);
+    DX_CUDA(ctx, cudaMemcpyAsync(h.data(), d.p, h.size() * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    DX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    for (int r = 0; r < n_rules; r++) counts_host[r] = (int64_t)h[r];
+    return DX_OK;
+}

@@ -10,3 +10,6 @@ int dx_rules_eval(dx_ctx* ctx, const BindScope& sc, const std::vector<dxsql::Exp
                   uint32_t* flags, int words, bool* used_fast, std::shared_ptr<void>* plan_cache = nullptr);
 // plan_cache: where the caller keeps this statement's plan between micro-batches (device tables included); it is
 // rebuilt when a referenced column changes type or dictionary.
+
+// hits per rule over a word-major flag bitmap -> counts_host[0..n_rules)
+int dx_rule_counts(dx_ctx* ctx, const uint32_t* flags, int64_t n_rows, int words, int n_rules, int64_t* counts_host);

@@ -130,6 +130,18 @@ def rules_of(table: Table, col="Rules"):
     return out
 
 
+def rule_hits(table: Table, col="Rules"):
+    """Rows for which each rule of a FLAGS column fired -> int64 ndarray, one entry per rule."""
+    L = _lib()
+    i = table._idx(col)
+    n = L.dx_table_rule_count(table.h, i)
+    out = np.zeros(max(n, 1), dtype=np.int64)
+    fn = L.dx_table_rule_hits
+    fn.restype, fn.argtypes = C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int]
+    table.ctx.check(fn(table.h, i, out.ctypes.data_as(C.c_void_p), n))
+    return out[:n]
+
+
 class CommonProcessor:
     """What createProcessor returns (CommonProcessor case class, datax/processor/CommonProcessor.scala:17-31),
     reduced to the ingest adapters this ABI serves: JSON strings, in host or device memory."""

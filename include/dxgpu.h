@@ -136,6 +136,9 @@ void dx_table_release(dx_table* t);
  * filterNull(Array(IF(cond_r, MAP(...), NULL), ...)) AS Rules (CodegenRules Engine.cs:232-266).   */
 int dx_table_rule_count(const dx_table* t, int col);
 int dx_table_rule_json(const dx_table* t, int col, int rule, const char** json, int64_t* len);
+/* Rows for which each rule fired (SURVEY.md 8(d) C2 "flags + per-rule counts"; what a sink would get from
+ * SELECT explode(Rules) ... GROUP BY ruleId): counts[r], r < dx_table_rule_count, computed on the device.       */
+int dx_table_rule_hits(const dx_table* t, int col, int64_t* counts, int n_counts);
 
 /* ---- the flow processor (drop-in boundary) ------------------------------------------------ */
 typedef struct dx_flow dx_flow;       /* one per flow: decoder, parsed SQL, window cache, state tables */

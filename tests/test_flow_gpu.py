@@ -50,6 +50,9 @@ def test_rules_flags_match_oracle(dx, ctx):
     assert_same_rows(t, ro["Rules"], dx, ordered=True)
     flags, _ = t.column("Rules")
     assert flags.shape == (50_000, 7)
+    # per-rule hit counts computed on the device == column sums of the flag bits
+    want = np.unpackbits(flags.view(np.uint8), axis=1, bitorder="little")[:, :200].sum(axis=0)
+    assert (dx.rule_hits(t, "Rules") == want).all()
     # every rule fires at least once on 50k events except the very selective ones; none fires always
     fired = np.unpackbits(flags.view(np.uint8), axis=1, bitorder="little")[:, :200].sum(axis=0)
     assert (fired > 0).sum() > 150 and (fired < 50_000).all()
