@@ -33,6 +33,7 @@ def main():
     ap.add_argument("--batches", type=int, default=10)
     ap.add_argument("--events-per-batch", type=int, default=20_000_000)
     ap.add_argument("--keys", type=int, default=1_000_000)
+    ap.add_argument("--rules", type=int, default=0, help="C5: evaluate this many generated rules on the local events before the shuffle (S2 events)")
     args = ap.parse_args()
     import numpy as np
     import torch
@@ -43,8 +44,10 @@ def main():
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     ctx = dx.Context(local)
-    schema = dxo.iot_schema_json(1)
-    dec = dx.CommonProcessorFactory.createProcessor(ctx, dx.flowgen.conf_text("dec"), schema, [PROJ], "")
+    shape = 2 if args.rules else 1
+    schema = dxo.iot_schema_json(shape)
+    rules_tr = dx.flowgen.process_rules_sql(dx.flowgen.make_rules(args.rules, seed=20260105, n_keys=args.keys, n_homes=max(1, args.keys // 10))) if args.rules else ""
+    dec = dx.CommonProcessorFactory.createProcessor(ctx, dx.flowgen.conf_text("dec"), schema, [PROJ], rules_tr)
     conf = dx.flowgen.conf_text("c5", timestamp_column="eventTimeStamp", watermark="60 second", windows=[("DataXProcessedInput_5minutes", "5 minutes")])
     agg = dx.CommonProcessorFactory.createProcessor(ctx, conf, schema, [PROJ], TR)
     n = args.events_per_batch
@@ -55,11 +58,15 @@ def main():
     groups = 0
     for b in range(args.batches):
         T = T0 + b * I
-        gp = dx.GenParams(9000 + rank, args.keys, max(1, args.keys // 10), T, I, 60_000, 1, 10, 1, 0)
+        gp = dx.GenParams(9000 + rank, args.keys, max(1, args.keys // 10), T, I, 60_000, shape, 10, 1, 0)
         ptr, nb, _ = ctx.gen_events(gp, b * n, n)
         torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
         ev[0].record()
-        proj = dx.parallel.project_device(dec, ptr, nb, n, T)
+        if args.rules:      # decode + projection + rules -> (columns, flag bitmap); the flags stay on the rank that decoded the event
+            r0 = dec.process_device(ptr, nb, T, I, n_events=n)
+            proj = r0.table("Rules")
+        else:
+            proj = dx.parallel.project_device(dec, ptr, nb, n, T)
         counts, rec_bytes = dx.parallel.pack_by_key(proj, COLS, COLS[:2], world, send.data_ptr())
         ev[1].record()
         recv_counts = dx.parallel.exchange_counts(counts)
@@ -77,6 +84,8 @@ def main():
             wire += int((counts.sum() - counts[rank]) * rec_bytes)
         groups = r.table("Tumbling").num_rows
         r.release(); ctx.free(ptr)
+        if args.rules:
+            r0.release()
     timed = args.batches - 1
     host = {k: round(ctx.take_counter("host_us:" + k) / 1e3 / args.batches, 3) for k in ("route", "stmt:Tumbling", "stmt:Sliding5m")}
     g = torch.tensor([groups], device="cuda", dtype=torch.int64)
@@ -89,7 +98,7 @@ def main():
                           "wire_bytes_out_per_gpu_per_batch": wire // max(timed, 1), "rec_bytes": 8 * rec_words,
                           "all_to_all_gbs_per_gpu_per_direction": round(wire / max(timed, 1) / max(a2a_ms / timed, 1e-9) / 1e6, 2),
                           "nvlink_peak_gbs": 900, "frac_of_nvlink": round(wire / max(timed, 1) / max(a2a_ms / timed, 1e-9) / 1e6 / 900, 4),
-                          "tumbling_groups_all_ranks": int(g.item()), "rank0_host_ms_per_batch": host, "scaling": "weak"}))
+                          "tumbling_groups_all_ranks": int(g.item()), "rules": args.rules, "rank0_host_ms_per_batch": host, "scaling": "weak"}))
     dist.barrier()
     dist.destroy_process_group()
 
