@@ -389,6 +389,73 @@ int dx_flow_process_table(dx_flow* f, const char* name_space, const dx_table* pr
     try { return f->route(name_space ? name_space : "", dx_unwrap_table(projected), batch_time_ms, interval_ms, now_ms, out); }
     catch (std::exception& e) { return f->ctx->set_error(DX_ERR_STATE, e.what()); }
 }
+static int shuffle_columns(const DxTable* t, const char* const* cols, int n_cols, const char* const* key_cols, int n_keys,
+                           std::vector<int>* idx_out, std::vector<int>* kpos_out);
+
+int dx_table_shuffle_count(const dx_table* h, const char* const* cols, int n_cols, const char* const* key_cols, int n_keys, int world, int64_t* counts) {
+    const DxTable* t = T(h);
+    cudaSetDevice(t->ctx->device);
+    if (!counts) return t->ctx->set_error(DX_ERR_ARG, "shuffle_count: bad arguments");
+    std::vector<int> idx, kpos;
+    int rc = shuffle_columns(t, cols, n_cols, key_cols, n_keys, &idx, &kpos); if (rc) return rc;
+    return dx_shuffle_count(t->ctx, t, idx, kpos, world, counts);
+}
+int dx_table_shuffle_put(const dx_table* h, const char* const* cols, int n_cols, const char* const* key_cols, int n_keys, int world,
+                         void* const* peer_bufs, const int64_t* first_record) {
+    const DxTable* t = T(h);
+    cudaSetDevice(t->ctx->device);
+    if (!peer_bufs || !first_record) return t->ctx->set_error(DX_ERR_ARG, "shuffle_put: bad arguments");
+    std::vector<int> idx, kpos;
+    int rc = shuffle_columns(t, cols, n_cols, key_cols, n_keys, &idx, &kpos); if (rc) return rc;
+    return dx_shuffle_put(t->ctx, t, idx, kpos, world, peer_bufs, first_record);
+}
+int dx_ipc_export(dx_ctx* c, const void* dev_ptr, uint8_t* handle64) {
+    if (!c || !dev_ptr || !handle64) return DX_ERR_ARG;
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    cudaSetDevice(c->device);
+    cudaIpcMemHandle_t hnd;
+    DX_CUDA(c, cudaIpcGetMemHandle(&hnd, const_cast<void*>(dev_ptr)));
+    memcpy(handle64, &hnd, 64);
+    return DX_OK;
+}
+int dx_ipc_open(dx_ctx* c, const uint8_t* handle64, void** dev_ptr) {
+    if (!c || !handle64 || !dev_ptr) return DX_ERR_ARG;
+    cudaSetDevice(c->device);
+    cudaIpcMemHandle_t hnd; memcpy(&hnd, handle64, 64);
+    DX_CUDA(c, cudaIpcOpenMemHandle(dev_ptr, hnd, cudaIpcMemLazyEnablePeerAccess));
+    return DX_OK;
+}
+int dx_ipc_close(dx_ctx* c, void* dev_ptr) {
+    if (!c || !dev_ptr) return DX_ERR_ARG;
+    cudaSetDevice(c->device);
+    DX_CUDA(c, cudaIpcCloseMemHandle(dev_ptr));
+    return DX_OK;
+}
+
+static int shuffle_columns(const DxTable* t, const char* const* cols, int n_cols, const char* const* key_cols, int n_keys,
+                           std::vector<int>* idx_out, std::vector<int>* kpos_out) {
+    dx_ctx* c = t->ctx;
+    if (n_cols < 1 || n_keys < 0 || n_keys > 8) return c->set_error(DX_ERR_ARG, "shuffle: bad arguments");
+    BindScope sc; sc.table = t;
+    std::vector<int> idx, kpos;
+    for (int i = 0; i < n_cols; i++) {
+        std::string err; std::vector<std::string> parts;
+        std::string nm = cols[i]; size_t p0 = 0;
+        while (true) { size_t d = nm.find('.', p0); if (d == std::string::npos) { parts.push_back(nm.substr(p0)); break; } parts.push_back(nm.substr(p0, d - p0)); p0 = d + 1; }
+        int ci = dx_resolve_column(sc, parts, &err);
+        if (ci < 0) return c->set_error(DX_ERR_ARG, "shuffle: " + err);
+        idx.push_back(ci);
+    }
+    for (int k = 0; k < n_keys; k++) {
+        int pos = -1;
+        for (int i = 0; i < n_cols; i++) if (std::string(cols[i]) == key_cols[k]) pos = i;
+        if (pos < 0) return c->set_error(DX_ERR_ARG, std::string("shuffle: key column '") + key_cols[k] + "' is not among the sent columns");
+        kpos.push_back(pos);
+    }
+    *idx_out = idx; *kpos_out = kpos;
+    return DX_OK;
+}
+
 int dx_table_shuffle_pack(const dx_table* h, const char* const* cols, int n_cols, const char* const* key_cols, int n_keys, int world,
                           void* packed_dev, int64_t* counts, int64_t* rec_bytes) {
     const DxTable* t = T(h);

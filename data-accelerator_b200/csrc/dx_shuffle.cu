@@ -73,6 +73,77 @@ __global__ void __launch_bounds__(256) k5_scatter(const __grid_constant__ Shuffl
     }
 }
 
+// K5 fused with the exchange: the record of every row is written straight into the receive buffer of the GPU that owns
+// its key — a peer pointer mapped over NVLink (CUDA IPC) — at the offset this rank was assigned there, so the hash, the
+// column gather and the transfer overlap row by row and neither a send buffer nor a separate all-to-all pass exists.
+struct PutTargets { unsigned long long* base[DX_SHUFFLE_MAX_WORLD]; unsigned long long first[DX_SHUFFLE_MAX_WORLD]; };
+__global__ void __launch_bounds__(256) k5_scatter_put(const __grid_constant__ ShuffleArgs a, const __grid_constant__ PutTargets tg, unsigned long long* cursor) {
+    const int rec_words = a.n_cols + 1;
+    const int lane = threadIdx.x & 31;
+    for (long long i0 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) - lane; i0 < a.n_rows; i0 += (long long)gridDim.x * blockDim.x) {
+        const long long i = i0 + lane;
+        const bool has = i < a.n_rows;
+        const int dst = has ? owner_of(a, i) : -1;
+        const unsigned peers = __match_any_sync(0xffffffffu, dst);
+        const int leader = __ffs(peers) - 1;
+        const int rank_in_group = __popc(peers & ((1u << lane) - 1u));
+        unsigned long long start = 0;
+        if (has && lane == leader) start = atomicAdd(&cursor[dst], (unsigned long long)__popc(peers));
+        start = __shfl_sync(0xffffffffu, start, leader);
+        if (!has) continue;
+        unsigned long long* rec = tg.base[dst] + (tg.first[dst] + start + rank_in_group) * rec_words;
+        unsigned long long valid = 0;
+        for (int c = 0; c < a.n_cols; c++) {
+            long long v; if (sh_load(a.cols[c], i, v)) valid |= 1ull << c;
+            rec[c] = (unsigned long long)v;
+        }
+        rec[a.n_cols] = valid;
+    }
+}
+
+// The same with coalesced remote stores: the lanes of a warp that share an owner first lay their records side by side in
+// shared memory, then the whole warp copies that run to the owner's buffer with consecutive 8-byte stores (a 40-byte
+// record written field by field from one lane would cross NVLink as five separate partial-line writes).
+__global__ void __launch_bounds__(256) k5_scatter_put_staged(const __grid_constant__ ShuffleArgs a, const __grid_constant__ PutTargets tg, unsigned long long* cursor) {
+    extern __shared__ unsigned long long s_stage[];          // per warp: 32 records
+    const int rec_words = a.n_cols + 1;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    unsigned long long* stage = s_stage + (size_t)warp * 32 * rec_words;
+    for (long long i0 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) - lane; i0 < a.n_rows; i0 += (long long)gridDim.x * blockDim.x) {
+        const long long i = i0 + lane;
+        const bool has = i < a.n_rows;
+        const int dst = has ? owner_of(a, i) : -1;
+        const unsigned peers = __match_any_sync(0xffffffffu, dst);
+        const int leader = __ffs(peers) - 1;
+        const int rank_in_group = __popc(peers & ((1u << lane) - 1u));
+        unsigned long long start = 0;
+        if (has && lane == leader) start = atomicAdd(&cursor[dst], (unsigned long long)__popc(peers));
+        start = __shfl_sync(0xffffffffu, start, leader);
+        // one group (owner) at a time, in order of its first lane
+        unsigned todo = __ballot_sync(0xffffffffu, has && lane == leader);
+        while (todo) {
+            const int gl = __ffs(todo) - 1; todo &= todo - 1;
+            const unsigned gmask = __shfl_sync(0xffffffffu, peers, gl);
+            const int gdst = __shfl_sync(0xffffffffu, dst, gl);
+            const unsigned long long gstart = __shfl_sync(0xffffffffu, start, gl);
+            if (has && dst == gdst) {
+                unsigned long long* r = stage + (size_t)rank_in_group * rec_words;
+                unsigned long long valid = 0;
+                for (int c = 0; c < a.n_cols; c++) {
+                    long long v; if (sh_load(a.cols[c], i, v)) valid |= 1ull << c;
+                    r[c] = (unsigned long long)v;
+                }
+                r[a.n_cols] = valid;
+            }
+            __syncwarp();
+            const int n_words = __popc(gmask) * rec_words;
+            unsigned long long* out = tg.base[gdst] + (tg.first[gdst] + gstart) * rec_words;
+            for (int w = lane; w < n_words; w += 32) out[w] = stage[w];
+            __syncwarp();
+        }
+    }
+}
+
 __global__ void __launch_bounds__(256) k5_unpack(const unsigned long long* packed, long long n_rows, int n_cols, UnpackCols cols, uint32_t* vmask32) {
     const int rec_words = n_cols + 1;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_rows; i += (long long)gridDim.x * blockDim.x) {
@@ -85,6 +156,65 @@ __global__ void __launch_bounds__(256) k5_unpack(const unsigned long long* packe
 static unsigned grid_of(dx_ctx* c, long long n) {
     long long b = (n + 255) / 256, cap = (long long)c->sm_count * 8;
     return (unsigned)(b > cap ? cap : (b < 1 ? 1 : b));
+}
+
+static int shuffle_args(dx_ctx* ctx, const DxTable* t, const std::vector<int>& cols, const std::vector<int>& key_pos, int world, ShuffleArgs* out);
+
+// rows per owner rank (k5_count only)
+int dx_shuffle_count(dx_ctx* ctx, const DxTable* t, const std::vector<int>& cols, const std::vector<int>& key_pos, int world, int64_t* counts_host) {
+    ShuffleArgs a; int rc = shuffle_args(ctx, t, cols, key_pos, world, &a); if (rc) return rc;
+    for (int r = 0; r < world; r++) counts_host[r] = 0;
+    if (t->n_rows == 0) return DX_OK;
+    DevBuf st(ctx, DX_SHUFFLE_MAX_WORLD * 8);
+    DX_CUDA(ctx, cudaMemsetAsync(st.p, 0, DX_SHUFFLE_MAX_WORLD * 8, ctx->stream));
+    {
+        StageTimer tm(ctx, "k5_count");
+        k5_count<<<grid_of(ctx, t->n_rows), 256, 0, ctx->stream>>>(a, st.as<unsigned long long>());
+        ctx->launches["k5_count"]++;
+    }
+    unsigned long long h[DX_SHUFFLE_MAX_WORLD];
+    DX_CUDA(ctx, cudaMemcpyAsync(h, st.p, world * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    DX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    for (int r = 0; r < world; r++) counts_host[r] = (int64_t)h[r];
+    return DX_OK;
+}
+
+// records written directly to each owner's buffer: peer_bufs[r] = rank r's receive buffer as mapped in this process,
+// first_record[r] = where this rank's block starts there
+int dx_shuffle_put(dx_ctx* ctx, const DxTable* t, const std::vector<int>& cols, const std::vector<int>& key_pos, int world,
+                   void* const* peer_bufs, const int64_t* first_record) {
+    ShuffleArgs a; int rc = shuffle_args(ctx, t, cols, key_pos, world, &a); if (rc) return rc;
+    if (t->n_rows == 0) return DX_OK;
+    PutTargets tg; memset(&tg, 0, sizeof tg);
+    for (int r = 0; r < world; r++) { tg.base[r] = reinterpret_cast<unsigned long long*>(peer_bufs[r]); tg.first[r] = (unsigned long long)first_record[r]; }
+    DevBuf cur(ctx, DX_SHUFFLE_MAX_WORLD * 8);
+    DX_CUDA(ctx, cudaMemsetAsync(cur.p, 0, DX_SHUFFLE_MAX_WORLD * 8, ctx->stream));
+    {
+        StageTimer tm(ctx, "k5_scatter_put");
+        const int rec_words = a.n_cols + 1;
+        if (rec_words <= 16) k5_scatter_put_staged<<<grid_of(ctx, t->n_rows), 256, (size_t)8 * 32 * rec_words * 8, ctx->stream>>>(a, tg, cur.as<unsigned long long>());
+        else k5_scatter_put<<<grid_of(ctx, t->n_rows), 256, 0, ctx->stream>>>(a, tg, cur.as<unsigned long long>());
+        ctx->launches["k5_scatter_put"]++;
+    }
+    DX_CUDA(ctx, cudaGetLastError());
+    DX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));      // the peers may read once every rank is past this point (the caller's barrier)
+    return DX_OK;
+}
+
+static int shuffle_args(dx_ctx* ctx, const DxTable* t, const std::vector<int>& cols, const std::vector<int>& key_pos, int world, ShuffleArgs* out) {
+    if (world < 1 || world > DX_SHUFFLE_MAX_WORLD) return ctx->set_error(DX_ERR_ARG, "shuffle: world size out of range");
+    if (cols.empty() || (int)cols.size() > DX_SHUFFLE_MAX_COLS) return ctx->set_error(DX_ERR_ARG, "shuffle: 1..32 columns");
+    ShuffleArgs a; memset(&a, 0, sizeof a);
+    a.n_cols = (int)cols.size(); a.n_keys = (int)key_pos.size(); a.world = world; a.n_rows = t->n_rows;
+    for (size_t c = 0; c < cols.size(); c++) {
+        const DxColumn& col = t->cols[cols[c]];
+        if (col.type == DX_T_STR || col.type == DX_T_FLAGS) return ctx->set_error(DX_ERR_UNSUPPORTED, "shuffle: dictionary-coded and flag columns are rank-local and cannot be sent ('" + col.name + "')");
+        if (!col.data || col.all_null) return ctx->set_error(DX_ERR_UNSUPPORTED, "shuffle: constant column '" + col.name + "'");
+        a.cols[c].data = col.data->p; a.cols[c].vmask = col.vmask ? col.vmask->p : nullptr; a.cols[c].vwidth = col.vwidth; a.cols[c].vbit = col.vbit; a.cols[c].width = dx_type_width(col.type);
+    }
+    for (size_t k = 0; k < key_pos.size(); k++) a.key_idx[k] = key_pos[k];
+    *out = a;
+    return DX_OK;
 }
 
 int dx_shuffle_pack(dx_ctx* ctx, const DxTable* t, const std::vector<int>& cols, const std::vector<int>& key_pos, int world,

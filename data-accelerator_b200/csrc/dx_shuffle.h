@@ -21,3 +21,9 @@ int dx_shuffle_pack(dx_ctx* ctx, const DxTable* t, const std::vector<int>& cols,
 // Rebuilds a table from n_rows received records.
 int dx_shuffle_unpack(dx_ctx* ctx, const std::vector<std::string>& names, const std::vector<int>& types, const void* packed_dev, int64_t n_rows,
                       DxTableP* out);
+
+// rows per owner rank only
+int dx_shuffle_count(dx_ctx* ctx, const DxTable* t, const std::vector<int>& cols, const std::vector<int>& key_pos, int world, int64_t* counts_host);
+// pack fused with the exchange: records go straight into the owners' receive buffers (peer pointers over NVLink)
+int dx_shuffle_put(dx_ctx* ctx, const DxTable* t, const std::vector<int>& cols, const std::vector<int>& key_pos, int world,
+                   void* const* peer_bufs, const int64_t* first_record);

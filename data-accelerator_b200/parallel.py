@@ -114,3 +114,83 @@ def shuffle_table(table, cols, types, key_cols, group=None):
     out = table_from_packed(table.ctx, cols, types, recv.data_ptr() if n_recv else 0, n_recv)
     return out, {"sent_records": int(counts.sum()), "received_records": n_recv, "rec_bytes": rec_bytes,
                  "wire_bytes_out": int((counts.sum() - counts[dist.get_rank(group)]) * rec_bytes)}
+
+
+# ---- pack fused with the exchange: records written straight into the owners' buffers over NVLink ----
+def count_by_key(table, cols, key_cols, world):
+    """K5 count only: rows of `table` per owner rank."""
+    L = N.lib()
+    L.dx_table_shuffle_count.restype, L.dx_table_shuffle_count.argtypes = i32, [vp, P(cp), i32, P(cp), i32, i32, P(i64)]
+    c_cols = (cp * len(cols))(*[c.encode() for c in cols])
+    c_keys = (cp * len(key_cols))(*[c.encode() for c in key_cols])
+    counts = (i64 * world)()
+    table.ctx.check(L.dx_table_shuffle_count(table.h, c_cols, len(cols), c_keys, len(key_cols), world, counts))
+    return np.array(list(counts), dtype=np.int64)
+
+
+def put_by_key(table, cols, key_cols, world, peer_ptrs, first_record):
+    """K5 fused put: every record goes to peer_ptrs[owner] at record index first_record[owner] + (position among this
+    rank's records for that owner)."""
+    L = N.lib()
+    L.dx_table_shuffle_put.restype, L.dx_table_shuffle_put.argtypes = i32, [vp, P(cp), i32, P(cp), i32, i32, P(vp), P(i64)]
+    c_cols = (cp * len(cols))(*[c.encode() for c in cols])
+    c_keys = (cp * len(key_cols))(*[c.encode() for c in key_cols])
+    ptrs = (vp * world)(*[C.c_void_p(int(p)) for p in peer_ptrs])
+    first = (i64 * world)(*[int(x) for x in first_record])
+    table.ctx.check(L.dx_table_shuffle_put(table.h, c_cols, len(cols), c_keys, len(key_cols), world, ptrs, first))
+
+
+class PeerExchange:
+    """Receive buffers of all ranks of one box, mapped into every process (CUDA IPC over NVLink), and the bookkeeping of
+    one fused exchange per micro-batch: counts -> all_gather -> block offsets -> put -> barrier -> local unpack.
+    torch.distributed carries only the small integers and the barrier; the records never pass through a collective."""
+
+    def __init__(self, ctx, capacity_records, rec_words, group=None):
+        import torch
+        import torch.distributed as dist
+        self.ctx, self.group, self.rec_words, self.capacity = ctx, group, rec_words, int(capacity_records)
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        L = N.lib()
+        L.dx_ipc_export.restype, L.dx_ipc_export.argtypes = i32, [vp, vp, C.c_char_p]
+        L.dx_ipc_open.restype, L.dx_ipc_open.argtypes = i32, [vp, C.c_char_p, P(vp)]
+        L.dx_ipc_close.restype, L.dx_ipc_close.argtypes = i32, [vp, vp]
+        self.L = L
+        self.local = ctx.alloc(self.capacity * rec_words * 8)
+        h = C.create_string_buffer(64)
+        ctx.check(L.dx_ipc_export(ctx.h, C.c_void_p(self.local), h))
+        mine = torch.frombuffer(bytearray(h.raw), dtype=torch.uint8).cuda()
+        allh = [torch.empty(64, dtype=torch.uint8, device="cuda") for _ in range(self.world)]
+        dist.all_gather(allh, mine, group=group)
+        self.ptrs = []
+        for r in range(self.world):
+            if r == self.rank:
+                self.ptrs.append(self.local)
+                continue
+            p = C.c_void_p()
+            ctx.check(L.dx_ipc_open(ctx.h, bytes(allh[r].cpu().numpy().tobytes()), C.byref(p)))
+            self.ptrs.append(p.value)
+
+    def exchange(self, table, cols, key_cols):
+        """-> (device pointer of this rank's received records, number of records, counts this rank sent)."""
+        import torch
+        import torch.distributed as dist
+        counts = count_by_key(table, cols, key_cols, self.world)
+        mine = torch.as_tensor(counts, device="cuda")
+        allc = [torch.empty_like(mine) for _ in range(self.world)]
+        dist.all_gather(allc, mine, group=self.group)          # also orders this batch after every rank's previous unpack
+        M = torch.stack(allc).cpu().numpy()                    # M[s][d] = records rank s sends to rank d
+        recv_total = M.sum(axis=0)
+        if int(recv_total.max()) > self.capacity:
+            raise RuntimeError("PeerExchange: %d records for one rank exceed the buffer capacity %d" % (int(recv_total.max()), self.capacity))
+        first = M[:self.rank].sum(axis=0) if self.rank else np.zeros(self.world, dtype=np.int64)
+        put_by_key(table, cols, key_cols, self.world, self.ptrs, first)
+        dist.barrier(group=self.group)                         # every rank's puts have landed
+        torch.cuda.synchronize()                               # (the barrier runs on torch's stream, the unpack on the library's)
+        return self.local, int(recv_total[self.rank]), counts
+
+    def close(self):
+        for r, p in enumerate(self.ptrs):
+            if r != self.rank and p:
+                self.L.dx_ipc_close(self.ctx.h, C.c_void_p(p))
+        self.ctx.free(self.local)
+        self.ptrs = []

@@ -209,6 +209,20 @@ int dx_flow_process_table(dx_flow* flow, const char* name_space, const dx_table*
  * and are refused.                                                                               */
 int dx_table_shuffle_pack(const dx_table* t, const char* const* cols, int n_cols, const char* const* key_cols,
                           int n_keys, int world, void* packed_dev, int64_t* counts, int64_t* rec_bytes);
+/* K5 fused with the exchange (one kernel does pack + transfer over peer memory instead of pack, NCCL all-to-all):
+ * dx_table_shuffle_count gives the rows per owner; the ranks exchange the counts (a few integers), each derives where
+ * its block starts in every owner's receive buffer, and dx_table_shuffle_put writes every record straight into the
+ * owner's buffer through peer pointers (peer_bufs[r] = rank r's buffer as mapped here, first_record[r] = first record
+ * index of this rank's block there).  The receive buffers are ordinary dx_dev_alloc memory made visible to the other
+ * processes with dx_ipc_export / dx_ipc_open (CUDA IPC, NVLink peer access); a barrier between the puts and the
+ * owners' dx_table_from_packed is the caller's.  Same Exchange(hashpartitioning) as above.                       */
+int dx_table_shuffle_count(const dx_table* t, const char* const* cols, int n_cols, const char* const* key_cols,
+                           int n_keys, int world, int64_t* counts);
+int dx_table_shuffle_put(const dx_table* t, const char* const* cols, int n_cols, const char* const* key_cols,
+                         int n_keys, int world, void* const* peer_bufs, const int64_t* first_record);
+int dx_ipc_export(dx_ctx* ctx, const void* dev_ptr, uint8_t* handle64);      /* 64-byte handle for another process */
+int dx_ipc_open(dx_ctx* ctx, const uint8_t* handle64, void** dev_ptr);        /* map a peer's buffer */
+int dx_ipc_close(dx_ctx* ctx, void* dev_ptr);
 /* K5 unpack: n_rows received records -> a table with the given column names and DX_TYPE_* types. */
 int dx_table_from_packed(dx_ctx* ctx, const char* const* col_names, const int* col_types, int n_cols,
                          const void* packed_dev, int64_t n_rows, dx_table** out);

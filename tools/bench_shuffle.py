@@ -33,6 +33,7 @@ def main():
     ap.add_argument("--batches", type=int, default=10)
     ap.add_argument("--events-per-batch", type=int, default=20_000_000)
     ap.add_argument("--keys", type=int, default=1_000_000)
+    ap.add_argument("--put", action="store_true", help="pack fused with the exchange: records written into the owners' buffers over NVLink peer memory (no NCCL all-to-all)")
     ap.add_argument("--rules", type=int, default=0, help="C5: evaluate this many generated rules on the local events before the shuffle (S2 events)")
     args = ap.parse_args()
     import numpy as np
@@ -52,7 +53,8 @@ def main():
     agg = dx.CommonProcessorFactory.createProcessor(ctx, conf, schema, [PROJ], TR)
     n = args.events_per_batch
     rec_words = len(COLS) + 1
-    send = torch.empty(n * rec_words, dtype=torch.int64, device="cuda")
+    send = torch.empty(n * rec_words, dtype=torch.int64, device="cuda") if not args.put else None
+    px = dx.parallel.PeerExchange(ctx, int(n * 1.25) + 1024, rec_words) if args.put else None
     a2a_ms, pack_ms, total_ms, wire = 0.0, 0.0, 0.0, 0
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
     groups = 0
@@ -67,13 +69,21 @@ def main():
             proj = r0.table("Rules")
         else:
             proj = dx.parallel.project_device(dec, ptr, nb, n, T)
-        counts, rec_bytes = dx.parallel.pack_by_key(proj, COLS, COLS[:2], world, send.data_ptr())
-        ev[1].record()
-        recv_counts = dx.parallel.exchange_counts(counts)
-        recv = dx.parallel.exchange_records(send, counts, recv_counts, rec_words)
-        ev[2].record()
-        n_recv = int(recv_counts.sum())
-        part = dx.parallel.table_from_packed(ctx, NAMES, TYPES, recv.data_ptr() if n_recv else 0, n_recv)
+        if args.put:
+            ev[1].record()
+            recv_ptr, n_recv, counts = px.exchange(proj, COLS, COLS[:2])
+            rec_bytes = 8 * rec_words
+            ev[2].record()
+            part = dx.parallel.table_from_packed(ctx, NAMES, TYPES, recv_ptr if n_recv else 0, n_recv)
+        else:
+            counts, rec_bytes = dx.parallel.pack_by_key(proj, COLS, COLS[:2], world, send.data_ptr())
+            ev[1].record()
+            recv_counts = dx.parallel.exchange_counts(counts)
+            recv = dx.parallel.exchange_records(send, counts, recv_counts, rec_words)
+            ev[2].record()
+            torch.cuda.synchronize()      # the collective runs on torch's stream, the unpack on the library's: order them
+            n_recv = int(recv_counts.sum())
+            part = dx.parallel.table_from_packed(ctx, NAMES, TYPES, recv.data_ptr() if n_recv else 0, n_recv)
         r = dx.parallel.process_table(agg, part, T, I)
         ev[3].record()
         torch.cuda.synchronize()
@@ -98,7 +108,7 @@ def main():
                           "wire_bytes_out_per_gpu_per_batch": wire // max(timed, 1), "rec_bytes": 8 * rec_words,
                           "all_to_all_gbs_per_gpu_per_direction": round(wire / max(timed, 1) / max(a2a_ms / timed, 1e-9) / 1e6, 2),
                           "nvlink_peak_gbs": 900, "frac_of_nvlink": round(wire / max(timed, 1) / max(a2a_ms / timed, 1e-9) / 1e6 / 900, 4),
-                          "tumbling_groups_all_ranks": int(g.item()), "rules": args.rules, "rank0_host_ms_per_batch": host, "scaling": "weak"}))
+                          "tumbling_groups_all_ranks": int(g.item()), "rules": args.rules, "exchange": "fused put over peer memory" if args.put else "K5 pack + NCCL all-to-all", "rank0_host_ms_per_batch": host, "scaling": "weak"}))
     dist.barrier()
     dist.destroy_process_group()
 
