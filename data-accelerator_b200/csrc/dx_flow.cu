@@ -357,7 +357,75 @@ struct Exec {
         return !conds->empty();
     }
 
+    // UNION ALL whose branches only forward columns (the accumulator pattern: SELECT cols FROM new UNION ALL SELECT cols
+    // FROM state WHERE retention, StateTableHandler / UserCodeIoTSample.txt): every branch's selected rows are gathered
+    // ONCE, straight into their slice of the result, instead of materialising each branch and concatenating the copies.
+    // *done = false: some branch needs the general path.
+    int exec_union_all_direct(const Statement& st, DxTableP* out, bool* done) {
+        *done = false;
+        struct Branch { const DxTable* src; std::vector<int> cols; DevBufP sel; int64_t n = 0; bool filtered = false; };
+        std::vector<Branch> br(st.selects.size());
+        std::vector<std::string> names;
+        for (bool all : st.union_all) if (!all) return DX_OK;
+        for (size_t k = 0; k < st.selects.size(); k++) {
+            const SelectCore& core = st.selects[k];
+            if (!core.joins.empty() || core.distinct || !core.group_by.empty()) return DX_OK;
+            auto vit = views->find(core.from);
+            if (vit == views->end() || vit->second.chunks.size() != 1) return DX_OK;
+            const View& v = vit->second;
+            const DxTable* t = v.chunks[0].get();
+            BindScope sc = scope_for(t, core); sc.qualifiers.push_back("Raw");
+            for (auto& it : core.items) {
+                if (it.expr->kind == EK::Star && it.expr->parts.empty()) {
+                    for (size_t c = 0; c < t->cols.size(); c++) { br[k].cols.push_back((int)c); if (k == 0) names.push_back(t->cols[c].name); }
+                } else if (it.expr->kind == EK::Col) {
+                    std::string err; int ci = dx_resolve_column(sc, it.expr->parts, &err);
+                    if (ci < 0) return DX_OK;
+                    br[k].cols.push_back(ci); if (k == 0) names.push_back(item_name(it));
+                } else return DX_OK;
+            }
+            if (br[k].cols.size() != br[0].cols.size()) return DX_OK;
+            for (size_t c = 0; c < br[k].cols.size(); c++) {
+                const DxColumn& a0 = br[0].src ? br[0].src->cols[br[0].cols[c]] : t->cols[br[k].cols[c]];
+                const DxColumn& ck = t->cols[br[k].cols[c]];
+                if (!ck.data || ck.all_null || ck.type == DX_T_FLAGS || ck.type == DX_T_NULL || !ck.nest_path.empty()) return DX_OK;
+                if (k > 0 && (a0.type != ck.type || (ck.type == DX_T_STR && a0.dict != ck.dict))) return DX_OK;
+            }
+            br[k].src = t;
+            int rc = chunk_selection(v, v.chunks[0], core, &br[k].sel, &br[k].n, &br[k].filtered); if (rc) return rc;
+        }
+        int64_t total = 0; for (auto& b : br) total += b.n;
+        auto t = std::make_shared<DxTable>(); t->ctx = ctx; t->n_rows = total;
+        MaskAlloc masks(ctx, total);
+        const size_t nc = br[0].cols.size();
+        for (size_t c = 0; c < nc; c++) {
+            const DxColumn& proto = br[0].src->cols[br[0].cols[c]];
+            DxColumn oc; oc.name = names[c]; oc.type = proto.type; oc.dict = proto.dict;
+            const int w = dx_type_width(oc.type);
+            oc.data = make_buf(ctx, (size_t)(total > 0 ? total : 1) * w);
+            if (!oc.data->p) return fail(DX_ERR_CUDA, "UNION ALL allocation failed");
+            int rc = masks.assign(&oc, (int)c); if (rc) return rc;
+            int64_t off = 0;
+            for (auto& b : br) {
+                if (b.n == 0) continue;
+                rc = dx_gather_column(ctx, b.src->cols[b.cols[c]], b.n, b.filtered ? b.sel->as<int64_t>() : nullptr,
+                                      oc.data->as<uint8_t>() + (size_t)off * w, oc.vmask->as<uint32_t>() + off, oc.vbit);
+                if (rc) return rc;
+                off += b.n;
+            }
+            t->cols.push_back(oc);
+        }
+        DX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        *out = t; *done = true;
+        return DX_OK;
+    }
+
     int exec_statement(const Statement& st, DxTableP* out) {
+        if (st.selects.size() > 1) {
+            bool done = false;
+            int rc = exec_union_all_direct(st, out, &done); if (rc) return rc;
+            if (done) return DX_OK;
+        }
         std::vector<DxTableP> parts;
         for (auto& core : st.selects) { DxTableP t; int rc = exec_core(core, &t); if (rc) return rc; parts.push_back(t); }
         if (parts.size() == 1) { *out = parts[0]; return DX_OK; }
