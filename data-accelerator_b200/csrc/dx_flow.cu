@@ -457,7 +457,10 @@ struct Exec {
                 if (type == DX_T_NULL) type = pc.type;
                 else if (type != pc.type) {
                     bool il = (type == DX_T_I64 || type == DX_T_BOOL) && (pc.type == DX_T_I64 || pc.type == DX_T_BOOL);
-                    if (!il) return fail(DX_ERR_UNSUPPORTED, "UNION column '" + oc.name + "' mixes types");
+                    // Spark widens timestamp + string to string (TypeCoercion: string promotion)
+                    const bool ts_str = (type == DX_T_STR && pc.type == DX_T_TS) || (type == DX_T_TS && pc.type == DX_T_STR);
+                    if (ts_str) type = DX_T_STR;
+                    else if (!il) return fail(DX_ERR_UNSUPPORTED, "UNION column '" + oc.name + "' mixes types");
                 }
                 if (pc.type == DX_T_STR && pc.data && p->n_rows > 0) {
                     if (!dict) dict = pc.dict;      // codes of the other sides are re-encoded into the first side's dictionary
@@ -483,6 +486,17 @@ struct Exec {
                 uint8_t* dst = oc.data->as<uint8_t>() + (size_t)off * w;
                 uint32_t* vm = oc.vmask->as<uint32_t>() + off;
                 if (pc.type == DX_T_NULL || pc.all_null) { DX_CUDA(ctx, cudaMemsetAsync(dst, 0, (size_t)p->n_rows * w, ctx->stream)); }
+                else if (type == DX_T_STR && pc.type == DX_T_TS) {
+                    // this side's timestamps as text, entered into the result's dictionary
+                    DxColumn src = pc;
+                    if (!src.data) { rc = materialize_const(&src, p->n_rows, nullptr); if (rc) return rc; }
+                    StrBuildArgs sa; memset(&sa, 0, sizeof sa);
+                    sa.n_parts = 1; sa.parts[0].kind = SP_TS;
+                    sa.parts[0].col.data = src.data->p; sa.parts[0].col.vmask = src.vmask ? src.vmask->p : nullptr;
+                    sa.parts[0].col.vwidth = src.vwidth; sa.parts[0].col.vbit = src.vbit; sa.parts[0].col.width = 8;
+                    sa.n_rows = p->n_rows; sa.sel = nullptr;
+                    rc = dx_strbuild(ctx, sa, std::string(), dict, reinterpret_cast<int32_t*>(dst), vm, oc.vbit); if (rc) return rc;
+                }
                 else if (!pc.data) {
                     DxColumn tmp = pc;
                     rc = materialize_const(&tmp, p->n_rows, dict); if (rc) return rc;
@@ -972,8 +986,8 @@ struct Exec {
                 if (c.type == DX_T_F64) return fail(DX_ERR_UNSUPPORTED, "double to string formatting");
                 sp.kind = SP_LIT; sp.off = (uint32_t)lit.size(); sp.len = (uint32_t)sv.size(); lit += sv; continue;
             }
-            if (c.type == DX_T_F64 || c.type == DX_T_TS || c.type == DX_T_FLAGS) return fail(DX_ERR_UNSUPPORTED, "only strings and integers can be turned into text here");
-            sp.kind = c.type == DX_T_STR ? SP_STRCOL : SP_I64;
+            if (c.type == DX_T_F64 || c.type == DX_T_FLAGS) return fail(DX_ERR_UNSUPPORTED, "only strings, integers and timestamps can be turned into text here");
+            sp.kind = c.type == DX_T_STR ? SP_STRCOL : (c.type == DX_T_TS ? SP_TS : SP_I64);
             sp.col.data = c.data->p; sp.col.vmask = c.vmask ? c.vmask->p : nullptr; sp.col.vwidth = c.vwidth; sp.col.vbit = c.vbit; sp.col.width = dx_type_width(c.type);
             if (c.type == DX_T_STR) { if (!c.dict) return fail(DX_ERR_STATE, "string column without dictionary"); sp.dict = c.dict->dev; }
             keep.push_back(c);

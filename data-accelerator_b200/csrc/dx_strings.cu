@@ -34,6 +34,40 @@ __global__ void __launch_bounds__(256) k_strbuild(const __grid_constant__ StrBui
                 if (code < 0) { isnull = true; break; }
                 const uint32_t off = sp.dict.code_off[code], len = sp.dict.code_len[code];
                 for (uint32_t k = 0; k < len; k++) { if (n < DX_STRBUILD_MAX) buf[n] = __ldcg(sp.dict.heap + off + k); else too_long = true; n++; }
+            } else if (sp.kind == SP_TS) {
+                // CAST(timestamp AS STRING) (Spark 2.4 DateTimeUtils.timestampToString): yyyy-MM-dd HH:mm:ss, then the fraction
+                // without trailing zeros, only if there is one
+                const long long us = reinterpret_cast<const long long*>(sp.col.data)[row];
+                long long days = us / 86400000000ll, rem = us % 86400000000ll;
+                if (rem < 0) { rem += 86400000000ll; days -= 1; }
+                // civil date from days since 1970-01-01 (proleptic Gregorian)
+                const long long z = days + 719468;
+                const long long era = (z >= 0 ? z : z - 146096) / 146097;
+                const unsigned doe = (unsigned)(z - era * 146097);
+                const unsigned yoe = (doe - doe / 1460 + doe / 36524 - doe / 146096) / 365;
+                long long y = (long long)yoe + era * 400;
+                const unsigned doy = doe - (365 * yoe + yoe / 4 - yoe / 100);
+                const unsigned mp = (5 * doy + 2) / 153;
+                const unsigned d = doy - (153 * mp + 2) / 5 + 1;
+                const unsigned mth = mp < 10 ? mp + 3 : mp - 9;
+                if (mth <= 2) y += 1;
+                const unsigned secs = (unsigned)(rem / 1000000ll), micro = (unsigned)(rem % 1000000ll);
+                uint8_t tmp[40]; int m = 0;
+                unsigned long long yy = y < 0 ? (unsigned long long)(-y) : (unsigned long long)y;
+                if (y < 0) tmp[m++] = '-';
+                { uint8_t dg[20]; int nd = 0; do { dg[nd++] = (uint8_t)('0' + yy % 10); yy /= 10; } while (yy); while (nd < 4) dg[nd++] = '0'; while (nd) tmp[m++] = dg[--nd]; }
+                tmp[m++] = '-'; tmp[m++] = (uint8_t)('0' + mth / 10); tmp[m++] = (uint8_t)('0' + mth % 10);
+                tmp[m++] = '-'; tmp[m++] = (uint8_t)('0' + d / 10); tmp[m++] = (uint8_t)('0' + d % 10);
+                const unsigned hh = secs / 3600, mi = (secs / 60) % 60, ss = secs % 60;
+                tmp[m++] = ' '; tmp[m++] = (uint8_t)('0' + hh / 10); tmp[m++] = (uint8_t)('0' + hh % 10);
+                tmp[m++] = ':'; tmp[m++] = (uint8_t)('0' + mi / 10); tmp[m++] = (uint8_t)('0' + mi % 10);
+                tmp[m++] = ':'; tmp[m++] = (uint8_t)('0' + ss / 10); tmp[m++] = (uint8_t)('0' + ss % 10);
+                if (micro) {
+                    tmp[m++] = '.';
+                    unsigned f = micro, div = 100000;
+                    while (f) { tmp[m++] = (uint8_t)('0' + f / div); f %= div; div /= 10; }
+                }
+                for (int k = 0; k < m; k++) { if (n < DX_STRBUILD_MAX) buf[n] = tmp[k]; else too_long = true; n++; }
             } else {    // SP_I64: decimal text, as Java's Long.toString
                 long long v = reinterpret_cast<const long long*>(sp.col.data)[row];
                 unsigned long long u = v < 0 ? 0ull - (unsigned long long)v : (unsigned long long)v;

@@ -6,7 +6,7 @@
 
 #define DX_STRBUILD_MAX 256
 #define DX_STRBUILD_MAX_PARTS 16
-enum { SP_LIT = 0, SP_STRCOL = 1, SP_I64 = 2 };
+enum { SP_LIT = 0, SP_STRCOL = 1, SP_I64 = 2, SP_TS = 3 };   // SP_TS: timestamp (us) as Spark casts it to string, UTC session zone
 
 struct StrPart {
     int32_t kind; uint32_t off, len; int32_t pad;     // SP_LIT: bytes [off, off+len) of lit_bytes

@@ -469,11 +469,16 @@ def concat_tabs(tabs):
             if t.cols[c][1] != "null":
                 ty = t.cols[c][1]
                 break
+        kinds = {t.cols[c][1] for t in tabs}
+        if ty == "ts" and "string" in kinds:
+            ty = "string"
         vals, oks = [], []
         for t in tabs:
             _, cty, v, ok = t.cols[c]
+            if cty == "ts" and ty == "string":     # Spark widens timestamp + string to string (TypeCoercion string promotion)
+                v = np.array([ts_to_string(int(x)) if k else None for x, k in zip(v, ok)], dtype=object) if len(v) else np.zeros(0, dtype=object)
+                cty = "string"
             if cty not in ("null", ty) and not {cty, ty} <= {"long", "bool"}:
-                # Spark would widen (e.g. timestamp + string -> string); the cast is outside the restated subset
                 raise ValueError(f"UNION column '{name}' mixes types {ty} and {cty}")
             if cty == "null" or v is None:
                 v = np.zeros(t.n, dtype=object if ty in ("string", "rules") else (np.float64 if ty == "double" else np.int64))
@@ -482,6 +487,20 @@ def concat_tabs(tabs):
         out.add(name, ty, np.concatenate(vals) if vals else np.zeros(0), np.concatenate(oks) if oks else np.zeros(0, bool))
     out.nest = dict(tabs[0].nest)
     return out
+
+
+def ts_to_string(us):
+    """CAST(timestamp AS STRING) as Spark 2.4 prints it (DateTimeUtils.timestampToString: java.sql.Timestamp.toString with a
+    trailing ".0" removed), UTC session zone: yyyy-MM-dd HH:mm:ss plus the fraction without trailing zeros, if any."""
+    import datetime
+    sec, micro = divmod(us, 1_000_000)
+    d = datetime.datetime(1970, 1, 1) + datetime.timedelta(seconds=sec)
+    txt = d.strftime("%Y-%m-%d %H:%M:%S")
+    if len(txt) < 19:                      # years below 1000 come out unpadded on some platforms
+        txt = txt.rjust(19, "0")
+    if micro:
+        txt += (".%06d" % micro).rstrip("0")
+    return txt.encode()
 
 
 def _like_regex(pat):
@@ -577,7 +596,7 @@ class Ev:
                     return ty, v, ok
                 out = np.empty(n, dtype=object)
                 for i in range(n):
-                    out[i] = str(int(v[i])).encode() if ok[i] else None
+                    out[i] = (ts_to_string(int(v[i])) if ty == "ts" else str(int(v[i])).encode()) if ok[i] else None
                 return "string", out, ok
             if to == "timestamp":
                 if ty == "ts":
@@ -700,7 +719,7 @@ class Ev:
                     if not k[i]:
                         parts = None
                         break
-                    parts.append(v[i] if ty == "string" else str(int(v[i])).encode())
+                    parts.append(v[i] if ty == "string" else (ts_to_string(int(v[i])) if ty == "ts" else str(int(v[i])).encode()))
                 if fn == "CONCAT":
                     if parts is None:
                         ok[i] = False

@@ -35,9 +35,8 @@ PREAMBLE = {
 }
 # statements that are not Spark SQL (the fixtures' custom output template writes MAP('k': v)): spark.sql would throw
 NOT_SQL = {"CGenNoCode.txt", "CGenSimRulNonTable.txt"}
-# UNION ALL of a string column (deviceDetails.eventTime) with the state table's timestamp column: Spark widens the
-# timestamp to a string; that cast is not built, and both implementations say so instead of guessing
-UNSUPPORTED = {"CGenCreateMetric2.txt": "mixes types"}
+# (CGenCreateMetric2 unions a string column with the state table's timestamp column: widened to string, as Spark does)
+UNSUPPORTED = {}
 
 
 def names():

@@ -263,6 +263,23 @@ perType = SELECT deviceType, COUNT(*) AS Cnt, MAX(EventTime) AS Last FROM acc GR
     g2.close()
 
 
+def test_timestamp_to_string_cast_and_union_widening(dx, ctx):
+    """CAST(timestamp AS STRING) (yyyy-MM-dd HH:mm:ss[.fraction without trailing zeros], UTC) and the string promotion Spark
+    applies when a UNION ALL meets a string column and a timestamp column."""
+    tr = """--DataXQuery--
+A = SELECT CAST(eventTimeStamp AS STRING) AS s, CONCAT('at ', eventTimeStamp) AS c, deviceDetails.deviceId FROM DataXProcessedInput
+--DataXQuery--
+U = SELECT deviceDetails.deviceType AS x, deviceDetails.deviceId FROM DataXProcessedInput WHERE deviceDetails.status = 1
+    UNION ALL SELECT eventTimeStamp AS x, deviceDetails.deviceId FROM DataXProcessedInput WHERE deviceDetails.status = 0
+--DataXQuery--
+D = SELECT x, COUNT(*) AS n FROM U GROUP BY x
+"""
+    g, o = both(dx, ctx, dx.flowgen.conf_text("tsstr"), SCHEMA1, [PROJ_TS], tr)
+    check_batch(dx, g, o, gen(dx, 4000, shape=1, n_keys=50), T0)
+    check_batch(dx, g, o, to_ndjson(all_records(1500, seed=5)), T0 + I)
+    g.close()
+
+
 def test_unsupported_sql_fails_at_create(dx, ctx):
     for bad in ["--DataXQuery--\nx = SELECT a FROM t ORDER BY a\n", "--DataXQuery--\nSET spark.x=1\n--DataXQuery--\n"]:
         with pytest.raises(dx.DxError):
