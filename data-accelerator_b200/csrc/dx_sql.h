@@ -147,7 +147,25 @@ class Parser {
             if (t.t == Tok::Id) {
                 if (u == "NULL") { take(); return mk(EK::Null); }
                 if (u == "TRUE" || u == "FALSE") { take(); auto e = mk(EK::Bool); e->ival = (u == "TRUE"); return e; }
-                if (u == "CASE") throw SqlError("CASE expressions are outside the supported SQL subset");
+                if (u == "CASE") {
+                    // CASE [x] WHEN a THEN v ... [ELSE w] END  ==  IF(cond1, v1, IF(cond2, v2, ... w | NULL)): same evaluation order and
+                    // the same treatment of a NULL condition (not taken) as Spark's CaseWhen
+                    take();
+                    ExprP subject;
+                    if (!is_kw("WHEN")) subject = expr();
+                    std::vector<std::pair<ExprP, ExprP>> arms;
+                    while (accept_kw("WHEN")) {
+                        ExprP c = expr();
+                        if (subject) { auto eq = mk(EK::Bin); eq->sval = "="; eq->args = {subject, c}; c = eq; }
+                        expect_kw("THEN");
+                        arms.emplace_back(c, expr());
+                    }
+                    if (arms.empty()) throw SqlError("CASE without WHEN");
+                    ExprP tail = accept_kw("ELSE") ? expr() : mk(EK::Null);
+                    expect_kw("END");
+                    for (size_t i = arms.size(); i-- > 0;) { auto f = mk(EK::Func); f->sval = "IF"; f->args = {arms[i].first, arms[i].second, tail}; tail = f; }
+                    return tail;
+                }
                 if (u == "CAST" && is_op("(", 1)) {
                     take(); take();
                     auto e = mk(EK::Cast); e->args.push_back(expr());

@@ -136,7 +136,7 @@ def parse_duration(s):
 # --------------------------------------------------------------------------------------------------
 _TOK = re.compile(r"""\s*(?:(?P<num>\d+\.\d*(?:[eE][+-]?\d+)?|\.\d+(?:[eE][+-]?\d+)?|\d+(?:[eE][+-]?\d+)?)|(?P<id>[A-Za-z_][A-Za-z0-9_]*)|`(?P<qid>[^`]*)`|'(?P<str>(?:[^'\\]|\\.)*)'|"(?P<dstr>(?:[^"\\]|\\.)*)"|(?P<op><>|!=|<=|>=|==|\|\||[-+*/%(),.=<>;]))""")
 _KW = {"SELECT", "FROM", "WHERE", "GROUP", "BY", "AS", "AND", "OR", "NOT", "IN", "BETWEEN", "LIKE", "IS", "JOIN", "INNER", "ON",
-       "UNION", "ALL", "DISTINCT", "HAVING", "ORDER", "LIMIT"}
+       "UNION", "ALL", "DISTINCT", "HAVING", "ORDER", "LIMIT", "CASE", "WHEN", "THEN", "ELSE", "END"}
 
 
 def _unescape(s):
@@ -248,6 +248,23 @@ class P:
                 if u in ("TRUE", "FALSE"):
                     self.take()
                     return ("bool", u == "TRUE")
+                if u == "CASE":
+                    self.take()
+                    subject = None if self.kw("WHEN") else self.expr()
+                    arms = []
+                    while self.accept_kw("WHEN"):
+                        c = self.expr()
+                        if subject is not None:
+                            c = ("bin", "=", subject, c)
+                        self.expect_kw("THEN")
+                        arms.append((c, self.expr()))
+                    if not arms:
+                        raise ValueError("CASE without WHEN")
+                    tail = self.expr() if self.accept_kw("ELSE") else ("null",)
+                    self.expect_kw("END")
+                    for c, v in reversed(arms):      # CaseWhen == nested IF (a NULL condition is not taken)
+                        tail = ("func", "IF", [c, v, tail], False, False)
+                    return tail
                 if u == "CAST" and self.op("(", 1):
                     self.take(); self.take()
                     e = self.expr()

@@ -280,6 +280,21 @@ D = SELECT x, COUNT(*) AS n FROM U GROUP BY x
     g.close()
 
 
+def test_case_when(dx, ctx):
+    """CASE WHEN / simple CASE (Spark's CaseWhen: first TRUE arm, a NULL condition is not taken, no ELSE -> NULL)."""
+    tr = """--DataXQuery--
+A = SELECT deviceDetails.deviceId, CASE WHEN deviceDetails.temperature > 50 THEN 1 WHEN deviceDetails.humidity > 50 THEN 2 END AS band,
+    CASE deviceDetails.status WHEN 1 THEN deviceDetails.temperature ELSE deviceDetails.humidity END AS v
+    FROM DataXProcessedInput WHERE CASE WHEN deviceDetails.homeId > 50 THEN deviceDetails.status = 1 ELSE deviceDetails.status = 0 END
+--DataXQuery--
+B = SELECT band, COUNT(*) AS n, MAX(v) AS mx FROM A GROUP BY band
+"""
+    g, o = both(dx, ctx, dx.flowgen.conf_text("case"), SCHEMA2, ["Raw.*\n"], tr)
+    check_batch(dx, g, o, gen(dx, 5000, n_keys=200), T0)
+    check_batch(dx, g, o, to_ndjson(all_records(2000, seed=21)), T0 + I)
+    g.close()
+
+
 def test_unsupported_sql_fails_at_create(dx, ctx):
     for bad in ["--DataXQuery--\nx = SELECT a FROM t ORDER BY a\n", "--DataXQuery--\nSET spark.x=1\n--DataXQuery--\n"]:
         with pytest.raises(dx.DxError):
