@@ -691,15 +691,18 @@ struct Exec {
                 keep.push_back(lk); keep.push_back(rk);
             }
             DevBufP li, ri; int64_t np = 0;
-            rc = dx_join_pairs(ctx, L, acc->n_rows, nullptr, R, right->n_rows, &li, &ri, &np); if (rc) return rc;
+            rc = dx_join_pairs(ctx, L, acc->n_rows, nullptr, R, right->n_rows, &li, &ri, &np, j.left_outer); if (rc) return rc;
             auto jt = std::make_shared<DxTable>(); jt->ctx = ctx; jt->n_rows = np;
             MaskAlloc masks(ctx, np);
             std::vector<std::string> new_owners;
             int idx = 0;
-            auto add_side = [&](const DxTable* t, const std::vector<std::string>& own, const DevBufP& sel) -> int {
+            auto add_side = [&](const DxTable* t, const std::vector<std::string>& own, const DevBufP& sel, bool outer_side) -> int {
                 for (size_t c = 0; c < t->cols.size(); c++) {
                     DxColumn oc = t->cols[c];
                     if (oc.type == DX_T_FLAGS) return fail(DX_ERR_UNSUPPORTED, "JOIN over a rule-flag column");
+                    if (outer_side && !oc.data && !oc.all_null && oc.type != DX_T_NULL) {     // a constant would survive on unmatched rows
+                        int rc3 = materialize_const(&oc, t->n_rows, nullptr); if (rc3) return rc3;
+                    }
                     if (oc.data && !oc.all_null) {
                         DevBufP nb = make_buf(ctx, (size_t)(np > 0 ? np : 1) * dx_type_width(oc.type));
                         DxColumn dst = oc; dst.data = nb;
@@ -711,9 +714,9 @@ struct Exec {
                 }
                 return DX_OK;
             };
-            rc = add_side(acc.get(), owners, li); if (rc) return rc;
+            rc = add_side(acc.get(), owners, li, false); if (rc) return rc;
             std::vector<std::string> rown(right->cols.size(), right_name);
-            rc = add_side(right.get(), rown, ri); if (rc) return rc;
+            rc = add_side(right.get(), rown, ri, j.left_outer); if (rc) return rc;
             DX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
             acc = jt; owners = new_owners;
         }

@@ -41,7 +41,7 @@ __global__ void k_join_build(const __grid_constant__ JoinSide R, long long n, lo
 // probe: pass 0 counts the matches of every left row, pass 1 writes the pairs at the scanned offsets
 __global__ void k_join_probe(const __grid_constant__ JoinSide L, const __grid_constant__ JoinSide R, long long n_left, const long long* sel,
                              const long long* head, unsigned long long mask, const long long* next, long long* counts_or_offsets,
-                             long long* out_left, long long* out_right, int pass) {
+                             long long* out_left, long long* out_right, int pass, int left_outer) {
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_left; i += (long long)gridDim.x * blockDim.x) {
         const long long row = sel ? sel[i] : i;
         long long kv[DX_JOIN_MAX_KEYS]; unsigned long long h;
@@ -54,6 +54,10 @@ __global__ void k_join_probe(const __grid_constant__ JoinSide L, const __grid_co
                 if (same) { if (pass) { out_left[base + cnt] = row; out_right[base + cnt] = r; } cnt++; }
             }
         }
+        if (left_outer && cnt == 0) {       // LEFT OUTER: an unmatched left row is kept once, its right side NULL (index -1)
+            if (pass) { out_left[base] = row; out_right[base] = -1; }
+            cnt = 1;
+        }
         if (!pass) counts_or_offsets[i] = cnt;
     }
 }
@@ -64,21 +68,21 @@ static unsigned grid_of(dx_ctx* c, long long n) {
 }
 
 int dx_join_pairs(dx_ctx* ctx, const JoinSide& L, int64_t n_left, const int64_t* sel_left, const JoinSide& R, int64_t n_right,
-                  DevBufP* left_idx, DevBufP* right_idx, int64_t* n_pairs) {
+                  DevBufP* left_idx, DevBufP* right_idx, int64_t* n_pairs, bool left_outer) {
     *n_pairs = 0;
     *left_idx = make_buf(ctx, 8); *right_idx = make_buf(ctx, 8);
-    if (n_left <= 0 || n_right <= 0) return DX_OK;
-    unsigned long long cap = 64; while (cap < (unsigned long long)n_right * 2) cap <<= 1;
-    DevBuf head(ctx, cap * 8), next(ctx, (size_t)n_right * 8), counts(ctx, (size_t)(n_left + 1) * 8), offs(ctx, (size_t)(n_left + 1) * 8);
+    if (n_left <= 0 || (n_right <= 0 && !left_outer)) return DX_OK;
+    unsigned long long cap = 64; while (cap < (unsigned long long)(n_right > 0 ? n_right : 1) * 2) cap <<= 1;
+    DevBuf head(ctx, cap * 8), next(ctx, (size_t)(n_right > 0 ? n_right : 1) * 8), counts(ctx, (size_t)(n_left + 1) * 8), offs(ctx, (size_t)(n_left + 1) * 8);
     if (!head.p || !next.p || !counts.p || !offs.p) return ctx->set_error(DX_ERR_CUDA, "join allocation failed");
     DX_CUDA(ctx, cudaMemsetAsync(head.p, 0xFF, cap * 8, ctx->stream));
     DX_CUDA(ctx, cudaMemsetAsync(counts.p, 0, (size_t)(n_left + 1) * 8, ctx->stream));
-    k_join_build<<<grid_of(ctx, n_right), 256, 0, ctx->stream>>>(R, n_right, head.as<long long>(), cap - 1, next.as<long long>());
+    if (n_right > 0) k_join_build<<<grid_of(ctx, n_right), 256, 0, ctx->stream>>>(R, n_right, head.as<long long>(), cap - 1, next.as<long long>());
     ctx->launches["k_join_build"]++;
     {
         StageTimer tm(ctx, "k_join_probe");
         k_join_probe<<<grid_of(ctx, n_left), 256, 0, ctx->stream>>>(L, R, n_left, reinterpret_cast<const long long*>(sel_left), head.as<long long>(), cap - 1,
-                                                                    next.as<long long>(), counts.as<long long>(), nullptr, nullptr, 0);
+                                                                    next.as<long long>(), counts.as<long long>(), nullptr, nullptr, 0, left_outer ? 1 : 0);
         ctx->launches["k_join_probe"]++;
     }
     size_t tmp_bytes = 0;
@@ -93,7 +97,7 @@ int dx_join_pairs(dx_ctx* ctx, const JoinSide& L, int64_t n_left, const int64_t*
     *left_idx = make_buf(ctx, (size_t)total * 8); *right_idx = make_buf(ctx, (size_t)total * 8);
     if (!(*left_idx)->p || !(*right_idx)->p) return ctx->set_error(DX_ERR_CUDA, "join output allocation failed");
     k_join_probe<<<grid_of(ctx, n_left), 256, 0, ctx->stream>>>(L, R, n_left, reinterpret_cast<const long long*>(sel_left), head.as<long long>(), cap - 1,
-                                                                next.as<long long>(), offs.as<long long>(), (*left_idx)->as<long long>(), (*right_idx)->as<long long>(), 1);
+                                                                next.as<long long>(), offs.as<long long>(), (*left_idx)->as<long long>(), (*right_idx)->as<long long>(), 1, left_outer ? 1 : 0);
     ctx->launches["k_join_probe"]++;
     DX_CUDA(ctx, cudaGetLastError());
     DX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));

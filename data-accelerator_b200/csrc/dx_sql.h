@@ -36,7 +36,7 @@ struct Expr {
 };
 
 struct SelectItem { ExprP expr; std::string alias; };
-struct JoinClause { std::string table, alias; ExprP on; };
+struct JoinClause { std::string table, alias; ExprP on; bool left_outer = false; };
 struct SelectCore {
     bool distinct = false;
     std::vector<SelectItem> items;
@@ -275,11 +275,13 @@ class Parser {
         Tok t = take(); if (t.t != Tok::Id && t.t != Tok::QId) throw SqlError("expected table name after FROM");
         s.from = t.s; s.from_alias = alias_opt();
         for (;;) {
-            if (is_kw("LEFT") || is_kw("RIGHT") || is_kw("FULL") || is_kw("CROSS"))
-                throw SqlError("only INNER JOIN is inside the supported SQL subset");
-            if (is_kw("INNER") && is_kw("JOIN", 1)) take();
+            if (is_kw("RIGHT") || is_kw("FULL") || is_kw("CROSS"))
+                throw SqlError("only INNER and LEFT [OUTER] JOIN are inside the supported SQL subset");
+            bool left_outer = false;
+            if (is_kw("LEFT") && (is_kw("JOIN", 1) || (is_kw("OUTER", 1) && is_kw("JOIN", 2)))) { take(); accept_kw("OUTER"); left_outer = true; }
+            else if (is_kw("INNER") && is_kw("JOIN", 1)) take();
             if (!accept_kw("JOIN")) break;
-            JoinClause j; Tok jt = take(); if (jt.t != Tok::Id && jt.t != Tok::QId) throw SqlError("expected table name after JOIN");
+            JoinClause j; j.left_outer = left_outer; Tok jt = take(); if (jt.t != Tok::Id && jt.t != Tok::QId) throw SqlError("expected table name after JOIN");
             j.table = jt.s; j.alias = alias_opt();
             expect_kw("ON"); j.on = expr();
             s.joins.push_back(j);
@@ -361,7 +363,7 @@ static inline std::string to_string(const Statement& st) {
             if (!s.items[i].alias.empty()) out += " AS " + s.items[i].alias;
         }
         out += " FROM " + s.from; if (!s.from_alias.empty()) out += " AS " + s.from_alias;
-        for (auto& j : s.joins) { out += " JOIN " + j.table; if (!j.alias.empty()) out += " AS " + j.alias; out += " ON " + to_string(j.on); }
+        for (auto& j : s.joins) { out += (j.left_outer ? " LEFT JOIN " : " JOIN ") + j.table; if (!j.alias.empty()) out += " AS " + j.alias; out += " ON " + to_string(j.on); }
         if (s.where) out += " WHERE " + to_string(s.where);
         if (!s.group_by.empty()) { out += " GROUP BY "; out += join_args(s.group_by); }
     }

@@ -135,7 +135,7 @@ def parse_duration(s):
 # SQL subset: tokenizer + parser (independent of the product's)
 # --------------------------------------------------------------------------------------------------
 _TOK = re.compile(r"""\s*(?:(?P<num>\d+\.\d*(?:[eE][+-]?\d+)?|\.\d+(?:[eE][+-]?\d+)?|\d+(?:[eE][+-]?\d+)?)|(?P<id>[A-Za-z_][A-Za-z0-9_]*)|`(?P<qid>[^`]*)`|'(?P<str>(?:[^'\\]|\\.)*)'|"(?P<dstr>(?:[^"\\]|\\.)*)"|(?P<op><>|!=|<=|>=|==|\|\||[-+*/%(),.=<>;]))""")
-_KW = {"SELECT", "FROM", "WHERE", "GROUP", "BY", "AS", "AND", "OR", "NOT", "IN", "BETWEEN", "LIKE", "IS", "JOIN", "INNER", "ON",
+_KW = {"SELECT", "FROM", "WHERE", "GROUP", "BY", "AS", "AND", "OR", "NOT", "IN", "BETWEEN", "LIKE", "IS", "JOIN", "INNER", "LEFT", "OUTER", "ON",
        "UNION", "ALL", "DISTINCT", "HAVING", "ORDER", "LIMIT", "CASE", "WHEN", "THEN", "ELSE", "END"}
 
 
@@ -399,14 +399,20 @@ class P:
         frm = self.take()[1]
         frm_alias = self.alias()
         joins = []
-        while self.kw("JOIN") or (self.kw("INNER") and self.kw("JOIN", 1)):
-            if self.kw("INNER"):
+        while True:
+            outer = False
+            if self.kw("LEFT") and (self.kw("JOIN", 1) or (self.kw("OUTER", 1) and self.kw("JOIN", 2))):
                 self.take()
-            self.take()
+                self.accept_kw("OUTER")
+                outer = True
+            elif self.kw("INNER") and self.kw("JOIN", 1):
+                self.take()
+            if not self.accept_kw("JOIN"):
+                break
             jt = self.take()[1]
             ja = self.alias()
             self.expect_kw("ON")
-            joins.append((jt, ja, self.expr()))
+            joins.append((jt, ja, self.expr(), outer))
         where = self.expr() if self.accept_kw("WHERE") else None
         group = []
         if self.kw("GROUP"):
@@ -474,6 +480,8 @@ class Tab:
         for name, ty, v, ok in self.cols:
             t.add(name, ty, v[idx] if v is not None else None, ok[idx])
         t.nest = dict(getattr(self, "nest", {}))
+        if getattr(self, "owners", None):
+            t.owners = list(self.owners)
         return t
 
 
@@ -904,7 +912,7 @@ def _join(core, views, now_us):
     lname = core["alias"] or core["from"]
     owners = list(getattr(left, "owners", None) or [lname] * len(left.cols))
     acc = left
-    for jt, ja, on in core["joins"]:
+    for jt, ja, on, outer in core["joins"]:
         right = views[jt]
         rname = ja or jt
         acc.owners = owners
@@ -933,17 +941,25 @@ def _join(core, views, now_us):
         li, ri = [], []
         for l in range(acc.n):
             k = tuple(col[l] for col in lkeys)
-            if None in k:
-                continue
-            for r in index.get(k, ()):
+            hits = () if None in k else index.get(k, ())
+            for r in hits:
                 li.append(l)
                 ri.append(r)
+            if outer and not hits:          # LEFT OUTER: the unmatched left row once, right side NULL
+                li.append(l)
+                ri.append(-1)
         li, ri = np.array(li, dtype=np.int64), np.array(ri, dtype=np.int64)
         out = Tab(len(li))
         for c in acc.cols:
             out.add(c[0], c[1], c[2][li] if c[2] is not None else None, c[3][li])
+        miss = ri < 0
+        rsafe = np.where(miss, 0, ri)
         for c in right.cols:
-            out.add(c[0], c[1], c[2][ri] if c[2] is not None else None, c[3][ri])
+            if right.n == 0:
+                vals = None if c[2] is None else np.zeros(len(ri), dtype=c[2].dtype)
+                out.add(c[0], c[1], vals, np.zeros(len(ri), bool))
+            else:
+                out.add(c[0], c[1], c[2][rsafe] if c[2] is not None else None, c[3][rsafe] & ~miss)
         owners = owners + [rname] * len(right.cols)
         acc = out
     acc.owners = owners

@@ -280,6 +280,28 @@ D = SELECT x, COUNT(*) AS n FROM U GROUP BY x
     g.close()
 
 
+def test_left_outer_join(dx, ctx):
+    """LEFT [OUTER] JOIN: unmatched left rows survive once with NULL right columns (reference data that does not
+    know every device; a derived table that lacks some keys), NULL keys never match."""
+    tr = """--DataXQuery--
+Named = SELECT deviceDetails.deviceId, deviceDetails.status, names.deviceName, names.floor FROM DataXProcessedInput
+    LEFT JOIN names ON deviceDetails.deviceId = names.deviceId
+--DataXQuery--
+PerHome = SELECT deviceDetails.homeId AS h, COUNT(*) AS n FROM DataXProcessedInput WHERE deviceDetails.status = 1 GROUP BY deviceDetails.homeId
+--DataXQuery--
+Both = SELECT a.deviceId, a.deviceName, b.n FROM Named a LEFT OUTER JOIN PerHome b ON a.deviceId = b.h WHERE a.status = 0
+--DataXQuery--
+Cnt = SELECT deviceName, COUNT(*) AS c, COUNT(floor) AS f FROM Named GROUP BY deviceName
+"""
+    csv = "deviceId,deviceName,floor\n1,door,0\n3,window,1\n5,heater,\n8,garage,2\n"
+    g, o = both(dx, ctx, dx.flowgen.conf_text("lj"), SCHEMA1, ["Raw.*\n"], tr)
+    g.add_refdata("names", csv)
+    o.add_refdata("names", csv)
+    check_batch(dx, g, o, gen(dx, 3000, shape=1, n_keys=12), T0)
+    check_batch(dx, g, o, to_ndjson(all_records(1500, seed=21)), T0 + I)
+    g.close()
+
+
 def test_case_when(dx, ctx):
     """CASE WHEN / simple CASE (Spark's CaseWhen: first TRUE arm, a NULL condition is not taken, no ELSE -> NULL)."""
     tr = """--DataXQuery--

@@ -64,7 +64,7 @@ def test_sql_subset_parser(dx):
     assert "NOT IN" in c("SELECT * FROM t WHERE x NOT IN (1,2) AND y BETWEEN 1 AND 3 AND z NOT LIKE '%a' AND w IS NOT NULL")
     assert c("SELECT CASE WHEN a > 1 THEN 'x' WHEN a > 0 THEN 'y' ELSE 'z' END AS k, CASE b WHEN 1 THEN 2 END FROM t") == \
         "SELECT IF((a > 1), 'x', IF((a > 0), 'y', 'z')) AS k, IF((b = 1), 2, NULL) FROM t"
-    for bad in ("SELECT a FROM t ORDER BY a", "SELECT CASE WHEN a THEN 1 FROM t", "SELECT a FROM t LEFT JOIN u ON a=b", "SELEC a"):
+    for bad in ("SELECT a FROM t ORDER BY a", "SELECT CASE WHEN a THEN 1 FROM t", "SELECT a FROM t RIGHT JOIN u ON a=b", "SELEC a"):
         with pytest.raises(dx.DxError):
             c(bad)
 
