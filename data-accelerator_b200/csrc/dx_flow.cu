@@ -577,7 +577,43 @@ struct Exec {
         return DX_OK;
     }
 
+    // HAVING cond  ==  the aggregation with every aggregate (and bare column) of cond added as a hidden item, then a WHERE over
+    // its result that keeps the visible items only.
+    ExprP having_rewrite(const ExprP& e, std::vector<SelectItem>* inner, const std::vector<SelectItem>& visible) {
+        if (!e) return e;
+        if (is_agg_func(e) || e->kind == EK::Col) {
+            const std::string key = to_string(e);
+            for (auto& it : *inner) if (to_string(it.expr) == key) {
+                auto c = std::make_shared<Expr>(); c->kind = EK::Col; c->parts = {item_name(it)}; return c;
+            }
+            if (e->kind == EK::Col && e->parts.size() == 1)          // a select alias
+                for (auto& it : visible) if (item_name(it) == e->parts[0]) return e;
+            SelectItem h; h.expr = e; h.alias = "__having" + std::to_string(inner->size());
+            inner->push_back(h);
+            auto c = std::make_shared<Expr>(); c->kind = EK::Col; c->parts = {h.alias}; return c;
+        }
+        auto cp = std::make_shared<Expr>(*e);
+        for (auto& a2 : cp->args) a2 = having_rewrite(a2, inner, visible);
+        return cp;
+    }
+
     int exec_core(const SelectCore& core, DxTableP* out) {
+        if (core.having) {
+            for (auto& it : core.items) if (it.expr->kind == EK::Star) return fail(DX_ERR_UNSUPPORTED, "HAVING with SELECT *");
+            SelectCore inner = core; inner.having = nullptr;
+            ExprP cond = having_rewrite(core.having, &inner.items, core.items);
+            DxTableP agg; int rc = exec_core(inner, &agg); if (rc) return rc;
+            View hv; hv.chunks.push_back(agg);
+            (*views)["__having"] = hv;
+            SelectCore outer; outer.from = "__having"; outer.where = cond;
+            for (auto& it : core.items) {
+                SelectItem oi; oi.expr = std::make_shared<Expr>(); oi.expr->kind = EK::Col; oi.expr->parts = {item_name(it)}; oi.alias = item_name(it);
+                outer.items.push_back(oi);
+            }
+            rc = exec_core(outer, out);
+            views->erase("__having");
+            return rc;
+        }
         bool nested = false;
         for (auto& it : core.items) if (is_nested_ctor(it.expr)) nested = true;
         if (nested) {

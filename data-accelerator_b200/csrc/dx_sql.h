@@ -1,5 +1,5 @@
 // dx_sql.h — parser for the Spark-SQL subset that Data Accelerator flows actually contain
-// (SURVEY.md §7.4): SELECT [DISTINCT] ... FROM t [[INNER] JOIN u ON ...] [WHERE ...] [GROUP BY ...]
+// (SURVEY.md §7.4): SELECT [DISTINCT] ... FROM t [[INNER | LEFT [OUTER]] JOIN u ON ...] [WHERE ...] [GROUP BY ...] [HAVING ...]
 // [UNION [ALL] SELECT ...], expressions with AND/OR/NOT, comparisons, IN, BETWEEN, LIKE, IS NULL,
 // arithmetic, function calls, CAST, dotted and back-ticked names.
 //
@@ -44,6 +44,7 @@ struct SelectCore {
     std::vector<JoinClause> joins;
     ExprP where;
     std::vector<ExprP> group_by;
+    ExprP having;
 };
 struct Statement {
     std::vector<SelectCore> selects;     // > 1: UNION [ALL] chain
@@ -288,7 +289,8 @@ class Parser {
         }
         if (accept_kw("WHERE")) s.where = expr();
         if (is_kw("GROUP")) { take(); expect_kw("BY"); do { s.group_by.push_back(expr()); } while (accept_op(",")); }
-        if (is_kw("HAVING") || is_kw("ORDER") || is_kw("LIMIT"))
+        if (accept_kw("HAVING")) s.having = expr();
+        if (is_kw("ORDER") || is_kw("LIMIT"))
             throw SqlError(upper(peek().s) + " is outside the supported SQL subset");
         return s;
     }
@@ -366,6 +368,7 @@ static inline std::string to_string(const Statement& st) {
         for (auto& j : s.joins) { out += (j.left_outer ? " LEFT JOIN " : " JOIN ") + j.table; if (!j.alias.empty()) out += " AS " + j.alias; out += " ON " + to_string(j.on); }
         if (s.where) out += " WHERE " + to_string(s.where);
         if (!s.group_by.empty()) { out += " GROUP BY "; out += join_args(s.group_by); }
+        if (s.having) out += " HAVING " + to_string(s.having);
     }
     return out;
 }

@@ -421,7 +421,9 @@ class P:
             group.append(self.expr())
             while self.accept_op(","):
                 group.append(self.expr())
-        return {"distinct": distinct, "items": items, "from": frm, "alias": frm_alias, "where": where, "group": group, "joins": joins}
+        having = self.expr() if self.accept_kw("HAVING") else None
+        return {"distinct": distinct, "items": items, "from": frm, "alias": frm_alias, "where": where, "group": group, "joins": joins,
+                "having": having}
 
     def statement(self):
         sel = [self.select_core()]
@@ -966,7 +968,31 @@ def _join(core, views, now_us):
     return acc
 
 
+def _having_rewrite(e, inner, visible):
+    """Aggregates and bare columns of a HAVING condition -> references to (possibly hidden) items of the aggregation."""
+    if not isinstance(e, tuple):
+        return e
+    if (e[0] == "func" and e[1] in AGGS) or e[0] == "col":
+        for x, alias in inner:
+            if x == e:
+                return ("col", [_item_name(x, alias)])
+        if e[0] == "col" and len(e[1]) == 1 and any(_item_name(x, a) == e[1][0] for x, a in visible):
+            return e
+        name = "__having%d" % len(inner)
+        inner.append((e, name))
+        return ("col", [name])
+    return tuple([_having_rewrite(y, inner, visible) for y in x] if isinstance(x, list) else _having_rewrite(x, inner, visible) for x in e)
+
+
 def exec_core(core, views, now_us):
+    if core.get("having") is not None:
+        inner_items = list(core["items"])
+        cond = _having_rewrite(core["having"], inner_items, core["items"])
+        v2 = CiDict(views)
+        v2["__having"] = exec_core(dict(core, items=inner_items, having=None), views, now_us)
+        outer_items = [(("col", [_item_name(e, a)]), _item_name(e, a)) for e, a in core["items"]]
+        return exec_core({"distinct": False, "items": outer_items, "from": "__having", "alias": None, "where": cond, "group": [],
+                          "joins": [], "having": None}, v2, now_us)
     if any(e[0] == "func" and e[1] in _NESTED for e, _ in core["items"]):
         items, nest = [], {}
         for e, alias in core["items"]:

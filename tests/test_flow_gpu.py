@@ -302,6 +302,21 @@ Cnt = SELECT deviceName, COUNT(*) AS c, COUNT(floor) AS f FROM Named GROUP BY de
     g.close()
 
 
+def test_having(dx, ctx):
+    """HAVING over aggregates that are and are not in the select list, a select alias and a group key."""
+    tr = """--DataXQuery--
+Busy = SELECT deviceDetails.homeId, COUNT(*) AS n, AVG(deviceDetails.temperature) AS t FROM DataXProcessedInput
+    GROUP BY deviceDetails.homeId HAVING COUNT(*) > 20 AND MAX(deviceDetails.humidity) > 90 AND n < 100000 AND deviceDetails.homeId <> 3
+--DataXQuery--
+Hot = SELECT deviceDetails.deviceType, MIN(deviceDetails.temperature) AS lo FROM DataXProcessedInput
+    WHERE deviceDetails.status = 1 GROUP BY deviceDetails.deviceType HAVING AVG(deviceDetails.temperature) >= 50 OR SUM(deviceDetails.status) IS NULL
+"""
+    g, o = both(dx, ctx, dx.flowgen.conf_text("having"), SCHEMA2, ["Raw.*\n"], tr)
+    check_batch(dx, g, o, gen(dx, 6000, n_keys=400), T0)
+    check_batch(dx, g, o, to_ndjson(all_records(2000, seed=21)), T0 + I)
+    g.close()
+
+
 def test_case_when(dx, ctx):
     """CASE WHEN / simple CASE (Spark's CaseWhen: first TRUE arm, a NULL condition is not taken, no ELSE -> NULL)."""
     tr = """--DataXQuery--
