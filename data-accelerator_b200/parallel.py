@@ -140,6 +140,14 @@ def put_by_key(table, cols, key_cols, world, peer_ptrs, first_record):
     table.ctx.check(L.dx_table_shuffle_put(table.h, c_cols, len(cols), c_keys, len(key_cols), world, ptrs, first))
 
 
+def block_offsets(M, rank):
+    """M[s][d] = records rank s sends to rank d  ->  (first[d]: where rank `rank`'s block starts in rank d's receive buffer —
+    blocks are laid out in sender order — and recv_total[d]: records rank d receives in all)."""
+    M = np.asarray(M, dtype=np.int64)
+    first = M[:rank].sum(axis=0) if rank else np.zeros(M.shape[1], dtype=np.int64)
+    return first, M.sum(axis=0)
+
+
 class PeerExchange:
     """Receive buffers of all ranks of one box, mapped into every process (CUDA IPC over NVLink), and the bookkeeping of
     one fused exchange per micro-batch: counts -> all_gather -> block offsets -> put -> barrier -> local unpack.
@@ -179,10 +187,9 @@ class PeerExchange:
         allc = [torch.empty_like(mine) for _ in range(self.world)]
         dist.all_gather(allc, mine, group=self.group)          # also orders this batch after every rank's previous unpack
         M = torch.stack(allc).cpu().numpy()                    # M[s][d] = records rank s sends to rank d
-        recv_total = M.sum(axis=0)
+        first, recv_total = block_offsets(M, self.rank)
         if int(recv_total.max()) > self.capacity:
             raise RuntimeError("PeerExchange: %d records for one rank exceed the buffer capacity %d" % (int(recv_total.max()), self.capacity))
-        first = M[:self.rank].sum(axis=0) if self.rank else np.zeros(self.world, dtype=np.int64)
         put_by_key(table, cols, key_cols, self.world, self.ptrs, first)
         dist.barrier(group=self.group)                         # every rank's puts have landed
         torch.cuda.synchronize()                               # (the barrier runs on torch's stream, the unpack on the library's)

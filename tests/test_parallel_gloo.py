@@ -84,3 +84,20 @@ def test_two_rank_key_hash_exchange_over_gloo():
     assert sent == recv == 40_000
     expected = _agg(np.concatenate([_make_records(r) for r in range(world)]))
     assert merged == expected
+
+
+def test_block_offsets_tile_every_receive_buffer():
+    """Fused put bookkeeping: the blocks the senders are assigned in one receiver's buffer are disjoint, in sender order,
+    and cover exactly the records that receiver is due."""
+    import numpy as np
+    import dxgpu as dx
+    rng = np.random.default_rng(3)
+    for world in (1, 2, 8):
+        M = rng.integers(0, 1000, size=(world, world))
+        firsts = [dx.parallel.block_offsets(M, r) for r in range(world)]
+        for d in range(world):
+            at = 0
+            for s in range(world):
+                assert firsts[s][0][d] == at
+                at += M[s][d]
+            assert at == firsts[0][1][d] == M[:, d].sum()
