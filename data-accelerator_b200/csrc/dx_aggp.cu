@@ -4,9 +4,11 @@
 #include <chrono>
 static inline long long now_us() { return std::chrono::duration_cast<std::chrono::microseconds>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
 
-#define K3P_SLOTS 1024          // shared hash-table slots per CTA
+#ifndef K3P_SLOTS
+#define K3P_SLOTS 512           // shared hash-table slots per CTA (512: four CTAs per SM; measured best of 256 / 512 / 1024)
+#endif
 #define K3P_NT 256
-#define K3P_MAX_GROUPS 700      // per partition; above this the caller re-partitions finer
+#define K3P_MAX_GROUPS (K3P_SLOTS * 7 / 10)      // per partition; above this the caller re-partitions finer
 
 static __device__ __forceinline__ unsigned long long pmix64(unsigned long long z) {
     z += 0x9E3779B97F4A7C15ull;
