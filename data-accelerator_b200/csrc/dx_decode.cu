@@ -200,12 +200,31 @@ __global__ void __launch_bounds__(K1_NT, K1_MIN_CTAS) k1_decode(const __grid_con
                     for (int i = 0; i < 16; i++) if (q0 + i < (long long)a.skew) m &= ~(1u << i);
                 }
                 if (r & 1) my_masks[r >> 1] |= m << 16; else my_masks[r >> 1] = m;
-                uint32_t c = __popc(m);
-                uint32_t inc = c;
+                excl_in_warp[r] = __popc(m);          // this lane's count for now; turned into a rank below
+            }
+            {
+                // one prefix sum for three rounds at a time: a lane's count is <= 16 and a round's total <= 512, so three 10-bit
+                // fields share a word and the rounds' shuffle chains run side by side instead of one after the other
+                constexpr int NW = (ROUNDS + 2) / 3;
+                uint32_t pk[NW];
 #pragma unroll
-                for (int s = 1; s < 32; s <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, inc, s); if (lane >= s) inc += t; }
-                excl_in_warp[r] = cnt_total + inc - c;
-                cnt_total += __shfl_sync(0xffffffffu, inc, 31);
+                for (int w = 0; w < NW; w++) {
+                    pk[w] = excl_in_warp[3 * w];
+                    if (3 * w + 1 < ROUNDS) pk[w] |= excl_in_warp[3 * w + 1] << 10;
+                    if (3 * w + 2 < ROUNDS) pk[w] |= excl_in_warp[3 * w + 2] << 20;
+                }
+#pragma unroll
+                for (int s = 1; s < 32; s <<= 1) {
+#pragma unroll
+                    for (int w = 0; w < NW; w++) { const uint32_t t = __shfl_up_sync(0xffffffffu, pk[w], s); if (lane >= s) pk[w] += t; }
+                }
+#pragma unroll
+                for (int r = 0; r < ROUNDS; r++) {
+                    const uint32_t incl = (pk[r / 3] >> (10 * (r % 3))) & 1023u;
+                    const uint32_t tot = (__shfl_sync(0xffffffffu, pk[r / 3], 31) >> (10 * (r % 3))) & 1023u;
+                    excl_in_warp[r] = cnt_total + incl - excl_in_warp[r];
+                    cnt_total += tot;
+                }
             }
             if (lane == 0) s_wtot[warp] = cnt_total;
             if (warp == K1_NT / 32 - 1) {
