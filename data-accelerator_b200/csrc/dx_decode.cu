@@ -178,6 +178,7 @@ __global__ void __launch_bounds__(K1_NT, K1_MIN_CTAS) k1_decode(const __grid_con
             constexpr int ROUNDS = CPW / 32;                  // 8
             uint32_t cnt_total = 0;
             uint32_t excl_in_warp[ROUNDS];
+            const bool edge_tile = lo < (long long)a.skew || lo + (long long)K1_T + 16 >= a.n_end;
 #pragma unroll
             for (int r = 0; r < ROUNDS; r++) {
                 const int chunk = warp * CPW + r * 32 + lane;
@@ -192,12 +193,14 @@ __global__ void __launch_bounds__(K1_NT, K1_MIN_CTAS) k1_decode(const __grid_con
                     m |= ((t * 0x00204081u) >> 28) << (k * 4);              // gather the four flags
                 }
                 // validity of each candidate q = lo + chunk*16 + i : start q+1 must be data (< n_end), q >= skew
-                const long long q0 = lo + (long long)chunk * 16;
-                if (q0 + 16 >= a.n_end) {
-                    for (int i = 0; i < 16; i++) if (q0 + i + 1 >= a.n_end) m &= ~(1u << i);
-                }
-                if (q0 < (long long)a.skew) {
-                    for (int i = 0; i < 16; i++) if (q0 + i < (long long)a.skew) m &= ~(1u << i);
+                if (edge_tile) {        // only the first and the last tile of a batch can hold candidates outside the data
+                    const long long q0 = lo + (long long)chunk * 16;
+                    if (q0 + 16 >= a.n_end) {
+                        for (int i = 0; i < 16; i++) if (q0 + i + 1 >= a.n_end) m &= ~(1u << i);
+                    }
+                    if (q0 < (long long)a.skew) {
+                        for (int i = 0; i < 16; i++) if (q0 + i < (long long)a.skew) m &= ~(1u << i);
+                    }
                 }
                 if (r & 1) my_masks[r >> 1] |= m << 16; else my_masks[r >> 1] = m;
                 excl_in_warp[r] = __popc(m);          // this lane's count for now; turned into a rank below
