@@ -284,13 +284,12 @@ __global__ void __launch_bounds__(K1_NT, K1_MIN_CTAS) k1_decode(const __grid_con
 #pragma unroll
                 for (int r = 0; r < ROUNDS; r++) {
                     uint32_t m = (r & 1) ? (my_masks[r >> 1] >> 16) : (my_masks[r >> 1] & 0xffffu);
-                    long long rank = (long long)my_base + excl_in_warp[r];
-                    const int chunk = warp * CPW + r * 32 + lane;
+                    uint32_t rel = my_base + excl_in_warp[r] - (uint32_t)round0;     // wraps to a huge value for earlier rounds' records
+                    const uint32_t pos0 = (uint32_t)(warp * CPW + r * 32 + lane) * 16 + 1;
                     while (m) {
-                        int i = __ffs(m) - 1; m &= m - 1;
-                        long long rel = rank - round0;
-                        if (rel >= 0 && rel <= K1_SC) s_starts[rel] = (uint16_t)(chunk * 16 + i + 1);
-                        rank++;
+                        const int i = __ffs(m) - 1; m &= m - 1;
+                        if (rel <= K1_SC) s_starts[rel] = (uint16_t)(pos0 + i);
+                        rel++;
                     }
                 }
                 __syncthreads();
