@@ -118,7 +118,7 @@ __global__ void __launch_bounds__(K1_NT, K1_MIN_CTAS) k1_decode(const __grid_con
 
     const uint32_t n_leaves = (uint32_t)S->n_leaves;
     const uint32_t all_valid = (n_leaves >= 32) ? 0xFFFFFFFFu : ((1u << n_leaves) - 1u);
-    unsigned long long c_rows = 0, c_null = 0, c_fast = 0; uint32_t c_err = 0;
+    uint32_t c_rows = 0, c_null = 0, c_fast = 0, c_err = 0;    // per thread (a thread sees far fewer than 2^32 records); widened when added to the statistics
     uint32_t phase_bits = 0;     // bit k: parity the next completion of stage k will have
 
     // Stages one tile: bulk (TMA) copy of the 16-byte-aligned part onto the stage's mbarrier, the ragged
@@ -294,9 +294,9 @@ __global__ void __launch_bounds__(K1_NT, K1_MIN_CTAS) k1_decode(const __grid_con
                 }
                 __syncthreads();
                 const long long row_base = s_rowbase;
-                long long cnt = n_rec - round0; if (cnt > K1_SC) cnt = K1_SC;
-                for (long long base = 0; base < cnt; base += K1_NT) {
-                    const long long idx = base + tid;
+                const int cnt = (int)((n_rec - round0 > K1_SC) ? K1_SC : (n_rec - round0));
+                for (int base = 0; base < cnt; base += K1_NT) {
+                    const int idx = base + tid;
                     const bool has = idx < cnt;
                     uint32_t st = 0, en = 0; bool in_smem = true; long long en_abs = 0;
                     const long long rank = round0 + idx;
@@ -424,9 +424,9 @@ __global__ void __launch_bounds__(K1_NT, K1_MIN_CTAS) k1_decode(const __grid_con
         c_err |= __shfl_xor_sync(0xffffffffu, c_err, s);
     }
     if (lane == 0) {
-        if (c_rows) atomicAdd(&a.stats->rows, c_rows);
-        if (c_null) atomicAdd(&a.stats->null_rows, c_null);
-        if (c_fast) atomicAdd(&a.stats->fast_rows, c_fast);
+        if (c_rows) atomicAdd(&a.stats->rows, (unsigned long long)c_rows);
+        if (c_null) atomicAdd(&a.stats->null_rows, (unsigned long long)c_null);
+        if (c_fast) atomicAdd(&a.stats->fast_rows, (unsigned long long)c_fast);
         if (c_err) atomicOr(&a.stats->flags, (unsigned long long)c_err);
     }
 }
