@@ -32,7 +32,7 @@
 #define K1_STAGES 1         // shared-memory tile stages; 2 = prefetch the next tile while parsing (measured slower: 3 CTAs/SM already overlap copy and parse)
 #endif
 #ifndef K1_MIN_CTAS
-#define K1_MIN_CTAS 3       // resident CTAs per SM the register allocation is held to
+#define K1_MIN_CTAS 4       // resident CTAs per SM the register allocation is held to (64 registers; measured 3 / 4 / 5: 3.27 / 3.03 / 3.03 ms per 25 M events)
 #endif
 
 // ------------------------------- PTX wrappers ------------------------------------------
@@ -169,16 +169,20 @@ __global__ void __launch_bounds__(K1_NT, K1_MIN_CTAS) k1_decode(const __grid_con
         __syncthreads();
 
         long long n_rec = 0; long long rec0 = 0;   // offsets mode: records [rec0, rec0+n_rec)
-        uint32_t my_masks[(K1_T / 128 / 32 + 1) / 2]; uint32_t my_base = 0; // NDJSON mode
         const bool first_virtual = (tile == 0 && (long long)a.skew < a.n_end);
         if (a.offsets == nullptr) {
             // --- structural scan: newline q in [lo, hi) owns the record starting at q+1 ---
             // warp w scans chunks [w*CPW, (w+1)*CPW), lane-strided so shared loads are conflict-free
             constexpr int CPW = (K1_T / 16) / (K1_NT / 32);   // 256
             constexpr int ROUNDS = CPW / 32;                  // 8
+            const bool edge_tile = lo < (long long)a.skew || lo + (long long)K1_T + 16 >= a.n_end;
+            // A tile with more than K1_SC records (records shorter than ~40 bytes) is parsed in rounds of K1_SC; every round
+            // repeats the scan instead of keeping its masks and ranks, so those registers are free while records are parsed.
+            for (uint32_t round0 = 0; ; round0 += K1_SC) {
+            if (round0 > 0) __syncthreads();      // the previous round's readers of s_starts / s_wtot are done
             uint32_t cnt_total = 0;
             uint32_t excl_in_warp[ROUNDS];
-            const bool edge_tile = lo < (long long)a.skew || lo + (long long)K1_T + 16 >= a.n_end;
+            uint32_t my_masks[(ROUNDS + 1) / 2];
 #pragma unroll
             for (int r = 0; r < ROUNDS; r++) {
                 const int chunk = warp * CPW + r * 32 + lane;
@@ -230,7 +234,7 @@ __global__ void __launch_bounds__(K1_NT, K1_MIN_CTAS) k1_decode(const __grid_con
                 }
             }
             if (lane == 0) s_wtot[warp] = cnt_total;
-            if (warp == K1_NT / 32 - 1) {
+            if (warp == K1_NT / 32 - 1 && round0 == 0) {
                 // the tile's last record ends at the first newline at or past the tile end: find it with the
                 // whole warp (16 bytes per lane per round) instead of one lane walking bytes
                 const uint32_t lim = (uint32_t)avail + ((lo + avail == a.n_end) ? 1u : 0u);
@@ -264,12 +268,7 @@ __global__ void __launch_bounds__(K1_NT, K1_MIN_CTAS) k1_decode(const __grid_con
 #pragma unroll
             for (int w = 0; w < K1_NT / 32; w++) { uint32_t t = s_wtot[w]; if (w < warp) wbase += t; total += t; }
             n_rec = total;
-            // fold warp base into per-round exclusive ranks; keep only round-0 rank + masks (ranks are
-            // recomputed from popcounts when emitting)
-            my_base = wbase;
-            // stash per-round exclusive offsets compactly: emit loop recomputes them in the same order
-            // (excl_in_warp[r] are kept in registers; ROUNDS is small)
-            if (warp == 0) {
+            if (warp == 0 && round0 == 0) {
 #ifdef K1_NO_LOOKBACK    /* tuning experiment only: what the row-index look-back costs (row numbers are wrong in this build) */
                 long long rb = tile * 200;
 #else
@@ -277,14 +276,12 @@ __global__ void __launch_bounds__(K1_NT, K1_MIN_CTAS) k1_decode(const __grid_con
 #endif
                 if (lane == 0) s_rowbase = rb;
             }
-            // emit + parse in rounds of K1_SC records
-            for (long long round0 = 0; round0 < n_rec || round0 == 0; round0 += K1_SC) {
-                if (round0 > 0) __syncthreads();      // later rounds reuse s_starts; the first is already fenced by the two barriers above
+            {
                 if (first_virtual && tid == 0 && round0 == 0) s_starts[0] = (uint16_t)a.skew;
 #pragma unroll
                 for (int r = 0; r < ROUNDS; r++) {
                     uint32_t m = (r & 1) ? (my_masks[r >> 1] >> 16) : (my_masks[r >> 1] & 0xffffu);
-                    uint32_t rel = my_base + excl_in_warp[r] - (uint32_t)round0;     // wraps to a huge value for earlier rounds' records
+                    uint32_t rel = wbase + excl_in_warp[r] - round0;     // wraps to a huge value for earlier rounds' records
                     const uint32_t pos0 = (uint32_t)(warp * CPW + r * 32 + lane) * 16 + 1;
                     while (m) {
                         const int i = __ffs(m) - 1; m &= m - 1;
@@ -345,7 +342,8 @@ __global__ void __launch_bounds__(K1_NT, K1_MIN_CTAS) k1_decode(const __grid_con
                         else reinterpret_cast<uint32_t*>(a.mask)[o.row] = o.valid | (ok ? 0x80000000u : 0u);
                     }
                 }
-                if (n_rec == 0) break;
+                if ((long long)round0 + K1_SC >= n_rec) break;
+            }
             }
         } else {
             // --- caller-provided framing: records whose first byte lies in [lo, hi) ---
