@@ -71,12 +71,13 @@ static __device__ __forceinline__ bool fast_record_warp(const uint8_t* buf, uint
     for (int si = 0; si < n_segs; si++) {
         __syncwarp();
         const DSeg sg = a.segs[si];                      // warp-uniform: constant-bank loads
-        if (ok) {
+        {
             // literal: whole words through a carried funnel shift (data word i+1 is loaded once and reused as the low half of
-            // the next compare); every load sits at a compile-time offset from the block base, so no pointer is advanced per word
-            // (indices, not pointers: the literal words stay constant-bank loads c[0][reg + imm])
-            uint32_t li = sg.lit_off >> 2, wo = pos & ~3u, nw = sg.lit_len >> 2;
-            const uint32_t L = sg.lit_len, sh = (pos & 3u) << 3;
+            // the next compare).  Every lane runs the compare, lanes that already failed on the tile's first bytes: the loop
+            // is then warp-uniform and the literal words are uniform constant-bank operands instead of per-lane indexed loads.
+            const uint32_t p0 = ok ? pos : 0u;
+            int li = (int)(sg.lit_off >> 2); uint32_t wo = p0 & ~3u, nw = sg.lit_len >> 2;
+            const uint32_t L = sg.lit_len, sh = (p0 & 3u) << 3;
             uint32_t lo = *reinterpret_cast<const uint32_t*>(buf + wo), diff = 0, hi;
 #define DX_LIT_WORD(i) hi = *reinterpret_cast<const uint32_t*>(buf + wo + 4 * ((i) + 1)); diff |= __funnelshift_r(lo, hi, sh) ^ a.lits[li + (i)]; lo = hi;
             while (nw >= 4) { DX_LIT_WORD(0) DX_LIT_WORD(1) DX_LIT_WORD(2) DX_LIT_WORD(3) wo += 16; li += 4; nw -= 4; }
@@ -84,7 +85,7 @@ static __device__ __forceinline__ bool fast_record_warp(const uint8_t* buf, uint
             if (nw) { DX_LIT_WORD(0) wo += 4; li += 1; }
 #undef DX_LIT_WORD
             if (sg.tail_mask) { hi = *reinterpret_cast<const uint32_t*>(buf + wo + 4); diff |= (__funnelshift_r(lo, hi, sh) ^ a.lits[li]) & sg.tail_mask; }
-            ok = diff == 0;
+            ok = ok && diff == 0;
             pos += L;
         }
         if (sg.type == 0) break;
