@@ -18,29 +18,30 @@ static __device__ __forceinline__ uint64_t ld64u(const uint8_t* buf, uint32_t po
 // number of leading ASCII digits among the 4 bytes of w (byte 0 first)
 static __device__ __forceinline__ int leading_digits4(uint32_t w) {
     const uint32_t nd = ((w + 0x46464646u) | (w - 0x30303030u)) & 0x80808080u;   // exact up to and including the first non-digit
-    return nd ? ((__ffs((int)nd) - 1) >> 3) : 4;
+    return __clz((int)__brev(nd)) >> 3;                    // trailing zeros / 8; no flag at all -> 32 / 8 = 4
 }
 
 // value of the first m (1..4) digits of the 32-bit window x
 static __device__ __forceinline__ uint32_t digits4(uint32_t x, int m) {
-    uint32_t t = (x - 0x30303030u) & (0xFFFFFFFFu >> ((4 - m) << 3));
-    t <<= (4 - m) << 3;                                    // right-align: missing leading digits are zero
+    // right-align: the shift drops the bytes past the m-th, missing leading digits become zero (a borrow of the subtraction can
+    // only start in a non-digit byte, i.e. above the digits, so the digit bytes are exact)
+    const uint32_t t = (x - 0x30303030u) << ((4 - m) << 3);
     const uint32_t p = (t * 10u + (t >> 8)) & 0x00FF00FFu; // [d0 d1] in byte 0, [d2 d3] in byte 2
-    return (p & 0xFFu) * 100u + (p >> 16);
+    return (p * 0x00640001u) >> 16;                        // (d0 d1) * 100 + (d2 d3)
 }
 
 static __constant__ uint32_t dx_pow10_u32[9] = {1u, 10u, 100u, 1000u, 10000u, 100000u, 1000000u, 10000000u, 100000000u};
 
 // Parses a run of digits at pos, four bytes per step through a carried pair of aligned words.
-// Returns the digit count (0 = none, -1 = more than 18) and the value.
-static __device__ __forceinline__ int parse_digit_run(const uint8_t* buf, uint32_t pos, unsigned long long* value, uint32_t* first_digit) {
+// Returns the digit count (0 = none, -1 = more than 18), the value, the first digit and the byte that ends the run.
+static __device__ __forceinline__ int parse_digit_run(const uint8_t* buf, uint32_t pos, unsigned long long* value, uint32_t* first_digit, uint32_t* term) {
     const uint32_t* wp = reinterpret_cast<const uint32_t*>(buf + (pos & ~3u));
     const uint32_t sh = (pos & 3u) << 3;
     uint32_t a = wp[0], b = wp[1];
     uint32_t w = __funnelshift_r(a, b, sh);
     *first_digit = (w & 0xffu) - '0';
     int n = leading_digits4(w);
-    if (n == 0) { *value = 0; return 0; }
+    if (n == 0) { *value = 0; *term = w & 0xffu; return 0; }
     uint32_t v32 = digits4(w, n); int nd = n;
     // up to 8 digits stay in 32-bit arithmetic
     if (n == 4) {
@@ -60,6 +61,7 @@ static __device__ __forceinline__ int parse_digit_run(const uint8_t* buf, uint32
         }
     }
     *value = v;
+    *term = (w >> (n << 3)) & 0xffu;          // n < 4 here: the run ended inside the last window
     return nd > 18 ? -1 : nd;
 }
 
@@ -94,8 +96,8 @@ static __device__ __forceinline__ bool fast_record_warp(const uint8_t* buf, uint
             case DX_T_I64: {
                 bool neg = buf[pos] == '-';
                 if (neg) pos++;
-                unsigned long long v; uint32_t d0;
-                const int nd = parse_digit_run(buf, pos, &v, &d0);
+                unsigned long long v; uint32_t d0, tm;
+                const int nd = parse_digit_run(buf, pos, &v, &d0, &tm);
                 if (nd <= 0 || (d0 == 0 && nd > 1)) { ok = false; break; }
                 sink_i64(o, sg.leaf, neg ? -(long long)v : (long long)v);
                 pos += nd;
@@ -104,18 +106,17 @@ static __device__ __forceinline__ bool fast_record_warp(const uint8_t* buf, uint
             case DX_T_F64: {
                 bool neg = buf[pos] == '-';
                 if (neg) pos++;
-                unsigned long long ip, fp = 0; uint32_t d0, f0;
-                const int ni = parse_digit_run(buf, pos, &ip, &d0);
+                unsigned long long ip, fp = 0; uint32_t d0, f0, tm;
+                const int ni = parse_digit_run(buf, pos, &ip, &d0, &tm);
                 if (ni <= 0 || (d0 == 0 && ni > 1)) { ok = false; break; }
                 pos += ni;
                 int nf = 0;
-                if (buf[pos] == '.') {
-                    nf = parse_digit_run(buf, pos + 1, &fp, &f0);
+                if (tm == '.') {
+                    nf = parse_digit_run(buf, pos + 1, &fp, &f0, &tm);
                     if (nf <= 0) { ok = false; break; }
                     pos += 1 + nf;
                 }
-                const uint32_t c = buf[pos];
-                if (ni + nf > 15 || c == 'e' || c == 'E') { ok = false; break; }
+                if (ni + nf > 15 || tm == 'e' || tm == 'E') { ok = false; break; }
                 double x;
                 if (nf == 0) x = (double)(neg ? -(long long)ip : (long long)ip);
                 else {
