@@ -69,6 +69,7 @@ struct RulesDev {
     int32_t total_rows, J, Wp, words;
     int32_t table_in_smem;
     const void* shared_vmask; int32_t shared_vwidth;   // validity mask array shared by most spaces (loaded once per row)
+    int32_t staged, stage_off, stage_buf_bytes;         // column tiles staged in shared memory by bulk copies (see K2_TILE)
     // generic leaves
     const uint32_t* code; const long long* gconsts; const ProgCol* gcols; const ProgLut* gluts; int32_t n_gcols;
 };
@@ -86,7 +87,35 @@ static __device__ __forceinline__ int bucket_f64(const long long* c, int m, int 
     return 2 * lo + ((lo < m && __longlong_as_double(c[lo]) == v) ? 1 : 0);
 }
 
-template <int J, bool NEEDF, int NSMAX>
+// a leaf the bucket planner does not take (arbitrary expression): the bytecode interpreter, kept out of line
+static __device__ __noinline__ int generic_bucket(const EvalView& gv, uint32_t prog_start, long long row) {
+    long long val; bool isnull;
+    eval_program(gv, prog_start, row, val, isnull);
+    return isnull ? 2 : (val != 0 ? 1 : 0);
+}
+
+// ---- bulk-copy staging of the column tiles (STAGED kernels) ----
+#define K2_TILE 256                  // rows per tile = threads per CTA
+#define K2_SLOT 2048                 // bytes per staged column slot (256 rows x 8 bytes)
+static __device__ __forceinline__ uint32_t k2_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+static __device__ __forceinline__ void k2_mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(k2_smem_u32(bar)), "r"(count) : "memory");
+}
+static __device__ __forceinline__ void k2_mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(k2_smem_u32(bar)), "r"(bytes) : "memory");
+}
+static __device__ __forceinline__ void k2_bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(k2_smem_u32(dst)), "l"(src), "r"(bytes), "r"(k2_smem_u32(bar)) : "memory");
+}
+static __device__ __forceinline__ bool k2_mbar_try_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(ok) : "r"(k2_smem_u32(bar)), "r"(parity) : "memory");
+    return ok != 0;
+}
+
+template <int J, bool NEEDF, int NSMAX, bool STAGED>
 __global__ void __launch_bounds__(256, K2_MIN_CTAS) k2_rules_bucket(const __grid_constant__ RulesDev D, long long n_rows, const long long* sel, uint32_t* flags) {
     extern __shared__ __align__(16) uint8_t rsm[];
     // shared layout: spaces | classes | class masks | consts | luts | [table_t | table_f]
@@ -118,76 +147,130 @@ __global__ void __launch_bounds__(256, K2_MIN_CTAS) k2_rules_bucket(const __grid
     EvalView gv{D.code, D.gconsts, D.gcols, D.gluts};
     const int n_wg = D.Wp / RB_WG;
     const int ns = D.n_spaces;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_rows; i += (long long)gridDim.x * blockDim.x) {
-        const long long row = sel ? sel[i] : i;
-        // phase A: every column value this rule set looks at, issued back to back (memory-level parallelism)
-        long long vv[NSMAX];
-        uint32_t shared_mask = 0xFFFFFFFFu;
-        if (D.shared_vmask) shared_mask = D.shared_vwidth == 1 ? reinterpret_cast<const uint8_t*>(D.shared_vmask)[row] : reinterpret_cast<const uint32_t*>(D.shared_vmask)[row];
-#pragma unroll
-        for (int s = 0; s < NSMAX; s++) {
-            if (s >= ns) break;
-            const RSpaceDev& sp = s_spaces[s];
-            long long v = 0;
-            if (sp.domain == DOM_CODE) v = reinterpret_cast<const int32_t*>(sp.col.data)[row];
-            else if (sp.domain != DOM_GENERIC) v = reinterpret_cast<const long long*>(sp.col.data)[row];
-            vv[s] = v;
+    // STAGED: the CTA walks tiles of K2_TILE rows; one thread moves every column slice of the next tile (and the shared
+    // validity bytes) into shared memory with bulk copies while the current tile is evaluated, so the column reads of
+    // phase A are shared-memory loads instead of global loads each warp waits ~1 us for.  Full tiles only: the last,
+    // ragged tile (bulk sizes must be multiples of 16 bytes) reads global memory directly.
+    __shared__ uint64_t s_bar[2];
+    uint8_t* s_stage = rsm + D.stage_off;
+    const long long n_tiles = (n_rows + K2_TILE - 1) / K2_TILE;
+    auto issue_tile = [&](long long t, int buf) {          // thread 0
+        const long long row0 = t * K2_TILE;
+        if (row0 + K2_TILE > n_rows) return;               // ragged tile: not staged
+        uint8_t* dst = s_stage + (size_t)buf * D.stage_buf_bytes;
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        uint32_t total = D.shared_vmask ? (uint32_t)(K2_TILE * D.shared_vwidth) : 0u;
+        for (int s = 0; s < D.n_spaces; s++) total += (uint32_t)(K2_TILE * s_spaces[s].col.width);
+        k2_mbar_expect_tx(&s_bar[buf], total);
+        for (int s = 0; s < D.n_spaces; s++) {
+            const int w = s_spaces[s].col.width;
+            k2_bulk_g2s(dst + s * K2_SLOT, reinterpret_cast<const uint8_t*>(s_spaces[s].col.data) + row0 * w, (uint32_t)(K2_TILE * w), &s_bar[buf]);
         }
-        // phase B: one bucket per space
-        int brow[NSMAX];
+        if (D.shared_vmask)
+            k2_bulk_g2s(dst + D.n_spaces * K2_SLOT, reinterpret_cast<const uint8_t*>(D.shared_vmask) + row0 * D.shared_vwidth,
+                        (uint32_t)(K2_TILE * D.shared_vwidth), &s_bar[buf]);
+    };
+    if (STAGED) {
+        if (threadIdx.x == 0) { k2_mbar_init(&s_bar[0], 1); k2_mbar_init(&s_bar[1], 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+        __syncthreads();
+        if (threadIdx.x == 0 && blockIdx.x < n_tiles) issue_tile(blockIdx.x, 0);
+    }
+    uint32_t it = 0;
+    for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, it++) {
+        const long long i = tile * K2_TILE + threadIdx.x;
+        const bool full = STAGED && tile * K2_TILE + K2_TILE <= n_rows;
+        const uint8_t* stg = s_stage + (size_t)(it & 1u) * D.stage_buf_bytes;
+        if (STAGED) {
+            if (threadIdx.x == 0 && tile + gridDim.x < n_tiles) issue_tile(tile + gridDim.x, (int)((it + 1) & 1u));
+            if (full) { while (!k2_mbar_try_wait(&s_bar[it & 1u], (it >> 1) & 1u)) {} }
+        }
+        if (i < n_rows) {
+        const long long row = sel ? sel[i] : i;
+        uint8_t* stw = s_stage + (size_t)(it & 1u) * D.stage_buf_bytes;
+        if (STAGED && !full) {
+            // ragged last tile: every thread puts its own row's values where the bulk copies would have (it reads only those back)
+            for (int s = 0; s < ns; s++) {
+                const RSpaceDev& sp = s_spaces[s];
+                if (sp.domain == DOM_CODE) reinterpret_cast<int32_t*>(stw + s * K2_SLOT)[threadIdx.x] = reinterpret_cast<const int32_t*>(sp.col.data)[row];
+                else reinterpret_cast<long long*>(stw + s * K2_SLOT)[threadIdx.x] = reinterpret_cast<const long long*>(sp.col.data)[row];
+            }
+            if (D.shared_vmask) {
+                if (D.shared_vwidth == 1) stw[ns * K2_SLOT + threadIdx.x] = reinterpret_cast<const uint8_t*>(D.shared_vmask)[row];
+                else reinterpret_cast<uint32_t*>(stw + ns * K2_SLOT)[threadIdx.x] = reinterpret_cast<const uint32_t*>(D.shared_vmask)[row];
+            }
+        }
+        uint32_t shared_mask = 0xFFFFFFFFu;
+        if (D.shared_vmask) {
+            if (STAGED) shared_mask = D.shared_vwidth == 1 ? stg[ns * K2_SLOT + threadIdx.x] : reinterpret_cast<const uint32_t*>(stg + ns * K2_SLOT)[threadIdx.x];
+            else shared_mask = D.shared_vwidth == 1 ? reinterpret_cast<const uint8_t*>(D.shared_vmask)[row] : reinterpret_cast<const uint32_t*>(D.shared_vmask)[row];
+        }
+        // phase A (direct kernels): every column value this rule set looks at, issued back to back (memory-level parallelism);
+        // the staged kernels read the values from the shared-memory tile where they are needed
+        long long vv[STAGED ? 1 : NSMAX];
+        if (!STAGED) {
 #pragma unroll
-        for (int s = 0; s < NSMAX; s++) {
-            if (s >= ns) break;
+            for (int s = 0; s < NSMAX; s++) {
+                if (s >= ns) break;
+                const RSpaceDev& sp = s_spaces[s];
+                long long v = 0;
+                if (sp.domain == DOM_CODE) v = reinterpret_cast<const int32_t*>(sp.col.data)[row];
+                else if (sp.domain != DOM_GENERIC) v = reinterpret_cast<const long long*>(sp.col.data)[row];
+                vv[s] = v;
+            }
+        }
+        // phase B: one bucket per space -> first table word of that bucket's row
+        auto bucket_row = [&](int s) -> int {
             const RSpaceDev& sp = s_spaces[s];
             int b;
-            if (sp.domain == DOM_GENERIC) {
-                long long val; bool isnull;
-                eval_program(gv, sp.prog_start, row, val, isnull);
-                b = isnull ? 2 : (val != 0 ? 1 : 0);
-            } else {
+            if (sp.domain == DOM_GENERIC) b = generic_bucket(gv, sp.prog_start, row);
+            else {
                 bool valid = true;
                 if (sp.col.vmask) {
                     uint32_t m = shared_mask;
-                    if (!D.shared_vmask || sp.col.vmask != D.shared_vmask)
+                    if (!STAGED && (!D.shared_vmask || sp.col.vmask != D.shared_vmask))
                         m = sp.col.vwidth == 1 ? reinterpret_cast<const uint8_t*>(sp.col.vmask)[row] : reinterpret_cast<const uint32_t*>(sp.col.vmask)[row];
                     valid = (m >> sp.col.vbit) & 1u;
                 }
-                const long long v = vv[s];
+                long long v;
+                if (!STAGED) v = vv[STAGED ? 0 : s];
+                else if (sp.domain == DOM_CODE) v = reinterpret_cast<const int32_t*>(stg + s * K2_SLOT)[threadIdx.x];
+                else v = reinterpret_cast<const long long*>(stg + s * K2_SLOT)[threadIdx.x];
                 if (!valid) b = sp.null_bucket;
                 else if (sp.domain == DOM_CODE) b = (v >= 0 && v < sp.lut_size) ? s_luts[sp.lut_off + (int)v] : sp.other_bucket;
                 else if (sp.domain == DOM_I64) b = bucket_i64(s_consts + sp.const_off, sp.n_consts, sp.pad, v);
                 else if (sp.domain == DOM_F64) b = bucket_f64(s_consts + sp.const_off, sp.n_consts, sp.pad, __longlong_as_double(v));
                 else b = bucket_f64(s_consts + sp.const_off, sp.n_consts, sp.pad, (double)v);
             }
-            brow[s] = (sp.row_base + b) * row_words;
-        }
-        for (int wg = 0; wg < n_wg; wg++) {
-            uint32_t T[J][RB_WG], F[NEEDF ? J : 1][RB_WG];
+            return (sp.row_base + b) * row_words;
+        };
+        uint32_t T[J][RB_WG], F[NEEDF ? J : 1][RB_WG];
+        // phase C: OR the bucket's truth-table row into the slots the space feeds
+        auto or_rows = [&](int s, int base) {
+            const uint32_t sm = s_spaces[s].slot_mask;
+#pragma unroll
+            for (int j = 0; j < J; j++) {
+                if ((sm >> j) & 1u) {
+                    const uint4 a = *reinterpret_cast<const uint4*>(tab_t + base + j * D.Wp);
+                    const uint4 b4 = *reinterpret_cast<const uint4*>(tab_t + base + j * D.Wp + 4);
+                    T[j][0] |= a.x; T[j][1] |= a.y; T[j][2] |= a.z; T[j][3] |= a.w;
+                    T[j][4] |= b4.x; T[j][5] |= b4.y; T[j][6] |= b4.z; T[j][7] |= b4.w;
+                    if (NEEDF) {
+                        const uint4 c = *reinterpret_cast<const uint4*>(tab_f + base + j * D.Wp);
+                        const uint4 d = *reinterpret_cast<const uint4*>(tab_f + base + j * D.Wp + 4);
+                        F[j][0] |= c.x; F[j][1] |= c.y; F[j][2] |= c.z; F[j][3] |= c.w;
+                        F[j][4] |= d.x; F[j][5] |= d.y; F[j][6] |= d.z; F[j][7] |= d.w;
+                    }
+                }
+            }
+        };
+        auto clear_slots = [&]() {
 #pragma unroll
             for (int j = 0; j < J; j++)
 #pragma unroll
                 for (int w = 0; w < RB_WG; w++) { T[j][w] = 0; if (NEEDF) F[j][w] = 0; }
-#pragma unroll
-            for (int s = 0; s < NSMAX; s++) {
-                if (s >= ns) break;
-                const uint32_t sm = s_spaces[s].slot_mask;
-                const int base = brow[s] + wg * RB_WG;
-#pragma unroll
-                for (int j = 0; j < J; j++) {
-                    if ((sm >> j) & 1u) {
-                        const uint4 a = *reinterpret_cast<const uint4*>(tab_t + base + j * D.Wp);
-                        const uint4 b4 = *reinterpret_cast<const uint4*>(tab_t + base + j * D.Wp + 4);
-                        T[j][0] |= a.x; T[j][1] |= a.y; T[j][2] |= a.z; T[j][3] |= a.w;
-                        T[j][4] |= b4.x; T[j][5] |= b4.y; T[j][6] |= b4.z; T[j][7] |= b4.w;
-                        if (NEEDF) {
-                            const uint4 c = *reinterpret_cast<const uint4*>(tab_f + base + j * D.Wp);
-                            const uint4 d = *reinterpret_cast<const uint4*>(tab_f + base + j * D.Wp + 4);
-                            F[j][0] |= c.x; F[j][1] |= c.y; F[j][2] |= c.z; F[j][3] |= c.w;
-                            F[j][4] |= d.x; F[j][5] |= d.y; F[j][6] |= d.z; F[j][7] |= d.w;
-                        }
-                    }
-                }
-            }
+        };
+        // phase D: class combination and the flag words of word group wg
+        auto combine_store = [&](int wg) {
             uint32_t out[RB_WG];
 #pragma unroll
             for (int w = 0; w < RB_WG; w++) out[w] = 0;
@@ -252,7 +335,35 @@ __global__ void __launch_bounds__(256, K2_MIN_CTAS) k2_rules_bucket(const __grid
                 const int gw = wg * RB_WG + w;
                 if (gw < D.words) flags[(long long)gw * n_rows + i] = out[w];
             }
+        };
+        if (n_wg == 1) {
+            // up to 256 rules: bucket search and row OR per space back to back, nothing kept per space
+            clear_slots();
+#pragma unroll
+            for (int s = 0; s < NSMAX; s++) {
+                if (s >= ns) break;
+                or_rows(s, bucket_row(s));
+            }
+            combine_store(0);
+        } else {
+            int brow[NSMAX];
+#pragma unroll
+            for (int s = 0; s < NSMAX; s++) {
+                if (s >= ns) break;
+                brow[s] = bucket_row(s);
+            }
+            for (int wg = 0; wg < n_wg; wg++) {
+                clear_slots();
+#pragma unroll
+                for (int s = 0; s < NSMAX; s++) {
+                    if (s >= ns) break;
+                    or_rows(s, brow[s] + wg * RB_WG);
+                }
+                combine_store(wg);
+            }
         }
+        }
+        if (STAGED) __syncthreads();        // the next iteration refills this tile's buffer: every reader must be done
     }
 }
 
@@ -487,15 +598,15 @@ static bool like_match2(const std::string& s, const std::string& p) {
 
 } // namespace
 
-template <int J, bool NEEDF, int NSMAX>
+template <int J, bool NEEDF, int NSMAX, bool STAGED>
 static void launch_rules(dx_ctx* ctx, const RulesDev& D, size_t smem, int64_t n_rows, const int64_t* sel, uint32_t* flags) {
-    cudaFuncSetAttribute(k2_rules_bucket<J, NEEDF, NSMAX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaFuncSetAttribute(k2_rules_bucket<J, NEEDF, NSMAX, STAGED>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     int occ = 1;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k2_rules_bucket<J, NEEDF, NSMAX>, 256, smem);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k2_rules_bucket<J, NEEDF, NSMAX, STAGED>, 256, smem);
     if (occ < 1) occ = 1;
     long long blocks = (n_rows + 255) / 256, cap = (long long)ctx->sm_count * occ;
     if (blocks > cap) blocks = cap;
-    k2_rules_bucket<J, NEEDF, NSMAX><<<(unsigned)blocks, 256, smem, ctx->stream>>>(D, n_rows, reinterpret_cast<const long long*>(sel), flags);
+    k2_rules_bucket<J, NEEDF, NSMAX, STAGED><<<(unsigned)blocks, 256, smem, ctx->stream>>>(D, n_rows, reinterpret_cast<const long long*>(sel), flags);
 }
 
 // A planned rule set kept across micro-batches: everything but the column pointers is a function of the statement text,
@@ -514,9 +625,32 @@ static void rules_shared_vmask(RulesDev& D, const std::vector<RSpaceDev>& sdev) 
     D.shared_vmask = bc >= 2 ? best : nullptr; D.shared_vwidth = bw;
 }
 
-static void rules_launch(dx_ctx* ctx, const RulesDev& D, int J, bool needf, size_t smem, int64_t n_rows, const int64_t* sel, uint32_t* flags) {
+// Whether the column tiles can be staged by bulk copies: rows taken in order, at most 8 plain column spaces, every column
+// (and the one validity array they share) 16-byte aligned, no space with a validity array of its own.
+static bool rules_can_stage(const RulesDev& D, const std::vector<RSpaceDev>& sdev, int64_t n_rows, const int64_t* sel) {
+    if (sel || n_rows < K2_TILE || sdev.size() > 8 || getenv("DX_K2_NO_STAGING")) return false;
+    for (auto& d : sdev) {
+        if (d.domain == DOM_GENERIC || !d.col.data || (reinterpret_cast<uintptr_t>(d.col.data) & 15)) return false;
+        if (d.col.width != (d.domain == DOM_CODE ? 4 : 8)) return false;
+        if (d.col.vmask && d.col.vmask != D.shared_vmask) return false;
+    }
+    if (D.shared_vmask && ((reinterpret_cast<uintptr_t>(D.shared_vmask) & 15) || (D.shared_vwidth != 1 && D.shared_vwidth != 4))) return false;
+    return true;
+}
+
+static void rules_launch(dx_ctx* ctx, const RulesDev& D0, const std::vector<RSpaceDev>& sdev, int J, bool needf, size_t smem, int64_t n_rows, const int64_t* sel, uint32_t* flags) {
     StageTimer tm(ctx, "k2_rules_bucket");
-#define RB_LAUNCH_NS(JJ, FF) do { if (D.n_spaces <= 8) launch_rules<JJ, FF, 8>(ctx, D, smem, n_rows, sel, flags); else launch_rules<JJ, FF, RB_MAX_SPACES>(ctx, D, smem, n_rows, sel, flags); } while (0)
+    RulesDev D = D0;
+    const bool staged = rules_can_stage(D, sdev, n_rows, sel);
+    D.staged = staged ? 1 : 0; D.stage_off = 0; D.stage_buf_bytes = 0;
+    if (staged) {
+        D.stage_off = (int32_t)((smem + 127) & ~size_t(127));
+        D.stage_buf_bytes = (int32_t)(sdev.size() * K2_SLOT + 1024);
+        smem = (size_t)D.stage_off + 2 * (size_t)D.stage_buf_bytes;
+    }
+#define RB_LAUNCH_NS(JJ, FF) do { if (staged) launch_rules<JJ, FF, 8, true>(ctx, D, smem, n_rows, sel, flags); \
+        else if (D.n_spaces <= 8) launch_rules<JJ, FF, 8, false>(ctx, D, smem, n_rows, sel, flags); \
+        else launch_rules<JJ, FF, RB_MAX_SPACES, false>(ctx, D, smem, n_rows, sel, flags); } while (0)
 #define RB_LAUNCH(JJ) do { if (needf) RB_LAUNCH_NS(JJ, true); else RB_LAUNCH_NS(JJ, false); } while (0)
     if (J == 1) RB_LAUNCH(1); else if (J == 2) RB_LAUNCH(2); else if (J == 3) RB_LAUNCH(3); else RB_LAUNCH(4);
 #undef RB_LAUNCH
@@ -542,7 +676,7 @@ int dx_rules_eval(dx_ctx* ctx, const BindScope& sc, const std::vector<ExprP>& co
         if (ok) {
             DX_CUDA(ctx, cudaMemcpyAsync(pc->b_spaces.p, pc->sdev.data(), pc->sdev.size() * sizeof(RSpaceDev), cudaMemcpyHostToDevice, ctx->stream));
             rules_shared_vmask(pc->D, pc->sdev);
-            rules_launch(ctx, pc->D, pc->J, pc->needf, pc->smem, n_rows, sel, flags);
+            rules_launch(ctx, pc->D, pc->sdev, pc->J, pc->needf, pc->smem, n_rows, sel, flags);
             DX_CUDA(ctx, cudaGetLastError());
             *used_fast = true;
             return DX_OK;
@@ -726,7 +860,7 @@ int dx_rules_eval(dx_ctx* ctx, const BindScope& sc, const std::vector<ExprP>& co
     D.table_in_smem = (fixed + tab_bytes <= RB_SMEM_TABLE_BYTES) ? 1 : 0;
     size_t smem = fixed + (D.table_in_smem ? tab_bytes : 0);
     if (fixed > 64 * 1024) return DX_OK;       // pathological constant count: generic kernel
-    rules_launch(ctx, D, J, needf, smem, n_rows, sel, flags);
+    rules_launch(ctx, D, sdev, J, needf, smem, n_rows, sel, flags);
     DX_CUDA(ctx, cudaGetLastError());
     bool cacheable = cache != nullptr && P.G.prog_start.empty();
     for (auto& sp : P.spaces) if (sp.per_code) cacheable = false;       // per-code LIKE tables follow the dictionary
