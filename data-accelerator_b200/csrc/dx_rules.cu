@@ -97,6 +97,9 @@ static __device__ __noinline__ int generic_bucket(const EvalView& gv, uint32_t p
 // ---- bulk-copy staging of the column tiles (STAGED kernels) ----
 #define K2_TILE 256                  // rows per tile = threads per CTA
 #define K2_SLOT 2048                 // bytes per staged column slot (256 rows x 8 bytes)
+#ifndef K2_NBUF
+#define K2_NBUF 1                    // staged tiles per CTA: with one, the resident CTAs of an SM cover each other's copies
+#endif
 static __device__ __forceinline__ uint32_t k2_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 static __device__ __forceinline__ void k2_mbar_init(uint64_t* bar, uint32_t count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(k2_smem_u32(bar)), "r"(count) : "memory");
@@ -179,14 +182,15 @@ __global__ void __launch_bounds__(256, K2_MIN_CTAS) k2_rules_bucket(const __grid
     for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, it++) {
         const long long i = tile * K2_TILE + threadIdx.x;
         const bool full = STAGED && tile * K2_TILE + K2_TILE <= n_rows;
-        const uint8_t* stg = s_stage + (size_t)(it & 1u) * D.stage_buf_bytes;
+        const uint32_t sbuf = it % K2_NBUF;
+        const uint8_t* stg = s_stage + (size_t)sbuf * D.stage_buf_bytes;
         if (STAGED) {
-            if (threadIdx.x == 0 && tile + gridDim.x < n_tiles) issue_tile(tile + gridDim.x, (int)((it + 1) & 1u));
-            if (full) { while (!k2_mbar_try_wait(&s_bar[it & 1u], (it >> 1) & 1u)) {} }
+            if (K2_NBUF == 2 && threadIdx.x == 0 && tile + gridDim.x < n_tiles) issue_tile(tile + gridDim.x, (int)((it + 1) & 1u));
+            if (full) { while (!k2_mbar_try_wait(&s_bar[sbuf], (it / K2_NBUF) & 1u)) {} }
         }
         if (i < n_rows) {
         const long long row = sel ? sel[i] : i;
-        uint8_t* stw = s_stage + (size_t)(it & 1u) * D.stage_buf_bytes;
+        uint8_t* stw = s_stage + (size_t)sbuf * D.stage_buf_bytes;
         if (STAGED && !full) {
             // ragged last tile: every thread puts its own row's values where the bulk copies would have (it reads only those back)
             for (int s = 0; s < ns; s++) {
@@ -363,7 +367,10 @@ __global__ void __launch_bounds__(256, K2_MIN_CTAS) k2_rules_bucket(const __grid
             }
         }
         }
-        if (STAGED) __syncthreads();        // the next iteration refills this tile's buffer: every reader must be done
+        if (STAGED) {
+            __syncthreads();        // the tile's buffer is about to be refilled: every reader must be done
+            if (K2_NBUF == 1 && threadIdx.x == 0 && tile + gridDim.x < n_tiles) issue_tile(tile + gridDim.x, 0);
+        }
     }
 }
 
@@ -646,7 +653,7 @@ static void rules_launch(dx_ctx* ctx, const RulesDev& D0, const std::vector<RSpa
     if (staged) {
         D.stage_off = (int32_t)((smem + 127) & ~size_t(127));
         D.stage_buf_bytes = (int32_t)(sdev.size() * K2_SLOT + 1024);
-        smem = (size_t)D.stage_off + 2 * (size_t)D.stage_buf_bytes;
+        smem = (size_t)D.stage_off + K2_NBUF * (size_t)D.stage_buf_bytes;
     }
 #define RB_LAUNCH_NS(JJ, FF) do { if (staged) launch_rules<JJ, FF, 8, true>(ctx, D, smem, n_rows, sel, flags); \
         else if (D.n_spaces <= 8) launch_rules<JJ, FF, 8, false>(ctx, D, smem, n_rows, sel, flags); \
