@@ -97,6 +97,18 @@ __device__ long long tile_lookback(unsigned long long* state, long long tile, un
     return excl;
 }
 
+// Only the first and the last tile of a batch can hold newline candidates outside the data; kept out of line so the nine
+// unrolled scan rounds stay compact in the instruction cache.
+__device__ __noinline__ uint32_t k1_edge_mask(uint32_t m, long long q0, long long n_end, long long skew) {
+    if (q0 + 16 >= n_end) {
+        for (int i = 0; i < 16; i++) if (q0 + i + 1 >= n_end) m &= ~(1u << i);
+    }
+    if (q0 < skew) {
+        for (int i = 0; i < 16; i++) if (q0 + i < skew) m &= ~(1u << i);
+    }
+    return m;
+}
+
 // The tile size is a template parameter chosen per launch from the batch's mean record length, so that a tile holds just
 // under K1_NT records and the one-lane-per-record parse keeps (nearly) every lane of every warp busy.
 template <int K1_T>
@@ -197,15 +209,7 @@ __global__ void __launch_bounds__(K1_NT, K1_MIN_CTAS) k1_decode(const __grid_con
                     m |= ((t * 0x00204081u) >> 28) << (k * 4);              // gather the four flags
                 }
                 // validity of each candidate q = lo + chunk*16 + i : start q+1 must be data (< n_end), q >= skew
-                if (edge_tile) {        // only the first and the last tile of a batch can hold candidates outside the data
-                    const long long q0 = lo + (long long)chunk * 16;
-                    if (q0 + 16 >= a.n_end) {
-                        for (int i = 0; i < 16; i++) if (q0 + i + 1 >= a.n_end) m &= ~(1u << i);
-                    }
-                    if (q0 < (long long)a.skew) {
-                        for (int i = 0; i < 16; i++) if (q0 + i < (long long)a.skew) m &= ~(1u << i);
-                    }
-                }
+                if (edge_tile) m = k1_edge_mask(m, lo + (long long)chunk * 16, a.n_end, (long long)a.skew);
                 if (r & 1) my_masks[r >> 1] |= m << 16; else my_masks[r >> 1] = m;
                 excl_in_warp[r] = __popc(m);          // this lane's count for now; turned into a rank below
             }
