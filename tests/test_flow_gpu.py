@@ -393,3 +393,29 @@ Named = SELECT CONCAT(deviceDetails.deviceType, '-', deviceDetails.deviceId) AS 
     check_batch(dx, g, o, data + extra, T0)
     check_batch(dx, g, o, data[:2000] + extra, T0 + I)     # second batch: lookup tables extend, dictionaries persist
     g.close()
+
+
+def test_staged_and_direct_rule_kernels_agree_on_ragged_sizes(dx, ctx):
+    """K2 stages full 256-row tiles in shared memory by bulk copies and reads the ragged last tile directly; the direct
+    kernel (DX_K2_NO_STAGING, also what row selections use) must give the same flags at every tile-boundary case."""
+    import os
+    rules = dx.flowgen.make_rules(200, seed=11, n_keys=1000, n_homes=100)
+    tr = dx.flowgen.process_rules_sql(rules)
+    conf = dx.flowgen.conf_text("k2s")
+    p = dx.CommonProcessorFactory.createProcessor(ctx, conf, SCHEMA2, ["Raw.*\n"], tr)
+    o = dxo_flow.Flow(conf, SCHEMA2, ["Raw.*\n"], tr)
+    cases = [gen(dx, n, seed=20260200 + n) for n in (1, 255, 256, 257, 511, 513, 30_011)] + [to_ndjson(all_records(3000, seed=21))]
+    for data in cases:
+        a = p.process_json(data, T0, I)
+        fa, _ = a.table("Rules").column("Rules")
+        os.environ["DX_K2_NO_STAGING"] = "1"
+        try:
+            b = p.process_json(data, T0, I)
+        finally:
+            del os.environ["DX_K2_NO_STAGING"]
+        fb, _ = b.table("Rules").column("Rules")
+        assert fa.shape == fb.shape and (fa == fb).all()
+        ro, _ = o.process(data, T0, I)
+        assert_same_rows(a.table("Rules"), ro["Rules"], dx, ordered=True)
+        a.release(); b.release()
+    p.close()
