@@ -105,9 +105,9 @@ def main():
            "value": round(total_events / (proc_ms / 1e3), 1), "unit": "events/s", "batches": args.batches, "events_per_batch": n,
            "keys": args.keys, "ms_per_batch": round(proc_ms / args.batches, 3),
            "k3_hash_agg": {"launches": k3_n, "total_ms": round(k3_ms, 2), "rows_visited": k3_rows,
-                           "alg_bytes_per_row": row_bytes, "gbs": round(k3_rows * row_bytes / max(k3_ms, 1e-9) / 1e6, 2),
-                           "frac_of_measured_hbm": round(k3_rows * row_bytes / max(k3_ms, 1e-9) / 1e6 / peak, 4),
-                           "rows_per_s": round(k3_rows / max(k3_ms, 1e-9) * 1e3, 1)},
+                           "alg_bytes_per_row": row_bytes, "gbs": round(k3_rows * row_bytes / k3_ms / 1e6, 2) if k3_n else None,
+                           "frac_of_measured_hbm": round(k3_rows * row_bytes / k3_ms / 1e6 / peak, 4) if k3_n else None,
+                           "rows_per_s": round(k3_rows / k3_ms * 1e3, 1) if k3_n else None},
            "k_gather": {"launches": kg_n, "total_ms": round(kg_ms, 2), "bytes": g_bytes, "gbs": round(g_bytes / max(kg_ms, 1e-9) / 1e6, 2),
                         "frac_of_measured_hbm": round(g_bytes / max(kg_ms, 1e-9) / 1e6 / peak, 4)},
            "k1_decode_total_ms": round(k1_ms, 2), "k3p": {k: ctx.take_counter(k) for k in ("k3p_partitions", "k3p_repartitions", "k3p_output_regrows", "k3_partial_rows_built")},
