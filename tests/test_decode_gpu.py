@@ -176,3 +176,29 @@ def test_unsupported_schema_fails_loudly(dx, ctx):
     bad = '{"type":"struct","fields":[{"name":"a","type":{"type":"array","elementType":"long","containsNull":true},"nullable":true,"metadata":{}}]}'
     with pytest.raises(dx.DxError):
         dx.Decoder(ctx, bad)
+
+
+def test_digit_runs_at_every_window_boundary(dx, ctx):
+    """The fast path reads digit runs four bytes at a time and takes the byte that ends a run from the last window:
+    every run length 1..19 for longs, every integer/fraction split for doubles, each followed by '.', 'e', 'E', ',' or '}',
+    with and without a sign, at every alignment of the record start (a prefix of blank padding records shifts it)."""
+    tmpl = '{"deviceDetails":{"deviceId":%s,"deviceType":"T","eventTime":%s,"homeId":1,"status":0,"temperature":%s,"humidity":%s}}'
+    digits = "1234567890123456789"
+    recs = []
+    for n in range(1, 20):
+        for sign in ("", "-"):
+            recs.append(tmpl % (sign + digits[:n], digits[:min(n, 13)], "1.5", "2"))
+    for ni in range(1, 17):
+        for nf in range(0, 17 - ni):
+            body = digits[:ni] + ("." + digits[3:3 + nf] if nf else "")
+            for tail in ("", "e2", "E-1", "e+0"):
+                recs.append(tmpl % ("7", "8", body + tail, "-" + body))
+    recs += [tmpl % ("0", "0", "0", "-0"), tmpl % ("-0", "1", "0.0", "-0.0"), tmpl % ("00", "1", "1", "1"), tmpl % ("1", "1", "01.5", "1"),
+             tmpl % ("1", "1", "1.", "1"), tmpl % ("1", "1", ".5", "1"), tmpl % ("1", "1", "-", "1"), tmpl % ("-", "1", "1", "1"),
+             tmpl % ("1.0", "1", "1", "1"), tmpl % ("1e2", "1", "1", "1"), tmpl % ("12345678", "12345678", "12345678", "1234.5678"),
+             tmpl % ("1234", "1234", "1234", "12345678.12345678")]
+    dec = dx.Decoder(ctx, SCHEMA2)
+    for pad in range(4):
+        data = to_ndjson(["x" * pad] + recs) if pad else to_ndjson(recs)
+        compare(dec.decode_host(data), dxo.decode(S2, data), S2)
+    dec.close()
