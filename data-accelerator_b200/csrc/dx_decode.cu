@@ -19,419 +19,7 @@
 #include "dx_json.h"
 #include "dx_decode_host.h"
 
-#ifndef K1_T_DEFAULT
-#define K1_T_DEFAULT 32768  // tile bytes when the record length is unknown (a multiple of 4096; see k1_pick_tile)
-#endif
-#define K1_OVL 2048         // overlap bytes past the tile (records starting in the tile may end here)
-#define K1_PAD 32
-#ifndef K1_NT
-#define K1_NT 256           // threads per CTA
-#endif
-#define K1_SC 1024          // record starts held in shared memory per round
-#ifndef K1_STAGES
-#define K1_STAGES 1         // shared-memory tile stages; 2 = prefetch the next tile while parsing (measured slower: 3 CTAs/SM already overlap copy and parse)
-#endif
-#ifndef K1_MIN_CTAS
-#define K1_MIN_CTAS 4       // resident CTAs per SM the register allocation is held to (64 registers; measured 3 / 4 / 5: 3.27 / 3.03 / 3.03 ms per 25 M events)
-#endif
-
-// ------------------------------- PTX wrappers ------------------------------------------
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
-    uint32_t ok;
-    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
-                 : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
-    return ok != 0;
-}
-__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-__device__ __forceinline__ void fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
-
-// ------------------------------- shared-memory readers ---------------------------------
-__device__ __forceinline__ uint32_t ld32u(const uint8_t* buf, uint32_t pos) {
-    const uint32_t* w = reinterpret_cast<const uint32_t*>(buf + (pos & ~3u));
-    return __funnelshift_r(w[0], w[1], (pos & 3u) << 3);
-}
-#include "dx_decode_fast.cuh"
-
-__device__ __forceinline__ unsigned long long ld_state(const unsigned long long* p) {
-    return *reinterpret_cast<const volatile unsigned long long*>(p);
-}
-
-// Decoupled look-back over per-tile record counts; executed by one full warp.
-__device__ long long tile_lookback(unsigned long long* state, long long tile, unsigned long long my_count) {
-    const unsigned full = 0xffffffffu;
-    const int lane = threadIdx.x & 31;
-    const unsigned long long VAL = (1ull << 62) - 1;
-    if (tile == 0) {
-        if (lane == 0) atomicExch(&state[0], (2ull << 62) | my_count);
-        return 0;
-    }
-    if (lane == 0) atomicExch(&state[tile], (1ull << 62) | my_count);
-    long long excl = 0;
-    long long j = tile - 1;
-    for (;;) {
-        long long idx = j - lane;
-        unsigned long long v;
-        do {
-            v = (idx >= 0) ? ld_state(&state[idx]) : (2ull << 62);
-        } while (__any_sync(full, (v >> 62) == 0));
-        unsigned pmask = __ballot_sync(full, (v >> 62) == 2);
-        int first = pmask ? (__ffs(pmask) - 1) : 31;
-        long long contrib = (lane <= first) ? (long long)(v & VAL) : 0;
-        for (int s = 16; s > 0; s >>= 1) contrib += __shfl_xor_sync(full, contrib, s);
-        excl += contrib;
-        if (pmask) break;
-        j -= 32;
-    }
-    if (lane == 0) atomicExch(&state[tile], (2ull << 62) | (unsigned long long)(excl + (long long)my_count));
-    return excl;
-}
-
-// Only the first and the last tile of a batch can hold newline candidates outside the data; kept out of line so the nine
-// unrolled scan rounds stay compact in the instruction cache.
-__device__ __noinline__ uint32_t k1_edge_mask(uint32_t m, long long q0, long long n_end, long long skew) {
-    if (q0 + 16 >= n_end) {
-        for (int i = 0; i < 16; i++) if (q0 + i + 1 >= n_end) m &= ~(1u << i);
-    }
-    if (q0 < skew) {
-        for (int i = 0; i < 16; i++) if (q0 + i < skew) m &= ~(1u << i);
-    }
-    return m;
-}
-
-// The tile size is a template parameter chosen per launch from the batch's mean record length, so that a tile holds just
-// under K1_NT records and the one-lane-per-record parse keeps (nearly) every lane of every warp busy.
-template <int K1_T>
-__global__ void __launch_bounds__(K1_NT, K1_MIN_CTAS) k1_decode(const __grid_constant__ DecodeArgs a) {
-    extern __shared__ __align__(128) uint8_t smem[];
-    constexpr int TILE_BYTES = K1_T + K1_OVL + K1_PAD;                     // one staged tile (multiple of 16)
-    uint16_t* s_starts = reinterpret_cast<uint16_t*>(smem + K1_STAGES * TILE_BYTES);   // K1_SC + 2
-    __shared__ uint64_t s_bar[K1_STAGES];
-    __shared__ long long s_tile;
-    __shared__ long long s_rowbase;
-    __shared__ uint32_t s_wtot[K1_NT / 32];
-    __shared__ long long s_r0;
-    __shared__ uint32_t s_tail_nl;   // first newline at or past the tile end (shared-memory position), ~0u if none loaded
-
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const DSchemaDev* S = a.schema;
-    if (tid == 0) { for (int k = 0; k < K1_STAGES; k++) mbar_init(&s_bar[k], 1); fence_mbar_init(); }
-    __syncthreads();
-
-    const uint32_t n_leaves = (uint32_t)S->n_leaves;
-    const uint32_t all_valid = (n_leaves >= 32) ? 0xFFFFFFFFu : ((1u << n_leaves) - 1u);
-    uint32_t c_rows = 0, c_null = 0, c_fast = 0, c_err = 0;    // per thread (a thread sees far fewer than 2^32 records); widened when added to the statistics
-    uint32_t phase_bits = 0;     // bit k: parity the next completion of stage k will have
-
-    // Stages one tile: bulk (TMA) copy of the 16-byte-aligned part onto the stage's mbarrier, the ragged
-    // tail (< 16 bytes) and the end-of-data sentinel by ordinary stores.  All threads call it.
-    auto stage_tile = [&](int slot, long long tile) {
-        uint8_t* dst = smem + slot * TILE_BYTES;
-        const long long lo_ = tile * (long long)K1_T;
-        long long av = a.n_end - lo_; if (av > K1_T + K1_OVL) av = K1_T + K1_OVL;
-        const uint32_t bulk_ = (uint32_t)av & ~15u;
-        if (tid == 0) {
-            fence_proxy_async();
-            if (bulk_) {
-                mbar_expect_tx(&s_bar[slot], bulk_);
-                uint32_t off = 0;
-                while (off < bulk_) {
-                    uint32_t n = bulk_ - off; if (n > 16384u) n = 16384u;
-                    bulk_g2s(dst + off, a.base_al + lo_ + off, n, &s_bar[slot]);
-                    off += n;
-                }
-            }
-        }
-        if (tid < (int)((uint32_t)av - bulk_)) dst[bulk_ + tid] = a.base_al[lo_ + bulk_ + tid];
-        if (tid == 32 && lo_ + av == a.n_end) dst[av] = '\n';
-    };
-
-    if (tid == 0) s_tile = (long long)atomicAdd(a.tile_counter, 1u);
-    __syncthreads();
-    long long tile = s_tile;
-    int slot = 0;
-    if (tile < a.n_tiles) stage_tile(0, tile);
-    for (;;) {
-        if (tile >= a.n_tiles) break;
-        long long next_tile = a.n_tiles;
-        if (K1_STAGES > 1) {
-            // claim the following tile now and start its copy into the other stage, so it lands while this one is parsed
-            __syncthreads();
-            if (tid == 0) s_tile = (long long)atomicAdd(a.tile_counter, 1u);
-            __syncthreads();
-            next_tile = s_tile;
-            if (next_tile < a.n_tiles) stage_tile(slot ^ 1, next_tile);
-        }
-        uint8_t* buf = smem + slot * TILE_BYTES;
-        const long long lo = tile * (long long)K1_T;                 // absolute (relative to base_al)
-        long long avail = a.n_end - lo;                              // bytes of data from lo on
-        if (avail > K1_T + K1_OVL) avail = K1_T + K1_OVL;
-        const uint32_t bulk = (uint32_t)avail & ~15u;
-        if (bulk) { while (!mbar_try_wait(&s_bar[slot], (phase_bits >> slot) & 1u)) {} phase_bits ^= 1u << slot; }
-        __syncthreads();
-
-        long long n_rec = 0; long long rec0 = 0;   // offsets mode: records [rec0, rec0+n_rec)
-        const bool first_virtual = (tile == 0 && (long long)a.skew < a.n_end);
-        if (a.offsets == nullptr) {
-            // --- structural scan: newline q in [lo, hi) owns the record starting at q+1 ---
-            // warp w scans chunks [w*CPW, (w+1)*CPW), lane-strided so shared loads are conflict-free
-            constexpr int CPW = (K1_T / 16) / (K1_NT / 32);   // 256
-            constexpr int ROUNDS = CPW / 32;                  // 8
-            const bool edge_tile = lo < (long long)a.skew || lo + (long long)K1_T + 16 >= a.n_end;
-            // A tile with more than K1_SC records (records shorter than ~40 bytes) is parsed in rounds of K1_SC; every round
-            // repeats the scan instead of keeping its masks and ranks, so those registers are free while records are parsed.
-            for (uint32_t round0 = 0; ; round0 += K1_SC) {
-            if (round0 > 0) __syncthreads();      // the previous round's readers of s_starts / s_wtot are done
-            uint32_t cnt_total = 0;
-            uint32_t excl_in_warp[ROUNDS];
-            uint32_t my_masks[(ROUNDS + 1) / 2];
-#pragma unroll
-            for (int r = 0; r < ROUNDS; r++) {
-                const int chunk = warp * CPW + r * 32 + lane;
-                const uint4 v = *reinterpret_cast<const uint4*>(buf + chunk * 16);
-                uint32_t m = 0;
-                const uint32_t ws[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-                for (int k = 0; k < 4; k++) {
-                    const uint32_t x = ws[k] ^ 0x0A0A0A0Au;                 // zero byte where '\n'
-                    uint32_t t = (x & 0x7F7F7F7Fu) + 0x7F7F7F7Fu;           // exact per-byte zero test
-                    t = ~(t | x | 0x7F7F7F7Fu);                             // 0x80 in each byte that was zero
-                    m |= ((t * 0x00204081u) >> 28) << (k * 4);              // gather the four flags
-                }
-                // validity of each candidate q = lo + chunk*16 + i : start q+1 must be data (< n_end), q >= skew
-                if (edge_tile) m = k1_edge_mask(m, lo + (long long)chunk * 16, a.n_end, (long long)a.skew);
-                if (r & 1) my_masks[r >> 1] |= m << 16; else my_masks[r >> 1] = m;
-                excl_in_warp[r] = __popc(m);          // this lane's count for now; turned into a rank below
-            }
-            {
-                // one prefix sum for three rounds at a time: a lane's count is <= 16 and a round's total <= 512, so three 10-bit
-                // fields share a word and the rounds' shuffle chains run side by side instead of one after the other
-                constexpr int NW = (ROUNDS + 2) / 3;
-                uint32_t pk[NW];
-#pragma unroll
-                for (int w = 0; w < NW; w++) {
-                    pk[w] = excl_in_warp[3 * w];
-                    if (3 * w + 1 < ROUNDS) pk[w] |= excl_in_warp[3 * w + 1] << 10;
-                    if (3 * w + 2 < ROUNDS) pk[w] |= excl_in_warp[3 * w + 2] << 20;
-                }
-#pragma unroll
-                for (int s = 1; s < 32; s <<= 1) {
-#pragma unroll
-                    for (int w = 0; w < NW; w++) { const uint32_t t = __shfl_up_sync(0xffffffffu, pk[w], s); if (lane >= s) pk[w] += t; }
-                }
-#pragma unroll
-                for (int r = 0; r < ROUNDS; r++) {
-                    const uint32_t incl = (pk[r / 3] >> (10 * (r % 3))) & 1023u;
-                    const uint32_t tot = (__shfl_sync(0xffffffffu, pk[r / 3], 31) >> (10 * (r % 3))) & 1023u;
-                    excl_in_warp[r] = cnt_total + incl - excl_in_warp[r];
-                    cnt_total += tot;
-                }
-            }
-            if (lane == 0) s_wtot[warp] = cnt_total;
-            if (warp == K1_NT / 32 - 1 && round0 == 0) {
-                // the tile's last record ends at the first newline at or past the tile end: find it with the
-                // whole warp (16 bytes per lane per round) instead of one lane walking bytes
-                const uint32_t lim = (uint32_t)avail + ((lo + avail == a.n_end) ? 1u : 0u);
-                uint32_t found = 0xFFFFFFFFu;
-                for (uint32_t c0 = K1_T / 16; c0 * 16 < lim && found == 0xFFFFFFFFu; c0 += 32) {
-                    const uint32_t chunk = c0 + lane;
-                    uint32_t m = 0;
-                    if (chunk * 16 < lim) {
-                        const uint4 v = *reinterpret_cast<const uint4*>(buf + chunk * 16);
-                        const uint32_t ws[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-                        for (int k = 0; k < 4; k++) {
-                            const uint32_t x = ws[k] ^ 0x0A0A0A0Au;
-                            uint32_t t = (x & 0x7F7F7F7Fu) + 0x7F7F7F7Fu;
-                            t = ~(t | x | 0x7F7F7F7Fu);
-                            m |= ((t * 0x00204081u) >> 28) << (k * 4);
-                        }
-                        if (chunk * 16 + 16 > lim) m &= (1u << (lim - chunk * 16)) - 1u;
-                    }
-                    const unsigned who = __ballot_sync(0xffffffffu, m != 0);
-                    if (who) {
-                        const int src = __ffs(who) - 1;
-                        const uint32_t mm = __shfl_sync(0xffffffffu, m, src);
-                        found = (c0 + src) * 16 + (__ffs(mm) - 1);
-                    }
-                }
-                if (lane == 0) s_tail_nl = found;
-            }
-            __syncthreads();
-            uint32_t wbase = first_virtual ? 1u : 0u, total = first_virtual ? 1u : 0u;
-#pragma unroll
-            for (int w = 0; w < K1_NT / 32; w++) { uint32_t t = s_wtot[w]; if (w < warp) wbase += t; total += t; }
-            n_rec = total;
-            if (warp == 0 && round0 == 0) {
-#ifdef K1_NO_LOOKBACK    /* tuning experiment only: what the row-index look-back costs (row numbers are wrong in this build) */
-                long long rb = tile * 200;
-#else
-                long long rb = tile_lookback(a.tile_state, tile, (unsigned long long)n_rec);
-#endif
-                if (lane == 0) s_rowbase = rb;
-            }
-            {
-                if (first_virtual && tid == 0 && round0 == 0) s_starts[0] = (uint16_t)a.skew;
-#pragma unroll
-                for (int r = 0; r < ROUNDS; r++) {
-                    uint32_t m = (r & 1) ? (my_masks[r >> 1] >> 16) : (my_masks[r >> 1] & 0xffffu);
-                    uint32_t rel = wbase + excl_in_warp[r] - round0;     // wraps to a huge value for earlier rounds' records
-                    const uint32_t pos0 = (uint32_t)(warp * CPW + r * 32 + lane) * 16 + 1;
-                    while (m) {
-                        const int i = __ffs(m) - 1; m &= m - 1;
-                        if (rel <= K1_SC) s_starts[rel] = (uint16_t)(pos0 + i);
-                        rel++;
-                    }
-                }
-                __syncthreads();
-                const long long row_base = s_rowbase;
-                const int cnt = (int)((n_rec - round0 > K1_SC) ? K1_SC : (n_rec - round0));
-                for (int base = 0; base < cnt; base += K1_NT) {
-                    const int idx = base + tid;
-                    const bool has = idx < cnt;
-                    uint32_t st = 0, en = 0; bool in_smem = true; long long en_abs = 0;
-                    const long long rank = round0 + idx;
-                    if (has) {
-                        st = s_starts[idx];
-                        if (rank + 1 < n_rec) en = (uint32_t)s_starts[idx + 1] - 1u;
-                        else {
-                            // last record owned by this tile: its newline lies at or past the tile end
-                            const uint32_t lim = (uint32_t)avail + ((lo + avail == a.n_end) ? 1u : 0u);
-                            const uint32_t p = s_tail_nl;
-                            if (p != 0xFFFFFFFFu) en = p;
-                            else if (lo + avail == a.n_end) {
-                                // the data ends inside the tile proper: the record runs to the final newline or the end of data
-                                const uint32_t av = (uint32_t)avail;
-                                en = (av > st && buf[av - 1] == '\n') ? av - 1 : av;
-                            } else {
-                                in_smem = false;
-                                long long g = lo + lim;
-                                while (g < a.n_end && a.base_al[g] != '\n') g++;
-                                en_abs = g;
-                            }
-                        }
-                    }
-                    RowSink o; o.a = &a; o.row = row_base + rank; o.valid = 0; o.err = 0;
-                    const bool overflow = has && o.row >= a.max_rows;
-                    if (overflow) c_err |= DXF_ROW_OVERFLOW;
-                    const bool live = has && !overflow;
-#ifdef K1_SKIP_PARSE     /* tuning experiment only (tools/build_variant.sh): cost of scan + row indexing without the record parse */
-                    bool ok = live; o.valid = all_valid; if (live) reinterpret_cast<long long*>(a.cols[0])[o.row] = st + en;
-#else
-                    bool ok = fast_record_warp(buf, st, en, live && in_smem, a, o);
-#endif
-                    if (live) {
-                        if (ok) c_fast++;
-                        else if (in_smem) ok = g_record(buf + st, buf + en, S, o);
-                        else ok = g_record(a.base_al + lo + st, a.base_al + en_abs, S, o);
-                        c_rows++; if (!ok) c_null++;
-                        c_err |= o.err;
-                        if (o.valid != all_valid) {
-                            for (uint32_t k = 0; k < n_leaves; k++) if (!((o.valid >> k) & 1u)) {
-                                if (S->leaf_type[k] == DX_T_STR) reinterpret_cast<int32_t*>(a.cols[k])[o.row] = -1;
-                                else reinterpret_cast<long long*>(a.cols[k])[o.row] = 0;
-                            }
-                        }
-                        if (a.mask_width == 1) reinterpret_cast<uint8_t*>(a.mask)[o.row] = (uint8_t)(o.valid | (ok ? 0x80u : 0u));
-                        else reinterpret_cast<uint32_t*>(a.mask)[o.row] = o.valid | (ok ? 0x80000000u : 0u);
-                    }
-                }
-                if ((long long)round0 + K1_SC >= n_rec) break;
-            }
-            }
-        } else {
-            // --- caller-provided framing: records whose first byte lies in [lo, hi) ---
-            if (warp == 0) {
-                // first record r with skew + offsets[r] >= target (offsets ascending, n_rows+1 entries): a 33-way search, the 32
-                // lanes probing evenly spaced entries per round, so a tile costs ~5 dependent global loads instead of ~25
-                auto lower_bound = [&](long long l, long long h, long long target) -> long long {
-                    while (l < h) {
-                        const long long step = (h - l + 32) / 33;
-                        const long long idx = l + (long long)(lane + 1) * step - 1;
-                        const bool ge = idx >= h || (long long)a.skew + a.offsets[idx] >= target;
-                        const unsigned b = __ballot_sync(0xffffffffu, ge);
-                        const int f = b ? __ffs(b) - 1 : 32;
-                        const long long pf = l + (long long)(f + 1) * step - 1;          // first probe that is >= target (if f < 32)
-                        const long long nl = f > 0 ? l + (long long)f * step : l;          // one past the last probe that is < target
-                        long long nh = h;
-                        if (f < 32 && pf < h) nh = pf;
-                        l = nl; h = nh;
-                    }
-                    return l;
-                };
-                const long long r_lo = lower_bound(0, a.max_rows, lo);
-                const long long r_hi = lower_bound(r_lo, a.max_rows, lo + K1_T);
-                if (lane == 0) { s_r0 = r_lo; s_rowbase = r_hi; }
-            }
-            __syncthreads();
-            rec0 = s_r0; n_rec = s_rowbase - rec0;
-            for (long long base = 0; base < n_rec; base += K1_NT) {
-                const long long idx = base + tid;
-                const bool has = idx < n_rec;
-                const long long r = rec0 + (has ? idx : 0);
-                long long st_abs = 0, en_abs = 0; uint32_t st = 0, en = 0, en_f = 0; bool in_smem = false;
-                if (has) {
-                    st_abs = (long long)a.skew + a.offsets[r];
-                    en_abs = (long long)a.skew + a.offsets[r + 1];
-                    in_smem = en_abs - lo <= avail;
-                    if (in_smem) {
-                        st = (uint32_t)(st_abs - lo); en = (uint32_t)(en_abs - lo);
-                        // a trailing newline inside the frame is whitespace; the fast path wants the bare record
-                        en_f = en; if (en_f > st && buf[en_f - 1] == '\n') en_f--;
-                    }
-                }
-                RowSink o; o.a = &a; o.row = r; o.valid = 0; o.err = 0;
-                bool ok = fast_record_warp(buf, st, en_f, has && in_smem, a, o);
-                if (has) {
-                    if (ok) c_fast++;
-                    else if (in_smem) ok = g_record(buf + st, buf + en, S, o);
-                    else ok = g_record(a.base_al + st_abs, a.base_al + en_abs, S, o);
-                    c_rows++; if (!ok) c_null++;
-                    c_err |= o.err;
-                    if (o.valid != all_valid) {
-                        for (uint32_t k = 0; k < n_leaves; k++) if (!((o.valid >> k) & 1u)) {
-                            if (S->leaf_type[k] == DX_T_STR) reinterpret_cast<int32_t*>(a.cols[k])[o.row] = -1;
-                            else reinterpret_cast<long long*>(a.cols[k])[o.row] = 0;
-                        }
-                    }
-                    if (a.mask_width == 1) reinterpret_cast<uint8_t*>(a.mask)[o.row] = (uint8_t)(o.valid | (ok ? 0x80u : 0u));
-                    else reinterpret_cast<uint32_t*>(a.mask)[o.row] = o.valid | (ok ? 0x80000000u : 0u);
-                }
-            }
-        }
-        __syncthreads();
-        if (K1_STAGES > 1) { tile = next_tile; slot ^= 1; }
-        else {
-            if (tid == 0) s_tile = (long long)atomicAdd(a.tile_counter, 1u);
-            __syncthreads();
-            tile = s_tile;
-            if (tile < a.n_tiles) stage_tile(0, tile);
-        }
-    }
-    // per-warp reduction of the counters, one atomic each
-    for (int s = 16; s > 0; s >>= 1) {
-        c_rows += __shfl_xor_sync(0xffffffffu, c_rows, s);
-        c_null += __shfl_xor_sync(0xffffffffu, c_null, s);
-        c_fast += __shfl_xor_sync(0xffffffffu, c_fast, s);
-        c_err |= __shfl_xor_sync(0xffffffffu, c_err, s);
-    }
-    if (lane == 0) {
-        if (c_rows) atomicAdd(&a.stats->rows, (unsigned long long)c_rows);
-        if (c_null) atomicAdd(&a.stats->null_rows, (unsigned long long)c_null);
-        if (c_fast) atomicAdd(&a.stats->fast_rows, (unsigned long long)c_fast);
-        if (c_err) atomicOr(&a.stats->flags, (unsigned long long)c_err);
-    }
-}
+#include "dx_decode_kernel.cuh"
 
 // Counts records of an NDJSON buffer (used only when the caller does not state n_events).
 __global__ void k1_count_records(const uint8_t* bytes, long long n, unsigned long long* out) {
@@ -445,9 +33,6 @@ __global__ void k1_count_records(const uint8_t* bytes, long long n, unsigned lon
 // =======================================================================================
 // host side
 // =======================================================================================
-static size_t k1_smem_bytes(int tile) {
-    return K1_STAGES * (tile + K1_OVL + K1_PAD) + (K1_SC + 2) * 2 + 64;
-}
 static const int k1_tiles[] = {16384, 20480, 24576, 28672, 32768, 36864, 40960, 45056, 49152};
 // tile bytes for a batch: the largest instantiated size that still keeps the expected records per tile under ~246
 static int k1_pick_tile(long long n_bytes, long long n_events) {
@@ -457,28 +42,32 @@ static int k1_pick_tile(long long n_bytes, long long n_events) {
     for (int t : k1_tiles) if ((double)t / avg <= 246.0) best = t;
     return best;
 }
-template <int T> static int k1_setup_one(dx_ctx* c, int* occ_out) {
-    DX_CUDA(c, cudaFuncSetAttribute(k1_decode<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k1_smem_bytes(T)));
+template <int T> static int k1_setup_one(dx_ctx* c, int* occ_out) {      // occ_out[0]: NDJSON kernel, occ_out[9]: framed kernel
+    DX_CUDA(c, cudaFuncSetAttribute(k1_decode<T, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k1_smem_bytes(T)));
     int occ = 0;
-    DX_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k1_decode<T>, K1_NT, k1_smem_bytes(T)));
-    *occ_out = occ > 0 ? occ : 1;
+    DX_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k1_decode<T, false>, K1_NT, k1_smem_bytes(T)));
+    occ_out[0] = occ > 0 ? occ : 1;
+    DX_CUDA(c, (cudaError_t)k1_framed_setup(T, &occ));
+    occ_out[9] = occ > 0 ? occ : 1;
     return DX_OK;
 }
 static int k1_launch(dx_ctx* c, int tile, const int* occ_by_tile, const DecodeArgs& a) {
     int idx = 0; for (int i = 0; i < 9; i++) if (k1_tiles[i] == tile) idx = i;
-    long long grid = (long long)c->sm_count * occ_by_tile[idx];
+    const bool framed = a.offsets != nullptr;
+    long long grid = (long long)c->sm_count * occ_by_tile[idx + (framed ? 9 : 0)];
     if (grid > a.n_tiles) grid = a.n_tiles;
     const size_t smem = k1_smem_bytes(tile);
+    if (framed) { k1_framed_launch(tile, (unsigned)grid, c->stream, a); c->launches["k1_decode"]++; return DX_OK; }
     switch (tile) {
-    case 16384: k1_decode<16384><<<(unsigned)grid, K1_NT, smem, c->stream>>>(a); break;
-    case 20480: k1_decode<20480><<<(unsigned)grid, K1_NT, smem, c->stream>>>(a); break;
-    case 24576: k1_decode<24576><<<(unsigned)grid, K1_NT, smem, c->stream>>>(a); break;
-    case 28672: k1_decode<28672><<<(unsigned)grid, K1_NT, smem, c->stream>>>(a); break;
-    case 36864: k1_decode<36864><<<(unsigned)grid, K1_NT, smem, c->stream>>>(a); break;
-    case 40960: k1_decode<40960><<<(unsigned)grid, K1_NT, smem, c->stream>>>(a); break;
-    case 45056: k1_decode<45056><<<(unsigned)grid, K1_NT, smem, c->stream>>>(a); break;
-    case 49152: k1_decode<49152><<<(unsigned)grid, K1_NT, smem, c->stream>>>(a); break;
-    default: k1_decode<32768><<<(unsigned)grid, K1_NT, smem, c->stream>>>(a); break;
+    case 16384: k1_decode<16384, false><<<(unsigned)grid, K1_NT, smem, c->stream>>>(a); break;
+    case 20480: k1_decode<20480, false><<<(unsigned)grid, K1_NT, smem, c->stream>>>(a); break;
+    case 24576: k1_decode<24576, false><<<(unsigned)grid, K1_NT, smem, c->stream>>>(a); break;
+    case 28672: k1_decode<28672, false><<<(unsigned)grid, K1_NT, smem, c->stream>>>(a); break;
+    case 36864: k1_decode<36864, false><<<(unsigned)grid, K1_NT, smem, c->stream>>>(a); break;
+    case 40960: k1_decode<40960, false><<<(unsigned)grid, K1_NT, smem, c->stream>>>(a); break;
+    case 45056: k1_decode<45056, false><<<(unsigned)grid, K1_NT, smem, c->stream>>>(a); break;
+    case 49152: k1_decode<49152, false><<<(unsigned)grid, K1_NT, smem, c->stream>>>(a); break;
+    default: k1_decode<32768, false><<<(unsigned)grid, K1_NT, smem, c->stream>>>(a); break;
     }
     c->launches["k1_decode"]++;
     return DX_OK;

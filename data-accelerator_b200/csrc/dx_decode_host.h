@@ -13,7 +13,7 @@ struct dx_decoder {
     uint32_t dict_capacity = 1u << 16;     // slots per string column (power of two)
     uint32_t dict_heap_bytes = 4u << 20;
     int ctas_per_sm = 1;
-    int occ_by_tile[9] = {1, 1, 1, 1, 1, 1, 1, 1, 1};   // resident CTAs per SM of each tile-size instantiation of K1
+    int occ_by_tile[18] = {1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1};   // resident CTAs per SM of each tile-size instantiation of K1: [0..9) NDJSON, [9..18) caller-framed
     int init(dx_ctx* c, const std::string& schema_json);
     int decode_device(const uint8_t* json_dev, int64_t n_bytes, const int64_t* offsets_dev, int64_t n_events, DxTableP* out);
     int decode_host(const uint8_t* json, int64_t n_bytes, const int64_t* offsets, int64_t n_events, DxTableP* out);
