@@ -15,6 +15,8 @@
 //   4. one thread per record: schema-ordered template fast path (word-wise literal compare,
 //      digit loops) with fall-through to a general Spark-2.4-conformant parser in the same
 //      kernel; lanes hold consecutive rows, so every column store is a coalesced 128/256 B line.
+// The kernel template lives in dx_decode_kernel.cuh; this file instantiates the NDJSON kernels and holds the host side,
+// dx_decode_framed.cu instantiates the kernels for caller-provided record offsets (step 2 replaced by a search in the offsets).
 #include "dx_decode.cuh"
 #include "dx_json.h"
 #include "dx_decode_host.h"

@@ -14,7 +14,7 @@
 #endif
 #define K1_SC 1024          // record starts held in shared memory per round
 #ifndef K1_STAGES
-#define K1_STAGES 1         // shared-memory tile stages; 2 = prefetch the next tile while parsing (measured slower: 3 CTAs/SM already overlap copy and parse)
+#define K1_STAGES 1         // shared-memory tile stages; 2 = prefetch the next tile while parsing (measured slower: the resident CTAs of an SM already overlap copy and parse)
 #endif
 #ifndef K1_MIN_CTAS_FRAMED
 #define K1_MIN_CTAS_FRAMED 5   // caller-provided framing: no scan state; the record parse alone runs best at 48 registers (2.74 -> 2.51 ms per 25 M events)
