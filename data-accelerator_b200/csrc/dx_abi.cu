@@ -117,6 +117,25 @@ int dx_decoder_decode_noalloc(dx_decoder* d, const uint8_t* json_dev, int64_t n_
     if (cudaSetDevice(d->ctx->device) != cudaSuccess) return d->ctx->set_error(DX_ERR_CUDA, "cudaSetDevice failed");
     return d->decode_noalloc(json_dev, n_bytes, n_events, column_ptrs, n_columns, mask_ptr, rows, null_rows);
 }
+int dx_decoder_dict_size(dx_decoder* d, int column, int64_t* n_codes) {
+    if (!d || !n_codes) return DX_ERR_ARG;
+    if (column < 0 || column >= (int)d->dicts.size() || !d->dicts[column]) return d->ctx->set_error(DX_ERR_ARG, "not a string column of this decoder");
+    int prev = -1; cudaGetDevice(&prev);
+    cudaSetDevice(d->ctx->device);
+    int rc = d->dicts[column]->sync_to_host();
+    if (prev >= 0) cudaSetDevice(prev);
+    if (rc) return rc;
+    *n_codes = (int64_t)d->dicts[column]->host_strings.size();
+    return DX_OK;
+}
+int dx_decoder_dict_string(dx_decoder* d, int column, int64_t code, const char** bytes, int64_t* len) {
+    if (!d || !bytes || !len) return DX_ERR_ARG;
+    if (column < 0 || column >= (int)d->dicts.size() || !d->dicts[column]) return d->ctx->set_error(DX_ERR_ARG, "not a string column of this decoder");
+    const auto& hs = d->dicts[column]->host_strings;
+    if (code < 0 || code >= (int64_t)hs.size()) return d->ctx->set_error(DX_ERR_ARG, "dictionary code out of range (call dx_decoder_dict_size first)");
+    *bytes = hs[(size_t)code].data(); *len = (int64_t)hs[(size_t)code].size();
+    return DX_OK;
+}
 int dx_decoder_stats(const dx_decoder* d, int64_t* rows, int64_t* null_rows, int64_t* fast_rows) {
     if (rows) *rows = (int64_t)d->last_stats.rows;
     if (null_rows) *null_rows = (int64_t)d->last_stats.null_rows;

@@ -65,9 +65,12 @@ __global__ void __launch_bounds__(256) k3_hash_agg(const __grid_constant__ AggTa
             unsigned long long* s = T.slots + idx * sw;
             unsigned long long cur = *reinterpret_cast<volatile unsigned long long*>(s);
             if (cur == tag) {
-                bool same = (s[nk + 1] == nullbits);
+                // The filler publishes the tag after a __threadfence, so the key words are in L2 once the tag is seen — but this
+                // SM's L1 may still hold the sector from before they were written (a slot can straddle the 32-byte sector of a
+                // neighbour that was compared earlier).  Read them from L2 (ld.global.cg), never through L1.
+                bool same = (__ldcg(s + nk + 1) == nullbits);
 #pragma unroll
-                for (int k = 0; k < KMAX; k++) if (k < nk) same = same && ((long long)s[1 + k] == kv[k]);
+                for (int k = 0; k < KMAX; k++) if (k < nk) same = same && ((long long)__ldcg(s + 1 + k) == kv[k]);
                 if (same) { slot = s; break; }
             } else if (cur == 0ull) {
                 if (atomicCAS(s, 0ull, 1ull) == 0ull) {

@@ -138,8 +138,9 @@ __global__ void __launch_bounds__(K3P_NT) k3p_aggregate(const __grid_constant__ 
                 unsigned long long* sl = tab + (size_t)idx * sw;
                 const unsigned long long cur = *reinterpret_cast<volatile unsigned long long*>(sl);
                 if (cur == tag) {
-                    bool same = sl[2 + A.nkk] == knull;
-                    for (int k = 0; k < A.nkk && same; k++) same = sl[2 + k] == r[1 + k];
+                    const volatile unsigned long long* vs = sl;     // ordered after the volatile read of the tag
+                    bool same = vs[2 + A.nkk] == knull;
+                    for (int k = 0; k < A.nkk && same; k++) same = vs[2 + k] == r[1 + k];
                     if (same) { slot = sl; break; }
                 } else if (cur == 0ull) {
                     if (atomicCAS(sl, 0ull, 1ull) == 0ull) {
@@ -231,10 +232,10 @@ static size_t p2_smem(int gw) { return (size_t)K3P_SLOTS * (gw + 1) * 8; }
 
 static int p2_launch(dx_ctx* ctx, const P2Args& A, int P) {
     const size_t smem = p2_smem(A.gw);
-    static size_t configured = 0;
-    if (smem > configured) {
+    // the attribute belongs to the (function, device) pair: remembered per context, i.e. per device, not process-wide
+    if (smem > ctx->k3p_smem_configured) {
         DX_CUDA(ctx, cudaFuncSetAttribute(k3p_aggregate, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = smem;
+        ctx->k3p_smem_configured = smem;
     }
     StageTimer tm(ctx, "k3p_aggregate");
     k3p_aggregate<<<(unsigned)P, K3P_NT, smem, ctx->stream>>>(A);

@@ -318,8 +318,7 @@ static int noalloc_scratch_address(dx_ctx* c, unsigned long long** out) {
     if (c->device < 0 || c->device >= DX_NOALLOC_MAX_DEVICES) return c->set_error(DX_ERR_ARG, "device ordinal out of range");
     std::lock_guard<std::mutex> g(g_noalloc_mu);
     if (!g_noalloc_dev_ptr[c->device]) {
-        DX_CUDA(c, cudaSetDevice(c->device));
-        void* p = nullptr;
+        void* p = nullptr;                        // the caller has made c->device current
         cudaError_t e = cudaGetSymbolAddress(&p, dx_noalloc_scratch);
         if (e != cudaSuccess || !p) {
             return c->set_error(DX_ERR_CUDA, std::string("cudaGetSymbolAddress(dx_noalloc_scratch) failed: ") + cudaGetErrorString(e));
@@ -363,10 +362,13 @@ int dx_decoder::decode_noalloc(const uint8_t* json_dev, int64_t n_bytes, int64_t
                  (long long)DX_NOALLOC_MAX_TILES * K1_T_DEFAULT);
         return c->set_error(DX_ERR_CAPACITY, b);
     }
+    // run on the context's device and hand the calling thread its own current device back on every way out
+    struct DeviceGuard { int prev = -1; ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); } } guard;
+    cudaGetDevice(&guard.prev);
+    DX_CUDA(c, cudaSetDevice(c->device));
     unsigned long long* scratch = nullptr;
     int rc = noalloc_scratch_address(c, &scratch);
     if (rc) return rc;
-    DX_CUDA(c, cudaSetDevice(c->device));
     // the array still holds the last call's counter, statistics and tile states: clear what this call reads
     DX_CUDA(c, cudaMemsetAsync(scratch, 0, (size_t)(DX_NOALLOC_HEADER_WORDS + a.n_tiles + 2) * 8, c->stream));
     a.max_rows = n_events;

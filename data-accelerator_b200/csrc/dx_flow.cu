@@ -254,6 +254,14 @@ struct Exec {
     std::string stmt_name;
 
     int fail(int code, const std::string& m) { return ctx->set_error(code, (stmt_name.empty() ? std::string() : "[" + stmt_name + "] ") + m); }
+    // Lookup tables are cached under their source dictionary's address and hold that dictionary alive; one whose dictionary
+    // nobody else references any more (a transient UNION / constant dictionary, a replaced state table) can never be asked
+    // for again and is dropped here, so the cache does not grow with the number of micro-batches.
+    void prune_luts() {
+        for (auto it = F->luts.begin(); it != F->luts.end(); ) {
+            if (it->second && it->second->src_dict && it->second->src_dict.use_count() == 1) it = F->luts.erase(it); else ++it;
+        }
+    }
 
     BindScope scope_for(const DxTable* t, const SelectCore& core) {
         BindScope sc; sc.table = t; sc.now_us = now_us;
@@ -506,7 +514,7 @@ struct Exec {
                     // per-(source, target) lookup table that only grows with the source dictionary
                     char kb[64]; snprintf(kb, sizeof kb, "recode@%p/%p", (void*)pc.dict.get(), (void*)dict.get());
                     std::shared_ptr<LutCache>& lut = F->luts[kb];
-                    if (!lut) { lut = std::make_shared<LutCache>(); lut->src_dict = pc.dict; lut->out_dict = dict; }
+                    if (!lut) { prune_luts(); lut = std::make_shared<LutCache>(); lut->src_dict = pc.dict; lut->out_dict = dict; }
                     DxDictP target = dict;
                     rc = dx_lut_refresh(ctx, lut.get(), pc.dict, [&](const std::string& sv, long long* v) {
                         int32_t code = -1; if (target->insert_host(sv, &code)) return false; *v = code; return true; });
@@ -661,7 +669,7 @@ struct Exec {
         if (c.type != DX_T_STR) return fail(DX_ERR_UNSUPPORTED, "join on a double or flag column");
         char kb[96]; snprintf(kb, sizeof kb, "@%p/%p/%d", (void*)c.dict.get(), left_str ? (void*)left_str->dict.get() : nullptr, (int)other_is_string);
         std::shared_ptr<LutCache>& lut = F->luts[std::string("joinkey") + kb];
-        if (!lut) lut = std::make_shared<LutCache>();
+        if (!lut) { prune_luts(); lut = std::make_shared<LutCache>(); lut->src_dict = c.dict; }    // the key is the dictionary's address: keep it alive
         int rc;
         if (!other_is_string) {
             rc = dx_lut_refresh(ctx, lut.get(), c.dict, [](const std::string& s, long long* v) {
@@ -972,7 +980,7 @@ struct Exec {
             const bool is_ts = e->sval == "STRINGTOTIMESTAMP";
             char kb[64]; snprintf(kb, sizeof kb, "@%p", (void*)arg.dict.get());
             std::shared_ptr<LutCache>& lut = F->luts[to_string(e) + kb];
-            if (!lut) lut = std::make_shared<LutCache>();
+            if (!lut) { prune_luts(); lut = std::make_shared<LutCache>(); lut->src_dict = arg.dict; }   // the key is the dictionary's address: keep it alive
             if (is_ts) {
                 rc = dx_lut_refresh(ctx, lut.get(), arg.dict, [](const std::string& s, long long* v) { return dx_string_to_timestamp_us(s, v); });
             } else {

@@ -8,10 +8,26 @@ out by hand in exactly the shape the reference emits:
      golden: DataX.Flow.CodegenRules.Tests/cgenDefault.txt:2-36)
   * <flow>.conf keys as flattened by flattenerConfig.json (golden: Local.Test/Resource/jobConfig.conf)
 """
+import json
 import math
 import random
 
 TYPES = ["DoorLock", "WindowLock", "Heating", "GarageDoorLock"]
+
+
+def iot_schema_json(shape=2, event_time_type="long"):
+    """Spark StructType JSON of the home-automation event (DeploymentLocal/sample/HomeAutomationLocal.json:288), plus the
+    two double fields of shape S2 (DeploymentLocal/sample/BasicLocal.json:185)."""
+    f = [{"name": "deviceId", "type": "long", "nullable": True, "metadata": {}},
+         {"name": "deviceType", "type": "string", "nullable": True, "metadata": {}},
+         {"name": "eventTime", "type": event_time_type, "nullable": True, "metadata": {}},
+         {"name": "homeId", "type": "long", "nullable": True, "metadata": {}},
+         {"name": "status", "type": "long", "nullable": True, "metadata": {}}]
+    if shape == 2:
+        f += [{"name": "temperature", "type": "double", "nullable": True, "metadata": {}},
+              {"name": "humidity", "type": "double", "nullable": True, "metadata": {}}]
+    return json.dumps({"type": "struct", "fields": [
+        {"name": "deviceDetails", "type": {"type": "struct", "fields": f}, "nullable": True, "metadata": {}}]})
 
 
 def sql_str(s):

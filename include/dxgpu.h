@@ -89,16 +89,27 @@ int dx_decoder_decode(dx_decoder* d, const uint8_t* json, int64_t n_bytes, const
  *   mask_ptr : n_events validity elements, 1 byte each when the schema has <= 7 leaf columns, else
  *       4 bytes: bit k = column k non-NULL, top bit = the event parsed to a non-NULL struct.
  *   rows / null_rows : optional counts for this call.
+ * String columns receive int32 dictionary codes; the text behind a code is read with
+ * dx_decoder_dict_size / dx_decoder_dict_string below (codes are per decoder and only ever grow).
  * Limit: one call handles at most 65536 tiles of 32 KiB = 2 GiB of JSON; larger batches are rejected
- * with an error (split them, or use dx_decoder_decode).
+ * with an error (split them, or use dx_decoder_decode).  The tile size is fixed at 32 KiB here because
+ * the scratch capacity is stated in tiles; dx_decoder_decode picks the tile from the mean record length
+ * and is a few percent faster on long records.
  * The scratch array is shared by all calls on a device and still holds the previous call's values, so
  * each call clears the part it uses first; calls whose GPU work overlaps (other streams, other
  * threads) race on it and must be serialised by the caller.  The first call on a device also looks up
  * the array's device address (a one-time runtime query): make that first call before any stream
- * capture is begun.                                                                              */
+ * capture is begun.  Every call waits for its kernel and reads the row counts back before it returns.
+ * The calling thread's current CUDA device is the same after the call as before it.                */
 int dx_decoder_decode_noalloc(dx_decoder* d, const uint8_t* json_dev, int64_t n_bytes, int64_t n_events,
                               void* const* column_ptrs, int n_columns, void* mask_ptr,
                               int64_t* rows, int64_t* null_rows);
+/* The decoder's dictionary of a string leaf column (column index as in the decoded table): number of codes handed out
+ * so far, and the UTF-8 text of one code.  For callers that hold only the code arrays dx_decoder_decode_noalloc wrote;
+ * a dx_table answers the same questions through dx_table_dict_size / dx_table_dict_string.  These two copy the new
+ * dictionary entries to the host on demand (no device allocation).                                                */
+int dx_decoder_dict_size(dx_decoder* d, int column, int64_t* n_codes);
+int dx_decoder_dict_string(dx_decoder* d, int column, int64_t code, const char** bytes, int64_t* len);
 /* rows decoded / rows that became NULL structs / rows taken by the template fast path, last call */
 int dx_decoder_stats(const dx_decoder* d, int64_t* rows, int64_t* null_rows, int64_t* fast_rows);
 

@@ -45,19 +45,39 @@ class Agg(C.Structure):
                 ("min_i", C.c_int64), ("max_i", C.c_int64), ("min_d", C.c_double), ("max_d", C.c_double)]
 
 
+def _lib_name():
+    """libdxo.<tag>.so, tag = hash of this host's CPU model + flags: the oracle is built -march=native, so a copy built on
+    another machine (the build container vs the GPU box) must not be loaded — it is rebuilt here instead (2 s of gcc)."""
+    import hashlib
+    key = ""
+    try:
+        for line in open("/proc/cpuinfo"):
+            if line.startswith(("model name", "flags")):
+                key += line
+            if line.startswith("flags"):
+                break
+    except OSError:
+        pass
+    return "libdxo.%s.so" % hashlib.md5(key.encode()).hexdigest()[:8]
+
+
 def build():
-    subprocess.check_call(["make", "-s", "-C", _HERE])
+    tmp = "libdxo.tmp%d.so" % os.getpid()       # built aside and renamed, so a concurrent loader never sees a partial file
+    subprocess.check_call(["make", "-s", "-C", _HERE, "OUT=" + tmp])
+    os.replace(os.path.join(_HERE, tmp), os.path.join(_HERE, _lib_name()))
 
 
 def lib():
     global _LIB
     if _LIB is None:
-        path = os.path.join(_HERE, "libdxo.so")
-        if not os.path.exists(path):
+        path = os.path.join(_HERE, _lib_name())
+        src_time = max(os.path.getmtime(os.path.join(_HERE, f)) for f in ("dxo_core.c", "dxo_rules.c"))
+        if not os.path.exists(path) or os.path.getmtime(path) < src_time:
             build()
         _LIB = C.CDLL(path)
         _LIB.dxo_decode.restype = C.c_int64
         _LIB.dxo_decode_mt.restype = C.c_int64
+        _LIB.dxo_decode_mt_h.restype = C.c_int64
         _LIB.dxo_split.restype = C.c_int64
         _LIB.dxo_gen_events.restype = C.c_int64
         _LIB.dxo_group_agg.restype = C.c_int64
@@ -132,10 +152,12 @@ def decode(schema: Schema, data: bytes, offsets=None, threads=0):
     used = C.c_int64(0)
     vp = C.c_void_p
     if threads and threads > 0:
-        rc = lib().dxo_decode_mt(buf.ctypes.data_as(vp), starts.ctypes.data_as(vp), ends.ctypes.data_as(vp),
-                                 C.c_int64(n), schema.c_structs, schema.c_fields, C.c_int32(nl),
-                                 vals.ctypes.data_as(vp), lens.ctypes.data_as(vp), valid.ctypes.data_as(vp),
-                                 rowok.ctypes.data_as(vp), C.c_int(threads))
+        # threaded baseline decode: string leaves come back as the FNV-1a hash of their bytes (see str_hash)
+        is_str = np.array([1 if t == STRING else 0 for t in schema.leaf_types], dtype=np.uint8)
+        rc = lib().dxo_decode_mt_h(buf.ctypes.data_as(vp), starts.ctypes.data_as(vp), ends.ctypes.data_as(vp),
+                                   C.c_int64(n), schema.c_structs, schema.c_fields, C.c_int32(nl),
+                                   vals.ctypes.data_as(vp), lens.ctypes.data_as(vp), valid.ctypes.data_as(vp),
+                                   rowok.ctypes.data_as(vp), C.c_int(threads), is_str.ctypes.data_as(vp))
     else:
         rc = lib().dxo_decode(buf.ctypes.data_as(vp), starts.ctypes.data_as(vp), ends.ctypes.data_as(vp),
                               C.c_int64(n), schema.c_structs, schema.c_fields, C.c_int32(nl),
@@ -158,6 +180,14 @@ def decode(schema: Schema, data: bytes, offsets=None, threads=0):
         else:
             out[name] = (vals[k, :n].copy(), v)
     return out
+
+
+def str_hash(b: bytes) -> int:
+    """FNV-1a 64 of a byte string as a signed int64: the string identity the threaded baseline decoder reports."""
+    h = 0xcbf29ce484222325
+    for c in b:
+        h = ((h ^ c) * 0x100000001b3) & 0xFFFFFFFFFFFFFFFF
+    return h - (1 << 64) if h >= (1 << 63) else h
 
 
 TYPES = [b"DoorLock", b"WindowLock", b"Heating", b"GarageDoorLock"]

@@ -450,7 +450,14 @@ typedef struct {
     const uint8_t *json; const int64_t *offsets; const int64_t *ends; int64_t lo, hi, n;
     const dxo_struct *structs; const dxo_field *fields; int32_t n_leaves;
     int64_t *vals; int32_t *lens; uint8_t *valid; uint8_t *rowok; int64_t rc;
+    const uint8_t *leaf_is_string;   /* optional: string leaves report the FNV-1a hash of their bytes as the value */
 } mt_arg;
+
+static inline int64_t fnv1a64(const uint8_t *p, int64_t n) {
+    uint64_t h = 0xcbf29ce484222325ull;
+    for (int64_t i = 0; i < n; i++) { h ^= p[i]; h *= 0x100000001b3ull; }
+    return (int64_t)h;
+}
 
 static void *mt_worker(void *p) {
     mt_arg *a = (mt_arg *)p;
@@ -473,7 +480,9 @@ static void *mt_worker(void *p) {
         if (r < 0) { a->rc = r; break; }
         a->rowok[i] = (uint8_t)r;
         for (int k = 0; k < a->n_leaves; k++) {
-            a->vals[(int64_t)k * a->n + i] = x.valid[k] ? x.vals[k] : 0;
+            int64_t v = x.valid[k] ? x.vals[k] : 0;
+            if (x.valid[k] && a->leaf_is_string && a->leaf_is_string[k]) v = fnv1a64(heap + x.vals[k], x.lens[k]);
+            a->vals[(int64_t)k * a->n + i] = v;
             a->lens[(int64_t)k * a->n + i] = x.valid[k] ? x.lens[k] : 0;
             a->valid[(int64_t)k * a->n + i] = x.valid[k];
         }
@@ -482,11 +491,23 @@ static void *mt_worker(void *p) {
     return NULL;
 }
 
-/* String leaves come back as (lens only; vals = offset within the record's private heap,
- * meaningless across rows) — the baseline is for timing, parity uses dxo_decode. */
+/* String leaves come back as lens plus, when leaf_is_string marks them, the FNV-1a 64-bit hash of their bytes as the
+ * value (a string identity the baseline's rule evaluation compares with the hashed literal; without the marks the
+ * value is an offset within the record's private heap, meaningless across rows) — the baseline is for timing,
+ * parity uses dxo_decode. */
+int64_t dxo_decode_mt_h(const uint8_t *json, const int64_t *offsets, const int64_t *ends, int64_t n,
+                        const dxo_struct *structs, const dxo_field *fields, int32_t n_leaves,
+                        int64_t *vals, int32_t *lens, uint8_t *valid, uint8_t *rowok, int n_threads,
+                        const uint8_t *leaf_is_string);
 int64_t dxo_decode_mt(const uint8_t *json, const int64_t *offsets, const int64_t *ends, int64_t n,
                       const dxo_struct *structs, const dxo_field *fields, int32_t n_leaves,
                       int64_t *vals, int32_t *lens, uint8_t *valid, uint8_t *rowok, int n_threads) {
+    return dxo_decode_mt_h(json, offsets, ends, n, structs, fields, n_leaves, vals, lens, valid, rowok, n_threads, NULL);
+}
+int64_t dxo_decode_mt_h(const uint8_t *json, const int64_t *offsets, const int64_t *ends, int64_t n,
+                        const dxo_struct *structs, const dxo_field *fields, int32_t n_leaves,
+                        int64_t *vals, int32_t *lens, uint8_t *valid, uint8_t *rowok, int n_threads,
+                        const uint8_t *leaf_is_string) {
     if (n_threads < 1) n_threads = 1;
     if (n_threads > 256) n_threads = 256;
     pthread_t th[256]; mt_arg args[256];
@@ -496,6 +517,7 @@ int64_t dxo_decode_mt(const uint8_t *json, const int64_t *offsets, const int64_t
         a->lo = n * t / n_threads; a->hi = n * (t + 1) / n_threads;
         a->structs = structs; a->fields = fields; a->n_leaves = n_leaves;
         a->vals = vals; a->lens = lens; a->valid = valid; a->rowok = rowok; a->rc = 0;
+        a->leaf_is_string = leaf_is_string;
         pthread_create(&th[t], NULL, mt_worker, a);
     }
     int64_t rc = n;

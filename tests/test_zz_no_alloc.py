@@ -29,12 +29,30 @@ def bind(ctx):
     return fn
 
 
-def decode_both_ways(dx, ctx, dec, fn, data, n_events):
-    """-> None; asserts the caller-owned outputs equal the ordinary entry point's table, byte for byte."""
+def decoder_dictionary(ctx, dec, column):
+    """code -> bytes for a string leaf of a decoder that only ever ran the allocation-free call."""
+    L = ctx.L
+    L.dx_decoder_dict_size.restype, L.dx_decoder_dict_size.argtypes = C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_int64)]
+    L.dx_decoder_dict_string.restype = C.c_int
+    L.dx_decoder_dict_string.argtypes = [C.c_void_p, C.c_int, C.c_int64, C.POINTER(C.c_void_p), C.POINTER(C.c_int64)]
+    n = C.c_int64()
+    ctx.check(L.dx_decoder_dict_size(dec.h, column, C.byref(n)))
+    out = []
+    for code in range(n.value):
+        p, ln = C.c_void_p(), C.c_int64()
+        ctx.check(L.dx_decoder_dict_string(dec.h, column, code, C.byref(p), C.byref(ln)))
+        out.append(C.string_at(p.value, ln.value) if ln.value else b"")
+    return out
+
+
+def decode_both_ways(dx, ctx, ref_dec, dec, fn, data, n_events):
+    """-> None; asserts the caller-owned outputs equal the ordinary entry point's table: numbers and validity bit for bit,
+    strings byte for byte through each decoder's own dictionary.  `dec` never sees the ordinary entry point, so every
+    dictionary entry it holds was inserted by the allocation-free call itself."""
     buf = np.frombuffer(data, dtype=np.uint8)
     src = ctx.alloc(len(data) + 64)
     ctx.h2d(src, buf)
-    ref = dec.decode_device(src, len(data), n_events=n_events)          # existing entry point
+    ref = ref_dec.decode_device(src, len(data), n_events=n_events)      # existing entry point, on its own decoder
     names = ref.columns
     widths = [4 if ref.column_type(i) == 3 else 8 for i in range(len(names))]
     cols = [ctx.alloc(max(1, n_events) * w) for w in widths]             # outputs owned by the caller
@@ -53,11 +71,18 @@ def decode_both_ways(dx, ctx, dec, fn, data, n_events):
         exp = np.zeros(n_events, dtype=got.dtype)
         exp_valid = np.zeros(n_events, dtype=np.uint8)
         ctx.check(ctx.L.dx_table_column_to_host(ref.h, i, exp.ctypes.data_as(C.c_void_p), exp_valid.ctypes.data_as(C.c_void_p)))
-        assert (got == exp).all(), name                                   # bit-exact, including the zeroed NULL slots
         assert (((got_mask >> i) & 1).astype(np.uint8) == exp_valid).all(), name
+        if widths[i] == 4:
+            # the two decoders number their strings independently: compare the text, and the NULL marker (-1) as it is
+            mine, theirs = decoder_dictionary(ctx, dec, i), ref.dictionary(i)
+            ok = exp_valid.astype(bool)
+            assert (got[~ok] == exp[~ok]).all(), name
+            assert [mine[c] for c in got[ok]] == [theirs[c] for c in exp[ok]], name
+        else:
+            assert (got == exp).all(), name                               # bit-exact, including the zeroed NULL slots
     top = 7 if mask_w == 1 else 31
     n_null_rows = int((((got_mask >> top) & 1) == 0).sum())
-    assert nulls.value == n_null_rows == dec.stats()["null_rows"]
+    assert nulls.value == n_null_rows == dec.stats()["null_rows"] == ref_dec.stats()["null_rows"]
     for p in cols + [mask, src]:
         ctx.free(p)
     ref.release()
@@ -65,17 +90,19 @@ def decode_both_ways(dx, ctx, dec, fn, data, n_events):
 
 def test_noalloc_decode_matches_ordinary_entry_point_twice_in_a_row(dx, ctx):
     fn = bind(ctx)
-    dec = dx.Decoder(ctx, SCHEMA2)
+    ref_dec = dx.Decoder(ctx, SCHEMA2)      # only ever runs dx_decoder_decode
+    dec = dx.Decoder(ctx, SCHEMA2)          # only ever runs dx_decoder_decode_noalloc: its dictionary inserts happen there
     # first call: clean generated events spanning many tiles
     p = dxo.GenParams(20260104, 5000, 500, 1_700_000_040_000, 60_000, 60_000, 2, 10, 1, 0)
     n1 = 120_000
-    decode_both_ways(dx, ctx, dec, fn, dxo.gen_events(p, 0, n1), n1)
+    decode_both_ways(dx, ctx, ref_dec, dec, fn, dxo.gen_events(p, 0, n1), n1)
     # second call straight after, smaller and messy: stale counters / tile states from call 1 must not leak in
     recs = all_records(4000, seed=11)
-    decode_both_ways(dx, ctx, dec, fn, to_ndjson(recs), len(recs))
+    decode_both_ways(dx, ctx, ref_dec, dec, fn, to_ndjson(recs), len(recs))
     # and a third, larger again
-    decode_both_ways(dx, ctx, dec, fn, dxo.gen_events(p, n1, 40_000), 40_000)
+    decode_both_ways(dx, ctx, ref_dec, dec, fn, dxo.gen_events(p, n1, 40_000), 40_000)
     dec.close()
+    ref_dec.close()
 
 
 def test_noalloc_decode_rejects_what_it_cannot_hold(dx, ctx):
