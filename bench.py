@@ -314,6 +314,10 @@ def run_ours(args):
         step_no += 1
     ctx.take_launches()
     pipe.wire = 0
+    host_keys = ["project", "route", "stmt:Rules", "stmt:Tumbling", "stmt:Sliding5m"]
+    for k in host_keys:
+        ctx.take_counter("host_us:" + k)
+    t_wall0 = time.perf_counter()
     sampler = ClockSampler(local).start()
     ms = 0.0
     for _ in range(args.steps):
@@ -322,6 +326,8 @@ def run_ours(args):
         step_no += 1
     clocks = sampler.stop()
     launches = ctx.take_launches()
+    host_ms = {k: round(ctx.take_counter("host_us:" + k) / 1e3 / args.steps, 3) for k in host_keys}     # host wall time inside the library per step
+    host_ms["wall_incl_generation"] = round((time.perf_counter() - t_wall0) * 1e3 / args.steps, 3)
     ms = max_over_ranks(ms)
     total_bytes = sum(nb for _, nb in chunks)
     value = world * n_events * args.steps / (ms / 1e3)
@@ -506,7 +512,7 @@ def run_ours(args):
                       "sharding": "events by range per GPU for decode/rules; keyed rows to owner = hash64(deviceId, homeId) %% %d through the %s" % (
                           world, "fused put over NVLink peer memory (all-to-all)" if args.exchange == "put" else "K5 pack + NCCL all-to-all"),
                       "exchange": args.exchange, "wire_bytes_out_per_gpu_per_step": int(wire_per_step)},
-           "roofline": roofline, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "stages": stages, "parity": parity,
+           "roofline": roofline, "host_ms_per_step": host_ms, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "stages": stages, "parity": parity,
            "rule_hits_sample": [int(x) for x in pipe.hits[:4]]}
     if shuffle:
         out["shuffle"] = shuffle

@@ -2,6 +2,7 @@
 #include "dx_aggp.h"
 #include <cub/device/device_scan.cuh>
 #include <chrono>
+#include <cmath>
 static inline long long now_us() { return std::chrono::duration_cast<std::chrono::microseconds>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
 
 #ifndef K3P_SLOTS
@@ -30,16 +31,33 @@ static __device__ __forceinline__ bool p_load(const ProgCol& c, long long row, l
     return true;
 }
 
+// floor(t / d) for d > 0 without the 64-bit integer division routine (~100 instructions): a double-precision estimate, exact
+// after one remainder step for |t| < 2^52 (timestamps in microseconds are < 2^51); wider values take the integer division.
+static __device__ __forceinline__ long long p_floor_div(long long t, long long d, double inv) {
+    if (t > -(1ll << 52) && t < (1ll << 52)) {
+        long long q = (long long)floor((double)t * inv);
+        const long long r = t - q * d;
+        if (r < 0) q--; else if (r >= d) q++;
+        return q;
+    }
+    return t >= 0 ? t / d : -((-t + d - 1) / d);
+}
+
 // ---- phase 1: rows -> records [hash][keys nk][pane][bits][vals nv], grouped by partition = top bits of the key hash ----
 // bits: low 16 = key-null bits, bit 16+v = value v present.  pass 0 counts, pass 1 writes.
+// pass 0 counts, pass 1 writes at bases[p] + cursor (the exact two-pass form); pass 2 is the single pass: every partition
+// owns a fixed slice of `stride` records (sized from the row count with headroom, see dx_aggp_build), the cursor alone places
+// the record, and a partition that outgrows its slice raises *overflow (the host then falls back to the two-pass form).
 __global__ void __launch_bounds__(256) k3p_scatter(const __grid_constant__ AggInput in, int nk, int nv, int pbits, int pass,
-                                                   unsigned int* counts, const unsigned int* bases, unsigned int* cursors, unsigned long long* recs) {
+                                                   unsigned int* counts, const unsigned int* bases, unsigned int* cursors, unsigned long long* recs,
+                                                   unsigned int stride, unsigned long long* overflow) {
     const int rw = nk + nv + 3;
+    const double inv_pane = 1.0 / (double)in.pane_us;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < in.n_rows; i += (long long)gridDim.x * blockDim.x) {
         const long long row = in.sel ? in.sel[i] : i;
         long long t;
         if (!p_load(in.range_col, row, t)) continue;                  // no timestamp: in no window
-        const long long pane = t >= 0 ? t / in.pane_us : -((-t + in.pane_us - 1) / in.pane_us);
+        const long long pane = p_floor_div(t, in.pane_us, inv_pane);
         long long kv[DX_AGG_MAX_KEYS];
         unsigned long long bits = 0, h = 0x2545F4914F6CDD1Dull;
         for (int k = 0; k < nk; k++) {
@@ -50,7 +68,12 @@ __global__ void __launch_bounds__(256) k3p_scatter(const __grid_constant__ AggIn
         h = pmix64(h ^ bits);
         const unsigned int p = pbits ? (unsigned int)(h >> (64 - pbits)) : 0u;
         if (pass == 0) { atomicAdd(&counts[p], 1u); continue; }
-        const unsigned int pos = bases[p] + atomicAdd(&cursors[p], 1u);
+        unsigned int pos;
+        if (pass == 2) {
+            const unsigned int at = atomicAdd(&cursors[p], 1u);
+            if (at >= stride) { *overflow = 1ull; continue; }
+            pos = p * stride + at;
+        } else pos = bases[p] + atomicAdd(&cursors[p], 1u);
         unsigned long long* r = recs + (size_t)pos * rw;
         r[0] = h;
         for (int k = 0; k < nk; k++) r[1 + k] = (unsigned long long)kv[k];
@@ -63,8 +86,111 @@ __global__ void __launch_bounds__(256) k3p_scatter(const __grid_constant__ AggIn
     }
 }
 
+// ---- phase 1, staged form (the one that normally runs): up to 4 group keys and 4 value columns -------------------------
+// A record written by the thread that built it is six (rw) 8-byte stores to a line no neighbouring lane touches: the
+// load/store unit sees 32 separate sectors per store instruction and the kernel crawls at ~8 G rows/s, every warp waiting
+// on it (ncu: long scoreboard 99.8, lg throttle 25).  Here a CTA takes tiles of SC_TILE rows; every thread builds its rows'
+// records into a shared-memory staging area (row-major) and claims their slots with independent atomics, and after a barrier
+// the whole CTA copies the staged words out, consecutive lanes writing consecutive words of the same record: a store
+// instruction then covers ~5 records (5-6 sectors) instead of 32, with 16-byte stores when the record length allows.
+#define SC_NT 256
+#define SC_RPT 4
+#define SC_TILE (SC_NT * SC_RPT)
+#define SC_MAXK 4
+#define SC_MAXV 4
+static __device__ __forceinline__ bool p_load_u(const ProgCol& c, long long row, long long& v) {
+    // branch-free on the hot path: mask and value loads are independent of each other
+    uint32_t m = 0xFFFFFFFFu;
+    if (c.vmask) m = c.vwidth == 1 ? (uint32_t)__ldg(reinterpret_cast<const uint8_t*>(c.vmask) + row) : __ldg(reinterpret_cast<const uint32_t*>(c.vmask) + row);
+    long long x = c.width == 4 ? (long long)__ldg(reinterpret_cast<const int32_t*>(c.data) + row) : __ldg(reinterpret_cast<const long long*>(c.data) + row);
+    const bool ok = (m >> c.vbit) & 1u;
+    v = ok ? x : 0;
+    return ok;
+}
+__global__ void __launch_bounds__(SC_NT) k3p_scatter_staged(const __grid_constant__ AggInput in, int nk, int nv, int pbits, int pass,
+                                                            unsigned int* counts, const unsigned int* bases, unsigned int* cursors,
+                                                            unsigned long long* recs, unsigned int stride, unsigned long long* overflow) {
+    extern __shared__ __align__(16) unsigned long long s_stage[];      // SC_TILE x rw words, then SC_TILE positions (uint32)
+    const int rw = nk + nv + 3, tid = threadIdx.x;
+    unsigned int* s_pos = reinterpret_cast<unsigned int*>(s_stage + (size_t)SC_TILE * rw);
+    const double inv_pane = 1.0 / (double)in.pane_us;
+    const long long n_tiles = (in.n_rows + SC_TILE - 1) / SC_TILE;
+    for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        unsigned int part[SC_RPT]; bool live[SC_RPT];
+#pragma unroll
+        for (int j = 0; j < SC_RPT; j++) {
+            const long long i = tile * SC_TILE + (long long)j * SC_NT + tid;
+            live[j] = false; part[j] = 0;
+            if (i >= in.n_rows) continue;
+            const long long row = in.sel ? in.sel[i] : i;
+            long long t;
+            const bool has_t = p_load_u(in.range_col, row, t);
+            long long kv[SC_MAXK], xv[SC_MAXV];
+            unsigned long long bits = 0, h = 0x2545F4914F6CDD1Dull;
+#pragma unroll
+            for (int k = 0; k < SC_MAXK; k++) if (k < nk) { if (!p_load_u(in.keys[k], row, kv[k])) bits |= 1ull << k; }
+#pragma unroll
+            for (int v = 0; v < SC_MAXV; v++) if (v < nv) { if (p_load_u(in.vals[v], row, xv[v])) bits |= 1ull << (16 + v); }
+            if (!has_t) continue;                                      // no timestamp: in no window
+#pragma unroll
+            for (int k = 0; k < SC_MAXK; k++) if (k < nk) h = pmix64(h ^ (unsigned long long)kv[k]);
+            h = pmix64(h ^ (bits & 0xFFFFull));
+            const long long pane = p_floor_div(t, in.pane_us, inv_pane);
+            part[j] = pbits ? (unsigned int)(h >> (64 - pbits)) : 0u;
+            live[j] = true;
+            if (pass == 0) continue;
+            unsigned long long* r = s_stage + (size_t)(j * SC_NT + tid) * rw;
+            r[0] = h;
+#pragma unroll
+            for (int k = 0; k < SC_MAXK; k++) if (k < nk) r[1 + k] = (unsigned long long)kv[k];
+            r[1 + nk] = (unsigned long long)pane;
+            r[2 + nk] = bits;
+#pragma unroll
+            for (int v = 0; v < SC_MAXV; v++) if (v < nv) r[3 + nk + v] = (unsigned long long)xv[v];
+        }
+        if (pass == 0) {
+#pragma unroll
+            for (int j = 0; j < SC_RPT; j++) if (live[j]) atomicAdd(&counts[part[j]], 1u);
+            continue;
+        }
+        // slots: SC_RPT independent atomics in flight per thread
+        unsigned int at[SC_RPT];
+#pragma unroll
+        for (int j = 0; j < SC_RPT; j++) at[j] = live[j] ? atomicAdd(&cursors[part[j]], 1u) : 0u;
+#pragma unroll
+        for (int j = 0; j < SC_RPT; j++) {
+            unsigned int pos = 0xFFFFFFFFu;
+            if (live[j]) {
+                if (pass == 2) { if (at[j] >= stride) *overflow = 1ull; else pos = part[j] * stride + at[j]; }
+                else pos = bases[part[j]] + at[j];
+            }
+            s_pos[j * SC_NT + tid] = pos;
+        }
+        __syncthreads();
+        if ((rw & 1) == 0) {
+            const int rq = rw >> 1;                                    // 16-byte chunks per record
+            const uint4* src = reinterpret_cast<const uint4*>(s_stage);
+            uint4* dst = reinterpret_cast<uint4*>(recs);
+            for (unsigned int f = tid; f < (unsigned int)(SC_TILE * rq); f += SC_NT) {
+                const unsigned int rec = f / (unsigned int)rq, w = f - rec * (unsigned int)rq;
+                const unsigned int pos = s_pos[rec];
+                if (pos != 0xFFFFFFFFu) dst[(size_t)pos * rq + w] = src[f];
+            }
+        } else {
+            for (unsigned int f = tid; f < (unsigned int)(SC_TILE * rw); f += SC_NT) {
+                const unsigned int rec = f / (unsigned int)rw, w = f - rec * (unsigned int)rw;
+                const unsigned int pos = s_pos[rec];
+                if (pos != 0xFFFFFFFFu) recs[(size_t)pos * rw + w] = s_stage[f];
+            }
+        }
+        __syncthreads();
+    }
+}
+static size_t sc_smem(int rw) { return (size_t)SC_TILE * rw * 8 + (size_t)SC_TILE * 4; }
+
 // ---- phase 2: one CTA per partition, shared-memory hash table --------------------------------------------------
-struct P2Seg { const unsigned long long* recs; const unsigned int* part_base; const unsigned int* part_cnt; };
+// part_base == nullptr: partition p is the fixed slice [p * stride, p * stride + min(part_cnt[p], stride))
+struct P2Seg { const unsigned long long* recs; const unsigned int* part_base; const unsigned int* part_cnt; unsigned long long stride; };
 struct P2Args {
     const P2Seg* segs; int n_seg;
     int rw;                 // words per input record
@@ -78,6 +204,24 @@ struct P2Args {
     unsigned int* out_base; unsigned int* out_cnt; unsigned long long* counters;   // [0] groups written, [1] overflow, [2] output too small
     unsigned long long out_cap;                       // groups the output holds
 };
+
+// 64-bit shared-memory atomics have no native form on sm_100 (add, min, max and double add all compile to LDS + CAS loops,
+// SASS ATOMS.CAST.SPIN.64).  Integer sums therefore go through two native 32-bit adds with an exact carry (the wraps of the
+// low word are counted one by one, whatever order the adds land in), counts through one, and MIN / MAX look before they
+// swap: after a group's first few rows almost no row changes its extremes.
+static __device__ __forceinline__ void s_add64(unsigned long long* p, unsigned long long v) {
+    unsigned int* w = reinterpret_cast<unsigned int*>(p);
+    const unsigned int lo = (unsigned int)v, hi = (unsigned int)(v >> 32);
+    unsigned int carry = 0;
+    if (lo) { const unsigned int old = atomicAdd(&w[0], lo); carry = (old + lo < old) ? 1u : 0u; }
+    if (hi + carry) atomicAdd(&w[1], hi + carry);
+}
+static __device__ __forceinline__ void s_min64(unsigned long long* p, long long v) {
+    if (v < *reinterpret_cast<volatile long long*>(p)) atomicMin(reinterpret_cast<long long*>(p), v);
+}
+static __device__ __forceinline__ void s_max64(unsigned long long* p, long long v) {
+    if (v > *reinterpret_cast<volatile long long*>(p)) atomicMax(reinterpret_cast<long long*>(p), v);
+}
 
 __global__ void __launch_bounds__(K3P_NT) k3p_aggregate(const __grid_constant__ P2Args A) {
     extern __shared__ __align__(16) unsigned long long tab[];      // K3P_SLOTS x sw: [tag][hash][keys nkk][bits][accs na]
@@ -100,7 +244,8 @@ __global__ void __launch_bounds__(K3P_NT) k3p_aggregate(const __grid_constant__ 
         if (tid < ns) {
             const P2Seg sg = A.segs[s0 + tid];
             mycnt = sg.part_cnt[p];
-            s_ptr[tid] = sg.recs + (size_t)sg.part_base[p] * A.rw;
+            if (sg.part_base) s_ptr[tid] = sg.recs + (size_t)sg.part_base[p] * A.rw;
+            else { if (mycnt > sg.stride) mycnt = (unsigned int)sg.stride; s_ptr[tid] = sg.recs + (size_t)p * sg.stride * A.rw; }
         }
         {   // exclusive prefix of the counts over the CTA
             unsigned int incl = mycnt;
@@ -114,6 +259,7 @@ __global__ void __launch_bounds__(K3P_NT) k3p_aggregate(const __grid_constant__ 
             __syncthreads();
         }
         const unsigned int total_recs = s_pref[ns];
+        if (tid == 0 && A.pane_in_key) atomicMax(&A.counters[4], (unsigned long long)total_recs);     // build: the fullest partition sizes the next batch's slices
         int seg = 0;
         // every thread makes the same number of trips, so the warp can be re-joined (__syncwarp) between the divergent slot
         // search and the accumulator updates: without it the updates run with a handful of active lanes
@@ -170,18 +316,18 @@ __global__ void __launch_bounds__(K3P_NT) k3p_aggregate(const __grid_constant__ 
             unsigned long long* acc = slot + 3 + A.nkk;
             for (int a = 0; a < A.na; a++) {
                 const int kind = A.accs[a].kind;
-                if (kind == ACC_COUNT_STAR) { atomicAdd(&acc[a], 1ull); continue; }
+                if (kind == ACC_COUNT_STAR) { s_add64(&acc[a], 1ull); continue; }
                 const int c = A.accs[a].col;
                 if (A.check_valid && !((bits >> (16 + c)) & 1ull)) continue;
                 const long long v = (long long)r[A.val0 + c];
                 switch (kind) {
-                case ACC_COUNT: atomicAdd(&acc[a], 1ull); break;
-                case ACC_SUM_I: atomicAdd(&acc[a], (unsigned long long)v); break;
+                case ACC_COUNT: s_add64(&acc[a], 1ull); break;
+                case ACC_SUM_I: s_add64(&acc[a], (unsigned long long)v); break;
                 case ACC_SUM_F: atomicAdd(reinterpret_cast<double*>(&acc[a]), __longlong_as_double(v)); break;
-                case ACC_MIN_I: atomicMin(reinterpret_cast<long long*>(&acc[a]), v); break;
-                case ACC_MAX_I: atomicMax(reinterpret_cast<long long*>(&acc[a]), v); break;
-                case ACC_MIN_F: atomicMin(reinterpret_cast<long long*>(&acc[a]), p_f64_order(v)); break;
-                case ACC_MAX_F: atomicMax(reinterpret_cast<long long*>(&acc[a]), p_f64_order(v)); break;
+                case ACC_MIN_I: s_min64(&acc[a], v); break;
+                case ACC_MAX_I: s_max64(&acc[a], v); break;
+                case ACC_MIN_F: s_min64(&acc[a], p_f64_order(v)); break;
+                case ACC_MAX_F: s_max64(&acc[a], p_f64_order(v)); break;
                 }
             }
         }
@@ -246,7 +392,8 @@ static int p2_launch(dx_ctx* ctx, const P2Args& A, int P) {
 
 bool dx_aggp_fits(int nk, int na) { return p2_smem(1 + (nk + 1) + 1 + na) <= 200 * 1024 && nk + 1 <= 15 && na <= DX_AGG_MAX_ACCS; }
 
-int dx_aggp_build(dx_ctx* ctx, const AggInput& in_, int nk, int nv, const std::vector<AggAccDesc>& accs, int P, AggPPartial* out, bool* overflow) {
+int dx_aggp_build(dx_ctx* ctx, const AggInput& in_, int nk, int nv, const std::vector<AggAccDesc>& accs, int P, AggPPartial* out, bool* overflow,
+                  long long* stride_hint, long long* hint_rows, bool force_two_pass) {
     *overflow = false;
     const long long t_b0 = now_us();
     out->n = 0; out->P = P; out->gw = 1 + (nk + 1) + 1 + (int)accs.size();
@@ -268,28 +415,52 @@ int dx_aggp_build(dx_ctx* ctx, const AggInput& in_, int nk, int nv, const std::v
     }
     long long blocks = (in.n_rows + 255) / 256, capb = (long long)ctx->sm_count * 8; if (blocks > capb) blocks = capb;
     ctx->counters["k3_rows"] += in.n_rows;
-    {
-        StageTimer tm(ctx, "k3p_scatter");
-        k3p_scatter<<<(unsigned)blocks, 256, 0, ctx->stream>>>(in, nk, nv, pbits, 0, counts.as<unsigned int>(), nullptr, nullptr, nullptr);
-        ctx->launches["k3p_scatter"]++;
+    const bool staged = nk <= SC_MAXK && nv <= SC_MAXV;
+    const size_t sc_bytes = sc_smem(rw);
+    long long sblocks = (in.n_rows + SC_TILE - 1) / SC_TILE;
+    if (staged) {
+        if (sc_bytes > ctx->k3p_scatter_smem_configured) {
+            DX_CUDA(ctx, cudaFuncSetAttribute(k3p_scatter_staged, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sc_bytes));
+            ctx->k3p_scatter_smem_configured = sc_bytes;
+        }
+        int occ = 1;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k3p_scatter_staged, SC_NT, sc_bytes);
+        if (occ < 1) occ = 1;
+        const long long scap = (long long)ctx->sm_count * occ; if (sblocks > scap) sblocks = scap;
     }
-    size_t tmp_bytes = 0;
-    cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, counts.as<unsigned int>(), bases.as<unsigned int>(), P, ctx->stream);
-    DevBuf tmp(ctx, tmp_bytes + 16);
-    DX_CUDA(ctx, cub::DeviceScan::ExclusiveSum(tmp.p, tmp_bytes, counts.as<unsigned int>(), bases.as<unsigned int>(), P, ctx->stream));
-    // every row with a timestamp becomes one record: at most n_rows of them
-    DevBuf recs(ctx, (size_t)in.n_rows * rw * 8 + 64);
-    if (!recs.p) return ctx->set_error(DX_ERR_CUDA, "pane partial allocation failed");
-    {
+    auto scatter = [&](int pass, unsigned int* cnt, const unsigned int* bas, unsigned int* cur, unsigned long long* rec, unsigned int strd, unsigned long long* ovf) {
         StageTimer tm(ctx, "k3p_scatter");
-        k3p_scatter<<<(unsigned)blocks, 256, 0, ctx->stream>>>(in, nk, nv, pbits, 1, nullptr, bases.as<unsigned int>(), cursors.as<unsigned int>(), recs.as<unsigned long long>());
+        if (staged) k3p_scatter_staged<<<(unsigned)sblocks, SC_NT, sc_bytes, ctx->stream>>>(in, nk, nv, pbits, pass, cnt, bas, cur, rec, strd, ovf);
+        else k3p_scatter<<<(unsigned)blocks, 256, 0, ctx->stream>>>(in, nk, nv, pbits, pass, cnt, bas, cur, rec, strd, ovf);
         ctx->launches["k3p_scatter"]++;
+    };
+    // Single pass when possible: every partition gets a fixed slice of records and the cursor alone places a record — no
+    // counting pass, no scan.  A partition that outgrows its slice (keys skewed since the last batch) raises a flag that comes
+    // back with the aggregation counters below, and the exact two-pass form runs instead.
+    // (rows of one key land in one partition, so the spread is wider than a binomial's: the slice is sized from the fullest
+    // partition the previous batch of this statement produced, with 25 % headroom; the first batch runs the two-pass form)
+    const unsigned long long stride = stride_hint ? (unsigned long long)((double)*stride_hint * ((double)in.n_rows / (double)std::max<long long>(1, hint_rows ? *hint_rows : in.n_rows)) * 1.25 + 64.0) : 0ull;
+    bool single_pass = !force_two_pass && stride_hint && *stride_hint > 0 && stride * (unsigned long long)P < (1ull << 32) &&
+                       stride * (unsigned long long)P <= (unsigned long long)in.n_rows * 4 + 128ull * P;
+    DevBuf recs;
+    if (single_pass) {
+        recs = DevBuf(ctx, (size_t)stride * P * rw * 8 + 64);
+        if (!recs.p) return ctx->set_error(DX_ERR_CUDA, "pane partial allocation failed");
+        scatter(2, nullptr, nullptr, cursors.as<unsigned int>(), recs.as<unsigned long long>(), (unsigned int)stride, ctr.as<unsigned long long>() + 3);
+    } else {
+        scatter(0, counts.as<unsigned int>(), nullptr, nullptr, nullptr, 0u, nullptr);
+        size_t tmp_bytes = 0;
+        cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, counts.as<unsigned int>(), bases.as<unsigned int>(), P, ctx->stream);
+        DevBuf tmp(ctx, tmp_bytes + 16);
+        DX_CUDA(ctx, cub::DeviceScan::ExclusiveSum(tmp.p, tmp_bytes, counts.as<unsigned int>(), bases.as<unsigned int>(), P, ctx->stream));
+        // every row with a timestamp becomes one record: at most n_rows of them
+        recs = DevBuf(ctx, (size_t)in.n_rows * rw * 8 + 64);
+        if (!recs.p) return ctx->set_error(DX_ERR_CUDA, "pane partial allocation failed");
+        scatter(1, nullptr, bases.as<unsigned int>(), cursors.as<unsigned int>(), recs.as<unsigned long long>(), 0u, nullptr);
     }
     DX_CUDA(ctx, cudaGetLastError());
-    DX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    ctx->counters["host_us:k3p_build_scatter"] += now_us() - t_b0;
     // aggregate each partition by (keys, pane)
-    P2Seg hseg{recs.as<unsigned long long>(), bases.as<unsigned int>(), counts.as<unsigned int>()};
+    P2Seg hseg{recs.as<unsigned long long>(), single_pass ? nullptr : bases.as<unsigned int>(), single_pass ? cursors.as<unsigned int>() : counts.as<unsigned int>(), stride};
     DevBuf dseg(ctx, sizeof(P2Seg));
     DX_CUDA(ctx, cudaMemcpyAsync(dseg.p, &hseg, sizeof hseg, cudaMemcpyHostToDevice, ctx->stream));
     // groups <= records; the output is sized by P * K3P_MAX_GROUPS or the row count, whichever is smaller
@@ -304,10 +475,15 @@ int dx_aggp_build(dx_ctx* ctx, const AggInput& in_, int nk, int nv, const std::v
     A.out = groups->as<unsigned long long>(); A.gw = out->gw; A.out_cap = (unsigned long long)max_groups;
     A.out_base = out->part_base->as<unsigned int>(); A.out_cnt = out->part_cnt->as<unsigned int>(); A.counters = ctr.as<unsigned long long>();
     int rc = p2_launch(ctx, A, P); if (rc) return rc;
-    unsigned long long h[3] = {0, 0, 0};
-    DX_CUDA(ctx, cudaMemcpyAsync(h, ctr.p, 24, cudaMemcpyDeviceToHost, ctx->stream));
+    unsigned long long h[5] = {0, 0, 0, 0, 0};
+    DX_CUDA(ctx, cudaMemcpyAsync(h, ctr.p, 40, cudaMemcpyDeviceToHost, ctx->stream));
     DX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     ctx->counters["host_us:k3p_build_total_to_agg"] += now_us() - t_b0;
+    if (h[3]) {      // a partition outgrew its fixed slice (skewed keys): the exact two-pass scatter
+        ctx->counters["k3p_two_pass_fallbacks"]++;
+        return dx_aggp_build(ctx, in_, nk, nv, accs, P, out, overflow, stride_hint, hint_rows, true);
+    }
+    if (stride_hint) { *stride_hint = (long long)h[4]; if (hint_rows) *hint_rows = in.n_rows; }      // fullest partition of this batch
     if (h[1] || h[2]) { *overflow = true; return DX_OK; }
     out->n = (int64_t)h[0];
     // keep only what the groups need (the worst-case buffer can be far larger than the partial)
@@ -322,7 +498,7 @@ int dx_aggp_build(dx_ctx* ctx, const AggInput& in_, int nk, int nv, const std::v
     return DX_OK;
 }
 
-int dx_aggp_combine(dx_ctx* ctx, const std::vector<const AggPPartial*>& parts, int nk, const std::vector<AggAccDesc>& accs,
+int dx_aggp_combine(dx_ctx* ctx, const std::vector<const AggPPartial*>& parts, int nk, const std::vector<AggAccDesc>& accs, const std::vector<int>& src_acc,
                     long long pane_lo, long long pane_hi, long long max_groups, long long* const* key_out,
                     unsigned long long* keynull_out, unsigned long long* const* acc_out, long long* n_groups, bool* overflow) {
     *overflow = false; *n_groups = 0;
@@ -331,7 +507,7 @@ int dx_aggp_combine(dx_ctx* ctx, const std::vector<const AggPPartial*>& parts, i
     std::vector<P2Seg> hsegs;
     for (auto* pp : parts) {
         if (pp->P != P || pp->gw != gw_in) return ctx->set_error(DX_ERR_STATE, "pane partials of different shapes cannot be combined");
-        if (pp->n > 0) hsegs.push_back(P2Seg{pp->recs->as<unsigned long long>(), pp->part_base->as<unsigned int>(), pp->part_cnt->as<unsigned int>()});
+        if (pp->n > 0) hsegs.push_back(P2Seg{pp->recs->as<unsigned long long>(), pp->part_base->as<unsigned int>(), pp->part_cnt->as<unsigned int>(), 0ull});
     }
     if (hsegs.empty()) return DX_OK;
     const int gw_out = 1 + nk + 1 + na;
@@ -348,7 +524,7 @@ int dx_aggp_combine(dx_ctx* ctx, const std::vector<const AggPPartial*>& parts, i
     A.na = na;
     for (int a = 0; a < na; a++) {      // COUNTs become sums of the partial counts; everything else keeps its operator
         A.accs[a].kind = (accs[a].kind == ACC_COUNT_STAR || accs[a].kind == ACC_COUNT) ? ACC_SUM_I : accs[a].kind;
-        A.accs[a].col = a;
+        A.accs[a].col = src_acc[a];          // where this accumulator sits among the partial's (the partial may carry more)
     }
     A.check_valid = 0;
     A.out = groups.as<unsigned long long>(); A.gw = gw_out; A.out_cap = (unsigned long long)cap;

@@ -23,11 +23,15 @@ bool dx_aggp_fits(int nk, int na);
 // the group keys (in.keys[0..nk)), the pane key computed from in.range_col / in.pane_us, and the value columns of one
 // cached batch -> partition-ordered partial.  *overflow: a partition held more groups than the shared table takes
 // (the caller retries with more partitions).
-int dx_aggp_build(dx_ctx* ctx, const AggInput& in, int nk, int nv, const std::vector<AggAccDesc>& accs, int P, AggPPartial* out, bool* overflow);
+int dx_aggp_build(dx_ctx* ctx, const AggInput& in, int nk, int nv, const std::vector<AggAccDesc>& accs, int P, AggPPartial* out, bool* overflow,
+                  long long* stride_hint = nullptr, long long* hint_rows = nullptr, bool force_two_pass = false);
+// stride_hint / hint_rows (in/out, per statement signature): records of the fullest partition and the row count of the
+// previous build; with them the scatter runs as one pass into fixed partition slices.
 
 // partials of one signature (same nk / accumulators / P), panes in [pane_lo, pane_hi) -> groups as column arrays
 // (key_out[k][g], keynull_out[g] with bit k set = NULL, acc_out[a][g] raw 64-bit, as AggTable::extract writes them).
+// src_acc[a]: index of accumulator a among the partials' accumulators (partials shared between statements may carry more).
 // The arrays must hold max_groups entries; *n_groups is the number written.
-int dx_aggp_combine(dx_ctx* ctx, const std::vector<const AggPPartial*>& parts, int nk, const std::vector<AggAccDesc>& accs,
+int dx_aggp_combine(dx_ctx* ctx, const std::vector<const AggPPartial*>& parts, int nk, const std::vector<AggAccDesc>& accs, const std::vector<int>& src_acc,
                     long long pane_lo, long long pane_hi, long long max_groups, long long* const* key_out,
                     unsigned long long* keynull_out, unsigned long long* const* acc_out, long long* n_groups, bool* overflow);

@@ -58,6 +58,7 @@ struct dx_ctx {
     std::map<std::string, std::vector<float>> stage_ms;
     std::map<std::string, long long> launches;
     std::map<std::string, long long> counters;     // work counters (rows visited by K3, rows moved by K4 ...)
+    size_t k3p_scatter_smem_configured = 0;
     size_t k3p_smem_configured = 0;                 // dynamic shared memory k3p_aggregate is configured for on this device
     int set_error(int code, const std::string& msg) { last_error = msg; return code; }
 };

@@ -1245,6 +1245,7 @@ struct Exec {
         std::vector<int> key_type(keys.size(), DX_T_I64); std::vector<DxDictP> key_dict(keys.size());
         // One chunk's columns as the aggregation kernel's input; `hold` keeps computed columns alive until the kernel has run.
         struct InputHold { std::vector<DevBufP> temps; DevBufP tmask; std::vector<DxColumn> string_keys; };
+        const std::vector<ExprP>* input_vals = &val_exprs;     // which value columns make_input lays out (a shared pane partial may carry more)
         auto make_input = [&](const DxTable* ch, const long long* sel, int64_t n, bool with_range, AggInput* inp, InputHold* hold) -> int {
             AggInput& in = *inp; memset(&in, 0, sizeof in);
             BindScope sc = scope_for(ch, core);
@@ -1294,13 +1295,14 @@ struct Exec {
                     key_dict[hashed[hk]] = full.dict;
                 } else { int ty; rc = eval_temp(ks.expr, &ty, &in.keys[hk]); if (rc) return rc; key_type[hashed[hk]] = ty; }
             }
-            for (size_t vi = 0; vi < val_exprs.size(); vi++) {
+            const std::vector<ExprP>& ivals = *input_vals;
+            for (size_t vi = 0; vi < ivals.size(); vi++) {
                 bool done = false;
-                if (val_exprs[vi]->kind == EK::Col) {
-                    std::string err; int ci = dx_resolve_column(sc, val_exprs[vi]->parts, &err);
+                if (ivals[vi]->kind == EK::Col) {
+                    std::string err; int ci = dx_resolve_column(sc, ivals[vi]->parts, &err);
                     if (ci >= 0 && ch->cols[ci].data && !ch->cols[ci].all_null) { in.vals[vi] = col_desc(ch->cols[ci]); done = true; }
                 }
-                if (!done) { int ty; rc = eval_temp(val_exprs[vi], &ty, &in.vals[vi]); if (rc) return rc; }
+                if (!done) { int ty; rc = eval_temp(ivals[vi], &ty, &in.vals[vi]); if (rc) return rc; }
             }
             return DX_OK;
         };
@@ -1316,10 +1318,35 @@ struct Exec {
         std::vector<DevBufP> pre_k, pre_a; DevBufP pre_knull; bool have_cols = false;
         const bool pane_smem = pane_mode && !F->pane_smem_off && dx_aggp_fits((int)hashed.size(), (int)accs.size());
         if (pane_smem) {
-            std::string sig = "P|" + std::to_string(pane_us) + "|" + v.ts_col;
-            for (int hk : hashed) sig += "|k:" + to_string(keys[hk].expr);
-            for (auto& ve : val_exprs) sig += "|v:" + to_string(ve);
-            for (auto& ac : accs) sig += "|a:" + std::to_string(ac.kind) + "," + std::to_string(ac.col);
+            // Partials are shared between statements: a statement takes any partial family member ("variant") of the same
+            // window source, pane width and group keys whose accumulators cover its own (Tumbling's COUNT/SUM/MIN/MAX partial
+            // also answers a 5-minute COUNT/SUM), so a cached batch is scattered and pre-aggregated once, not once per statement.
+            std::string fam = "P|" + std::to_string(pane_us) + "|" + v.ts_col;
+            for (int hk : hashed) fam += "|k:" + to_string(keys[hk].expr);
+            std::vector<std::string> need(accs.size());
+            for (size_t a = 0; a < accs.size(); a++) need[a] = std::to_string(accs[a].kind) + ":" + (accs[a].col >= 0 ? to_string(val_exprs[accs[a].col]) : std::string("*"));
+            auto& variants = F->pane_variants[fam];
+            auto covers = [](const std::vector<std::string>& have, const std::vector<std::string>& want) {
+                for (auto& w : want) if (std::find(have.begin(), have.end(), w) == have.end()) return false;
+                return true;
+            };
+            int vi = -1;
+            for (size_t q = 0; q < variants.size(); q++)
+                if (covers(variants[q].desc, need) && (vi < 0 || variants[q].desc.size() < variants[vi].desc.size())) vi = (int)q;
+            if (vi < 0) {
+                // a variant the new one covers is superseded: its statements find the wider one from their next batch on
+                for (size_t q = 0; q < variants.size();) {
+                    if (covers(need, variants[q].desc)) { F->pane_partials_p.erase(variants[q].sig); F->pane_P.erase(variants[q].sig); variants.erase(variants.begin() + q); }
+                    else q++;
+                }
+                dx_flow::PaneVariant nv2; nv2.vals = val_exprs; nv2.accs = accs; nv2.desc = need;
+                nv2.sig = fam + "|#" + std::to_string(F->pane_variant_seq++);
+                variants.push_back(nv2); vi = (int)variants.size() - 1;
+            }
+            const dx_flow::PaneVariant var = variants[vi];       // by value: the vector may be edited by a later statement
+            std::vector<int> amap(accs.size());
+            for (size_t a = 0; a < accs.size(); a++) amap[a] = (int)(std::find(var.desc.begin(), var.desc.end(), need[a]) - var.desc.begin());
+            const std::string sig = var.sig;
             auto& cache = F->pane_partials_p[sig];
             const int nk = (int)hashed.size();
             for (auto it2 = cache.begin(); it2 != cache.end();) {
@@ -1347,13 +1374,17 @@ struct Exec {
                         continue;
                     }
                     InputHold hold; AggInput in;
-                    int rc = make_input(chp.get(), nullptr, chp->n_rows, true, &in, &hold); if (rc) return rc;
+                    input_vals = &var.vals;            // the partial carries the variant's value columns, not only this statement's
+                    int rc = make_input(chp.get(), nullptr, chp->n_rows, true, &in, &hold);
+                    input_vals = &val_exprs;
+                    if (rc) return rc;
                     if (P == 0 && F->pane_partitions_first > 0) P = F->pane_partitions_first;      // tests start too coarse on purpose
                     if (P == 0) { P = 256; while (P < 16384 && (long long)P * 1200 < chp->n_rows) P <<= 1; }
                     in.has_range = 0; in.pane_us = pane_us;
                     PanePartialP pp; pp.chunk = chp;
                     bool ovf = false;
-                    rc = dx_aggp_build(ctx, in, nk, (int)val_exprs.size(), accs, P, &pp.ap, &ovf); if (rc) return rc;
+                    auto& fill = F->pane_fill[sig];
+                    rc = dx_aggp_build(ctx, in, nk, (int)var.vals.size(), var.accs, P, &pp.ap, &ovf, &fill.first, &fill.second); if (rc) return rc;
                     if (ovf) { again = true; break; }
                     ctx->counters["k3_partial_rows_built"] += (long long)pp.ap.n;
                     cache[chp.get()] = std::move(pp);
@@ -1372,7 +1403,7 @@ struct Exec {
                         for (size_t a2 = 0; a2 < accs.size(); a2++) { pre_a[a2] = make_buf(ctx, nr * 8); ap2[a2] = pre_a[a2]->as<unsigned long long>(); }
                         pre_knull = make_buf(ctx, nr * 8);
                         long long ng = 0; bool ovf = false;
-                        int rc = dx_aggp_combine(ctx, parts, nk, accs, v.lo_us / pane_us, v.hi_us / pane_us, maxg, kp, pre_knull->as<unsigned long long>(), ap2, &ng, &ovf);
+                        int rc = dx_aggp_combine(ctx, parts, nk, accs, amap, v.lo_us / pane_us, v.hi_us / pane_us, maxg, kp, pre_knull->as<unsigned long long>(), ap2, &ng, &ovf);
                         if (rc) return rc;
                         if (!ovf) { n_groups = (unsigned long long)ng; have_cols = true; break; }
                         if (maxg < rows) { ctx->counters["k3p_output_regrows"]++; maxg = rows; continue; }     // the remembered size was too small: the row count always suffices
@@ -1382,7 +1413,7 @@ struct Exec {
                 ctx->counters["k3p_partitions"] = P;
                 if (!again) break;
                 ctx->counters["k3p_repartitions"]++;
-                P = std::min(P * 4, 1 << 16); cache.clear();             // finer partitions; every partial of this signature is rebuilt
+                P = std::min(P * 4, 1 << 16); cache.clear(); F->pane_fill.erase(sig);   // finer partitions; every partial of this signature is rebuilt
                 if (P >= (1 << 16) && round > 3) return fail(DX_ERR_CAPACITY, "pane partitions overflow");
             }
         } else

@@ -98,6 +98,12 @@ struct dx_flow {
     std::map<std::string, std::map<const DxTable*, PanePartial>> pane_partials;   // partial signature -> cached batch -> partial
     std::map<std::string, std::map<const DxTable*, PanePartialP>> pane_partials_p;   // same, partitioned shared-memory form (dx_aggp.h)
     std::map<std::string, int> pane_P;       // partitions per signature (every partial of a signature shares it)
+    // the partial shapes built so far for one (window source, pane width, group keys) family; a statement uses any member
+    // whose accumulators cover its own
+    struct PaneVariant { std::vector<dxsql::ExprP> vals; std::vector<AggAccDesc> accs; std::vector<std::string> desc; std::string sig; };
+    std::map<std::string, std::vector<PaneVariant>> pane_variants;
+    int pane_variant_seq = 0;
+    std::map<std::string, std::pair<long long, long long>> pane_fill;   // per signature: (fullest partition, rows) of the last build
     int pane_partitions_first = 0;  // conf datax.job.process.gpu.panepartitions: first partition count tried (tests force the re-partition path)
     bool pane_smem_off = false;     // conf datax.job.process.gpu.panesmem=false: partials through the global hash table (dx_agg.cu)
     std::map<std::string, std::shared_ptr<void>> rule_plans;        // (statement, item) -> planned rule set with its device tables (dx_rules.h)

@@ -1,5 +1,7 @@
 """Flow-level parity: libdxgpu's processor (C ABI) vs the CPU oracle's restatement of
 CommonProcessorFactory.processDataset on the same batches."""
+import json
+
 import numpy as np
 import pytest
 
@@ -200,6 +202,38 @@ Total = SELECT COUNT(*) AS Count, AVG(deviceDetails.temperature) AS Tavg FROM Da
     assert ctx.take_counter("k3_partial_rows_built") > 0           # the partial path really ran
     assert ctx.take_counter("k3p_repartitions") > 0
     g.close(); g_rescan.close(); g_global.close(); g_coarse.close()
+
+
+def test_pane_partials_shared_between_statements_and_skewed_keys(dx, ctx):
+    """Two statements over the same keys share one partial per cached batch when the accumulators of one cover the
+    other's (whichever comes first in the file), and a hot key that outgrows its partition's fixed slice in the
+    single-pass scatter takes the exact two-pass form: results equal the oracle's either way."""
+    def flow(order):
+        a = "Narrow = SELECT deviceDetails.deviceId, COUNT(*) AS Count, SUM(deviceDetails.status) AS S FROM DataXProcessedInput_5minutes GROUP BY deviceDetails.deviceId\n"
+        b = ("Wide = SELECT deviceDetails.deviceId, COUNT(*) AS Count, SUM(deviceDetails.status) AS S, MIN(deviceDetails.status) AS Mn, MAX(deviceDetails.status) AS Mx, "
+             "AVG(deviceDetails.status) AS Av FROM DataXProcessedInput_3minutes GROUP BY deviceDetails.deviceId\n")
+        return "".join("--DataXQuery--\n" + q for q in ((a, b) if order == 0 else (b, a)))
+    windows = [("DataXProcessedInput_5minutes", "5 minutes"), ("DataXProcessedInput_3minutes", "3 minutes")]
+    conf = dx.flowgen.conf_text("share", timestamp_column="eventTimeStamp", watermark="60 second", windows=windows)
+    for order in (0, 1):
+        g, o = both(dx, ctx, conf, SCHEMA1, [PROJ_TS], flow(order))
+        ctx.take_counter("k3_partial_rows_built"); ctx.take_counter("k3p_two_pass_fallbacks")
+        built = []
+        for b in range(6):
+            T = T0 + b * I
+            if b == 3:      # 9 of 10 events carry one device id: its partition gets far more than mean + 8 sigma records
+                recs = [json.dumps({"deviceDetails": {"deviceId": 7 if k % 10 else 1000 + k, "deviceType": "DoorLock", "eventTime": T - 1000 - (k % 50000),
+                                                      "homeId": 3, "status": k % 2}}, separators=(",", ":")) for k in range(60_000)]
+                data = ("\n".join(recs) + "\n").encode()
+            else:
+                data = gen(dx, 3000, first=b * 3000, shape=1, n_keys=500, base=T, late=30, future=20)
+            check_batch(dx, g, o, data, T)
+            built.append(ctx.take_counter("k3_partial_rows_built"))
+        assert ctx.take_counter("k3p_two_pass_fallbacks") >= 1
+        # from the third batch on (windows span several cached batches, the wider partial exists) one partial per batch serves both statements
+        if order == 1:
+            assert built[4] > 0 and built[5] > 0
+        g.close()
 
 
 def test_state_table_append_with_retention_and_upsert(dx, ctx):
