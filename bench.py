@@ -191,18 +191,30 @@ def run_ours(args):
             self.wire += int((counts.sum() - counts[rank]) * 8 * rec_words)
             return recv_ptr, n_recv
 
-        def batch(self, b, table_or_result, mode, results=None, time_exchange=False):
+        def batch(self, b, table_or_result, mode, results=None, time_exchange=False, trace=None):
             """Everything after decode+rules for micro-batch b: per-rule counts, exchange, owner-side windows."""
             T = T0 + b * INTERVAL_MS
+
+            def mark(name):
+                if trace is not None:
+                    ctx.synchronize(); torch.cuda.synchronize()
+                    now = time.perf_counter()
+                    trace[name] = trace.get(name, 0.0) + (now - trace["_t"]) * 1e3
+                    trace["_t"] = now
+            mark("decode+rules")
             t = table_or_result.table("Rules")
             self.hits += dx.rule_hits(t)
+            mark("rule_hits")
             if time_exchange:
                 self.ev[0].record(stream)
             recv_ptr, n_recv = self.exchange(t, mode)
             if time_exchange:
                 self.ev[1].record(stream)
+            mark("exchange")
             part = dx.parallel.table_from_packed(ctx, NAMES, TYPES, recv_ptr if n_recv else 0, n_recv)
+            mark("unpack")
             r = dx.parallel.process_table(self.agg, part, T, INTERVAL_MS)
+            mark("windows")
             if time_exchange:
                 self.ev[1].synchronize()
                 self.a2a_ms += self.ev[0].elapsed_time(self.ev[1])
@@ -290,11 +302,13 @@ def run_ours(args):
 
     pipe = Pipeline()
 
-    def step_device(step, mode=args.exchange, time_exchange=False):
+    def step_device(step, mode=args.exchange, time_exchange=False, trace=None):
         for c, (ptr, nb) in enumerate(chunks):
             b = step * N_CHUNKS + c
+            if trace is not None:
+                ctx.synchronize(); trace["_t"] = time.perf_counter()
             r0 = pipe.dec.process_device(ptr, nb, T0 + b * INTERVAL_MS, INTERVAL_MS, n_events=per_chunk)
-            pipe.batch(b, r0, mode, time_exchange=time_exchange)
+            pipe.batch(b, r0, mode, time_exchange=time_exchange, trace=trace)
             r0.release()
 
     def timed_step(fn, step):
@@ -346,6 +360,13 @@ def run_ours(args):
         t, n = ctx.take_stage_ms(s)
         if n:
             stage_ms[s] = (t, n)
+    if args.trace:       # host wall time per phase of one more step, every phase closed by a synchronize (stderr; not a bench value)
+        generate(step_no)
+        tr = {}
+        step_device(step_no, trace=tr)
+        step_no += 1
+        tr.pop("_t", None)
+        print("trace ms/step:", {k: round(v, 2) for k, v in tr.items()}, "sum", round(sum(tr.values()), 2), file=sys.stderr)
     peak, peak_src = peaks()
     rows = n_events
     alg = {  # algorithmic bytes per step, SURVEY.md §8(d) / DESIGN.md §5
@@ -638,6 +659,7 @@ def main():
     ap.add_argument("--exchange", default="put", choices=["put", "nccl"], help="how keyed records reach their owner: fused put over peer memory, or K5 pack + NCCL all-to-all")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-stages", action="store_true", help="skip the c3 / c4 stage runs")
+    ap.add_argument("--trace", action="store_true", help="print the host wall time per pipeline phase of one extra step to stderr")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -441,8 +441,9 @@ int dx_aggp_build(dx_ctx* ctx, const AggInput& in_, int nk, int nv, const std::v
     // partition the previous batch of this statement produced, with 25 % headroom; the first batch runs the two-pass form)
     const unsigned long long stride = stride_hint ? (unsigned long long)((double)*stride_hint * ((double)in.n_rows / (double)std::max<long long>(1, hint_rows ? *hint_rows : in.n_rows)) * 1.25 + 64.0) : 0ull;
     bool single_pass = !force_two_pass && stride_hint && *stride_hint > 0 && stride * (unsigned long long)P < (1ull << 32) &&
-                       stride * (unsigned long long)P <= (unsigned long long)in.n_rows * 4 + 128ull * P;
+                       stride * (unsigned long long)P <= (unsigned long long)in.n_rows * 8 + 128ull * P;
     DevBuf recs;
+    ctx->counters[single_pass ? "k3p_single_pass_builds" : "k3p_two_pass_builds"]++;
     if (single_pass) {
         recs = DevBuf(ctx, (size_t)stride * P * rw * 8 + 64);
         if (!recs.p) return ctx->set_error(DX_ERR_CUDA, "pane partial allocation failed");

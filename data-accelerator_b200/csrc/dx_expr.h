@@ -69,6 +69,7 @@ int dx_compile_expr(dx_ctx* ctx, const BindScope& sc, const dxsql::ExprP& e, Exp
 struct DevPrograms {
     DevBuf code, consts, cols, luts, starts;
     int n_progs = 0, n_code = 0, n_consts = 0, n_cols = 0, n_luts = 0;
+    std::vector<uint32_t> host_starts;   // offset of each program in code (host copy of `starts`)
 };
 int dx_upload_programs(dx_ctx* ctx, ExprPrograms* P, DevPrograms* D);   // also (re)builds LUTs for grown dictionaries
 

@@ -891,7 +891,49 @@ int dx_rules_eval(dx_ctx* ctx, const BindScope& sc, const std::vector<ExprP>& co
 // =======================================================================================
 // per-rule hit counts of a flag bitmap ("200-bit flags/event + per-rule counts")
 // =======================================================================================
-// One warp takes 32 consecutive rows of one flag word; bit b of the 32 lanes' words is counted with one ballot.
+// Bit-sliced counting: a lane never looks at single bits of the words it reads.  It adds them, 32 rules at a time, into a
+// vertical counter (one register per binary digit: ones, twos, fours, then five more) with carry-save adders — 7 three-input
+// adders (14 LOP3) take in eight flag words — and only when the counter is about to overflow, or at the end, are the digits
+// of each of the 32 rule positions put back together and summed over the warp (REDUX).  About three instructions per flag
+// word, against four per BIT for the ballot form this replaces (2.5 ms per 25 M events x 7 words); it runs at memory speed.
+struct RcAcc { uint32_t ones, twos, fours, c[5]; };
+static __device__ __forceinline__ void rc_csa(uint32_t& hi, uint32_t& lo, uint32_t a, uint32_t b, uint32_t c) {
+    lo = a ^ b ^ c; hi = (a & b) | (a & c) | (b & c);
+}
+static __device__ __forceinline__ void rc_ripple(RcAcc& A, uint32_t carry) {       // adds `carry` at weight 8
+#pragma unroll
+    for (int l = 0; l < 5; l++) { const uint32_t t = A.c[l] & carry; A.c[l] ^= carry; carry = t; }
+}
+static __device__ __forceinline__ void rc_add8(RcAcc& A, const uint32_t* x) {
+    uint32_t ta, tb, fa, fb, ea;
+    rc_csa(ta, A.ones, A.ones, x[0], x[1]);
+    rc_csa(tb, A.ones, A.ones, x[2], x[3]);
+    rc_csa(fa, A.twos, A.twos, ta, tb);
+    rc_csa(ta, A.ones, A.ones, x[4], x[5]);
+    rc_csa(tb, A.ones, A.ones, x[6], x[7]);
+    rc_csa(fb, A.twos, A.twos, ta, tb);
+    rc_csa(ea, A.fours, A.fours, fa, fb);
+    rc_ripple(A, ea);
+}
+static __device__ __forceinline__ void rc_add1(RcAcc& A, uint32_t x) {
+    uint32_t t = A.ones & x; A.ones ^= x; x = t;
+    t = A.twos & x; A.twos ^= x; x = t;
+    t = A.fours & x; A.fours ^= x; x = t;
+    rc_ripple(A, x);
+}
+// digits -> per-rule counts, summed over the warp; lane b keeps rule position b.  The counter holds at most 255 per position.
+static __device__ __forceinline__ void rc_flush(RcAcc& A, unsigned int& mine, int lane) {
+#pragma unroll
+    for (int b = 0; b < 32; b++) {
+        const unsigned int v = ((A.ones >> b) & 1u) + (((A.twos >> b) & 1u) << 1) + (((A.fours >> b) & 1u) << 2) + (((A.c[0] >> b) & 1u) << 3) +
+                               (((A.c[1] >> b) & 1u) << 4) + (((A.c[2] >> b) & 1u) << 5) + (((A.c[3] >> b) & 1u) << 6) + (((A.c[4] >> b) & 1u) << 7);
+        const unsigned int tot = __reduce_add_sync(0xffffffffu, v);
+        if (lane == b) mine += tot;
+    }
+    A.ones = A.twos = A.fours = 0;
+#pragma unroll
+    for (int l = 0; l < 5; l++) A.c[l] = 0;
+}
 __global__ void __launch_bounds__(256) k2_rule_counts(const uint32_t* flags, long long n_rows, int words, unsigned long long* counts) {
     __shared__ unsigned int s_cnt[32];
     const int lane = threadIdx.x & 31, w = blockIdx.y;
@@ -899,17 +941,33 @@ __global__ void __launch_bounds__(256) k2_rule_counts(const uint32_t* flags, lon
     __syncthreads();
     unsigned int mine = 0;                      // lane b keeps the count of bit b
     const uint32_t* col = flags + (size_t)w * n_rows;
-    const long long warp_id = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5, n_warps = ((long long)gridDim.x * blockDim.x) >> 5;
-    for (long long base = warp_id * 32; base < n_rows; base += n_warps * 32) {
-        const long long i = base + lane;
-        const uint32_t v = i < n_rows ? col[i] : 0u;
+    RcAcc A; A.ones = A.twos = A.fours = 0;
 #pragma unroll
-        for (int b = 0; b < 32; b++) {
-            const unsigned int c = __popc(__ballot_sync(0xffffffffu, (v >> b) & 1u));
-            if (lane == b) mine += c;
-        }
+    for (int l = 0; l < 5; l++) A.c[l] = 0;
+    int held = 0;                               // words added since the last flush (per lane; the same for every lane of a warp)
+    // rows before the first 16-byte boundary of this word's column, then 16-byte vectors (two per step), then the tail
+    long long head = (long long)(((16 - (reinterpret_cast<uintptr_t>(col) & 15)) & 15) >> 2);
+    if (head > n_rows) head = n_rows;
+    const long long n_vec = (n_rows - head) >> 2, tail0 = head + (n_vec << 2);
+    const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x, gsz = (long long)gridDim.x * blockDim.x;
+    if (gid < head) rc_add1(A, col[gid]);
+    if (gid < n_rows - tail0) rc_add1(A, col[tail0 + gid]);
+    held = 2;
+    const uint4* vec = reinterpret_cast<const uint4*>(col + head);
+    // every lane of a warp makes the same number of trips (the flush is a warp-wide reduction): lanes past the end add zeros
+    const long long warp0 = gid - lane;
+    for (long long v0 = warp0; v0 < n_vec; v0 += 2 * gsz) {
+        const long long va = v0 + lane, vb = v0 + gsz + lane;
+        uint4 a = make_uint4(0, 0, 0, 0), b4 = make_uint4(0, 0, 0, 0);
+        if (va < n_vec) a = __ldcs(vec + va);
+        if (vb < n_vec) b4 = __ldcs(vec + vb);
+        const uint32_t x[8] = {a.x, a.y, a.z, a.w, b4.x, b4.y, b4.z, b4.w};
+        rc_add8(A, x);
+        held += 8;
+        if (held > 240) { rc_flush(A, mine, lane); held = 0; }
     }
-    atomicAdd(&s_cnt[lane], mine);
+    rc_flush(A, mine, lane);
+    if (mine) atomicAdd(&s_cnt[lane], mine);
     __syncthreads();
     if (threadIdx.x < 32 && s_cnt[threadIdx.x]) atomicAdd(&counts[w * 32 + threadIdx.x], (unsigned long long)s_cnt[threadIdx.x]);
 }
@@ -921,7 +979,10 @@ int dx_rule_counts(dx_ctx* ctx, const uint32_t* flags, int64_t n_rows, int words
     if (!d.p) return ctx->set_error(DX_ERR_CUDA, "rule count allocation failed");
     DX_CUDA(ctx, cudaMemsetAsync(d.p, 0, (size_t)words * 32 * 8, ctx->stream));
     long long bx = (n_rows + 8191) / 8192; if (bx > ctx->sm_count * 4) bx = ctx->sm_count * 4; if (bx < 1) bx = 1;
-    k2_rule_counts<<<dim3((unsigned)bx, (unsigned)words), 256, 0, ctx->stream>>>(flags, n_rows, words, d.as<unsigned long long>());
+    {
+        StageTimer tm(ctx, "k2_rule_counts");
+        k2_rule_counts<<<dim3((unsigned)bx, (unsigned)words), 256, 0, ctx->stream>>>(flags, n_rows, words, d.as<unsigned long long>());
+    }
     ctx->launches["k2_rule_counts"]++;
     DX_CUDA(ctx, cudaGetLastError());
     std::vector<unsigned long long> h((size_t)words * 32);
