@@ -873,7 +873,7 @@ struct Exec {
                     BindScope sc = scope_for(v.chunks[k].get(), core);
                     const int64_t* selp = cs[k].filtered ? cs[k].sel->as<int64_t>() : nullptr;
                     bool fast = false;
-                    int rc = F->generic_rules_only ? DX_OK : dx_rules_eval(ctx, sc, conds, cs[k].n, selp, oc.data->as<uint32_t>() + off, oc.flag_words, &fast, &F->rule_plans[stmt_name + "#" + oc.name]);
+                    int rc = F->generic_rules_only ? DX_OK : dx_rules_eval(ctx, sc, conds, cs[k].n, selp, oc.data->as<uint32_t>() + off, oc.flag_words, &fast, &F->rule_plans[stmt_name + "#" + oc.name], F->rules_mode);
                     if (rc) return rc;
                     if (!fast) {   // rule set outside the bucketed planner's limits: generic interpreter
                         ExprPrograms P;
@@ -1683,6 +1683,8 @@ int dx_flow_build(dx_ctx* ctx, const char* conf_text, const char* schema_json, c
         }
     }
     { auto g = F->conf.find(root + "gpu.genericrules"); F->generic_rules_only = g != F->conf.end() && lower(g->second) == "true"; }
+    { auto g = F->conf.find(root + "gpu.rulesstaging"); if (g != F->conf.end() && lower(g->second) == "false") F->rules_mode |= DX_RULES_NO_STAGING; }
+    { auto g = F->conf.find(root + "gpu.rulesfast"); if (g != F->conf.end() && lower(g->second) == "false") F->rules_mode |= DX_RULES_NO_FAST; }
     { auto g = F->conf.find(root + "gpu.panepartials"); F->pane_partials_off = g != F->conf.end() && lower(g->second) == "false"; }
     { auto g = F->conf.find(root + "gpu.panesmem"); F->pane_smem_off = g != F->conf.end() && lower(g->second) == "false"; }
     { auto g = F->conf.find(root + "gpu.panepartitions"); if (g != F->conf.end()) { int v = atoi(g->second.c_str()); int p2 = 1; while (p2 < v) p2 <<= 1; F->pane_partitions_first = v > 0 ? p2 : 0; } }

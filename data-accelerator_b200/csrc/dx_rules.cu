@@ -24,6 +24,7 @@
 #include "dx_rules.h"
 #include "dx_expr_eval.cuh"
 #include <cmath>
+#include <array>
 
 using namespace dxsql;
 
@@ -375,6 +376,181 @@ __global__ void __launch_bounds__(256, K2_MIN_CTAS) k2_rules_bucket(const __grid
 }
 
 // =======================================================================================
+// k2_rules_fast — the same bucketed, bit-sliced evaluation with everything a rule set has in common hoisted out of the row
+// loop.  The class kernel above costs ~1500 thread-instructions per row for 200 rules (ncu, round 1: 47 warp-instructions per
+// event, a third of them descriptor loads, predicate tests and the per-class switch).  Here
+//   * the per-space descriptors ride in the kernel parameter block, read at compile-time offsets of the constant bank;
+//   * constants are padded to 2^k - 1 entries, so a bucket search is k steps of {LDS, compare, predicated add} with no bound
+//     test (integer columns whose constants fit 32 bits search 4-byte keys after clamping the value);
+//   * every rule is put in ONE normal form, out = (a1 AND a2 AND ...) AND (o1 OR o2 OR ...), either part optional (a; a AND b;
+//     a OR b; a AND (b OR c); x IN (...) AND y; ...).  Each space keeps at most two R-bit vectors per bucket: A, the conjunction
+//     of the rule's AND-leaves that live in this space (all ones where the rule has none), and O, the disjunction of its
+//     OR-leaves here (zero where it has none) — leaves of one rule in the same column (BETWEEN, IN lists) are folded into the
+//     table.  A row is then out = AND_s A_s[bucket_s] & (OR_s O_s[bucket_s] | no-OR-group bias): at most two table reads per
+//     referenced column and one LOP3 per flag word at the end, whatever the number of rule shapes;
+//   * table entries are padded to an odd number of 16-byte slots, so random buckets spread over all shared-memory banks
+//     (entries of 128 bytes put every lane's first read on the same four banks: 8-way conflicts);
+//   * flag words are a template parameter: 200 rules work on 7 words, not on a padded 8.
+// Rule sets with NOT over a leaf, more than four distinct leaves, DNF shapes outside the normal form, LIKE over a growing dictionary,
+// computed leaves or more than 256 rules keep the class kernel.  Monotone formulas need only the TRUE plane for exact
+// three-valued logic: TRUE(a AND b) = TRUE(a) & TRUE(b), TRUE(a OR b) = TRUE(a) | TRUE(b).
+// =======================================================================================
+#define RF_MAX_SPACES 8
+#ifndef RF_NT
+#define RF_NT 256                    // rows per tile = threads per CTA
+#endif
+#ifndef RF_NBUF
+#define RF_NBUF 2                    // staged tiles per CTA
+#endif
+#ifndef RF_MIN_CTAS
+#define RF_MIN_CTAS 3
+#endif
+enum { RF_F64 = 0, RF_F64_FROM_I64 = 1, RF_I32 = 2, RF_I64 = 3, RF_CODE = 4 };
+struct RFSpace {
+    const void* data;
+    int32_t domain, width;
+    int32_t m;               // real constants
+    int32_t top;             // first search step in BYTES of the padded constant array ((padded length + 1) / 2 entries); 0: no constants
+    int32_t const_off;       // byte offset of the padded constants in the image
+    int32_t lut_off, lut_size, other_bucket;      // RF_CODE: code -> bucket
+    int32_t null_bucket;
+    int32_t tab_off;         // byte offset of this space's truth table in the image
+    int32_t row_bytes;       // bytes per bucket: the A and / or O vectors (WS words each), padded to an odd number of 16-byte slots
+    int32_t role_mask;       // bit 0: has an A vector, bit 1: has an O vector
+    int32_t vbit;            // bit of the shared validity mask; -1: never NULL
+    int32_t stage_off;       // byte offset of the column's slot in a stage buffer
+    int32_t pad;
+};
+struct RFDev {
+    RFSpace sp[RF_MAX_SPACES];
+    int32_t ns, words, image_bytes, stage_bytes;
+    const uint8_t* image;
+    const void* vmask; int32_t vwidth, vmask_stage_off;
+    uint32_t bias_o[8];      // rules without an OR group
+};
+
+template <int W, bool STAGED>
+__global__ void __launch_bounds__(RF_NT, RF_MIN_CTAS) k2_rules_fast(const __grid_constant__ RFDev D, long long n_rows, const long long* sel, uint32_t* flags) {
+    constexpr int WS = W <= 1 ? 1 : (W <= 2 ? 2 : (W <= 4 ? 4 : 8));      // words a (row, role) entry occupies
+    extern __shared__ __align__(128) uint8_t fsm[];
+    __shared__ uint64_t f_bar[RF_NBUF];
+    const int tid = threadIdx.x;
+    {
+        const uint4* src = reinterpret_cast<const uint4*>(D.image); uint4* dst = reinterpret_cast<uint4*>(fsm);
+        for (int i = tid; i < (D.image_bytes >> 4); i += RF_NT) dst[i] = src[i];
+    }
+    uint8_t* const stage0 = fsm + ((D.image_bytes + 127) & ~127);
+    const long long n_tiles = (n_rows + RF_NT - 1) / RF_NT;
+    auto issue_tile = [&](long long t, int buf) {          // thread 0
+        const long long row0 = t * RF_NT;
+        if (row0 + RF_NT > n_rows) return;                 // ragged tile: read directly
+        uint8_t* dst = stage0 + (size_t)buf * D.stage_bytes;
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        uint32_t total = D.vmask ? (uint32_t)(RF_NT * D.vwidth) : 0u;
+#pragma unroll
+        for (int s = 0; s < RF_MAX_SPACES; s++) if (s < D.ns) total += (uint32_t)(RF_NT * D.sp[s].width);
+        k2_mbar_expect_tx(&f_bar[buf], total);
+#pragma unroll
+        for (int s = 0; s < RF_MAX_SPACES; s++) if (s < D.ns)
+            k2_bulk_g2s(dst + D.sp[s].stage_off, reinterpret_cast<const uint8_t*>(D.sp[s].data) + row0 * D.sp[s].width, (uint32_t)(RF_NT * D.sp[s].width), &f_bar[buf]);
+        if (D.vmask) k2_bulk_g2s(dst + D.vmask_stage_off, reinterpret_cast<const uint8_t*>(D.vmask) + row0 * D.vwidth, (uint32_t)(RF_NT * D.vwidth), &f_bar[buf]);
+    };
+    if (STAGED) {
+        if (tid == 0) {
+            for (int k = 0; k < RF_NBUF; k++) k2_mbar_init(&f_bar[k], 1);
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
+    }
+    __syncthreads();
+    if (STAGED && tid == 0 && blockIdx.x < n_tiles) issue_tile(blockIdx.x, 0);
+    uint32_t it = 0;
+    for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, it++) {
+        const long long i = tile * RF_NT + tid;
+        const bool full = STAGED && tile * RF_NT + RF_NT <= n_rows;
+        const uint32_t sbuf = it % RF_NBUF;
+        const uint8_t* stg = stage0 + (size_t)sbuf * D.stage_bytes;
+        if (STAGED) {
+            if (RF_NBUF > 1 && tid == 0 && tile + gridDim.x < n_tiles) issue_tile(tile + gridDim.x, (int)((it + 1) % RF_NBUF));
+            if (full) { while (!k2_mbar_try_wait(&f_bar[sbuf], (it / RF_NBUF) & 1u)) {} }
+        }
+        if (i < n_rows) {
+            const long long row = sel ? sel[i] : i;
+            uint32_t vm = 0xFFFFFFFFu;
+            if (D.vmask) {
+                if (full) vm = D.vwidth == 1 ? stg[D.vmask_stage_off + tid] : reinterpret_cast<const uint32_t*>(stg + D.vmask_stage_off)[tid];
+                else vm = D.vwidth == 1 ? reinterpret_cast<const uint8_t*>(D.vmask)[row] : reinterpret_cast<const uint32_t*>(D.vmask)[row];
+            }
+            uint32_t TA[W], TO[W];
+#pragma unroll
+            for (int w = 0; w < W; w++) { TA[w] = 0xFFFFFFFFu; TO[w] = D.bias_o[w]; }
+#pragma unroll
+            for (int s = 0; s < RF_MAX_SPACES; s++) {
+                if (s >= D.ns) break;
+                const RFSpace& sp = D.sp[s];
+                long long v;
+                if (sp.width == 4) v = full ? (long long)reinterpret_cast<const int32_t*>(stg + sp.stage_off)[tid] : (long long)reinterpret_cast<const int32_t*>(sp.data)[row];
+                else v = full ? reinterpret_cast<const long long*>(stg + sp.stage_off)[tid] : reinterpret_cast<const long long*>(sp.data)[row];
+                int b;
+                const uint8_t* c = fsm + sp.const_off;
+                if (sp.domain == RF_CODE) {
+                    b = (v >= 0 && v < sp.lut_size) ? reinterpret_cast<const int32_t*>(fsm + sp.lut_off)[(int)v] : sp.other_bucket;
+                } else if (sp.domain == RF_I32) {
+                    const int x = v < -2147483647ll - 1 ? (-2147483647 - 1) : (v > 2147483647ll ? 2147483647 : (int)v);
+                    int lo = 0;                                        // bytes
+                    for (int step = sp.top; step >= 4; step >>= 1) if (*reinterpret_cast<const int*>(c + lo + step - 4) < x) lo += step;
+                    const bool eq = lo < sp.m * 4 && *reinterpret_cast<const int*>(c + lo) == x;
+                    b = (lo >> 1) + (eq ? 1 : 0);                      // 2 * (lo / 4) + eq
+                } else if (sp.domain == RF_I64) {
+                    int lo = 0;
+                    for (int step = sp.top; step >= 8; step >>= 1) if (*reinterpret_cast<const long long*>(c + lo + step - 8) < v) lo += step;
+                    const bool eq = lo < sp.m * 8 && *reinterpret_cast<const long long*>(c + lo) == v;
+                    b = (lo >> 2) + (eq ? 1 : 0);                      // 2 * (lo / 8) + eq
+                } else {
+                    const double x = sp.domain == RF_F64 ? __longlong_as_double(v) : (double)v;
+                    int lo = 0;
+                    for (int step = sp.top; step >= 8; step >>= 1) if (*reinterpret_cast<const double*>(c + lo + step - 8) < x) lo += step;
+                    const bool eq = lo < sp.m * 8 && *reinterpret_cast<const double*>(c + lo) == x;
+                    b = (lo >> 2) + (eq ? 1 : 0);
+                    if (x != x) b = 2 * sp.m;                          // NaN is greater than every constant
+                }
+                if (sp.vbit >= 0 && !((vm >> sp.vbit) & 1u)) b = sp.null_bucket;
+                const uint8_t* tr = fsm + sp.tab_off + b * sp.row_bytes;
+                uint32_t x8[8];
+                auto fetch = [&]() {
+                    if (WS == 8) {
+                        const uint4 a = *reinterpret_cast<const uint4*>(tr), b4 = *reinterpret_cast<const uint4*>(tr + 16);
+                        x8[0] = a.x; x8[1] = a.y; x8[2] = a.z; x8[3] = a.w; x8[4] = b4.x; x8[5] = b4.y; x8[6] = b4.z; x8[7] = b4.w;
+                    } else if (WS == 4) {
+                        const uint4 a = *reinterpret_cast<const uint4*>(tr);
+                        x8[0] = a.x; x8[1] = a.y; x8[2] = a.z; x8[3] = a.w;
+                    } else if (WS == 2) {
+                        const uint2 a = *reinterpret_cast<const uint2*>(tr);
+                        x8[0] = a.x; x8[1] = a.y;
+                    } else x8[0] = *reinterpret_cast<const uint32_t*>(tr);
+                    tr += WS * 4;
+                };
+                if (sp.role_mask & 1) {
+                    fetch();
+#pragma unroll
+                    for (int w = 0; w < W; w++) TA[w] &= x8[w];
+                }
+                if (sp.role_mask & 2) {
+                    fetch();
+#pragma unroll
+                    for (int w = 0; w < W; w++) TO[w] |= x8[w];
+                }
+            }
+#pragma unroll
+            for (int w = 0; w < W; w++) flags[(long long)w * n_rows + i] = TA[w] & TO[w];
+        }
+        if (STAGED) {
+            __syncthreads();        // the tile's buffer is refilled next: every reader must be done
+            if (RF_NBUF == 1 && tid == 0 && tile + gridDim.x < n_tiles) issue_tile(tile + gridDim.x, 0);
+        }
+    }
+}
+
+// =======================================================================================
 // host-side planner
 // =======================================================================================
 namespace {
@@ -616,6 +792,62 @@ static void launch_rules(dx_ctx* ctx, const RulesDev& D, size_t smem, int64_t n_
     k2_rules_bucket<J, NEEDF, NSMAX, STAGED><<<(unsigned)blocks, 256, smem, ctx->stream>>>(D, n_rows, reinterpret_cast<const long long*>(sel), flags);
 }
 
+template <int W, bool STAGED>
+static void launch_fast_w(dx_ctx* ctx, const RFDev& D, size_t smem, int64_t n_rows, const int64_t* sel, uint32_t* flags) {
+    cudaFuncSetAttribute(k2_rules_fast<W, STAGED>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    int occ = 1;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k2_rules_fast<W, STAGED>, RF_NT, smem);
+    if (occ < 1) occ = 1;
+    long long blocks = (n_rows + RF_NT - 1) / RF_NT, cap = (long long)ctx->sm_count * occ;
+    if (blocks > cap) blocks = cap;
+    k2_rules_fast<W, STAGED><<<(unsigned)blocks, RF_NT, smem, ctx->stream>>>(D, n_rows, reinterpret_cast<const long long*>(sel), flags);
+}
+template <bool STAGED>
+static void launch_fast(dx_ctx* ctx, const RFDev& D, size_t smem, int64_t n_rows, const int64_t* sel, uint32_t* flags) {
+    switch (D.words) {
+    case 1: launch_fast_w<1, STAGED>(ctx, D, smem, n_rows, sel, flags); break;
+    case 2: launch_fast_w<2, STAGED>(ctx, D, smem, n_rows, sel, flags); break;
+    case 3: launch_fast_w<3, STAGED>(ctx, D, smem, n_rows, sel, flags); break;
+    case 4: launch_fast_w<4, STAGED>(ctx, D, smem, n_rows, sel, flags); break;
+    case 5: launch_fast_w<5, STAGED>(ctx, D, smem, n_rows, sel, flags); break;
+    case 6: launch_fast_w<6, STAGED>(ctx, D, smem, n_rows, sel, flags); break;
+    case 7: launch_fast_w<7, STAGED>(ctx, D, smem, n_rows, sel, flags); break;
+    default: launch_fast_w<8, STAGED>(ctx, D, smem, n_rows, sel, flags); break;
+    }
+}
+// fills the per-batch parts of a fast plan (column pointers, validity mask, staging layout) and launches it
+static int fast_launch(dx_ctx* ctx, RFDev D, const std::vector<ProgCol>& cols, int64_t n_rows, const int64_t* sel, uint32_t* flags, bool no_staging, bool* ok) {
+    *ok = false;
+    const void* vm = nullptr; int vw = 0;
+    for (size_t k = 0; k < cols.size(); k++) {
+        D.sp[k].data = cols[k].data; D.sp[k].width = cols[k].width;
+        if (cols[k].width != (D.sp[k].domain == RF_CODE ? 4 : 8)) { ctx->counters["k2_fast_reject_width"]++; return DX_OK; }
+        if (cols[k].vmask) {
+            if (vm && cols[k].vmask != vm) { ctx->counters["k2_fast_reject_vmask"]++; return DX_OK; }          // one validity array for all referenced columns (the decoder's), or the class kernel
+            vm = cols[k].vmask; vw = cols[k].vwidth; D.sp[k].vbit = cols[k].vbit;
+        } else D.sp[k].vbit = -1;
+    }
+    if (vm && vw != 1 && vw != 4) return DX_OK;
+    D.vmask = vm; D.vwidth = vw;
+    bool staged = !no_staging && !sel && n_rows >= RF_NT;
+    int off = 0;
+    for (size_t k = 0; k < cols.size(); k++) {
+        if (reinterpret_cast<uintptr_t>(cols[k].data) & 15) staged = false;
+        D.sp[k].stage_off = off; off += RF_NT * cols[k].width;
+    }
+    if (vm && (reinterpret_cast<uintptr_t>(vm) & 15)) staged = false;
+    D.vmask_stage_off = off; off += vm ? RF_NT * vw : 0;
+    D.stage_bytes = (off + 127) & ~127;
+    const size_t smem = (size_t)((D.image_bytes + 127) & ~127) + (staged ? (size_t)RF_NBUF * D.stage_bytes : 0);
+    if (smem > 110 * 1024) { ctx->counters["k2_fast_reject_smem"]++; return DX_OK; }
+    StageTimer tm(ctx, "k2_rules_bucket");
+    if (staged) launch_fast<true>(ctx, D, smem, n_rows, sel, flags); else launch_fast<false>(ctx, D, smem, n_rows, sel, flags);
+    ctx->launches["k2_rules_fast"]++;
+    ctx->counters["k2_rules_fast_launches"]++;
+    *ok = true;
+    return DX_OK;
+}
+
 // A planned rule set kept across micro-batches: everything but the column pointers is a function of the statement text,
 // the column types and the dictionaries' literal codes, so a steady-state batch only refreshes the pointers and launches.
 struct PlanCache {
@@ -623,6 +855,7 @@ struct PlanCache {
     std::vector<const void*> space_dict;
     DevBuf b_spaces, b_classes, b_cmask, b_consts, b_luts, b_tt, b_tf;
     RulesDev D; size_t smem = 0; int J = 1; bool needf = false; int R = 0, words = 0;
+    bool fast = false; RFDev FD; DevBuf b_image;        // the normal-form plan (k2_rules_fast) when the rule set fits it
 };
 
 static void rules_shared_vmask(RulesDev& D, const std::vector<RSpaceDev>& sdev) {
@@ -634,8 +867,8 @@ static void rules_shared_vmask(RulesDev& D, const std::vector<RSpaceDev>& sdev) 
 
 // Whether the column tiles can be staged by bulk copies: rows taken in order, at most 8 plain column spaces, every column
 // (and the one validity array they share) 16-byte aligned, no space with a validity array of its own.
-static bool rules_can_stage(const RulesDev& D, const std::vector<RSpaceDev>& sdev, int64_t n_rows, const int64_t* sel) {
-    if (sel || n_rows < K2_TILE || sdev.size() > 8 || getenv("DX_K2_NO_STAGING")) return false;
+static bool rules_can_stage(const RulesDev& D, const std::vector<RSpaceDev>& sdev, int64_t n_rows, const int64_t* sel, bool no_staging) {
+    if (sel || n_rows < K2_TILE || sdev.size() > 8 || no_staging) return false;
     for (auto& d : sdev) {
         if (d.domain == DOM_GENERIC || !d.col.data || (reinterpret_cast<uintptr_t>(d.col.data) & 15)) return false;
         if (d.col.width != (d.domain == DOM_CODE ? 4 : 8)) return false;
@@ -645,10 +878,10 @@ static bool rules_can_stage(const RulesDev& D, const std::vector<RSpaceDev>& sde
     return true;
 }
 
-static void rules_launch(dx_ctx* ctx, const RulesDev& D0, const std::vector<RSpaceDev>& sdev, int J, bool needf, size_t smem, int64_t n_rows, const int64_t* sel, uint32_t* flags) {
+static void rules_launch(dx_ctx* ctx, const RulesDev& D0, const std::vector<RSpaceDev>& sdev, int J, bool needf, size_t smem, int64_t n_rows, const int64_t* sel, uint32_t* flags, bool no_staging) {
     StageTimer tm(ctx, "k2_rules_bucket");
     RulesDev D = D0;
-    const bool staged = rules_can_stage(D, sdev, n_rows, sel);
+    const bool staged = rules_can_stage(D, sdev, n_rows, sel, no_staging);
     D.staged = staged ? 1 : 0; D.stage_off = 0; D.stage_buf_bytes = 0;
     if (staged) {
         D.stage_off = (int32_t)((smem + 127) & ~size_t(127));
@@ -666,7 +899,7 @@ static void rules_launch(dx_ctx* ctx, const RulesDev& D0, const std::vector<RSpa
 }
 
 int dx_rules_eval(dx_ctx* ctx, const BindScope& sc, const std::vector<ExprP>& conds, int64_t n_rows, const int64_t* sel,
-                  uint32_t* flags, int words, bool* used_fast, std::shared_ptr<void>* cache) {
+                  uint32_t* flags, int words, bool* used_fast, std::shared_ptr<void>* cache, int mode) {
     *used_fast = false;
     if (n_rows <= 0 || conds.empty()) return DX_OK;
     const int R = (int)conds.size();
@@ -680,15 +913,21 @@ int dx_rules_eval(dx_ctx* ctx, const BindScope& sc, const std::vector<ExprP>& co
             ok = c.name == pc->space_name[s2] && c.type == pc->space_type[s2] && c.data && !c.all_null && (const void*)c.dict.get() == pc->space_dict[s2];
             if (ok) { ProgCol& pcol = pc->sdev[s2].col; pcol.data = c.data->p; pcol.vmask = c.vmask ? c.vmask->p : nullptr; pcol.vwidth = c.vwidth; pcol.vbit = c.vbit; pcol.width = dx_type_width(c.type); }
         }
-        if (ok) {
+        if (ok && pc->fast && !(mode & DX_RULES_NO_FAST)) {
+            std::vector<ProgCol> cols; for (auto& d : pc->sdev) cols.push_back(d.col);
+            bool launched = false;
+            int rc = fast_launch(ctx, pc->FD, cols, n_rows, sel, flags, (mode & DX_RULES_NO_STAGING) != 0, &launched); if (rc) return rc;
+            if (launched) { DX_CUDA(ctx, cudaGetLastError()); *used_fast = true; return DX_OK; }
+        }
+        if (ok && pc->b_spaces.p) {
             DX_CUDA(ctx, cudaMemcpyAsync(pc->b_spaces.p, pc->sdev.data(), pc->sdev.size() * sizeof(RSpaceDev), cudaMemcpyHostToDevice, ctx->stream));
             rules_shared_vmask(pc->D, pc->sdev);
-            rules_launch(ctx, pc->D, pc->sdev, pc->J, pc->needf, pc->smem, n_rows, sel, flags);
+            rules_launch(ctx, pc->D, pc->sdev, pc->J, pc->needf, pc->smem, n_rows, sel, flags, (mode & DX_RULES_NO_STAGING) != 0);
             DX_CUDA(ctx, cudaGetLastError());
             *used_fast = true;
             return DX_OK;
         }
-        cache->reset();        // schema or dictionaries changed: plan again
+        cache->reset();        // schema or dictionaries changed (or the cached plan has no class tables): plan again
     }
     Planner P(ctx, sc);
     // per rule: DNF over leaf ids
@@ -763,6 +1002,139 @@ int dx_rules_eval(dx_ctx* ctx, const BindScope& sc, const std::vector<ExprP>& co
                 if (sp.domain == DOM_I64) same = sp.consts[k] == l.cbits;
                 else { double x, y; memcpy(&x, &sp.consts[k], 8); memcpy(&y, &l.cbits, 8); same = x == y; }
                 if (same) l.cidx = (int)k;
+            }
+        }
+    }
+    // ---- the normal-form plan (k2_rules_fast), when every rule fits out = p AND s AND (q OR r) ----
+    std::shared_ptr<PlanCache> fpc;
+    if (!(mode & DX_RULES_NO_FAST) && words <= 8 && P.spaces.size() <= RF_MAX_SPACES) {
+        bool fits = true;
+        for (auto& sp : P.spaces) if (sp.domain == DOM_GENERIC || sp.per_code) fits = false;
+        std::vector<std::vector<int>> and_leaves(R), or_leaves(R);
+        for (int r = 0; r < R && fits; r++) {
+            for (auto& t : rule_terms[r]) for (auto& l : t) if (l.neg) fits = false;
+            if (!fits) break;
+            // terms as sorted leaf sets, without duplicates and without absorbed terms (a OR (a AND b) = a also holds in Kleene logic)
+            std::vector<std::vector<int>> terms;
+            for (auto& t : rule_terms[r]) { std::vector<int> ls; for (auto& l : t) ls.push_back(l.leaf); std::sort(ls.begin(), ls.end()); ls.erase(std::unique(ls.begin(), ls.end()), ls.end()); terms.push_back(ls); }
+            for (size_t a = 0; a < terms.size();) {
+                bool absorbed = false;
+                for (size_t b = 0; b < terms.size() && !absorbed; b++)
+                    if (b != a && std::includes(terms[a].begin(), terms[a].end(), terms[b].begin(), terms[b].end()) && (terms[a] != terms[b] || b < a)) absorbed = true;
+                if (absorbed) terms.erase(terms.begin() + a); else a++;
+            }
+            if (terms.empty()) { fits = false; break; }
+            if (terms.size() == 1) { and_leaves[r] = terms[0]; continue; }
+            // (common leaves) AND (one further leaf per term)
+            std::vector<int> common = terms[0];
+            for (size_t t = 1; t < terms.size(); t++) {
+                std::vector<int> keep;
+                for (int l : common) if (std::find(terms[t].begin(), terms[t].end(), l) != terms[t].end()) keep.push_back(l);
+                common.swap(keep);
+            }
+            for (auto& t : terms) {
+                if (t.size() != common.size() + 1) { fits = false; break; }
+                for (int l : t) if (std::find(common.begin(), common.end(), l) == common.end()) or_leaves[r].push_back(l);
+            }
+            and_leaves[r] = common;
+        }
+        if (!fits) ctx->counters["k2_fast_reject_shape"]++;
+        if (fits) {
+            const int W = words, WS = W <= 1 ? 1 : (W <= 2 ? 2 : (W <= 4 ? 4 : 8));
+            RFDev FD; memset(&FD, 0, sizeof FD);
+            FD.ns = (int)P.spaces.size(); FD.words = W;
+            for (int r = 0; r < R; r++) {
+                if (or_leaves[r].empty()) FD.bias_o[r / 32] |= 1u << (r % 32);
+                for (int l : and_leaves[r]) FD.sp[P.leaves[l].space].role_mask |= 1;
+                for (int l : or_leaves[r]) FD.sp[P.leaves[l].space].role_mask |= 2;
+            }
+            std::vector<uint8_t> image;
+            auto align_to = [&](size_t a) { while (image.size() % a) image.push_back(0); };
+            for (size_t s2 = 0; s2 < P.spaces.size() && fits; s2++) {
+                SpaceDef& sp = P.spaces[s2]; RFSpace& d = FD.sp[s2];
+                d.null_bucket = sp.null_bucket; d.other_bucket = sp.other_bucket; d.vbit = -1;
+                if (sp.domain == DOM_CODE) {
+                    d.domain = RF_CODE;
+                    align_to(4);
+                    d.lut_off = (int)image.size(); d.lut_size = sdev[s2].lut_size;
+                    for (int k = 0; k < sdev[s2].lut_size; k++) { int32_t v = all_luts[sdev[s2].lut_off + k]; const uint8_t* b = reinterpret_cast<const uint8_t*>(&v); image.insert(image.end(), b, b + 4); }
+                } else {
+                    const int m = (int)sp.consts.size();
+                    int Pm = 0; while (Pm < m) Pm = Pm * 2 + 1;                       // 2^k - 1 >= m
+                    bool narrow = sp.domain == DOM_I64;
+                    if (narrow) for (long long cv : sp.consts) if (cv <= -2147483647ll || cv >= 2147483647ll) narrow = false;
+                    d.domain = sp.domain == DOM_F64 ? RF_F64 : (sp.domain == DOM_F64_FROM_I64 ? RF_F64_FROM_I64 : (narrow ? RF_I32 : RF_I64));
+                    const int esz = d.domain == RF_I32 ? 4 : 8;
+                    d.m = m; d.top = ((Pm + 1) / 2) * esz; if (m == 0) d.top = 0;
+                    align_to(8);
+                    d.const_off = (int)image.size();
+                    for (int k = 0; k <= Pm; k++) {                                     // Pm + 1 entries: the equality probe may look one past the last step
+                        if (esz == 4) { int32_t v = k < m ? (int32_t)sp.consts[k] : 2147483647; const uint8_t* b = reinterpret_cast<const uint8_t*>(&v); image.insert(image.end(), b, b + 4); }
+                        else {
+                            long long v = k < m ? sp.consts[k] : (d.domain == RF_I64 ? 0x7FFFFFFFFFFFFFFFll : 0x7FF8000000000000ll);   // int64 max / NaN: never below any value
+                            const uint8_t* b = reinterpret_cast<const uint8_t*>(&v); image.insert(image.end(), b, b + 8);
+                        }
+                    }
+                }
+            }
+            // truth tables: per space and bucket the A vector (if any rule has an AND-leaf here) then the O vector, WS words each
+            for (size_t s2 = 0; s2 < P.spaces.size(); s2++) {
+                SpaceDef& sp = P.spaces[s2]; RFSpace& d = FD.sp[s2];
+                const int n_vec = (d.role_mask & 1) + ((d.role_mask >> 1) & 1);
+                int slots = (n_vec * WS * 4 + 15) / 16; if (slots > 0 && slots % 2 == 0) slots++;      // odd number of 16-byte slots
+                d.row_bytes = slots * 16;
+                align_to(16);
+                d.tab_off = (int)image.size();
+                image.resize(image.size() + (size_t)sp.n_buckets * d.row_bytes, 0);
+                if (d.role_mask & 1)        // A starts as all ones: rules without an AND-leaf in this space do not constrain it
+                    for (int b = 0; b < sp.n_buckets; b++) memset(image.data() + d.tab_off + (size_t)b * d.row_bytes, 0xFF, (size_t)WS * 4);
+            }
+            for (int r = 0; r < R; r++) {
+                for (size_t s2 = 0; s2 < P.spaces.size(); s2++) {
+                    const SpaceDef& sp = P.spaces[s2]; const RFSpace& d = FD.sp[s2];
+                    std::vector<int> al, ol;
+                    for (int l : and_leaves[r]) if (P.leaves[l].space == (int)s2) al.push_back(l);
+                    for (int l : or_leaves[r]) if (P.leaves[l].space == (int)s2) ol.push_back(l);
+                    for (int b = 0; b < sp.n_buckets; b++) {
+                        uint8_t* row = image.data() + d.tab_off + (size_t)b * d.row_bytes;
+                        if (!al.empty()) {
+                            bool all_true = true; for (int l : al) if (leaf_truth(P.leaves[l], sp, b) != 1) all_true = false;
+                            if (!all_true) reinterpret_cast<uint32_t*>(row)[r / 32] &= ~(1u << (r % 32));
+                        }
+                        if (!ol.empty()) {
+                            bool any_true = false; for (int l : ol) if (leaf_truth(P.leaves[l], sp, b) == 1) any_true = true;
+                            if (any_true) reinterpret_cast<uint32_t*>(row + ((d.role_mask & 1) ? WS * 4 : 0))[r / 32] |= 1u << (r % 32);
+                        }
+                    }
+                }
+            }
+            // (bits past the last rule: A vectors hold ones there, O vectors and the bias zeros, so the output bits are zero)
+            align_to(16);
+            FD.image_bytes = (int)image.size();
+            if (image.size() > 96 * 1024) ctx->counters["k2_fast_reject_image"]++;
+            if (image.size() <= 96 * 1024) {
+                DevBuf b_image(ctx, image.size() + 64);
+                if (!b_image.p) return ctx->set_error(DX_ERR_CUDA, "rule table allocation failed");
+                DX_CUDA(ctx, cudaMemcpyAsync(b_image.p, image.data(), image.size(), cudaMemcpyHostToDevice, ctx->stream));
+                FD.image = b_image.as<uint8_t>();
+                std::vector<ProgCol> cols; for (auto& d : sdev) cols.push_back(d.col);
+                bool launched = false;
+                int rc2 = fast_launch(ctx, FD, cols, n_rows, sel, flags, (mode & DX_RULES_NO_STAGING) != 0, &launched); if (rc2) return rc2;
+                if (launched) {
+                    DX_CUDA(ctx, cudaGetLastError());
+                    DX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));     // `image` (host) was the source of an asynchronous copy
+                    if (cache) {
+                        fpc = std::make_shared<PlanCache>();
+                        fpc->sdev = sdev; fpc->R = R; fpc->words = words; fpc->fast = true; fpc->FD = FD; fpc->b_image = std::move(b_image);
+                        for (auto& sp : P.spaces) {
+                            const DxColumn& c = sc.table->cols[sp.table_col];
+                            fpc->space_col.push_back(sp.table_col); fpc->space_name.push_back(c.name); fpc->space_type.push_back(c.type); fpc->space_dict.push_back(c.dict.get());
+                        }
+                        *cache = fpc;
+                    }
+                    *used_fast = true;
+                    return DX_OK;
+                }
             }
         }
     }
@@ -867,7 +1239,7 @@ int dx_rules_eval(dx_ctx* ctx, const BindScope& sc, const std::vector<ExprP>& co
     D.table_in_smem = (fixed + tab_bytes <= RB_SMEM_TABLE_BYTES) ? 1 : 0;
     size_t smem = fixed + (D.table_in_smem ? tab_bytes : 0);
     if (fixed > 64 * 1024) return DX_OK;       // pathological constant count: generic kernel
-    rules_launch(ctx, D, sdev, J, needf, smem, n_rows, sel, flags);
+    rules_launch(ctx, D, sdev, J, needf, smem, n_rows, sel, flags, (mode & DX_RULES_NO_STAGING) != 0);
     DX_CUDA(ctx, cudaGetLastError());
     bool cacheable = cache != nullptr && P.G.prog_start.empty();
     for (auto& sp : P.spaces) if (sp.per_code) cacheable = false;       // per-code LIKE tables follow the dictionary

@@ -430,26 +430,75 @@ Named = SELECT CONCAT(deviceDetails.deviceType, '-', deviceDetails.deviceId) AS 
 
 
 def test_staged_and_direct_rule_kernels_agree_on_ragged_sizes(dx, ctx):
-    """K2 stages full 256-row tiles in shared memory by bulk copies and reads the ragged last tile directly; the direct
-    kernel (DX_K2_NO_STAGING, also what row selections use) must give the same flags at every tile-boundary case."""
-    import os
+    """K2 stages full row tiles in shared memory by bulk copies and reads the ragged last tile directly; the direct kernels
+    (gpu.rulesstaging=false, also what row selections use) must give the same flags at every tile-boundary case, and so must
+    the per-class kernel (gpu.rulesfast=false) the normal-form kernel replaces for rule sets like this one."""
     rules = dx.flowgen.make_rules(200, seed=11, n_keys=1000, n_homes=100)
     tr = dx.flowgen.process_rules_sql(rules)
     conf = dx.flowgen.conf_text("k2s")
-    p = dx.CommonProcessorFactory.createProcessor(ctx, conf, SCHEMA2, ["Raw.*\n"], tr)
+    variants = [conf, conf + "datax.job.process.gpu.rulesstaging=false\n", conf + "datax.job.process.gpu.rulesfast=false\n",
+                conf + "datax.job.process.gpu.rulesfast=false\ndatax.job.process.gpu.rulesstaging=false\n"]
+    procs = [dx.CommonProcessorFactory.createProcessor(ctx, c, SCHEMA2, ["Raw.*\n"], tr) for c in variants]
     o = dxo_flow.Flow(conf, SCHEMA2, ["Raw.*\n"], tr)
     cases = [gen(dx, n, seed=20260200 + n) for n in (1, 255, 256, 257, 511, 513, 30_011)] + [to_ndjson(all_records(3000, seed=21))]
     for data in cases:
-        a = p.process_json(data, T0, I)
-        fa, _ = a.table("Rules").column("Rules")
-        os.environ["DX_K2_NO_STAGING"] = "1"
-        try:
-            b = p.process_json(data, T0, I)
-        finally:
-            del os.environ["DX_K2_NO_STAGING"]
-        fb, _ = b.table("Rules").column("Rules")
-        assert fa.shape == fb.shape and (fa == fb).all()
+        ctx.take_launches()
+        res = [p.process_json(data, T0, I) for p in procs]
+        fa, _ = res[0].table("Rules").column("Rules")
+        for r in res[1:]:
+            fb, _ = r.table("Rules").column("Rules")
+            assert fa.shape == fb.shape and (fa == fb).all()
         ro, _ = o.process(data, T0, I)
-        assert_same_rows(a.table("Rules"), ro["Rules"], dx, ordered=True)
-        a.release(); b.release()
-    p.close()
+        assert_same_rows(res[0].table("Rules"), ro["Rules"], dx, ordered=True)
+        for r in res:
+            r.release()
+    for p in procs:
+        p.close()
+
+
+def test_rule_widths_and_shapes_through_the_normal_form_kernel(dx, ctx):
+    """Rule sets of every flag-word count from 1 to 8 (the normal-form kernel is instantiated per count), with every shape it
+    takes — a, a AND b, a OR b, a AND (b OR c), (a OR b) AND c AND d, a AND b AND c, x IN (..) AND y, x BETWEEN .. AND y —
+    plus constants at int32 / int64 edges and equal constants shared between rules; each against the per-class kernel and
+    the oracle."""
+    import random
+    rng = random.Random(5)
+    leaves = ["deviceDetails.temperature > %.2f", "deviceDetails.humidity <= %.2f", "deviceDetails.homeId = %d", "deviceDetails.status = %d",
+              "deviceDetails.deviceId < %d", "deviceDetails.deviceType = '%s'", "deviceDetails.deviceId >= %d", "deviceDetails.temperature <= %d"]
+
+    def leaf():
+        k = rng.randrange(len(leaves))
+        if k in (0, 1):
+            return leaves[k] % rng.uniform(0, 100)
+        if k == 5:
+            return leaves[k] % rng.choice(["DoorLock", "WindowLock", "Heating", "GarageDoorLock", "Nope"])
+        if k == 3:
+            return leaves[k] % rng.randrange(3)
+        if k == 7:
+            return leaves[k] % rng.randrange(0, 100)
+        return leaves[k] % rng.choice([1, 5, 50, 500, 2147483646, 2147483647, 2147483648, -2147483648, 4000000000, -1])
+    shapes = ["%s", "%s AND %s", "%s OR %s", "%s AND (%s OR %s)", "(%s OR %s) AND %s AND %s", "%s AND %s AND %s",
+              "deviceDetails.homeId IN (1, 2, 3) AND %s", "deviceDetails.temperature BETWEEN 20 AND 30.5 AND %s"]
+    for n_rules in (7, 33, 64, 65, 100, 129, 161, 193, 225, 256, 40):
+        rules = []
+        n_shapes = len(shapes) if n_rules == 40 else 6        # the last set mixes in IN / BETWEEN rules: leaves of one rule in the same column
+        for r in range(n_rules):
+            sh = shapes[r % n_shapes]
+            cond = sh % tuple(leaf() for _ in range(sh.count("%s")))
+            rules.append({"ruleId": "R%d" % r, "ruleDescription": "d", "severity": "Low", "tagName": "Tag", "tag": "T", "condition": cond})
+        tr = dx.flowgen.process_rules_sql(rules)
+        conf = dx.flowgen.conf_text("k2w")
+        g = dx.CommonProcessorFactory.createProcessor(ctx, conf, SCHEMA2, ["Raw.*\n"], tr)
+        g2 = dx.CommonProcessorFactory.createProcessor(ctx, conf + "datax.job.process.gpu.rulesfast=false\n", SCHEMA2, ["Raw.*\n"], tr)
+        o = dxo_flow.Flow(conf, SCHEMA2, ["Raw.*\n"], tr)
+        for data in (gen(dx, 5000, seed=n_rules, n_keys=600), to_ndjson(all_records(1500, seed=n_rules))):
+            ctx.take_counter("k2_rules_fast_launches")
+            a, b = g.process_json(data, T0, I), g2.process_json(data, T0, I)
+            assert ctx.take_counter("k2_rules_fast_launches") == 1
+            fa, _ = a.table("Rules").column("Rules")
+            fb, _ = b.table("Rules").column("Rules")
+            assert (fa == fb).all(), n_rules
+            ro, _ = o.process(data, T0, I)
+            assert_same_rows(a.table("Rules"), ro["Rules"], dx, ordered=True)
+            a.release(); b.release()
+        g.close(); g2.close()
