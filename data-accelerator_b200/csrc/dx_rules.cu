@@ -405,31 +405,35 @@ __global__ void __launch_bounds__(256, K2_MIN_CTAS) k2_rules_bucket(const __grid
 #ifndef RF_MIN_CTAS
 #define RF_MIN_CTAS 3
 #endif
-enum { RF_F64 = 0, RF_F64_FROM_I64 = 1, RF_I32 = 2, RF_I64 = 3, RF_CODE = 4 };
+enum { RF_F64 = 0, RF_F64_FROM_I64 = 1, RF_I32 = 2, RF_I64 = 3, RF_CODE = 4, RF_IDX = 5 };
 struct RFSpace {
     const void* data;
     int32_t domain, width;
     int32_t m;               // real constants
-    int32_t top;             // first search step in BYTES of the padded constant array ((padded length + 1) / 2 entries); 0: no constants
-    int32_t const_off;       // byte offset of the padded constants in the image
+    int32_t top;             // RF_I64: first search step in BYTES of the padded constant array; 0: no constants
+    int32_t const_off;       // byte offset in the image of: the 2^KS 32-bit search keys (RF_F64*, RF_I32), the padded int64
+                             // constants (RF_I64), the value -> bucket table of uint16 (RF_IDX)
+    int32_t exact_off;       // RF_F64*: the m constants as doubles, read only when a value's key equals a constant's
+    int32_t idx_span;        // RF_IDX: last index of the table (values are clamped to [idx_base, idx_base + idx_span])
+    long long idx_base;
     int32_t lut_off, lut_size, other_bucket;      // RF_CODE: code -> bucket
     int32_t null_bucket;
     int32_t tab_off;         // byte offset of this space's truth table in the image
     int32_t row_bytes;       // bytes per bucket: the A and / or O vectors (WS words each), padded to an odd number of 16-byte slots
     int32_t role_mask;       // bit 0: has an A vector, bit 1: has an O vector
-    int32_t vbit;            // bit of the shared validity mask; -1: never NULL
+    uint32_t vbitmask;       // this column's bit in the shared validity mask; 0: never NULL
     int32_t stage_off;       // byte offset of the column's slot in a stage buffer
-    int32_t pad;
 };
 struct RFDev {
     RFSpace sp[RF_MAX_SPACES];
     int32_t ns, words, image_bytes, stage_bytes;
+    int32_t search_steps, pad0;              // steps of the key search the instantiation that runs makes (6 or 8)
     const uint8_t* image;
     const void* vmask; int32_t vwidth, vmask_stage_off;
     uint32_t bias_o[8];      // rules without an OR group
 };
 
-template <int W, bool STAGED>
+template <int W, int KS, bool STAGED>
 __global__ void __launch_bounds__(RF_NT, RF_MIN_CTAS) k2_rules_fast(const __grid_constant__ RFDev D, long long n_rows, const long long* sel, uint32_t* flags) {
     constexpr int WS = W <= 1 ? 1 : (W <= 2 ? 2 : (W <= 4 ? 4 : 8));      // words a (row, role) entry occupies
     extern __shared__ __align__(128) uint8_t fsm[];
@@ -492,28 +496,54 @@ __global__ void __launch_bounds__(RF_NT, RF_MIN_CTAS) k2_rules_fast(const __grid
                 else v = full ? reinterpret_cast<const long long*>(stg + sp.stage_off)[tid] : reinterpret_cast<const long long*>(sp.data)[row];
                 int b;
                 const uint8_t* c = fsm + sp.const_off;
+                if (sp.domain > RF_I32) {
                 if (sp.domain == RF_CODE) {
                     b = (v >= 0 && v < sp.lut_size) ? reinterpret_cast<const int32_t*>(fsm + sp.lut_off)[(int)v] : sp.other_bucket;
-                } else if (sp.domain == RF_I32) {
-                    const int x = v < -2147483647ll - 1 ? (-2147483647 - 1) : (v > 2147483647ll ? 2147483647 : (int)v);
-                    int lo = 0;                                        // bytes
-                    for (int step = sp.top; step >= 4; step >>= 1) if (*reinterpret_cast<const int*>(c + lo + step - 4) < x) lo += step;
-                    const bool eq = lo < sp.m * 4 && *reinterpret_cast<const int*>(c + lo) == x;
-                    b = (lo >> 1) + (eq ? 1 : 0);                      // 2 * (lo / 4) + eq
-                } else if (sp.domain == RF_I64) {
+                } else if (sp.domain == RF_IDX) {
+                    // a small integer range (status codes, hours, enumerations): the bucket of every value in it, tabulated
+                    long long d = v - sp.idx_base;
+                    d = d < 0 ? 0 : (d > sp.idx_span ? (long long)sp.idx_span : d);
+                    b = reinterpret_cast<const uint16_t*>(c)[(int)d];
+                } else {      // RF_I64
                     int lo = 0;
                     for (int step = sp.top; step >= 8; step >>= 1) if (*reinterpret_cast<const long long*>(c + lo + step - 8) < v) lo += step;
                     const bool eq = lo < sp.m * 8 && *reinterpret_cast<const long long*>(c + lo) == v;
                     b = (lo >> 2) + (eq ? 1 : 0);                      // 2 * (lo / 8) + eq
-                } else {
-                    const double x = sp.domain == RF_F64 ? __longlong_as_double(v) : (double)v;
-                    int lo = 0;
-                    for (int step = sp.top; step >= 8; step >>= 1) if (*reinterpret_cast<const double*>(c + lo + step - 8) < x) lo += step;
-                    const bool eq = lo < sp.m * 8 && *reinterpret_cast<const double*>(c + lo) == x;
-                    b = (lo >> 2) + (eq ? 1 : 0);
-                    if (x != x) b = 2 * sp.m;                          // NaN is greater than every constant
                 }
-                if (sp.vbit >= 0 && !((vm >> sp.vbit) & 1u)) b = sp.null_bucket;
+                } else {
+                    // One search for every other numeric column: KS fully unrolled steps over 2^KS - 1 order-preserving 32-bit keys
+                    // (padded with 0xFFFFFFFF, which no value's key exceeds).  An int64 value is clamped into the int32 range the
+                    // constants lie strictly inside; a double is represented by the top half of its order-preserving bit pattern,
+                    // which decides every comparison except against a constant with the same top half — only then are the exact
+                    // doubles compared.
+                    uint32_t key; double x = 0.0; bool isnan = false;
+                    const bool is_int = sp.domain == RF_I32;
+                    if (is_int) {
+                        const int xi = v < -2147483647ll - 1 ? (-2147483647 - 1) : (v > 2147483647ll ? 2147483647 : (int)v);
+                        key = (uint32_t)xi ^ 0x80000000u;
+                    } else {
+                        x = (sp.domain == RF_F64 ? __longlong_as_double(v) : (double)v) + 0.0;      // -0.0 -> +0.0
+                        isnan = x != x;
+                        const int hi = __double2hiint(x);
+                        key = (uint32_t)hi ^ ((uint32_t)(hi >> 31) | 0x80000000u);
+                    }
+                    const uint32_t* ck = reinterpret_cast<const uint32_t*>(c);
+                    uint32_t lo = 0;
+#pragma unroll
+                    for (int k = KS - 1; k >= 0; k--) if (ck[lo + (1u << k) - 1u] < key) lo += 1u << k;
+                    bool eq = false;
+                    if ((int)lo < sp.m && ck[lo] == key) {
+                        if (is_int) eq = true;
+                        else {
+                            const double* cd = reinterpret_cast<const double*>(fsm + sp.exact_off);
+                            while ((int)lo < sp.m && ck[lo] == key && cd[lo] < x) lo++;
+                            eq = (int)lo < sp.m && cd[lo] == x;
+                        }
+                    }
+                    b = (int)(2u * lo) + (eq ? 1 : 0);
+                    if (isnan) b = 2 * sp.m;                           // NaN is greater than every constant
+                }
+                if (~vm & sp.vbitmask) b = sp.null_bucket;
                 const uint8_t* tr = fsm + sp.tab_off + b * sp.row_bytes;
                 uint32_t x8[8];
                 auto fetch = [&]() {
@@ -540,8 +570,9 @@ __global__ void __launch_bounds__(RF_NT, RF_MIN_CTAS) k2_rules_fast(const __grid
                     for (int w = 0; w < W; w++) TO[w] |= x8[w];
                 }
             }
+            uint32_t* op = flags + i;
 #pragma unroll
-            for (int w = 0; w < W; w++) flags[(long long)w * n_rows + i] = TA[w] & TO[w];
+            for (int w = 0; w < W; w++) { *op = TA[w] & TO[w]; op += n_rows; }
         }
         if (STAGED) {
             __syncthreads();        // the tile's buffer is refilled next: every reader must be done
@@ -792,28 +823,34 @@ static void launch_rules(dx_ctx* ctx, const RulesDev& D, size_t smem, int64_t n_
     k2_rules_bucket<J, NEEDF, NSMAX, STAGED><<<(unsigned)blocks, 256, smem, ctx->stream>>>(D, n_rows, reinterpret_cast<const long long*>(sel), flags);
 }
 
-template <int W, bool STAGED>
+template <int W, int KS, bool STAGED>
 static void launch_fast_w(dx_ctx* ctx, const RFDev& D, size_t smem, int64_t n_rows, const int64_t* sel, uint32_t* flags) {
-    cudaFuncSetAttribute(k2_rules_fast<W, STAGED>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaFuncSetAttribute(k2_rules_fast<W, KS, STAGED>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     int occ = 1;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k2_rules_fast<W, STAGED>, RF_NT, smem);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k2_rules_fast<W, KS, STAGED>, RF_NT, smem);
     if (occ < 1) occ = 1;
     long long blocks = (n_rows + RF_NT - 1) / RF_NT, cap = (long long)ctx->sm_count * occ;
     if (blocks > cap) blocks = cap;
-    k2_rules_fast<W, STAGED><<<(unsigned)blocks, RF_NT, smem, ctx->stream>>>(D, n_rows, reinterpret_cast<const long long*>(sel), flags);
+    k2_rules_fast<W, KS, STAGED><<<(unsigned)blocks, RF_NT, smem, ctx->stream>>>(D, n_rows, reinterpret_cast<const long long*>(sel), flags);
+}
+// instantiated for every flag-word count from 1 to 8 and for searches of 6 or 8 steps
+template <int KS, bool STAGED>
+static void launch_fast_k(dx_ctx* ctx, const RFDev& D, size_t smem, int64_t n_rows, const int64_t* sel, uint32_t* flags) {
+    switch (D.words) {
+    case 1: launch_fast_w<1, KS, STAGED>(ctx, D, smem, n_rows, sel, flags); break;
+    case 2: launch_fast_w<2, KS, STAGED>(ctx, D, smem, n_rows, sel, flags); break;
+    case 3: launch_fast_w<3, KS, STAGED>(ctx, D, smem, n_rows, sel, flags); break;
+    case 4: launch_fast_w<4, KS, STAGED>(ctx, D, smem, n_rows, sel, flags); break;
+    case 5: launch_fast_w<5, KS, STAGED>(ctx, D, smem, n_rows, sel, flags); break;
+    case 6: launch_fast_w<6, KS, STAGED>(ctx, D, smem, n_rows, sel, flags); break;
+    case 7: launch_fast_w<7, KS, STAGED>(ctx, D, smem, n_rows, sel, flags); break;
+    default: launch_fast_w<8, KS, STAGED>(ctx, D, smem, n_rows, sel, flags); break;
+    }
 }
 template <bool STAGED>
 static void launch_fast(dx_ctx* ctx, const RFDev& D, size_t smem, int64_t n_rows, const int64_t* sel, uint32_t* flags) {
-    switch (D.words) {
-    case 1: launch_fast_w<1, STAGED>(ctx, D, smem, n_rows, sel, flags); break;
-    case 2: launch_fast_w<2, STAGED>(ctx, D, smem, n_rows, sel, flags); break;
-    case 3: launch_fast_w<3, STAGED>(ctx, D, smem, n_rows, sel, flags); break;
-    case 4: launch_fast_w<4, STAGED>(ctx, D, smem, n_rows, sel, flags); break;
-    case 5: launch_fast_w<5, STAGED>(ctx, D, smem, n_rows, sel, flags); break;
-    case 6: launch_fast_w<6, STAGED>(ctx, D, smem, n_rows, sel, flags); break;
-    case 7: launch_fast_w<7, STAGED>(ctx, D, smem, n_rows, sel, flags); break;
-    default: launch_fast_w<8, STAGED>(ctx, D, smem, n_rows, sel, flags); break;
-    }
+    if (D.search_steps <= 6) launch_fast_k<6, STAGED>(ctx, D, smem, n_rows, sel, flags);
+    else launch_fast_k<8, STAGED>(ctx, D, smem, n_rows, sel, flags);
 }
 // fills the per-batch parts of a fast plan (column pointers, validity mask, staging layout) and launches it
 static int fast_launch(dx_ctx* ctx, RFDev D, const std::vector<ProgCol>& cols, int64_t n_rows, const int64_t* sel, uint32_t* flags, bool no_staging, bool* ok) {
@@ -824,8 +861,8 @@ static int fast_launch(dx_ctx* ctx, RFDev D, const std::vector<ProgCol>& cols, i
         if (cols[k].width != (D.sp[k].domain == RF_CODE ? 4 : 8)) { ctx->counters["k2_fast_reject_width"]++; return DX_OK; }
         if (cols[k].vmask) {
             if (vm && cols[k].vmask != vm) { ctx->counters["k2_fast_reject_vmask"]++; return DX_OK; }          // one validity array for all referenced columns (the decoder's), or the class kernel
-            vm = cols[k].vmask; vw = cols[k].vwidth; D.sp[k].vbit = cols[k].vbit;
-        } else D.sp[k].vbit = -1;
+            vm = cols[k].vmask; vw = cols[k].vwidth; D.sp[k].vbitmask = 1u << cols[k].vbit;
+        } else D.sp[k].vbitmask = 0;
     }
     if (vm && vw != 1 && vw != 4) return DX_OK;
     D.vmask = vm; D.vwidth = vw;
@@ -1050,9 +1087,10 @@ int dx_rules_eval(dx_ctx* ctx, const BindScope& sc, const std::vector<ExprP>& co
             }
             std::vector<uint8_t> image;
             auto align_to = [&](size_t a) { while (image.size() % a) image.push_back(0); };
+            int max_steps = 0; std::vector<int> key_spaces;
             for (size_t s2 = 0; s2 < P.spaces.size() && fits; s2++) {
                 SpaceDef& sp = P.spaces[s2]; RFSpace& d = FD.sp[s2];
-                d.null_bucket = sp.null_bucket; d.other_bucket = sp.other_bucket; d.vbit = -1;
+                d.null_bucket = sp.null_bucket; d.other_bucket = sp.other_bucket; d.vbitmask = 0;
                 if (sp.domain == DOM_CODE) {
                     d.domain = RF_CODE;
                     align_to(4);
@@ -1060,23 +1098,56 @@ int dx_rules_eval(dx_ctx* ctx, const BindScope& sc, const std::vector<ExprP>& co
                     for (int k = 0; k < sdev[s2].lut_size; k++) { int32_t v = all_luts[sdev[s2].lut_off + k]; const uint8_t* b = reinterpret_cast<const uint8_t*>(&v); image.insert(image.end(), b, b + 4); }
                 } else {
                     const int m = (int)sp.consts.size();
-                    int Pm = 0; while (Pm < m) Pm = Pm * 2 + 1;                       // 2^k - 1 >= m
+                    d.m = m;
                     bool narrow = sp.domain == DOM_I64;
                     if (narrow) for (long long cv : sp.consts) if (cv <= -2147483647ll || cv >= 2147483647ll) narrow = false;
-                    d.domain = sp.domain == DOM_F64 ? RF_F64 : (sp.domain == DOM_F64_FROM_I64 ? RF_F64_FROM_I64 : (narrow ? RF_I32 : RF_I64));
-                    const int esz = d.domain == RF_I32 ? 4 : 8;
-                    d.m = m; d.top = ((Pm + 1) / 2) * esz; if (m == 0) d.top = 0;
-                    align_to(8);
-                    d.const_off = (int)image.size();
-                    for (int k = 0; k <= Pm; k++) {                                     // Pm + 1 entries: the equality probe may look one past the last step
-                        if (esz == 4) { int32_t v = k < m ? (int32_t)sp.consts[k] : 2147483647; const uint8_t* b = reinterpret_cast<const uint8_t*>(&v); image.insert(image.end(), b, b + 4); }
-                        else {
-                            long long v = k < m ? sp.consts[k] : (d.domain == RF_I64 ? 0x7FFFFFFFFFFFFFFFll : 0x7FF8000000000000ll);   // int64 max / NaN: never below any value
-                            const uint8_t* b = reinterpret_cast<const uint8_t*>(&v); image.insert(image.end(), b, b + 8);
+                    auto put = [&](const void* ptr, size_t n) { const uint8_t* b = reinterpret_cast<const uint8_t*>(ptr); image.insert(image.end(), b, b + n); };
+                    if (sp.domain == DOM_I64 && m > 0 && sp.consts.back() - sp.consts.front() <= 1020 && 2 * m + 2 < 65536) {
+                        // small range: bucket of every integer from one below the least constant to one above the greatest
+                        d.domain = RF_IDX; d.idx_base = sp.consts.front() - 1; d.idx_span = (int)(sp.consts.back() + 1 - d.idx_base);
+                        align_to(4);
+                        d.const_off = (int)image.size();
+                        for (long long u = d.idx_base; u <= d.idx_base + d.idx_span; u++) {
+                            const int lo = (int)(std::lower_bound(sp.consts.begin(), sp.consts.end(), u) - sp.consts.begin());
+                            const uint16_t bk = (uint16_t)(2 * lo + ((lo < m && sp.consts[lo] == u) ? 1 : 0));
+                            put(&bk, 2);
+                        }
+                    } else if (sp.domain == DOM_I64 && !narrow) {
+                        d.domain = RF_I64;
+                        int Pm = 0; while (Pm < m) Pm = Pm * 2 + 1;                       // 2^k - 1 >= m
+                        d.top = ((Pm + 1) / 2) * 8; if (m == 0) d.top = 0;
+                        align_to(8);
+                        d.const_off = (int)image.size();
+                        for (int k = 0; k <= Pm; k++) { long long v = k < m ? sp.consts[k] : 0x7FFFFFFFFFFFFFFFll; put(&v, 8); }   // one extra entry: the equality probe
+                    } else {
+                        d.domain = sp.domain == DOM_F64 ? RF_F64 : (sp.domain == DOM_F64_FROM_I64 ? RF_F64_FROM_I64 : RF_I32);
+                        int ks = 0; while ((1 << ks) - 1 < m) ks++;
+                        max_steps = std::max(max_steps, ks);
+                        key_spaces.push_back((int)s2);
+                        if (d.domain != RF_I32) {
+                            align_to(8);
+                            d.exact_off = (int)image.size();
+                            for (int k = 0; k < m; k++) { double cv; memcpy(&cv, &sp.consts[k], 8); cv += 0.0; put(&cv, 8); }
                         }
                     }
                 }
             }
+            if (max_steps > 8) { fits = false; ctx->counters["k2_fast_reject_consts"]++; }
+            FD.search_steps = max_steps <= 6 ? 6 : 8;
+            for (int s2 : key_spaces) {           // 2^KS search keys per space (the last one is only ever the equality probe's)
+                SpaceDef& sp = P.spaces[s2]; RFSpace& d = FD.sp[s2];
+                align_to(4);
+                d.const_off = (int)image.size();
+                for (int k = 0; k < (1 << FD.search_steps); k++) {
+                    uint32_t key = 0xFFFFFFFFu;
+                    if (k < d.m) {
+                        if (d.domain == RF_I32) key = (uint32_t)(int32_t)sp.consts[k] ^ 0x80000000u;
+                        else { double cv; memcpy(&cv, &sp.consts[k], 8); cv += 0.0; long long bits; memcpy(&bits, &cv, 8); const int hi = (int)(bits >> 32); key = (uint32_t)hi ^ ((uint32_t)(hi >> 31) | 0x80000000u); }
+                    }
+                    const uint8_t* b = reinterpret_cast<const uint8_t*>(&key); image.insert(image.end(), b, b + 4);
+                }
+            }
+            if (fits) {
             // truth tables: per space and bucket the A vector (if any rule has an AND-leaf here) then the O vector, WS words each
             for (size_t s2 = 0; s2 < P.spaces.size(); s2++) {
                 SpaceDef& sp = P.spaces[s2]; RFSpace& d = FD.sp[s2];
@@ -1135,6 +1206,7 @@ int dx_rules_eval(dx_ctx* ctx, const BindScope& sc, const std::vector<ExprP>& co
                     *used_fast = true;
                     return DX_OK;
                 }
+            }
             }
         }
     }
