@@ -185,7 +185,7 @@ def run_ours(args):
                 counts, rec_bytes = dx.parallel.pack_by_key(table, COLS, COLS[:2], world, send.data_ptr())
                 recv_counts = dx.parallel.exchange_counts(counts)
                 ctx.synchronize()          # the pack runs on the library's stream, the collective on torch's
-                recv = dx.parallel.exchange_records(send, counts, recv_counts, rec_words)
+                recv = dx.parallel.exchange_records(send[: int(counts.sum()) * rec_words], counts, recv_counts, rec_words)
                 torch.cuda.synchronize()
                 n_recv, recv_ptr, self.keep = int(recv_counts.sum()), recv.data_ptr(), recv
             self.wire += int((counts.sum() - counts[rank]) * 8 * rec_words)
