@@ -1,6 +1,7 @@
 // dx_abi.cu — extern "C" entry points of libdxgpu.so (see include/dxgpu.h).
 #include "dx_common.h"
 #include "dx_abi_types.h"
+#include <memory>
 #include "dx_decode_host.h"
 #include "dx_flow.h"
 #include "dx_rules.h"
@@ -36,6 +37,7 @@ void dx_ctx_destroy(dx_ctx* c) {
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     cudaStreamDestroy(c->stream);
+    if (c->copy_stream) { cudaStreamSynchronize(c->copy_stream); cudaStreamDestroy(c->copy_stream); }
     delete c;
 }
 const char* dx_ctx_last_error(const dx_ctx* c) { return c ? c->last_error.c_str() : "null context"; }
@@ -298,6 +300,43 @@ int dx_flow_process_batch(dx_flow* f, const char* name_space, const uint8_t* jso
     cudaSetDevice(f->ctx->device);
     try { return f->process(name_space ? name_space : "", json, n_bytes, offsets, n_events, memory_kind, batch_time_ms, interval_ms, now_ms, out); }
     catch (std::exception& e) { return f->ctx->set_error(DX_ERR_STATE, e.what()); }
+}
+// ---- ingest running ahead of the processor -------------------------------------------------------
+struct dx_staged { dx_ctx* ctx = nullptr; DevBuf buf; int64_t n_bytes = 0; cudaEvent_t done = nullptr; };
+int dx_flow_stage_batch(dx_flow* f, const uint8_t* json_host, int64_t n_bytes, dx_staged** out) {
+    if (!f || !out || n_bytes < 0 || (n_bytes > 0 && !json_host)) return DX_ERR_ARG;
+    dx_ctx* c = f->ctx;
+    cudaSetDevice(c->device);
+    if (!c->copy_stream) DX_CUDA(c, cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+    std::unique_ptr<dx_staged> st(new dx_staged());
+    st->ctx = c; st->n_bytes = n_bytes;
+    st->buf = DevBuf(c, (size_t)n_bytes + 64);
+    if (!st->buf.p) return c->set_error(DX_ERR_CUDA, "dx_flow_stage_batch: device allocation failed");
+    DX_CUDA(c, cudaEventCreateWithFlags(&st->done, cudaEventDisableTiming));
+    if (n_bytes) DX_CUDA(c, cudaMemcpyAsync(st->buf.p, json_host, (size_t)n_bytes, cudaMemcpyHostToDevice, c->copy_stream));
+    DX_CUDA(c, cudaEventRecord(st->done, c->copy_stream));
+    *out = st.release();
+    return DX_OK;
+}
+void dx_staged_release(dx_staged* st) {
+    if (!st) return;
+    cudaSetDevice(st->ctx->device);
+    if (st->done) { cudaEventSynchronize(st->done); cudaEventDestroy(st->done); }      // the copy must not outlive its target
+    delete st;
+}
+int dx_flow_process_staged(dx_flow* f, const char* name_space, dx_staged* st, int64_t n_events, int64_t batch_time_ms, int64_t interval_ms,
+                           int64_t output_partition_time_ms, int64_t now_ms, dx_result** out) {
+    if (!f || !out || !st || st->ctx != f->ctx) return DX_ERR_ARG;
+    (void)output_partition_time_ms;
+    dx_ctx* c = f->ctx;
+    cudaSetDevice(c->device);
+    DX_CUDA(c, cudaStreamWaitEvent(c->stream, st->done, 0));      // the processor's stream waits on the device; the host does not
+    int rc;
+    try { rc = f->process(name_space ? name_space : "", st->buf.as<uint8_t>(), st->n_bytes, nullptr, n_events, DX_MEM_DEVICE, batch_time_ms, interval_ms, now_ms, out); }
+    catch (std::exception& e) { rc = c->set_error(DX_ERR_STATE, e.what()); }
+    cudaStreamSynchronize(c->stream);       // every reader of the staged bytes is done before the buffer returns to the pool
+    dx_staged_release(st);
+    return rc;
 }
 int dx_result_metrics(dx_result* r, const char* const** keys, const double** vals, int* n) {
     *keys = r->metric_key_ptrs.data(); *vals = r->metric_vals.data(); *n = (int)r->metric_vals.size();

@@ -50,6 +50,7 @@ struct DxPool {
 struct dx_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
+    cudaStream_t copy_stream = nullptr;            // created on first use: host->device copies that run ahead of the processor (dx_flow_stage_batch)
     DxPool pool;
     std::string last_error;
     int sm_count = 148;
@@ -59,6 +60,7 @@ struct dx_ctx {
     std::map<std::string, long long> launches;
     std::map<std::string, long long> counters;     // work counters (rows visited by K3, rows moved by K4 ...)
     size_t k3p_scatter_smem_configured = 0;
+    size_t k5_put_smem_configured = 0;
     size_t k3p_smem_configured = 0;                 // dynamic shared memory k3p_aggregate is configured for on this device
     int set_error(int code, const std::string& msg) { last_error = msg; return code; }
 };

@@ -144,6 +144,83 @@ __global__ void __launch_bounds__(256) k5_scatter_put_staged(const __grid_consta
     }
 }
 
+// The form that normally runs, for the fused put and for the local pack alike: a CTA takes a tile of PT_TILE rows, counts them
+// per owner in shared memory (one shared atomic per warp and owner), reserves each owner's run in that owner's buffer with ONE
+// global atomic per owner per tile, lays the records down in shared memory sorted by owner, and copies the staging area out
+// with consecutive lanes writing consecutive 8-byte words: every owner receives one contiguous run per tile (128 records =
+// 5 KB at 8 owners), so the stores that cross NVLink are full lines instead of the per-warp fragments of a few records the
+// warp-staged kernel above produces, and the source columns are read four rows per thread with the loads in flight together.
+#define PT_NT 256
+#define PT_RPT 4
+#define PT_TILE (PT_NT * PT_RPT)
+__global__ void __launch_bounds__(PT_NT) k5_put_tiled(const __grid_constant__ ShuffleArgs a, const __grid_constant__ PutTargets tg, unsigned long long* cursor) {
+    extern __shared__ __align__(16) unsigned long long pt_stage[];       // PT_TILE x rec_words words, then PT_TILE destination pointers
+    __shared__ unsigned int s_cnt[DX_SHUFFLE_MAX_WORLD], s_base[DX_SHUFFLE_MAX_WORLD + 1];
+    __shared__ unsigned long long s_gstart[DX_SHUFFLE_MAX_WORLD];
+    const int rw = a.n_cols + 1, tid = threadIdx.x, lane = tid & 31;
+    unsigned long long** s_dst = reinterpret_cast<unsigned long long**>(pt_stage + (size_t)PT_TILE * rw);
+    const long long n_tiles = (a.n_rows + PT_TILE - 1) / PT_TILE;
+    for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        if (tid < a.world) s_cnt[tid] = 0;
+        __syncthreads();
+        int dst[PT_RPT]; unsigned int rank[PT_RPT];
+#pragma unroll
+        for (int j = 0; j < PT_RPT; j++) {
+            const long long i = tile * PT_TILE + (long long)j * PT_NT + tid;
+            dst[j] = i < a.n_rows ? owner_of(a, i) : -1;
+        }
+#pragma unroll
+        for (int j = 0; j < PT_RPT; j++) {
+            const unsigned peers = __match_any_sync(0xffffffffu, dst[j]);
+            const int leader = __ffs(peers) - 1;
+            unsigned int start = 0;
+            if (dst[j] >= 0 && lane == leader) start = atomicAdd(&s_cnt[dst[j]], (unsigned int)__popc(peers));
+            start = __shfl_sync(0xffffffffu, start, leader);
+            rank[j] = start + __popc(peers & ((1u << lane) - 1u));
+        }
+        __syncthreads();
+        if (tid == 0) { unsigned int acc = 0; for (int d = 0; d < a.world; d++) { s_base[d] = acc; acc += s_cnt[d]; } s_base[a.world] = acc; }
+        if (tid < a.world && s_cnt[tid]) s_gstart[tid] = atomicAdd(&cursor[tid], (unsigned long long)s_cnt[tid]);
+        __syncthreads();
+#pragma unroll
+        for (int j = 0; j < PT_RPT; j++) {
+            if (dst[j] < 0) continue;
+            const long long i = tile * PT_TILE + (long long)j * PT_NT + tid;
+            const unsigned int slot = s_base[dst[j]] + rank[j];
+            unsigned long long* r = pt_stage + (size_t)slot * rw;
+            unsigned long long valid = 0;
+            for (int c = 0; c < a.n_cols; c++) {
+                long long v; if (sh_load(a.cols[c], i, v)) valid |= 1ull << c;
+                r[c] = (unsigned long long)v;
+            }
+            r[a.n_cols] = valid;
+            s_dst[slot] = tg.base[dst[j]] + (tg.first[dst[j]] + s_gstart[dst[j]] + rank[j]) * rw;
+        }
+        __syncthreads();
+        const unsigned int n_words = s_base[a.world] * (unsigned int)rw;
+        for (unsigned int f = tid; f < n_words; f += PT_NT) {
+            const unsigned int slot = f / (unsigned int)rw, w = f - slot * (unsigned int)rw;
+            s_dst[slot][w] = pt_stage[f];
+        }
+        __syncthreads();
+    }
+}
+static size_t pt_smem(int rec_words) { return (size_t)PT_TILE * rec_words * 8 + (size_t)PT_TILE * 8; }
+static int pt_launch(dx_ctx* ctx, const ShuffleArgs& a, const PutTargets& tg, unsigned long long* cursor) {
+    const size_t smem = pt_smem(a.n_cols + 1);
+    if (smem > ctx->k5_put_smem_configured) {
+        DX_CUDA(ctx, cudaFuncSetAttribute(k5_put_tiled, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        ctx->k5_put_smem_configured = smem;
+    }
+    int occ = 1;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k5_put_tiled, PT_NT, smem);
+    if (occ < 1) occ = 1;
+    long long blocks = (a.n_rows + PT_TILE - 1) / PT_TILE, cap = (long long)ctx->sm_count * occ;
+    if (blocks > cap) blocks = cap;
+    k5_put_tiled<<<(unsigned)blocks, PT_NT, smem, ctx->stream>>>(a, tg, cursor);
+    return DX_OK;
+}
+
 __global__ void __launch_bounds__(256) k5_unpack(const unsigned long long* packed, long long n_rows, int n_cols, UnpackCols cols, uint32_t* vmask32) {
     const int rec_words = n_cols + 1;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_rows; i += (long long)gridDim.x * blockDim.x) {
@@ -192,7 +269,8 @@ int dx_shuffle_put(dx_ctx* ctx, const DxTable* t, const std::vector<int>& cols, 
     {
         StageTimer tm(ctx, "k5_scatter_put");
         const int rec_words = a.n_cols + 1;
-        if (rec_words <= 16) k5_scatter_put_staged<<<grid_of(ctx, t->n_rows), 256, (size_t)8 * 32 * rec_words * 8, ctx->stream>>>(a, tg, cur.as<unsigned long long>());
+        if (rec_words <= 12) { rc = pt_launch(ctx, a, tg, cur.as<unsigned long long>()); if (rc) return rc; }
+        else if (rec_words <= 16) k5_scatter_put_staged<<<grid_of(ctx, t->n_rows), 256, (size_t)8 * 32 * rec_words * 8, ctx->stream>>>(a, tg, cur.as<unsigned long long>());
         else k5_scatter_put<<<grid_of(ctx, t->n_rows), 256, 0, ctx->stream>>>(a, tg, cur.as<unsigned long long>());
         ctx->launches["k5_scatter_put"]++;
     }
@@ -250,7 +328,11 @@ int dx_shuffle_pack(dx_ctx* ctx, const DxTable* t, const std::vector<int>& cols,
     DX_CUDA(ctx, cudaMemcpyAsync(base, hb, world * 8, cudaMemcpyHostToDevice, ctx->stream));
     {
         StageTimer tm(ctx, "k5_scatter");
-        k5_scatter<<<grid_of(ctx, t->n_rows), 256, 0, ctx->stream>>>(a, base, cursor, reinterpret_cast<unsigned long long*>(packed_dev));
+        if (a.n_cols + 1 <= 12) {      // the tiled kernel with every owner's run in the one local buffer
+            PutTargets tg; memset(&tg, 0, sizeof tg);
+            for (int r = 0; r < world; r++) { tg.base[r] = reinterpret_cast<unsigned long long*>(packed_dev); tg.first[r] = hb[r]; }
+            int rc2 = pt_launch(ctx, a, tg, cursor); if (rc2) return rc2;
+        } else k5_scatter<<<grid_of(ctx, t->n_rows), 256, 0, ctx->stream>>>(a, base, cursor, reinterpret_cast<unsigned long long*>(packed_dev));
         ctx->launches["k5_scatter"]++;
     }
     DX_CUDA(ctx, cudaGetLastError());

@@ -188,6 +188,25 @@ class CommonProcessor:
             now_ms if now_ms is not None else batch_time_ms, C.byref(r)))
         return BatchResult(self.ctx, r)
 
+    def stage_json(self, host_ptr, n_bytes):
+        """Starts the host->device copy of the NEXT batch (page-locked host memory at host_ptr) and returns a handle for
+        process_staged; the copy overlaps whatever the processor is doing meanwhile."""
+        fn = self.L.dx_flow_stage_batch
+        fn.restype, fn.argtypes = C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.POINTER(C.c_void_p)]
+        h = C.c_void_p()
+        self.ctx.check(fn(self.h, C.c_void_p(host_ptr), n_bytes, C.byref(h)))
+        return h
+
+    def process_staged(self, staged, batch_time_ms, batch_interval_ms, namespace="", now_ms=None, n_events=-1) -> BatchResult:
+        """processJson on a batch whose copy was started with stage_json (the handle is consumed)."""
+        fn = self.L.dx_flow_process_staged
+        fn.restype = C.c_int
+        fn.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.POINTER(C.c_void_p)]
+        r = C.c_void_p()
+        self.ctx.check(fn(self.h, namespace.encode(), staged, n_events, batch_time_ms, batch_interval_ms, batch_time_ms,
+                          now_ms if now_ms is not None else batch_time_ms, C.byref(r)))
+        return BatchResult(self.ctx, r)
+
     def add_refdata(self, name, csv_text, delimiter=",", header=True):
         """Reference data view (ReferenceDataHandler.scala:42-60): CSV text, all columns strings."""
         fn = self.L.dx_flow_add_refdata

@@ -171,6 +171,20 @@ int dx_flow_process_batch(dx_flow* flow, const char* name_space, const uint8_t* 
                           const int64_t* offsets, int64_t n_events, int memory_kind,
                           int64_t batch_time_ms, int64_t interval_ms, int64_t output_partition_time_ms,
                           int64_t now_ms, dx_result** out);
+/* Ingest that runs ahead of the processor.  In the reference the receivers fill the next micro-batch while the job thread
+ * works on the current one (Spark Streaming's receiver / job split behind StreamingHost.scala:62-95); over PCIe that overlap
+ * is worth having, because copying a batch of JSON takes far longer than processing it.  dx_flow_stage_batch starts the
+ * host->device copy of one NDJSON batch on a side stream and returns at once; dx_flow_process_staged is
+ * dx_flow_process_batch on that batch (it makes the processor's stream wait for the copy on the device, consumes the
+ * handle and returns its device buffer to the pool).  json_host must stay unchanged until dx_flow_process_staged returns
+ * and should be page-locked (dx_host_alloc), or the copy is neither asynchronous nor at link speed.  A handle that is
+ * never processed is dropped with dx_staged_release.                                                                  */
+typedef struct dx_staged dx_staged;
+int dx_flow_stage_batch(dx_flow* flow, const uint8_t* json_host, int64_t n_bytes, dx_staged** out);
+int dx_flow_process_staged(dx_flow* flow, const char* name_space, dx_staged* staged, int64_t n_events,
+                           int64_t batch_time_ms, int64_t interval_ms, int64_t output_partition_time_ms,
+                           int64_t now_ms, dx_result** out);
+void dx_staged_release(dx_staged* staged);
 /* The Map[String, Double] processDataset returns (Input_Normalized_Events_Count, ...). */
 int dx_result_metrics(dx_result* r, const char* const** keys, const double** vals, int* n);
 int dx_result_num_tables(const dx_result* r);

@@ -502,3 +502,42 @@ def test_rule_widths_and_shapes_through_the_normal_form_kernel(dx, ctx):
             assert_same_rows(a.table("Rules"), ro["Rules"], dx, ordered=True)
             a.release(); b.release()
         g.close(); g2.close()
+
+
+def test_staged_ingest_equals_process_json(dx, ctx):
+    """dx_flow_stage_batch + dx_flow_process_staged (the copy of batch i+1 started before batch i is processed) give the
+    tables of dx_flow_process_batch on host memory, over a windowed flow whose state carries from batch to batch."""
+    import ctypes as C
+    conf = dx.flowgen.conf_text("stg", timestamp_column="eventTimeStamp", watermark="60 second",
+                                windows=[("DataXProcessedInput_3minutes", "3 minutes")])
+    tr = """--DataXQuery--
+K = SELECT deviceDetails.deviceId, COUNT(*) AS Count, MAX(deviceDetails.temperature) AS Tmax FROM DataXProcessedInput_3minutes GROUP BY deviceDetails.deviceId
+"""
+    g, o = both(dx, ctx, conf, SCHEMA2, [PROJ_TS], tr)
+    L = ctx.L
+    L.dx_host_alloc.restype, L.dx_host_alloc.argtypes = C.c_int, [C.c_void_p, C.c_int64, C.POINTER(C.c_void_p)]
+    L.dx_host_free.argtypes = [C.c_void_p, C.c_void_p]
+    batches = [gen(dx, 4000, first=b * 4000, shape=2, n_keys=300, base=T0 + b * I) for b in range(5)]
+    pinned = []
+    for data in batches:
+        hp = C.c_void_p()
+        ctx.check(L.dx_host_alloc(ctx.h, len(data), C.byref(hp)))
+        C.memmove(hp.value, data, len(data))
+        pinned.append(hp)
+    staged = g.stage_json(pinned[0].value, len(batches[0]))
+    for b, data in enumerate(batches):
+        nxt = g.stage_json(pinned[b + 1].value, len(batches[b + 1])) if b + 1 < len(batches) else None
+        rg = g.process_staged(staged, T0 + b * I, I)
+        ro, mo = o.process(data, T0 + b * I, I)
+        assert rg.metrics == mo
+        assert_same_rows(rg.table("K"), ro["K"], dx)
+        rg.release()
+        staged = nxt
+    # a handle that is never processed
+    extra = g.stage_json(pinned[0].value, len(batches[0]))
+    fn = L.dx_staged_release
+    fn.restype, fn.argtypes = None, [C.c_void_p]
+    fn(extra)
+    for hp in pinned:
+        L.dx_host_free(ctx.h, hp)
+    g.close()
