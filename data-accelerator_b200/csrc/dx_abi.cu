@@ -138,6 +138,7 @@ int dx_decoder_dict_string(dx_decoder* d, int column, int64_t code, const char**
     *bytes = hs[(size_t)code].data(); *len = (int64_t)hs[(size_t)code].size();
     return DX_OK;
 }
+int64_t dx_decoder_limited_rows(const dx_decoder* d) { return d ? (int64_t)d->last_stats.limited_rows : 0; }
 int dx_decoder_stats(const dx_decoder* d, int64_t* rows, int64_t* null_rows, int64_t* fast_rows) {
     if (rows) *rows = (int64_t)d->last_stats.rows;
     if (null_rows) *null_rows = (int64_t)d->last_stats.null_rows;

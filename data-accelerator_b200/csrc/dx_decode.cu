@@ -221,7 +221,7 @@ int dx_decoder::decode_device(const uint8_t* json_dev, int64_t n_bytes, const in
     }
     if (n_events == 0 || n_bytes == 0) {
         if (n_events > 0) DX_CUDA(c, cudaMemsetAsync(mask->p, 0, (size_t)n_events * mw, c->stream));
-        last_stats = DecodeStats{(unsigned long long)n_events, (unsigned long long)n_events, 0, 0};
+        last_stats = DecodeStats{(unsigned long long)n_events, (unsigned long long)n_events, 0, 0, 0};
         *out = t; return DX_OK;
     }
     uintptr_t addr = reinterpret_cast<uintptr_t>(json_dev);
@@ -251,10 +251,10 @@ int dx_decoder::decode_device(const uint8_t* json_dev, int64_t n_bytes, const in
     DX_CUDA(c, cudaGetLastError());
     DX_CUDA(c, cudaMemcpyAsync(&last_stats, dev_stats.p, sizeof(DecodeStats), cudaMemcpyDeviceToHost, c->stream));
     DX_CUDA(c, cudaStreamSynchronize(c->stream));
-    if (last_stats.flags) {
+    if (last_stats.flags & ~(unsigned long long)DXF_ROW_LIMITS) {      // per-record limits NULL the record (limited_rows); only these fail the call
         char b[256];
-        snprintf(b, sizeof b, "decode failed: flags=0x%llx (1 dictionary overflow, 2 number beyond 19-digit window, "
-                 "4 object/array into string field, 8 escaped string > %d bytes, 16 more records than n_events)",
+        snprintf(b, sizeof b, "decode failed: flags=0x%llx (1 dictionary overflow, 16 more records than n_events; "
+                 "2 / 4 / 8 only mark records this implementation could not take: %d-byte escaped strings, > 19-digit ties, nested values under a string field)",
                  last_stats.flags, DX_UNESC_CAP);
         return c->set_error((last_stats.flags & DXF_DICT_OVERFLOW) ? DX_ERR_CAPACITY : DX_ERR_UNSUPPORTED, b);
     }
@@ -301,7 +301,7 @@ int dx_decoder::decode_host(const uint8_t* json, int64_t n_bytes, const int64_t*
 // streams or threads) would race on it — callers serialise.
 // =======================================================================================
 #define DX_NOALLOC_MAX_TILES 65536                                   /* x 32 KiB tiles = 2 GiB of JSON per call */
-#define DX_NOALLOC_HEADER_WORDS 8                                    /* [0] tile counter, [2..5] DecodeStats */
+#define DX_NOALLOC_HEADER_WORDS 8                                    /* [0] tile counter, [2..6] DecodeStats */
 #define DX_NOALLOC_SCRATCH_WORDS (DX_NOALLOC_HEADER_WORDS + DX_NOALLOC_MAX_TILES + 2)
 #define DX_NOALLOC_SCRATCH_BYTES (DX_NOALLOC_SCRATCH_WORDS * 8)
 static __device__ __align__(256) unsigned long long dx_noalloc_scratch[DX_NOALLOC_SCRATCH_WORDS];
@@ -386,10 +386,9 @@ int dx_decoder::decode_noalloc(const uint8_t* json_dev, int64_t n_bytes, int64_t
     DX_CUDA(c, cudaMemcpyAsync(&st, a.stats, sizeof st, cudaMemcpyDeviceToHost, c->stream));
     DX_CUDA(c, cudaStreamSynchronize(c->stream));
     last_stats = st;
-    if (st.flags) {
+    if (st.flags & ~(unsigned long long)DXF_ROW_LIMITS) {
         char b[200];
-        snprintf(b, sizeof b, "decode_noalloc failed: flags=0x%llx (1 dictionary overflow, 2 number beyond 19-digit window, "
-                 "4 object/array into string field, 8 long escaped string, 16 more records than n_events)", st.flags);
+        snprintf(b, sizeof b, "decode_noalloc failed: flags=0x%llx (1 dictionary overflow, 16 more records than n_events)", st.flags);
         return c->set_error((st.flags & DXF_DICT_OVERFLOW) ? DX_ERR_CAPACITY : DX_ERR_UNSUPPORTED, b);
     }
     if ((int64_t)st.rows != n_events) {

@@ -20,6 +20,9 @@
 #define DXF_STRUCT_AS_STRING 4u  // object/array token for a string field (Spark re-serialises it)
 #define DXF_LONG_ESCAPED 8u      // escaped string longer than the unescape buffer
 #define DXF_ROW_OVERFLOW 16u     // more records than the caller said
+// Conditions that concern ONE record and that Spark would have parsed: the record becomes a NULL struct (as a malformed one
+// does), is counted in DecodeStats::limited_rows and reported as a metric — one odd or hostile event must not fail the batch.
+#define DXF_ROW_LIMITS (DXF_NUM_PRECISION | DXF_STRUCT_AS_STRING | DXF_LONG_ESCAPED)
 
 struct DField { uint16_t name_off, name_len; int32_t type; int32_t target; };
 struct DStruct { int32_t first_field, n_fields, first_leaf, n_leaves; };
@@ -39,6 +42,7 @@ struct DSchemaDev {
 
 struct DecodeStats {
     unsigned long long rows, null_rows, fast_rows, flags;
+    unsigned long long limited_rows;     // rows made NULL structs by a limit of this implementation (DXF_ROW_LIMITS), not by Spark's rules
 };
 
 struct DecodeArgs {

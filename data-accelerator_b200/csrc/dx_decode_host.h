@@ -9,7 +9,7 @@ struct dx_decoder {
     std::vector<int> leaf_types;
     std::vector<DxDictP> dicts;            // per leaf; null for non-string leaves
     DevBuf dev_schema, dev_dicts, dev_stats, tile_state, staging, staging_off;
-    DecodeStats last_stats{0, 0, 0, 0};
+    DecodeStats last_stats{0, 0, 0, 0, 0};
     uint32_t dict_capacity = 1u << 16;     // slots per string column (power of two)
     uint32_t dict_heap_bytes = 4u << 20;
     int ctas_per_sm = 1;

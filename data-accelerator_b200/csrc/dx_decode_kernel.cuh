@@ -118,7 +118,7 @@ __global__ void __launch_bounds__(K1_NT, FRAMED ? K1_MIN_CTAS_FRAMED : K1_MIN_CT
 
     const uint32_t n_leaves = (uint32_t)S->n_leaves;
     const uint32_t all_valid = (n_leaves >= 32) ? 0xFFFFFFFFu : ((1u << n_leaves) - 1u);
-    uint32_t c_rows = 0, c_null = 0, c_fast = 0, c_err = 0;    // per thread (a thread sees far fewer than 2^32 records); widened when added to the statistics
+    uint32_t c_rows = 0, c_null = 0, c_fast = 0, c_err = 0, c_lim = 0;    // per thread (a thread sees far fewer than 2^32 records); widened when added to the statistics
     uint32_t phase_bits = 0;     // bit k: parity the next completion of stage k will have
 
     // Stages one tile: bulk (TMA) copy of the 16-byte-aligned part onto the stage's mbarrier, the ragged
@@ -323,7 +323,7 @@ __global__ void __launch_bounds__(K1_NT, FRAMED ? K1_MIN_CTAS_FRAMED : K1_MIN_CT
                         else if (in_smem) ok = g_record(buf + st, buf + en, S, o);
                         else ok = g_record(a.base_al + lo + st, a.base_al + en_abs, S, o);
                         c_rows++; if (!ok) c_null++;
-                        c_err |= o.err;
+                        c_err |= o.err; if (o.err & DXF_ROW_LIMITS) c_lim++;
                         if (o.valid != all_valid) {
                             for (uint32_t k = 0; k < n_leaves; k++) if (!((o.valid >> k) & 1u)) {
                                 if (S->leaf_type[k] == DX_T_STR) reinterpret_cast<int32_t*>(a.cols[k])[o.row] = -1;
@@ -385,7 +385,7 @@ __global__ void __launch_bounds__(K1_NT, FRAMED ? K1_MIN_CTAS_FRAMED : K1_MIN_CT
                     else if (in_smem) ok = g_record(buf + st, buf + en, S, o);
                     else ok = g_record(a.base_al + st_abs, a.base_al + en_abs, S, o);
                     c_rows++; if (!ok) c_null++;
-                    c_err |= o.err;
+                    c_err |= o.err; if (o.err & DXF_ROW_LIMITS) c_lim++;
                     if (o.valid != all_valid) {
                         for (uint32_t k = 0; k < n_leaves; k++) if (!((o.valid >> k) & 1u)) {
                             if (S->leaf_type[k] == DX_T_STR) reinterpret_cast<int32_t*>(a.cols[k])[o.row] = -1;
@@ -412,12 +412,14 @@ __global__ void __launch_bounds__(K1_NT, FRAMED ? K1_MIN_CTAS_FRAMED : K1_MIN_CT
         c_null += __shfl_xor_sync(0xffffffffu, c_null, s);
         c_fast += __shfl_xor_sync(0xffffffffu, c_fast, s);
         c_err |= __shfl_xor_sync(0xffffffffu, c_err, s);
+        c_lim += __shfl_xor_sync(0xffffffffu, c_lim, s);
     }
     if (lane == 0) {
         if (c_rows) atomicAdd(&a.stats->rows, (unsigned long long)c_rows);
         if (c_null) atomicAdd(&a.stats->null_rows, (unsigned long long)c_null);
         if (c_fast) atomicAdd(&a.stats->fast_rows, (unsigned long long)c_fast);
         if (c_err) atomicOr(&a.stats->flags, (unsigned long long)c_err);
+        if (c_lim) atomicAdd(&a.stats->limited_rows, (unsigned long long)c_lim);
     }
 }
 

@@ -1775,7 +1775,9 @@ int dx_flow::process(const std::string& name_space, const uint8_t* json, int64_t
     int rc = project(json, n_bytes, offsets, n_events, memory_kind, now_ms, &projected);
     if (rc) return rc;
     const auto t1 = std::chrono::steady_clock::now();
+    pending_unparsed = (long long)decoder->last_stats.limited_rows;
     rc = route(name_space, projected, batch_ms, interval_ms, now_ms, out);
+    pending_unparsed = 0;
     ctx->counters["host_us:project"] += std::chrono::duration_cast<std::chrono::microseconds>(t1 - t0).count();
     ctx->counters["host_us:route"] += std::chrono::duration_cast<std::chrono::microseconds>(std::chrono::steady_clock::now() - t1).count();
     return rc;
@@ -1792,6 +1794,8 @@ int dx_flow::route(const std::string& name_space, const DxTableP& projected, lon
     Exec X{this, ctx, &views, now_ms * 1000, ""};
     // ---- route() (CPF:131-328)
     metric("Input_Normalized_Events_Count", (double)projected->n_rows);
+    // events Spark would have parsed that this decoder made NULL rows (dx_decoder_limited_rows); the key appears only when there are any
+    if (pending_unparsed > 0) metric("Input_Unparsed_Events_Count", (double)pending_unparsed);
     NamespaceState& NS = ns[name_space];
     if (windows_enabled) {
         const long long T = batch_ms;

@@ -115,6 +115,7 @@ struct dx_flow {
     std::map<std::string, Udf> udfs;                               // upper-cased name -> callback
     std::map<std::string, std::shared_ptr<LutCache>> luts;        // (expression, dictionary) -> device lookup table
     std::map<std::string, DxDictP> expr_dicts;                     // (statement, item) -> dictionary of a string-valued result, stable across batches
+    long long pending_unparsed = 0;    // decoder->last_stats.limited_rows of the batch being routed
     int rules_mode = 0;                // DX_RULES_* bits from conf datax.job.process.gpu.rulesstaging / .rulesfast (dx_rules.h)
     bool generic_rules_only = false;   // tests: force the bytecode interpreter for rule arrays (conf datax.job.process.gpu.genericrules=true)
     int project(const uint8_t* json, int64_t n_bytes, const int64_t* offsets, int64_t n_events, int memory_kind, long long now_ms, DxTableP* out);

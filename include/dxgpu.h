@@ -112,6 +112,11 @@ int dx_decoder_dict_size(dx_decoder* d, int column, int64_t* n_codes);
 int dx_decoder_dict_string(dx_decoder* d, int column, int64_t code, const char** bytes, int64_t* len);
 /* rows decoded / rows that became NULL structs / rows taken by the template fast path, last call */
 int dx_decoder_stats(const dx_decoder* d, int64_t* rows, int64_t* null_rows, int64_t* fast_rows);
+/* Records of the last call that Spark's from_json would have parsed but this decoder turned into NULL structs because they
+ * exceed one of its per-record limits (an object or array under a string field, an escaped string longer than
+ * 256 bytes, a number of more than 19 significant digits that sits exactly between two doubles).  They are counted in
+ * null_rows as well; the flow reports them as the metric Input_Unparsed_Events_Count.  Such a record never fails the batch. */
+int64_t dx_decoder_limited_rows(const dx_decoder* d);
 
 /* ---- tables ----------------------------------------------------------------------------- */
 /* What the Scala shim wraps into a DataFrame for the unchanged sinks

@@ -19,6 +19,7 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB = None
+last_limited = 0
 
 LONG, DOUBLE, STRING, BOOL, STRUCT = 1, 2, 3, 4, 5
 _TYPE = {"long": LONG, "integer": LONG, "int": LONG, "short": LONG, "byte": LONG, "double": DOUBLE,
@@ -164,8 +165,10 @@ def decode(schema: Schema, data: bytes, offsets=None, threads=0):
                               vals.ctypes.data_as(vp), lens.ctypes.data_as(vp), valid.ctypes.data_as(vp),
                               rowok.ctypes.data_as(vp), heap.ctypes.data_as(vp), C.c_int64(heap.size), C.byref(used))
     if rc < 0:
-        raise RuntimeError(f"oracle limitation hit (code {rc}): -2 heap, -3 object/array into string field")
-    out = {"__rowok": rowok[:n].astype(bool)}
+        raise RuntimeError(f"oracle limitation hit (code {rc}): -2 heap")
+    global last_limited
+    last_limited = int((rowok[:n] == 2).sum())       # rows made NULL by a limit of the restatement (nested value under a string field)
+    out = {"__rowok": rowok[:n] == 1}
     for k, name in enumerate(schema.leaf_names):
         v = valid[k, :n].astype(bool)
         t = schema.leaf_types[k]

@@ -59,6 +59,7 @@ typedef struct {
     uint8_t *heap;
     int64_t heap_used;
     int64_t heap_cap;
+    int limited;     /* the record being parsed hit a limit of the restatement, not a Spark rule */
 } dxo_ctx;
 
 typedef struct {
@@ -291,7 +292,8 @@ static int parse_leaf(dxo_ctx *x, cur_t *c, const dxo_field *f) {
     }
     if (b == '{' || b == '[') {
         /* string field: Spark re-serialises the structure; not restated */
-        return f->type == DXO_STRING ? -3 : -1;
+        if (f->type == DXO_STRING) x->limited = 1;   /* Spark re-serialises the nested value; not restated: the row becomes NULL and is counted */
+        return -1;
     }
     const uint8_t *s, *e; int isf, nn;
     if (scan_number(c, &s, &e, &isf, &nn)) return -1;
@@ -430,9 +432,10 @@ int64_t dxo_decode(const uint8_t *json, const int64_t *offsets, const int64_t *e
     for (int64_t i = 0; i < n; i++) {
         const uint8_t *s = json + offsets[i];
         const uint8_t *e = json + (ends ? ends[i] : offsets[i + 1]);
+        x.limited = 0;
         int r = decode_record(&x, s, e);
         if (r < 0) { rc = r; break; }
-        rowok[i] = (uint8_t)r;
+        rowok[i] = (uint8_t)(r == 1 ? 1 : (x.limited ? 2 : 0));     /* 2: NULL row by a limit of the restatement */
         for (int k = 0; k < n_leaves; k++) {
             vals[(int64_t)k * n + i] = x.valid[k] ? x.vals[k] : 0;
             lens[(int64_t)k * n + i] = x.valid[k] ? x.lens[k] : 0;
@@ -476,9 +479,10 @@ static void *mt_worker(void *p) {
         x.heap_used = 0; /* baseline keeps only the last string (dictionary coding is the product's job) */
         const uint8_t *s = a->json + a->offsets[i];
         const uint8_t *e = a->json + (a->ends ? a->ends[i] : a->offsets[i + 1]);
+        x.limited = 0;
         int r = decode_record(&x, s, e);
         if (r < 0) { a->rc = r; break; }
-        a->rowok[i] = (uint8_t)r;
+        a->rowok[i] = (uint8_t)(r == 1 ? 1 : (x.limited ? 2 : 0));
         for (int k = 0; k < a->n_leaves; k++) {
             int64_t v = x.valid[k] ? x.vals[k] : 0;
             if (x.valid[k] && a->leaf_is_string && a->leaf_is_string[k]) v = fnv1a64(heap + x.vals[k], x.lens[k]);

@@ -448,6 +448,8 @@ class Tab:
         self.n = n
         self.cols = []
         self.nest = {}       # MAP/STRUCT leaves: column name -> (key path, 'm'/'s' per level)
+        self.approx = set()  # double columns whose value depends on summation order (SUM / AVG of doubles and what is computed
+                             # from them): the only columns a comparison may give a tolerance; everything else is bit-exact
 
     def add(self, name, ty, vals, valid):
         self.cols.append([name, ty, vals, valid])
@@ -482,6 +484,7 @@ class Tab:
         for name, ty, v, ok in self.cols:
             t.add(name, ty, v[idx] if v is not None else None, ok[idx])
         t.nest = dict(getattr(self, "nest", {}))
+        t.approx = set(getattr(self, "approx", ()))
         if getattr(self, "owners", None):
             t.owners = list(self.owners)
         return t
@@ -513,7 +516,34 @@ def concat_tabs(tabs):
             oks.append(ok)
         out.add(name, ty, np.concatenate(vals) if vals else np.zeros(0), np.concatenate(oks) if oks else np.zeros(0, bool))
     out.nest = dict(tabs[0].nest)
+    for t in tabs:      # positional UNION: a column is order-dependent if it is in any branch
+        for c, c0 in zip(t.cols, tabs[0].cols):
+            if c[0] in getattr(t, "approx", ()):
+                out.approx.add(c0[0])
     return out
+
+
+def _col_refs(e, out):
+    if isinstance(e, (list, tuple)):
+        if e and e[0] == "col":
+            out.append(e[1])
+            return
+        for x in e:
+            _col_refs(x, out)
+
+
+def _mark_approx(out, src, q, items):
+    """an output column computed from an order-dependent input column is order-dependent too"""
+    sa = getattr(src, "approx", ())
+    if not sa:
+        return
+    for (e, alias), c in zip(items, out.cols):
+        refs = []
+        _col_refs(e, refs)
+        for parts in refs:
+            sc = src.find(parts, q)
+            if sc is not None and sc[0] in sa:
+                out.approx.add(c[0])
 
 
 def ts_to_string(us):
@@ -1044,6 +1074,8 @@ def exec_core(core, views, now_us):
                     cols = [c for c in src.cols if c[0].startswith(prefix)]
                 for c in cols:
                     out.add(*c)
+                    if c[0] in getattr(src, "approx", ()):
+                        out.approx.add(c[0])
                     if c[0] in getattr(src, "nest", {}):
                         out.nest = dict(getattr(out, "nest", {}))
                         out.nest[c[0]] = src.nest[c[0]]
@@ -1062,6 +1094,10 @@ def exec_core(core, views, now_us):
                 continue
             ty, v, ok = ev.ev(e)
             out.add(_item_name(e, alias), ty, v, ok)
+            refs = []
+            _col_refs(e, refs)
+            if any((src.find(pp, q) or [None])[0] in getattr(src, "approx", ()) for pp in refs):
+                out.approx.add(_item_name(e, alias))
         return out
     # aggregation
     gexprs = []
@@ -1115,6 +1151,7 @@ def exec_core(core, views, now_us):
                     s = np.zeros(ng, np.float64)
                     np.add.at(s, gid[ok], v[ok])
                     out.add(name, "double", s, cnt > 0)
+                    out.approx.add(name)            # the sum of doubles depends on the order rows arrive in
                 else:
                     s = np.zeros(ng, np.int64)
                     with np.errstate(over="ignore"):
@@ -1125,6 +1162,8 @@ def exec_core(core, views, now_us):
                 np.add.at(s, gid[ok], v[ok].astype(np.float64))
                 with np.errstate(all="ignore"):
                     out.add(name, "double", np.where(cnt > 0, s / np.maximum(cnt, 1), 0.0), cnt > 0)
+                if ty == "double":
+                    out.approx.add(name)            # AVG(double) = order-dependent sum / count; AVG(long) sums exactly representable values up to 2^53
             else:
                 if ty == "double":
                     x = v[ok]
@@ -1169,6 +1208,12 @@ def exec_core(core, views, now_us):
             out.add(name, ty, v[first], ok[first])
         else:
             out.add(name, ty, v[:0], ok[:0])
+    # an aggregate (MIN, MAX, group key) over an order-dependent input stays order-dependent
+    for (e, alias), c in zip(items, out.cols):
+        refs = []
+        _col_refs(e, refs)
+        if any((src.find(pp, q) or [None])[0] in getattr(src, "approx", ()) for pp in refs):
+            out.approx.add(c[0])
     for (e, alias), c in zip(items, out.cols):      # DISTINCT / GROUP BY over MAP/STRUCT leaves keeps their shaping
         if e[0] == "col":
             sc = src.find(e[1], q)
@@ -1270,6 +1315,8 @@ class Flow:
             core = {"distinct": False, "items": step, "from": "Raw", "alias": None, "where": None, "group": []}
             projected = exec_core(core, {"Raw": projected}, now_us)
         metrics["Input_Normalized_Events_Count"] = float(projected.n)
+        if dxo.last_limited:          # events made NULL rows by a limit of the implementation, not by Spark's rules
+            metrics["Input_Unparsed_Events_Count"] = float(dxo.last_limited)
         views = CiDict()
         for rn, rt in getattr(self, 'refdata', {}).items():
             views[rn] = rt

@@ -39,7 +39,7 @@ def test_home_automation_local_flow(dx, ctx):
     o.add_refdata("myDevicesRefData", rd("devices.csv"))
     dxo_flow.UDFS["WHOOPENED"] = who_opened
     rng = random.Random(1)
-    for b in range(12):
+    for b in range(100):            # 100 batches x 120 events (2 events/s, 60 s interval)
         T = T0 + b * I
         now = T + 1500 + b          # current_timestamp() of the batch: after the batch time, as in a live run
         data = events(rng, 120, now)
