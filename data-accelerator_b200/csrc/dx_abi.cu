@@ -302,6 +302,26 @@ int dx_flow_process_batch(dx_flow* f, const char* name_space, const uint8_t* jso
     try { return f->process(name_space ? name_space : "", json, n_bytes, offsets, n_events, memory_kind, batch_time_ms, interval_ms, now_ms, out); }
     catch (std::exception& e) { return f->ctx->set_error(DX_ERR_STATE, e.what()); }
 }
+int dx_flow_set_batch_info(dx_flow* f, const dx_batch_info* info) {
+    if (!f) return DX_ERR_ARG;
+    dx_flow::BatchInfo b;
+    if (info) {
+        auto set = [](const char* src, bool* has, std::string* dst) { *has = src != nullptr; if (src) *dst = src; };
+        set(info->input_path, &b.has_input_path, &b.input_path);
+        set(info->output_file_name, &b.has_output_file_name, &b.output_file_name);
+        set(info->rule_index_prefix, &b.has_rule_index_prefix, &b.rule_index_prefix);
+        set(info->target, &b.has_target, &b.target);
+        b.has_file_time = info->has_file_time != 0; b.file_time_ms = info->file_time_ms;
+        b.has_output_folders = info->n_output_folders >= 0;
+        for (int i = 0; i < info->n_output_folders; i++) b.output_folders.emplace_back(info->output_folder_keys[i], info->output_folder_values[i]);
+        for (int i = 0; i < info->n_properties; i++) b.properties.emplace_back(info->property_keys[i], info->property_values[i]);
+        for (int i = 0; i < info->n_system_properties; i++) b.system_properties.emplace_back(info->system_property_keys[i], info->system_property_values[i]);
+        if (info->executor_id) b.executor_id = info->executor_id;
+    }
+    f->batch_info = b;
+    return DX_OK;
+}
+
 // ---- ingest running ahead of the processor -------------------------------------------------------
 struct dx_staged { dx_ctx* ctx = nullptr; DevBuf buf; int64_t n_bytes = 0; cudaEvent_t done = nullptr; };
 int dx_flow_stage_batch(dx_flow* f, const uint8_t* json_host, int64_t n_bytes, dx_staged** out) {

@@ -805,7 +805,10 @@ struct Exec {
             const ExprP& e = it.expr;
             std::vector<int> src_cols;   // columns forwarded as they are
             if (e->kind == EK::Star) {
-                if (e->parts.empty() || e->parts[0] == core.from || e->parts[0] == core.from_alias || (e->parts.size() == 1 && e->parts[0] == "Raw"))
+                if (e->parts.size() == 1 && e->parts[0] == "Raw" && stmt_name == "projection") {
+                    // Raw.* in a projection: the decoded leaves, not the transport metadata columns that sit beside Raw
+                    for (size_t c = 0; c < proto->cols.size(); c++) if (!dx_is_metadata_column(proto->cols[c].name)) src_cols.push_back((int)c);
+                } else if (e->parts.empty() || e->parts[0] == core.from || e->parts[0] == core.from_alias || (e->parts.size() == 1 && e->parts[0] == "Raw"))
                     for (size_t c = 0; c < proto->cols.size(); c++) src_cols.push_back((int)c);
                 else {
                     std::string prefix; for (auto& p : e->parts) prefix += p + ".";
@@ -817,10 +820,23 @@ struct Exec {
                 BindScope sc = scope_for(proto, core); sc.qualifiers.push_back("Raw");
                 std::string err; int ci = dx_resolve_column(sc, e->parts, &err);
                 if (ci < 0) {
-                    // transport metadata the ABI does not carry: NULL columns
+                    // a whole struct / map of transport metadata (`Properties AS _Properties`, `__DataX_FileInfo`): every leaf below
+                    // it, renamed under the item's name; an empty map (or metadata this batch carries none of) is a NULL column
                     const std::string& n0 = e->parts[0];
-                    if (n0 == "Properties" || n0 == "SystemProperties" || n0 == "__DataX_FileInfo" || n0 == "DataXProperties") {
-                        DxColumn c; c.name = item_name(it); c.type = DX_T_NULL; c.all_null = true; t->cols.push_back(c); out_index++; continue;
+                    std::string prefix; for (auto& pp : e->parts) prefix += pp + ".";
+                    bool nested_parent = false;       // e.g. `_Properties` in a later step: the leaves `_Properties.<key>` of an earlier one
+                    for (auto& pc : proto->cols) if (!pc.nest_kinds.empty() && !pc.data && pc.name.compare(0, prefix.size(), prefix) == 0) nested_parent = true;
+                    if (nested_parent || n0 == "Properties" || n0 == "SystemProperties" || n0 == "__DataX_FileInfo" || n0 == "DataXProperties") {
+                        bool any = false;
+                        for (size_t c = 0; c < proto->cols.size(); c++) {
+                            if (proto->cols[c].name.compare(0, prefix.size(), prefix) != 0) continue;
+                            DxColumn oc = proto->cols[c];
+                            if (oc.data) return fail(DX_ERR_UNSUPPORTED, "materialised metadata column '" + oc.name + "'");
+                            oc.name = item_name(it) + "." + oc.name.substr(prefix.size());
+                            t->cols.push_back(oc); out_index++; any = true;
+                        }
+                        if (!any) { DxColumn c; c.name = item_name(it); c.type = DX_T_NULL; c.all_null = true; t->cols.push_back(c); out_index++; }
+                        continue;
                     }
                     return fail(DX_ERR_ARG, err);
                 }
@@ -1682,6 +1698,9 @@ int dx_flow_build(dx_ctx* ctx, const char* conf_text, const char* schema_json, c
             if (std::find(F->outputs.begin(), F->outputs.end(), name) == F->outputs.end()) F->outputs.push_back(name);
         }
     }
+    for (auto& kv : F->conf)      // PropertiesHandler.buildAppendProperties: datax.job.process.appendproperty.<key>=<value>
+        if (kv.first.compare(0, (root + "appendproperty.").size(), root + "appendproperty.") == 0)
+            F->append_properties.emplace_back(kv.first.substr((root + "appendproperty.").size()), kv.second);
     { auto g = F->conf.find(root + "gpu.genericrules"); F->generic_rules_only = g != F->conf.end() && lower(g->second) == "true"; }
     { auto g = F->conf.find(root + "gpu.rulesstaging"); if (g != F->conf.end() && lower(g->second) == "false") F->rules_mode |= DX_RULES_NO_STAGING; }
     { auto g = F->conf.find(root + "gpu.rulesfast"); if (g != F->conf.end() && lower(g->second) == "false") F->rules_mode |= DX_RULES_NO_FAST; }
@@ -1748,21 +1767,83 @@ int dx_flow_add_refdata_impl(dx_flow* F, const std::string& name, const std::str
 // =======================================================================================
 // one micro-batch: processDataset -> project -> route (CommonProcessorFactory.scala:333-399)
 // =======================================================================================
+static DxColumn meta_const(const std::string& name, bool has, const std::string& v, std::vector<std::string> path, const std::string& kinds) {
+    DxColumn c; c.name = name; c.is_const = true; c.nest_path = std::move(path); c.nest_kinds = kinds;
+    if (has) { c.type = DX_T_STR; c.const_s = v; c.const_i = -1; } else { c.type = DX_T_NULL; c.all_null = true; }
+    return c;
+}
+// java.sql.Timestamp.toString in the UTC session: yyyy-mm-dd hh:mm:ss.f (at least one fractional digit)
+static std::string java_timestamp_string(long long ms) {
+    long long s = ms / 1000, frac = ms % 1000; if (frac < 0) { frac += 1000; s--; }
+    time_t tt = (time_t)s; struct tm g; gmtime_r(&tt, &g);
+    char b[64]; snprintf(b, sizeof b, "%04d-%02d-%02d %02d:%02d:%02d", g.tm_year + 1900, g.tm_mon + 1, g.tm_mday, g.tm_hour, g.tm_min, g.tm_sec);
+    std::string out = b;
+    if (frac == 0) return out + ".0";
+    char f[8]; snprintf(f, sizeof f, "%03lld", frac); std::string fs = f; while (fs.size() > 1 && fs.back() == '0') fs.pop_back();
+    return out + "." + fs;
+}
+void dx_flow::add_metadata_columns(DxTable* t, long long batch_ms, long long now_ms) const {
+    const BatchInfo& b = batch_info;
+    const std::string fi = "__DataX_FileInfo";
+    t->cols.push_back(meta_const(fi + ".inputPath", b.has_input_path, b.input_path, {"inputPath"}, "s"));
+    if (b.has_output_folders && !b.output_folders.empty())
+        for (auto& kv : b.output_folders) t->cols.push_back(meta_const(fi + ".outputFolders." + kv.first, true, kv.second, {"outputFolders", kv.first}, "sm"));
+    else t->cols.push_back(meta_const(fi + ".outputFolders", false, "", {"outputFolders"}, "s"));
+    t->cols.push_back(meta_const(fi + ".outputFileName", b.has_output_file_name, b.output_file_name, {"outputFileName"}, "s"));
+    {
+        DxColumn c; c.name = fi + ".fileTime"; c.is_const = true; c.nest_path = {"fileTime"}; c.nest_kinds = "s";
+        if (b.has_file_time) { c.type = DX_T_TS; c.const_i = b.file_time_ms * 1000; } else { c.type = DX_T_NULL; c.all_null = true; }
+        t->cols.push_back(c);
+    }
+    t->cols.push_back(meta_const(fi + ".ruleIndexPrefix", b.has_rule_index_prefix, b.rule_index_prefix, {"ruleIndexPrefix"}, "s"));
+    t->cols.push_back(meta_const(fi + ".target", b.has_target, b.target, {"target"}, "s"));
+    // DataXProperties (PropertiesHandler.scala:26-35): appendproperty.* of the conf, then the processing properties; null values dropped
+    std::vector<std::pair<std::string, std::string>> props = append_properties;
+    auto put = [&](const std::string& k, const std::string& v) { for (auto& kv : props) if (kv.first == k) { kv.second = v; return; } props.emplace_back(k, v); };
+    put("BatchTime", java_timestamp_string(batch_ms));
+    if (b.has_file_time) put("BlobTime", java_timestamp_string(b.file_time_ms));
+    if (b.has_output_file_name) put("BlobPathHint", b.output_file_name);
+    put("CPTime", java_timestamp_string(now_ms));
+    put("CPExecutor", b.executor_id);
+    for (auto& kv : props) t->cols.push_back(meta_const("DataXProperties." + kv.first, true, kv.second, {kv.first}, "m"));
+    for (auto& kv : b.properties) t->cols.push_back(meta_const("Properties." + kv.first, true, kv.second, {kv.first}, "m"));
+    for (auto& kv : b.system_properties) t->cols.push_back(meta_const("SystemProperties." + kv.first, true, kv.second, {kv.first}, "m"));
+}
+bool dx_is_metadata_column(const std::string& n) {
+    return n.compare(0, 8, "__DataX_") == 0 || n.compare(0, 16, "DataXProperties.") == 0 || n.compare(0, 11, "Properties.") == 0 || n.compare(0, 17, "SystemProperties.") == 0;
+}
+
 // project(): from_json + selectExpr steps (CommonProcessorFactory.scala:90-103)
 int dx_flow::project(const uint8_t* json, int64_t n_bytes, const int64_t* offsets, int64_t n_events, int memory_kind,
-                     long long now_ms, DxTableP* out) {
+                     long long now_ms, DxTableP* out, long long batch_ms) {
+    const long long batch_ms_for_props = batch_ms >= 0 ? batch_ms : now_ms;
     DxTableP raw;
     int rc = memory_kind == 1 ? decoder->decode_device(json, n_bytes, offsets, n_events, &raw) : decoder->decode_host(json, n_bytes, offsets, n_events, &raw);
     if (rc) return rc;
     ViewMap views;
     Exec X{this, ctx, &views, now_ms * 1000, ""};
-    DxTableP projected = raw;
+    // the frame the ingest adapters build around Raw (CPF:405-421, 458-461, 628-654): __DataX_FileInfo beside every event, and
+    // what project() adds before the steps (CPF:97): DataXProperties; Properties / SystemProperties when the batch carries them
+    DxTableP projected = std::make_shared<DxTable>(*raw);
+    add_metadata_columns(projected.get(), batch_ms_for_props, now_ms);
+    bool first = true;
     for (auto& step : projections) {
         View v; v.chunks.push_back(projected); views["Raw"] = v;
         SelectCore core; core.from = "Raw"; core.items = step;
         X.stmt_name = "projection";
         DxTableP next; rc = X.exec_plain(core, views["Raw"], &next); if (rc) return rc;
-        projected = next;
+        // selectExpr(projection ++ preservedColumns) (CPF:95-100): the __DataX_* columns survive every step
+        for (auto& c : projected->cols) {
+            if (c.name.compare(0, 8, "__DataX_") != 0) continue;
+            bool have = false; for (auto& n : next->cols) if (n.name == c.name) have = true;
+            if (!have) next->cols.push_back(c);
+        }
+        projected = next; first = false;
+    }
+    if (first) {       // no projection step: the frame as it is, minus what only project() sees
+        auto keep = std::make_shared<DxTable>(*projected); keep->cols.clear();
+        for (auto& c : projected->cols) if (!dx_is_metadata_column(c.name) || c.name.compare(0, 8, "__DataX_") == 0) keep->cols.push_back(c);
+        projected = keep;
     }
     *out = projected;
     return DX_OK;
@@ -1772,12 +1853,13 @@ int dx_flow::process(const std::string& name_space, const uint8_t* json, int64_t
                      int memory_kind, long long batch_ms, long long interval_ms, long long now_ms, dx_result** out) {
     DxTableP projected;
     const auto t0 = std::chrono::steady_clock::now();
-    int rc = project(json, n_bytes, offsets, n_events, memory_kind, now_ms, &projected);
+    batch_t0 = t0; batch_t0_set = true;
+    int rc = project(json, n_bytes, offsets, n_events, memory_kind, now_ms, &projected, batch_ms);
     if (rc) return rc;
     const auto t1 = std::chrono::steady_clock::now();
     pending_unparsed = (long long)decoder->last_stats.limited_rows;
     rc = route(name_space, projected, batch_ms, interval_ms, now_ms, out);
-    pending_unparsed = 0;
+    pending_unparsed = 0; batch_t0_set = false;
     ctx->counters["host_us:project"] += std::chrono::duration_cast<std::chrono::microseconds>(t1 - t0).count();
     ctx->counters["host_us:route"] += std::chrono::duration_cast<std::chrono::microseconds>(std::chrono::steady_clock::now() - t1).count();
     return rc;
@@ -1789,6 +1871,7 @@ int dx_flow::route(const std::string& name_space, const DxTableP& projected, lon
                    dx_result** out) {
     std::unique_ptr<dx_result> R(new dx_result()); R->flow = this;
     auto metric = [&](const std::string& k, double v) { R->metric_keys.push_back(k); R->metric_vals.push_back(v); };
+    if (!batch_t0_set) batch_t0 = std::chrono::steady_clock::now();       // route() called on its own (dx_flow_process_table)
     int rc = DX_OK;
     ViewMap views;
     Exec X{this, ctx, &views, now_ms * 1000, ""};
@@ -1874,8 +1957,17 @@ int dx_flow::route(const std::string& name_space, const DxTableP& projected, lon
         }
         R->datasets[cmd.name] = res; R->dataset_order.push_back(cmd.name);
     }
-    for (auto& o : outputs) if (!R->datasets.count(o)) return ctx->set_error(DX_ERR_ARG, "could not find data set name '" + o + "' for output '" + o + "'");
+    for (auto& o : outputs) {
+        auto it = R->datasets.find(o);
+        if (it == R->datasets.end()) return ctx->set_error(DX_ERR_ARG, "could not find data set name '" + o + "' for output '" + o + "'");
+        // what OutputManager.sink reports before it fans out (OutputManager.scala:121-122: df.count() as Sink_InputEvents, prefixed
+        // Output_<name>_ at CPF:304); the sinks' own counters (Sink_<sinker>_All ...) are added by the unchanged sinks on the host side
+        metric("Output_" + o + "_Sink_InputEvents", (double)it->second->n_rows);
+    }
     R->datasets["DataXProcessedInput_Batch"] = projected;
+    // CPF:372-377: seconds spent on the batch, and the age of the batch when its processing ended (wall clock)
+    metric("Latency-Process", std::chrono::duration<double>(std::chrono::steady_clock::now() - batch_t0).count());
+    metric("Latency-Batch", (double)(std::chrono::duration_cast<std::chrono::milliseconds>(std::chrono::system_clock::now().time_since_epoch()).count() - batch_ms) / 1000.0);
     for (auto& k : R->metric_keys) R->metric_key_ptrs.push_back(k.c_str());
     *out = R.release();
     return DX_OK;

@@ -13,6 +13,7 @@
 #include "dx_decode_host.h"
 #include "dx_strings.h"
 #include <set>
+#include <chrono>
 
 struct SqlCommand {
     std::string text, name;        // name empty => "Command" type (TransformSqlParser.scala:24-26)
@@ -79,6 +80,8 @@ struct dx_result {
     std::vector<const char*> metric_key_ptrs;
 };
 
+bool dx_is_metadata_column(const std::string& name);      // __DataX_*, DataXProperties.*, Properties.*, SystemProperties.*
+
 struct dx_flow {
     dx_ctx* ctx = nullptr;
     std::map<std::string, std::string> conf;
@@ -93,6 +96,16 @@ struct dx_flow {
     std::map<std::string, StateTable, CiLess> state_tables;
     std::map<std::string, DxTableP, CiLess> ref_tables;           // reference data views (ReferenceDataHandler.scala:42-60)
     std::vector<std::string> outputs;
+    // transport metadata of the batch being processed (dx_flow_set_batch_info): the FileInternal struct behind __DataX_FileInfo
+    // (datax/data/FileInternal.scala:14-20; all NULL for the streaming adapters, CPF:417, 459) and the per-batch maps
+    struct BatchInfo {
+        bool has_input_path = false, has_output_folders = false, has_output_file_name = false, has_file_time = false,
+             has_rule_index_prefix = false, has_target = false;
+        std::string input_path, output_file_name, rule_index_prefix, target, executor_id = "driver";
+        long long file_time_ms = 0;
+        std::vector<std::pair<std::string, std::string>> output_folders, properties, system_properties;
+    } batch_info;
+    std::vector<std::pair<std::string, std::string>> append_properties;   // conf datax.job.process.appendproperty.* (PropertiesHandler.scala:22-24)
     std::map<std::string, NamespaceState> ns;
     std::map<std::string, unsigned long long> agg_capacity_hint;  // per statement name
     std::map<std::string, std::map<const DxTable*, PanePartial>> pane_partials;   // partial signature -> cached batch -> partial
@@ -115,10 +128,12 @@ struct dx_flow {
     std::map<std::string, Udf> udfs;                               // upper-cased name -> callback
     std::map<std::string, std::shared_ptr<LutCache>> luts;        // (expression, dictionary) -> device lookup table
     std::map<std::string, DxDictP> expr_dicts;                     // (statement, item) -> dictionary of a string-valued result, stable across batches
+    std::chrono::steady_clock::time_point batch_t0; bool batch_t0_set = false;   // start of the batch being processed (Latency-Process)
     long long pending_unparsed = 0;    // decoder->last_stats.limited_rows of the batch being routed
     int rules_mode = 0;                // DX_RULES_* bits from conf datax.job.process.gpu.rulesstaging / .rulesfast (dx_rules.h)
     bool generic_rules_only = false;   // tests: force the bytecode interpreter for rule arrays (conf datax.job.process.gpu.genericrules=true)
-    int project(const uint8_t* json, int64_t n_bytes, const int64_t* offsets, int64_t n_events, int memory_kind, long long now_ms, DxTableP* out);
+    int project(const uint8_t* json, int64_t n_bytes, const int64_t* offsets, int64_t n_events, int memory_kind, long long now_ms, DxTableP* out, long long batch_ms = -1);
+    void add_metadata_columns(DxTable* t, long long batch_ms, long long now_ms) const;
     int route(const std::string& name_space, const DxTableP& projected, long long batch_ms, long long interval_ms, long long now_ms, dx_result** out);
     int process(const std::string& name_space, const uint8_t* json, int64_t n_bytes, const int64_t* offsets, int64_t n_events,
                 int memory_kind, long long batch_ms, long long interval_ms, long long now_ms, dx_result** out);

@@ -188,6 +188,35 @@ class CommonProcessor:
             now_ms if now_ms is not None else batch_time_ms, C.byref(r)))
         return BatchResult(self.ctx, r)
 
+    def set_batch_info(self, input_path=None, output_folders=None, output_file_name=None, file_time_ms=None, rule_index_prefix=None,
+                       target=None, properties=None, system_properties=None, executor_id=None, reset=False):
+        """The per-batch constants behind __DataX_FileInfo / DataXProperties / Properties / SystemProperties (dx_flow_set_batch_info):
+        what a blob or EventHub adapter knows about the partition it hands over next.  reset=True: back to FileInternal()."""
+        fn = self.L.dx_flow_set_batch_info
+        fn.restype, fn.argtypes = C.c_int, [C.c_void_p, C.c_void_p]
+        if reset:
+            self.ctx.check(fn(self.h, None))
+            return
+        PP = C.POINTER(C.c_char_p)
+
+        class Info(C.Structure):
+            _fields_ = [("input_path", C.c_char_p), ("of_k", PP), ("of_v", PP), ("n_of", C.c_int), ("output_file_name", C.c_char_p),
+                        ("file_time_ms", C.c_int64), ("has_file_time", C.c_int), ("rule_index_prefix", C.c_char_p), ("target", C.c_char_p),
+                        ("p_k", PP), ("p_v", PP), ("n_p", C.c_int), ("sp_k", PP), ("sp_v", PP), ("n_sp", C.c_int), ("executor_id", C.c_char_p)]
+        enc = lambda x: None if x is None else x.encode("utf-8")
+
+        def arr(d):
+            d = d or {}
+            k = (C.c_char_p * max(1, len(d)))(*[x.encode("utf-8") for x in d.keys()])
+            v = (C.c_char_p * max(1, len(d)))(*[x.encode("utf-8") for x in d.values()])
+            return k, v, len(d)
+        ofk, ofv, nof = arr(output_folders)
+        pk, pv, np_ = arr(properties)
+        spk, spv, nsp = arr(system_properties)
+        info = Info(enc(input_path), ofk, ofv, nof if output_folders is not None else -1, enc(output_file_name),
+                    file_time_ms or 0, 0 if file_time_ms is None else 1, enc(rule_index_prefix), enc(target), pk, pv, np_, spk, spv, nsp, enc(executor_id))
+        self.ctx.check(fn(self.h, C.byref(info)))
+
     def stage_json(self, host_ptr, n_bytes):
         """Starts the host->device copy of the NEXT batch (page-locked host memory at host_ptr) and returns a handle for
         process_staged; the copy overlaps whatever the processor is doing meanwhile."""

@@ -176,6 +176,28 @@ int dx_flow_process_batch(dx_flow* flow, const char* name_space, const uint8_t* 
                           const int64_t* offsets, int64_t n_events, int memory_kind,
                           int64_t batch_time_ms, int64_t interval_ms, int64_t output_partition_time_ms,
                           int64_t now_ms, dx_result** out);
+/* The frame the reference's ingest adapters build around every event (CommonProcessorFactory.scala:405-421, 458-461, 628-654):
+ * beside Raw, the column __DataX_FileInfo (datax/data/FileInternal.scala:14-20: inputPath, outputFolders, outputFileName,
+ * fileTime, ruleIndexPrefix, target), kept through every projection step (CPF:95-100), and, visible to the projection
+ * expressions, DataXProperties (PropertiesHandler.scala:26-35: BatchTime, BlobTime, BlobPathHint, CPTime, CPExecutor plus the
+ * conf's appendproperty.* entries) and the transport's Properties / SystemProperties maps.  Here they are per-BATCH constants:
+ * without a call every field of __DataX_FileInfo is NULL (what the streaming adapters pass, FileInternal()) and the two
+ * transport maps are empty; a blob or EventHub shim calls dx_flow_set_batch_info before dx_flow_process_batch with the values
+ * of the partition it is about to hand over (per-event property values are not carried).  Result tables show the struct as one
+ * column per leaf (dx_table_column_nesting: __DataX_FileInfo.inputPath ..., outputFolders.<group>).  info == NULL resets.      */
+typedef struct dx_batch_info {
+    const char* input_path;                       /* NULL = SQL NULL, as for every string below */
+    const char* const* output_folder_keys; const char* const* output_folder_values; int n_output_folders;   /* < 0: NULL map */
+    const char* output_file_name;
+    int64_t file_time_ms; int has_file_time;
+    const char* rule_index_prefix;
+    const char* target;
+    const char* const* property_keys; const char* const* property_values; int n_properties;
+    const char* const* system_property_keys; const char* const* system_property_values; int n_system_properties;
+    const char* executor_id;                      /* DataXProperties.CPExecutor; NULL = "driver" */
+} dx_batch_info;
+int dx_flow_set_batch_info(dx_flow* flow, const dx_batch_info* info);
+
 /* Ingest that runs ahead of the processor.  In the reference the receivers fill the next micro-batch while the job thread
  * works on the current one (Spark Streaming's receiver / job split behind StreamingHost.scala:62-95); over PCIe that overlap
  * is worth having, because copying a batch of JSON takes far longer than processing it.  dx_flow_stage_batch starts the

@@ -441,6 +441,20 @@ class P:
 # --------------------------------------------------------------------------------------------------
 # tables and expression evaluation (Spark semantics)
 # --------------------------------------------------------------------------------------------------
+def is_metadata_column(name):
+    return name.startswith(("__DataX_", "DataXProperties.", "Properties.", "SystemProperties."))
+
+
+def java_timestamp_string(ms):
+    """java.sql.Timestamp.toString in the UTC session: yyyy-mm-dd hh:mm:ss.f with at least one fractional digit."""
+    s, frac = divmod(ms, 1000)
+    t = calendar.timegm
+    import time as _t
+    g = _t.gmtime(s)
+    base = "%04d-%02d-%02d %02d:%02d:%02d" % (g.tm_year, g.tm_mon, g.tm_mday, g.tm_hour, g.tm_min, g.tm_sec)
+    return base + ("." + ("%03d" % frac).rstrip("0") if frac else ".0")
+
+
 class Tab:
     """columns: list of (name, type, values, valid).  type in long|double|string|bool|ts|null|rules."""
 
@@ -1065,7 +1079,9 @@ def exec_core(core, views, now_us):
         for e, alias in items:
             if e[0] == "star":
                 parts = e[1]
-                if not parts or parts[0] in q:
+                if core.get("projection") and parts == ["Raw"]:
+                    cols = [c for c in src.cols if not is_metadata_column(c[0])]     # Raw.* : the decoded leaves, not the frame around Raw
+                elif not parts or parts[0] in q:
                     cols = src.cols
                 else:
                     prefix = ".".join(parts) + "."
@@ -1089,8 +1105,19 @@ def exec_core(core, views, now_us):
                 out.add(_item_name(e, alias), "rules", flags, np.ones(src.n, bool))
                 out.rule_table = [d for _, d in rs]
                 continue
-            if e[0] == "col" and src.find(e[1], q) is None and e[1][0] in ("Properties", "SystemProperties", "__DataX_FileInfo", "DataXProperties"):
-                out.add(_item_name(e, alias), "null", None, np.zeros(src.n, bool))
+            if e[0] == "col" and src.find(e[1], q) is None and (
+                    e[1][0] in ("Properties", "SystemProperties", "__DataX_FileInfo", "DataXProperties") or
+                    any(c[0].startswith(".".join(e[1]) + ".") and c[0] in src.nest for c in src.cols)):
+                # a whole struct / map of transport metadata: its leaves renamed under the item's name; none -> a NULL column
+                prefix = ".".join(e[1]) + "."
+                hits = [c for c in src.cols if c[0].startswith(prefix)]
+                for c in hits:
+                    nm = _item_name(e, alias) + "." + c[0][len(prefix):]
+                    out.add(nm, c[1], c[2], c[3])
+                    if c[0] in src.nest:
+                        out.nest[nm] = src.nest[c[0]]
+                if not hits:
+                    out.add(_item_name(e, alias), "null", None, np.zeros(src.n, bool))
                 continue
             ty, v, ok = ev.ev(e)
             out.add(_item_name(e, alias), ty, v, ok)
@@ -1277,6 +1304,68 @@ class Flow:
         self.ts_col = tc
         self.max_window = max(self.windows.values()) if self.enabled else 0
         self.past = {}        # namespace -> {batch_ms: Tab}
+        # transport metadata of the batch about to be processed (set_batch_info; None = FileInternal(), CPF:417) and the conf's
+        # appendproperty.* entries (PropertiesHandler.scala:22-24)
+        self.batch_info = None
+        self.append_properties = [(k[len(root + "appendproperty."):], v) for k, v in self.conf.items() if k.startswith(root + "appendproperty.")]
+        # outputs (OutputManager.getOperatators: one per name under datax.job.output.<name>.<sink>.*), in order of appearance
+        self.outputs = []
+        for k in self.conf:
+            m = re.fullmatch(r"datax\.job\.output\.([^.]+)\..+", k)
+            if m and m.group(1) not in self.outputs:
+                self.outputs.append(m.group(1))
+
+    def set_batch_info(self, info):
+        """info: None or a dict with any of input_path, output_folders (dict), output_file_name, file_time_ms, rule_index_prefix,
+        target, properties (dict), system_properties (dict), executor_id — the per-batch constants of dx_flow_set_batch_info."""
+        self.batch_info = info
+
+    def _add_metadata(self, t, batch_ms, now_ms):
+        b = self.batch_info or {}
+        n = t.n
+
+        def const(name, val, path, kinds, ty="string"):
+            if val is None:
+                t.add(name, "null", None, np.zeros(n, bool))
+            elif ty == "ts":
+                t.add(name, "ts", np.full(n, val, np.int64), np.ones(n, bool))
+            else:
+                v = np.empty(n, dtype=object)
+                v[:] = val.encode("utf-8")
+                t.add(name, "string", v, np.ones(n, bool))
+            t.nest[name] = (path, kinds)
+        fi = "__DataX_FileInfo"
+        const(fi + ".inputPath", b.get("input_path"), ["inputPath"], "s")
+        if b.get("output_folders"):
+            for k, v in b["output_folders"].items():
+                const(fi + ".outputFolders." + k, v, ["outputFolders", k], "sm")
+        else:
+            const(fi + ".outputFolders", None, ["outputFolders"], "s")
+        const(fi + ".outputFileName", b.get("output_file_name"), ["outputFileName"], "s")
+        const(fi + ".fileTime", None if b.get("file_time_ms") is None else b["file_time_ms"] * 1000, ["fileTime"], "s", "ts")
+        const(fi + ".ruleIndexPrefix", b.get("rule_index_prefix"), ["ruleIndexPrefix"], "s")
+        const(fi + ".target", b.get("target"), ["target"], "s")
+        props = list(self.append_properties)
+
+        def put(k, v):
+            for i, (k2, _) in enumerate(props):
+                if k2 == k:
+                    props[i] = (k, v)
+                    return
+            props.append((k, v))
+        put("BatchTime", java_timestamp_string(batch_ms))
+        if b.get("file_time_ms") is not None:
+            put("BlobTime", java_timestamp_string(b["file_time_ms"]))
+        if b.get("output_file_name") is not None:
+            put("BlobPathHint", b["output_file_name"])
+        put("CPTime", java_timestamp_string(now_ms))
+        put("CPExecutor", b.get("executor_id") or "driver")
+        for k, v in props:
+            const("DataXProperties." + k, v, [k], "m")
+        for k, v in (b.get("properties") or {}).items():
+            const("Properties." + k, v, [k], "m")
+        for k, v in (b.get("system_properties") or {}).items():
+            const("SystemProperties." + k, v, [k], "m")
 
     def add_refdata(self, name, csv_text, delimiter=",", header=True):
         """ReferenceDataHandler / CSVUtil.scala:27-29: every column is a string; empty field -> NULL."""
@@ -1308,12 +1397,30 @@ class Flow:
         return t
 
     def process(self, data, batch_ms, interval_ms, now_ms=None, namespace="", offsets=None):
+        import time
+        t_start = time.perf_counter()
         now_us = (batch_ms if now_ms is None else now_ms) * 1000
         metrics = {}
         projected = self.decode(data, offsets)
+        # the frame around Raw (CPF:405-421, 458-461) and what project() adds before the steps (CPF:97)
+        self._add_metadata(projected, batch_ms, batch_ms if now_ms is None else now_ms)
+        if not self.projections:
+            keep = Tab(projected.n)
+            for c in projected.cols:
+                if not is_metadata_column(c[0]) or c[0].startswith("__DataX_"):
+                    keep.add(*c)
+                    if c[0] in projected.nest:
+                        keep.nest[c[0]] = projected.nest[c[0]]
+            projected = keep
         for step in self.projections:
-            core = {"distinct": False, "items": step, "from": "Raw", "alias": None, "where": None, "group": []}
-            projected = exec_core(core, {"Raw": projected}, now_us)
+            core = {"distinct": False, "items": step, "from": "Raw", "alias": None, "where": None, "group": [], "projection": True}
+            nxt = exec_core(core, {"Raw": projected}, now_us)
+            for c in projected.cols:          # selectExpr(projection ++ preservedColumns) (CPF:95-100)
+                if c[0].startswith("__DataX_") and c[0] not in nxt.names():
+                    nxt.add(*c)
+                    if c[0] in projected.nest:
+                        nxt.nest[c[0]] = projected.nest[c[0]]
+            projected = nxt
         metrics["Input_Normalized_Events_Count"] = float(projected.n)
         if dxo.last_limited:          # events made NULL rows by a limit of the implementation, not by Spark's rules
             metrics["Input_Unparsed_Events_Count"] = float(dxo.last_limited)
@@ -1362,7 +1469,13 @@ class Flow:
                 st["active"], st["standby"] = st["standby"], st["active"]   # flip
             views[name] = res
             datasets[name] = res
+        for o in self.outputs:           # CPF:297-306 + OutputManager.scala:121-122: the sink stage's input count per output
+            if o not in datasets:
+                raise ValueError(f"could not find data set name '{o}' for output '{o}'")
+            metrics[f"Output_{o}_Sink_InputEvents"] = float(datasets[o].n)
         datasets["DataXProcessedInput_Batch"] = projected
+        metrics["Latency-Process"] = time.perf_counter() - t_start              # CPF:372-377 (wall-clock values: never compared)
+        metrics["Latency-Batch"] = (time.time() * 1000.0 - batch_ms) / 1000.0
         return datasets, metrics
 
 

@@ -93,3 +93,18 @@ def assert_same_rows(table, tab, dx, ordered=False):
                     assert _bits(x) == _bits(y), (tab.names()[k], "exact double column differs", a, b)
             else:
                 assert x == y, (tab.names()[k], a, b)
+
+
+def same_metrics(a, b):
+    """The Map[String, Double] processDataset returns: same keys, same values — except Latency-Process / Latency-Batch
+    (CommonProcessorFactory.scala:372-377), which are wall-clock readings: present, non-negative where meaningful, not compared."""
+    if set(a) != set(b):
+        return False
+    for k in a:
+        if k.startswith("Latency-"):
+            if k == "Latency-Process" and not (a[k] >= 0.0 and b[k] >= 0.0):
+                return False
+            continue
+        if a[k] != b[k]:
+            return False
+    return "Latency-Process" in a and "Latency-Batch" in a

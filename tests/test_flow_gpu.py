@@ -8,7 +8,7 @@ import pytest
 import dxo
 import dxo_flow
 from adversarial import all_records, to_ndjson
-from flowcmp import assert_same_rows
+from flowcmp import assert_same_rows, same_metrics
 
 pytestmark = pytest.mark.gpu
 
@@ -33,7 +33,7 @@ def gen(dx, n, first=0, shape=2, n_keys=1000, base=T0, seed=20260103, late=10, f
 def check_batch(dx, g, o, data, batch_ms, now_ms=None, tables=None):
     rg = g.process_json(data, batch_ms, I, now_ms=now_ms)
     ro, mo = o.process(data, batch_ms, I, now_ms=now_ms)
-    assert rg.metrics == mo, (rg.metrics, mo)
+    assert same_metrics(rg.metrics, mo), (rg.metrics, mo)
     for name in (tables or rg.table_names):
         assert_same_rows(rg.table(name), ro[name], dx)
     rg.release()
@@ -195,7 +195,7 @@ Total = SELECT COUNT(*) AS Count, AVG(deviceDetails.temperature) AS Tavg FROM Da
         ro, mo = o.process(data, T, I)
         for proc in (g, g_rescan, g_global, g_coarse):
             rg = proc.process_json(data, T, I)
-            assert rg.metrics == mo
+            assert same_metrics(rg.metrics, mo)
             for name in ("ByKey", "ByHome", "Total"):
                 assert_same_rows(rg.table(name), ro[name], dx)
             rg.release()
@@ -529,7 +529,7 @@ K = SELECT deviceDetails.deviceId, COUNT(*) AS Count, MAX(deviceDetails.temperat
         nxt = g.stage_json(pinned[b + 1].value, len(batches[b + 1])) if b + 1 < len(batches) else None
         rg = g.process_staged(staged, T0 + b * I, I)
         ro, mo = o.process(data, T0 + b * I, I)
-        assert rg.metrics == mo
+        assert same_metrics(rg.metrics, mo)
         assert_same_rows(rg.table("K"), ro["K"], dx)
         rg.release()
         staged = nxt
@@ -540,4 +540,42 @@ K = SELECT deviceDetails.deviceId, COUNT(*) AS Count, MAX(deviceDetails.temperat
     fn(extra)
     for hp in pinned:
         L.dx_host_free(ctx.h, hp)
+    g.close()
+
+
+def test_transport_metadata_columns(dx, ctx):
+    """__DataX_FileInfo beside every event and through every projection step and SELECT * (CPF:95-100, 405-421), DataXProperties
+    (PropertiesHandler.scala:26-35, conf appendproperty.*) and the transport's Properties / SystemProperties maps as per-batch
+    constants: the streaming default (all of FileInternal() NULL), then a batch a blob adapter described."""
+    conf = dx.flowgen.conf_text("meta") + "datax.job.process.appendproperty.Region=westus2\n"
+    proj = ["Raw.*\nDataXProperties.BatchTime AS bt\nDataXProperties.Region AS region\nProperties AS _Properties\nSystemProperties.offset AS off\n",
+            "deviceDetails.deviceId AS id\nbt\nregion\n_Properties\noff\n"]
+    tr = "--DataXQuery--\nAll = SELECT * FROM DataXProcessedInput WHERE id > 0\n--DataXQuery--\nPaths = SELECT DISTINCT __DataX_FileInfo.inputPath AS p, bt FROM DataXProcessedInput\n"
+    g, o = both(dx, ctx, conf, SCHEMA2, proj, tr)
+    data = gen(dx, 500, n_keys=50)
+    rg = g.process_json(data, T0, I, now_ms=T0 + 1234)
+    ro, mo = o.process(data, T0, I, now_ms=T0 + 1234)
+    assert same_metrics(rg.metrics, mo)
+    t = rg.table("All")
+    assert t.columns == ["id", "bt", "region", "_Properties", "off", "__DataX_FileInfo.inputPath", "__DataX_FileInfo.outputFolders",
+                         "__DataX_FileInfo.outputFileName", "__DataX_FileInfo.fileTime", "__DataX_FileInfo.ruleIndexPrefix", "__DataX_FileInfo.target"]
+    assert t.nesting("__DataX_FileInfo.fileTime") == (["fileTime"], "s")
+    for name in ("All", "Paths"):
+        assert_same_rows(rg.table(name), ro[name], dx)
+    assert set(t.column("bt")[0]) == {b"2023-11-14 22:14:00.0"} and set(t.column("region")[0]) == {b"westus2"}
+    rg.release()
+    info = dict(input_path="wasbs://in/2023/11/14/part-7.json", output_folders={"default": "out/2023/11/14", "alerts": "alerts/14"},
+                output_file_name="part-7", file_time_ms=T0 - 5000, rule_index_prefix="r", target="t1",
+                properties={"tenant": "contoso"}, system_properties={"offset": "42", "partition": "3"}, executor_id="7")
+    g.set_batch_info(**info)
+    o.set_batch_info(info)
+    rg = g.process_json(data, T0 + I, I, now_ms=T0 + I + 5)
+    ro, mo = o.process(data, T0 + I, I, now_ms=T0 + I + 5)
+    t = rg.table("All")
+    assert "__DataX_FileInfo.outputFolders.alerts" in t.columns and "_Properties.tenant" in t.columns
+    assert t.nesting("__DataX_FileInfo.outputFolders.alerts") == (["outputFolders", "alerts"], "sm")
+    assert set(t.column("off")[0]) == {b"42"} and set(t.column("__DataX_FileInfo.inputPath")[0]) == {info["input_path"].encode()}
+    for name in ("All", "Paths"):
+        assert_same_rows(rg.table(name), ro[name], dx)
+    rg.release()
     g.close()
