@@ -446,7 +446,25 @@ int dx_flow_add_refdata(dx_flow* f, const char* name, const char* csv_text, char
 }
 int dx_flow_register_udf(dx_flow* f, const char* name, dx_udf1_fn fn, void* user) {
     if (!f || !name || !fn) return DX_ERR_ARG;
-    f->udfs[dxsql::upper(name)] = dx_flow::Udf{fn, user};
+    dx_flow::Udf u; u.fn = fn; u.user = user; u.n_args = 1;
+    f->udfs[dxsql::upper(name)] = u;
+    return DX_OK;
+}
+int dx_flow_register_udfn(dx_flow* f, const char* name, int n_args, dx_udfn_fn fn, void* user, int refresh_each_batch) {
+    if (!f || !name || !fn) return DX_ERR_ARG;
+    if (n_args < 0 || n_args > 3) return f->ctx->set_error(DX_ERR_UNSUPPORTED, "user functions take 0 to 3 arguments (DynamicUDF.Generator0..3)");
+    dx_flow::Udf u; u.fnn = fn; u.user = user; u.n_args = n_args; u.refresh = refresh_each_batch != 0;
+    f->udfs[dxsql::upper(name)] = u;
+    return DX_OK;
+}
+int dx_flow_set_interval_hook(dx_flow* f, dx_interval_fn fn, void* user) {
+    if (!f) return DX_ERR_ARG;
+    f->on_interval = fn; f->on_interval_user = user;
+    return DX_OK;
+}
+int dx_flow_set_normalizer(dx_flow* f, dx_normalizer_fn fn, void* user) {
+    if (!f) return DX_ERR_ARG;
+    f->normalizer = fn; f->normalizer_user = user;
     return DX_OK;
 }
 

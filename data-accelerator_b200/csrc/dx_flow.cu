@@ -954,7 +954,11 @@ struct Exec {
     }
 
     // ---------------- string-valued expressions (dictionary columns) ----------------
-    bool is_udf(const ExprP& e) const { return e->kind == EK::Func && F->udfs.count(e->sval) && e->args.size() == 1; }
+    bool is_udf(const ExprP& e) const {
+        if (e->kind != EK::Func) return false;
+        auto it = F->udfs.find(e->sval);
+        return it != F->udfs.end() && (int)e->args.size() == it->second.n_args;
+    }
     bool string_valued(const ExprP& e, const BindScope& sc) const {
         if (e->kind == EK::Str) return true;
         if (e->kind == EK::Col) { std::string er; int ci = dx_resolve_column(sc, e->parts, &er); return ci >= 0 && sc.table->cols[ci].type == DX_T_STR; }
@@ -988,12 +992,47 @@ struct Exec {
         DX_CUDA(ctx, cudaMemsetAsync(mask->p, 0, (size_t)(n > 0 ? n : 1) * 4, ctx->stream));
         out->vmask = mask; out->vwidth = 4; out->vbit = 0; out->is_const = false; out->all_null = false;
         if (e->kind == EK::Func && (e->sval == "STRINGTOTIMESTAMP" || is_udf(e))) {
-            DxColumn arg; int rc = eval_string_full(sc, t, e->args[0], key + "/arg", &arg); if (rc) return rc;
+            const bool is_ts = e->sval == "STRINGTOTIMESTAMP";
+            const dx_flow::Udf u = is_ts ? dx_flow::Udf() : F->udfs[e->sval];
+            // one text per call: the argument itself, or the arguments joined by a separator the callback wrapper splits at
+            // (every distinct combination becomes one dictionary entry, so the host function runs once per combination)
+            static const char SEP = '\x1f';
+            auto call = [&](const std::string& joined, std::string* result, bool* is_null, std::string* err) {
+                std::vector<char> buf(4096); int64_t ol = -1; int rcc;
+                if (u.fnn) {
+                    std::vector<std::string> parts; size_t a0 = 0;
+                    for (int k = 0; k < u.n_args; k++) { size_t p1 = k + 1 < u.n_args ? joined.find(SEP, a0) : std::string::npos; parts.push_back(joined.substr(a0, p1 == std::string::npos ? std::string::npos : p1 - a0)); a0 = p1 == std::string::npos ? joined.size() : p1 + 1; }
+                    std::vector<const char*> ptrs; std::vector<int64_t> lens;
+                    for (auto& p2 : parts) { ptrs.push_back(p2.data()); lens.push_back((int64_t)p2.size()); }
+                    rcc = u.fnn(u.user, u.n_args, ptrs.data(), lens.data(), buf.data(), (int64_t)buf.size(), &ol);
+                } else rcc = u.fn(u.user, joined.data(), (int64_t)joined.size(), buf.data(), (int64_t)buf.size(), &ol);
+                if (rcc != 0) { *err = "user function " + e->sval + " failed"; return; }
+                *is_null = ol < 0; if (ol >= 0) result->assign(buf.data(), (size_t)ol);
+            };
+            if (!is_ts && u.n_args == 0) {     // Generator0 / UDF0: one call per batch, a constant column
+                std::string res, uerr; bool is_null = true;
+                call("", &res, &is_null, &uerr);
+                if (!uerr.empty()) return fail(DX_ERR_STATE, uerr);
+                out->vmask = nullptr; out->data = nullptr; out->is_const = true; out->type = DX_T_STR;
+                if (is_null) { out->all_null = true; return DX_OK; }
+                out->const_s = res; out->const_i = -1;
+                return materialize_const(out, n, result_dict(key));          // callers of the string engine take row-aligned columns
+            }
+            ExprP arg_expr = e->args[0];
+            if (!is_ts && u.n_args >= 2) {
+                auto cc = std::make_shared<Expr>(); cc->kind = EK::Func; cc->sval = "CONCAT";
+                for (int k = 0; k < u.n_args; k++) {
+                    if (k) { auto sp = std::make_shared<Expr>(); sp->kind = EK::Str; sp->sval = std::string(1, SEP); cc->args.push_back(sp); }
+                    cc->args.push_back(e->args[k]);
+                }
+                arg_expr = cc;
+            }
+            DxColumn arg; int rc = eval_string_full(sc, t, arg_expr, key + "/arg", &arg); if (rc) return rc;
+            if (arg.all_null || arg.type == DX_T_NULL) { out->type = DX_T_STR; out->all_null = true; out->data = nullptr; return DX_OK; }
             if (arg.type != DX_T_STR) return fail(DX_ERR_UNSUPPORTED, e->sval + " needs a string argument");
             if (!arg.data) {   // constant argument: materialise through a one-entry dictionary
                 rc = materialize_const(&arg, n, nullptr); if (rc) return rc;
             }
-            const bool is_ts = e->sval == "STRINGTOTIMESTAMP";
             char kb[64]; snprintf(kb, sizeof kb, "@%p", (void*)arg.dict.get());
             std::shared_ptr<LutCache>& lut = F->luts[to_string(e) + kb];
             if (!lut) { prune_luts(); lut = std::make_shared<LutCache>(); lut->src_dict = arg.dict; }   // the key is the dictionary's address: keep it alive
@@ -1001,13 +1040,12 @@ struct Exec {
                 rc = dx_lut_refresh(ctx, lut.get(), arg.dict, [](const std::string& s, long long* v) { return dx_string_to_timestamp_us(s, v); });
             } else {
                 if (!lut->out_dict) { lut->out_dict = std::make_shared<DxDict>(); rc = lut->out_dict->init(ctx, 1u << 16, 4u << 20); if (rc) return rc; }
-                const dx_flow::Udf u = F->udfs[e->sval];
                 DxDictP od = lut->out_dict; dx_ctx* c = ctx; std::string uerr;
                 rc = dx_lut_refresh(ctx, lut.get(), arg.dict, [&](const std::string& s, long long* v) {
-                    std::vector<char> buf(4096); int64_t ol = -1;
-                    if (u.fn(u.user, s.data(), (int64_t)s.size(), buf.data(), (int64_t)buf.size(), &ol) != 0) { uerr = "user function " + e->sval + " failed"; return false; }
-                    if (ol < 0) return false;
-                    int32_t code; if (od->insert_host(std::string(buf.data(), (size_t)ol), &code)) { uerr = c->last_error; return false; }
+                    std::string res; bool is_null = true;
+                    call(s, &res, &is_null, &uerr);
+                    if (!uerr.empty() || is_null) return false;
+                    int32_t code; if (od->insert_host(res, &code)) { uerr = c->last_error; return false; }
                     *v = code; return true;
                 });
                 if (!uerr.empty()) return fail(DX_ERR_STATE, uerr);
@@ -1854,6 +1892,21 @@ int dx_flow::process(const std::string& name_space, const uint8_t* json, int64_t
     DxTableP projected;
     const auto t0 = std::chrono::steady_clock::now();
     batch_t0 = t0; batch_t0_set = true;
+    if (on_interval) on_interval(on_interval_user, batch_ms);                 // CPF:351-353
+    for (auto& kv : udfs) if (kv.second.refresh)                              // answers of a refreshing function are not kept across batches
+        for (auto it = luts.begin(); it != luts.end();) { if (it->first.compare(0, kv.first.size() + 1, kv.first + "(") == 0) it = luts.erase(it); else ++it; }
+    normalizer_seconds = 0;
+    if (normalizer) {
+        if (memory_kind == 1) return ctx->set_error(DX_ERR_UNSUPPORTED, "an input normalizer is set (user code on the host): the batch must be passed in host memory");
+        if (offsets) return ctx->set_error(DX_ERR_UNSUPPORTED, "an input normalizer needs NDJSON framing (the normalised records have other offsets)");
+        const auto n0 = std::chrono::steady_clock::now();
+        normalized.resize((size_t)n_bytes * 2 + 64);
+        int64_t n_out = -1;
+        if (normalizer(normalizer_user, json, n_bytes, normalized.data(), (int64_t)normalized.size(), &n_out) != 0 || n_out < 0 || n_out > (int64_t)normalized.size())
+            return ctx->set_error(DX_ERR_STATE, "the input normalizer failed");
+        json = normalized.data(); n_bytes = n_out;
+        normalizer_seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - n0).count();
+    }
     int rc = project(json, n_bytes, offsets, n_events, memory_kind, now_ms, &projected, batch_ms);
     if (rc) return rc;
     const auto t1 = std::chrono::steady_clock::now();
@@ -1966,6 +2019,7 @@ int dx_flow::route(const std::string& name_space, const DxTableP& projected, lon
     }
     R->datasets["DataXProcessedInput_Batch"] = projected;
     // CPF:372-377: seconds spent on the batch, and the age of the batch when its processing ended (wall clock)
+    if (normalizer) metric("Latency-Normalizer", normalizer_seconds);       // user code on the host, outside the GPU path: visible, not hidden
     metric("Latency-Process", std::chrono::duration<double>(std::chrono::steady_clock::now() - batch_t0).count());
     metric("Latency-Batch", (double)(std::chrono::duration_cast<std::chrono::milliseconds>(std::chrono::system_clock::now().time_since_epoch()).count() - batch_ms) / 1000.0);
     for (auto& k : R->metric_keys) R->metric_key_ptrs.push_back(k.c_str());

@@ -124,7 +124,16 @@ struct dx_flow {
     std::string last_error;
     // user functions evaluated on the host side of the boundary, once per distinct dictionary entry
     typedef int (*udf1_fn)(void* user, const char* arg, int64_t arg_len, char* out, int64_t out_cap, int64_t* out_len);
-    struct Udf { udf1_fn fn; void* user; };
+    typedef int (*udfn_fn)(void* user, int n_args, const char* const* args, const int64_t* arg_lens, char* out, int64_t out_cap, int64_t* out_len);
+    // n_args 0..3; fn (one string argument) or fnn (any arity); refresh: results are not kept from batch to batch (DynamicUDF
+    // with an onInterval handler, DynamicUDF.scala:12-46: the function may answer differently after every refresh)
+    struct Udf { udf1_fn fn = nullptr; void* user = nullptr; int n_args = 1; udfn_fn fnn = nullptr; bool refresh = false; };
+    typedef void (*interval_fn)(void* user, int64_t batch_time_ms);
+    interval_fn on_interval = nullptr; void* on_interval_user = nullptr;          // CPF:351-353: udfs.foreach(onInterval(spark, batchTime))
+    typedef int (*normalizer_fn)(void* user, const uint8_t* in, int64_t n_in, uint8_t* out, int64_t out_cap, int64_t* n_out);
+    normalizer_fn normalizer = nullptr; void* normalizer_user = nullptr;          // StringNormalizer before from_json (CPF:82, 93)
+    std::vector<uint8_t> normalized;                                              // the normalised batch of the call in progress
+    double normalizer_seconds = 0;
     std::map<std::string, Udf> udfs;                               // upper-cased name -> callback
     std::map<std::string, std::shared_ptr<LutCache>> luts;        // (expression, dictionary) -> device lookup table
     std::map<std::string, DxDictP> expr_dicts;                     // (statement, item) -> dictionary of a string-valued result, stable across batches

@@ -267,6 +267,62 @@ class CommonProcessor:
         fn.restype, fn.argtypes = C.c_int, [C.c_void_p, C.c_char_p, proto, C.c_void_p]
         self.ctx.check(fn(self.h, name.encode(), cb, None))
 
+    def register_udfn(self, name, n_args, func, refresh_each_batch=False):
+        """A user function of 0 to 3 arguments returning a string (DynamicUDF.Generator0..3 / Java UDF0..UDF3): func(*str) -> str | None.
+        Called once per distinct combination of argument values; every batch anew with refresh_each_batch."""
+        proto = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int, C.POINTER(C.POINTER(C.c_char)), C.POINTER(C.c_int64), C.POINTER(C.c_char), C.c_int64, C.POINTER(C.c_int64))
+
+        def thunk(user, n, args, lens, out, out_cap, out_len):
+            try:
+                r = func(*[C.string_at(args[k], lens[k]).decode("utf-8") for k in range(n)])
+                if r is None:
+                    out_len[0] = -1
+                    return 0
+                b = r.encode("utf-8")
+                if len(b) > out_cap:
+                    return 1
+                C.memmove(out, b, len(b))
+                out_len[0] = len(b)
+                return 0
+            except Exception:
+                return 1
+        cb = proto(thunk)
+        self._udf_keepalive = getattr(self, "_udf_keepalive", []) + [cb]
+        fn = self.L.dx_flow_register_udfn
+        fn.restype, fn.argtypes = C.c_int, [C.c_void_p, C.c_char_p, C.c_int, proto, C.c_void_p, C.c_int]
+        self.ctx.check(fn(self.h, name.encode(), n_args, cb, None, 1 if refresh_each_batch else 0))
+
+    def set_interval_hook(self, func):
+        """IntervalUpdateHandler.onInterval: func(batch_time_ms) at the start of every batch (CPF:351-353)."""
+        proto = C.CFUNCTYPE(None, C.c_void_p, C.c_int64)
+        cb = proto(lambda user, t: func(t))
+        self._udf_keepalive = getattr(self, "_udf_keepalive", []) + [cb]
+        fn = self.L.dx_flow_set_interval_hook
+        fn.restype, fn.argtypes = C.c_int, [C.c_void_p, proto, C.c_void_p]
+        self.ctx.check(fn(self.h, cb, None))
+
+    def set_normalizer(self, func):
+        """StringNormalizer (extension/StringNormalizer.scala:10-12): func(str) -> str applied to every record before from_json,
+        on the host, over batches passed in host memory."""
+        proto = C.CFUNCTYPE(C.c_int, C.c_void_p, C.POINTER(C.c_char), C.c_int64, C.POINTER(C.c_char), C.c_int64, C.POINTER(C.c_int64))
+
+        def thunk(user, inp, n_in, out, out_cap, n_out):
+            try:
+                lines = C.string_at(inp, n_in).split(b"\n")
+                res = b"\n".join(func(l.decode("utf-8", "replace")).encode("utf-8") if l else l for l in lines)
+                if len(res) > out_cap:
+                    return 1
+                C.memmove(out, res, len(res))
+                n_out[0] = len(res)
+                return 0
+            except Exception:
+                return 1
+        cb = proto(thunk)
+        self._udf_keepalive = getattr(self, "_udf_keepalive", []) + [cb]
+        fn = self.L.dx_flow_set_normalizer
+        fn.restype, fn.argtypes = C.c_int, [C.c_void_p, proto, C.c_void_p]
+        self.ctx.check(fn(self.h, cb, None))
+
     def import_state(self, name, columns, active="A"):
         """Restart (StateTableHandler.scala:70-96): `columns` = [(values ndarray | list of bytes/None for strings, valid
         bool ndarray | None)] in the order of the table's declared schema, as read back from the persisted copy."""

@@ -242,6 +242,26 @@ int dx_flow_add_refdata(dx_flow* flow, const char* name, const char* csv_text, c
  * table.  Return 0 on success; *out_len = -1 yields NULL; the result is copied out of `out` (out_cap bytes). */
 typedef int (*dx_udf1_fn)(void* user, const char* arg, int64_t arg_len, char* out, int64_t out_cap, int64_t* out_len);
 int dx_flow_register_udf(dx_flow* flow, const char* name, dx_udf1_fn fn, void* user);
+/* The other arities (DynamicUDF.Generator0..3, Java UDF0..UDF3 by class name, SparkJarLoader.scala:82-155; Azure-function
+ * UDFs of 0-3 arguments, AzureFunctionHandler.scala:42-64): a function of n_args in 0..3 values returning a string.
+ * Arguments reach the callback as text — strings as they are, integers in decimal, timestamps as Spark prints them — and the
+ * library calls it once per DISTINCT combination of argument values (once per batch for n_args == 0), keeping the answers
+ * as a device lookup table.  A NULL argument makes the result NULL without a call when n_args >= 2.  refresh_each_batch != 0
+ * is for functions whose answers change with time (a DynamicUDF with an onInterval handler): nothing is kept from one batch
+ * to the next.  Doubles cannot be passed (no decimal rendering of doubles here): CAST them in the SQL or fail at first use.  */
+typedef int (*dx_udfn_fn)(void* user, int n_args, const char* const* args, const int64_t* arg_lens, char* out, int64_t out_cap, int64_t* out_len);
+int dx_flow_register_udfn(dx_flow* flow, const char* name, int n_args, dx_udfn_fn fn, void* user, int refresh_each_batch);
+/* IntervalUpdateHandler.onInterval (DynamicUDF.scala:40-46, called for every dynamic UDF at the start of each batch,
+ * CommonProcessorFactory.scala:351-353): the host refreshes whatever its functions depend on.                              */
+typedef void (*dx_interval_fn)(void* user, int64_t batch_time_ms);
+int dx_flow_set_interval_hook(dx_flow* flow, dx_interval_fn fn, void* user);
+/* StringNormalizer (datax-core extension/StringNormalizer.scala:10-12; applied to Raw before from_json, CPF:82, 93; sample:
+ * datax-udf-samples RemoveInvalidChars).  User code runs on the host: before decoding a batch that arrives in HOST memory the
+ * library hands the whole NDJSON batch to fn, which writes the normalised batch (the same records, one per line) to out
+ * (out_cap = 2 * n_in + 64 bytes) and returns 0.  The time it takes is reported as the metric Latency-Normalizer.  A batch in
+ * device memory cannot be normalised: with a normalizer set such a call fails.  fn == NULL removes it.                     */
+typedef int (*dx_normalizer_fn)(void* user, const uint8_t* in, int64_t n_in, uint8_t* out, int64_t out_cap, int64_t* n_out);
+int dx_flow_set_normalizer(dx_flow* flow, dx_normalizer_fn fn, void* user);
 
 /* ---- one 8xB200 box: event-range sharding + key-hash shuffle ------------------------------- */
 /* Spark runs every GROUP BY as partial aggregate -> Exchange(hashpartitioning(keys)) -> final aggregate

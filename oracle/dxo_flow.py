@@ -797,8 +797,18 @@ class Ev:
                         out[i] = None
                     else:
                         out[i] = b"".join(parts)
-                else:
+                elif len(vals) == 1:
                     r = UDFS[fn](None if parts is None else parts[0].decode("utf-8"))
+                    ok[i] = r is not None
+                    out[i] = None if r is None else r.encode("utf-8")
+                else:
+                    # 0 arguments: one value per batch; 2 or 3: a NULL argument gives NULL without a call (dxgpu.h, dx_flow_register_udfn)
+                    if len(vals) == 0:
+                        if i == 0:
+                            const0 = UDFS[fn]()
+                        r = const0
+                    else:
+                        r = None if parts is None else UDFS[fn](*[p.decode("utf-8") for p in parts])
                     ok[i] = r is not None
                     out[i] = None if r is None else r.encode("utf-8")
             return "string", out, ok
@@ -815,7 +825,7 @@ class Ev:
         raise NotImplementedError(fn)
 
 
-UDFS = {}      # upper-cased name -> python callable(str | None) -> str | None (the flow's registered user functions)
+UDFS = {}      # upper-cased name -> python callable(*str) -> str | None (the flow's registered user functions, 0 to 3 arguments)
 
 
 AGGS = {"COUNT", "SUM", "MIN", "MAX", "AVG"}

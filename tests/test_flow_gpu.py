@@ -579,3 +579,45 @@ def test_transport_metadata_columns(dx, ctx):
         assert_same_rows(rg.table(name), ro[name], dx)
     rg.release()
     g.close()
+
+
+def test_user_function_arities_interval_hook_and_normalizer(dx, ctx):
+    """The hook surface of datax-core's extension package: functions of 0, 2 and 3 arguments (DynamicUDF.Generator0..3), a
+    function refreshed by onInterval whose answers change from batch to batch, and a StringNormalizer (RemoveInvalidChars of
+    datax-udf-samples) applied before from_json — each against the oracle running the same Python callables."""
+    state = {"greeting": "hi", "ticks": 0}
+
+    def on_interval(batch_ms):
+        state["ticks"] += 1
+        state["greeting"] = "hi%d" % state["ticks"]
+    udfs = {"SITE": (0, lambda: "plant-7"), "PAIR": (2, lambda a, b: a + "/" + b), "TRIPLE": (3, lambda a, b, c: None if b == "3" else "|".join([a, b, c])),
+            "GREET": (1, lambda a: state["greeting"] + " " + a)}
+    tr = """--DataXQuery--
+U = SELECT deviceDetails.deviceId, site() AS s, pair(deviceDetails.deviceType, CAST(deviceDetails.homeId AS String)) AS p,
+    triple(deviceDetails.deviceType, deviceDetails.status, deviceDetails.deviceType) AS t, greet(deviceDetails.deviceType) AS g FROM DataXProcessedInput
+"""
+    conf = dx.flowgen.conf_text("udfn")
+    g, o = both(dx, ctx, conf, SCHEMA1, ["Raw.*\n"], tr)
+    for name, (n, f) in udfs.items():
+        g.register_udfn(name, n, f, refresh_each_batch=(name == "GREET"))
+        dxo_flow.UDFS[name] = f
+    g.set_interval_hook(on_interval)
+    g.set_normalizer(lambda s: s.replace("\x01", ""))
+    try:
+        for b in range(3):
+            data = gen(dx, 800, first=b * 800, shape=1, n_keys=40, base=T0 + b * I)
+            dirty = data.replace(b'"deviceType":"', b'"deviceType":"\x01')       # an unescaped control character: the row would be NULL
+            greeting_before = state["greeting"]
+            rg = g.process_json(dirty, T0 + b * I, I)
+            assert state["ticks"] == b + 1 and "Latency-Normalizer" in rg.metrics
+            greeting_gpu = state["greeting"]
+            state["greeting"] = greeting_gpu                                        # the oracle sees the refreshed state of this batch
+            ro, mo = o.process(data, T0 + b * I, I)
+            assert_same_rows(rg.table("U"), ro["U"], dx)
+            vals = set(rg.table("U").column("g")[0])
+            assert all(v.startswith(greeting_gpu.encode() + b" ") for v in vals) and greeting_before != greeting_gpu
+            rg.release()
+    finally:
+        for name in udfs:
+            dxo_flow.UDFS.pop(name, None)
+    g.close()
