@@ -130,6 +130,11 @@ struct DxDict {
     int init(dx_ctx* c, uint32_t capacity_pow2, uint32_t heap_bytes);
     int insert_host(const std::string& s, int32_t* code_out);   // pre-seed literals
     int sync_to_host();                                          // pulls new entries
+    // A column of unbounded cardinality (event ids, CAST(timestamp AS STRING)) outgrows any fixed table.  grow() rebuilds the
+    // device table four times larger from the host mirror, every string keeping its code, so a streaming flow never dies of a
+    // full dictionary; callers re-run the kernel that reported the overflow.  overflowed(): the device counters say so.
+    int grow();
+    int overflowed(bool* yes);
     int lookup_host(const std::string& s) const;                 // -1 if absent (after sync)
 };
 typedef std::shared_ptr<DxDict> DxDictP;

@@ -119,6 +119,50 @@ int DxDict::sync_to_host() {
     return DX_OK;
 }
 
+__global__ void dict_bulk_insert(DictDev d, const uint8_t* bytes, const uint32_t* offs, uint32_t n, unsigned long long* err) {
+    // one thread, in code order: string k gets code k again
+    for (uint32_t k = 0; k < n; k++) {
+        const uint8_t* b = bytes + offs[k]; const uint32_t len = offs[k + 1] - offs[k];
+        uint64_t w0, w1; dict_pack(b, len, w0, w1);
+        if (dict_get_or_insert(d, w0, w1, len, b, err) != (int32_t)k) atomicOr(err, 1ull << 40);
+    }
+}
+
+int DxDict::overflowed(bool* yes) {
+    dx_ctx* c = ctx;
+    uint32_t cnt[4] = {0, 0, 0, 0};
+    DX_CUDA(c, cudaMemcpyAsync(cnt, counters.p, 16, cudaMemcpyDeviceToHost, c->stream));
+    DX_CUDA(c, cudaStreamSynchronize(c->stream));
+    *yes = cnt[0] > dev.max_codes || cnt[1] > dev.heap_cap;
+    return DX_OK;
+}
+
+int DxDict::grow() {
+    dx_ctx* c = ctx;
+    int rc = sync_to_host(); if (rc) return rc;          // every entry that fitted (codes < max_codes, bytes inside the heap)
+    const unsigned long long new_cap = ((unsigned long long)dev.cap_mask + 1) * 4, new_heap = (unsigned long long)dev.heap_cap * 4;
+    if (new_cap > (1ull << 28) || new_heap > (1ull << 31)) return c->set_error(DX_ERR_CAPACITY, "string dictionary cannot grow further (64 M entries / 2 GiB of text)");
+    std::vector<std::string> keep = host_strings;
+    std::map<std::string, int32_t> keep_seeded = seeded;
+    rc = init(c, (uint32_t)new_cap, (uint32_t)new_heap); if (rc) return rc;
+    host_strings = keep; seeded = keep_seeded;
+    if (keep.empty()) return DX_OK;
+    std::vector<uint32_t> offs(keep.size() + 1, 0); std::string blob;
+    for (size_t k = 0; k < keep.size(); k++) { blob += keep[k]; offs[k + 1] = (uint32_t)blob.size(); }
+    DevBuf dbytes(c, blob.size() + 16), doffs(c, offs.size() * 4), derr(c, 16);
+    if (!dbytes.p || !doffs.p || !derr.p) return c->set_error(DX_ERR_CUDA, "dictionary growth: allocation failed");
+    if (!blob.empty()) DX_CUDA(c, cudaMemcpyAsync(dbytes.p, blob.data(), blob.size(), cudaMemcpyHostToDevice, c->stream));
+    DX_CUDA(c, cudaMemcpyAsync(doffs.p, offs.data(), offs.size() * 4, cudaMemcpyHostToDevice, c->stream));
+    DX_CUDA(c, cudaMemsetAsync(derr.p, 0, 16, c->stream));
+    dict_bulk_insert<<<1, 1, 0, c->stream>>>(dev, dbytes.as<uint8_t>(), doffs.as<uint32_t>(), (uint32_t)keep.size(), derr.as<unsigned long long>());
+    unsigned long long e = 0;
+    DX_CUDA(c, cudaMemcpyAsync(&e, derr.p, 8, cudaMemcpyDeviceToHost, c->stream));
+    DX_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (e) return c->set_error(DX_ERR_STATE, "dictionary growth: codes changed while re-inserting");
+    c->counters["dict_grows"]++;
+    return DX_OK;
+}
+
 int DxDict::lookup_host(const std::string& s) const {
     for (size_t i = 0; i < host_strings.size(); i++) if (host_strings[i] == s) return (int)i;
     return -1;

@@ -251,6 +251,26 @@ int dx_decoder::decode_device(const uint8_t* json_dev, int64_t n_bytes, const in
     DX_CUDA(c, cudaGetLastError());
     DX_CUDA(c, cudaMemcpyAsync(&last_stats, dev_stats.p, sizeof(DecodeStats), cudaMemcpyDeviceToHost, c->stream));
     DX_CUDA(c, cudaStreamSynchronize(c->stream));
+    if ((last_stats.flags & DXF_DICT_OVERFLOW) && dict_retries < 6) {
+        // a string column has more distinct values than its dictionary holds: rebuild the full dictionaries four times larger
+        // (every string keeps its code) and decode this batch again — a stream of new values must not stop the flow
+        bool grew = false;
+        std::vector<DictDev> dd(hs.n_leaves); memset(dd.data(), 0, sizeof(DictDev) * hs.n_leaves);
+        for (int k = 0; k < hs.n_leaves; k++) {
+            if (!dicts[k]) continue;
+            bool full = false; int rc2 = dicts[k]->overflowed(&full); if (rc2) return rc2;
+            if (full) { rc2 = dicts[k]->grow(); if (rc2) return rc2; grew = true; }
+            dd[k] = dicts[k]->dev;
+        }
+        if (grew) {
+            DX_CUDA(c, cudaMemcpyAsync(dev_dicts.p, dd.data(), sizeof(DictDev) * hs.n_leaves, cudaMemcpyHostToDevice, c->stream));
+            DX_CUDA(c, cudaStreamSynchronize(c->stream));
+            dict_retries++;
+            int rc3 = decode_device(json_dev, n_bytes, offsets_dev, n_events, out);
+            dict_retries = 0;
+            return rc3;
+        }
+    }
     if (last_stats.flags & ~(unsigned long long)DXF_ROW_LIMITS) {      // per-record limits NULL the record (limited_rows); only these fail the call
         char b[256];
         snprintf(b, sizeof b, "decode failed: flags=0x%llx (1 dictionary overflow, 16 more records than n_events; "

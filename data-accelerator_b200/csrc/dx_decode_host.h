@@ -12,6 +12,7 @@ struct dx_decoder {
     DecodeStats last_stats{0, 0, 0, 0, 0};
     uint32_t dict_capacity = 1u << 16;     // slots per string column (power of two)
     uint32_t dict_heap_bytes = 4u << 20;
+    int dict_retries = 0;                  // decode passes repeated after a dictionary grew (decode_device)
     int ctas_per_sm = 1;
     int occ_by_tile[18] = {1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1};   // resident CTAs per SM of each tile-size instantiation of K1: [0..9) NDJSON, [9..18) caller-framed
     int init(dx_ctx* c, const std::string& schema_json);

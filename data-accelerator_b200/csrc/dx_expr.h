@@ -44,7 +44,7 @@ struct ExprPrograms {
     std::vector<long long> consts;
     std::vector<ProgCol> cols;
     std::vector<int> col_index;          // table column index behind cols[i]
-    struct LutSpec { int table_col; DxDictP dict; std::string pattern; bool negated; int kind; DevBufP bits; uint32_t built_for = 0; };
+    struct LutSpec { int table_col; DxDictP dict; std::string pattern; bool negated; int kind; DevBufP bits; uint32_t built_for = 0; uint32_t cap = 0; };
     std::vector<LutSpec> luts;           // kind 0 = LIKE pattern
     std::vector<DxDictP> result_dict;    // per program: dictionary of a STR result (else null)
     int max_stack = 0;

@@ -118,19 +118,25 @@ int dx_strbuild(dx_ctx* ctx, StrBuildArgs& a, const std::string& lit_bytes, cons
     if (!lit_bytes.empty()) DX_CUDA(ctx, cudaMemcpyAsync(lits.p, lit_bytes.data(), lit_bytes.size(), cudaMemcpyHostToDevice, ctx->stream));
     DX_CUDA(ctx, cudaMemsetAsync(err.p, 0, 16, ctx->stream));
     a.lit_bytes = lits.as<uint8_t>();
-    a.out_dict = out_dict->dev;
-    {
-        StageTimer tm(ctx, "k_strbuild");
-        k_strbuild<<<grid_of(ctx, a.n_rows), 256, 0, ctx->stream>>>(a, out_codes, vmask32, vbit, err.as<unsigned long long>());
-        ctx->launches["k_strbuild"]++;
+    for (int attempt = 0;; attempt++) {
+        a.out_dict = out_dict->dev;
+        {
+            StageTimer tm(ctx, "k_strbuild");
+            k_strbuild<<<grid_of(ctx, a.n_rows), 256, 0, ctx->stream>>>(a, out_codes, vmask32, vbit, err.as<unsigned long long>());
+            ctx->launches["k_strbuild"]++;
+        }
+        DX_CUDA(ctx, cudaGetLastError());
+        unsigned long long h = 0;
+        DX_CUDA(ctx, cudaMemcpyAsync(&h, err.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
+        DX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        if (h & 32ull) return ctx->set_error(DX_ERR_UNSUPPORTED, "string expression produced a value longer than 256 bytes");
+        if (!h) return DX_OK;
+        // the result dictionary is full: rebuild it larger (codes are kept) and build the strings again
+        if (attempt >= 6) return ctx->set_error(DX_ERR_CAPACITY, "string dictionary overflow while building strings");
+        int rc = out_dict->grow(); if (rc) return rc;
+        DX_CUDA(ctx, cudaMemsetAsync(err.p, 0, 16, ctx->stream));
+        // (vmask32 bits set by the failed pass are set again by the next: every row writes the same validity)
     }
-    DX_CUDA(ctx, cudaGetLastError());
-    unsigned long long h = 0;
-    DX_CUDA(ctx, cudaMemcpyAsync(&h, err.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
-    DX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    if (h & 32ull) return ctx->set_error(DX_ERR_UNSUPPORTED, "string expression produced a value longer than 256 bytes");
-    if (h) return ctx->set_error(DX_ERR_CAPACITY, "string dictionary overflow while building strings");
-    return DX_OK;
 }
 
 int dx_lut_apply(dx_ctx* ctx, const DxColumn& in, const LutCache& lut, int64_t n_rows, const int64_t* sel, void* out, int out_width,
@@ -150,10 +156,15 @@ int dx_lut_apply(dx_ctx* ctx, const DxColumn& in, const LutCache& lut, int64_t n
 int dx_lut_refresh(dx_ctx* ctx, LutCache* lut, const DxDictP& dict, const std::function<bool(const std::string&, long long*)>& fn) {
     int rc = dict->sync_to_host(); if (rc) return rc;
     const uint32_t n = (uint32_t)dict->host_strings.size();
-    if (!lut->vals.p) {
-        lut->vals = DevBuf(ctx, (size_t)dict->dev.max_codes * 8 + 16);
-        lut->valid = DevBuf(ctx, (size_t)dict->dev.max_codes + 16);
-        if (!lut->vals.p || !lut->valid.p) return ctx->set_error(DX_ERR_CUDA, "lookup table allocation failed");
+    if (!lut->vals.p || lut->cap < dict->dev.max_codes) {      // first use, or the dictionary has grown since
+        DevBuf nv(ctx, (size_t)dict->dev.max_codes * 8 + 16), nok(ctx, (size_t)dict->dev.max_codes + 16);
+        if (!nv.p || !nok.p) return ctx->set_error(DX_ERR_CUDA, "lookup table allocation failed");
+        if (lut->vals.p && lut->built) {
+            DX_CUDA(ctx, cudaMemcpyAsync(nv.p, lut->vals.p, (size_t)lut->built * 8, cudaMemcpyDeviceToDevice, ctx->stream));
+            DX_CUDA(ctx, cudaMemcpyAsync(nok.p, lut->valid.p, (size_t)lut->built, cudaMemcpyDeviceToDevice, ctx->stream));
+            DX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        }
+        lut->vals = std::move(nv); lut->valid = std::move(nok); lut->cap = dict->dev.max_codes;
     }
     if (n > lut->built) {
         std::vector<long long> v(n - lut->built); std::vector<uint8_t> ok(n - lut->built);

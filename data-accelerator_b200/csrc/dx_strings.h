@@ -26,6 +26,7 @@ struct StrBuildArgs {
 struct LutCache {
     DevBuf vals, valid;
     uint32_t built = 0;          // codes [0, built) are filled
+    uint32_t cap = 0;            // codes the two arrays hold (the source dictionary's max_codes when they were allocated)
     DxDictP out_dict;            // string-valued tables (UDF results): dictionary of the results
     DxDictP src_dict;            // kept alive where the cache key is the source dictionary's address
 };

@@ -239,3 +239,27 @@ def test_oversize_and_nested_values_null_the_row_not_the_batch(dx, ctx):
     assert mo["Input_Unparsed_Events_Count"] == 1.0
     r.release()
     g.close()
+
+
+def test_dictionaries_grow_instead_of_failing_the_stream(dx, ctx):
+    """A string column of unbounded cardinality: 90 000 distinct device types over two batches (a dictionary starts with room
+    for 32 768), and 50 000 distinct CONCAT results.  The dictionaries are rebuilt larger with every code kept; the batches
+    decode, and every string reads back as the oracle has it."""
+    import dxo_flow
+    from flowcmp import assert_same_rows
+    ctx.take_counter("dict_grows")
+    rec = '{"deviceDetails":{"deviceId":%d,"deviceType":"type-%d-%s","eventTime":1700000039000,"homeId":%d,"status":1}}'
+    S1 = dxo.iot_schema_json(1)
+    conf = dx.flowgen.conf_text("grow")
+    tr = "--DataXQuery--\nT = SELECT deviceDetails.deviceType, CONCAT('id-', CAST(deviceDetails.deviceId AS String)) AS s FROM DataXProcessedInput\n"
+    g = dx.CommonProcessorFactory.createProcessor(ctx, conf, S1, ["Raw.*\n"], tr)
+    o = dxo_flow.Flow(conf, S1, ["Raw.*\n"], tr)
+    for b in range(2):
+        recs = [rec % (b * 50_000 + k, (b * 45_000 + k) % 90_000, "x" * (k % 23), k % 7) for k in range(50_000)]
+        data = ("\n".join(recs) + "\n").encode()
+        rg = g.process_json(data, 1_700_000_040_000 + b * 60_000, 60_000)
+        ro, _ = o.process(data, 1_700_000_040_000 + b * 60_000, 60_000)
+        assert_same_rows(rg.table("T"), ro["T"], dx)
+        rg.release()
+    assert ctx.take_counter("dict_grows") >= 2          # the decoder's deviceType dictionary and the CONCAT result dictionary
+    g.close()
