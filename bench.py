@@ -70,16 +70,21 @@ def traffic_of(kernel, events_per_launch):
 
 
 class ClockSampler:
-    """nvidia-smi clocks/throttle reasons sampled DURING a timed region."""
+    """nvidia-smi clocks/throttle reasons sampled DURING a timed region.  ONE poller per run (rank 0), over the GPUs the run uses:
+    a poller per rank at 50 Hz means eight processes taking the driver's lock while every rank is issuing launches and small
+    synchronising copies, and the step time of the whole job then follows the unluckiest rank."""
 
-    def __init__(self, gpu_index):
-        self.rows, self.proc, self.idx = [], None, gpu_index
+    def __init__(self, gpu_index, n_gpus=1, enabled=True):
+        self.rows, self.proc, self.idx, self.n, self.enabled = [], None, gpu_index, n_gpus, enabled
 
     def start(self):
+        if not self.enabled:
+            return self
         q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        ids = ",".join(str(i) for i in range(self.n)) if self.n > 1 else str(self.idx)
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + q, "--format=csv,noheader,nounits", "-lms", "20"],
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", ids, "--query-gpu=" + q, "--format=csv,noheader,nounits", "-lms", "20" if self.n == 1 else "100"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             threading.Thread(target=self._read, daemon=True).start()
         except OSError:
@@ -101,7 +106,7 @@ class ClockSampler:
                 if v.lower().startswith("active"):
                     reasons.add(name)
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                "reasons": sorted(reasons), "samples": len(sm), "gpus_sampled": self.n if self.enabled else 0}
 
 
 def artefacts(dx):
@@ -332,7 +337,7 @@ def run_ours(args):
     for k in host_keys:
         ctx.take_counter("host_us:" + k)
     t_wall0 = time.perf_counter()
-    sampler = ClockSampler(local).start()
+    sampler = ClockSampler(local, world, enabled=(rank == 0)).start()
     ms = 0.0
     for _ in range(args.steps):
         generate(step_no)
@@ -426,7 +431,7 @@ def run_ours(args):
             r.release()
     for _ in range(3):
         step_c2(0)
-    smp = ClockSampler(local).start()
+    smp = ClockSampler(local, world, enabled=(rank == 0)).start()
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(stream)

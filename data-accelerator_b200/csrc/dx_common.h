@@ -1,5 +1,6 @@
 // dx_common.h — shared host/device definitions for libdxgpu (sm_100a only).
 #pragma once
+#include <nvtx3/nvToolsExt.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
@@ -182,9 +183,18 @@ struct DxTable {
 typedef std::shared_ptr<DxTable> DxTableP;
 
 // stage timing helper
+// NVTX range for the life of the object: every kernel stage (through StageTimer) and every phase of a micro-batch (project,
+// route, each statement) shows up by name on a profiler's timeline; without a tool attached the calls are no-ops.
+struct NvtxRange {
+    explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+    explicit NvtxRange(const std::string& name) { nvtxRangePushA(name.c_str()); }
+    ~NvtxRange() { nvtxRangePop(); }
+    NvtxRange(const NvtxRange&) = delete; NvtxRange& operator=(const NvtxRange&) = delete;
+};
+
 struct StageTimer {
-    dx_ctx* ctx; const char* name; cudaEvent_t a = nullptr, b = nullptr;
-    StageTimer(dx_ctx* c, const char* n) : ctx(c), name(n) {
+    dx_ctx* ctx; const char* name; cudaEvent_t a = nullptr, b = nullptr; NvtxRange range;
+    StageTimer(dx_ctx* c, const char* n) : ctx(c), name(n), range(n) {
         if (ctx->timing) { cudaEventCreate(&a); cudaEventCreate(&b); cudaEventRecord(a, ctx->stream); }
     }
     void stop() {

@@ -1855,6 +1855,7 @@ bool dx_is_metadata_column(const std::string& n) {
 int dx_flow::project(const uint8_t* json, int64_t n_bytes, const int64_t* offsets, int64_t n_events, int memory_kind,
                      long long now_ms, DxTableP* out, long long batch_ms) {
     const long long batch_ms_for_props = batch_ms >= 0 ? batch_ms : now_ms;
+    NvtxRange nvtx_project("project");
     DxTableP raw;
     int rc = memory_kind == 1 ? decoder->decode_device(json, n_bytes, offsets, n_events, &raw) : decoder->decode_host(json, n_bytes, offsets, n_events, &raw);
     if (rc) return rc;
@@ -1925,6 +1926,7 @@ int dx_flow::route(const std::string& name_space, const DxTableP& projected, lon
     std::unique_ptr<dx_result> R(new dx_result()); R->flow = this;
     auto metric = [&](const std::string& k, double v) { R->metric_keys.push_back(k); R->metric_vals.push_back(v); };
     if (!batch_t0_set) batch_t0 = std::chrono::steady_clock::now();       // route() called on its own (dx_flow_process_table)
+    NvtxRange nvtx_route("route");
     int rc = DX_OK;
     ViewMap views;
     Exec X{this, ctx, &views, now_ms * 1000, ""};
@@ -1994,7 +1996,9 @@ int dx_flow::route(const std::string& name_space, const DxTableP& projected, lon
     for (auto& cmd : transform.commands) {
         X.stmt_name = cmd.name;
         const auto t_stmt = std::chrono::steady_clock::now();
-        DxTableP res; rc = X.exec_statement(cmd.stmt, &res); if (rc) return rc;
+        DxTableP res;
+        { NvtxRange nvtx_stmt("stmt:" + cmd.name); rc = X.exec_statement(cmd.stmt, &res); }
+        if (rc) return rc;
         ctx->counters["host_us:stmt:" + cmd.name] += std::chrono::duration_cast<std::chrono::microseconds>(std::chrono::steady_clock::now() - t_stmt).count();
         res->name = cmd.name;
         auto st = state_tables.find(cmd.name);
