@@ -197,10 +197,11 @@ __global__ void __launch_bounds__(PT_NT) k5_put_tiled(const __grid_constant__ Sh
             s_dst[slot] = tg.base[dst[j]] + (tg.first[dst[j]] + s_gstart[dst[j]] + rank[j]) * rw;
         }
         __syncthreads();
-        const unsigned int n_words = s_base[a.world] * (unsigned int)rw;
-        for (unsigned int f = tid; f < n_words; f += PT_NT) {
-            const unsigned int slot = f / (unsigned int)rw, w = f - slot * (unsigned int)rw;
-            s_dst[slot][w] = pt_stage[f];
+        {   // no division: word index = thread id modulo the next power of two >= the record length (the lanes past it idle)
+            int sh = 0; while ((1 << sh) < rw) sh++;
+            const unsigned int w = tid & ((1u << sh) - 1u), r0 = tid >> sh, rstep = PT_NT >> sh, n_slots = s_base[a.world];
+            if (w < (unsigned int)rw)
+                for (unsigned int slot = r0; slot < n_slots; slot += rstep) s_dst[slot][w] = pt_stage[slot * rw + w];
         }
         __syncthreads();
     }
