@@ -12,7 +12,8 @@
 #ifndef K1_NT
 #define K1_NT 256           // threads per CTA
 #endif
-#define K1_SC 1024          // record starts held in shared memory per round
+#define K1_SC 1024          // (caller-framed kernels only) kept for the shared-memory layout
+#define K1_WCAP 126         // record starts a warp holds per round (a slice normally has ~30 records)
 #ifndef K1_STAGES
 #define K1_STAGES 1         // shared-memory tile stages; 2 = prefetch the next tile while parsing (measured slower: the resident CTAs of an SM already overlap copy and parse)
 #endif
@@ -103,13 +104,12 @@ template <int K1_T, bool FRAMED>
 __global__ void __launch_bounds__(K1_NT, FRAMED ? K1_MIN_CTAS_FRAMED : K1_MIN_CTAS) k1_decode(const __grid_constant__ DecodeArgs a) {
     extern __shared__ __align__(128) uint8_t smem[];
     constexpr int TILE_BYTES = K1_T + K1_OVL + K1_PAD;                     // one staged tile (multiple of 16)
-    uint16_t* s_starts = reinterpret_cast<uint16_t*>(smem + K1_STAGES * TILE_BYTES);   // K1_SC + 2
+    uint16_t* s_starts = reinterpret_cast<uint16_t*>(smem + K1_STAGES * TILE_BYTES);   // per warp: chunk list (K1_T / 128 entries) + K1_WCAP + 2 record starts
     __shared__ uint64_t s_bar[K1_STAGES];
     __shared__ long long s_tile;
     __shared__ long long s_rowbase;
     __shared__ uint32_t s_wtot[K1_NT / 32];
     __shared__ long long s_r0;
-    __shared__ uint32_t s_tail_nl;   // first newline at or past the tile end (shared-memory position), ~0u if none loaded
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const DSchemaDev* S = a.schema;
@@ -171,24 +171,40 @@ __global__ void __launch_bounds__(K1_NT, FRAMED ? K1_MIN_CTAS_FRAMED : K1_MIN_CT
         long long n_rec = 0; long long rec0 = 0;   // offsets mode: records [rec0, rec0+n_rec)
         const bool first_virtual = (tile == 0 && (long long)a.skew < a.n_end);
         if (!FRAMED) {
-            // --- structural scan: newline q in [lo, hi) owns the record starting at q+1 ---
-            // warp w scans chunks [w*CPW, (w+1)*CPW), lane-strided so shared loads are conflict-free
-            constexpr int CPW = (K1_T / 16) / (K1_NT / 32);   // 256
-            constexpr int ROUNDS = CPW / 32;                  // 8
+            // --- structural scan and parse, warp by warp: warp w owns the records whose preceding newline q lies in its slice
+            // [w * SLICE, (w + 1) * SLICE) of the tile (newline q owns the record starting at q + 1).  A warp scans its own slice,
+            // lists its own record starts and parses its own records: the only thing the warps of a CTA exchange is their record
+            // counts (for the row numbers), so a tile costs two CTA barriers between load and parse instead of a CTA-wide scan,
+            // prefix sum and record redistribution.
+            // Scan: newlines are sparse (one per ~150 bytes), so a lane first only decides whether its 16 bytes hold ANY 0x0A
+            // (three instructions per word, exact as a yes / no); the chunks that do are listed in shared memory by ballot rank,
+            // and the exact per-byte masks, the data-bounds masking of a batch's first and last tile and the prefix sums run once
+            // per slice over that list with every lane busy, not once per round with three lanes busy.
+            constexpr int NWARP = K1_NT / 32;
+            constexpr int SLICE = K1_T / NWARP;               // bytes per warp: a multiple of 512
+            constexpr int ROUNDS = SLICE / 512;
+            constexpr int LCAP = SLICE / 16;                  // chunks per slice: the list cannot overflow
+            uint16_t* w_list = s_starts + warp * (LCAP + K1_WCAP + 2);
+            uint16_t* w_starts = w_list + LCAP;               // K1_WCAP + 2 record starts of the round being parsed
             const bool edge_tile = lo < (long long)a.skew || lo + (long long)K1_T + 16 >= a.n_end;
-            // A tile with more than K1_SC records (records shorter than ~40 bytes) is parsed in rounds of K1_SC; every round
-            // repeats the scan instead of keeping its masks and ranks, so those registers are free while records are parsed.
-            for (uint32_t round0 = 0; ; round0 += K1_SC) {
-            if (round0 > 0) __syncthreads();      // the previous round's readers of s_starts / s_wtot are done
-            uint32_t cnt_total = 0;
-            uint32_t excl_in_warp[ROUNDS];
-            uint32_t my_masks[(ROUNDS + 1) / 2];
+            const uint32_t lt_mask = (1u << lane) - 1u;
+            uint32_t n_list = 0;
 #pragma unroll
             for (int r = 0; r < ROUNDS; r++) {
-                const int chunk = warp * CPW + r * 32 + lane;
+                const int chunk = warp * LCAP + r * 32 + lane;
                 const uint4 v = *reinterpret_cast<const uint4*>(buf + chunk * 16);
-                uint32_t m = 0;
+                const uint32_t x0 = v.x ^ 0x0A0A0A0Au, x1 = v.y ^ 0x0A0A0A0Au, x2 = v.z ^ 0x0A0A0A0Au, x3 = v.w ^ 0x0A0A0A0Au;
+                const uint32_t z = (((x0 - 0x01010101u) & ~x0) | ((x1 - 0x01010101u) & ~x1) | ((x2 - 0x01010101u) & ~x2) | ((x3 - 0x01010101u) & ~x3)) & 0x80808080u;
+                const uint32_t bal = __ballot_sync(0xffffffffu, z != 0);
+                if (z) w_list[n_list + __popc(bal & lt_mask)] = (uint16_t)chunk;
+                n_list += __popc(bal);
+            }
+            __syncwarp();
+            // exact newline mask of one listed chunk (bit i: byte i is a newline that starts a record of this batch)
+            auto chunk_mask = [&](uint32_t chunk) -> uint32_t {
+                const uint4 v = *reinterpret_cast<const uint4*>(buf + chunk * 16);
                 const uint32_t ws[4] = {v.x, v.y, v.z, v.w};
+                uint32_t m = 0;
 #pragma unroll
                 for (int k = 0; k < 4; k++) {
                     const uint32_t x = ws[k] ^ 0x0A0A0A0Au;                 // zero byte where '\n'
@@ -196,42 +212,39 @@ __global__ void __launch_bounds__(K1_NT, FRAMED ? K1_MIN_CTAS_FRAMED : K1_MIN_CT
                     t = ~(t | x | 0x7F7F7F7Fu);                             // 0x80 in each byte that was zero
                     m |= ((t * 0x00204081u) >> 28) << (k * 4);              // gather the four flags
                 }
-                // validity of each candidate q = lo + chunk*16 + i : start q+1 must be data (< n_end), q >= skew
                 if (edge_tile) m = k1_edge_mask(m, lo + (long long)chunk * 16, a.n_end, (long long)a.skew);
-                if (r & 1) my_masks[r >> 1] |= m << 16; else my_masks[r >> 1] = m;
-                excl_in_warp[r] = __popc(m);          // this lane's count for now; turned into a rank below
-            }
+                return m;
+            };
+            const bool first_virtual_w = first_virtual && warp == 0;       // the batch's first record has no newline before it
+            // one pass over the list: counts the warp's records and stores the starts of ranks [round0, round0 + K1_WCAP]
+            auto list_pass = [&](uint32_t round0) -> uint32_t {
+                uint32_t total = first_virtual_w ? 1u : 0u;
+                if (first_virtual_w && round0 == 0 && lane == 0) w_starts[0] = (uint16_t)a.skew;
+                for (uint32_t e0 = 0; e0 < n_list; e0 += 32) {
+                    const uint32_t e = e0 + lane;
+                    uint32_t chunk = 0, m = 0;
+                    if (e < n_list) { chunk = w_list[e]; m = chunk_mask(chunk); }
+                    const uint32_t c = __popc(m);
+                    uint32_t incl = c;
+#pragma unroll
+                    for (int sft = 1; sft < 32; sft <<= 1) { const uint32_t t = __shfl_up_sync(0xffffffffu, incl, sft); if (lane >= sft) incl += t; }
+                    uint32_t rel = total + incl - c - round0;              // wraps to a huge value for ranks of earlier rounds
+                    const uint32_t pos0 = chunk * 16 + 1;
+                    while (m) {
+                        const int i = __ffs(m) - 1; m &= m - 1;
+                        if (rel <= K1_WCAP) w_starts[rel] = (uint16_t)(pos0 + i);
+                        rel++;
+                    }
+                    total += __shfl_sync(0xffffffffu, incl, 31);
+                }
+                return total;
+            };
+            const uint32_t total_w = list_pass(0);
+            // the warp's last record ends at the first newline at or past the slice end: found by the whole warp, 16 bytes per lane
+            uint32_t w_tail = 0xFFFFFFFFu;
             {
-                // one prefix sum for three rounds at a time: a lane's count is <= 16 and a round's total <= 512, so three 10-bit
-                // fields share a word and the rounds' shuffle chains run side by side instead of one after the other
-                constexpr int NW = (ROUNDS + 2) / 3;
-                uint32_t pk[NW];
-#pragma unroll
-                for (int w = 0; w < NW; w++) {
-                    pk[w] = excl_in_warp[3 * w];
-                    if (3 * w + 1 < ROUNDS) pk[w] |= excl_in_warp[3 * w + 1] << 10;
-                    if (3 * w + 2 < ROUNDS) pk[w] |= excl_in_warp[3 * w + 2] << 20;
-                }
-#pragma unroll
-                for (int s = 1; s < 32; s <<= 1) {
-#pragma unroll
-                    for (int w = 0; w < NW; w++) { const uint32_t t = __shfl_up_sync(0xffffffffu, pk[w], s); if (lane >= s) pk[w] += t; }
-                }
-#pragma unroll
-                for (int r = 0; r < ROUNDS; r++) {
-                    const uint32_t incl = (pk[r / 3] >> (10 * (r % 3))) & 1023u;
-                    const uint32_t tot = (__shfl_sync(0xffffffffu, pk[r / 3], 31) >> (10 * (r % 3))) & 1023u;
-                    excl_in_warp[r] = cnt_total + incl - excl_in_warp[r];
-                    cnt_total += tot;
-                }
-            }
-            if (lane == 0) s_wtot[warp] = cnt_total;
-            if (warp == K1_NT / 32 - 1 && round0 == 0) {
-                // the tile's last record ends at the first newline at or past the tile end: find it with the
-                // whole warp (16 bytes per lane per round) instead of one lane walking bytes
                 const uint32_t lim = (uint32_t)avail + ((lo + avail == a.n_end) ? 1u : 0u);
-                uint32_t found = 0xFFFFFFFFu;
-                for (uint32_t c0 = K1_T / 16; c0 * 16 < lim && found == 0xFFFFFFFFu; c0 += 32) {
+                for (uint32_t c0 = (uint32_t)(warp + 1) * LCAP; c0 * 16 < lim && w_tail == 0xFFFFFFFFu; c0 += 32) {
                     const uint32_t chunk = c0 + lane;
                     uint32_t m = 0;
                     if (chunk * 16 < lim) {
@@ -250,17 +263,17 @@ __global__ void __launch_bounds__(K1_NT, FRAMED ? K1_MIN_CTAS_FRAMED : K1_MIN_CT
                     if (who) {
                         const int src = __ffs(who) - 1;
                         const uint32_t mm = __shfl_sync(0xffffffffu, m, src);
-                        found = (c0 + src) * 16 + (__ffs(mm) - 1);
+                        w_tail = (c0 + src) * 16 + (__ffs(mm) - 1);
                     }
                 }
-                if (lane == 0) s_tail_nl = found;
             }
+            if (lane == 0) s_wtot[warp] = total_w;
             __syncthreads();
-            uint32_t wbase = first_virtual ? 1u : 0u, total = first_virtual ? 1u : 0u;
+            uint32_t wbase = 0, total = 0;
 #pragma unroll
-            for (int w = 0; w < K1_NT / 32; w++) { uint32_t t = s_wtot[w]; if (w < warp) wbase += t; total += t; }
+            for (int w = 0; w < NWARP; w++) { const uint32_t t = s_wtot[w]; if (w < warp) wbase += t; total += t; }
             n_rec = total;
-            if (warp == 0 && round0 == 0) {
+            if (warp == 0) {
 #ifdef K1_NO_LOOKBACK    /* tuning experiment only: what the row-index look-back costs (row numbers are wrong in this build) */
                 long long rb = tile * 200;
 #else
@@ -268,37 +281,26 @@ __global__ void __launch_bounds__(K1_NT, FRAMED ? K1_MIN_CTAS_FRAMED : K1_MIN_CT
 #endif
                 if (lane == 0) s_rowbase = rb;
             }
-            {
-                if (first_virtual && tid == 0 && round0 == 0) s_starts[0] = (uint16_t)a.skew;
-#pragma unroll
-                for (int r = 0; r < ROUNDS; r++) {
-                    uint32_t m = (r & 1) ? (my_masks[r >> 1] >> 16) : (my_masks[r >> 1] & 0xffffu);
-                    uint32_t rel = wbase + excl_in_warp[r] - round0;     // wraps to a huge value for earlier rounds' records
-                    const uint32_t pos0 = (uint32_t)(warp * CPW + r * 32 + lane) * 16 + 1;
-                    while (m) {
-                        const int i = __ffs(m) - 1; m &= m - 1;
-                        if (rel <= K1_SC) s_starts[rel] = (uint16_t)(pos0 + i);
-                        rel++;
-                    }
-                }
-                __syncthreads();
-                const long long row_base = s_rowbase;
-                const int cnt = (int)((n_rec - round0 > K1_SC) ? K1_SC : (n_rec - round0));
-                for (int base = 0; base < cnt; base += K1_NT) {
-                    const int idx = base + tid;
+            __syncthreads();
+            const long long row_base = s_rowbase + wbase;
+            for (uint32_t round0 = 0; round0 < total_w; round0 += K1_WCAP) {
+                if (round0 > 0) { __syncwarp(); list_pass(round0); }          // a slice of very short records: the next K1_WCAP starts
+                __syncwarp();
+                const int cnt = (int)((total_w - round0 > K1_WCAP) ? K1_WCAP : (total_w - round0));
+                for (int base = 0; base < cnt; base += 32) {
+                    const int idx = base + lane;
                     const bool has = idx < cnt;
                     uint32_t st = 0, en = 0; bool in_smem = true; long long en_abs = 0;
-                    const long long rank = round0 + idx;
+                    const uint32_t rank = round0 + idx;
                     if (has) {
-                        st = s_starts[idx];
-                        if (rank + 1 < n_rec) en = (uint32_t)s_starts[idx + 1] - 1u;
+                        st = w_starts[idx];
+                        if (rank + 1 < total_w) en = (uint32_t)w_starts[idx + 1] - 1u;
                         else {
-                            // last record owned by this tile: its newline lies at or past the tile end
+                            // last record owned by this warp: its newline lies at or past the slice end
                             const uint32_t lim = (uint32_t)avail + ((lo + avail == a.n_end) ? 1u : 0u);
-                            const uint32_t p = s_tail_nl;
-                            if (p != 0xFFFFFFFFu) en = p;
+                            if (w_tail != 0xFFFFFFFFu) en = w_tail;
                             else if (lo + avail == a.n_end) {
-                                // the data ends inside the tile proper: the record runs to the final newline or the end of data
+                                // the data ends inside the loaded bytes: the record runs to the final newline or the end of data
                                 const uint32_t av = (uint32_t)avail;
                                 en = (av > st && buf[av - 1] == '\n') ? av - 1 : av;
                             } else {
@@ -334,8 +336,6 @@ __global__ void __launch_bounds__(K1_NT, FRAMED ? K1_MIN_CTAS_FRAMED : K1_MIN_CT
                         else reinterpret_cast<uint32_t*>(a.mask)[o.row] = o.valid | (ok ? 0x80000000u : 0u);
                     }
                 }
-                if ((long long)round0 + K1_SC >= n_rec) break;
-            }
             }
         } else {
             // --- caller-provided framing: records whose first byte lies in [lo, hi) ---
@@ -424,7 +424,7 @@ __global__ void __launch_bounds__(K1_NT, FRAMED ? K1_MIN_CTAS_FRAMED : K1_MIN_CT
 }
 
 static inline size_t k1_smem_bytes(int tile) {
-    return K1_STAGES * (tile + K1_OVL + K1_PAD) + (K1_SC + 2) * 2 + 64;
+    return K1_STAGES * (tile + K1_OVL + K1_PAD) + (size_t)(K1_NT / 32) * (tile / (K1_NT / 32) / 16 + K1_WCAP + 2) * 2 + 64;
 }
 
 // dx_decode_framed.cu
