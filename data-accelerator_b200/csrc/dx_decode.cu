@@ -36,12 +36,12 @@ __global__ void k1_count_records(const uint8_t* bytes, long long n, unsigned lon
 // host side
 // =======================================================================================
 static const int k1_tiles[] = {16384, 20480, 24576, 28672, 32768, 36864, 40960, 45056, 49152};
-// tile bytes for a batch: the largest instantiated size that still keeps the expected records per tile under ~246
+// tile bytes for a batch: the largest instantiated size that still keeps the expected records per tile just under the CTA's thread count
 static int k1_pick_tile(long long n_bytes, long long n_events) {
     if (n_events <= 0 || n_bytes <= 0) return K1_T_DEFAULT;
     const double avg = (double)n_bytes / (double)n_events;
     int best = k1_tiles[0];
-    for (int t : k1_tiles) if ((double)t / avg <= 246.0) best = t;
+    for (int t : k1_tiles) if ((double)t / avg <= (double)(K1_NT - 10)) best = t;
     return best;
 }
 template <int T> static int k1_setup_one(dx_ctx* c, int* occ_out) {      // occ_out[0]: NDJSON kernel, occ_out[9]: framed kernel
@@ -153,12 +153,13 @@ int dx_decoder::init(dx_ctx* c, const std::string& schema_json) {
         size_t L = b.seg_lits[i].size(), Lp = (L + 3) & ~size_t(3);
         if (lit_used + Lp > DX_LITS_BYTES) { tmpl_ok = false; break; }
         memcpy(reinterpret_cast<char*>(hs.lits) + lit_used, b.seg_lits[i].data(), L);
-        hs.segs[i].lit_off = (uint16_t)lit_used; hs.segs[i].lit_len = (uint16_t)L;
-        hs.segs[i].type = (int16_t)b.seg_types[i]; hs.segs[i].leaf = (int16_t)b.seg_leaves[i];
-        hs.segs[i].tail_mask = (L & 3) ? ((1u << ((L & 3) << 3)) - 1u) : 0u;
+        if (L == 0) { tmpl_ok = false; break; }
+        hs.segs[i].lit_word = (uint32_t)(lit_used >> 2); hs.segs[i].n_words = (uint32_t)(Lp >> 2); hs.segs[i].lit_len = (uint32_t)L;
+        hs.segs[i].type = b.seg_types[i]; hs.segs[i].leaf = b.seg_leaves[i];
+        hs.segs[i].last_mask = (L & 3) ? ((1u << ((L & 3) << 3)) - 1u) : 0xffffffffu;
         lit_used += Lp; hs.n_segs++;
     }
-    if (!tmpl_ok) { hs.n_segs = 1; hs.segs[0].lit_off = 0; hs.segs[0].lit_len = 4; hs.segs[0].type = 0; hs.segs[0].tail_mask = 0; memcpy(hs.lits, "\x01\x01\x01\x01", 4); }
+    if (!tmpl_ok) { hs.n_segs = 1; hs.segs[0] = DSeg{0u, 1u, 4u, 0xffffffffu, 0, 0}; memcpy(hs.lits, "\x01\x01\x01\x01", 4); }
     for (int k = 0; k < hs.n_leaves; k++) leaf_types.push_back(hs.leaf_type[k]);
     dev_schema = DevBuf(c, sizeof(DSchemaDev));
     DX_CUDA(c, cudaMemcpyAsync(dev_schema.p, &hs, sizeof hs, cudaMemcpyHostToDevice, c->stream));

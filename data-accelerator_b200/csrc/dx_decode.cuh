@@ -26,7 +26,10 @@
 
 struct DField { uint16_t name_off, name_len; int32_t type; int32_t target; };
 struct DStruct { int32_t first_field, n_fields, first_leaf, n_leaves; };
-struct DSeg { uint16_t lit_off, lit_len; int16_t type, leaf; uint32_t tail_mask; };   // type 0: trailing literal only; tail_mask: the 1..3 bytes past the last whole literal word (0 = none)
+// One template segment: a literal, then (type != 0) one leaf value.  All fields are ready-to-use 32-bit values so that the
+// warp-uniform constant-bank reads in the fast path need no unpacking: the literal occupies words lit_word .. lit_word + n_words - 1
+// of lits (n_words >= 1), the last of them compared under last_mask (all ones when the literal ends on a word boundary).
+struct DSeg { uint32_t lit_word, n_words, lit_len, last_mask; int32_t type, leaf; };
 
 struct DSchemaDev {
     DStruct structs[DX_MAX_STRUCTS];

@@ -74,21 +74,31 @@ static __device__ __forceinline__ bool fast_record_warp(const uint8_t* buf, uint
         __syncwarp();
         const DSeg sg = a.segs[si];                      // warp-uniform: constant-bank loads
         {
-            // literal: whole words through a carried funnel shift (data word i+1 is loaded once and reused as the low half of
-            // the next compare).  Every lane runs the compare, lanes that already failed on the tile's first bytes: the loop
-            // is then warp-uniform and the literal words are uniform constant-bank operands instead of per-lane indexed loads.
-            const uint32_t p0 = ok ? pos : 0u;
-            int li = (int)(sg.lit_off >> 2); uint32_t wo = p0 & ~3u, nw = sg.lit_len >> 2;
-            const uint32_t L = sg.lit_len, sh = (p0 & 3u) << 3;
-            uint32_t lo = *reinterpret_cast<const uint32_t*>(buf + wo), diff = 0, hi;
-#define DX_LIT_WORD(i) hi = *reinterpret_cast<const uint32_t*>(buf + wo + 4 * ((i) + 1)); diff |= __funnelshift_r(lo, hi, sh) ^ a.lits[li + (i)]; lo = hi;
-            while (nw >= 4) { DX_LIT_WORD(0) DX_LIT_WORD(1) DX_LIT_WORD(2) DX_LIT_WORD(3) wo += 16; li += 4; nw -= 4; }
-            if (nw >= 2) { DX_LIT_WORD(0) DX_LIT_WORD(1) wo += 8; li += 2; nw -= 2; }
-            if (nw) { DX_LIT_WORD(0) wo += 4; li += 1; }
+            // literal: a straight line of word compares entered at the literal's length (fall-through switch), each word two
+            // shared loads, a funnel shift and an XOR against a constant-bank operand; the last word goes under its mask.
+            // Every lane runs the compare, lanes that already failed on the tile's first bytes: the dispatch is then
+            // warp-uniform and the literal words are uniform operands instead of per-lane indexed loads.
+            const uint32_t p0 = ok ? pos : 0u, sh = (p0 & 3u) << 3;
+            const uint32_t* wp = reinterpret_cast<const uint32_t*>(buf + (p0 & ~3u));
+            const uint32_t* lp = a.lits + sg.lit_word;
+            uint32_t nf = sg.n_words - 1u, diff = 0;
+#define DX_LIT_WORD(i) diff |= __funnelshift_r(wp[i], wp[(i) + 1], sh) ^ lp[i];
+            while (nf > 8u) { DX_LIT_WORD(0) DX_LIT_WORD(1) DX_LIT_WORD(2) DX_LIT_WORD(3) DX_LIT_WORD(4) DX_LIT_WORD(5) DX_LIT_WORD(6) DX_LIT_WORD(7) wp += 8; lp += 8; nf -= 8u; }
+            diff |= (__funnelshift_r(wp[nf], wp[nf + 1u], sh) ^ lp[nf]) & sg.last_mask;
+            switch (nf) {
+            case 8: DX_LIT_WORD(7)
+            case 7: DX_LIT_WORD(6)
+            case 6: DX_LIT_WORD(5)
+            case 5: DX_LIT_WORD(4)
+            case 4: DX_LIT_WORD(3)
+            case 3: DX_LIT_WORD(2)
+            case 2: DX_LIT_WORD(1)
+            case 1: DX_LIT_WORD(0)
+            default: break;
+            }
 #undef DX_LIT_WORD
-            if (sg.tail_mask) { hi = *reinterpret_cast<const uint32_t*>(buf + wo + 4); diff |= (__funnelshift_r(lo, hi, sh) ^ a.lits[li]) & sg.tail_mask; }
             ok = ok && diff == 0;
-            pos += L;
+            pos += sg.lit_len;
         }
         if (sg.type == 0) break;
         if (ok) {

@@ -108,7 +108,7 @@ __global__ void __launch_bounds__(K1_NT, FRAMED ? K1_MIN_CTAS_FRAMED : K1_MIN_CT
     __shared__ uint64_t s_bar[K1_STAGES];
     __shared__ long long s_tile;
     __shared__ long long s_rowbase;
-    __shared__ uint32_t s_wtot[K1_NT / 32];
+    __shared__ uint32_t s_wtot[K1_NT / 32], s_wtail[K1_NT / 32], s_next;
     __shared__ long long s_r0;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -267,11 +267,12 @@ __global__ void __launch_bounds__(K1_NT, FRAMED ? K1_MIN_CTAS_FRAMED : K1_MIN_CT
                     }
                 }
             }
-            if (lane == 0) s_wtot[warp] = total_w;
+            if (lane == 0) { s_wtot[warp] = total_w; s_wtail[warp] = w_tail; }
+            if (tid == 0) s_next = 0;
             __syncthreads();
-            uint32_t wbase = 0, total = 0;
+            uint32_t wbase = 0, total = 0, wmax = 0;
 #pragma unroll
-            for (int w = 0; w < NWARP; w++) { const uint32_t t = s_wtot[w]; if (w < warp) wbase += t; total += t; }
+            for (int w = 0; w < NWARP; w++) { const uint32_t t = s_wtot[w]; if (w < warp) wbase += t; total += t; wmax = t > wmax ? t : wmax; }
             n_rec = total;
             if (warp == 0) {
 #ifdef K1_NO_LOOKBACK    /* tuning experiment only: what the row-index look-back costs (row numbers are wrong in this build) */
@@ -282,23 +283,42 @@ __global__ void __launch_bounds__(K1_NT, FRAMED ? K1_MIN_CTAS_FRAMED : K1_MIN_CT
                 if (lane == 0) s_rowbase = rb;
             }
             __syncthreads();
-            const long long row_base = s_rowbase + wbase;
-            for (uint32_t round0 = 0; round0 < total_w; round0 += K1_WCAP) {
-                if (round0 > 0) { __syncwarp(); list_pass(round0); }          // a slice of very short records: the next K1_WCAP starts
-                __syncwarp();
-                const int cnt = (int)((total_w - round0 > K1_WCAP) ? K1_WCAP : (total_w - round0));
-                for (int base = 0; base < cnt; base += 32) {
-                    const int idx = base + lane;
-                    const bool has = idx < cnt;
+            // Parse.  Normally no slice holds more than K1_WCAP records: the tile's records then form one flat list (warp w's
+            // starts follow warp w-1's) and the warps draw rounds of 32 consecutive records from a shared counter, so every
+            // round but the tile's last runs with 32 busy lanes wherever the slice boundaries fall.  A tile of very short
+            // records keeps the records with the warp that listed them, K1_WCAP at a time.
+            const bool flat = wmax <= K1_WCAP;
+            const long long row_base = s_rowbase;
+            uint32_t round0 = 0; int base = 0;
+            for (;;) {
+                uint32_t idx, rank, tot_w, tail; const uint16_t* ws; bool has;
+                if (flat) {
+                    uint32_t b = 0;
+                    if (lane == 0) b = atomicAdd(&s_next, 32u);
+                    b = __shfl_sync(0xffffffffu, b, 0);
+                    if (b >= total) break;
+                    rank = b + lane; has = rank < total;
+                    uint32_t w = 0, pre = 0;
+#pragma unroll
+                    for (int k = 0; k < NWARP - 1; k++) { const uint32_t t = s_wtot[k]; if (w == (uint32_t)k && rank >= pre + t) { pre += t; w = k + 1; } }
+                    ws = s_starts + w * (LCAP + K1_WCAP + 2) + LCAP; idx = rank - pre; tot_w = s_wtot[w]; tail = s_wtail[w];
+                } else {
+                    if (round0 >= total_w) break;
+                    if (base == 0 && round0 > 0) { __syncwarp(); list_pass(round0); }          // the next K1_WCAP starts of this slice
+                    __syncwarp();
+                    const int cnt = (int)((total_w - round0 > K1_WCAP) ? K1_WCAP : (total_w - round0));
+                    idx = base + lane; has = (int)idx < cnt; rank = wbase + round0 + idx; ws = w_starts; tot_w = total_w - round0; tail = w_tail;
+                    base += 32; if (base >= cnt) { base = 0; round0 += K1_WCAP; }
+                }
+                {
                     uint32_t st = 0, en = 0; bool in_smem = true; long long en_abs = 0;
-                    const uint32_t rank = round0 + idx;
                     if (has) {
-                        st = w_starts[idx];
-                        if (rank + 1 < total_w) en = (uint32_t)w_starts[idx + 1] - 1u;
+                        st = ws[idx];
+                        if (idx + 1 < tot_w) en = (uint32_t)ws[idx + 1] - 1u;
                         else {
-                            // last record owned by this warp: its newline lies at or past the slice end
+                            // last record owned by its warp: its newline lies at or past the slice end
                             const uint32_t lim = (uint32_t)avail + ((lo + avail == a.n_end) ? 1u : 0u);
-                            if (w_tail != 0xFFFFFFFFu) en = w_tail;
+                            if (tail != 0xFFFFFFFFu) en = tail;
                             else if (lo + avail == a.n_end) {
                                 // the data ends inside the loaded bytes: the record runs to the final newline or the end of data
                                 const uint32_t av = (uint32_t)avail;

@@ -8,7 +8,7 @@ import bench, dxgpu as dx, dxo
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 25_000_000
 ctx = dx.Context(0)
 dec = dx.Decoder(ctx, dxo.iot_schema_json(2))
-gp = bench.gen_params(dx.GenParams, 0)
+gp = bench.gen_params(dx.GenParams, 0, 0)
 ptr, nb, off = ctx.gen_events(gp, 0, n, want_offsets=True)
 ctx.set_timing(True)
 for mode, o in (("ndjson", None), ("offsets", off)):
