@@ -4,6 +4,7 @@
 #include <memory>
 #include "dx_decode_host.h"
 #include "dx_flow.h"
+#include "dx_tojson.h"
 #include "dx_rules.h"
 #include "dx_shuffle.h"
 
@@ -283,6 +284,55 @@ int dx_table_rule_json(const dx_table* h, int col, int rule, const char** json, 
     buf += "}";
     *json = buf.c_str(); *len = (int64_t)buf.size();
     return DX_OK;
+}
+
+// ---- sink hand-off: rows -> JSON on the device (dx_tojson.cu) --------------------------------
+int dx_table_to_json(const dx_table* h, dx_json** out) {
+    const DxTable* t = T(h);
+    if (!t || !out) return DX_ERR_ARG;
+    cudaSetDevice(t->ctx->device);
+    try { return dx_json_build(t, out); } catch (std::exception& e) { return t->ctx->set_error(DX_ERR_UNSUPPORTED, e.what()); }
+}
+int64_t dx_json_num_rows(const dx_json* j) { return j ? j->n_rows : 0; }
+int64_t dx_json_num_bytes(const dx_json* j) { return j ? j->n_bytes : 0; }
+int dx_json_device(const dx_json* j, const uint8_t** bytes, const int64_t** offsets) {
+    if (!j) return DX_ERR_ARG;
+    if (bytes) *bytes = j->bytes ? j->bytes->as<uint8_t>() : nullptr;
+    if (offsets) *offsets = j->offsets->as<int64_t>();
+    return DX_OK;
+}
+int dx_json_to_host(const dx_json* j, uint8_t* bytes, int64_t* offsets) {
+    if (!j) return DX_ERR_ARG;
+    dx_ctx* c = j->ctx;
+    cudaSetDevice(c->device);
+    if (bytes && j->n_bytes) DX_CUDA(c, cudaMemcpyAsync(bytes, j->bytes->p, (size_t)j->n_bytes, cudaMemcpyDeviceToHost, c->stream));
+    if (offsets) DX_CUDA(c, cudaMemcpyAsync(offsets, j->offsets->p, (size_t)(j->n_rows + 1) * 8, cudaMemcpyDeviceToHost, c->stream));
+    DX_CUDA(c, cudaStreamSynchronize(c->stream));
+    return DX_OK;
+}
+void dx_json_release(dx_json* j) { delete j; }
+int dx_table_filter_flags(const dx_table* h, const char* expr, uint8_t* flags) {
+    const DxTable* t = T(h);
+    if (!t || !expr || (!flags && t->n_rows)) return DX_ERR_ARG;
+    dx_ctx* c = t->ctx;
+    cudaSetDevice(c->device);
+    try {
+        dxsql::Parser ps(expr);
+        dxsql::ExprP e = ps.condition();
+        BindScope sc; sc.table = t;
+        ExprPrograms P; DevPrograms D;
+        int rc = dx_compile_expr(c, sc, e, &P); if (rc) return rc;
+        if (P.result_type[0] != DX_T_BOOL) return c->set_error(DX_ERR_UNSUPPORTED, std::string("sink filter '") + expr + "' is not a boolean expression");
+        rc = dx_upload_programs(c, &P, &D); if (rc) return rc;
+        if (t->n_rows == 0) return DX_OK;
+        DevBuf fl(c, (size_t)t->n_rows * 4);
+        rc = dx_eval_flags(c, D, t->n_rows, nullptr, fl.as<uint32_t>(), 1); if (rc) return rc;
+        std::vector<uint32_t> hf((size_t)t->n_rows);
+        DX_CUDA(c, cudaMemcpyAsync(hf.data(), fl.p, hf.size() * 4, cudaMemcpyDeviceToHost, c->stream));
+        DX_CUDA(c, cudaStreamSynchronize(c->stream));
+        for (int64_t i = 0; i < t->n_rows; i++) flags[i] = (uint8_t)(hf[(size_t)i] & 1u);
+        return DX_OK;
+    } catch (std::exception& ex) { return c->set_error(DX_ERR_PARSE, std::string("sink filter: ") + ex.what()); }
 }
 
 // ---- flow ------------------------------------------------------------------------------------

@@ -352,7 +352,7 @@ struct Exec {
     static bool match_rules(const ExprP& e, std::vector<ExprP>* conds, std::shared_ptr<RuleTable>* rt) {
         auto table = std::make_shared<RuleTable>();
         ExprP c; std::vector<std::pair<std::string, std::string>> m;
-        if (match_rule_if(e, &c, &m)) { conds->push_back(c); table->rules.push_back(m); *rt = table; return true; }
+        if (match_rule_if(e, &c, &m)) { conds->push_back(c); table->rules.push_back(m); table->single = true; *rt = table; return true; }
         if (e->kind != EK::Func || upper(e->sval) != "FILTERNULL" || e->args.size() != 1) return false;
         const ExprP& arr = e->args[0];
         if (arr->kind != EK::Func || arr->sval != "ARRAY") return false;

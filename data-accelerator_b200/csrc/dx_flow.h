@@ -27,7 +27,10 @@ struct ParsedTransform {
 // TransformSQLParser.parse restated (reference: datax/sql/TransformSqlParser.scala:27-95)
 int dx_parse_transform(const std::string& text, ParsedTransform* out, std::string* err);
 
-struct RuleTable { std::vector<std::vector<std::pair<std::string, std::string>>> rules; };   // MAP('k','v',...) per rule
+struct RuleTable {
+    std::vector<std::vector<std::pair<std::string, std::string>>> rules;   // MAP('k','v',...) per rule
+    bool single = false;   // a lone IF(cond, MAP(...), NULL): the column is a nullable map, not filterNull(Array(...))'s array
+};
 
 struct CiLess {   // Spark resolves table (and column) names case-insensitively (spark.sql.caseSensitive=false)
     bool operator()(const std::string& a, const std::string& b) const {

@@ -161,6 +161,41 @@ class Table:
             out.append(C.string_at(p.value, ln.value) if ln.value else b"")
         return out
 
+    def to_json(self, device=False):
+        """The sink hand-off (OutputManager.sink, sink/OutputManager.scala:103-118): to_json(struct(output columns)) per row,
+        serialised on the device.  -> list of bytes, one JSON object per row; device=True -> (bytes_ptr, offsets_ptr, n_rows,
+        n_bytes, release) without the copy to the host."""
+        L = self.L
+        L.dx_table_to_json.restype, L.dx_table_to_json.argtypes = C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]
+        L.dx_json_num_rows.restype, L.dx_json_num_rows.argtypes = C.c_int64, [C.c_void_p]
+        L.dx_json_num_bytes.restype, L.dx_json_num_bytes.argtypes = C.c_int64, [C.c_void_p]
+        L.dx_json_device.restype, L.dx_json_device.argtypes = C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]
+        L.dx_json_to_host.restype, L.dx_json_to_host.argtypes = C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]
+        L.dx_json_release.restype, L.dx_json_release.argtypes = None, [C.c_void_p]
+        j = C.c_void_p()
+        self.ctx.check(L.dx_table_to_json(self.h, C.byref(j)))
+        n, nb = L.dx_json_num_rows(j), L.dx_json_num_bytes(j)
+        if device:
+            b, o = C.c_void_p(), C.c_void_p()
+            self.ctx.check(L.dx_json_device(j, C.byref(b), C.byref(o)))
+            return b.value, o.value, n, nb, (lambda: L.dx_json_release(j))
+        data = np.empty(max(nb, 1), dtype=np.uint8)
+        off = np.zeros(n + 1, dtype=np.int64)
+        try:
+            self.ctx.check(L.dx_json_to_host(j, data.ctypes.data_as(C.c_void_p), off.ctypes.data_as(C.c_void_p)))
+        finally:
+            L.dx_json_release(j)
+        raw = data.tobytes()
+        return [raw[off[r]:off[r + 1] - 1] for r in range(n)]
+
+    def filter_flags(self, expr):
+        """One sink's filter column (OutputManager.scala:53-61): bool per row, TRUE only where the expression is TRUE."""
+        L = self.L
+        L.dx_table_filter_flags.restype, L.dx_table_filter_flags.argtypes = C.c_int, [C.c_void_p, C.c_char_p, C.c_void_p]
+        out = np.zeros(max(self.num_rows, 1), dtype=np.uint8)
+        self.ctx.check(L.dx_table_filter_flags(self.h, expr.encode("utf-8"), out.ctypes.data_as(C.c_void_p)))
+        return out[: self.num_rows].astype(bool)
+
     def device_view(self, col):
         i = self._idx(col)
         d, m, w, b = C.c_void_p(), C.c_void_p(), C.c_int(), C.c_int()

@@ -156,6 +156,28 @@ int dx_table_rule_json(const dx_table* t, int col, int rule, const char** json, 
  * SELECT explode(Rules) ... GROUP BY ruleId): counts[r], r < dx_table_rule_count, computed on the device.       */
 int dx_table_rule_hits(const dx_table* t, int col, int64_t* counts, int n_counts);
 
+/* ---- sink hand-off: rows as JSON ---------------------------------------------------------- */
+/* What OutputManager.sink builds before it calls the JSON sinks (datax-host sink/OutputManager.scala:103-118):
+ * to_json(struct(<every column whose name does not start with "__DataX_">)) for each row of an output table, produced on the
+ * device as NDJSON: row r is bytes[offsets[r] .. offsets[r+1] - 1) and is followed by one '\n' (so the byte string is also what
+ * BlobSinker writes, sink/BlobSinker.scala:54-92, before gzip).  Serialisation rules (Spark 2.4.5 JacksonGenerator restated):
+ * NULL struct fields are skipped, map values are written as null; doubles as java.lang.Double.toString prints them (shortest
+ * round-trip digits; NaN and the infinities quoted); strings with Jackson's default escapes; timestamps as
+ * yyyy-MM-dd'T'HH:mm:ss.SSSXXX in UTC; the values of one MAP(...) in Spark's common type; a rule-flag column as the array of the
+ * fired rules' objects (filterNull(Array(IF(cond, MAP(...), NULL), ...)), CodegenRules Engine.cs:232-266).  The handle owns the
+ * device buffers until dx_json_release.                                                                                     */
+typedef struct dx_json dx_json;
+int dx_table_to_json(const dx_table* t, dx_json** out);
+int64_t dx_json_num_rows(const dx_json* j);
+int64_t dx_json_num_bytes(const dx_json* j);
+int dx_json_device(const dx_json* j, const uint8_t** bytes, const int64_t** offsets);     /* device pointers; offsets has n_rows + 1 entries */
+int dx_json_to_host(const dx_json* j, uint8_t* bytes, int64_t* offsets);                  /* either destination may be NULL */
+void dx_json_release(dx_json* j);
+/* One sink's filter column (OutputManager.scala:53-61, 110-113: `<filter expr> AS _<prefix>_<sink>`, e.g. conf.filter of the
+ * EventHub / HTTP / SQL sinks, blobConf.groupEvaluation): flags[r] = 1 where the SQL boolean expression is TRUE for row r, 0 where
+ * it is FALSE or NULL (SinkerUtil.outputFilteredEvents keeps a row when the flag is not NULL and true, SinkerUtil.scala:31).   */
+int dx_table_filter_flags(const dx_table* t, const char* expr, uint8_t* flags);
+
 /* ---- the flow processor (drop-in boundary) ------------------------------------------------ */
 typedef struct dx_flow dx_flow;       /* one per flow: decoder, parsed SQL, window cache, state tables */
 typedef struct dx_result dx_result;   /* what one micro-batch produced                                */

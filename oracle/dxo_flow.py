@@ -501,6 +501,9 @@ class Tab:
         t.approx = set(getattr(self, "approx", ()))
         if getattr(self, "owners", None):
             t.owners = list(self.owners)
+        for a in ("rule_table", "rule_single"):
+            if hasattr(self, a):
+                setattr(t, a, getattr(self, a))
         return t
 
 
@@ -1114,6 +1117,7 @@ def exec_core(core, views, now_us):
                     flags[:, r] = ok & v.astype(bool)
                 out.add(_item_name(e, alias), "rules", flags, np.ones(src.n, bool))
                 out.rule_table = [d for _, d in rs]
+                out.rule_single = not (e[0] == "func" and e[1] == "FILTERNULL")     # a lone IF(cond, MAP(...), NULL): a nullable map
                 continue
             if e[0] == "col" and src.find(e[1], q) is None and (
                     e[1][0] in ("Properties", "SystemProperties", "__DataX_FileInfo", "DataXProperties") or
