@@ -531,6 +531,14 @@ def run_ours(args):
             smp = ClockSampler(local).start()
             stages[name] = bw.run(dx, ctx, peak=peak, **kw)
             stages[name]["clocks"] = smp.stop()
+        # the sink hand-off: to_json of an output table's rows on the device
+        import bench_tojson as bj
+        for shape in ("flat", "alerts"):
+            smp = ClockSampler(local).start()
+            r = bj.run(dx, ctx, 5_000_000, shape)
+            r["frac_of_hbm_peak"] = round(r["alg_gbs"] / peak, 4)
+            r["clocks"] = smp.stop()
+            stages["to_json_" + shape] = r
 
     out = {"metric": METRIC, "value": round(value, 1), "unit": "events/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
            "ms_per_step": round(ms / args.steps, 3), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8/int64/f64",

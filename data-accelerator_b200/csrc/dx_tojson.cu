@@ -331,14 +331,14 @@ __global__ void __launch_bounds__(K6_NT) k6_json_len(const JOp* __restrict__ ops
 static __device__ __forceinline__ uint32_t k6_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
 __global__ void __launch_bounds__(K6_NT) k6_json_write(const JOp* __restrict__ ops, int n_ops, const uint8_t* __restrict__ lits, long long n_rows,
-                                                       const long long* __restrict__ off, uint8_t* __restrict__ out) {
+                                                       const long long* __restrict__ off, uint8_t* __restrict__ out, uint32_t stage_cap) {
     extern __shared__ __align__(128) uint8_t stage[];
     const long long r0 = (long long)blockIdx.x * K6_NT;
     const long long r1 = r0 + K6_NT < n_rows ? r0 + K6_NT : n_rows;
     const long long row = r0 + threadIdx.x;
     const long long base = off[r0], span = off[r1] - base;
     const uint32_t skew = (uint32_t)(base & 15);
-    const bool staged = span + skew <= K6_STAGE;          // CTA-uniform
+    const bool staged = span + skew <= (long long)stage_cap;          // CTA-uniform
     if (row < n_rows) {
         WriteSink s;
         s.out = staged ? stage + skew + (uint32_t)(off[row] - base) : out + off[row];
@@ -557,9 +557,15 @@ int dx_json_build(const DxTable* t, dx_json** out) {
         DX_CUDA(c, cudaFuncSetAttribute(k6_json_write, cudaFuncAttributeMaxDynamicSharedMemorySize, K6_STAGE + 128));
         c->k6_smem_configured = (size_t)K6_STAGE + 128;
     }
+    // the stage holds the output span of one CTA's 128 rows: sized from the mean row (known from the scan) with a third to spare,
+    // so short rows leave room for more resident CTAs; a CTA whose span is larger than that writes straight to global memory
+    size_t stage = (size_t)((double)total / (double)n * K6_NT * 1.35) + 512;
+    stage = (stage + 1023) & ~size_t(1023);
+    if (stage < 8192) stage = 8192;
+    if (stage > K6_STAGE) stage = K6_STAGE;
     {
         StageTimer tm(c, "k6_json_write");
-        k6_json_write<<<grid_w, K6_NT, K6_STAGE + 128, c->stream>>>(d_ops->as<JOp>(), (int)P.ops.size(), d_lits->as<uint8_t>(), n, js->offsets->as<long long>(), js->bytes->as<uint8_t>());
+        k6_json_write<<<grid_w, K6_NT, stage + 128, c->stream>>>(d_ops->as<JOp>(), (int)P.ops.size(), d_lits->as<uint8_t>(), n, js->offsets->as<long long>(), js->bytes->as<uint8_t>(), (uint32_t)stage);
         c->launches["k6_json_write"]++;
     }
     DX_CUDA(c, cudaGetLastError());
