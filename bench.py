@@ -119,6 +119,30 @@ def artefacts(dx):
     return dec, agg
 
 
+def bind_to_gpu_node(ctx):
+    """Keeps this rank's host threads on the CPUs of the NUMA node its GPU hangs off (the library already takes the pinned pages
+    from that node): with one rank per GPU, host->device copies that cross the inter-socket link share it with every other rank.
+    -> {"node": n, "cpus": k} or {"node": -1} when the platform reports no node."""
+    fn = ctx.L.dx_ctx_numa_node
+    fn.restype, fn.argtypes = C.c_int, [C.c_void_p]
+    node = int(fn(ctx.h))
+    info = {"node": node}
+    try:
+        if node >= 0:
+            cpus = set()
+            for part in open("/sys/devices/system/node/node%d/cpulist" % node).read().strip().split(","):
+                a, _, b = part.partition("-")
+                cpus.update(range(int(a), int(b or a) + 1))
+            allowed = cpus & os.sched_getaffinity(0)
+            if allowed:
+                info["all_cpus"] = sorted(os.sched_getaffinity(0))
+                os.sched_setaffinity(0, allowed)
+                info["cpus"] = len(allowed)
+    except (OSError, ValueError):
+        pass
+    return info
+
+
 def gen_params(cls, rank, batch):
     return cls(SEED + rank, N_KEYS, N_HOMES, T0 + batch * INTERVAL_MS, INTERVAL_MS, 60_000, 2, 10, 1, 0)
 
@@ -151,6 +175,7 @@ def run_ours(args):
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", local))
     ctx = dx.Context(local)
+    numa = bind_to_gpu_node(ctx)
     L = ctx.L
     dec_art, agg_art = artefacts(dx)
     mk = dx.CommonProcessorFactory.createProcessor
@@ -513,7 +538,8 @@ def run_ours(args):
     ms_e2e = max_over_ranks(ms_e2e)
     e2e = {"value": round(world * n_events * e2e_steps / (ms_e2e / 1e3), 1), "unit": "events/s",
            "h2d_bytes_per_step": int(total_bytes), "d2h_bytes_per_step": int(d2h[0] // e2e_steps), "ms_per_step": round(ms_e2e / e2e_steps, 3),
-           "what": "pinned host NDJSON -> dx_flow_stage_batch (H2D of batches i+1 and i+2 queued while batch i is processed) -> dx_flow_process_staged, per-rule counts, exchange, windows, D2H of flag words + both window tables"}
+           "what": "pinned host NDJSON -> dx_flow_stage_batch (H2D of batches i+1 and i+2 queued while batch i is processed) -> dx_flow_process_staged, per-rule counts, exchange, windows, D2H of flag words + both window tables",
+           "numa": {k: v for k, v in numa.items() if k != "all_cpus"}}
     for hp in host_in + host_out:
         L.dx_host_free(ctx.h, hp)
     for c in range(N_CHUNKS):
@@ -556,6 +582,8 @@ def run_ours(args):
     if shuffle:
         out["shuffle"] = shuffle
     if rank == 0 and not args.no_cpu_baseline:
+        if numa.get("all_cpus"):
+            os.sched_setaffinity(0, numa["all_cpus"])      # the CPU leg uses every host core
         out["cpu_baseline"] = cpu_baseline(sample_events=args.cpu_sample)
     if rank == 0:
         print(json.dumps(out))

@@ -5,6 +5,8 @@
 #include "dx_decode_host.h"
 #include "dx_flow.h"
 #include "dx_tojson.h"
+#include <sys/syscall.h>
+#include <unistd.h>
 #include "dx_rules.h"
 #include "dx_shuffle.h"
 
@@ -71,10 +73,34 @@ int dx_dev_alloc(dx_ctx* c, int64_t bytes, void** out) {
     *out = p; return DX_OK;
 }
 void dx_dev_free(dx_ctx* c, void* p) { if (c && p) c->pool.release(p); }
+// NUMA node the GPU hangs off (sysfs; -1 when the platform does not say, e.g. a single-node VM)
+int dx_ctx_numa_node(dx_ctx* c) {
+    char bus[32] = {0};
+    if (!c || cudaDeviceGetPCIBusId(bus, sizeof bus, c->device) != cudaSuccess) return -1;
+    for (char* p = bus; *p; p++) *p = (char)tolower((unsigned char)*p);
+    const std::string path = std::string("/sys/bus/pci/devices/") + bus + "/numa_node";
+    FILE* f = fopen(path.c_str(), "r");
+    if (!f) return -1;
+    int node = -1;
+    if (fscanf(f, "%d", &node) != 1) node = -1;
+    fclose(f);
+    return node;
+}
 int dx_host_alloc(dx_ctx* c, int64_t bytes, void** out) {
     if (bytes < 0 || !out) return c->set_error(DX_ERR_ARG, "dx_host_alloc: bad arguments");
     cudaSetDevice(c->device);
-    DX_CUDA(c, cudaHostAlloc(out, (size_t)bytes + 64, cudaHostAllocDefault));
+    // The pages are taken from the memory of the GPU's own NUMA node (preferred, not bound: a full node still allocates): a
+    // copy from the other socket's memory crosses the inter-socket link and, with one rank per GPU, eight of them share it.
+    const int node = dx_ctx_numa_node(c);
+    bool policy_set = false;
+    if (node >= 0 && node < 1024) {
+        unsigned long mask[16] = {0};
+        mask[node / 64] |= 1ul << (node % 64);
+        policy_set = syscall(SYS_set_mempolicy, 1 /* MPOL_PREFERRED */, mask, 1025ul) == 0;
+    }
+    const cudaError_t e = cudaHostAlloc(out, (size_t)bytes + 64, cudaHostAllocDefault);
+    if (policy_set) syscall(SYS_set_mempolicy, 0 /* MPOL_DEFAULT */, nullptr, 0ul);
+    DX_CUDA(c, e);
     return DX_OK;
 }
 void dx_host_free(dx_ctx* c, void* p) { if (c && p) { cudaSetDevice(c->device); cudaFreeHost(p); } }

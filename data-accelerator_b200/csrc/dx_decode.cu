@@ -35,13 +35,13 @@ __global__ void k1_count_records(const uint8_t* bytes, long long n, unsigned lon
 // =======================================================================================
 // host side
 // =======================================================================================
-static const int k1_tiles[] = {16384, 20480, 24576, 28672, 32768, 36864, 40960, 45056, 49152};
+static const int k1_tiles[] = {K1_TS(16384), K1_TS(20480), K1_TS(24576), K1_TS(28672), K1_TS(32768), K1_TS(36864), K1_TS(40960), K1_TS(45056), K1_TS(49152)};
 // tile bytes for a batch: the largest instantiated size that still keeps the expected records per tile just under the CTA's thread count
 static int k1_pick_tile(long long n_bytes, long long n_events) {
     if (n_events <= 0 || n_bytes <= 0) return K1_T_DEFAULT;
     const double avg = (double)n_bytes / (double)n_events;
     int best = k1_tiles[0];
-    for (int t : k1_tiles) if ((double)t / avg <= (double)(K1_NT - 10)) best = t;
+    for (int t : k1_tiles) if ((double)t / avg <= (double)(K1_NT - (K1_NT >= 128 ? 10 : 3))) best = t;
     return best;
 }
 template <int T> static int k1_setup_one(dx_ctx* c, int* occ_out) {      // occ_out[0]: NDJSON kernel, occ_out[9]: framed kernel
@@ -61,15 +61,15 @@ static int k1_launch(dx_ctx* c, int tile, const int* occ_by_tile, const DecodeAr
     const size_t smem = k1_smem_bytes(tile);
     if (framed) { k1_framed_launch(tile, (unsigned)grid, c->stream, a); c->launches["k1_decode"]++; return DX_OK; }
     switch (tile) {
-    case 16384: k1_decode<16384, false><<<(unsigned)grid, K1_NT, smem, c->stream>>>(a); break;
-    case 20480: k1_decode<20480, false><<<(unsigned)grid, K1_NT, smem, c->stream>>>(a); break;
-    case 24576: k1_decode<24576, false><<<(unsigned)grid, K1_NT, smem, c->stream>>>(a); break;
-    case 28672: k1_decode<28672, false><<<(unsigned)grid, K1_NT, smem, c->stream>>>(a); break;
-    case 36864: k1_decode<36864, false><<<(unsigned)grid, K1_NT, smem, c->stream>>>(a); break;
-    case 40960: k1_decode<40960, false><<<(unsigned)grid, K1_NT, smem, c->stream>>>(a); break;
-    case 45056: k1_decode<45056, false><<<(unsigned)grid, K1_NT, smem, c->stream>>>(a); break;
-    case 49152: k1_decode<49152, false><<<(unsigned)grid, K1_NT, smem, c->stream>>>(a); break;
-    default: k1_decode<32768, false><<<(unsigned)grid, K1_NT, smem, c->stream>>>(a); break;
+    case K1_TS(16384): k1_decode<K1_TS(16384), false><<<(unsigned)grid, K1_NT, smem, c->stream>>>(a); break;
+    case K1_TS(20480): k1_decode<K1_TS(20480), false><<<(unsigned)grid, K1_NT, smem, c->stream>>>(a); break;
+    case K1_TS(24576): k1_decode<K1_TS(24576), false><<<(unsigned)grid, K1_NT, smem, c->stream>>>(a); break;
+    case K1_TS(28672): k1_decode<K1_TS(28672), false><<<(unsigned)grid, K1_NT, smem, c->stream>>>(a); break;
+    case K1_TS(36864): k1_decode<K1_TS(36864), false><<<(unsigned)grid, K1_NT, smem, c->stream>>>(a); break;
+    case K1_TS(40960): k1_decode<K1_TS(40960), false><<<(unsigned)grid, K1_NT, smem, c->stream>>>(a); break;
+    case K1_TS(45056): k1_decode<K1_TS(45056), false><<<(unsigned)grid, K1_NT, smem, c->stream>>>(a); break;
+    case K1_TS(49152): k1_decode<K1_TS(49152), false><<<(unsigned)grid, K1_NT, smem, c->stream>>>(a); break;
+    default: k1_decode<K1_TS(32768), false><<<(unsigned)grid, K1_NT, smem, c->stream>>>(a); break;
     }
     c->launches["k1_decode"]++;
     return DX_OK;
@@ -176,9 +176,9 @@ int dx_decoder::init(dx_ctx* c, const std::string& schema_json) {
     DX_CUDA(c, cudaMemcpyAsync(dev_dicts.p, dd.data(), sizeof(DictDev) * hs.n_leaves, cudaMemcpyHostToDevice, c->stream));
     dev_stats = DevBuf(c, sizeof(DecodeStats) + 16);
     { int rc2;
-      if ((rc2 = k1_setup_one<16384>(c, &occ_by_tile[0])) || (rc2 = k1_setup_one<20480>(c, &occ_by_tile[1])) || (rc2 = k1_setup_one<24576>(c, &occ_by_tile[2])) ||
-          (rc2 = k1_setup_one<28672>(c, &occ_by_tile[3])) || (rc2 = k1_setup_one<32768>(c, &occ_by_tile[4])) || (rc2 = k1_setup_one<36864>(c, &occ_by_tile[5])) ||
-          (rc2 = k1_setup_one<40960>(c, &occ_by_tile[6])) || (rc2 = k1_setup_one<45056>(c, &occ_by_tile[7])) || (rc2 = k1_setup_one<49152>(c, &occ_by_tile[8]))) return rc2; }
+      if ((rc2 = k1_setup_one<K1_TS(16384)>(c, &occ_by_tile[0])) || (rc2 = k1_setup_one<K1_TS(20480)>(c, &occ_by_tile[1])) || (rc2 = k1_setup_one<K1_TS(24576)>(c, &occ_by_tile[2])) ||
+          (rc2 = k1_setup_one<K1_TS(28672)>(c, &occ_by_tile[3])) || (rc2 = k1_setup_one<K1_TS(32768)>(c, &occ_by_tile[4])) || (rc2 = k1_setup_one<K1_TS(36864)>(c, &occ_by_tile[5])) ||
+          (rc2 = k1_setup_one<K1_TS(40960)>(c, &occ_by_tile[6])) || (rc2 = k1_setup_one<K1_TS(45056)>(c, &occ_by_tile[7])) || (rc2 = k1_setup_one<K1_TS(49152)>(c, &occ_by_tile[8]))) return rc2; }
     ctas_per_sm = occ_by_tile[4];
     DX_CUDA(c, cudaStreamSynchronize(c->stream));
     return DX_OK;

@@ -4,14 +4,17 @@
 #pragma once
 #include "dx_decode.cuh"
 
-#ifndef K1_T_DEFAULT
-#define K1_T_DEFAULT 32768  // tile bytes when the record length is unknown (a multiple of 4096; see k1_pick_tile)
-#endif
-#define K1_OVL 2048         // overlap bytes past the tile (records starting in the tile may end here)
-#define K1_PAD 32
 #ifndef K1_NT
 #define K1_NT 256           // threads per CTA
 #endif
+#define K1_TS(x) ((x) * K1_NT / 256)     // tile sizes are stated for 256 threads and scale with the CTA
+#ifndef K1_T_DEFAULT
+#define K1_T_DEFAULT K1_TS(32768)  // tile bytes when the record length is unknown (see k1_pick_tile)
+#endif
+#ifndef K1_OVL
+#define K1_OVL 2048         // overlap bytes past the tile (records starting in the tile may end here)
+#endif
+#define K1_PAD 32
 #define K1_SC 1024          // (caller-framed kernels only) kept for the shared-memory layout
 #define K1_WCAP 126         // record starts a warp holds per round (a slice normally has ~30 records)
 #ifndef K1_STAGES
@@ -141,7 +144,7 @@ __global__ void __launch_bounds__(K1_NT, FRAMED ? K1_MIN_CTAS_FRAMED : K1_MIN_CT
             }
         }
         if (tid < (int)((uint32_t)av - bulk_)) dst[bulk_ + tid] = a.base_al[lo_ + bulk_ + tid];
-        if (tid == 32 && lo_ + av == a.n_end) dst[av] = '\n';
+        if (tid == (K1_NT > 32 ? 32 : 0) && lo_ + av == a.n_end) dst[av] = '\n';
     };
 
     if (tid == 0) s_tile = (long long)atomicAdd(a.tile_counter, 1u);

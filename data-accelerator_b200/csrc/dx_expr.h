@@ -81,5 +81,14 @@ int dx_eval_column(dx_ctx* ctx, const DevPrograms& D, int prog, int64_t n_rows, 
                    void* out, int out_width, uint32_t* vmask32, int vbit);
 // gather: out[i] = in[sel[i]] for a column (+ its validity bit into vmask32)
 int dx_gather_column(dx_ctx* ctx, const DxColumn& in, int64_t n_out, const int64_t* sel, void* out, uint32_t* vmask32, int vbit);
+// the same for up to DX_GATHER_MAX columns of one source table that share the selection and the destination mask word: the
+// selection is read once per row and the validity bits leave as one reduction
+#define DX_GATHER_MAX 8
+struct GatherJobs {
+    int n = 0;
+    const void* in[DX_GATHER_MAX]; const void* vmask[DX_GATHER_MAX]; void* out[DX_GATHER_MAX];
+    uint8_t width[DX_GATHER_MAX], vwidth[DX_GATHER_MAX], vbit_in[DX_GATHER_MAX], vbit[DX_GATHER_MAX];
+};
+int dx_gather_columns(dx_ctx* ctx, const GatherJobs& jobs, int64_t n_out, const int64_t* sel, uint32_t* vmask32);
 // row selection: indices of rows whose flag bit 0 is set -> sel (device), count to host
 int dx_select_rows(dx_ctx* ctx, const uint32_t* flags, int words, int64_t n_rows, DevBufP* sel_out, int64_t* n_sel);

@@ -207,7 +207,15 @@ __global__ void k_minmax_i64(const long long* v, const void* vmask, int vwidth, 
         long long a = __shfl_xor_sync(0xffffffffu, mn, s), b = __shfl_xor_sync(0xffffffffu, mx, s);
         mn = a < mn ? a : mn; mx = b > mx ? b : mx; cnt += __shfl_xor_sync(0xffffffffu, cnt, s);
     }
-    if ((threadIdx.x & 31) == 0 && cnt) { atomicMin(&out[0], mn); atomicMax(&out[1], mx); atomicAdd(reinterpret_cast<unsigned long long*>(&out[2]), (unsigned long long)cnt); }
+    // one atomic triple per CTA: thousands of warps on the same three addresses serialise in L2
+    __shared__ long long s_mn[8], s_mx[8], s_cnt[8];
+    const int w = threadIdx.x >> 5;
+    if ((threadIdx.x & 31) == 0) { s_mn[w] = mn; s_mx[w] = mx; s_cnt[w] = cnt; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int k = 1; k < (int)(blockDim.x >> 5); k++) { mn = s_mn[k] < mn ? s_mn[k] : mn; mx = s_mx[k] > mx ? s_mx[k] : mx; cnt += s_cnt[k]; }
+        if (cnt) { atomicMin(&out[0], mn); atomicMax(&out[1], mx); atomicAdd(reinterpret_cast<unsigned long long*>(&out[2]), (unsigned long long)cnt); }
+    }
 }
 __global__ void k_finalize(int mode, const unsigned long long* a, const unsigned long long* cnt, const unsigned long long* keynull, int keybit,
                            long long n, void* out, int out_width, uint32_t* vmask32, int vbit) {
@@ -801,6 +809,15 @@ struct Exec {
         MaskAlloc masks(ctx, total);
         const DxTable* proto = v.chunks[0].get();
         int out_index = 0;
+        struct PendingGather { GatherJobs jobs; uint32_t* mask = nullptr; std::vector<DevBufP> keep; };
+        std::vector<PendingGather> pending(v.chunks.size());
+        auto flush_gather = [&](size_t k) -> int {
+            PendingGather& pg = pending[k];
+            if (!pg.jobs.n) return DX_OK;
+            int rc = dx_gather_columns(ctx, pg.jobs, cs[k].n, cs[k].filtered ? cs[k].sel->as<int64_t>() : nullptr, pg.mask);
+            pg.jobs.n = 0; pg.mask = nullptr; pg.keep.clear();
+            return rc;
+        };
         for (auto& it : core.items) {
             const ExprP& e = it.expr;
             std::vector<int> src_cols;   // columns forwarded as they are
@@ -864,9 +881,20 @@ struct Exec {
                                     auto alias = std::make_shared<DevBuf>(); alias->p = sc.data->as<uint8_t>() + (size_t)wd * v.chunks[k]->n_rows * 4;
                                     view.data = alias;   // non-owning (ctx == nullptr => no release)
                                 }
-                                int rc2 = dx_gather_column(ctx, view, cs[k].n, cs[k].filtered ? cs[k].sel->as<int64_t>() : nullptr,
-                                                           nb->as<uint8_t>() + ((size_t)wd * total + off) * w, dst.vmask->as<uint32_t>() + off, dst.vbit);
-                                if (rc2) return rc2;
+                                if (oc.type == DX_T_FLAGS) {
+                                    int rc2 = dx_gather_column(ctx, view, cs[k].n, cs[k].filtered ? cs[k].sel->as<int64_t>() : nullptr,
+                                                               nb->as<uint8_t>() + ((size_t)wd * total + off) * w, dst.vmask->as<uint32_t>() + off, dst.vbit);
+                                    if (rc2) return rc2;
+                                    continue;
+                                }
+                                // forwarded columns of one chunk that share a destination mask word go out together
+                                PendingGather& pg = pending[k];
+                                uint32_t* mdst = dst.vmask->as<uint32_t>() + off;
+                                if (pg.jobs.n == DX_GATHER_MAX || (pg.jobs.n && pg.mask != mdst)) { int rc2 = flush_gather(k); if (rc2) return rc2; }
+                                const int j = pg.jobs.n++;
+                                pg.mask = mdst; pg.keep.push_back(view.data); pg.keep.push_back(view.vmask); pg.keep.push_back(nb); pg.keep.push_back(dst.vmask);
+                                pg.jobs.in[j] = view.data->p; pg.jobs.vmask[j] = view.vmask ? view.vmask->p : nullptr; pg.jobs.out[j] = nb->as<uint8_t>() + (size_t)off * w;
+                                pg.jobs.width[j] = (uint8_t)w; pg.jobs.vwidth[j] = (uint8_t)view.vwidth; pg.jobs.vbit_in[j] = (uint8_t)view.vbit; pg.jobs.vbit[j] = (uint8_t)dst.vbit;
                             }
                             off += cs[k].n;
                         }
@@ -950,6 +978,7 @@ struct Exec {
                 t->cols.push_back(oc); out_index++;
             }
         }
+        for (size_t k = 0; k < pending.size(); k++) { int rc = flush_gather(k); if (rc) return rc; }
         *out = t; return DX_OK;
     }
 
@@ -1968,7 +1997,7 @@ int dx_flow::route(const std::string& name_space, const DxTableP& projected, lon
                 DevBuf mm(ctx, 32);
                 long long init[3] = {0x7FFFFFFFFFFFFFFFll, (long long)0x8000000000000000ull, 0};
                 DX_CUDA(ctx, cudaMemcpyAsync(mm.p, init, 24, cudaMemcpyHostToDevice, ctx->stream));
-                k_minmax_i64<<<(unsigned)std::min<long long>((cur->n_rows + 255) / 256, 2048), 256, 0, ctx->stream>>>(
+                k_minmax_i64<<<(unsigned)std::min<long long>((cur->n_rows + 255) / 256, (long long)ctx->sm_count * 8), 256, 0, ctx->stream>>>(
                     c.data->as<long long>(), c.vmask ? c.vmask->p : nullptr, c.vwidth, c.vbit, cur->n_rows, mm.as<long long>());
                 ctx->launches["k_minmax"]++;
                 long long h[3];

@@ -54,8 +54,10 @@ int dx_ctx_synchronize(dx_ctx* ctx);
 /* pooled device memory for callers that stage inputs themselves */
 int dx_dev_alloc(dx_ctx* ctx, int64_t bytes, void** out);
 void dx_dev_free(dx_ctx* ctx, void* p);
-/* page-locked host memory, so that the copies inside process_batch / decode run at link speed */
+/* page-locked host memory, so that the copies inside process_batch / decode run at link speed; the pages are taken from the
+ * NUMA node the context's GPU is attached to when the platform reports one (dx_ctx_numa_node: -1 if it does not) */
 int dx_host_alloc(dx_ctx* ctx, int64_t bytes, void** out);
+int dx_ctx_numa_node(dx_ctx* ctx);
 void dx_host_free(dx_ctx* ctx, void* p);
 int dx_copy_d2h_async(dx_ctx* ctx, void* dst_host, const void* src_dev, int64_t bytes);   /* on the ctx stream */
 int dx_copy_h2d(dx_ctx* ctx, void* dst_dev, const void* src_host, int64_t bytes);
