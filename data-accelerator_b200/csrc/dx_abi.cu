@@ -68,7 +68,7 @@ int dx_ctx_synchronize(dx_ctx* c) { DX_CUDA(c, cudaStreamSynchronize(c->stream))
 int dx_dev_alloc(dx_ctx* c, int64_t bytes, void** out) {
     if (bytes < 0 || !out) return c->set_error(DX_ERR_ARG, "dx_dev_alloc: bad arguments");
     cudaSetDevice(c->device);
-    void* p = c->pool.alloc((size_t)bytes + 64);
+    void* p = c->pool.alloc((size_t)bytes + 64, true);      // the caller's blocks are allocation bases (CUDA IPC exports them)
     if (!p) return c->set_error(DX_ERR_CUDA, "device allocation failed");
     *out = p; return DX_OK;
 }

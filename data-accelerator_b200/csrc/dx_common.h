@@ -34,18 +34,27 @@ static inline int dx_type_width(int t) { return t == DX_T_STR ? 4 : 8; }
 
 struct dx_ctx;
 
-// Device memory pool: cudaMalloc'ed blocks recycled by size class so a steady-state
-// micro-batch loop performs no allocation calls.
+// Device memory pool.  Memory comes from the driver in large slabs (each at least half of what is already held, so a
+// growing working set — a window cache filling up over its first hour of batches — costs O(log) cudaMalloc calls, not several
+// per micro-batch) and is handed out best-fit from an address-ordered free list with splitting and coalescing; a steady-state
+// micro-batch loop performs no allocation calls at all.  Blocks for the caller (dx_dev_alloc) are dedicated allocations, so
+// their addresses are allocation bases (what CUDA IPC exports).
 struct DxPool {
-    std::multimap<size_t, void*> free_blocks;
+    std::map<char*, size_t> slabs;                  // base -> bytes, as obtained from cudaMalloc
+    std::map<char*, size_t> free_by_addr;           // free blocks; neighbours inside one slab are merged
+    std::multimap<size_t, char*> free_by_size;
     std::map<void*, size_t> live;
     size_t bytes_reserved = 0;
     std::mutex mu;
     int device = 0;
-    void* alloc(size_t bytes);
+    void* alloc(size_t bytes, bool dedicated = false);
     void release(void* p);
-    void trim();
+    void trim();                                    // returns every slab that is entirely free to the driver
     ~DxPool();
+private:
+    void add_free(char* p, size_t n);
+    void take_free(std::map<char*, size_t>::iterator it);
+    char* new_slab(size_t bytes);
 };
 
 struct dx_ctx {

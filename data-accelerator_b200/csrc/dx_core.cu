@@ -3,34 +3,66 @@
 
 // ------------------------------- pool ---------------------------------------------------
 static size_t round_size(size_t n) {
-    // size classes: next multiple of 1/8 of the leading power of two (<= 12.5 % slack), min 512 B
+    // 512-byte granules up to 1 MiB, 64 KiB granules above (keeps splits of large blocks from littering the free list)
     if (n < 512) return 512;
-    size_t p = 1; while ((p << 1) <= n) p <<= 1;
-    size_t step = p >> 3;
-    return (n + step - 1) / step * step;
+    const size_t g = n >= (1u << 20) ? 65536 : 512;
+    return (n + g - 1) / g * g;
 }
-
-void* DxPool::alloc(size_t bytes) {
-    size_t sz = round_size(bytes);
+void DxPool::add_free(char* p, size_t n) {
+    // merge with the free neighbours that lie in the same slab
+    auto sl = slabs.upper_bound(p); --sl;
+    char* lo = sl->first; char* hi = sl->first + sl->second;
+    auto nx = free_by_addr.lower_bound(p);
+    if (nx != free_by_addr.end() && nx->first == p + n && nx->first < hi) { n += nx->second; take_free(nx); }
+    auto pv = free_by_addr.lower_bound(p);
+    if (pv != free_by_addr.begin()) {
+        --pv;
+        if (pv->first + pv->second == p && pv->first >= lo) { p = pv->first; n += pv->second; take_free(pv); }
+    }
+    free_by_addr[p] = n;
+    free_by_size.emplace(n, p);
+}
+void DxPool::take_free(std::map<char*, size_t>::iterator it) {
+    auto r = free_by_size.equal_range(it->second);
+    for (auto k = r.first; k != r.second; ++k) if (k->second == it->first) { free_by_size.erase(k); break; }
+    free_by_addr.erase(it);
+}
+char* DxPool::new_slab(size_t bytes) {
+    void* p = nullptr;
+    if (cudaMalloc(&p, bytes) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    slabs[(char*)p] = bytes; bytes_reserved += bytes;
+    return (char*)p;
+}
+void* DxPool::alloc(size_t bytes, bool dedicated) {
+    const size_t sz = round_size(bytes);
     std::lock_guard<std::mutex> g(mu);
-    auto it = free_blocks.lower_bound(sz);
-    if (it != free_blocks.end() && it->first <= sz + sz / 4) {
-        void* p = it->second; size_t s = it->first;
-        free_blocks.erase(it); live[p] = s;
+    if (dedicated) {
+        // a free block that is a whole slab of a fitting size serves as well as a new allocation
+        for (auto it = free_by_size.lower_bound(sz); it != free_by_size.end() && it->first <= sz + sz / 4; ++it) {
+            auto sl = slabs.find(it->second);
+            if (sl != slabs.end() && sl->second == it->first) { char* p = it->second; const size_t n = it->first; take_free(free_by_addr.find(p)); live[p] = n; return p; }
+        }
+        char* p = new_slab(sz);
+        if (!p) { mu.unlock(); trim(); mu.lock(); p = new_slab(sz); }
+        if (!p) return nullptr;
+        live[p] = sz;
         return p;
     }
-    void* p = nullptr;
-    cudaError_t e = cudaMalloc(&p, sz);
-    if (e != cudaSuccess) {
-        // release cached blocks and retry once
-        for (auto& kv : free_blocks) { cudaFree(kv.second); bytes_reserved -= kv.first; }
-        free_blocks.clear();
-        cudaGetLastError();
-        e = cudaMalloc(&p, sz);
-        if (e != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    auto it = free_by_size.lower_bound(sz);
+    char* p; size_t have;
+    if (it != free_by_size.end()) { p = it->second; have = it->first; take_free(free_by_addr.find(p)); }
+    else {
+        size_t grow = bytes_reserved / 2;
+        if (grow < (64u << 20)) grow = 64u << 20;
+        if (grow > ((size_t)4 << 30)) grow = (size_t)4 << 30;
+        size_t want = sz > grow ? sz : grow;
+        want = (want + (2u << 20) - 1) / (2u << 20) * (2u << 20);
+        p = new_slab(want); have = want;
+        if (!p) { mu.unlock(); trim(); mu.lock(); p = new_slab(sz); have = sz; }     // memory is tight: exactly what is needed
+        if (!p) return nullptr;
     }
-    bytes_reserved += sz;
-    live[p] = sz;
+    if (have - sz >= 65536 || (have - sz >= 512 && sz < 65536)) { add_free(p + sz, have - sz); have = sz; }
+    live[p] = have;
     return p;
 }
 void DxPool::release(void* p) {
@@ -38,17 +70,21 @@ void DxPool::release(void* p) {
     std::lock_guard<std::mutex> g(mu);
     auto it = live.find(p);
     if (it == live.end()) return;
-    free_blocks.emplace(it->second, p);
+    const size_t n = it->second;
     live.erase(it);
+    add_free((char*)p, n);
 }
 void DxPool::trim() {
     std::lock_guard<std::mutex> g(mu);
-    for (auto& kv : free_blocks) { cudaFree(kv.second); bytes_reserved -= kv.first; }
-    free_blocks.clear();
+    for (auto sl = slabs.begin(); sl != slabs.end();) {
+        auto f = free_by_addr.find(sl->first);
+        if (f != free_by_addr.end() && f->second == sl->second) {
+            take_free(f); cudaFree(sl->first); bytes_reserved -= sl->second; sl = slabs.erase(sl);
+        } else ++sl;
+    }
 }
 DxPool::~DxPool() {
-    for (auto& kv : free_blocks) cudaFree(kv.second);
-    for (auto& kv : live) cudaFree(kv.first);
+    for (auto& kv : slabs) cudaFree(kv.first);
 }
 
 // ------------------------------- dictionary ---------------------------------------------
