@@ -403,7 +403,7 @@ __global__ void __launch_bounds__(256, K2_MIN_CTAS) k2_rules_bucket(const __grid
 #define RF_NBUF 2                    // staged tiles per CTA
 #endif
 #ifndef RF_MIN_CTAS
-#define RF_MIN_CTAS 3
+#define RF_MIN_CTAS 4
 #endif
 enum { RF_F64 = 0, RF_F64_FROM_I64 = 1, RF_I32 = 2, RF_I64 = 3, RF_CODE = 4, RF_IDX = 5 };
 struct RFSpace {
