@@ -57,6 +57,7 @@ __global__ void __launch_bounds__(256) k3p_scatter(const __grid_constant__ AggIn
         const long long row = in.sel ? in.sel[i] : i;
         long long t;
         if (!p_load(in.range_col, row, t)) continue;                  // no timestamp: in no window
+        if (in.has_range && (t < in.range_lo || t >= in.range_hi)) continue;      // a cached batch's late-event cut
         const long long pane = p_floor_div(t, in.pane_us, inv_pane);
         long long kv[DX_AGG_MAX_KEYS];
         unsigned long long bits = 0, h = 0x2545F4914F6CDD1Dull;
@@ -131,7 +132,7 @@ __global__ void __launch_bounds__(SC_NT) k3p_scatter_staged(const __grid_constan
             for (int k = 0; k < SC_MAXK; k++) if (k < nk) { if (!p_load_u(in.keys[k], row, kv[k])) bits |= 1ull << k; }
 #pragma unroll
             for (int v = 0; v < SC_MAXV; v++) if (v < nv) { if (p_load_u(in.vals[v], row, xv[v])) bits |= 1ull << (16 + v); }
-            if (!has_t) continue;                                      // no timestamp: in no window
+            if (!has_t || (in.has_range && (t < in.range_lo || t >= in.range_hi))) continue;      // no timestamp: in no window; below a cached batch's late-event cut: not in the batch
 #pragma unroll
             for (int k = 0; k < SC_MAXK; k++) if (k < nk) h = pmix64(h ^ (unsigned long long)kv[k]);
             h = pmix64(h ^ (bits & 0xFFFFull));

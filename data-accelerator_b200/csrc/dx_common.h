@@ -185,6 +185,9 @@ struct DxTable {
     std::vector<std::string> col_owner;   // join results: the table (name or alias) each column came from, for qualified references
     bool has_ts_bounds = false;     // window cache: bounds of the flow's timestamp column over this table's rows
     long long ts_min = 0, ts_max = 0;
+    // window cache: rows whose timestamp is NULL or below ts_cut are not part of this cached batch (the late-event drop of
+    // CPF:161-167 kept as a predicate instead of a filtered copy); every reader of a cached batch applies it with its time range
+    bool has_cut = false; long long ts_cut = 0;
     int find(const std::string& n) const {
         for (size_t i = 0; i < cols.size(); i++) if (cols[i].name == n) return (int)i;
         return -1;

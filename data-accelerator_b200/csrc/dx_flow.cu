@@ -196,12 +196,12 @@ static std::string last_part(const std::string& n) { size_t k = n.rfind('.'); re
 __global__ void k_fill_i64(long long* p, long long n, long long v) {
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) p[i] = v;
 }
-__global__ void k_minmax_i64(const long long* v, const void* vmask, int vwidth, int vbit, long long n, long long* out /* [min, max, count] */) {
+__global__ void k_minmax_i64(const long long* v, const void* vmask, int vwidth, int vbit, long long n, long long cut, long long* out /* [min, max, count] over the non-NULL values >= cut */) {
     long long mn = 0x7FFFFFFFFFFFFFFFll, mx = (long long)0x8000000000000000ull, cnt = 0;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
         bool valid = true;
         if (vmask) { uint32_t m = vwidth == 1 ? reinterpret_cast<const uint8_t*>(vmask)[i] : reinterpret_cast<const uint32_t*>(vmask)[i]; valid = (m >> vbit) & 1u; }
-        if (valid) { long long x = v[i]; mn = x < mn ? x : mn; mx = x > mx ? x : mx; cnt++; }
+        if (valid) { long long x = v[i]; if (x >= cut) { mn = x < mn ? x : mn; mx = x > mx ? x : mx; cnt++; } }
     }
     for (int s = 16; s > 0; s >>= 1) {
         long long a = __shfl_xor_sync(0xffffffffu, mn, s), b = __shfl_xor_sync(0xffffffffu, mx, s);
@@ -283,7 +283,7 @@ struct Exec {
         ExprP cond = core.where;
         if (v.ranged) {
             auto col = std::make_shared<Expr>(); col->kind = EK::Col; col->parts = {v.ts_col};
-            auto ge = std::make_shared<Expr>(); ge->kind = EK::Bin; ge->sval = ">="; ge->args = {col, ts_const(v.lo_us)};
+            auto ge = std::make_shared<Expr>(); ge->kind = EK::Bin; ge->sval = ">="; ge->args = {col, ts_const(chunk->has_cut ? std::max(v.lo_us, chunk->ts_cut) : v.lo_us)};
             auto lt = std::make_shared<Expr>(); lt->kind = EK::Bin; lt->sval = "<"; lt->args = {col, ts_const(v.hi_us)};
             auto rng = std::make_shared<Expr>(); rng->kind = EK::Bin; rng->sval = "AND"; rng->args = {ge, lt};
             if (cond) { auto both = std::make_shared<Expr>(); both->kind = EK::Bin; both->sval = "AND"; both->args = {rng, cond}; cond = both; }
@@ -1340,7 +1340,7 @@ struct Exec {
                 if (!c.data || c.type != DX_T_TS) return fail(DX_ERR_UNSUPPORTED, "window timestamp column must be a materialised timestamp");
                 in.range_col.data = c.data->p; in.range_col.vmask = c.vmask ? c.vmask->p : nullptr; in.range_col.vwidth = c.vwidth;
                 in.range_col.vbit = c.vbit; in.range_col.width = 8;
-                in.range_lo = v.lo_us; in.range_hi = v.hi_us; in.has_range = 1;
+                in.range_lo = ch->has_cut ? std::max(v.lo_us, ch->ts_cut) : v.lo_us; in.range_hi = v.hi_us; in.has_range = 1;
             }
             auto col_desc = [&](const DxColumn& c) { ProgCol pc; pc.data = c.data->p; pc.vmask = c.vmask ? c.vmask->p : nullptr; pc.vwidth = c.vwidth; pc.vbit = c.vbit; pc.width = dx_type_width(c.type); pc.pad = 0; return pc; };
             auto eval_temp = [&](const ExprP& e, int* type_out, ProgCol* pc) -> int {
@@ -1463,7 +1463,7 @@ struct Exec {
                     if (rc) return rc;
                     if (P == 0 && F->pane_partitions_first > 0) P = F->pane_partitions_first;      // tests start too coarse on purpose
                     if (P == 0) { P = 256; while (P < 16384 && (long long)P * 1200 < chp->n_rows) P <<= 1; }
-                    in.has_range = 0; in.pane_us = pane_us;
+                    in.has_range = chp->has_cut ? 1 : 0; in.range_lo = chp->ts_cut; in.range_hi = 0x7FFFFFFFFFFFFFFFll; in.pane_us = pane_us;   // every row of the cached batch, keyed by its pane
                     PanePartialP pp; pp.chunk = chp;
                     bool ovf = false;
                     auto& fill = F->pane_fill[sig];
@@ -1540,7 +1540,7 @@ struct Exec {
                     AggTable P; int rc = P.init(ctx, nk + 1, (int)val_exprs.size(), accs, pcap); if (rc) return rc;
                     InputHold hold; AggInput in;
                     rc = make_input(chp.get(), nullptr, chp->n_rows, true, &in, &hold); if (rc) return rc;
-                    in.has_range = 0; in.pane_us = pane_us;          // every row with a timestamp, keyed by its pane
+                    in.has_range = chp->has_cut ? 1 : 0; in.range_lo = chp->ts_cut; in.range_hi = 0x7FFFFFFFFFFFFFFFll; in.pane_us = pane_us;          // every row of the cached batch, keyed by its pane
                     memset(&in.keys[nk], 0, sizeof(ProgCol));
                     rc = P.update(in); if (rc) return rc;
                     unsigned long long ng = 0; bool ovf = false;
@@ -1978,34 +1978,35 @@ int dx_flow::route(const std::string& name_space, const DxTableP& projected, lon
                 rc = X.materialize_const(&proj_w->cols[tc], proj_w->n_rows, nullptr); if (rc) return rc;
             }
         }
-        View all; all.chunks.push_back(proj_w);
-        views["__projected"] = all;
-        SelectCore keep; keep.from = "__projected";
-        SelectItem star; star.expr = std::make_shared<Expr>(); star.expr->kind = EK::Star; keep.items.push_back(star);
-        auto col = std::make_shared<Expr>(); col->kind = EK::Col; col->parts = {ts_column};
-        auto ge = std::make_shared<Expr>(); ge->kind = EK::Bin; ge->sval = ">="; ge->args = {col, ts_const(E * 1000)};
-        keep.where = ge;
-        X.stmt_name = "window-cache";
-        DxTableP cur; rc = X.exec_plain(keep, views["__projected"], &cur); if (rc) return rc;
-        views.erase("__projected");
-        metric("Input_DataXProcessedInput_Events_Count", (double)cur->n_rows);
-        {   // bounds of the timestamp column over the cached rows: later window views skip batches that cannot intersect them
+        // The late-event drop (CPF:161-167: rows with timestamp >= E stay) is kept as a predicate on the cached batch, not as a
+        // filtered copy: cur shares the projected table's buffers, and every reader of a cached batch — window views, pane partial
+        // builds — applies ts >= ts_cut together with its own time range.  One pass over the timestamp column gives the count of
+        // the kept rows (the metric) and their timestamp bounds (later window views skip batches that cannot intersect them).
+        DxTableP cur = std::make_shared<DxTable>(*proj_w);
+        cur->has_cut = true; cur->ts_cut = E * 1000; cur->has_ts_bounds = false;
+        long long kept = 0;
+        {
             BindScope bs; bs.table = cur.get();
             std::string err; int tc = dx_resolve_column(bs, std::vector<std::string>{ts_column}, &err);
-            if (tc >= 0 && cur->cols[tc].data && cur->cols[tc].type == DX_T_TS && cur->n_rows > 0) {
-                const DxColumn& c = cur->cols[tc];
+            if (tc < 0) return ctx->set_error(DX_ERR_ARG, "timestamp column: " + err);
+            const DxColumn& c = cur->cols[tc];
+            if (cur->n_rows > 0 && !c.all_null && c.type != DX_T_NULL) {
+                if (!c.data || c.type != DX_T_TS) return ctx->set_error(DX_ERR_UNSUPPORTED, "window timestamp column must be a materialised timestamp");
                 DevBuf mm(ctx, 32);
                 long long init[3] = {0x7FFFFFFFFFFFFFFFll, (long long)0x8000000000000000ull, 0};
                 DX_CUDA(ctx, cudaMemcpyAsync(mm.p, init, 24, cudaMemcpyHostToDevice, ctx->stream));
                 k_minmax_i64<<<(unsigned)std::min<long long>((cur->n_rows + 255) / 256, (long long)ctx->sm_count * 8), 256, 0, ctx->stream>>>(
-                    c.data->as<long long>(), c.vmask ? c.vmask->p : nullptr, c.vwidth, c.vbit, cur->n_rows, mm.as<long long>());
+                    c.data->as<long long>(), c.vmask ? c.vmask->p : nullptr, c.vwidth, c.vbit, cur->n_rows, cur->ts_cut, mm.as<long long>());
                 ctx->launches["k_minmax"]++;
                 long long h[3];
                 DX_CUDA(ctx, cudaMemcpyAsync(h, mm.p, 24, cudaMemcpyDeviceToHost, ctx->stream));
                 DX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+                kept = h[2];
                 if (h[2] > 0) { cur->has_ts_bounds = true; cur->ts_min = h[0]; cur->ts_max = h[1]; }
-            } else if (cur->n_rows == 0) { cur->has_ts_bounds = true; cur->ts_min = 1; cur->ts_max = 0; }
+            }
+            if (kept == 0) { cur->has_ts_bounds = true; cur->ts_min = 1; cur->ts_max = 0; }      // nothing kept: outside every window
         }
+        metric("Input_DataXProcessedInput_Events_Count", (double)kept);
         const long long cut = T - (watermark_s + max_window_s) * 1000;
         for (auto it = NS.past_batches.begin(); it != NS.past_batches.end();) { if (it->first <= cut) it = NS.past_batches.erase(it); else ++it; }
         std::vector<DxTableP> U; U.push_back(cur);
