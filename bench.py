@@ -209,8 +209,10 @@ def run_ours(args):
 
         def exchange(self, table, mode):
             if mode == "put":
-                recv_ptr, n_recv, counts = px.exchange(table, COLS, COLS[:2])
+                recv_ptr, firsts, cnts, counts = px.exchange_blocks(table, COLS, COLS[:2])
                 self.keep = None
+                self.blocks = (firsts, cnts)
+                n_recv = int(cnts.sum())
             else:
                 counts, rec_bytes = dx.parallel.pack_by_key(table, COLS, COLS[:2], world, send.data_ptr())
                 recv_counts = dx.parallel.exchange_counts(counts)
@@ -218,6 +220,7 @@ def run_ours(args):
                 recv = dx.parallel.exchange_records(send[: int(counts.sum()) * rec_words], counts, recv_counts, rec_words)
                 torch.cuda.synchronize()
                 n_recv, recv_ptr, self.keep = int(recv_counts.sum()), recv.data_ptr(), recv
+                self.blocks = None
             self.wire += int((counts.sum() - counts[rank]) * 8 * rec_words)
             return recv_ptr, n_recv
 
@@ -241,7 +244,10 @@ def run_ours(args):
             if time_exchange:
                 self.ev[1].record(stream)
             mark("exchange")
-            part = dx.parallel.table_from_packed(ctx, NAMES, TYPES, recv_ptr if n_recv else 0, n_recv)
+            if self.blocks is not None:
+                part = dx.parallel.table_from_packed_blocks(ctx, NAMES, TYPES, recv_ptr, *self.blocks)
+            else:
+                part = dx.parallel.table_from_packed(ctx, NAMES, TYPES, recv_ptr if n_recv else 0, n_recv)
             mark("unpack")
             r = dx.parallel.process_table(self.agg, part, T, INTERVAL_MS)
             mark("windows")
@@ -443,7 +449,7 @@ def run_ours(args):
             shuffle[mode] = {"exchange_ms_per_batch": round(a2a, 3), "wire_bytes_out_per_gpu_per_batch": int(wire),
                              "gbs_per_gpu_per_direction": round(wire / max(a2a, 1e-9) / 1e6, 2),
                              "frac_of_nvlink_900": round(wire / max(a2a, 1e-9) / 1e6 / 900, 4),
-                             "what": "count + offsets all-gather + fused put over peer memory + barrier" if mode == "put"
+                             "what": "fused put into per-sender blocks over peer memory + one all-gather of the counts (no count round before the put)" if mode == "put"
                                      else "count exchange + NCCL all_to_all_single (the K5 pack before it is not in this time)"}
 
     # ---- stage c2: decode + rules only (the round-1 headline; no projection of the timestamp, no exchange, no windows)

@@ -582,6 +582,16 @@ int dx_table_shuffle_put(const dx_table* h, const char* const* cols, int n_cols,
     int rc = shuffle_columns(t, cols, n_cols, key_cols, n_keys, &idx, &kpos); if (rc) return rc;
     return dx_shuffle_put(t->ctx, t, idx, kpos, world, peer_bufs, first_record);
 }
+
+int dx_table_shuffle_put_blocks(const dx_table* h, const char* const* cols, int n_cols, const char* const* key_cols, int n_keys, int world,
+                                void* const* peer_bufs, const int64_t* first_record, const int64_t* block_records, int64_t* sent) {
+    const DxTable* t = T(h);
+    cudaSetDevice(t->ctx->device);
+    if (!peer_bufs || !first_record || !block_records || !sent) return t->ctx->set_error(DX_ERR_ARG, "shuffle_put_blocks: bad arguments");
+    std::vector<int> idx, kpos;
+    int rc = shuffle_columns(t, cols, n_cols, key_cols, n_keys, &idx, &kpos); if (rc) return rc;
+    return dx_shuffle_put(t->ctx, t, idx, kpos, world, peer_bufs, first_record, block_records, sent);
+}
 int dx_ipc_export(dx_ctx* c, const void* dev_ptr, uint8_t* handle64) {
     if (!c || !dev_ptr || !handle64) return DX_ERR_ARG;
     static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
@@ -663,6 +673,19 @@ int dx_table_from_packed(dx_ctx* c, const char* const* col_names, const int* col
     for (int i = 0; i < n_cols; i++) { names.push_back(col_names[i]); types.push_back(col_types[i]); }
     DxTableP t;
     int rc = dx_shuffle_unpack(c, names, types, packed_dev, n_rows, &t);
+    if (rc) return rc;
+    *out = dx_wrap_table(t);
+    return DX_OK;
+}
+
+int dx_table_from_packed_blocks(dx_ctx* c, const char* const* col_names, const int* col_types, int n_cols, const void* packed_dev,
+                                int n_blocks, const int64_t* block_first, const int64_t* block_count, dx_table** out) {
+    if (!c || !out || n_cols < 1 || n_blocks < 1 || !block_first || !block_count) return DX_ERR_ARG;
+    cudaSetDevice(c->device);
+    std::vector<std::string> names; std::vector<int> types;
+    for (int i = 0; i < n_cols; i++) { names.push_back(col_names[i]); types.push_back(col_types[i]); }
+    DxTableP t;
+    int rc = dx_shuffle_unpack(c, names, types, packed_dev, 0, &t, n_blocks, block_first, block_count);
     if (rc) return rc;
     *out = dx_wrap_table(t);
     return DX_OK;

@@ -76,7 +76,10 @@ __global__ void __launch_bounds__(256) k5_scatter(const __grid_constant__ Shuffl
 // K5 fused with the exchange: the record of every row is written straight into the receive buffer of the GPU that owns
 // its key — a peer pointer mapped over NVLink (CUDA IPC) — at the offset this rank was assigned there, so the hash, the
 // column gather and the transfer overlap row by row and neither a send buffer nor a separate all-to-all pass exists.
-struct PutTargets { unsigned long long* base[DX_SHUFFLE_MAX_WORLD]; unsigned long long first[DX_SHUFFLE_MAX_WORLD]; };
+struct PutTargets {
+    unsigned long long* base[DX_SHUFFLE_MAX_WORLD]; unsigned long long first[DX_SHUFFLE_MAX_WORLD];
+    unsigned long long limit[DX_SHUFFLE_MAX_WORLD];      // records this rank's block holds in that owner's buffer (>= 1): nothing is written past it
+};
 __global__ void __launch_bounds__(256) k5_scatter_put(const __grid_constant__ ShuffleArgs a, const __grid_constant__ PutTargets tg, unsigned long long* cursor) {
     const int rec_words = a.n_cols + 1;
     const int lane = threadIdx.x & 31;
@@ -194,7 +197,10 @@ __global__ void __launch_bounds__(PT_NT) k5_put_tiled(const __grid_constant__ Sh
                 r[c] = (unsigned long long)v;
             }
             r[a.n_cols] = valid;
-            s_dst[slot] = tg.base[dst[j]] + (tg.first[dst[j]] + s_gstart[dst[j]] + rank[j]) * rw;
+            // a record past the block's end is written over the block's last record: the call fails anyway (the cursor says so),
+            // and no store ever leaves the block
+            const unsigned long long at = s_gstart[dst[j]] + rank[j], lim = tg.limit[dst[j]];
+            s_dst[slot] = tg.base[dst[j]] + (tg.first[dst[j]] + (at < lim ? at : lim - 1ull)) * rw;
         }
         __syncthreads();
         {   // no division: word index = thread id modulo the next power of two >= the record length (the lanes past it idle)
@@ -222,10 +228,21 @@ static int pt_launch(dx_ctx* ctx, const ShuffleArgs& a, const PutTargets& tg, un
     return DX_OK;
 }
 
-__global__ void __launch_bounds__(256) k5_unpack(const unsigned long long* packed, long long n_rows, int n_cols, UnpackCols cols, uint32_t* vmask32) {
+// segs: the received records lie in up to DX_SHUFFLE_MAX_WORLD runs (one block per sender); row i of the table is record
+// first[s] + (i - pre[s]) of the run s with pre[s] <= i < pre[s + 1]
+struct UnpackSegs { int n; long long first[DX_SHUFFLE_MAX_WORLD]; long long pre[DX_SHUFFLE_MAX_WORLD + 1]; };
+__global__ void __launch_bounds__(256) k5_unpack(const unsigned long long* packed, long long n_rows, int n_cols, UnpackCols cols, uint32_t* vmask32, const __grid_constant__ UnpackSegs segs) {
     const int rec_words = n_cols + 1;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_rows; i += (long long)gridDim.x * blockDim.x) {
-        const unsigned long long* rec = packed + i * rec_words;
+        long long src = i;
+        if (segs.n == 1) src = segs.first[0] + i;
+        else if (segs.n > 1) {
+            int sg = 0;
+#pragma unroll
+            for (int k = 1; k < DX_SHUFFLE_MAX_WORLD; k++) if (k < segs.n && i >= segs.pre[k]) sg = k;
+            src = segs.first[sg] + (i - segs.pre[sg]);
+        }
+        const unsigned long long* rec = packed + src * rec_words;
         for (int c = 0; c < n_cols; c++) cols.p[c][i] = (long long)rec[c];
         vmask32[i] = (uint32_t)rec[n_cols];
     }
@@ -260,23 +277,35 @@ int dx_shuffle_count(dx_ctx* ctx, const DxTable* t, const std::vector<int>& cols
 // records written directly to each owner's buffer: peer_bufs[r] = rank r's receive buffer as mapped in this process,
 // first_record[r] = where this rank's block starts there
 int dx_shuffle_put(dx_ctx* ctx, const DxTable* t, const std::vector<int>& cols, const std::vector<int>& key_pos, int world,
-                   void* const* peer_bufs, const int64_t* first_record) {
+                   void* const* peer_bufs, const int64_t* first_record, const int64_t* block_records, int64_t* sent) {
     ShuffleArgs a; int rc = shuffle_args(ctx, t, cols, key_pos, world, &a); if (rc) return rc;
+    if (sent) for (int r = 0; r < world; r++) sent[r] = 0;
     if (t->n_rows == 0) return DX_OK;
     PutTargets tg; memset(&tg, 0, sizeof tg);
-    for (int r = 0; r < world; r++) { tg.base[r] = reinterpret_cast<unsigned long long*>(peer_bufs[r]); tg.first[r] = (unsigned long long)first_record[r]; }
+    for (int r = 0; r < world; r++) {
+        tg.base[r] = reinterpret_cast<unsigned long long*>(peer_bufs[r]); tg.first[r] = (unsigned long long)first_record[r];
+        tg.limit[r] = block_records ? (unsigned long long)(block_records[r] > 0 ? block_records[r] : 1) : ~0ull;
+    }
+    const int rec_words = a.n_cols + 1;
+    if (block_records && rec_words > 12) return ctx->set_error(DX_ERR_UNSUPPORTED, "shuffle put into fixed blocks: at most 11 columns");
     DevBuf cur(ctx, DX_SHUFFLE_MAX_WORLD * 8);
     DX_CUDA(ctx, cudaMemsetAsync(cur.p, 0, DX_SHUFFLE_MAX_WORLD * 8, ctx->stream));
     {
         StageTimer tm(ctx, "k5_scatter_put");
-        const int rec_words = a.n_cols + 1;
         if (rec_words <= 12) { rc = pt_launch(ctx, a, tg, cur.as<unsigned long long>()); if (rc) return rc; }
         else if (rec_words <= 16) k5_scatter_put_staged<<<grid_of(ctx, t->n_rows), 256, (size_t)8 * 32 * rec_words * 8, ctx->stream>>>(a, tg, cur.as<unsigned long long>());
         else k5_scatter_put<<<grid_of(ctx, t->n_rows), 256, 0, ctx->stream>>>(a, tg, cur.as<unsigned long long>());
         ctx->launches["k5_scatter_put"]++;
     }
     DX_CUDA(ctx, cudaGetLastError());
+    unsigned long long h[DX_SHUFFLE_MAX_WORLD];
+    DX_CUDA(ctx, cudaMemcpyAsync(h, cur.p, DX_SHUFFLE_MAX_WORLD * 8, cudaMemcpyDeviceToHost, ctx->stream));
     DX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));      // the peers may read once every rank is past this point (the caller's barrier)
+    for (int r = 0; r < world; r++) {
+        if (sent) sent[r] = (int64_t)h[r];
+        if (block_records && h[r] > (unsigned long long)block_records[r])
+            return ctx->set_error(DX_ERR_CAPACITY, "shuffle put: " + std::to_string(h[r]) + " records for rank " + std::to_string(r) + " exceed this rank's block of " + std::to_string(block_records[r]));
+    }
     return DX_OK;
 }
 
@@ -331,7 +360,7 @@ int dx_shuffle_pack(dx_ctx* ctx, const DxTable* t, const std::vector<int>& cols,
         StageTimer tm(ctx, "k5_scatter");
         if (a.n_cols + 1 <= 12) {      // the tiled kernel with every owner's run in the one local buffer
             PutTargets tg; memset(&tg, 0, sizeof tg);
-            for (int r = 0; r < world; r++) { tg.base[r] = reinterpret_cast<unsigned long long*>(packed_dev); tg.first[r] = hb[r]; }
+            for (int r = 0; r < world; r++) { tg.base[r] = reinterpret_cast<unsigned long long*>(packed_dev); tg.first[r] = hb[r]; tg.limit[r] = ~0ull; }
             int rc2 = pt_launch(ctx, a, tg, cursor); if (rc2) return rc2;
         } else k5_scatter<<<grid_of(ctx, t->n_rows), 256, 0, ctx->stream>>>(a, base, cursor, reinterpret_cast<unsigned long long*>(packed_dev));
         ctx->launches["k5_scatter"]++;
@@ -342,7 +371,14 @@ int dx_shuffle_pack(dx_ctx* ctx, const DxTable* t, const std::vector<int>& cols,
 }
 
 int dx_shuffle_unpack(dx_ctx* ctx, const std::vector<std::string>& names, const std::vector<int>& types, const void* packed_dev, int64_t n_rows,
-                      DxTableP* out) {
+                      DxTableP* out, int n_segs, const int64_t* seg_first, const int64_t* seg_count) {
+    UnpackSegs sg; memset(&sg, 0, sizeof sg);
+    if (n_segs > 0) {
+        if (n_segs > DX_SHUFFLE_MAX_WORLD || !seg_first || !seg_count) return ctx->set_error(DX_ERR_ARG, "unpack: bad segment list");
+        sg.n = n_segs; n_rows = 0;
+        for (int k = 0; k < n_segs; k++) { sg.first[k] = seg_first[k]; sg.pre[k] = n_rows; n_rows += seg_count[k]; }
+        sg.pre[n_segs] = n_rows;
+    }
     if (names.empty() || names.size() != types.size() || (int)names.size() > DX_SHUFFLE_MAX_COLS) return ctx->set_error(DX_ERR_ARG, "unpack: 1..32 columns");
     auto t = std::make_shared<DxTable>(); t->ctx = ctx; t->n_rows = n_rows;
     DevBufP mask = make_buf(ctx, (size_t)(n_rows > 0 ? n_rows : 1) * 4);
@@ -357,7 +393,7 @@ int dx_shuffle_unpack(dx_ctx* ctx, const std::vector<std::string>& names, const 
     }
     if (n_rows > 0) {
         StageTimer tm(ctx, "k5_unpack");
-        k5_unpack<<<grid_of(ctx, n_rows), 256, 0, ctx->stream>>>(reinterpret_cast<const unsigned long long*>(packed_dev), n_rows, (int)names.size(), uc, mask->as<uint32_t>());
+        k5_unpack<<<grid_of(ctx, n_rows), 256, 0, ctx->stream>>>(reinterpret_cast<const unsigned long long*>(packed_dev), n_rows, (int)names.size(), uc, mask->as<uint32_t>(), sg);
         ctx->launches["k5_unpack"]++;
         DX_CUDA(ctx, cudaGetLastError());
     }

@@ -140,6 +140,36 @@ def put_by_key(table, cols, key_cols, world, peer_ptrs, first_record):
     table.ctx.check(L.dx_table_shuffle_put(table.h, c_cols, len(cols), c_keys, len(key_cols), world, ptrs, first))
 
 
+def put_blocks_by_key(table, cols, key_cols, world, peer_ptrs, first_record, block_records):
+    """K5 fused put into fixed per-sender blocks (no count exchange before it) -> records written per owner."""
+    L = N.lib()
+    L.dx_table_shuffle_put_blocks.restype = i32
+    L.dx_table_shuffle_put_blocks.argtypes = [vp, P(cp), i32, P(cp), i32, i32, P(vp), P(i64), P(i64), P(i64)]
+    c_cols = (cp * len(cols))(*[c.encode() for c in cols])
+    c_keys = (cp * len(key_cols))(*[c.encode() for c in key_cols])
+    ptrs = (vp * world)(*[C.c_void_p(int(p)) for p in peer_ptrs])
+    first = (i64 * world)(*[int(x) for x in first_record])
+    blocks = (i64 * world)(*[int(x) for x in block_records])
+    sent = (i64 * world)()
+    table.ctx.check(L.dx_table_shuffle_put_blocks(table.h, c_cols, len(cols), c_keys, len(key_cols), world, ptrs, first, blocks, sent))
+    return np.array(list(sent), dtype=np.int64)
+
+
+def table_from_packed_blocks(ctx, names, types, ptr, block_first, block_count):
+    """K5 unpack of records that lie in one run per sender (block_first / block_count in records)."""
+    L = _lib()
+    L.dx_table_from_packed_blocks.restype = i32
+    L.dx_table_from_packed_blocks.argtypes = [vp, P(cp), P(i32), i32, vp, i32, P(i64), P(i64), P(vp)]
+    c_names = (cp * len(names))(*[n.encode() for n in names])
+    c_types = (i32 * len(types))(*types)
+    nb = len(block_first)
+    bf = (i64 * nb)(*[int(x) for x in block_first])
+    bc = (i64 * nb)(*[int(x) for x in block_count])
+    t = C.c_void_p()
+    ctx.check(L.dx_table_from_packed_blocks(ctx.h, c_names, c_types, len(names), C.c_void_p(ptr), nb, bf, bc, C.byref(t)))
+    return Table(ctx, t)
+
+
 def block_offsets(M, rank):
     """M[s][d] = records rank s sends to rank d  ->  (first[d]: where rank `rank`'s block starts in rank d's receive buffer —
     blocks are laid out in sender order — and recv_total[d]: records rank d receives in all)."""
@@ -150,7 +180,8 @@ def block_offsets(M, rank):
 
 class PeerExchange:
     """Receive buffers of all ranks of one box, mapped into every process (CUDA IPC over NVLink), and the bookkeeping of
-    one fused exchange per micro-batch: counts -> all_gather -> block offsets -> put -> barrier -> local unpack.
+    one fused exchange per micro-batch: put into per-sender blocks -> all_gather of the counts -> local unpack (exchange_blocks),
+    or counts -> all_gather -> block offsets -> put -> barrier -> local unpack (exchange: blocks laid out back to back).
     torch.distributed carries only the small integers and the barrier; the records never pass through a collective."""
 
     def __init__(self, ctx, capacity_records, rec_words, group=None):
@@ -163,20 +194,30 @@ class PeerExchange:
         L.dx_ipc_open.restype, L.dx_ipc_open.argtypes = i32, [vp, C.c_char_p, P(vp)]
         L.dx_ipc_close.restype, L.dx_ipc_close.argtypes = i32, [vp, vp]
         self.L = L
-        self.local = ctx.alloc(self.capacity * rec_words * 8)
-        h = C.create_string_buffer(64)
-        ctx.check(L.dx_ipc_export(ctx.h, C.c_void_p(self.local), h))
-        mine = torch.frombuffer(bytearray(h.raw), dtype=torch.uint8).cuda()
-        allh = [torch.empty(64, dtype=torch.uint8, device="cuda") for _ in range(self.world)]
+        # two receive buffers, used by alternate batches (exchange_blocks: a fast rank's next put must not land in the buffer a
+        # slow rank is still unpacking)
+        self.locals = [ctx.alloc(self.capacity * rec_words * 8) for _ in range(2)]
+        self.local = self.locals[0]
+        self.batch_no = 0
+        raw = bytearray()
+        for buf in self.locals:
+            h = C.create_string_buffer(64)
+            ctx.check(L.dx_ipc_export(ctx.h, C.c_void_p(buf), h))
+            raw += h.raw
+        mine = torch.frombuffer(raw, dtype=torch.uint8).cuda()
+        allh = [torch.empty(128, dtype=torch.uint8, device="cuda") for _ in range(self.world)]
         dist.all_gather(allh, mine, group=group)
-        self.ptrs = []
+        self.ptrs2 = [[], []]
         for r in range(self.world):
-            if r == self.rank:
-                self.ptrs.append(self.local)
-                continue
-            p = C.c_void_p()
-            ctx.check(L.dx_ipc_open(ctx.h, bytes(allh[r].cpu().numpy().tobytes()), C.byref(p)))
-            self.ptrs.append(p.value)
+            hb = allh[r].cpu().numpy().tobytes()
+            for k in range(2):
+                if r == self.rank:
+                    self.ptrs2[k].append(self.locals[k])
+                    continue
+                p = C.c_void_p()
+                ctx.check(L.dx_ipc_open(ctx.h, hb[64 * k: 64 * k + 64], C.byref(p)))
+                self.ptrs2[k].append(p.value)
+        self.ptrs = self.ptrs2[0]
 
     def exchange(self, table, cols, key_cols):
         """-> (device pointer of this rank's received records, number of records, counts this rank sent)."""
@@ -195,9 +236,29 @@ class PeerExchange:
         torch.cuda.synchronize()                               # (the barrier runs on torch's stream, the unpack on the library's)
         return self.local, int(recv_total[self.rank]), counts
 
+    def exchange_blocks(self, table, cols, key_cols):
+        """The exchange without a count round before it: every sender owns a fixed block (capacity / world records) in every
+        owner's buffer, puts straight away, and ONE all-gather of the per-owner counts afterwards both tells the owners what
+        arrived and that every put has landed.  -> (receive buffer, first record of each sender's block, records in each
+        block, counts this rank sent); unpack with table_from_packed_blocks."""
+        import torch
+        import torch.distributed as dist
+        par = self.batch_no & 1
+        self.batch_no += 1
+        block = self.capacity // self.world
+        sent = put_blocks_by_key(table, cols, key_cols, self.world, self.ptrs2[par], [self.rank * block] * self.world, [block] * self.world)
+        mine = torch.as_tensor(sent, device="cuda")
+        allc = [torch.empty_like(mine) for _ in range(self.world)]
+        dist.all_gather(allc, mine, group=self.group)          # a rank enters only after its put kernel has completed
+        M = torch.stack(allc).cpu().numpy()                    # M[s][d] = records rank s sent to rank d
+        return self.locals[par], [s_ * block for s_ in range(self.world)], M[:, self.rank].copy(), sent
+
     def close(self):
-        for r, p in enumerate(self.ptrs):
-            if r != self.rank and p:
-                self.L.dx_ipc_close(self.ctx.h, C.c_void_p(p))
-        self.ctx.free(self.local)
+        for k in range(2):
+            for r, p in enumerate(self.ptrs2[k]):
+                if r != self.rank and p:
+                    self.L.dx_ipc_close(self.ctx.h, C.c_void_p(p))
+        for buf in self.locals:
+            self.ctx.free(buf)
         self.ptrs = []
+        self.ptrs2 = [[], []]

@@ -316,12 +316,24 @@ int dx_table_shuffle_count(const dx_table* t, const char* const* cols, int n_col
                            int n_keys, int world, int64_t* counts);
 int dx_table_shuffle_put(const dx_table* t, const char* const* cols, int n_cols, const char* const* key_cols,
                          int n_keys, int world, void* const* peer_bufs, const int64_t* first_record);
+/* The same put without the count exchange before it: every sender owns a fixed block in every owner's receive buffer
+ * (first_record[r] = where this rank's block starts in rank r's buffer, block_records[r] = how many records it holds), so
+ * the ranks exchange their per-owner counts (sent[r]) once AFTER the puts — the one collective that also tells an owner that
+ * every put has landed — and the owner unpacks the blocks with dx_table_from_packed_blocks.  A block that turns out too small
+ * is an error of the call (nothing is written past it).                                                                  */
+int dx_table_shuffle_put_blocks(const dx_table* t, const char* const* cols, int n_cols, const char* const* key_cols,
+                                int n_keys, int world, void* const* peer_bufs, const int64_t* first_record,
+                                const int64_t* block_records, int64_t* sent);
 int dx_ipc_export(dx_ctx* ctx, const void* dev_ptr, uint8_t* handle64);      /* 64-byte handle for another process */
 int dx_ipc_open(dx_ctx* ctx, const uint8_t* handle64, void** dev_ptr);        /* map a peer's buffer */
 int dx_ipc_close(dx_ctx* ctx, void* dev_ptr);
 /* K5 unpack: n_rows received records -> a table with the given column names and DX_TYPE_* types. */
 int dx_table_from_packed(dx_ctx* ctx, const char* const* col_names, const int* col_types, int n_cols,
                          const void* packed_dev, int64_t n_rows, dx_table** out);
+/* ... from n_blocks runs of the buffer (block_first / block_count in records, one block per sender), in block order. */
+int dx_table_from_packed_blocks(dx_ctx* ctx, const char* const* col_names, const int* col_types, int n_cols,
+                                const void* packed_dev, int n_blocks, const int64_t* block_first,
+                                const int64_t* block_count, dx_table** out);
 
 /* ---- host-side artefact parsers, exposed for tests (no GPU needed) ------------------------- */
 /* Canonical text of a statement as the SQL-subset parser understood it; error text on failure. */

@@ -121,3 +121,53 @@ def test_fused_put_lands_every_record_in_its_owners_buffer(dx, ctx):
         assert sorted(map(tuple, recs.tolist())) == sorted(want)
     for b in bufs + srcs:
         ctx.free(b)
+
+
+def test_put_into_sender_blocks_and_unpack_from_blocks(dx, ctx):
+    """The exchange without a count round: each of two senders owns a fixed block in each of four owners' buffers, puts
+    without knowing the counts, reports what it sent, and the owner unpacks the blocks in sender order.  The unpacked table
+    must hold exactly the records the separate pack assigns to that owner; a block that is too small fails the call and
+    writes nothing outside it."""
+    world, senders, block = 4, 2, 6000
+    schema = dxo.iot_schema_json(1)
+    f = dx.CommonProcessorFactory.createProcessor(ctx, dx.flowgen.conf_text("dec"), schema, [PROJ], "")
+    tables, srcs = [], []
+    for s in range(senders):
+        p = dxo.GenParams(900 + s, 3000, 300, T0, I, 60_000, 1, 20, 5, 0)
+        n = 14_000 + 3000 * s
+        data = np.frombuffer(dxo.gen_events(p, 0, n), dtype=np.uint8)
+        src = ctx.alloc(data.size + 64)
+        ctx.h2d(src, data)
+        srcs.append(src)
+        tables.append(dx.parallel.project_device(f, src, data.size, n, T0))
+    bufs = [ctx.alloc(senders * block * 40 + 64) for _ in range(world)]
+    sent = []
+    for s, t in enumerate(tables):
+        sent.append(dx.parallel.put_blocks_by_key(t, COLS, COLS[:2], world, bufs, [s * block] * world, [block] * world))
+        assert (sent[-1] == dx.parallel.count_by_key(t, COLS, COLS[:2], world)).all()
+    M = np.stack(sent)
+    for d in range(world):
+        part = dx.parallel.table_from_packed_blocks(ctx, RECV_NAMES, RECV_TYPES, bufs[d], [s * block for s in range(senders)], M[:, d])
+        assert part.num_rows == int(M[:, d].sum())
+        got = sorted(gpu_rows(part, dx))
+        want = []
+        for t in tables:
+            buf = ctx.alloc(t.num_rows * 40 + 64)
+            counts, _ = dx.parallel.pack_by_key(t, COLS, COLS[:2], world, buf)
+            b = np.concatenate([[0], np.cumsum(counts)])
+            one = dx.parallel.table_from_packed(ctx, RECV_NAMES, RECV_TYPES, buf + int(b[d]) * 40, int(counts[d]))
+            want += gpu_rows(one, dx)
+            one.release(); ctx.free(buf)
+        assert got == sorted(want)
+        part.release()
+    # a block one record too small for the fullest owner: the call fails, the record after the block stays untouched
+    tight = int(sent[0].max()) - 1
+    guard = ctx.alloc((tight + 1) * 40 + 64)
+    ctx.h2d(guard, np.full((tight + 1) * 5, -7, dtype=np.int64))
+    with pytest.raises(dx.DxError) as e:
+        dx.parallel.put_blocks_by_key(tables[0], COLS, COLS[:2], world, [guard] * world, [0] * world, [tight] * world)
+    assert "exceed this rank's block" in str(e.value)
+    assert (ctx.d2h(guard + tight * 40, 40).view(np.int64) == -7).all()
+    for b in bufs + srcs + [guard]:
+        ctx.free(b)
+    f.close()
