@@ -621,3 +621,36 @@ U = SELECT deviceDetails.deviceId, site() AS s, pair(deviceDetails.deviceType, C
         for name in udfs:
             dxo_flow.UDFS.pop(name, None)
     g.close()
+
+
+def test_batch_of_only_late_events_leaves_the_windows_untouched(dx, ctx):
+    """The late-event drop (CPF:161-167) is a predicate on the cached batch here, not a filtered copy: a batch in which EVERY
+    event is older than the watermark must count zero kept events, add nothing to any window, and still age out like any
+    other cached batch; a batch of events without any timestamp behaves the same."""
+    conf = dx.flowgen.conf_text("late", timestamp_column="eventTimeStamp", watermark="60 second",
+                                windows=[("DataXProcessedInput_3minutes", "3 minutes")])
+    tr = """--DataXQuery--
+W = SELECT deviceDetails.deviceId, COUNT(*) AS Count, SUM(deviceDetails.status) AS S, MIN(eventTimeStamp) AS First FROM DataXProcessedInput_3minutes GROUP BY deviceDetails.deviceId
+--DataXQuery--
+B = SELECT deviceDetails.homeId, COUNT(*) AS Count FROM DataXProcessedInput GROUP BY deviceDetails.homeId
+--DataXQuery--
+Rows = SELECT deviceDetails.deviceId, eventTimeStamp FROM DataXProcessedInput_3minutes WHERE deviceDetails.status = 1
+"""
+    g, o = both(dx, ctx, conf, SCHEMA1, [PROJ_TS], tr)
+    for b in range(7):
+        T = T0 + b * I
+        if b == 2:      # events of an hour ago: all late
+            data = gen(dx, 2500, first=b * 2500, shape=1, n_keys=200, base=T - 3_600_000, late=0, future=0)
+        elif b == 4:    # no timestamps at all
+            data = b"\n".join(b'{"deviceDetails":{"deviceId":%d,"deviceType":"Heating","homeId":%d,"status":1}}' % (i % 50, i % 7) for i in range(800)) + b"\n"
+        else:
+            data = gen(dx, 2500, first=b * 2500, shape=1, n_keys=200, base=T, late=20, future=10)
+        rg = g.process_json(data, T, I)
+        ro, mo = o.process(data, T, I)
+        assert same_metrics(rg.metrics, mo), (b, rg.metrics, mo)
+        if b in (2, 4):
+            assert rg.metrics["Input_DataXProcessedInput_Events_Count"] == 0
+        for name in rg.table_names:
+            assert_same_rows(rg.table(name), ro[name], dx)
+        rg.release()
+    g.close()
