@@ -378,6 +378,11 @@ int dx_flow_process_batch(dx_flow* f, const char* name_space, const uint8_t* jso
     try { return f->process(name_space ? name_space : "", json, n_bytes, offsets, n_events, memory_kind, batch_time_ms, interval_ms, now_ms, out); }
     catch (std::exception& e) { return f->ctx->set_error(DX_ERR_STATE, e.what()); }
 }
+int dx_flow_set_event_property(dx_flow* f, int which, const char* key, const uint8_t* bytes, const int64_t* offsets, const uint8_t* valid, int64_t n_events) {
+    if (!f) return DX_ERR_ARG;
+    cudaSetDevice(f->ctx->device);
+    try { return f->set_event_property(which, key, bytes, offsets, valid, n_events); } catch (std::exception& e) { return f->ctx->set_error(DX_ERR_ARG, e.what()); }
+}
 int dx_flow_set_batch_info(dx_flow* f, const dx_batch_info* info) {
     if (!f) return DX_ERR_ARG;
     dx_flow::BatchInfo b;

@@ -140,6 +140,7 @@ struct DxDict {
     std::map<std::string, int32_t> seeded;   // literals already entered from the host
     int init(dx_ctx* c, uint32_t capacity_pow2, uint32_t heap_bytes);
     int insert_host(const std::string& s, int32_t* code_out);   // pre-seed literals
+    int insert_host_many(const std::vector<std::string>& strs, std::vector<int32_t>* codes_out);   // one launch for all of them; grows the table when it is full
     int sync_to_host();                                          // pulls new entries
     // A column of unbounded cardinality (event ids, CAST(timestamp AS STRING)) outgrows any fixed table.  grow() rebuilds the
     // device table four times larger from the host mirror, every string keeping its code, so a streaming flow never dies of a

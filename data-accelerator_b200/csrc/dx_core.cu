@@ -164,6 +164,46 @@ __global__ void dict_bulk_insert(DictDev d, const uint8_t* bytes, const uint32_t
     }
 }
 
+// many host strings at once, one thread per string (the table's insert is the one K1's lanes use concurrently)
+__global__ void dict_insert_many(DictDev d, const uint8_t* bytes, const uint32_t* offs, uint32_t n, int32_t* codes, unsigned long long* err) {
+    for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
+        const uint8_t* b = bytes + offs[k]; const uint32_t len = offs[k + 1] - offs[k];
+        uint64_t w0, w1; dict_pack(b, len, w0, w1);
+        codes[k] = dict_get_or_insert(d, w0, w1, len, b, err);
+    }
+}
+int DxDict::insert_host_many(const std::vector<std::string>& strs, std::vector<int32_t>* codes_out) {
+    dx_ctx* c = ctx;
+    codes_out->assign(strs.size(), -1);
+    std::vector<size_t> todo;
+    for (size_t k = 0; k < strs.size(); k++) { auto hit = seeded.find(strs[k]); if (hit != seeded.end()) (*codes_out)[k] = hit->second; else todo.push_back(k); }
+    if (todo.empty()) return DX_OK;
+    for (int attempt = 0; attempt < 8; attempt++) {
+        std::vector<uint32_t> offs(todo.size() + 1, 0); std::string blob;
+        for (size_t i = 0; i < todo.size(); i++) { blob += strs[todo[i]]; offs[i + 1] = (uint32_t)blob.size(); }
+        DevBuf dbytes(c, blob.size() + 16), doffs(c, offs.size() * 4), dcodes(c, todo.size() * 4 + 16), derr(c, 16);
+        if (!dbytes.p || !doffs.p || !dcodes.p || !derr.p) return c->set_error(DX_ERR_CUDA, "dictionary insert: allocation failed");
+        if (!blob.empty()) DX_CUDA(c, cudaMemcpyAsync(dbytes.p, blob.data(), blob.size(), cudaMemcpyHostToDevice, c->stream));
+        DX_CUDA(c, cudaMemcpyAsync(doffs.p, offs.data(), offs.size() * 4, cudaMemcpyHostToDevice, c->stream));
+        DX_CUDA(c, cudaMemsetAsync(derr.p, 0, 16, c->stream));
+        const unsigned blocks = (unsigned)std::min<size_t>((todo.size() + 127) / 128, 1024);
+        dict_insert_many<<<blocks, 128, 0, c->stream>>>(dev, dbytes.as<uint8_t>(), doffs.as<uint32_t>(), (uint32_t)todo.size(), dcodes.as<int32_t>(), derr.as<unsigned long long>());
+        std::vector<int32_t> got(todo.size());
+        unsigned long long e = 0;
+        DX_CUDA(c, cudaMemcpyAsync(got.data(), dcodes.p, todo.size() * 4, cudaMemcpyDeviceToHost, c->stream));
+        DX_CUDA(c, cudaMemcpyAsync(&e, derr.p, 8, cudaMemcpyDeviceToHost, c->stream));
+        DX_CUDA(c, cudaStreamSynchronize(c->stream));
+        bool full = e != 0;
+        for (int32_t g : got) if (g < 0) full = true;
+        if (!full) {
+            for (size_t i = 0; i < todo.size(); i++) { (*codes_out)[todo[i]] = got[i]; seeded[strs[todo[i]]] = got[i]; }
+            return DX_OK;
+        }
+        int rc = grow(); if (rc) return rc;      // every string that fitted keeps its code; the rest is inserted again
+    }
+    return c->set_error(DX_ERR_CAPACITY, "string dictionary overflow");
+}
+
 int DxDict::overflowed(bool* yes) {
     dx_ctx* c = ctx;
     uint32_t cnt[4] = {0, 0, 0, 0};

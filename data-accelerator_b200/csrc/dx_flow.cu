@@ -821,6 +821,7 @@ struct Exec {
         for (auto& it : core.items) {
             const ExprP& e = it.expr;
             std::vector<int> src_cols;   // columns forwarded as they are
+            std::map<int, std::string> renames;      // leaves of a selected metadata map / struct: their names under the item
             if (e->kind == EK::Star) {
                 if (e->parts.size() == 1 && e->parts[0] == "Raw" && stmt_name == "projection") {
                     // Raw.* in a projection: the decoded leaves, not the transport metadata columns that sit beside Raw
@@ -844,26 +845,43 @@ struct Exec {
                     bool nested_parent = false;       // e.g. `_Properties` in a later step: the leaves `_Properties.<key>` of an earlier one
                     for (auto& pc : proto->cols) if (!pc.nest_kinds.empty() && !pc.data && pc.name.compare(0, prefix.size(), prefix) == 0) nested_parent = true;
                     if (nested_parent || n0 == "Properties" || n0 == "SystemProperties" || n0 == "__DataX_FileInfo" || n0 == "DataXProperties") {
-                        bool any = false;
+                        // every leaf below it goes the way of a forwarded column (constants as they are, per-event values gathered
+                        // like any other column), renamed under the item's name and keeping its place in the map / struct
                         for (size_t c = 0; c < proto->cols.size(); c++) {
                             if (proto->cols[c].name.compare(0, prefix.size(), prefix) != 0) continue;
-                            DxColumn oc = proto->cols[c];
-                            if (oc.data) return fail(DX_ERR_UNSUPPORTED, "materialised metadata column '" + oc.name + "'");
-                            oc.name = item_name(it) + "." + oc.name.substr(prefix.size());
-                            t->cols.push_back(oc); out_index++; any = true;
+                            src_cols.push_back((int)c);
+                            renames[(int)c] = item_name(it) + "." + proto->cols[c].name.substr(prefix.size());
                         }
-                        if (!any) { DxColumn c; c.name = item_name(it); c.type = DX_T_NULL; c.all_null = true; t->cols.push_back(c); out_index++; }
-                        continue;
-                    }
-                    return fail(DX_ERR_ARG, err);
-                }
-                src_cols.push_back(ci);
+                        if (src_cols.empty()) { DxColumn c; c.name = item_name(it); c.type = DX_T_NULL; c.all_null = true; t->cols.push_back(c); out_index++; continue; }
+                    } else return fail(DX_ERR_ARG, err);
+                } else src_cols.push_back(ci);
             }
             if (!src_cols.empty()) {
                 for (int ci : src_cols) {
                     DxColumn oc = proto->cols[ci];
-                    if (e->kind == EK::Col) { oc.name = item_name(it); oc.nest_path.clear(); oc.nest_kinds.clear(); }
-                    if (!(oc.all_null || !oc.data || zero_copy)) {
+                    auto rn = renames.find(ci);
+                    if (rn != renames.end()) oc.name = rn->second;
+                    else if (e->kind == EK::Col) { oc.name = item_name(it); oc.nest_path.clear(); oc.nest_kinds.clear(); }
+                    // A per-batch constant (DataXProperties.BatchTime, a Properties value of the batch) is a different constant in
+                    // every cached batch of a window view: the rows keep the value of the batch they arrived in, so the column is
+                    // laid out chunk by chunk.
+                    bool mixed = false; DxDictP mixed_dict;
+                    if (!oc.data && v.chunks.size() > 1) {
+                        for (auto& chp : v.chunks) {
+                            const DxColumn& sc = chp->cols[ci];
+                            if (sc.data || sc.all_null != oc.all_null || sc.type != oc.type || sc.const_i != oc.const_i || sc.const_f != oc.const_f || sc.const_s != oc.const_s) mixed = true;
+                        }
+                        if (mixed) {
+                            int ty = DX_T_NULL;
+                            for (auto& chp : v.chunks) { const DxColumn& sc = chp->cols[ci]; if (ty == DX_T_NULL && sc.type != DX_T_NULL && !sc.all_null) ty = sc.type; }
+                            if (ty == DX_T_NULL) mixed = false;
+                            else {
+                                oc.type = ty; oc.all_null = false; oc.is_const = false;
+                                if (ty == DX_T_STR) { mixed_dict = std::make_shared<DxDict>(); int rc = mixed_dict->init(ctx, 1024, 1 << 16); if (rc) return rc; oc.dict = mixed_dict; }
+                            }
+                        }
+                    }
+                    if (mixed || !(oc.all_null || !oc.data || zero_copy)) {
                         const int words = oc.type == DX_T_FLAGS ? oc.flag_words : 1;
                         const int w = oc.type == DX_T_FLAGS ? 4 : dx_type_width(oc.type);
                         DevBufP nb = make_buf(ctx, (size_t)(total > 0 ? total : 1) * w * words);
@@ -871,8 +889,12 @@ struct Exec {
                         int rc = masks.assign(&dst, out_index); if (rc) return rc;
                         int64_t off = 0;
                         for (size_t k = 0; k < v.chunks.size(); k++) {
-                            const DxColumn& sc = v.chunks[k]->cols[ci];
+                            DxColumn sc = v.chunks[k]->cols[ci];
                             if (cs[k].n == 0) continue;
+                            if (!sc.data) {        // this cached batch's constant (mixed): NULL rows stay NULL, a value is laid out for the batch's rows
+                                if (sc.all_null || sc.type == DX_T_NULL) { off += cs[k].n; continue; }
+                                int rc2 = materialize_const(&sc, v.chunks[k]->n_rows, mixed_dict); if (rc2) return rc2;
+                            }
                             for (int wd = 0; wd < words; wd++) {
                                 DxColumn view = sc;
                                 if (oc.type == DX_T_FLAGS) {
@@ -1876,6 +1898,50 @@ void dx_flow::add_metadata_columns(DxTable* t, long long batch_ms, long long now
     for (auto& kv : b.properties) t->cols.push_back(meta_const("Properties." + kv.first, true, kv.second, {kv.first}, "m"));
     for (auto& kv : b.system_properties) t->cols.push_back(meta_const("SystemProperties." + kv.first, true, kv.second, {kv.first}, "m"));
 }
+int dx_flow::set_event_property(int which, const char* key, const uint8_t* bytes, const int64_t* offsets, const uint8_t* valid, int64_t n_events) {
+    if ((which != 0 && which != 1) || !key || !*key || n_events < 0 || (n_events > 0 && (!bytes || !offsets)))
+        return ctx->set_error(DX_ERR_ARG, "dx_flow_set_event_property: bad arguments");
+    EventProperty ep; ep.column = std::string(which ? "SystemProperties." : "Properties.") + key;
+    DxDictP& dict = event_prop_dicts[ep.column];
+    if (!dict) { dict = std::make_shared<DxDict>(); int rc = dict->init(ctx, 1u << 16, 1u << 22); if (rc) return rc; }
+    ep.codes.assign((size_t)n_events, -1); ep.valid.assign((size_t)n_events, 0u);
+    std::map<std::string, int32_t> seen; std::vector<std::string> distinct; std::vector<int32_t> which_str((size_t)n_events, -1);
+    for (int64_t r = 0; r < n_events; r++) {
+        if (valid && !valid[r]) continue;
+        if (offsets[r + 1] < offsets[r]) return ctx->set_error(DX_ERR_ARG, "dx_flow_set_event_property: offsets are not ascending");
+        std::string sv(reinterpret_cast<const char*>(bytes) + offsets[r], (size_t)(offsets[r + 1] - offsets[r]));
+        auto hit = seen.find(sv);
+        if (hit == seen.end()) { hit = seen.emplace(sv, (int32_t)distinct.size()).first; distinct.push_back(sv); }
+        which_str[(size_t)r] = hit->second; ep.valid[(size_t)r] = 1u;
+    }
+    std::vector<int32_t> codes;
+    int rc = dict->insert_host_many(distinct, &codes); if (rc) return rc;
+    for (int64_t r = 0; r < n_events; r++) if (which_str[(size_t)r] >= 0) ep.codes[(size_t)r] = codes[(size_t)which_str[(size_t)r]];
+    for (auto& e : event_props) if (e.column == ep.column) { e = std::move(ep); return DX_OK; }
+    event_props.push_back(std::move(ep));
+    return DX_OK;
+}
+// the per-event map values become dictionary columns beside Raw, replacing a per-batch constant of the same key
+int dx_flow::add_event_property_columns(DxTable* t) {
+    for (auto& ep : event_props) {
+        if ((int64_t)ep.codes.size() != t->n_rows)
+            return ctx->set_error(DX_ERR_ARG, "event property '" + ep.column + "' was given for " + std::to_string(ep.codes.size()) + " events, the batch has " + std::to_string(t->n_rows));
+        DxColumn c; c.name = ep.column; c.type = DX_T_STR; c.dict = event_prop_dicts[ep.column];
+        c.nest_path = {ep.column.substr(ep.column.find('.') + 1)}; c.nest_kinds = "m";
+        const size_t nr = (size_t)(t->n_rows > 0 ? t->n_rows : 1);
+        c.data = make_buf(ctx, nr * 4); c.vmask = make_buf(ctx, nr * 4); c.vwidth = 4; c.vbit = 0;
+        if (t->n_rows > 0) {
+            DX_CUDA(ctx, cudaMemcpyAsync(c.data->p, ep.codes.data(), nr * 4, cudaMemcpyHostToDevice, ctx->stream));
+            DX_CUDA(ctx, cudaMemcpyAsync(c.vmask->p, ep.valid.data(), nr * 4, cudaMemcpyHostToDevice, ctx->stream));
+            DX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        }
+        bool replaced = false;
+        for (auto& old : t->cols) if (old.name == c.name) { old = c; replaced = true; }
+        if (!replaced) t->cols.push_back(c);
+    }
+    event_props.clear();
+    return DX_OK;
+}
 bool dx_is_metadata_column(const std::string& n) {
     return n.compare(0, 8, "__DataX_") == 0 || n.compare(0, 16, "DataXProperties.") == 0 || n.compare(0, 11, "Properties.") == 0 || n.compare(0, 17, "SystemProperties.") == 0;
 }
@@ -1894,6 +1960,7 @@ int dx_flow::project(const uint8_t* json, int64_t n_bytes, const int64_t* offset
     // what project() adds before the steps (CPF:97): DataXProperties; Properties / SystemProperties when the batch carries them
     DxTableP projected = std::make_shared<DxTable>(*raw);
     add_metadata_columns(projected.get(), batch_ms_for_props, now_ms);
+    rc = add_event_property_columns(projected.get()); if (rc) return rc;
     bool first = true;
     for (auto& step : projections) {
         View v; v.chunks.push_back(projected); views["Raw"] = v;

@@ -101,6 +101,13 @@ struct dx_flow {
     std::vector<std::string> outputs;
     // transport metadata of the batch being processed (dx_flow_set_batch_info): the FileInternal struct behind __DataX_FileInfo
     // (datax/data/FileInternal.scala:14-20; all NULL for the streaming adapters, CPF:417, 459) and the per-batch maps
+    // per-EVENT values of one Properties / SystemProperties key for the next batch (dx_flow_set_event_property): the maps the
+    // EventHub and Kafka adapters build per record (CPF:405-421, 628-654)
+    struct EventProperty { std::string column; std::vector<int32_t> codes; std::vector<uint32_t> valid; };
+    std::vector<EventProperty> event_props;                   // consumed by the next project()
+    std::map<std::string, DxDictP> event_prop_dicts;          // one dictionary per column for the life of the flow (codes stay comparable across batches)
+    int set_event_property(int which, const char* key, const uint8_t* bytes, const int64_t* offsets, const uint8_t* valid, int64_t n_events);
+    int add_event_property_columns(DxTable* t);
     struct BatchInfo {
         bool has_input_path = false, has_output_folders = false, has_output_file_name = false, has_file_time = false,
              has_rule_index_prefix = false, has_target = false;

@@ -217,6 +217,19 @@ class CommonProcessor:
                     file_time_ms or 0, 0 if file_time_ms is None else 1, enc(rule_index_prefix), enc(target), pk, pv, np_, spk, spv, nsp, enc(executor_id))
         self.ctx.check(fn(self.h, C.byref(info)))
 
+    def set_event_property(self, key, values, system=False):
+        """Per-event values of one Properties (system=True: SystemProperties) key for the NEXT batch (dx_flow_set_event_property):
+        values[i] is bytes / str, or None where event i does not carry the key."""
+        fn = self.L.dx_flow_set_event_property
+        fn.restype, fn.argtypes = C.c_int, [C.c_void_p, C.c_int, C.c_char_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64]
+        enc = [b"" if v is None else (v.encode("utf-8") if isinstance(v, str) else bytes(v)) for v in values]
+        off = np.zeros(len(enc) + 1, dtype=np.int64)
+        off[1:] = np.cumsum([len(e) for e in enc])
+        blob = np.frombuffer(b"".join(enc) + b"\0", dtype=np.uint8)
+        valid = np.array([0 if v is None else 1 for v in values], dtype=np.uint8)
+        self.ctx.check(fn(self.h, 1 if system else 0, key.encode("utf-8"), blob.ctypes.data_as(C.c_void_p), off.ctypes.data_as(C.c_void_p),
+                          valid.ctypes.data_as(C.c_void_p) if len(values) else None, len(values)))
+
     def stage_json(self, host_ptr, n_bytes):
         """Starts the host->device copy of the NEXT batch (page-locked host memory at host_ptr) and returns a handle for
         process_staged; the copy overlaps whatever the processor is doing meanwhile."""

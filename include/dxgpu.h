@@ -221,6 +221,14 @@ typedef struct dx_batch_info {
     const char* executor_id;                      /* DataXProperties.CPExecutor; NULL = "driver" */
 } dx_batch_info;
 int dx_flow_set_batch_info(dx_flow* flow, const dx_batch_info* info);
+/* Per-EVENT transport properties: the Properties (which = 0) or SystemProperties (which = 1) value of one key for every event of the
+ * NEXT batch, as the EventHub and Kafka adapters put them beside each body (processEventData CPF:405-422: Row(body, properties,
+ * systemProperties, ...); processConsumerRecord CPF:628-655).  bytes + offsets (n_events + 1, ascending) hold the UTF-8 values;
+ * valid[i] == 0 (valid may be NULL: all present) means event i does not carry the key (SQL NULL).  The values become a string
+ * column `Properties.<key>` / `SystemProperties.<key>` for that batch (replacing a per-batch constant of the same key from
+ * dx_flow_set_batch_info) and are consumed by the next process call, whose event count must equal n_events.            */
+int dx_flow_set_event_property(dx_flow* flow, int which, const char* key, const uint8_t* bytes, const int64_t* offsets,
+                               const uint8_t* valid, int64_t n_events);
 
 /* Ingest that runs ahead of the processor.  In the reference the receivers fill the next micro-batch while the job thread
  * works on the current one (Spark Streaming's receiver / job split behind StreamingHost.scala:62-95); over PCIe that overlap

@@ -1334,6 +1334,14 @@ class Flow:
         target, properties (dict), system_properties (dict), executor_id — the per-batch constants of dx_flow_set_batch_info."""
         self.batch_info = info
 
+    def set_event_property(self, key, values, system=False):
+        """Per-event Properties / SystemProperties values of the next batch (CPF:405-421, 628-654): bytes / str, or None."""
+        if not hasattr(self, "event_props"):
+            self.event_props = []
+        name = ("SystemProperties." if system else "Properties.") + key
+        vals = [None if v is None else (v.encode("utf-8") if isinstance(v, str) else bytes(v)) for v in values]
+        self.event_props = [e for e in self.event_props if e[0] != name] + [(name, key, vals)]
+
     def _add_metadata(self, t, batch_ms, now_ms):
         b = self.batch_info or {}
         n = t.n
@@ -1380,6 +1388,19 @@ class Flow:
             const("Properties." + k, v, [k], "m")
         for k, v in (b.get("system_properties") or {}).items():
             const("SystemProperties." + k, v, [k], "m")
+        for name, key, vals in getattr(self, "event_props", []):
+            if len(vals) != n:
+                raise ValueError("event property '%s' was given for %d events, the batch has %d" % (name, len(vals), n))
+            v = np.empty(n, dtype=object)
+            v[:] = [x if x is not None else b"" for x in vals]
+            col = [name, "string", v, np.array([x is not None for x in vals], dtype=bool)]
+            hit = [i for i, c in enumerate(t.cols) if c[0] == name]
+            if hit:
+                t.cols[hit[0]] = col
+            else:
+                t.cols.append(col)
+            t.nest[name] = ([key], "m")
+        self.event_props = []
 
     def add_refdata(self, name, csv_text, delimiter=",", header=True):
         """ReferenceDataHandler / CSVUtil.scala:27-29: every column is a string; empty field -> NULL."""

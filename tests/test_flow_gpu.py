@@ -654,3 +654,49 @@ Rows = SELECT deviceDetails.deviceId, eventTimeStamp FROM DataXProcessedInput_3m
             assert_same_rows(rg.table(name), ro[name], dx)
         rg.release()
     g.close()
+
+
+def test_per_event_transport_properties(dx, ctx):
+    """processEventData / processConsumerRecord put a Properties and a SystemProperties map beside every body (CPF:405-421,
+    628-654).  Here the adapter hands over the per-event values of the keys the flow uses (dx_flow_set_event_property); they are
+    string columns for that batch: selectable as a whole map, by key, groupable across the batches of a window, and NULL where an
+    event does not carry the key.  A per-batch constant of the same key is replaced; the other constants stay."""
+    import dxo_json
+    proj = "CAST(Raw.deviceDetails.eventTime / 1000 AS timestamp) AS eventTimeStamp\nRaw.*\nProperties AS _Properties\nProperties.partition AS part\nSystemProperties.seq AS seq\n"
+    tr = """--DataXQuery--
+ByPart = SELECT part, COUNT(*) AS Count, COUNT(seq) AS WithSeq, MIN(deviceDetails.status) AS Mn FROM DataXProcessedInput_3minutes GROUP BY part
+--DataXQuery--
+P1 = SELECT deviceDetails.deviceId, _Properties.partition AS p, _Properties.source AS src, seq FROM DataXProcessedInput WHERE _Properties.partition = 'p1' AND deviceDetails.status = 1
+--DataXQuery--
+Maps = SELECT deviceDetails.deviceId, _Properties FROM DataXProcessedInput WHERE deviceDetails.deviceId < 40
+"""
+    conf = dx.flowgen.conf_text("props", timestamp_column="eventTimeStamp", watermark="60 second",
+                                windows=[("DataXProcessedInput_3minutes", "3 minutes")], outputs=["Maps"])
+    g, o = both(dx, ctx, conf, SCHEMA1, [proj], tr)
+    n = 3000
+    for b in range(5):
+        T = T0 + b * I
+        data = gen(dx, n, first=b * n, shape=1, n_keys=300, base=T, late=10, future=5)
+        part = [None if (i + b) % 11 == 0 else "p%d" % ((i * 7 + b) % 5) for i in range(n)]
+        seq = [None if i % 3 == 0 else str(b * n + i) for i in range(n)]            # high-cardinality: every value new
+        props = {"partition": "constant-that-is-replaced", "source": "hub-%d" % b}
+        g.set_batch_info(properties=props)
+        o.set_batch_info({"properties": props})
+        for f in (g, o):
+            f.set_event_property("partition", part)
+            f.set_event_property("seq", seq, system=True)
+        rg = g.process_json(data, T, I)
+        ro, mo = o.process(data, T, I)
+        assert same_metrics(rg.metrics, mo)
+        for name in rg.table_names:
+            assert_same_rows(rg.table(name), ro[name], dx)
+        rows = rg.table("Maps").to_json()
+        assert rows == dxo_json.to_json_rows(ro["Maps"])
+        if b >= 2:      # the base table lags by the watermark (CPF:225-227): the first batches' rows show up later
+            assert rows and any(b'"partition":null' in r for r in rows) and all(b'"source":"hub-' in r for r in rows)
+        rg.release()
+    # the count must match the batch
+    g.set_event_property("partition", ["x"] * 5)
+    with pytest.raises(dx.DxError):
+        g.process_json(gen(dx, 100, shape=1), T0 + 5 * I, I)
+    g.close()
