@@ -5,6 +5,7 @@
 #include "dx_decode_host.h"
 #include "dx_flow.h"
 #include "dx_tojson.h"
+#include "dx_inflate.h"
 #include <sys/syscall.h>
 #include <unistd.h>
 #include "dx_rules.h"
@@ -309,6 +310,17 @@ int dx_table_rule_json(const dx_table* h, int col, int rule, const char** json, 
     }
     buf += "}";
     *json = buf.c_str(); *len = (int64_t)buf.size();
+    return DX_OK;
+}
+
+// ---- blob input: gzip members inflated on the device (dx_inflate.cu) --------------------------
+int dx_gunzip_device(dx_ctx* c, const uint8_t* gz, const int64_t* member_offsets, int n_members, int memory_kind, void** out_dev, int64_t* n_bytes) {
+    if (!c || !out_dev || !n_bytes) return DX_ERR_ARG;
+    cudaSetDevice(c->device);
+    DevBufP buf;
+    int rc = dx_gunzip(c, gz, member_offsets, n_members, memory_kind, &buf, n_bytes);
+    if (rc) return rc;
+    *out_dev = buf->p; buf->p = nullptr;          // ownership passes to the caller (dx_dev_free)
     return DX_OK;
 }
 

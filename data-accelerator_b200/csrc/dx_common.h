@@ -71,6 +71,7 @@ struct dx_ctx {
     std::map<std::string, long long> counters;     // work counters (rows visited by K3, rows moved by K4 ...)
     size_t k3p_scatter_smem_configured = 0;
     size_t k5_put_smem_configured = 0;
+    size_t k7_smem_configured = 0;                  // ... k7_inflate ...
     size_t k6_smem_configured = 0;                  // dynamic shared memory k6_json_write is configured for on this device
     size_t k3p_smem_configured = 0;                 // dynamic shared memory k3p_aggregate is configured for on this device
     int set_error(int code, const std::string& msg) { last_error = msg; return code; }

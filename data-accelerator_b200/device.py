@@ -70,6 +70,18 @@ class Context:
             self.check(self.L.dx_copy_d2h(self.h, out.ctypes.data_as(C.c_void_p), C.c_void_p(src), nbytes))
         return out
 
+    def gunzip(self, members):
+        """gzip members (list of bytes, one per blob file) -> (device pointer, n_bytes) of their contents back to back, inflated on
+        the device (dx_gunzip_device); free the pointer with free()."""
+        fn = self.L.dx_gunzip_device
+        fn.restype, fn.argtypes = C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_int64)]
+        blob = np.frombuffer(b"".join(members) + b"\0", dtype=np.uint8)
+        off = np.zeros(len(members) + 1, dtype=np.int64)
+        off[1:] = np.cumsum([len(m) for m in members])
+        p, n = C.c_void_p(), C.c_int64()
+        self.check(fn(self.h, blob.ctypes.data_as(C.c_void_p), off.ctypes.data_as(C.c_void_p), len(members), 0, C.byref(p), C.byref(n)))
+        return p.value, n.value
+
     def gen_events(self, params: GenParams, first, n, want_offsets=False):
         """Synthetic events on the device -> (device_ptr, n_bytes, offsets_ptr|None)."""
         b, nb, off = C.c_void_p(), C.c_int64(), C.c_void_p()

@@ -158,6 +158,16 @@ int dx_table_rule_json(const dx_table* t, int col, int rule, const char** json, 
  * SELECT explode(Rules) ... GROUP BY ruleId): counts[r], r < dx_table_rule_count, computed on the device.       */
 int dx_table_rule_hits(const dx_table* t, int col, int64_t* counts, int n_counts);
 
+/* ---- blob input: gzip on the device ------------------------------------------------------- */
+/* The blob input's files are gzip-compressed JSON lines (datax/input/BlobPointerInput.scala; the lines reach project() through
+ * CPF:463-515).  dx_gunzip_device inflates the n_members gzip members that lie back to back in gz (member m = bytes
+ * [member_offsets[m], member_offsets[m+1]); one member per file, RFC 1952; host memory for memory_kind 0, device for 1) into ONE
+ * device buffer holding their contents in order — ready for dx_flow_process_batch(..., memory_kind = device).  Output offsets
+ * come from the members' ISIZE trailers and the decoded length is checked against them; the trailer's CRC-32 is not verified.
+ * *out_dev is pool memory: release it with dx_dev_free.                                                                  */
+int dx_gunzip_device(dx_ctx* ctx, const uint8_t* gz, const int64_t* member_offsets, int n_members, int memory_kind,
+                     void** out_dev, int64_t* n_bytes);
+
 /* ---- sink hand-off: rows as JSON ---------------------------------------------------------- */
 /* What OutputManager.sink builds before it calls the JSON sinks (datax-host sink/OutputManager.scala:103-118):
  * to_json(struct(<every column whose name does not start with "__DataX_">)) for each row of an output table, produced on the
