@@ -3,17 +3,18 @@
   python tools/bench_gunzip.py [members] [events_per_member] [level]"""
 import gzip, io, json, os, sys, time, zlib
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "oracle"))
+sys.path.insert(0, ROOT)
 import numpy as np
 
 
 def run(dx, ctx, members=512, events=20_000, level=6, reps=5):
     import ctypes as C
-    import dxo
     plain = []
     for k in range(8):      # eight distinct files, repeated: the decoder does not care, the host prep stays short
-        p = dxo.GenParams(20260200 + k, 1_000_000, 100_000, 1_700_000_040_000, 60_000, 60_000, 2, 10, 1, 0)
-        plain.append(dxo.gen_events(p, k * events, events))
+        p = dx.GenParams(20260200 + k, 1_000_000, 100_000, 1_700_000_040_000, 60_000, 60_000, 2, 10, 1, 0)
+        ptr, nb, _ = ctx.gen_events(p, k * events, events)          # the library's own generator; compressed on the host below
+        plain.append(ctx.d2h(ptr, nb).tobytes())
+        ctx.free(ptr)
     gz = []
     for k in range(8):
         buf = io.BytesIO()
