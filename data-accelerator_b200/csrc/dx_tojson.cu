@@ -65,11 +65,30 @@ struct WriteSink {
 // ---------------------------------------------------------------------------------------------------------------------
 // value formatting
 // ---------------------------------------------------------------------------------------------------------------------
-template <class S> static __device__ void emit_u64(S& s, unsigned long long v) {
-    char buf[20]; int n = 0;
-    do { buf[n++] = (char)('0' + (int)(v % 10ull)); v /= 10ull; } while (v);
+// decimal digits of v < 2^32 without a division loop
+static __device__ __forceinline__ int j_ndigits32(uint32_t v) {
+    return v < 10u ? 1 : v < 100u ? 2 : v < 1000u ? 3 : v < 10000u ? 4 : v < 100000u ? 5 : v < 1000000u ? 6 : v < 10000000u ? 7 : v < 100000000u ? 8 : v < 1000000000u ? 9 : 10;
+}
+template <class S> static __device__ __forceinline__ void emit_u32(S& s, uint32_t v) {
+    const int n = j_ndigits32(v);
     if (S::counting) { s.p += (uint32_t)n; return; }
-    while (n) s.put((uint8_t)buf[--n]);
+    char buf[10];
+    for (int i = n - 1; i >= 0; i--) { buf[i] = (char)('0' + v % 10u); v /= 10u; }
+    for (int i = 0; i < n; i++) s.put((uint8_t)buf[i]);
+}
+template <class S> static __device__ __forceinline__ void emit_u32_padded(S& s, uint32_t v, int width) {      // exactly `width` digits
+    if (S::counting) { s.p += (uint32_t)width; return; }
+    char buf[10];
+    for (int i = width - 1; i >= 0; i--) { buf[i] = (char)('0' + v % 10u); v /= 10u; }
+    for (int i = 0; i < width; i++) s.put((uint8_t)buf[i]);
+}
+// 64-bit values go out as up to three 32-bit pieces (32-bit arithmetic is a third of the instructions of 64-bit)
+template <class S> static __device__ void emit_u64(S& s, unsigned long long v) {
+    if (v < 1000000000ull) { emit_u32(s, (uint32_t)v); return; }
+    const unsigned long long hi = v / 1000000000ull; const uint32_t lo = (uint32_t)(v - hi * 1000000000ull);
+    if (hi < 1000000000ull) emit_u32(s, (uint32_t)hi);
+    else { const unsigned long long top = hi / 1000000000ull; emit_u32(s, (uint32_t)top); emit_u32_padded(s, (uint32_t)(hi - top * 1000000000ull), 9); }
+    emit_u32_padded(s, lo, 9);
 }
 template <class S> static __device__ void emit_i64(S& s, long long v) {
     if (v < 0) { s.put('-'); emit_u64(s, 0ull - (unsigned long long)v); } else emit_u64(s, (unsigned long long)v);
@@ -131,8 +150,24 @@ template <class S> static __device__ void emit_f64(S& s, double x, bool quoted) 
     unsigned long long d; int e10;
     j_shortest(mag, &d, &e10);
     char buf[20]; int n = 0;
-    while (d % 10ull == 0ull) { d /= 10ull; e10++; }
-    do { buf[n++] = (char)('0' + (int)(d % 10ull)); d /= 10ull; } while (d);      // buf[n-1] is the first digit
+    {   // d < 10^17: two pieces of at most 9 and 8 digits, trailing zeros dropped and digits produced in 32-bit arithmetic
+        uint32_t hi = (uint32_t)(d / 100000000ull), lo = (uint32_t)(d - (unsigned long long)hi * 100000000ull);
+        if (lo == 0u) { e10 += 8; lo = hi; hi = 0u; }
+        while (lo % 10u == 0u && (hi != 0u || lo != 0u)) {
+            // a trailing zero of the low piece; when the high piece exists the low piece keeps its 8-digit place, so only its value shrinks
+            if (hi) break;
+            lo /= 10u; e10++;
+        }
+        if (hi) {
+            int z = 0; uint32_t t = lo;
+            while (t % 10u == 0u) { t /= 10u; z++; }                           // lo != 0 here
+            e10 += z;
+            for (int i = 0; i < 8 - z; i++) { buf[n++] = (char)('0' + t % 10u); t /= 10u; }
+            do { buf[n++] = (char)('0' + hi % 10u); hi /= 10u; } while (hi);
+        } else {
+            do { buf[n++] = (char)('0' + lo % 10u); lo /= 10u; } while (lo);
+        }
+    }                                                                              // buf[n-1] is the first digit
     const int e = n - 1 + e10;                                                    // scientific exponent
     if (e >= 0 && e <= 6) {
         for (int i = 0; i <= e; i++) s.put(i < n ? (uint8_t)buf[n - 1 - i] : (uint8_t)'0');
