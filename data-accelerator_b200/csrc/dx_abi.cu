@@ -6,6 +6,7 @@
 #include "dx_flow.h"
 #include "dx_tojson.h"
 #include "dx_inflate.h"
+#include "dx_parquet.h"
 #include <sys/syscall.h>
 #include <unistd.h>
 #include "dx_rules.h"
@@ -311,6 +312,115 @@ int dx_table_rule_json(const dx_table* h, int col, int rule, const char** json, 
     buf += "}";
     *json = buf.c_str(); *len = (int64_t)buf.size();
     return DX_OK;
+}
+
+// ---- state tables on disk: Parquet A/B + metadata.info (dx_parquet.cu) -------------------------
+static void pq_err(char* err, int64_t cap, const std::string& m) { if (err && cap > 0) { snprintf(err, (size_t)cap, "%s", m.c_str()); } }
+int dx_parquet_write(const char* path, int n_columns, const char* const* names, const int* types, int64_t n_rows, const void* const* column_data,
+                     const uint8_t* const* column_valid, const uint8_t* const* string_bytes, char* err, int64_t err_cap) {
+    if (!path || n_columns < 1 || !names || !types || n_rows < 0 || !column_data) { pq_err(err, err_cap, "dx_parquet_write: bad arguments"); return DX_ERR_ARG; }
+    std::vector<std::string> nm; std::vector<int> ty;
+    for (int i = 0; i < n_columns; i++) { nm.push_back(names[i]); ty.push_back(types[i]); }
+    std::string e; int rc = dx_parquet_write_impl(path, nm, ty, n_rows, column_data, column_valid, string_bytes, &e);
+    if (rc) pq_err(err, err_cap, e);
+    return rc;
+}
+int dx_parquet_read(const char* path_or_dir, dx_parquet** out, char* err, int64_t err_cap) {
+    if (!path_or_dir || !out) return DX_ERR_ARG;
+    std::string e; int rc = dx_parquet_read_impl(path_or_dir, out, &e);
+    if (rc) pq_err(err, err_cap, e);
+    return rc;
+}
+int64_t dx_parquet_num_rows(const dx_parquet* p) { return p ? p->n_rows : 0; }
+int dx_parquet_num_columns(const dx_parquet* p) { return p ? (int)p->cols.size() : 0; }
+const char* dx_parquet_column_name(const dx_parquet* p, int c) { return p && c >= 0 && c < (int)p->cols.size() ? p->cols[c].name.c_str() : nullptr; }
+int dx_parquet_column_type(const dx_parquet* p, int c) { return p && c >= 0 && c < (int)p->cols.size() ? p->cols[c].type : 0; }
+int dx_parquet_column(const dx_parquet* p, int c, const void** data, const uint8_t** valid, const uint8_t** string_bytes) {
+    if (!p || c < 0 || c >= (int)p->cols.size()) return DX_ERR_ARG;
+    const dx_parquet::Col& col = p->cols[c];
+    if (data) *data = col.type == DX_T_STR ? (const void*)col.offsets.data() : (const void*)col.values.data();
+    if (valid) *valid = col.valid.data();
+    if (string_bytes) *string_bytes = col.type == DX_T_STR ? reinterpret_cast<const uint8_t*>(col.bytes.data()) : nullptr;
+    return DX_OK;
+}
+void dx_parquet_release(dx_parquet* p) { delete p; }
+
+int dx_flow_state_save(dx_flow* f, const char* table, const char* location) {
+    if (!f || !table || !location) return DX_ERR_ARG;
+    dx_ctx* c = f->ctx;
+    cudaSetDevice(c->device);
+    auto it = f->state_tables.find(table);
+    if (it == f->state_tables.end()) return c->set_error(DX_ERR_ARG, std::string("no state table '") + table + "'");
+    StateTable& st = it->second;
+    const DxTableP t = st.phys[st.active];
+    const std::string loc = std::string(location).substr(0, std::string(location).find_last_not_of('/') + 1);
+    const std::string active = st.active ? "B" : "A", standby = st.active ? "A" : "B";
+    std::vector<std::string> names; std::vector<int> types;
+    for (auto& kv : st.schema) { names.push_back(kv.first); types.push_back(kv.second); }
+    const int64_t n = t ? t->n_rows : 0;
+    // the columns on the host, strings as offsets + bytes
+    std::vector<std::vector<int64_t>> vals(names.size()); std::vector<std::vector<uint8_t>> valid(names.size()); std::vector<std::string> bytes(names.size());
+    for (size_t k = 0; k < names.size(); k++) {
+        valid[k].assign((size_t)(n > 0 ? n : 1), 0);
+        if (types[k] == DX_T_STR) {
+            vals[k].assign((size_t)n + 1, 0);
+            if (n > 0) {
+                if ((size_t)k >= t->cols.size()) return c->set_error(DX_ERR_STATE, "state table has fewer columns than its schema");
+                std::vector<int32_t> codes((size_t)n);
+                dx_table* h = dx_wrap_table(t);
+                int rc = dx_table_column_to_host(h, (int)k, codes.data(), valid[k].data());
+                dx_table_release(h);
+                if (rc) return rc;
+                const DxColumn& col = t->cols[k];
+                if (col.dict) { rc = col.dict->sync_to_host(); if (rc) return rc; }
+                for (int64_t r = 0; r < n; r++) {
+                    if (valid[k][(size_t)r] && col.dict && codes[(size_t)r] >= 0 && codes[(size_t)r] < (int32_t)col.dict->host_strings.size()) bytes[k] += col.dict->host_strings[(size_t)codes[(size_t)r]];
+                    else if (valid[k][(size_t)r] && !col.dict) bytes[k] += col.const_s;
+                    vals[k][(size_t)r + 1] = (int64_t)bytes[k].size();
+                }
+            }
+        } else {
+            vals[k].assign((size_t)(n > 0 ? n : 1), 0);
+            if (n > 0) { dx_table* h = dx_wrap_table(t); int rc = dx_table_column_to_host(h, (int)k, vals[k].data(), valid[k].data()); dx_table_release(h); if (rc) return rc; }
+        }
+    }
+    std::vector<const void*> dp; std::vector<const uint8_t*> vp, sp;
+    for (size_t k = 0; k < names.size(); k++) { dp.push_back(vals[k].data()); vp.push_back(valid[k].data()); sp.push_back(reinterpret_cast<const uint8_t*>(bytes[k].data())); }
+    std::string e;
+    dx_clear_directory_files(loc + "/" + active);
+    int rc = dx_parquet_write_impl(loc + "/" + active + "/part-00000.parquet", names, types, n, dp.data(), vp.data(), sp.data(), &e);
+    if (rc) return c->set_error(rc, "state table '" + st.name + "': " + e);
+    rc = dx_state_metadata_write(loc, active, standby, &e);
+    if (rc) return c->set_error(rc, "state table '" + st.name + "': " + e);
+    return DX_OK;
+}
+int dx_flow_state_load(dx_flow* f, const char* table, const char* location) {
+    if (!f || !table || !location) return DX_ERR_ARG;
+    dx_ctx* c = f->ctx;
+    auto it = f->state_tables.find(table);
+    if (it == f->state_tables.end()) return c->set_error(DX_ERR_ARG, std::string("no state table '") + table + "'");
+    StateTable& st = it->second;
+    const std::string loc = std::string(location).substr(0, std::string(location).find_last_not_of('/') + 1);
+    std::string active, standby, e;
+    int rc = dx_state_metadata_read(loc, &active, &standby, &e);
+    if (rc) return c->set_error(rc, e);
+    if (active != "A" && active != "B") return c->set_error(DX_ERR_PARSE, "metadata.info of '" + st.name + "': active=" + active);
+    dx_parquet* pq = nullptr;
+    rc = dx_parquet_read_impl(loc + "/" + active, &pq, &e);
+    if (rc && e.find("cannot open") == std::string::npos && !e.empty()) return c->set_error(rc, "state table '" + st.name + "': " + e);
+    std::unique_ptr<dx_parquet> hold(pq);
+    if (!pq || pq->cols.empty()) { st.active = active == "B" ? 1 : 0; return DX_OK; }        // CREATE TABLE IF NOT EXISTS over an empty location: an empty table
+    if (pq->cols.size() != st.schema.size()) return c->set_error(DX_ERR_ARG, "state table '" + st.name + "': the files have " + std::to_string(pq->cols.size()) + " columns, the schema " + std::to_string(st.schema.size()));
+    std::vector<const void*> dp; std::vector<const uint8_t*> vp, sp;
+    for (size_t k = 0; k < pq->cols.size(); k++) {
+        const dx_parquet::Col& col = pq->cols[k];
+        const int want = st.schema[k].second;
+        const bool ok = col.type == want || (want == DX_T_I64 && col.type == DX_T_BOOL) || (want == DX_T_BOOL && col.type == DX_T_I64);
+        if (!ok) return c->set_error(DX_ERR_ARG, "state table '" + st.name + "': column '" + st.schema[k].first + "' has another type in the files");
+        dp.push_back(col.type == DX_T_STR ? (const void*)col.offsets.data() : (const void*)col.values.data());
+        vp.push_back(col.valid.data()); sp.push_back(reinterpret_cast<const uint8_t*>(col.bytes.data()));
+    }
+    return dx_flow_state_import(f, table, pq->n_rows, (int)pq->cols.size(), dp.data(), vp.data(), sp.data(), active == "B" ? 1 : 0);
 }
 
 // ---- blob input: gzip members inflated on the device (dx_inflate.cu) --------------------------

@@ -365,6 +365,20 @@ class CommonProcessor:
         arr = lambda xs: (C.c_void_p * k)(*[C.c_void_p(x) if x else None for x in xs])
         self.ctx.check(fn(self.h, name.encode(), n, k, arr(data), arr(valid), arr(sbytes), 1 if active == "B" else 0))
 
+    def save_state(self, name, location):
+        """The table's active copy as Parquet under <location>/<A|B>/ plus <location>/metadata.info (dx_flow_state_save: what
+        StateTableHandler's INSERT OVERWRITE + flip + persist leave behind, StateTableHandler.scala:99-125)."""
+        fn = self.L.dx_flow_state_save
+        fn.restype, fn.argtypes = C.c_int, [C.c_void_p, C.c_char_p, C.c_char_p]
+        self.ctx.check(fn(self.h, name.encode(), str(location).encode()))
+
+    def load_state(self, name, location):
+        """Restart from <location> (dx_flow_state_load): metadata.info says which copy is active; its part files — written by
+        save_state or by Spark 2.4 — become the flow's table."""
+        fn = self.L.dx_flow_state_load
+        fn.restype, fn.argtypes = C.c_int, [C.c_void_p, C.c_char_p, C.c_char_p]
+        self.ctx.check(fn(self.h, name.encode(), str(location).encode()))
+
     def state_table(self, name):
         t, b = C.c_void_p(), C.c_int()
         self.ctx.check(self.L.dx_flow_state_export(self.h, name.encode(), C.byref(t), C.byref(b)))

@@ -158,6 +158,32 @@ int dx_table_rule_json(const dx_table* t, int col, int rule, const char** json, 
  * SELECT explode(Rules) ... GROUP BY ruleId): counts[r], r < dx_table_rule_count, computed on the device.       */
 int dx_table_rule_hits(const dx_table* t, int col, int64_t* counts, int n_counts);
 
+/* ---- state tables on disk ------------------------------------------------------------------- */
+/* StateTableHandler keeps every accumulator table as two Hive tables `STORED AS PARQUET LOCATION '<location>/A/'` and `.../B/'` plus
+ * `<location>/metadata.info` holding `active=A|B` and `standby=B|A` (datax/handler/StateTableHandler.scala:26-52, 70-83); a batch
+ * INSERT-OVERWRITEs the standby copy, flips and persists the metadata (:99-125).  dx_flow_state_save writes the table's ACTIVE copy
+ * as one Parquet file into `<location>/<active>/` (the directory's other files are removed, as INSERT OVERWRITE does) and the
+ * metadata file; dx_flow_state_load reads metadata.info and every part file of the active directory — files written by
+ * dx_flow_state_save or by Spark 2.4 (v1 data pages, PLAIN or dictionary encoded, UNCOMPRESSED or SNAPPY, INT96 timestamps) — into
+ * the flow's table; an absent location is an empty table with active=A, as CREATE TABLE IF NOT EXISTS gives.  Local paths only:
+ * moving the files to and from HDFS / blob storage stays with the JVM side.                                             */
+struct dx_flow;
+int dx_flow_state_save(struct dx_flow* flow, const char* table, const char* location);
+int dx_flow_state_load(struct dx_flow* flow, const char* table, const char* location);
+/* The same file format on host columns (column_data: int64 / double bits / boolean 0|1 / timestamp microseconds per row; strings:
+ * n_rows + 1 int64 offsets into string_bytes; column_valid: one byte per row or NULL = no NULLs).  No GPU is involved.      */
+typedef struct dx_parquet dx_parquet;
+int dx_parquet_write(const char* path, int n_columns, const char* const* names, const int* types, int64_t n_rows,
+                     const void* const* column_data, const uint8_t* const* column_valid, const uint8_t* const* string_bytes,
+                     char* err, int64_t err_cap);
+int dx_parquet_read(const char* path_or_dir, dx_parquet** out, char* err, int64_t err_cap);
+int64_t dx_parquet_num_rows(const dx_parquet* p);
+int dx_parquet_num_columns(const dx_parquet* p);
+const char* dx_parquet_column_name(const dx_parquet* p, int column);
+int dx_parquet_column_type(const dx_parquet* p, int column);
+int dx_parquet_column(const dx_parquet* p, int column, const void** data, const uint8_t** valid, const uint8_t** string_bytes);
+void dx_parquet_release(dx_parquet* p);
+
 /* ---- blob input: gzip on the device ------------------------------------------------------- */
 /* The blob input's files are gzip-compressed JSON lines (datax/input/BlobPointerInput.scala; the lines reach project() through
  * CPF:463-515).  dx_gunzip_device inflates the n_members gzip members that lie back to back in gz (member m = bytes

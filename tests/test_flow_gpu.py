@@ -700,3 +700,55 @@ Maps = SELECT deviceDetails.deviceId, _Properties FROM DataXProcessedInput WHERE
     with pytest.raises(dx.DxError):
         g.process_json(gen(dx, 100, shape=1), T0 + 5 * I, I)
     g.close()
+
+
+def test_restart_from_parquet_state_on_disk(dx, ctx, tmp_path):
+    """Restart through the state table's on-disk form (StateTableHandler.scala:26-52, 70-125): the stopped processor leaves
+    <location>/<A|B>/part-*.parquet + metadata.info (dx_flow_state_save), a new one loads them (dx_flow_state_load) and continues
+    exactly like one that never stopped.  The files are plain Parquet: pyarrow (standing in for Spark's reader) sees the same
+    rows, and a copy re-written by pyarrow the way Spark 2.4 writes (snappy, dictionary pages, INT96) loads just as well."""
+    import pyarrow.parquet as pq
+    tr = """--DataXQuery--
+acc_new = SELECT deviceDetails.deviceId, deviceDetails.deviceType, eventTimeStamp AS EventTime, deviceDetails.status AS Reading
+    FROM DataXProcessedInput WHERE deviceDetails.status = 1
+    UNION ALL SELECT deviceId, deviceType, EventTime, Reading FROM acc WHERE unix_timestamp() - to_unix_timestamp(EventTime, 'yyyy-MM-dd') < 150
+--DataXQuery--
+acc = SELECT deviceId, deviceType, EventTime, Reading FROM acc_new
+--DataXQuery--
+perType = SELECT deviceType, COUNT(*) AS Cnt, MAX(EventTime) AS Last FROM acc GROUP BY deviceType
+"""
+    conf = dx.flowgen.conf_text("restart", state_tables=[("acc", "deviceId long, deviceType string, EventTime Timestamp, Reading long")])
+    g, o = both(dx, ctx, conf, SCHEMA1, [PROJ_TS], tr)
+    batch = lambda b: gen(dx, 2000, first=b * 2000, shape=1, n_keys=100, base=T0 + b * I)
+    for b in range(3):
+        check_batch(dx, g, o, batch(b), T0 + b * I, now_ms=T0 + b * I + 5)
+    loc = tmp_path / "state" / "acc"
+    g.save_state("acc", loc)
+    _, which = g.state_table("acc")
+    g.close()
+    assert (loc / "metadata.info").read_text() == "active=%s\nstandby=%s" % (which, "A" if which == "B" else "B")
+    seen = pq.read_table(str(loc / which))
+    want = o.state["acc"]["tables"][which]
+    assert seen.num_rows == want.n and seen.column_names == ["deviceId", "deviceType", "EventTime", "Reading"]
+    assert sorted(seen.column("deviceId").to_pylist()) == sorted(int(x) for x in want.cols[0][2])
+    # a Spark-style rewrite of the same rows in two part files
+    for k, part in enumerate([seen.slice(0, seen.num_rows // 2), seen.slice(seen.num_rows // 2)]):
+        pq.write_table(part, str(loc / which / ("part-%05d-spark.snappy.parquet" % k)), compression="snappy", use_dictionary=True,
+                       use_deprecated_int96_timestamps=True, flavor="spark", data_page_version="1.0", row_group_size=300)
+    (loc / which / "part-00000.parquet").unlink()
+    g2 = dx.CommonProcessorFactory.createProcessor(ctx, conf, SCHEMA1, [PROJ_TS], tr)
+    g2.load_state("acc", loc)
+    t2, which2 = g2.state_table("acc")
+    assert which2 == which
+    assert_same_rows(t2, want, dx)
+    for b in range(3, 6):
+        check_batch(dx, g2, o, batch(b), T0 + b * I, now_ms=T0 + b * I + 5)
+        t2, which2 = g2.state_table("acc")
+        assert which2 == o.state["acc"]["active"]
+        assert_same_rows(t2, o.state["acc"]["tables"][which2], dx)
+    # a location nobody has written to: an empty table, active = A
+    g3 = dx.CommonProcessorFactory.createProcessor(ctx, conf, SCHEMA1, [PROJ_TS], tr)
+    g3.load_state("acc", tmp_path / "nowhere")
+    t3, which3 = g3.state_table("acc")
+    assert which3 == "A"
+    g2.close(); g3.close()
