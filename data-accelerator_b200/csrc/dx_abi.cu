@@ -7,6 +7,7 @@
 #include "dx_tojson.h"
 #include "dx_inflate.h"
 #include "dx_parquet.h"
+#include "dx_codegen.h"
 #include <sys/syscall.h>
 #include <unistd.h>
 #include "dx_rules.h"
@@ -311,6 +312,26 @@ int dx_table_rule_json(const dx_table* h, int col, int rule, const char** json, 
     }
     buf += "}";
     *json = buf.c_str(); *len = (int64_t)buf.size();
+    return DX_OK;
+}
+
+// ---- design time: rules + user code -> transform text (dx_codegen.cu) ---------------------------
+int dx_codegen_rules(const char* user_code, const char* rules_json, const char* query_templates_xml, const char* output_templates_xml,
+                     const char* product_id, char* code_out, int64_t code_cap, char* info_out, int64_t info_cap) {
+    if (!user_code || !rules_json || !query_templates_xml || !output_templates_xml || !code_out || code_cap < 1) return DX_ERR_ARG;
+    dx_codegen_result res; std::string err;
+    int rc = dx_codegen_impl(user_code, rules_json, query_templates_xml, output_templates_xml, product_id ? product_id : "", &res, &err);
+    if (rc) { snprintf(code_out, (size_t)code_cap, "%s", err.c_str()); return rc; }
+    if ((int64_t)res.code.size() + 1 > code_cap) { snprintf(code_out, (size_t)code_cap, "generated code needs %zu bytes", res.code.size() + 1); return DX_ERR_CAPACITY; }
+    memcpy(code_out, res.code.c_str(), res.code.size() + 1);
+    if (info_out && info_cap > 0) {
+        std::string info;
+        for (auto& o : res.outputs) info += "output\t" + o.first + "\t" + o.second + "\n";
+        for (auto& t : res.tables) info += "table\t" + t.first + "\t" + t.second + "\n";
+        for (auto& w : res.windows) info += "window\t" + w.first + "\t" + w.second + "\n";
+        for (auto& m : res.metrics) info += "metric\t" + m + "\n";
+        snprintf(info_out, (size_t)info_cap, "%s", info.c_str());
+    }
     return DX_OK;
 }
 

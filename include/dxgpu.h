@@ -158,6 +158,17 @@ int dx_table_rule_json(const dx_table* t, int col, int rule, const char** json, 
  * SELECT explode(Rules) ... GROUP BY ruleId): counts[r], r < dx_table_rule_count, computed on the device.       */
 int dx_table_rule_hits(const dx_table* t, int col, int64_t* counts, int n_counts);
 
+/* ---- design time: the rules / flow code generator ------------------------------------------ */
+/* Engine.GenerateCode(code, rules, queryTemplates, outputTemplates, productId) of DataX.Flow.CodegenRules (Engine.cs:32-107): the
+ * user's code (ProcessRules / ProcessAlerts / ProcessAggregateRules / ProcessAggregateAlerts / CreateMetric calls, OUTPUT ... TO,
+ * CREATE TABLE, WITH UPSERT, TIMEWINDOW) + the rule definitions (JSON) + the two template files -> the transform text
+ * (`--DataXQuery--` statements, RulesCode.Code) that dx_flow_create takes, byte for byte what the reference's generator emits
+ * (its 18 test expectations are this repo's tests).  info_out (optional) receives one line per side result:
+ * "output<TAB>table<TAB>sink", "table<TAB>name<TAB>schema" (CREATE TABLE), "window<TAB>view<TAB>duration", "metric<TAB>table".
+ * On failure code_out holds the message.  No GPU is involved.                                                              */
+int dx_codegen_rules(const char* user_code, const char* rules_json, const char* query_templates_xml, const char* output_templates_xml,
+                     const char* product_id, char* code_out, int64_t code_cap, char* info_out, int64_t info_cap);
+
 /* ---- state tables on disk ------------------------------------------------------------------- */
 /* StateTableHandler keeps every accumulator table as two Hive tables `STORED AS PARQUET LOCATION '<location>/A/'` and `.../B/'` plus
  * `<location>/metadata.info` holding `active=A|B` and `standby=B|A` (datax/handler/StateTableHandler.scala:26-52, 70-83); a batch
