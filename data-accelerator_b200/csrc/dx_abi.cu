@@ -316,11 +316,7 @@ int dx_table_rule_json(const dx_table* h, int col, int rule, const char** json, 
 }
 
 // ---- design time: rules + user code -> transform text (dx_codegen.cu) ---------------------------
-int dx_codegen_rules(const char* user_code, const char* rules_json, const char* query_templates_xml, const char* output_templates_xml,
-                     const char* product_id, char* code_out, int64_t code_cap, char* info_out, int64_t info_cap) {
-    if (!user_code || !rules_json || !query_templates_xml || !output_templates_xml || !code_out || code_cap < 1) return DX_ERR_ARG;
-    dx_codegen_result res; std::string err;
-    int rc = dx_codegen_impl(user_code, rules_json, query_templates_xml, output_templates_xml, product_id ? product_id : "", &res, &err);
+static int codegen_out(int rc, const dx_codegen_result& res, const std::string& err, char* code_out, int64_t code_cap, char* info_out, int64_t info_cap) {
     if (rc) { snprintf(code_out, (size_t)code_cap, "%s", err.c_str()); return rc; }
     if ((int64_t)res.code.size() + 1 > code_cap) { snprintf(code_out, (size_t)code_cap, "generated code needs %zu bytes", res.code.size() + 1); return DX_ERR_CAPACITY; }
     memcpy(code_out, res.code.c_str(), res.code.size() + 1);
@@ -333,6 +329,20 @@ int dx_codegen_rules(const char* user_code, const char* rules_json, const char* 
         snprintf(info_out, (size_t)info_cap, "%s", info.c_str());
     }
     return DX_OK;
+}
+int dx_codegen_rules(const char* user_code, const char* rules_json, const char* query_templates_xml, const char* output_templates_xml,
+                     const char* product_id, char* code_out, int64_t code_cap, char* info_out, int64_t info_cap) {
+    if (!user_code || !rules_json || !query_templates_xml || !output_templates_xml || !code_out || code_cap < 1) return DX_ERR_ARG;
+    dx_codegen_result res; std::string err;
+    int rc = dx_codegen_impl(user_code, rules_json, query_templates_xml, output_templates_xml, product_id ? product_id : "", &res, &err);
+    return codegen_out(rc, res, err, code_out, code_cap, info_out, info_cap);
+}
+int dx_codegen_flow(const char* flow_json, const char* query_templates_xml, const char* output_templates_xml, char* code_out, int64_t code_cap,
+                    char* info_out, int64_t info_cap) {
+    if (!flow_json || !query_templates_xml || !output_templates_xml || !code_out || code_cap < 1) return DX_ERR_ARG;
+    dx_codegen_result res; std::string err;
+    int rc = dx_codegen_flow_impl(flow_json, query_templates_xml, output_templates_xml, &res, &err);
+    return codegen_out(rc, res, err, code_out, code_cap, info_out, info_cap);
 }
 
 // ---- state tables on disk: Parquet A/B + metadata.info (dx_parquet.cu) -------------------------

@@ -417,6 +417,50 @@ struct Engine {
 };
 }  // namespace
 
+// S450_PrepareTransformFile.Process (DataX.Config/ConfigGeneration/Processor/S450_PrepareTransformFile.cs:48-64) +
+// RuleDefinitionGenerator.GenerateRuleDefinitions (DataX.Config/InternalService/RuleDefinitionGenerator.cs:15-33): the flow's GUI
+// JSON -> user code (gui.process.queries joined by '\n') and rule definitions (gui.rules[].properties with $productId = the flow's
+// name), then the generator.  The stored form of a flow writes "_S_" for a leading "$" of a property name
+// (LocalDesignTimeStorage.cs:169-174, CosmosDBUtility.cs:108-116); both spellings are read.  A rule without a $ruleId gets a GUID in
+// the reference; here it gets "<flow name>-rule-<position>" so that the output is reproducible.
+static void json_write(const JVal& v, S* o) {
+    switch (v.kind) {
+    case JVal::NUL: *o += "null"; break;
+    case JVal::BOOL: *o += v.b ? "true" : "false"; break;
+    case JVal::NUM: { char b[64]; if (v.num == (double)(long long)v.num) snprintf(b, sizeof b, "%lld", (long long)v.num); else snprintf(b, sizeof b, "%.17g", v.num); *o += b; break; }
+    case JVal::STR: { *o += '"'; for (unsigned char c : v.str) { if (c == '"' || c == '\\') { *o += '\\'; *o += (char)c; } else if (c < 0x20) { char b[8]; snprintf(b, sizeof b, "\\u%04x", c); *o += b; } else *o += (char)c; } *o += '"'; break; }
+    case JVal::ARR: { *o += '['; for (size_t i = 0; i < v.arr.size(); i++) { if (i) *o += ','; json_write(v.arr[i], o); } *o += ']'; break; }
+    case JVal::OBJ: { *o += '{'; for (size_t i = 0; i < v.obj.size(); i++) { if (i) *o += ','; JVal k; k.kind = JVal::STR; k.str = v.obj[i].first; json_write(k, o); *o += ':'; json_write(v.obj[i].second, o); } *o += '}'; break; }
+    }
+}
+int dx_codegen_flow_impl(const std::string& flow_json, const std::string& query_xml, const std::string& output_xml, dx_codegen_result* res, std::string* err) {
+    try {
+        S text = flow_json.compare(0, 3, "\xEF\xBB\xBF") == 0 ? flow_json.substr(3) : flow_json;
+        text = replace_all(text, "\"_S_", "\"$");
+        JVal root = dx_parse_json(strip_json_comments(text));
+        const JVal* gui = root.get("gui"); if (!gui) gui = &root;
+        const JVal* name = gui->get("name");
+        if (!name || name->kind != JVal::STR) throw std::runtime_error("flow JSON: no name");
+        S code;
+        if (const JVal* pr = gui->get("process")) if (const JVal* q = pr->get("queries")) for (size_t i = 0; i < q->arr.size(); i++) code += (i ? "\n" : "") + q->arr[i].str;
+        JVal defs; defs.kind = JVal::ARR;
+        if (const JVal* rules = gui->get("rules")) for (size_t i = 0; i < rules->arr.size(); i++) {
+            const JVal* props = rules->arr[i].get("properties"); if (!props) continue;
+            JVal r = *props; bool have_id = false, have_product = false;
+            for (auto& kv : r.obj) {
+                if (kv.first == "$ruleId") { have_id = true; if (kv.second.kind != JVal::STR || kv.second.str.empty()) { kv.second.kind = JVal::STR; kv.second.str = name->str + "-rule-" + std::to_string(i + 1); } }
+                if (kv.first == "$productId") { have_product = true; kv.second.kind = JVal::STR; kv.second.str = name->str; }
+            }
+            JVal sv; sv.kind = JVal::STR;
+            if (!have_id) { sv.str = name->str + "-rule-" + std::to_string(i + 1); r.obj.push_back({"$ruleId", sv}); }
+            if (!have_product) { sv.str = name->str; r.obj.push_back({"$productId", sv}); }
+            defs.arr.push_back(r);
+        }
+        S rules_json; json_write(defs, &rules_json);
+        return dx_codegen_impl(code, rules_json, query_xml, output_xml, name->str, res, err);
+    } catch (std::exception& e) { *err = e.what(); return DX_ERR_PARSE; }
+}
+
 int dx_codegen_impl(const std::string& user_code, const std::string& rules_json, const std::string& query_xml, const std::string& output_xml,
                     const std::string& product, dx_codegen_result* res, std::string* err) {
     try {

@@ -12,3 +12,4 @@ struct dx_codegen_result {
 };
 int dx_codegen_impl(const std::string& user_code, const std::string& rules_json, const std::string& query_xml, const std::string& output_xml,
                     const std::string& product, dx_codegen_result* res, std::string* err);
+int dx_codegen_flow_impl(const std::string& flow_json, const std::string& query_xml, const std::string& output_xml, dx_codegen_result* res, std::string* err);

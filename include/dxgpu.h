@@ -168,6 +168,11 @@ int dx_table_rule_hits(const dx_table* t, int col, int64_t* counts, int n_counts
  * On failure code_out holds the message.  No GPU is involved.                                                              */
 int dx_codegen_rules(const char* user_code, const char* rules_json, const char* query_templates_xml, const char* output_templates_xml,
                      const char* product_id, char* code_out, int64_t code_cap, char* info_out, int64_t info_cap);
+/* The same from a flow's GUI JSON, as the config generation does it (S450_PrepareTransformFile.cs:48-64: gui.process.queries joined by
+ * newlines; RuleDefinitionGenerator.cs:15-33: gui.rules[].properties with $productId = the flow's name; property names stored as "_S_x"
+ * are read as "$x").  A rule without a $ruleId gets "<flow name>-rule-<position>" (the reference draws a GUID).                 */
+int dx_codegen_flow(const char* flow_json, const char* query_templates_xml, const char* output_templates_xml, char* code_out,
+                    int64_t code_cap, char* info_out, int64_t info_cap);
 
 /* ---- state tables on disk ------------------------------------------------------------------- */
 /* StateTableHandler keeps every accumulator table as two Hive tables `STORED AS PARQUET LOCATION '<location>/A/'` and `.../B/'` plus

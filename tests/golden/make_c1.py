@@ -62,3 +62,6 @@ datax.job.process.jar.udf.whoOpened.path=datax-udf-samples.jar
 open(os.path.join(OUT, "HomeAutomationLocal.conf"), "w").write(conf)
 open(os.path.join(OUT, "devices.csv"), "w").write(open(CSV, encoding="utf-8-sig").read())
 print(open(os.path.join(OUT, "HomeAutomationLocal-combined.txt")).read()[:600])
+# the flow's GUI section as it is stored: the input of the restated code generator (dx_codegen_flow), which makes the transform above
+# from it without the hand-applied rewrites of this script
+json.dump({"gui": gui}, open(os.path.join(OUT, "flow_gui.json"), "w"), indent=1)

@@ -55,3 +55,31 @@ def test_home_automation_local_flow(dx, ctx):
     # the sample flow does produce alerts on this data
     assert ro["DoorUnlockedSimpleAlert"].n > 0 and ro["CLOSEAlert"].n == 1
     g.close()
+
+
+def test_home_automation_flow_from_its_gui_json(dx, ctx):
+    """The same flow with its transform GENERATED from the flow's GUI JSON by the restated code generator (dx_codegen_flow:
+    S450_PrepareTransformFile + RuleDefinitionGenerator + Engine.GenerateCode with the default templates) instead of the
+    hand-derived text: the processor and the oracle both take the generated transform and must agree on every table."""
+    from test_codegen_restatement import flow_transform
+    code, _ = flow_transform()
+    rd = lambda f: open(os.path.join(C1, f), encoding="utf-8-sig").read()
+    g = dx.CommonProcessorFactory.createProcessor(ctx, rd("HomeAutomationLocal.conf"), rd("inputschema.json"), [rd("projection.txt")], code)
+    g.add_refdata("myDevicesRefData", rd("devices.csv"))
+    g.register_udf("whoOpened", who_opened)
+    o = dxo_flow.Flow(rd("HomeAutomationLocal.conf"), rd("inputschema.json"), [rd("projection.txt")], code)
+    o.add_refdata("myDevicesRefData", rd("devices.csv"))
+    dxo_flow.UDFS["WHOOPENED"] = who_opened
+    rng = random.Random(2)
+    for b in range(30):
+        T = T0 + b * I
+        now = T + 1500 + b
+        data = events(rng, 120, now)
+        rg = g.process_json(data, T, I, now_ms=now)
+        ro, mo = o.process(data, T, I, now_ms=now)
+        assert same_metrics(rg.metrics, mo)
+        assert {"DeviceWindowedInput", "DeviceInfoTimeWindow", "Rules", "CLOSEAlert"} <= set(rg.table_names)
+        for name in rg.table_names:
+            assert_same_rows(rg.table(name), ro[name], dx)
+        rg.release()
+    g.close()

@@ -56,3 +56,61 @@ def test_side_results_outputs_tables_windows():
     assert ["table", "EventCount", "Count: INT"] in lines
     assert ["window", "DataXProcessedInput_50seconds", "50 seconds"] in lines and ["window", "DataXProcessedInput_40seconds", "40 seconds"] in lines
     assert any(l[0] == "output" and l[2] == "Metrics" for l in lines) and any(l[0] == "metric" for l in lines)
+
+
+def flow_transform():
+    from importlib import import_module
+    L = import_module("data-accelerator_b200._native").lib()
+    fn = L.dx_codegen_flow
+    fn.restype, fn.argtypes = C.c_int, [C.c_char_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_int64, C.c_char_p, C.c_int64]
+    c1 = os.path.join(HERE, "golden", "c1_homeautomation")
+    out, info = C.create_string_buffer(1 << 20), C.create_string_buffer(1 << 16)
+    rc = fn(open(os.path.join(c1, "flow_gui.json"), "rb").read(), read("defaultQueryTemplate.xml").encode(), read("defaultOutputTemplate.xml").encode(),
+            out, len(out), info, len(info))
+    assert rc == 0, out.value.decode()
+    return out.value.decode(), info.value.decode()
+
+
+def test_home_automation_flow_json_to_transform():
+    """The local sample flow's GUI JSON (DeploymentLocal/sample/HomeAutomationLocal.json) through the config generation's path
+    (S450_PrepareTransformFile + RuleDefinitionGenerator + the generator with its default templates): the time window, the outputs
+    and the statements come out, and the oracle computes from the generated transform exactly what it computes from the transform
+    this repository used to derive by hand (tests/golden/make_c1.py) — rule ids aside, which the reference draws at random."""
+    import json as _json
+    import random
+    import numpy as np
+    import dxo_flow
+    code, info = flow_transform()
+    lines = [l.split("\t") for l in info.splitlines()]
+    assert ["window", "DataXProcessedInput_5minutes", "5 minutes"] in lines
+    assert ["output", "CLOSEAlert", "Metrics"] in lines and ["metric", "CLOSEAlert"] in lines
+    assert "TIMEWINDOW" not in code and "ProcessRules" not in code and "OUTPUT" not in code and ";" not in code
+    c1 = os.path.join(HERE, "golden", "c1_homeautomation")
+    rd = lambda f: open(os.path.join(c1, f), encoding="utf-8-sig").read()
+    flows = [dxo_flow.Flow(rd("HomeAutomationLocal.conf"), rd("inputschema.json"), [rd("projection.txt")], t) for t in (code, rd("HomeAutomationLocal-combined.txt"))]
+    for f in flows:
+        f.add_refdata("myDevicesRefData", rd("devices.csv"))
+    dxo_flow.UDFS["WHOOPENED"] = lambda s: "hello, " + str(s if s is not None else "null")
+    rng = random.Random(4)
+    T0, I = 1_700_000_040_000, 60_000
+    for b in range(8):
+        T = T0 + b * I
+        now = T + 1500
+        ev = []
+        for _ in range(120):
+            ev.append(_json.dumps({"deviceDetails": {"deviceId": rng.choice([1, 2, 3, 4, 5, 6]), "deviceType": rng.choice(["DoorLock", "WindowLock", "Heating"]),
+                                                     "eventTime": now - rng.randrange(1000), "homeId": rng.choice([32, 150, 25, 81]), "status": rng.choice([0, 1])}}, separators=(",", ":")))
+        data = ("\n".join(ev) + "\n").encode()
+        (ra, _), (rb, _) = [f.process(data, T, I, now_ms=now) for f in flows]
+        assert set(ra) == set(rb)
+        for name in ra:
+            a, bt = ra[name], rb[name]
+            assert a.n == bt.n and a.names() == bt.names(), name
+            for ca, cb in zip(a.cols, bt.cols):
+                if ca[0].lower() == "ruleid":
+                    continue                      # "HomeAutomationLocal-rule-1" here, "R1" in the hand-derived text
+                if ca[1] == "rules":
+                    assert (np.asarray(ca[2]) == np.asarray(cb[2])).all(), name
+                else:
+                    assert sorted(map(repr, zip(ca[2].tolist() if ca[2] is not None else [None] * a.n, ca[3].tolist()))) == \
+                           sorted(map(repr, zip(cb[2].tolist() if cb[2] is not None else [None] * bt.n, cb[3].tolist()))), (name, ca[0])
