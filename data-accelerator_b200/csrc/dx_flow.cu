@@ -217,18 +217,32 @@ __global__ void k_minmax_i64(const long long* v, const void* vmask, int vwidth, 
         if (cnt) { atomicMin(&out[0], mn); atomicMax(&out[1], mx); atomicAdd(reinterpret_cast<unsigned long long*>(&out[2]), (unsigned long long)cnt); }
     }
 }
-__global__ void k_finalize(int mode, const unsigned long long* a, const unsigned long long* cnt, const unsigned long long* keynull, int keybit,
-                           long long n, void* out, int out_width, uint32_t* vmask32, int vbit) {
-    // mode 0: key copy (valid = !keynull bit); 1: accumulator copy, always valid; 2: accumulator copy, valid iff cnt>0;
-    // 3: average = sum_f / cnt
+// every output column of one group-by in one launch: the key-null word is read once per row and the validity bits of the columns
+// that share a mask word leave as one reduction.  mode 0: key copy (valid = !keynull bit); 1: accumulator copy, always valid;
+// 2: accumulator copy, valid iff cnt > 0; 3: average = sum / cnt
+#define FIN_MAX 16
+struct FinJobs {
+    int n;
+    int mode[FIN_MAX], keybit[FIN_MAX], width[FIN_MAX], vbit[FIN_MAX];
+    const unsigned long long* a[FIN_MAX]; const unsigned long long* cnt[FIN_MAX]; void* out[FIN_MAX];
+};
+__global__ void __launch_bounds__(256) k_finalize_multi(const __grid_constant__ FinJobs J, const unsigned long long* __restrict__ keynull, long long n, uint32_t* __restrict__ vmask32) {
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
-        bool valid = true; unsigned long long v = a ? a[i] : 0;
-        if (mode == 0) valid = !((keynull[i] >> keybit) & 1ull);
-        else if (mode == 2) valid = cnt[i] > 0;
-        else if (mode == 3) { valid = cnt[i] > 0; double s = __longlong_as_double((long long)v); v = valid ? (unsigned long long)__double_as_longlong(s / (double)cnt[i]) : 0ull; }
-        if (!valid) v = 0;
-        if (out_width == 4) reinterpret_cast<int32_t*>(out)[i] = (int32_t)v; else reinterpret_cast<unsigned long long*>(out)[i] = v;
-        if (valid) atomicOr(&vmask32[i], 1u << vbit);
+        const unsigned long long kn = keynull[i];
+        uint32_t bits = 0;
+#pragma unroll
+        for (int j = 0; j < FIN_MAX; j++) {
+            if (j >= J.n) break;
+            bool valid = true; unsigned long long v = J.a[j] ? J.a[j][i] : 0;
+            const int mode = J.mode[j];
+            if (mode == 0) valid = !((kn >> J.keybit[j]) & 1ull);
+            else if (mode == 2) valid = J.cnt[j][i] > 0;
+            else if (mode == 3) { const unsigned long long c = J.cnt[j][i]; valid = c > 0; double s = __longlong_as_double((long long)v); v = valid ? (unsigned long long)__double_as_longlong(s / (double)c) : 0ull; }
+            if (!valid) v = 0;
+            if (J.width[j] == 4) reinterpret_cast<int32_t*>(J.out[j])[i] = (int32_t)v; else reinterpret_cast<unsigned long long*>(J.out[j])[i] = v;
+            if (valid) bits |= 1u << J.vbit[j];
+        }
+        if (bits) atomicOr(&vmask32[i], bits);
     }
 }
 
@@ -1652,14 +1666,23 @@ struct Exec {
 
         auto t = std::make_shared<DxTable>(); t->ctx = ctx; t->n_rows = n_out;
         MaskAlloc masks(ctx, n_out);
+        FinJobs fin; fin.n = 0; uint32_t* fin_mask = nullptr; std::vector<DevBufP> fin_keep;
+        auto flush_fin = [&]() {
+            if (!fin.n) return;
+            k_finalize_multi<<<(unsigned)std::min<long long>((n_out + 255) / 256, (long long)ctx->sm_count * 8), 256, 0, ctx->stream>>>(fin, knull->as<unsigned long long>(), n_out, fin_mask);
+            ctx->launches["k_finalize"]++;
+            fin.n = 0; fin_mask = nullptr;
+        };
         auto finalize = [&](int mode, const unsigned long long* a, const unsigned long long* cnt, int keybit, DxColumn* oc, int index) -> int {
             int w = dx_type_width(oc->type);
             oc->data = make_buf(ctx, (size_t)(n_out > 0 ? n_out : 1) * w);
             int rc = masks.assign(oc, index); if (rc) return rc;
             if (n_out > 0) {
-                k_finalize<<<(unsigned)std::min<long long>((n_out + 255) / 256, 8192), 256, 0, ctx->stream>>>(mode, a, cnt, knull->as<unsigned long long>(), keybit, n_out,
-                    oc->data->p, w, oc->vmask->as<uint32_t>(), oc->vbit);
-                ctx->launches["k_finalize"]++;
+                uint32_t* m = oc->vmask->as<uint32_t>();
+                if (fin.n == FIN_MAX || (fin.n && fin_mask != m)) flush_fin();
+                const int j = fin.n++;
+                fin_mask = m; fin_keep.push_back(oc->data); fin_keep.push_back(oc->vmask);
+                fin.mode[j] = mode; fin.keybit[j] = keybit; fin.width[j] = w; fin.vbit[j] = oc->vbit; fin.a[j] = a; fin.cnt[j] = cnt; fin.out[j] = oc->data->p;
             }
             return DX_OK;
         };
@@ -1692,6 +1715,7 @@ struct Exec {
             if (rc) return rc;
             t->cols.push_back(oc);
         }
+        flush_fin();
         // DISTINCT / GROUP BY over MAP/STRUCT leaves keeps their shaping
         for (size_t i = 0; i < items.size() && i < t->cols.size(); i++) {
             DxColumn& oc = t->cols[i]; oc.nest_path.clear(); oc.nest_kinds.clear();
