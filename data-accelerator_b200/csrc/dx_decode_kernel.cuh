@@ -180,7 +180,7 @@ __global__ void __launch_bounds__(K1_NT, FRAMED ? K1_MIN_CTAS_FRAMED : K1_MIN_CT
             // counts (for the row numbers), so a tile costs two CTA barriers between load and parse instead of a CTA-wide scan,
             // prefix sum and record redistribution.
             // Scan: newlines are sparse (one per ~150 bytes), so a lane first only decides whether its 16 bytes hold ANY 0x0A
-            // (three instructions per word, exact as a yes / no); the chunks that do are listed in shared memory by ballot rank,
+            // (one subtraction per word; never a miss, rarely a false alarm); the chunks that do are listed in shared memory by ballot rank,
             // and the exact per-byte masks, the data-bounds masking of a batch's first and last tile and the prefix sums run once
             // per slice over that list with every lane busy, not once per round with three lanes busy.
             constexpr int NWARP = K1_NT / 32;
@@ -196,8 +196,9 @@ __global__ void __launch_bounds__(K1_NT, FRAMED ? K1_MIN_CTAS_FRAMED : K1_MIN_CT
             for (int r = 0; r < ROUNDS; r++) {
                 const int chunk = warp * LCAP + r * 32 + lane;
                 const uint4 v = *reinterpret_cast<const uint4*>(buf + chunk * 16);
-                const uint32_t x0 = v.x ^ 0x0A0A0A0Au, x1 = v.y ^ 0x0A0A0A0Au, x2 = v.z ^ 0x0A0A0A0Au, x3 = v.w ^ 0x0A0A0A0Au;
-                const uint32_t z = (((x0 - 0x01010101u) & ~x0) | ((x1 - 0x01010101u) & ~x1) | ((x2 - 0x01010101u) & ~x2) | ((x3 - 0x01010101u) & ~x3)) & 0x80808080u;
+                // "may hold a newline": a byte below 0x10 borrows and leaves its top bit set whatever the borrow coming in, so a newline is
+                // never missed; bytes from 0x90 up (UTF-8 tails) and tabs also flag their chunk, which only costs them the exact mask below
+                const uint32_t z = ((v.x - 0x10101010u) | (v.y - 0x10101010u) | (v.z - 0x10101010u) | (v.w - 0x10101010u)) & 0x80808080u;
                 const uint32_t bal = __ballot_sync(0xffffffffu, z != 0);
                 if (z) w_list[n_list + __popc(bal & lt_mask)] = (uint16_t)chunk;
                 n_list += __popc(bal);
