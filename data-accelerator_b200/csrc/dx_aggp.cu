@@ -94,8 +94,12 @@ __global__ void __launch_bounds__(256) k3p_scatter(const __grid_constant__ AggIn
 // records into a shared-memory staging area (row-major) and claims their slots with independent atomics, and after a barrier
 // the whole CTA copies the staged words out, consecutive lanes writing consecutive words of the same record: a store
 // instruction then covers ~5 records (5-6 sectors) instead of 32, with 16-byte stores when the record length allows.
+#ifndef SC_NT
 #define SC_NT 256
-#define SC_RPT 4
+#endif
+#ifndef SC_RPT
+#define SC_RPT 2
+#endif
 #define SC_TILE (SC_NT * SC_RPT)
 #define SC_MAXK 4
 #define SC_MAXV 4

@@ -153,8 +153,12 @@ __global__ void __launch_bounds__(256) k5_scatter_put_staged(const __grid_consta
 // with consecutive lanes writing consecutive 8-byte words: every owner receives one contiguous run per tile (128 records =
 // 5 KB at 8 owners), so the stores that cross NVLink are full lines instead of the per-warp fragments of a few records the
 // warp-staged kernel above produces, and the source columns are read four rows per thread with the loads in flight together.
+#ifndef PT_NT
 #define PT_NT 256
-#define PT_RPT 4
+#endif
+#ifndef PT_RPT
+#define PT_RPT 2
+#endif
 #define PT_TILE (PT_NT * PT_RPT)
 __global__ void __launch_bounds__(PT_NT) k5_put_tiled(const __grid_constant__ ShuffleArgs a, const __grid_constant__ PutTargets tg, unsigned long long* cursor) {
     extern __shared__ __align__(16) unsigned long long pt_stage[];       // PT_TILE x rec_words words, then PT_TILE destination pointers
