@@ -261,6 +261,7 @@ struct Printer {
                     parens_since_select--;
                     if (parens_since_select < 0) {
                         indent--;
+                        if (saved_parens.empty()) throw std::runtime_error("formatter: ')' without a matching '(' (the reference's formatter fails on its empty stack here)");
                         parens_since_select = saved_parens.back(); saved_parens.pop_back();
                         after_list_kw = saved_after.back(); saved_after.pop_back();
                     }

@@ -114,3 +114,15 @@ def test_home_automation_flow_json_to_transform():
                 else:
                     assert sorted(map(repr, zip(ca[2].tolist() if ca[2] is not None else [None] * a.n, ca[3].tolist()))) == \
                            sorted(map(repr, zip(cb[2].tolist() if cb[2] is not None else [None] * bt.n, cb[3].tolist()))), (name, ca[0])
+
+
+def test_unbalanced_parenthesis_in_user_code_is_an_error_not_a_crash():
+    # the reference's formatter pops an empty stack here and throws; so does this one (found by mutating the goldens' user code)
+    from importlib import import_module
+    L = import_module("data-accelerator_b200._native").lib()
+    out, info = C.create_string_buffer(1 << 16), C.create_string_buffer(1 << 12)
+    L.dx_codegen_rules.restype = C.c_int
+    L.dx_codegen_rules.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_int64, C.c_char_p, C.c_int64]
+    rc = L.dx_codegen_rules(b"T1 = ProcessRulesoo);(Foo);", read("Rules.json").encode(), read("QueryTemplates.xml").encode(),
+                            read("OutputTemplates.xml").encode(), b"P1", out, len(out), info, len(info))
+    assert rc != 0 and b"formatter" in out.value
