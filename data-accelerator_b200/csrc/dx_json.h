@@ -22,7 +22,8 @@ struct JVal {
 };
 
 class JParser {
-    const char* p; const char* e;
+    const char* p; const char* e; int depth = 0;
+    struct Nest { int& d; explicit Nest(int& x) : d(x) { d++; } ~Nest() { d--; } };
     void ws() { while (p < e && (*p == ' ' || *p == '\t' || *p == '\n' || *p == '\r')) p++; }
     [[noreturn]] void fail(const char* m) { throw std::runtime_error(std::string("schema JSON: ") + m); }
     std::string str() {
@@ -59,6 +60,8 @@ public:
         ws();
         if (p >= e) fail("unexpected end");
         JVal v;
+        Nest nest(depth);
+        if (depth > 512) fail("nested deeper than 512 levels");
         if (*p == '{') {
             v.kind = JVal::OBJ; p++; ws();
             if (p < e && *p == '}') { p++; return v; }

@@ -33,7 +33,10 @@ struct Expr {
     bool distinct = false;            // COUNT(DISTINCT x)
     bool star_arg = false;            // COUNT(*)
     std::string alias;                // STRUCT(x AS name): alias on a function argument
+    int depth = 1;                    // height of the tree below (the parser refuses more than DX_SQL_MAX_DEPTH: its consumers recurse)
 };
+#define DX_SQL_MAX_DEPTH 1000
+#define DX_SQL_MAX_NESTING 256
 
 struct SelectItem { ExprP expr; std::string alias; };
 struct JoinClause { std::string table, alias; ExprP on; bool left_outer = false; };
@@ -126,8 +129,18 @@ class Parser {
         return false;
     }
     static ExprP mk(EK k) { auto e = std::make_shared<Expr>(); e->kind = k; return e; }
+    // called once the operands are in place
+    static ExprP fin(ExprP e) {
+        int d = 0; for (auto& a : e->args) if (a && a->depth > d) d = a->depth;
+        e->depth = d + 1;
+        if (e->depth > DX_SQL_MAX_DEPTH) throw SqlError("expression deeper than " + std::to_string(DX_SQL_MAX_DEPTH) + " levels");
+        return e;
+    }
+    int nesting = 0;
+    struct Nest { int& n; explicit Nest(int& x) : n(x) { if (++n > DX_SQL_MAX_NESTING) { --n; throw SqlError("expression nested deeper than " + std::to_string(DX_SQL_MAX_NESTING) + " levels"); } } ~Nest() { --n; } };
 
     ExprP primary() {
+        Nest nest(nesting);
         const Tok& t = peek();
         if (t.t == Tok::Num) {
             take();
@@ -141,7 +154,7 @@ class Parser {
         if (t.t == Tok::Str) { take(); auto e = mk(EK::Str); e->sval = t.s; return e; }
         if (t.t == Tok::Op && t.s == "(") { take(); ExprP e = expr(); expect_op(")"); return e; }
         if (t.t == Tok::Op && t.s == "*") { take(); return mk(EK::Star); }
-        if (t.t == Tok::Op && t.s == "-") { take(); auto e = mk(EK::Neg); e->args.push_back(unary()); return e; }
+        if (t.t == Tok::Op && t.s == "-") { take(); auto e = mk(EK::Neg); e->args.push_back(unary()); return fin(e); }
         if (t.t == Tok::Op && t.s == "+") { take(); return unary(); }
         if (t.t == Tok::Id || t.t == Tok::QId) {
             std::string u = upper(t.s);
@@ -157,14 +170,14 @@ class Parser {
                     std::vector<std::pair<ExprP, ExprP>> arms;
                     while (accept_kw("WHEN")) {
                         ExprP c = expr();
-                        if (subject) { auto eq = mk(EK::Bin); eq->sval = "="; eq->args = {subject, c}; c = eq; }
+                        if (subject) { auto eq = mk(EK::Bin); eq->sval = "="; eq->args = {subject, c}; c = fin(eq); }
                         expect_kw("THEN");
                         arms.emplace_back(c, expr());
                     }
                     if (arms.empty()) throw SqlError("CASE without WHEN");
                     ExprP tail = accept_kw("ELSE") ? expr() : mk(EK::Null);
                     expect_kw("END");
-                    for (size_t i = arms.size(); i-- > 0;) { auto f = mk(EK::Func); f->sval = "IF"; f->args = {arms[i].first, arms[i].second, tail}; tail = f; }
+                    for (size_t i = arms.size(); i-- > 0;) { auto f = mk(EK::Func); f->sval = "IF"; f->args = {arms[i].first, arms[i].second, tail}; tail = fin(f); }
                     return tail;
                 }
                 if (u == "CAST" && is_op("(", 1)) {
@@ -175,7 +188,7 @@ class Parser {
                     e->sval = lower(ty.s);
                     if (accept_op("(")) { while (!is_op(")") && peek().t != Tok::End) take(); expect_op(")"); }
                     expect_op(")");
-                    return e;
+                    return fin(e);
                 }
                 if (is_op("(", 1) && !reserved(u)) {
                     take(); take();
@@ -186,7 +199,7 @@ class Parser {
                         else { e->args.push_back(arg()); while (accept_op(",")) e->args.push_back(arg()); }
                     }
                     expect_op(")");
-                    return e;
+                    return fin(e);
                 }
                 if (reserved(u)) throw SqlError("unexpected keyword '" + t.s + "'");
             }
@@ -212,12 +225,12 @@ class Parser {
     ExprP unary() { return primary(); }
     ExprP mul() {
         ExprP l = unary();
-        while (is_op("*") || is_op("/") || is_op("%")) { auto e = mk(EK::Bin); e->sval = take().s; e->args = {l, unary()}; l = e; }
+        while (is_op("*") || is_op("/") || is_op("%")) { auto e = mk(EK::Bin); e->sval = take().s; e->args = {l, unary()}; l = fin(e); }
         return l;
     }
     ExprP add() {
         ExprP l = mul();
-        while (is_op("+") || is_op("-") || is_op("||")) { auto e = mk(EK::Bin); e->sval = take().s; e->args = {l, mul()}; l = e; }
+        while (is_op("+") || is_op("-") || is_op("||")) { auto e = mk(EK::Bin); e->sval = take().s; e->args = {l, mul()}; l = fin(e); }
         return l;
     }
     ExprP cmp() {
@@ -225,7 +238,7 @@ class Parser {
         for (;;) {
             if (is_op("=") || is_op("==") || is_op("<>") || is_op("!=") || is_op("<") || is_op("<=") || is_op(">") || is_op(">=")) {
                 std::string op = take().s; if (op == "==") op = "="; if (op == "!=") op = "<>";
-                auto e = mk(EK::Bin); e->sval = op; e->args = {l, add()}; l = e; continue;
+                auto e = mk(EK::Bin); e->sval = op; e->args = {l, add()}; l = fin(e); continue;
             }
             bool neg = false; size_t save = p;
             if (is_kw("NOT") && (is_kw("IN", 1) || is_kw("BETWEEN", 1) || is_kw("LIKE", 1))) { take(); neg = true; }
@@ -233,33 +246,33 @@ class Parser {
                 expect_op("(");
                 auto e = mk(EK::In); e->negated = neg; e->args.push_back(l);
                 e->args.push_back(expr()); while (accept_op(",")) e->args.push_back(expr());
-                expect_op(")"); l = e; continue;
+                expect_op(")"); l = fin(e); continue;
             }
             if (accept_kw("BETWEEN")) {
                 auto e = mk(EK::Between); e->negated = neg; e->args.push_back(l);
-                e->args.push_back(add()); expect_kw("AND"); e->args.push_back(add()); l = e; continue;
+                e->args.push_back(add()); expect_kw("AND"); e->args.push_back(add()); l = fin(e); continue;
             }
-            if (accept_kw("LIKE")) { auto e = mk(EK::Like); e->negated = neg; e->args = {l, add()}; l = e; continue; }
+            if (accept_kw("LIKE")) { auto e = mk(EK::Like); e->negated = neg; e->args = {l, add()}; l = fin(e); continue; }
             if (is_kw("IS")) {
                 take(); bool n = accept_kw("NOT"); expect_kw("NULL");
-                auto e = mk(EK::IsNull); e->negated = n; e->args.push_back(l); l = e; continue;
+                auto e = mk(EK::IsNull); e->negated = n; e->args.push_back(l); l = fin(e); continue;
             }
             p = save;
             return l;
         }
     }
     ExprP not_() {
-        if (is_kw("NOT")) { take(); auto e = mk(EK::Not); e->args.push_back(not_()); return e; }
+        if (is_kw("NOT")) { Nest nest(nesting); take(); auto e = mk(EK::Not); e->args.push_back(not_()); return fin(e); }
         return cmp();
     }
     ExprP and_() {
         ExprP l = not_();
-        while (is_kw("AND")) { take(); auto e = mk(EK::Bin); e->sval = "AND"; e->args = {l, not_()}; l = e; }
+        while (is_kw("AND")) { take(); auto e = mk(EK::Bin); e->sval = "AND"; e->args = {l, not_()}; l = fin(e); }
         return l;
     }
     ExprP or_() {
         ExprP l = and_();
-        while (is_kw("OR")) { take(); auto e = mk(EK::Bin); e->sval = "OR"; e->args = {l, and_()}; l = e; }
+        while (is_kw("OR")) { take(); auto e = mk(EK::Bin); e->sval = "OR"; e->args = {l, and_()}; l = fin(e); }
         return l;
     }
     std::string alias_opt() {

@@ -126,3 +126,13 @@ def test_unbalanced_parenthesis_in_user_code_is_an_error_not_a_crash():
     rc = L.dx_codegen_rules(b"T1 = ProcessRulesoo);(Foo);", read("Rules.json").encode(), read("QueryTemplates.xml").encode(),
                             read("OutputTemplates.xml").encode(), b"P1", out, len(out), info, len(info))
     assert rc != 0 and b"formatter" in out.value
+
+
+def test_runaway_json_nesting_is_an_error_not_a_stack_overflow():
+    from importlib import import_module
+    L = import_module("data-accelerator_b200._native").lib()
+    out, info = C.create_string_buffer(1 << 16), C.create_string_buffer(1 << 12)
+    L.dx_codegen_rules.restype = C.c_int
+    L.dx_codegen_rules.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_int64, C.c_char_p, C.c_int64]
+    rc = L.dx_codegen_rules(b"x", b"[" * 200000 + b"]" * 200000, b"<a/>", b"<a/>", b"P1", out, len(out), info, len(info))
+    assert rc != 0 and b"nested deeper" in out.value

@@ -91,3 +91,16 @@ def test_parses_every_generated_statement_of_the_reference_goldens(dx):
             dx.sql_canonical(sql)
             n += 1
     assert n > 200
+
+
+def test_sql_parser_refuses_runaway_nesting_with_a_message(dx):
+    # the parser and everything that walks its trees recurse: depth is bounded at parse time (a stack overflow would take the host down)
+    assert dx.sql_canonical("SELECT " + "(" * 200 + "1" + ")" * 200 + " AS x FROM t") == "SELECT 1 AS x FROM t"
+    dx.sql_canonical("SELECT a FROM t WHERE " + " AND ".join(["a > 1"] * 900))
+    for sql in ("SELECT " + "(" * 100000 + "1" + ")" * 100000 + " AS x FROM t",
+                "SELECT a FROM t WHERE " + "NOT " * 100000 + "a",
+                "SELECT " + "-" * 100000 + "1 AS x FROM t",
+                "SELECT a FROM t WHERE " + " AND ".join(["a > 1"] * 100000),
+                "SELECT " + " + ".join(["a"] * 100000) + " AS x FROM t"):
+        with pytest.raises(dx.DxError, match="deeper than"):
+            dx.sql_canonical(sql)
