@@ -74,29 +74,39 @@ static __device__ __forceinline__ bool fast_record_warp(const uint8_t* buf, uint
         __syncwarp();
         const DSeg sg = a.segs[si];                      // warp-uniform: constant-bank loads
         {
-            // literal: a straight line of word compares entered at the literal's length (fall-through switch), each word two
-            // shared loads, a funnel shift and an XOR against a constant-bank operand; the last word goes under its mask.
+            // literal: a straight line of word compares entered at the literal's length (fall-through switch), each word one
+            // shared load, a funnel shift and an XOR against a constant-bank operand; the last word goes under its mask.
             // Every lane runs the compare, lanes that already failed on the tile's first bytes: the dispatch is then
             // warp-uniform and the literal words are uniform operands instead of per-lane indexed loads.
             const uint32_t p0 = ok ? pos : 0u, sh = (p0 & 3u) << 3;
             const uint32_t* wp = reinterpret_cast<const uint32_t*>(buf + (p0 & ~3u));
-            const uint32_t* lp = a.lits + sg.lit_word;
+            // the literal words are read as a.lits[index]: indexing the parameter block keeps them constant-bank loads (a pointer
+            // into it that is advanced in a loop turns into generic global loads, one round of memory latency per segment)
+            int li = (int)sg.lit_word;       // signed: the +i folds into the load's immediate offset
             uint32_t nf = sg.n_words - 1u, diff = 0;
-#define DX_LIT_WORD(i) diff |= __funnelshift_r(wp[i], wp[(i) + 1], sh) ^ lp[i];
-            while (nf > 8u) { DX_LIT_WORD(0) DX_LIT_WORD(1) DX_LIT_WORD(2) DX_LIT_WORD(3) DX_LIT_WORD(4) DX_LIT_WORD(5) DX_LIT_WORD(6) DX_LIT_WORD(7) wp += 8; lp += 8; nf -= 8u; }
-            diff |= (__funnelshift_r(wp[nf], wp[nf + 1u], sh) ^ lp[nf]) & sg.last_mask;
+#define DX_LIT_WORD(i) diff |= __funnelshift_r(wp[i], wp[(i) + 1], sh) ^ a.lits[li + (i)];
+#pragma unroll 1
+            while (nf > 8u) { DX_LIT_WORD(0) DX_LIT_WORD(1) DX_LIT_WORD(2) DX_LIT_WORD(3) DX_LIT_WORD(4) DX_LIT_WORD(5) DX_LIT_WORD(6) DX_LIT_WORD(7) wp += 8; li += 8; nf -= 8u; }
+#undef DX_LIT_WORD
+            // from the last word down, each step's low data word is the next step's high one: one shared load per literal word
+            // (two registers swap the roles from case to case, so the fall-through needs no copy between the steps)
+            uint32_t wa = wp[nf], wb = wa;
+            diff |= (__funnelshift_r(wa, wp[nf + 1u], sh) ^ a.lits[li + (int)nf]) & sg.last_mask;
+#define DX_LIT_EVEN(i) wb = wp[i]; diff |= __funnelshift_r(wb, wa, sh) ^ a.lits[li + (i)];     /* entered with nf even: high word in wa */
+#define DX_LIT_ODD(i)  wa = wp[i]; diff |= __funnelshift_r(wa, wb, sh) ^ a.lits[li + (i)];     /* entered with nf odd: high word in wb */
             switch (nf) {
-            case 8: DX_LIT_WORD(7)
-            case 7: DX_LIT_WORD(6)
-            case 6: DX_LIT_WORD(5)
-            case 5: DX_LIT_WORD(4)
-            case 4: DX_LIT_WORD(3)
-            case 3: DX_LIT_WORD(2)
-            case 2: DX_LIT_WORD(1)
-            case 1: DX_LIT_WORD(0)
+            case 8: DX_LIT_EVEN(7)
+            case 7: DX_LIT_ODD(6)
+            case 6: DX_LIT_EVEN(5)
+            case 5: DX_LIT_ODD(4)
+            case 4: DX_LIT_EVEN(3)
+            case 3: DX_LIT_ODD(2)
+            case 2: DX_LIT_EVEN(1)
+            case 1: DX_LIT_ODD(0)
             default: break;
             }
-#undef DX_LIT_WORD
+#undef DX_LIT_EVEN
+#undef DX_LIT_ODD
             ok = ok && diff == 0;
             pos += sg.lit_len;
         }
