@@ -421,11 +421,12 @@ __global__ void __launch_bounds__(K1_NT, FRAMED ? K1_MIN_CTAS_FRAMED : K1_MIN_CT
                 }
             }
         }
+        // the next tile is claimed by thread 0 on its way into the barrier that ends this tile (every thread copied s_tile into a
+        // register two barriers ago): the atomic's round trip overlaps the other warps' last records and the tile costs one barrier less
+        if (K1_STAGES == 1 && tid == 0) s_tile = (long long)atomicAdd(a.tile_counter, 1u);
         __syncthreads();
         if (K1_STAGES > 1) { tile = next_tile; slot ^= 1; }
         else {
-            if (tid == 0) s_tile = (long long)atomicAdd(a.tile_counter, 1u);
-            __syncthreads();
             tile = s_tile;
             if (tile < a.n_tiles) stage_tile(0, tile);
         }
