@@ -1,6 +1,6 @@
 """The oracle's SQL loop against an engine nobody here wrote: the same statements, over the same rows, in SQLite (python's sqlite3).
 SQLite follows the SQL standard where Spark 2.4 does on everything exercised here — three-valued AND / OR / NOT, comparisons with
-NULL, IN / NOT IN / BETWEEN with NULLs, IS [NOT] NULL, CASE WHEN, NULL-skipping COUNT / SUM / MIN / MAX / AVG, SUM over no rows = NULL,
+NULL, IN / NOT IN / BETWEEN with NULLs, IS [NOT] NULL, LIKE / NOT LIKE (case-sensitive), CASE WHEN, NULL-skipping COUNT / SUM / MIN / MAX / AVG, SUM over no rows = NULL,
 NULL keys forming one group, HAVING, DISTINCT and UNION treating NULLs as equal, UNION ALL, INNER / LEFT OUTER equi-joins,
 COUNT(DISTINCT) — so a rule the oracle's author misread shows up as a difference.  Left out on purpose, because the engines differ by
 design: '/' and '%' (Spark divides as double, NULL on zero), NaN, string-to-number coercions, booleans as a column type.
@@ -38,6 +38,9 @@ STATEMENTS = [
     ("F9", "SELECT deviceId FROM DataXProcessedInput WHERE status NOT IN (0, NULL)"),
     ("F10", "SELECT deviceId FROM DataXProcessedInput WHERE temperature > humidity AND NOT (deviceType = 'WindowLock')"),
     ("F11", "SELECT deviceId, homeId + 1 AS h1, deviceId * 2 - homeId AS mix, -status AS neg FROM DataXProcessedInput WHERE homeId * 2 > deviceId - 10"),
+    ("L1", "SELECT deviceId, deviceType FROM DataXProcessedInput WHERE deviceType LIKE 'Door%' OR deviceType LIKE '%eat%' OR deviceType LIKE '_indowLock'"),
+    ("L2", "SELECT deviceId FROM DataXProcessedInput WHERE deviceType NOT LIKE '%Lock' AND status = 1"),
+    ("L3", "SELECT deviceId FROM DataXProcessedInput WHERE deviceType LIKE 'door%' OR deviceType LIKE 'Heating_' OR deviceType = 'heating'"),
     ("C1", "SELECT deviceId, CASE WHEN status = 1 THEN 'on' WHEN status = 0 THEN 'off' ELSE 'unknown' END AS state, "
            "CASE WHEN temperature > 80 THEN 2 WHEN temperature > 50 THEN 1 END AS level FROM DataXProcessedInput"),
     ("G1", "SELECT homeId, COUNT(*) AS n, COUNT(status) AS ns, SUM(status) AS s, MIN(deviceId) AS mn, MAX(deviceId) AS mx, AVG(deviceId) AS av "
@@ -84,6 +87,7 @@ def transform_text():
 
 def sqlite_results(rows):
     db = sqlite3.connect(":memory:")
+    db.execute("PRAGMA case_sensitive_like = ON")            # Spark's LIKE compares bytes
     db.execute("CREATE TABLE DataXProcessedInput (deviceId INTEGER, deviceType TEXT, homeId INTEGER, status INTEGER, temperature REAL, humidity REAL)")
     db.executemany("INSERT INTO DataXProcessedInput VALUES (?,?,?,?,?,?)", rows)
     out = {}
